@@ -1,0 +1,240 @@
+/*
+ * pilosa_b200.h — C ABI of libpilosa_b200.so, the B200 (sm_100a) execution engine for
+ * Pilosa's per-shard bitmap query hot path.
+ *
+ * The reference (travisturner/pilosa) is pure Go and has no FFI for this path; the
+ * boundary below is what a cgo shim placed behind the reference's own call surface
+ * binds (see INTEGRATION.md for the shim). Each entry point cites the reference
+ * function(s) it replaces, as file:line in the reference tree.
+ *
+ * Conventions
+ *  - every function returns an int status: 0 = OK, <0 = error; pb200_strerror(status)
+ *    gives a static message and pb200_last_error(ctx) the detailed text of the last
+ *    failure on that context (Go side: turn into `error`; never a crash/longjmp).
+ *  - all integers are fixed width, little endian; all buffers are caller allocated.
+ *  - the library never retains a host pointer after a call returns (cgo pointer rule;
+ *    reference containers may alias an mmap that is unmapped at the next snapshot,
+ *    fragment.go:394-431).
+ *  - a context is bound to ONE CUDA device. Calls on the same context are serialised
+ *    by an internal mutex (the reference serialises per fragment, fragment.go:601);
+ *    use one context per GPU and batch entry points for throughput.
+ *  - there is NO CPU fallback: if no CUDA device is usable pb200_init fails with
+ *    PB200_ERR_CUDA and nothing else can be called.
+ */
+#ifndef PILOSA_B200_H
+#define PILOSA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PB200_ABI_VERSION 1
+
+/* ShardWidth = 2^20 columns (shardwidth/20.go, fragment.go:53): 16 containers per row. */
+#define PB200_SHARD_WIDTH_EXP 20
+#define PB200_SHARD_WIDTH (1ull << PB200_SHARD_WIDTH_EXP)
+#define PB200_ROW_CONTAINERS 16
+
+/* status codes */
+#define PB200_OK 0
+#define PB200_ERR_INVALID (-1)   /* bad argument / malformed expression            */
+#define PB200_ERR_CUDA (-2)      /* CUDA runtime error (text in pb200_last_error)   */
+#define PB200_ERR_FORMAT (-3)    /* malformed Pilosa roaring bytes                  */
+#define PB200_ERR_NOMEM (-4)     /* HBM budget exhausted                            */
+#define PB200_ERR_NOTFOUND (-5)  /* unknown family / fragment                       */
+#define PB200_ERR_RANGE (-6)     /* caller buffer too small / size limit exceeded   */
+#define PB200_ERR_UNSUPPORTED (-7)
+
+typedef struct pb200_ctx pb200_ctx;
+
+/* A "family" is one (index, field, view) triple: the set of fragments, one per shard,
+ * that holder.go:496-502 Holder.fragment(index, field, view, shard) would return. */
+typedef uint32_t pb200_family;
+
+/* ---- expression programs ------------------------------------------------------------
+ * A bitmap call tree (executor.go:654-680 executeBitmapCallShard) is passed flattened in
+ * post order. N-ary nodes consume their `nargs` operands from the evaluation stack and
+ * combine them as a LEFT FOLD in PQL order, exactly like executor.go:1668-1733,1003-1025.
+ */
+enum pb200_op {
+  PB200_OP_ROW = 1,        /* Row(f=row): fragment.row, fragment.go:600-641; executor.go:1444-1499 */
+  PB200_OP_INTERSECT = 2,  /* executeIntersectShard executor.go:1668; Row.Intersect row.go:107     */
+  PB200_OP_UNION = 3,      /* executeUnionShard executor.go:1693; Row.Union row.go:153             */
+  PB200_OP_DIFFERENCE = 4, /* executeDifferenceShard executor.go:1003; Row.Difference row.go:198   */
+  PB200_OP_XOR = 5,        /* executeXorShard executor.go:1715; Row.Xor row.go:133                 */
+  PB200_OP_NOT = 6,        /* executeNotShard executor.go:1737-1768: family = existence field,
+                              row = 0, one operand: exists.row(0) \ operand                         */
+  PB200_OP_SHIFT = 7,      /* executeShiftShard executor.go:1771; Bitmap.Shift roaring.go:944 (n=1)*/
+  PB200_OP_BSI_RANGE = 8,  /* fragment.rangeOp / rangeBetween / notNull fragment.go:1271-1534      */
+  PB200_OP_EMPTY = 9       /* NewRow(): used by hosts for out-of-range BSI predicates
+                              (executor.go:1611,1641) and Union()/Xor() with no children           */
+};
+
+enum pb200_bsi_op {        /* pql/token.go:22-31 */
+  PB200_BSI_EQ = 1, PB200_BSI_NEQ = 2, PB200_BSI_LT = 3, PB200_BSI_LTE = 4,
+  PB200_BSI_GT = 5, PB200_BSI_GTE = 6, PB200_BSI_BETWEEN = 7, PB200_BSI_NOTNULL = 8
+};
+
+typedef struct pb200_node {
+  uint32_t op;         /* enum pb200_op                                                    */
+  uint32_t family;     /* ROW / NOT / BSI_RANGE: family handle                             */
+  uint64_t row;        /* ROW: row id                                                      */
+  uint32_t nargs;      /* INTERSECT/UNION/DIFFERENCE/XOR: operand count (>=1; UNION/XOR >=0)*/
+  uint32_t bsi_op;     /* BSI_RANGE: enum pb200_bsi_op                                     */
+  uint32_t bit_depth;  /* BSI_RANGE: bsiGroup.BitDepth (field.go:1505-1512)                */
+  uint32_t reserved;
+  int64_t a;           /* BSI_RANGE: predicate (already re-based by the host,
+                          field.go:1526-1567 baseValue / baseValueBetween lo)              */
+  int64_t b;           /* BSI_RANGE BETWEEN: hi predicate                                  */
+} pb200_node;
+
+typedef struct pb200_pair {  /* cache.go:337-341 Pair{ID, Count} */
+  uint64_t id;
+  uint64_t count;
+} pb200_pair;
+
+typedef struct pb200_timing {
+  double kernel_ms;        /* device time of the kernels of the last query call (CUDA events) */
+  double h2d_ms, d2h_ms;   /* copies issued by the last call                                   */
+  uint64_t algo_bytes;     /* algorithmic bytes of the last call: sum of operand container
+                              payloads read once + 16 B descriptor each        */
+  uint64_t h2d_bytes, d2h_bytes;
+  uint32_t launches;       /* kernels launched by the last call                               */
+  uint32_t reserved;
+} pb200_timing;
+
+/* ---- lifecycle ------------------------------------------------------------------------ */
+
+/* Bind a context to CUDA device `device`. hbm_budget_bytes == 0 means "no explicit budget".
+ * Replaces nothing in the reference (there is no device today); called where
+ * server.Open wires the holder (server.go). */
+int pb200_init(int device, size_t hbm_budget_bytes, pb200_ctx** out);
+int pb200_shutdown(pb200_ctx* ctx);
+const char* pb200_strerror(int status);
+const char* pb200_last_error(pb200_ctx* ctx);
+int pb200_abi_version(void);
+
+/* Run the engine's kernels on a caller-owned CUDA stream (a cudaStream_t passed as void*,
+ * e.g. torch.cuda.current_stream().cuda_stream). NULL restores the context's own stream. */
+int pb200_set_stream(pb200_ctx* ctx, void* cuda_stream);
+
+/* ---- fragments (storage objects resident in HBM) --------------------------------------- */
+
+/* holder.go:496-502: create the (index, field, view) handle fragments are filed under. */
+int pb200_family_create(pb200_ctx* ctx, pb200_family* out);
+
+/* Load / replace the fragment of `family` for `shard` from the exact bytes of a Pilosa
+ * fragment file: roaring snapshot + appended ops log, which is replayed
+ * (roaring.go:1562-1653 unmarshalPilosaRoaring; format roaring.go:1044-1122; ops
+ * roaring.go:4459-4559). Go passes its mmap slice (fragment.go:330-401 openStorage).
+ * Container keys must lie in rows of this shard: key = row*16 + (col>>16)
+ * (fragment.go:3078-3081 pos). The bytes are copied; nothing is retained. */
+int pb200_frag_load(pb200_ctx* ctx, pb200_family family, uint64_t shard,
+                    const void* roaring_bytes, size_t len);
+
+/* Write-path coherence: apply set/clear of storage positions (pos = row*2^20 + col%2^20)
+ * to the device copy; hook for fragment.go:680-779 (set/clearBit), :2051 importPositions,
+ * :2243 importRoaring. Clears are applied after sets. */
+int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t shard,
+                     const uint64_t* set_pos, size_t n_set,
+                     const uint64_t* clear_pos, size_t n_clear);
+
+/* fragment.go:574 closeStorage / drop of a fragment. */
+int pb200_frag_drop(pb200_ctx* ctx, pb200_family family, uint64_t shard);
+
+/* The Go rank cache stays authoritative for TopN candidate order (cache.go:136-288
+ * rankCache.Top(), fragment.go:1702-1738 topBitmapPairs): hand the engine the ranked
+ * (row id, cached count) list of one fragment, in rank order. */
+int pb200_rank_set(pb200_ctx* ctx, pb200_family family, uint64_t shard,
+                   const uint64_t* row_ids, const uint64_t* counts, size_t n);
+
+/* Number of rows / containers / payload bytes resident for a fragment (diagnostics). */
+int pb200_frag_stat(pb200_ctx* ctx, pb200_family family, uint64_t shard,
+                    uint64_t* n_rows, uint64_t* n_containers, uint64_t* payload_bytes);
+
+/* ---- queries --------------------------------------------------------------------------- */
+
+/* Count(<bitmap call>) over the given shards: executor.go:1793-1825 executeCount with
+ * mapFn = executeBitmapCallShard(...).Count() and reduceFn = uint64 add, i.e. the whole
+ * executor.go:2576-2611 mapperLocal pass in one call. */
+int pb200_count(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
+                const uint64_t* shards, uint32_t n_shards, uint64_t* out_count);
+
+/* Batch of independent Count queries sharing one shard list. Programs are concatenated
+ * in `progs`; query q occupies nodes [prog_off[q], prog_off[q+1]). out_counts[n_queries]. */
+int pb200_count_batch(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off,
+                      uint32_t n_queries, const uint64_t* shards, uint32_t n_shards,
+                      uint64_t* out_counts);
+
+/* Same as pb200_count but also returns per-shard counts (the mapFn results before the
+ * reduce), out_per_shard[n_shards]; used by hosts that merge across GPUs themselves. */
+int pb200_count_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
+                       const uint64_t* shards, uint32_t n_shards, uint64_t* out_per_shard);
+
+/* Evaluate a bitmap call on ONE shard and return the resulting row segment as Pilosa
+ * roaring bytes (containers optimize()d, keys = shard*16 + i as fragment.go:629
+ * OffsetRange produces). Two-call protocol: with out == NULL only *out_len is written.
+ * Replaces executor.go:654-680 executeBitmapCallShard for bitmap-returning calls. */
+int pb200_eval(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard,
+               void* out, size_t cap, size_t* out_len);
+
+/* Evaluate a bitmap call on one shard into the sorted list of absolute column ids
+ * (row.go:302-327 Row.Columns). Two-call protocol as above (cap in elements). */
+int pb200_eval_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard,
+                       uint64_t* out_cols, size_t cap, size_t* out_n);
+
+/* TopN over the ranked rows of `family`: executor.go:863-1000 executeTopN (both passes and
+ * the Pairs.Add merge, cache.go:356-374) with fragment.top semantics (fragment.go:1568-1700)
+ * per shard. src_prog may be NULL (no Src). ids non-NULL selects the explicit-ids path
+ * (N forced 0, fragment.go:1573). min_threshold 0 means defaultMinThreshold=1
+ * (executor.go:37,984). Attribute filters stay on the host. On return *n_out pairs are
+ * written (sorted by count desc, ties by ascending id); cap is the capacity of `out`. */
+int pb200_topn(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog,
+               uint32_t n_src_nodes, uint32_t n, const uint64_t* ids, size_t n_ids,
+               uint64_t min_threshold, uint64_t tanimoto_threshold, const uint64_t* shards,
+               uint32_t n_shards, pb200_pair* out, size_t cap, size_t* n_out);
+
+/* One shard of TopN, exactly fragment.top (fragment.go:1568-1700): pass-1 style when
+ * ids == NULL, explicit-ids style otherwise. Output order = the reference's heap-pop order. */
+int pb200_topn_shard(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog,
+                     uint32_t n_src_nodes, uint32_t n, const uint64_t* ids, size_t n_ids,
+                     uint64_t min_threshold, uint64_t tanimoto_threshold, uint64_t shard,
+                     pb200_pair* out, size_t cap, size_t* n_out);
+
+/* BSI aggregates over a bsig_ view family (view.go:37). filter_prog may be NULL.
+ * Sum: fragment.sum (fragment.go:1109-1141) per shard + ValCount.add (executor.go:3002);
+ * the caller adds count*Base (executor.go:718). Reproduces the reference quirk that
+ * magnitudes of ALL negative columns are subtracted even outside the filter
+ * (fragment.go:1118,1134) unless PB200_SUM_STRICT is set in flags. */
+#define PB200_SUM_STRICT 1u
+int pb200_bsi_sum(pb200_ctx* ctx, pb200_family bsi_family, uint32_t bit_depth,
+                  const pb200_node* filter_prog, uint32_t n_filter_nodes, uint32_t flags,
+                  const uint64_t* shards, uint32_t n_shards, int64_t* out_sum, uint64_t* out_count);
+
+/* Min / Max: fragment.min/max (fragment.go:1145-1225) per shard, reduced with
+ * ValCount.smaller / larger (executor.go:3010-3029) in ascending shard-list order
+ * ("lowest shard wins ties; counts are not summed" — one legal reference outcome).
+ * Values are un-based: the caller adds Base (executor.go:759,797). */
+int pb200_bsi_min(pb200_ctx* ctx, pb200_family bsi_family, uint32_t bit_depth,
+                  const pb200_node* filter_prog, uint32_t n_filter_nodes,
+                  const uint64_t* shards, uint32_t n_shards, int64_t* out_val, uint64_t* out_count);
+int pb200_bsi_max(pb200_ctx* ctx, pb200_family bsi_family, uint32_t bit_depth,
+                  const pb200_node* filter_prog, uint32_t n_filter_nodes,
+                  const uint64_t* shards, uint32_t n_shards, int64_t* out_val, uint64_t* out_count);
+
+/* Per-shard (value, count) pairs of Min (is_max=0) or Max (is_max=1) before the reduce. */
+int pb200_bsi_minmax_shards(pb200_ctx* ctx, pb200_family bsi_family, uint32_t bit_depth,
+                            const pb200_node* filter_prog, uint32_t n_filter_nodes, int is_max,
+                            const uint64_t* shards, uint32_t n_shards,
+                            int64_t* out_vals, uint64_t* out_counts);
+
+/* Timing / byte accounting of the last query call on this context. */
+int pb200_last_timing(pb200_ctx* ctx, pb200_timing* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PILOSA_B200_H */
