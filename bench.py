@@ -1,0 +1,393 @@
+#!/usr/bin/env python
+"""bench.py — Count(Intersect(Row(f=a), Row(f=b))) throughput of the B200 engine.
+
+Workload (BASELINE.json configs[0] scaled to where HBM bandwidth is measurable, SURVEY.md
+§8d "C1 batched"): index `i`, set field `f`, 16 shards x 2^20 columns PER GPU, R rows of iid
+Bernoulli(0.10) columns (every container is a bitmap container), one step = one batch of B
+distinct random row pairs (a, b), each a Count(Intersect(Row(f=a), Row(f=b))) over all
+shards. Per step every GPU reads B x 16 shards x 16 containers x 2 x 8 KiB = 4 GiB of
+operand payload, far beyond the 126 MB L2, so no L2 flush is needed between steps.
+
+  value   device-resident throughput: prepared batches (programs already in HBM) launched
+          back to back, timed with CUDA events on the launching stream, max over ranks.
+  e2e     the same metric through the C-ABI call with HOST buffers: per step the query
+          programs are copied host->device, the kernel runs and the counts come back
+          device->host (pb200_count_batch_begin/_end), wall clock, max over ranks.
+  N > 1   shards are partitioned over ranks (shard s -> rank s % N, 16 shards per GPU, weak
+          scaling); the only exchange is the all-reduce(sum) of the B per-query counts over
+          NCCL, inside the timed step. `value` counts 16-shard query units: N x B per step.
+
+--impl reference times the CPU restatement of the reference's Go path (oracle/, mode A:
+materialise the intersection, then count — executor.go:1804-1810) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import random
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SHARDS_PER_GPU = 16
+P_DENSITY = 0.10
+SEED = 20190416
+METRIC = "count_intersect_queries_per_sec"
+UNIT = "queries/s"
+SAMPLE_ROWS = 64       # rows the CPU baseline holds (a bounded sample of the same index)
+SAMPLE_QUERIES = 256   # queries per CPU-baseline step
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.idx)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+class DevArray:
+    """Zero-copy view of a device buffer for torch (CUDA array interface)."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i8", "data": (ptr, False), "version": 2}
+
+
+def make_batches(n_batches: int, batch: int, rows: int):
+    rnd = random.Random(SEED)
+    out = []
+    for _ in range(n_batches):
+        seen, pairs = set(), []
+        while len(pairs) < batch:
+            a, b = rnd.randrange(rows), rnd.randrange(rows)
+            if a != b and (a, b) not in seen:
+                seen.add((a, b))
+                pairs.append((a, b))
+        out.append(pairs)
+    return out
+
+
+def pack_pairs(pairs, fam: int):
+    """(flat pb200_node[3B], prog_off[B+1]) for Count(Intersect(Row(a), Row(b))) queries."""
+    from pilosa_b200 import abi
+
+    n = len(pairs)
+    flat = (abi.Node * (3 * n))()
+    off = (C.c_uint32 * (n + 1))()
+    for i, (a, b) in enumerate(pairs):
+        flat[3 * i] = abi.Node(op=abi.OP_ROW, family=fam, row=a)
+        flat[3 * i + 1] = abi.Node(op=abi.OP_ROW, family=fam, row=b)
+        flat[3 * i + 2] = abi.Node(op=abi.OP_INTERSECT, nargs=2)
+        off[i] = 3 * i
+    off[n] = 3 * n
+    return flat, off
+
+
+def sample_queries(rows: int):
+    rnd = random.Random(SEED + 1)
+    srows = sorted(rnd.sample(range(rows), min(SAMPLE_ROWS, rows)))
+    pairs = []
+    while len(pairs) < SAMPLE_QUERIES:
+        a, b = rnd.sample(srows, 2)
+        pairs.append((a, b))
+    return srows, pairs
+
+
+def cpu_leg(shards, rows: int, steps: int, warmup: int, min_seconds: float):
+    """Times the oracle (reference restatement) on the host cores: mode A (materialise then
+    count, what the reference does) and mode B (fused intersectionCount)."""
+    import oracle
+    from pilosa_b200 import synth
+
+    cores = os.cpu_count() or 1
+    orc = oracle.Oracle(workers=cores)
+    fam = orc.family_create()
+    srows, pairs = sample_queries(rows)
+    with ThreadPoolExecutor(max_workers=min(cores, len(shards))) as tp:
+        frs = list(tp.map(lambda s: synth.bernoulli_rows(s, srows, P_DENSITY, SEED), shards))
+    for s, fb in zip(shards, frs):
+        orc.frag_load(fam, s, fb)
+    del frs
+    flat, off = pack_pairs(pairs, fam)
+    progs = [(type(flat[0]) * 3)(flat[3 * i], flat[3 * i + 1], flat[3 * i + 2]) for i in range(len(pairs))]
+
+    def run(fused: bool):
+        return [orc.count(p, shards, fused) for p in progs]
+
+    for _ in range(max(1, warmup)):
+        counts = run(False)
+    t0 = time.perf_counter()
+    n_steps = 0
+    while n_steps < steps or (time.perf_counter() - t0) < min_seconds:
+        run(False)
+        n_steps += 1
+        if n_steps >= steps and min_seconds <= 0:
+            break
+    dt_a = time.perf_counter() - t0
+    t1 = time.perf_counter()
+    for _ in range(max(1, n_steps // 2)):
+        run(True)
+    dt_b = time.perf_counter() - t1
+    qa = n_steps * len(pairs) / dt_a
+    qb = max(1, n_steps // 2) * len(pairs) / dt_b
+    return {"value": qa, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{len(pairs)} queries/step over {len(srows)} of the {rows} rows x {len(shards)} shards, {n_steps} steps, "
+                      f"mode A (materialise then count, executor.go:1804); worker pool = {cores} threads",
+            "fused_intersection_count_value": qb, "seconds": dt_a}, pairs, counts
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    shards = list(range(SHARDS_PER_GPU))
+    cpu, pairs, _ = cpu_leg(shards, args.rows, args.steps, args.warmup, 0.0)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * len(pairs) / cpu["value"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": workload_config(args, 1) | {"reference_arm": "CPU restatement of the reference's Go path (oracle/, Go toolchain unavailable); "
+                                                               "each step = a bounded sample of the batch"},
+        "cpu_baseline": cpu,
+        "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world):
+    return {
+        "workload": f"C1 batched: Count(Intersect(Row(f=a),Row(f=b))), {SHARDS_PER_GPU} shards x 2^20 cols per GPU, 10% random density "
+                    f"(all bitmap containers), {args.rows} rows, batch of {args.batch} distinct random row pairs per step",
+        "shards_per_gpu": SHARDS_PER_GPU, "total_shards": SHARDS_PER_GPU * world, "rows": args.rows, "batch": args.batch,
+        "density": P_DENSITY, "seed": SEED, "partition": f"shard s -> rank s % {world}",
+        "l2": "inputs larger than L2 (4 GiB of operands per step per GPU); no flush needed",
+        "value_unit_note": "one unit = one Count(Intersect) over 16 shards (16.8M columns per operand row); a query over the whole "
+                           "N x 16-shard index is N units",
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--rows", type=int, default=int(os.environ.get("PB200_BENCH_ROWS", "4096")))
+    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from pilosa_b200 import synth
+    from pilosa_b200.engine import Engine
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: pilosa_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    stream = torch.cuda.Stream()
+    eng = Engine(local_rank)
+    eng.set_stream(stream.cuda_stream)
+    fam = eng.family_create()
+    shards = [rank + world * i for i in range(SHARDS_PER_GPU)]
+
+    # ---- build + load the index (not timed) ----
+    t_build = time.perf_counter()
+    workers = max(1, min(8, (os.cpu_count() or 8) // max(1, world)))
+    with ThreadPoolExecutor(max_workers=workers) as tp:
+        futs = [tp.submit(synth.bernoulli, s, 0, args.rows, P_DENSITY, SEED) for s in shards]
+        for s, f in zip(shards, futs):
+            fb = f.result()
+            eng.frag_load(fam, s, fb)
+            del fb
+    t_build = time.perf_counter() - t_build
+    shards_arr = (C.c_uint64 * len(shards))(*shards)
+
+    n_batches = args.warmup + args.steps
+    batches = [pack_pairs(p, fam) for p in make_batches(n_batches, args.batch, args.rows)]
+    B = args.batch
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    sampler = ClockSampler(local_rank)
+    with torch.cuda.stream(stream):
+        # ---- leg 1: device-resident (prepared batches) ----
+        prepared = [eng.batch_prepare(fl, off, B, shards_arr, len(shards)) for fl, off in batches]
+        tens = [torch.as_tensor(DevArray(eng.batch_device_counts(b), B), device="cuda") for b in prepared] if world > 1 else None
+
+        def step_resident(i):
+            eng.batch_launch(prepared[i])
+            if world > 1:
+                dist.all_reduce(tens[i], op=dist.ReduceOp.SUM)
+
+        for i in range(args.warmup):
+            step_resident(i)
+        barrier()
+        sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for i in range(args.warmup, n_batches):
+            step_resident(i)
+        ev1.record(stream)
+        barrier()
+        ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+        out = (C.c_uint64 * B)()
+        eng.batch_fetch(prepared[-1], out)
+        last_resident = list(out)
+        for b in prepared:
+            eng.batch_free(b)
+
+        # ---- leg 2: end to end through the C ABI with host buffers ----
+        out_e2e = (C.c_uint64 * B)()
+
+        def step_e2e(i):
+            fl, off = batches[i]
+            eng.count_batch_begin(fl, off, B, shards_arr, len(shards))   # host programs -> pinned -> H2D, kernel
+            if world > 1:
+                t = torch.as_tensor(DevArray(eng.count_batch_device(), B), device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            eng.count_batch_end(out_e2e)                                   # D2H + wait
+
+        for i in range(args.warmup):
+            step_e2e(i)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(args.warmup, n_batches):
+            step_e2e(i)
+        torch.cuda.synchronize()
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        clocks = sampler.stop()
+        tm = eng.last_timing()
+        assert list(out_e2e) == last_resident, "resident and e2e legs disagree"
+
+    ms_per_step = ms_total / args.steps
+    units_per_step = B * world
+    value = units_per_step / (ms_per_step * 1e-3)
+    e2e_value = units_per_step * args.steps / e2e_s
+    algo_bytes = B * len(shards) * 16 * 2 * (8192 + 16)   # per launch per GPU (payload + 16 B/container)
+    peak, peak_src = peaks()
+    achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+        "data": "synthetic", "config": workload_config(args, world),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(tm.h2d_bytes), "d2h_bytes_per_step": int(tm.d2h_bytes) + 8,
+                "ms_per_step": 1e3 * e2e_s / args.steps},
+        "gpu_launches": args.steps * 2 * int(max(1, tm.launches)),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "kernel": "eval_fast_kernel (K1: 128-bit AND + popcount over bitmap container pairs)",
+                     "algo_bytes_per_launch": algo_bytes, "peak_source": peak_src,
+                     "note": "achieved = algorithmic bytes per launch / mean launch duration from CUDA events over the timed region "
+                             "(includes the per-step 8 KiB count memset" + (" and the NCCL all-reduce of the counts" if world > 1 else "") + ")"},
+        "columns_per_s": value * SHARDS_PER_GPU * (1 << 20) * 2,
+        "global_queries_per_s": value / world,
+        "index_build_s": t_build,
+        "engine_algo_bytes_last_call": int(tm.algo_bytes),
+    }
+
+    # ---- CPU baseline (rank 0, N = 1 only) + parity spot check against it ----
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu, pairs, cpu_counts = cpu_leg(shards, args.rows, 1, 1, args.cpu_seconds)
+        fl, off = pack_pairs(pairs, fam)
+        got = (C.c_uint64 * len(pairs))()
+        eng.count_batch_raw(fl, off, len(pairs), shards_arr, len(shards), got)
+        ok = list(got) == list(cpu_counts)
+        line["cpu_baseline"] = cpu
+        line["parity_check"] = "ok: %d sample queries bit-exact vs oracle" % len(pairs) if ok else "MISMATCH vs oracle"
+        if not ok:
+            print(json.dumps(line), flush=True)
+            raise SystemExit("parity check against the oracle failed")
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -174,6 +174,30 @@ int pb200_count_batch(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* p
 int pb200_count_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
                        const uint64_t* shards, uint32_t n_shards, uint64_t* out_per_shard);
 
+/* Split form of pb200_count_batch for hosts that merge across GPUs: _begin compiles,
+ * uploads and launches asynchronously; between the two calls the per-query partial counts
+ * are resident in HBM at *device_counts (uint64[n_queries]) where an NCCL all-reduce over
+ * NVLink can sum them in place (the reduceFn of executor.go:1813 across devices); _end
+ * copies them to the host and waits. One batch may be in flight per context. */
+int pb200_count_batch_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off,
+                            uint32_t n_queries, const uint64_t* shards, uint32_t n_shards);
+int pb200_count_batch_device(pb200_ctx* ctx, void** device_counts);
+int pb200_count_batch_end(pb200_ctx* ctx, uint64_t* out_counts);
+
+/* Prepared batches: compile + upload a batch of Count programs once (Row / Intersect /
+ * Union / Difference / Xor / Not trees), then launch it any number of times with no
+ * host<->device traffic; counts stay in HBM until fetched. The serving loop of a host that
+ * re-issues the same dashboard queries; also what bench.py times as the device-resident
+ * throughput. Launches are asynchronous on the context's stream. */
+typedef struct pb200_batch pb200_batch;
+int pb200_batch_prepare(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off,
+                        uint32_t n_queries, const uint64_t* shards, uint32_t n_shards,
+                        pb200_batch** out);
+int pb200_batch_launch(pb200_ctx* ctx, pb200_batch* batch);
+int pb200_batch_device_counts(pb200_ctx* ctx, pb200_batch* batch, void** device_counts);
+int pb200_batch_fetch(pb200_ctx* ctx, pb200_batch* batch, uint64_t* out_counts);
+int pb200_batch_free(pb200_ctx* ctx, pb200_batch* batch);
+
 /* Evaluate a bitmap call on ONE shard and return the resulting row segment as Pilosa
  * roaring bytes (containers optimize()d, keys = shard*16 + i as fragment.go:629
  * OffsetRange produces). Two-call protocol: with out == NULL only *out_len is written.
@@ -191,11 +215,16 @@ int pb200_eval_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
  * per shard. src_prog may be NULL (no Src). ids non-NULL selects the explicit-ids path
  * (N forced 0, fragment.go:1573). min_threshold 0 means defaultMinThreshold=1
  * (executor.go:37,984). Attribute filters stay on the host. On return *n_out pairs are
- * written (sorted by count desc, ties by ascending id); cap is the capacity of `out`. */
+ * written (sorted by count desc, ties by ascending id); cap is the capacity of `out`.
+ * flags & PB200_TOPN_REMOTE: behave like a remote node of a distributed query
+ * (execOptions.Remote, executor.go:884-887): run the first pass only and return its merged
+ * pairs untrimmed, so that a coordinator (another GPU's host) can merge and issue pass 2. */
+#define PB200_TOPN_REMOTE 1u
 int pb200_topn(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog,
                uint32_t n_src_nodes, uint32_t n, const uint64_t* ids, size_t n_ids,
-               uint64_t min_threshold, uint64_t tanimoto_threshold, const uint64_t* shards,
-               uint32_t n_shards, pb200_pair* out, size_t cap, size_t* n_out);
+               uint64_t min_threshold, uint64_t tanimoto_threshold, uint32_t flags,
+               const uint64_t* shards, uint32_t n_shards, pb200_pair* out, size_t cap,
+               size_t* n_out);
 
 /* One shard of TopN, exactly fragment.top (fragment.go:1568-1700): pass-1 style when
  * ids == NULL, explicit-ids style otherwise. Output order = the reference's heap-pop order. */

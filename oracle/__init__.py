@@ -89,7 +89,7 @@ def lib() -> C.CDLL:
         "orc_count_shards": (C.c_int, [vp, np_, C.c_uint32, u64p, C.c_uint32, C.c_int, u64p]),
         "orc_eval_columns": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, u64p, sz, C.POINTER(sz)]),
         "orc_eval_roaring": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, C.c_char_p, sz, C.POINTER(sz)]),
-        "orc_topn": (C.c_int, [vp, C.c_uint32, np_, C.c_uint32, C.c_uint32, u64p, sz, C.c_uint64, C.c_uint64, u64p,
+        "orc_topn": (C.c_int, [vp, C.c_uint32, np_, C.c_uint32, C.c_uint32, u64p, sz, C.c_uint64, C.c_uint64, C.c_uint32, u64p,
                                C.c_uint32, C.POINTER(Pair), sz, C.POINTER(sz)]),
         "orc_topn_shard": (C.c_int, [vp, C.c_uint32, np_, C.c_uint32, C.c_uint32, u64p, sz, C.c_uint64, C.c_uint64,
                                      C.c_uint64, C.POINTER(Pair), sz, C.POINTER(sz)]),
@@ -302,8 +302,14 @@ class Oracle:
     def family_create(self) -> int:
         return lib().orc_family_create(self._h)
 
-    def frag_load(self, fam: int, shard: int, data: bytes) -> None:
-        _check(lib().orc_frag_load(self._h, fam, shard, data, len(data)))
+    def frag_load(self, fam: int, shard: int, data) -> None:
+        if hasattr(data, "ptr"):  # synth.FragBytes: pass the generator's buffer without a copy
+            _check(lib().orc_frag_load(self._h, fam, shard, C.cast(C.c_void_p(data.ptr), C.c_char_p), data.size))
+        else:
+            _check(lib().orc_frag_load(self._h, fam, shard, data, len(data)))
+
+    def count_batch(self, progs, shards: Sequence[int], fused: bool = False) -> List[int]:
+        return [self.count(p, shards, fused) for p in progs]
 
     def set_bit(self, fam, shard, row, col) -> bool:
         return bool(lib().orc_frag_set_bit(self._h, fam, shard, row, col))
@@ -370,10 +376,10 @@ class Oracle:
         _check(fn(*args, out, cap, C.byref(n)))
         return [(out[i].id, out[i].count) for i in range(min(cap, n.value))]
 
-    def topn(self, fam, src_prog, n, shards, ids=(), min_threshold=0, tanimoto=0):
+    def topn(self, fam, src_prog, n, shards, ids=(), min_threshold=0, tanimoto=0, remote=False):
         sp, ns = (src_prog, len(src_prog)) if src_prog is not None else (None, 0)
         return self._pairs(lib().orc_topn, self._h, fam, sp, ns, n, u64_array(ids) if ids else None, len(ids),
-                           min_threshold, tanimoto, u64_array(shards), len(shards))
+                           min_threshold, tanimoto, 1 if remote else 0, u64_array(shards), len(shards))
 
     def topn_shard(self, fam, src_prog, n, shard, ids=(), min_threshold=0, tanimoto=0):
         sp, ns = (src_prog, len(src_prog)) if src_prog is not None else (None, 0)

@@ -262,9 +262,9 @@ int orc_eval_roaring(void* h, const pb200_node* prog, uint32_t n, uint64_t shard
   });
 }
 int orc_topn(void* h, uint32_t fam, const pb200_node* src, uint32_t nsrc, uint32_t n, const uint64_t* ids, size_t nids,
-             uint64_t min_threshold, uint64_t tanimoto, const uint64_t* shards, uint32_t ns, pb200_pair* out, size_t cap, size_t* n_out) {
+             uint64_t min_threshold, uint64_t tanimoto, uint32_t flags, const uint64_t* shards, uint32_t ns, pb200_pair* out, size_t cap, size_t* n_out) {
   return guard([&] {
-    auto r = ((Orc*)h)->exec.topn(fam, src, nsrc, n, vec(ids, nids), min_threshold, tanimoto, vec(shards, ns));
+    auto r = ((Orc*)h)->exec.topn(fam, src, nsrc, n, vec(ids, nids), min_threshold, tanimoto, vec(shards, ns), (flags & PB200_TOPN_REMOTE) != 0);
     *n_out = r.size();
     for (size_t i = 0; i < r.size() && i < cap; i++) out[i] = {r[i].id, r[i].count};
   });

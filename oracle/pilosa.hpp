@@ -727,9 +727,9 @@ struct Executor {
   // executor.go:863-903 executeTopN (two passes)
   std::vector<Pair> topn(uint32_t fam, const pb200_node* src, uint32_t nsrc, uint32_t n,
                          const std::vector<uint64_t>& ids, uint64_t min_threshold, uint64_t tanimoto,
-                         const std::vector<uint64_t>& shards) const {
+                         const std::vector<uint64_t>& shards, bool remote = false) const {
     auto pairs = topn_shards(fam, src, nsrc, n, ids, min_threshold, tanimoto, shards);
-    if (pairs.empty() || !ids.empty()) return pairs;
+    if (pairs.empty() || !ids.empty() || remote) return pairs;  // executor.go:884-887
     std::vector<uint64_t> ids2;
     for (auto& p : pairs) ids2.push_back(p.id);
     std::sort(ids2.begin(), ids2.end());

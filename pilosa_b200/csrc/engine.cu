@@ -1,0 +1,779 @@
+// libpilosa_b200: context, fragment loader, program compiler and the C ABI entry points.
+// Single translation unit with the kernels (kernels*.cuh) so nvcc -lineinfo maps the ncu
+// source page onto this tree.
+#include "engine.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+
+#include "kernels.cuh"
+#include "kernels_bsi.cuh"
+#include "kernels_topn.cuh"
+
+using namespace pb200;
+
+// ---------------------------------------------------------------------------------------
+// helpers
+// ---------------------------------------------------------------------------------------
+#define CUDA_TRY(ctx, call)                                                                   \
+  do {                                                                                        \
+    cudaError_t e__ = (call);                                                                 \
+    if (e__ != cudaSuccess) {                                                                 \
+      (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);                       \
+      return PB200_ERR_CUDA;                                                                  \
+    }                                                                                         \
+  } while (0)
+
+#define TRY(expr)             \
+  do {                        \
+    int rc__ = (expr);        \
+    if (rc__ != PB200_OK) return rc__; \
+  } while (0)
+
+static int fail(pb200_ctx* ctx, int code, const std::string& msg) {
+  ctx->err = msg;
+  return code;
+}
+
+static int ensure_dev(pb200_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return PB200_OK;
+  size_t ncap = std::max(bytes, b.cap * 2);
+  ncap = (ncap + 255) & ~size_t(255);
+  if (b.p) {
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    CUDA_TRY(ctx, cudaFree(b.p));
+    b.p = nullptr; b.cap = 0;
+  }
+  CUDA_TRY(ctx, cudaMalloc(&b.p, ncap));
+  b.cap = ncap;
+  return PB200_OK;
+}
+
+static int ensure_pin(pb200_ctx* ctx, PinBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return PB200_OK;
+  size_t ncap = std::max(bytes, b.cap * 2);
+  if (b.p) {
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    CUDA_TRY(ctx, cudaFreeHost(b.p));
+    b.p = nullptr; b.cap = 0;
+  }
+  CUDA_TRY(ctx, cudaMallocHost(&b.p, ncap));
+  b.cap = ncap;
+  return PB200_OK;
+}
+
+struct DeviceGuard {  // make ctx->device current for the duration of a call
+  int prev = -1;
+  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+#define ENTER(ctx)                                   \
+  if (!(ctx)) return PB200_ERR_INVALID;              \
+  std::lock_guard<std::mutex> lock__((ctx)->mu);     \
+  DeviceGuard guard__((ctx)->device);                \
+  (ctx)->err.clear()
+
+// ---------------------------------------------------------------------------------------
+// lifecycle
+// ---------------------------------------------------------------------------------------
+extern "C" int pb200_abi_version(void) { return PB200_ABI_VERSION; }
+
+extern "C" const char* pb200_strerror(int status) {
+  switch (status) {
+    case PB200_OK: return "ok";
+    case PB200_ERR_INVALID: return "invalid argument";
+    case PB200_ERR_CUDA: return "CUDA error";
+    case PB200_ERR_FORMAT: return "malformed roaring data";
+    case PB200_ERR_NOMEM: return "HBM budget exhausted";
+    case PB200_ERR_NOTFOUND: return "not found";
+    case PB200_ERR_RANGE: return "buffer too small or size limit exceeded";
+    case PB200_ERR_UNSUPPORTED: return "unsupported";
+    default: return "unknown status";
+  }
+}
+
+extern "C" const char* pb200_last_error(pb200_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+extern "C" int pb200_init(int device, size_t hbm_budget_bytes, pb200_ctx** out) {
+  if (!out) return PB200_ERR_INVALID;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0 || device < 0 || device >= ndev) return PB200_ERR_CUDA;  // no CPU fallback
+  auto* ctx = new pb200_ctx();
+  ctx->device = device;
+  ctx->budget = hbm_budget_bytes;
+  DeviceGuard g(device);
+  cudaDeviceProp prop{};
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return PB200_ERR_CUDA; }
+  ctx->sm_count = prop.multiProcessorCount;
+  if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
+    delete ctx;
+    return PB200_ERR_CUDA;
+  }
+  ctx->stream = ctx->own_stream;
+  *out = ctx;
+  return PB200_OK;
+}
+
+static void free_fragment(Fragment& f) {
+  if (f.blob) cudaFree(f.blob);
+  f.blob = nullptr;
+}
+
+extern "C" int pb200_shutdown(pb200_ctx* ctx) {
+  if (!ctx) return PB200_ERR_INVALID;
+  {
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    DeviceGuard g(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto& fam : ctx->families) {
+      for (auto& kv : fam.frags) free_fragment(kv.second);
+      if (fam.d_frags) cudaFree(fam.d_frags);
+    }
+    if (ctx->d_families) cudaFree(ctx->d_families);
+    for (DevBuf* b : {&ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi})
+      if (b->p) cudaFree(b->p);
+    for (PinBuf* b : {&ctx->h_stage, &ctx->h_out, &ctx->h_algo})
+      if (b->p) cudaFreeHost(b->p);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  }
+  delete ctx;
+  return PB200_OK;
+}
+
+extern "C" int pb200_set_stream(pb200_ctx* ctx, void* cuda_stream) {
+  ENTER(ctx);
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  return PB200_OK;
+}
+
+extern "C" int pb200_last_timing(pb200_ctx* ctx, pb200_timing* out) {
+  if (!ctx || !out) return PB200_ERR_INVALID;
+  std::lock_guard<std::mutex> lock(ctx->mu);
+  *out = ctx->timing;
+  return PB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// families and fragments
+// ---------------------------------------------------------------------------------------
+extern "C" int pb200_family_create(pb200_ctx* ctx, pb200_family* out) {
+  ENTER(ctx);
+  if (!out) return PB200_ERR_INVALID;
+  ctx->families.emplace_back();
+  ctx->families_dirty = true;
+  *out = uint32_t(ctx->families.size() - 1);
+  return PB200_OK;
+}
+
+static int family_grow(pb200_ctx* ctx, Family& fam, uint64_t shard) {
+  if (shard < fam.cap) return PB200_OK;
+  if (shard >= (1ull << 26)) return fail(ctx, PB200_ERR_RANGE, "shard number too large");
+  uint32_t ncap = std::max<uint32_t>(64, fam.cap);
+  while (ncap <= shard) ncap *= 2;
+  FragDev* nd = nullptr;
+  CUDA_TRY(ctx, cudaMalloc(&nd, size_t(ncap) * sizeof(FragDev)));
+  fam.h_frags.resize(ncap, FragDev{});
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpy(nd, fam.h_frags.data(), size_t(ncap) * sizeof(FragDev), cudaMemcpyHostToDevice));
+  if (fam.d_frags) CUDA_TRY(ctx, cudaFree(fam.d_frags));
+  fam.d_frags = nd;
+  fam.cap = ncap;
+  ctx->families_dirty = true;
+  return PB200_OK;
+}
+
+static int sync_families(pb200_ctx* ctx) {
+  if (!ctx->families_dirty) return PB200_OK;
+  uint32_t n = uint32_t(ctx->families.size());
+  if (n > ctx->d_families_cap) {
+    uint32_t ncap = std::max<uint32_t>(16, ctx->d_families_cap);
+    while (ncap < n) ncap *= 2;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->d_families) CUDA_TRY(ctx, cudaFree(ctx->d_families));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_families, size_t(ncap) * sizeof(FamilyDev)));
+    ctx->d_families_cap = ncap;
+  }
+  std::vector<FamilyDev> h(n);
+  for (uint32_t i = 0; i < n; i++) { h[i].frags = ctx->families[i].d_frags; h[i].cap = ctx->families[i].cap; h[i].pad = 0; }
+  if (n) {
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpy(ctx->d_families, h.data(), size_t(n) * sizeof(FamilyDev), cudaMemcpyHostToDevice));
+  }
+  ctx->families_dirty = false;
+  return PB200_OK;
+}
+
+static void default_rank(Fragment& f) {
+  // Exact row counts, count desc / id asc, trimmed to DefaultCacheSize = 50000 (field.go:47);
+  // rows with count 0 never enter the cache.
+  size_t n = f.row_ids.size();
+  std::vector<uint32_t> order(n);
+  for (size_t i = 0; i < n; i++) order[i] = uint32_t(i);
+  std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return f.row_counts[a] > f.row_counts[b]; });
+  if (n > 50000) order.resize(50000);
+  f.rank_ids.clear(); f.rank_counts.clear();
+  for (uint32_t i : order) { f.rank_ids.push_back(f.row_ids[i]); f.rank_counts.push_back(f.row_counts[i]); }
+  f.rank_from_host = false;
+}
+
+static int upload_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const std::vector<HostContainer>& cs) {
+  FragImage img;
+  std::string err;
+  if (!build_image(cs, img, err)) return fail(ctx, PB200_ERR_FORMAT, err);
+  if (ctx->budget && ctx->used + img.blob.size() > ctx->budget) return fail(ctx, PB200_ERR_NOMEM, "HBM budget exhausted");
+  TRY(family_grow(ctx, fam, shard));
+  void* blob = nullptr;
+  CUDA_TRY(ctx, cudaMalloc(&blob, img.blob.size()));
+  // fix up payload addresses now that the base is known
+  auto* descs = reinterpret_cast<ContainerDesc*>(img.blob.data() + img.descs_off);
+  const uint64_t base = reinterpret_cast<uint64_t>(blob);
+  for (size_t i = 0; i < size_t(img.nrows) * kRowContainers; i++)
+    if (descs[i].n) descs[i].addr += base;
+  cudaError_t e = cudaMemcpy(blob, img.blob.data(), img.blob.size(), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { cudaFree(blob); return fail(ctx, PB200_ERR_CUDA, std::string("cudaMemcpy fragment: ") + cudaGetErrorString(e)); }
+
+  Fragment nf;
+  nf.blob = blob;
+  nf.blob_bytes = img.blob.size();
+  nf.row_ids_off = img.row_ids_off; nf.descs_off = img.descs_off; nf.payload_off = img.payload_off;
+  nf.dev.row_ids = reinterpret_cast<const uint64_t*>(base + img.row_ids_off);
+  nf.dev.rows = reinterpret_cast<const ContainerDesc*>(base + img.descs_off);
+  nf.dev.nrows = img.nrows;
+  nf.dev.dense = img.dense ? 1u : 0u;
+  nf.n_containers = img.n_containers;
+  nf.payload_bytes = img.payload_bytes;
+  nf.all_bitmap = img.all_bitmap;
+  nf.row_ids = std::move(img.row_ids);
+  nf.row_counts = std::move(img.row_counts);
+  default_rank(nf);
+
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // no query may still read the old copy
+  auto it = fam.frags.find(shard);
+  if (it != fam.frags.end()) {
+    if (!it->second.all_bitmap) fam.n_not_all_bitmap--;
+    ctx->used -= it->second.blob_bytes;
+    free_fragment(it->second);
+    fam.frags.erase(it);
+  }
+  ctx->used += nf.blob_bytes;
+  if (!nf.all_bitmap) fam.n_not_all_bitmap++;
+  fam.h_frags[shard] = nf.dev;
+  CUDA_TRY(ctx, cudaMemcpy(fam.d_frags + shard, &nf.dev, sizeof(FragDev), cudaMemcpyHostToDevice));
+  fam.frags.emplace(shard, std::move(nf));
+  return PB200_OK;
+}
+
+extern "C" int pb200_frag_load(pb200_ctx* ctx, pb200_family family, uint64_t shard, const void* roaring_bytes, size_t len) {
+  ENTER(ctx);
+  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
+  if (!roaring_bytes && len) return PB200_ERR_INVALID;
+  std::vector<HostContainer> cs;
+  std::string err;
+  if (!parse_fragment(static_cast<const uint8_t*>(roaring_bytes), len, cs, err)) return fail(ctx, PB200_ERR_FORMAT, err);
+  return upload_fragment(ctx, ctx->families[family], shard, cs);
+}
+
+// Rebuild the host view of a resident fragment from its device blob (no host shadow is kept).
+static int download_containers(pb200_ctx* ctx, const Fragment& f, std::vector<uint8_t>& blob, std::vector<HostContainer>& cs) {
+  blob.resize(f.blob_bytes);
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpy(blob.data(), f.blob, f.blob_bytes, cudaMemcpyDeviceToHost));
+  const auto* descs = reinterpret_cast<const ContainerDesc*>(blob.data() + f.descs_off);
+  const uint64_t base = reinterpret_cast<uint64_t>(f.blob);
+  cs.clear();
+  for (uint32_t r = 0; r < f.dev.nrows; r++) {
+    uint64_t row = f.dev.dense ? r : f.row_ids[r];
+    for (int c = 0; c < kRowContainers; c++) {
+      const ContainerDesc& d = descs[size_t(r) * kRowContainers + c];
+      if (!d.n) continue;
+      HostContainer hc;
+      hc.key = row * kRowContainers + c;
+      hc.type = desc_type(d); hc.n = d.n; hc.len = desc_len(d);
+      hc.data = blob.data() + (d.addr - base);
+      cs.push_back(std::move(hc));
+    }
+  }
+  return PB200_OK;
+}
+
+extern "C" int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t shard, const uint64_t* set_pos, size_t n_set,
+                                const uint64_t* clear_pos, size_t n_clear) {
+  ENTER(ctx);
+  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
+  if ((n_set && !set_pos) || (n_clear && !clear_pos)) return PB200_ERR_INVALID;
+  Family& fam = ctx->families[family];
+  std::vector<uint8_t> blob;
+  std::vector<HostContainer> cs;
+  auto it = fam.frags.find(shard);
+  if (it != fam.frags.end()) TRY(download_containers(ctx, it->second, blob, cs));
+  std::map<uint64_t, HostContainer> m;
+  for (auto& c : cs) m.emplace(c.key, std::move(c));
+  if (n_set) apply_bits(m, set_pos, n_set, true);
+  if (n_clear) apply_bits(m, clear_pos, n_clear, false);
+  cs.clear();
+  for (auto& kv : m) {
+    cs.push_back(std::move(kv.second));
+    if (!cs.back().owned.empty()) cs.back().data = cs.back().owned.data();
+  }
+  return upload_fragment(ctx, fam, shard, cs);
+}
+
+extern "C" int pb200_frag_drop(pb200_ctx* ctx, pb200_family family, uint64_t shard) {
+  ENTER(ctx);
+  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
+  Family& fam = ctx->families[family];
+  auto it = fam.frags.find(shard);
+  if (it == fam.frags.end()) return fail(ctx, PB200_ERR_NOTFOUND, "no such fragment");
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  FragDev empty{};
+  fam.h_frags[shard] = empty;
+  CUDA_TRY(ctx, cudaMemcpy(fam.d_frags + shard, &empty, sizeof(FragDev), cudaMemcpyHostToDevice));
+  if (!it->second.all_bitmap) fam.n_not_all_bitmap--;
+  ctx->used -= it->second.blob_bytes;
+  free_fragment(it->second);
+  fam.frags.erase(it);
+  return PB200_OK;
+}
+
+extern "C" int pb200_rank_set(pb200_ctx* ctx, pb200_family family, uint64_t shard, const uint64_t* row_ids, const uint64_t* counts, size_t n) {
+  ENTER(ctx);
+  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
+  if (n && (!row_ids || !counts)) return PB200_ERR_INVALID;
+  auto it = ctx->families[family].frags.find(shard);
+  if (it == ctx->families[family].frags.end()) return fail(ctx, PB200_ERR_NOTFOUND, "no such fragment");
+  it->second.rank_ids.assign(row_ids, row_ids + n);
+  it->second.rank_counts.assign(counts, counts + n);
+  it->second.rank_from_host = true;
+  return PB200_OK;
+}
+
+extern "C" int pb200_frag_stat(pb200_ctx* ctx, pb200_family family, uint64_t shard, uint64_t* n_rows, uint64_t* n_containers, uint64_t* payload_bytes) {
+  ENTER(ctx);
+  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
+  auto it = ctx->families[family].frags.find(shard);
+  if (it == ctx->families[family].frags.end()) return fail(ctx, PB200_ERR_NOTFOUND, "no such fragment");
+  if (n_rows) *n_rows = it->second.row_ids.size();
+  if (n_containers) *n_containers = it->second.n_containers;
+  if (payload_bytes) *payload_bytes = it->second.payload_bytes;
+  return PB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// program compiler: post-order pb200_node tree -> accumulator machine (layout.h)
+// ---------------------------------------------------------------------------------------
+namespace {
+
+struct TNode {
+  uint32_t op = 0;  // pb200_op of an n-ary node, or 0 for a leaf, or PB200_OP_NOT
+  int leaf = -1;    // leaf index (leaf nodes; NOT: the existence leaf)
+  std::vector<int> kids;
+};
+
+struct Compiler {
+  pb200_ctx* ctx;
+  Compiled& out;
+  uint32_t leaf_base = 0;
+  std::vector<TNode> tree;
+  std::string err;
+
+  Compiler(pb200_ctx* c, Compiled& o) : ctx(c), out(o) {}
+
+  int add_leaf(uint32_t kind, uint32_t family, uint64_t row) {
+    Leaf lf; lf.kind = kind; lf.family = family; lf.row = row;
+    out.leaves.push_back(lf);
+    if (kind == L_TEMP) out.may_need_staging = true;
+    else if (kind == L_ROW && family < ctx->families.size() && ctx->families[family].n_not_all_bitmap) out.may_need_staging = true;
+    return int(out.leaves.size() - 1 - leaf_base);
+  }
+  int leaf_node(int leaf) { TNode t; t.leaf = leaf; tree.push_back(t); return int(tree.size() - 1); }
+
+  void emit(int n, std::vector<Instr>& ins) {
+    const TNode& t = tree[n];
+    if (t.op == 0) { ins.push_back({I_LOAD, uint8_t(t.leaf)}); return; }
+    if (t.op == PB200_OP_NOT) { emit(t.kids[0], ins); ins.push_back({I_RANDNOT_LEAF, uint8_t(t.leaf)}); return; }
+    uint8_t lop, sop;
+    switch (t.op) {
+      case PB200_OP_INTERSECT: lop = I_AND_LEAF; sop = I_AND_STACK; break;
+      case PB200_OP_UNION: lop = I_OR_LEAF; sop = I_OR_STACK; break;
+      case PB200_OP_XOR: lop = I_XOR_LEAF; sop = I_XOR_STACK; break;
+      default: lop = I_ANDNOT_LEAF; sop = I_ANDNOT_STACK; break;
+    }
+    emit(t.kids[0], ins);
+    for (size_t k = 1; k < t.kids.size(); k++) {
+      const TNode& ch = tree[t.kids[k]];
+      if (ch.op == 0) ins.push_back({lop, uint8_t(ch.leaf)});
+      else { emit(t.kids[k], ins); ins.push_back({sop, 0}); }
+    }
+  }
+
+  // Emits the program of subtree `root` as a new Prog; returns false on limits.
+  bool finish(int root, Prog& pg) {
+    std::vector<Instr> ins;
+    emit(root, ins);
+    int sp = 0, maxsp = 0; bool live = false;
+    for (auto& i : ins) {
+      if (i.op == I_LOAD) { if (live) { sp++; maxsp = std::max(maxsp, sp); } live = true; }
+      else if (i.op >= I_AND_STACK) sp--;
+    }
+    if (maxsp > kMaxStack) { err = "expression too deeply nested (stack depth > 4)"; return false; }
+    if (ins.size() > size_t(kMaxInstr)) { err = "expression too long (> 64 instructions)"; return false; }
+    pg.instr_off = uint32_t(out.instrs.size());
+    pg.n_instr = uint32_t(ins.size());
+    pg.leaf_off = leaf_base;
+    pg.n_leaves = uint32_t(out.leaves.size() - leaf_base);
+    if (pg.n_leaves > uint32_t(kMaxLeaves)) { err = "too many leaves in one expression (> 32)"; return false; }
+    out.instrs.insert(out.instrs.end(), ins.begin(), ins.end());
+    return true;
+  }
+
+  // Compiles one post-order program; appends a Prog to out.progs.
+  bool compile(const pb200_node* nodes, uint32_t n) {
+    if (!nodes || n == 0) { err = "empty program"; return false; }
+    leaf_base = uint32_t(out.leaves.size());
+    tree.clear();
+    std::vector<int> st;
+    for (uint32_t k = 0; k < n; k++) {
+      const pb200_node& nd = nodes[k];
+      switch (nd.op) {
+        case PB200_OP_ROW:
+          if (nd.family >= ctx->families.size()) { err = "unknown family in Row()"; return false; }
+          st.push_back(leaf_node(add_leaf(L_ROW, nd.family, nd.row)));
+          break;
+        case PB200_OP_EMPTY: st.push_back(leaf_node(add_leaf(L_ZERO, 0, 0))); break;
+        case PB200_OP_BSI_RANGE: {
+          if (nd.family >= ctx->families.size()) { err = "unknown family in BSI range"; return false; }
+          if (nd.bsi_op < PB200_BSI_EQ || nd.bsi_op > PB200_BSI_NOTNULL) { err = "invalid range operation"; return false; }
+          if (nd.bit_depth > 63) { err = "bit depth > 63"; return false; }
+          Compiled::PreTask pt; pt.kind = 0; pt.node = nd; pt.slot = out.n_temp_slots++;
+          out.pre.push_back(pt);
+          st.push_back(leaf_node(add_leaf(L_TEMP, pt.slot, 0)));
+          break;
+        }
+        case PB200_OP_INTERSECT: case PB200_OP_UNION: case PB200_OP_DIFFERENCE: case PB200_OP_XOR: {
+          if (nd.nargs == 0) {
+            if (nd.op == PB200_OP_UNION || nd.op == PB200_OP_XOR) { st.push_back(leaf_node(add_leaf(L_ZERO, 0, 0))); break; }
+            err = nd.op == PB200_OP_INTERSECT ? "empty Intersect query is currently not supported"   // executor.go:1673
+                                              : "empty Difference query is currently not supported";  // executor.go:1008
+            return false;
+          }
+          if (st.size() < nd.nargs) { err = "malformed program: operand stack underflow"; return false; }
+          if (nd.nargs == 1) break;  // identity
+          TNode t; t.op = nd.op;
+          t.kids.assign(st.end() - nd.nargs, st.end());
+          st.resize(st.size() - nd.nargs);
+          tree.push_back(t);
+          st.push_back(int(tree.size() - 1));
+          break;
+        }
+        case PB200_OP_NOT: {
+          if (st.empty()) { err = "Not() requires an input row"; return false; }  // executor.go:1741
+          if (nd.family >= ctx->families.size()) { err = "index does not support existence tracking"; return false; }
+          TNode t; t.op = PB200_OP_NOT; t.kids = {st.back()}; t.leaf = add_leaf(L_ROW, nd.family, 0);
+          st.pop_back();
+          tree.push_back(t);
+          st.push_back(int(tree.size() - 1));
+          break;
+        }
+        case PB200_OP_SHIFT: {
+          if (st.empty()) { err = "Shift() requires an input row"; return false; }  // executor.go:1777
+          // materialise the operand, then shift it by one with carry across containers
+          Compiled::PreTask ev; ev.kind = 2; ev.slot = out.n_temp_slots++;
+          // The operand's leaves sit in [leaf_base, now): compile it as its own program over the same table.
+          if (!finish(st.back(), ev.prog)) return false;
+          st.pop_back();
+          out.pre.push_back(ev);
+          Compiled::PreTask sh; sh.kind = 1; sh.src_slot = ev.slot; sh.slot = out.n_temp_slots++;
+          out.pre.push_back(sh);
+          st.push_back(leaf_node(add_leaf(L_TEMP, sh.slot, 0)));
+          break;
+        }
+        default: err = "unknown op " + std::to_string(nd.op); return false;
+      }
+    }
+    if (st.size() != 1) { err = "malformed program: " + std::to_string(st.size()) + " values left on the stack"; return false; }
+    Prog pg;
+    if (!finish(st[0], pg)) return false;
+    out.progs.push_back(pg);
+    return true;
+  }
+};
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
+// batch upload + evaluation
+// ---------------------------------------------------------------------------------------
+namespace {
+
+struct BatchDev {  // device pointers of an uploaded batch
+  const Prog* progs; const Instr* instrs; const Leaf* leaves; const uint64_t* shards;
+};
+
+int upload_batch(pb200_ctx* ctx, const Compiled& cp, const uint64_t* shards, uint32_t n_shards, BatchDev& bd) {
+  size_t o_prog = 0;
+  size_t o_leaf = align_up(o_prog + cp.progs.size() * sizeof(Prog) + cp.pre.size() * sizeof(Prog), 16);
+  size_t o_ins = align_up(o_leaf + cp.leaves.size() * sizeof(Leaf), 16);
+  size_t o_sh = align_up(o_ins + cp.instrs.size() * sizeof(Instr), 16);
+  size_t total = o_sh + size_t(n_shards) * 8;
+  TRY(ensure_pin(ctx, ctx->h_stage, total));
+  TRY(ensure_dev(ctx, ctx->d_batch, total));
+  uint8_t* h = static_cast<uint8_t*>(ctx->h_stage.p);
+  std::memcpy(h + o_prog, cp.progs.data(), cp.progs.size() * sizeof(Prog));
+  Prog* pre_progs = reinterpret_cast<Prog*>(h + o_prog + cp.progs.size() * sizeof(Prog));
+  for (size_t i = 0; i < cp.pre.size(); i++) pre_progs[i] = cp.pre[i].prog;
+  std::memcpy(h + o_leaf, cp.leaves.data(), cp.leaves.size() * sizeof(Leaf));
+  std::memcpy(h + o_ins, cp.instrs.data(), cp.instrs.size() * sizeof(Instr));
+  std::memcpy(h + o_sh, shards, size_t(n_shards) * 8);
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->d_batch.p, h, total, cudaMemcpyHostToDevice, ctx->stream));
+  uint8_t* d = static_cast<uint8_t*>(ctx->d_batch.p);
+  bd.progs = reinterpret_cast<const Prog*>(d + o_prog);
+  bd.leaves = reinterpret_cast<const Leaf*>(d + o_leaf);
+  bd.instrs = reinterpret_cast<const Instr*>(d + o_ins);
+  bd.shards = reinterpret_cast<const uint64_t*>(d + o_sh);
+  ctx->timing.h2d_bytes += total;
+  return PB200_OK;
+}
+
+// Launches the fast + staged kernels for `n_queries` programs starting at `progs`.
+int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards, bool staging,
+                unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, uint8_t* dense_out, uint32_t* dense_n) {
+  const uint64_t n_items = uint64_t(n_queries) * n_shards * kRowContainers;
+  if (n_items == 0) return PB200_OK;
+  if (n_items >= (1ull << 32)) return fail(ctx, PB200_ERR_RANGE, "batch too large: queries x shards x 16 must be < 2^32");
+  // scratch: slow list + counter + algo-bytes counter
+  size_t slow_bytes = staging ? size_t(n_items) * 4 : 4;
+  TRY(ensure_dev(ctx, ctx->d_slow, slow_bytes));
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  EvalParams p{};
+  p.families = ctx->d_families;
+  p.n_families = uint32_t(ctx->families.size());
+  p.progs = progs; p.instrs = bd.instrs; p.leaves = bd.leaves; p.shards = bd.shards;
+  p.n_shards = n_shards; p.n_queries = n_queries;
+  p.temp_base = static_cast<const uint8_t*>(ctx->d_temp.p);
+  p.out_counts = out_counts; p.out_qstride = qstride; p.out_sstride = sstride;
+  p.dense_out = dense_out; p.dense_n = dense_n;
+  p.slow_list = static_cast<uint32_t*>(ctx->d_slow.p);
+  p.slow_count = static_cast<uint32_t*>(ctx->d_misc.p);
+  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 8);
+  CUDA_TRY(ctx, cudaMemsetAsync(p.slow_count, 0, 4, ctx->stream));
+  const uint64_t want = (n_items + kFastWarps - 1) / kFastWarps;
+  const uint32_t grid = uint32_t(std::min<uint64_t>(want, uint64_t(ctx->sm_count) * 8));
+  eval_fast_kernel<<<grid, kFastWarps * 32, 0, ctx->stream>>>(p);
+  ctx->timing.launches++;
+  if (staging) {
+    const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, uint64_t(ctx->sm_count) * 6));
+    eval_staged_kernel<<<sgrid, kStagedThreads, 0, ctx->stream>>>(p);
+    ctx->timing.launches++;
+  }
+  CUDA_TRY(ctx, cudaGetLastError());
+  return PB200_OK;
+}
+
+int validate_shards(pb200_ctx* ctx, const uint64_t* shards, uint32_t n_shards) {
+  if (n_shards && !shards) return fail(ctx, PB200_ERR_INVALID, "null shard list");
+  return PB200_OK;
+}
+
+void timing_begin(pb200_ctx* ctx) {
+  ctx->timing = pb200_timing{};
+  cudaMemsetAsync(static_cast<uint8_t*>(ctx->d_misc.p) + 8, 0, 8, ctx->stream);
+}
+
+// Runs the pre-tasks (BSI range / shift / sub-expression temps) of a compiled batch.
+int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_t n_shards);
+
+// Ends a query call: fetches the algorithmic-byte counter with the other results, waits for
+// the stream once, and reads the kernel time between the ev0/ev1 events.
+int finish_call(pb200_ctx* ctx) {
+  TRY(ensure_pin(ctx, ctx->h_algo, 64));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_algo.p, static_cast<uint8_t*>(ctx->d_misc.p) + 8, 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  float ms = 0;
+  if (cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) == cudaSuccess) ctx->timing.kernel_ms = ms;
+  ctx->timing.algo_bytes = *static_cast<unsigned long long*>(ctx->h_algo.p);
+  return PB200_OK;
+}
+
+// Compiles a batch of post-order programs.
+int compile_batch(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries, Compiled& cp) {
+  Compiler cc(ctx, cp);
+  for (uint32_t q = 0; q < n_queries; q++) {
+    const uint32_t b = prog_off[q], e = prog_off[q + 1];
+    if (e < b) return fail(ctx, PB200_ERR_INVALID, "prog_off not ascending");
+    if (!cc.compile(progs + b, e - b)) return fail(ctx, PB200_ERR_INVALID, cc.err);
+  }
+  return PB200_OK;
+}
+
+// First half of a Count call: compile, upload, launch (asynchronous on the stream). The
+// counts stay in ctx->d_out until count_end fetches them.
+int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries, const uint64_t* shards,
+                uint32_t n_shards, bool per_shard) {
+  TRY(validate_shards(ctx, shards, n_shards));
+  const size_t n_out = per_shard ? size_t(n_queries) * n_shards : n_queries;
+  ctx->pending_n_out = n_out;
+  ctx->pending_launched = false;
+  TRY(ensure_dev(ctx, ctx->d_out, std::max<size_t>(n_out, 1) * 8));
+  TRY(ensure_pin(ctx, ctx->h_out, std::max<size_t>(n_out, 1) * 8));
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  timing_begin(ctx);
+  if (n_queries == 0) return PB200_OK;
+  if (n_shards == 0) { CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_out.p, 0, n_out * 8, ctx->stream)); ctx->pending_launched = true; CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream)); CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream)); return PB200_OK; }
+  Compiled cp;
+  TRY(compile_batch(ctx, progs, prog_off, n_queries, cp));
+  TRY(sync_families(ctx));
+  BatchDev bd{};
+  TRY(upload_batch(ctx, cp, shards, n_shards, bd));
+  if (cp.n_temp_slots) TRY(ensure_dev(ctx, ctx->d_temp, size_t(cp.n_temp_slots) * n_shards * kRowContainers * kBitmapBytes));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_out.p, 0, n_out * 8, ctx->stream));
+  TRY(run_pretasks(ctx, cp, bd, n_shards));
+  TRY(launch_eval(ctx, bd, bd.progs, n_queries, n_shards, cp.may_need_staging, static_cast<unsigned long long*>(ctx->d_out.p),
+                  per_shard ? n_shards : 1, per_shard ? 1 : 0, nullptr, nullptr));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  ctx->pending_launched = true;
+  return PB200_OK;
+}
+
+// Second half: device -> host copy of the counts and the single stream wait.
+int count_end(pb200_ctx* ctx, uint64_t* out) {
+  const size_t n_out = ctx->pending_n_out;
+  if (n_out == 0) return PB200_OK;
+  if (!out) return PB200_ERR_INVALID;
+  if (!ctx->pending_launched) return fail(ctx, PB200_ERR_INVALID, "no Count batch in flight");
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_out.p, ctx->d_out.p, n_out * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  TRY(finish_call(ctx));
+  std::memcpy(out, ctx->h_out.p, n_out * 8);
+  ctx->timing.d2h_bytes += n_out * 8;
+  ctx->pending_launched = false;
+  return PB200_OK;
+}
+
+int count_impl(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries, const uint64_t* shards,
+               uint32_t n_shards, bool per_shard, uint64_t* out) {
+  if (!out) return PB200_ERR_INVALID;
+  TRY(count_begin(ctx, progs, prog_off, n_queries, shards, n_shards, per_shard));
+  return count_end(ctx, out);
+}
+
+}  // namespace
+
+#include "engine_queries.inl"
+
+extern "C" int pb200_count(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards, uint64_t* out_count) {
+  ENTER(ctx);
+  const uint32_t off[2] = {0, n_nodes};
+  return count_impl(ctx, prog, off, 1, shards, n_shards, false, out_count);
+}
+
+extern "C" int pb200_count_batch(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries,
+                                 const uint64_t* shards, uint32_t n_shards, uint64_t* out_counts) {
+  ENTER(ctx);
+  if (n_queries && (!progs || !prog_off)) return PB200_ERR_INVALID;
+  return count_impl(ctx, progs, prog_off, n_queries, shards, n_shards, false, out_counts);
+}
+
+extern "C" int pb200_count_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards, uint64_t* out_per_shard) {
+  ENTER(ctx);
+  const uint32_t off[2] = {0, n_nodes};
+  return count_impl(ctx, prog, off, 1, shards, n_shards, true, out_per_shard);
+}
+
+// ---- split Count batch: launch now, fetch later (multi-GPU hosts reduce the device-resident
+// counts with NCCL between the two calls) ----
+extern "C" int pb200_count_batch_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries,
+                                       const uint64_t* shards, uint32_t n_shards) {
+  ENTER(ctx);
+  if (n_queries && (!progs || !prog_off)) return PB200_ERR_INVALID;
+  return count_begin(ctx, progs, prog_off, n_queries, shards, n_shards, false);
+}
+
+extern "C" int pb200_count_batch_device(pb200_ctx* ctx, void** device_counts) {
+  ENTER(ctx);
+  if (!device_counts) return PB200_ERR_INVALID;
+  *device_counts = ctx->d_out.p;
+  return PB200_OK;
+}
+
+extern "C" int pb200_count_batch_end(pb200_ctx* ctx, uint64_t* out_counts) {
+  ENTER(ctx);
+  return count_end(ctx, out_counts);
+}
+
+// ---- prepared batches: compile + upload once, launch many times, results stay in HBM ----
+struct pb200_batch {
+  DevBuf d_batch, d_counts;
+  Compiled cp;
+  BatchDev bd{};
+  uint32_t n_queries = 0, n_shards = 0;
+};
+
+extern "C" int pb200_batch_prepare(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries,
+                                   const uint64_t* shards, uint32_t n_shards, pb200_batch** out) {
+  ENTER(ctx);
+  if (!out || !n_queries || !progs || !prog_off || !n_shards || !shards) return PB200_ERR_INVALID;
+  auto* b = new pb200_batch();
+  int rc = compile_batch(ctx, progs, prog_off, n_queries, b->cp);
+  if (rc == PB200_OK && (b->cp.n_temp_slots || !b->cp.pre.empty())) rc = fail(ctx, PB200_ERR_UNSUPPORTED, "prepared batches do not take BSI range / Shift leaves");
+  if (rc == PB200_OK) rc = sync_families(ctx);
+  if (rc == PB200_OK) {
+    std::swap(ctx->d_batch, b->d_batch);  // upload into the batch's own buffer
+    rc = upload_batch(ctx, b->cp, shards, n_shards, b->bd);
+    std::swap(ctx->d_batch, b->d_batch);
+  }
+  if (rc == PB200_OK) rc = ensure_dev(ctx, b->d_counts, size_t(n_queries) * 8);
+  if (rc == PB200_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(ctx, PB200_ERR_CUDA, "sync after batch upload failed");
+  if (rc != PB200_OK) {
+    if (b->d_batch.p) cudaFree(b->d_batch.p);
+    if (b->d_counts.p) cudaFree(b->d_counts.p);
+    delete b;
+    return rc;
+  }
+  b->n_queries = n_queries; b->n_shards = n_shards;
+  *out = b;
+  return PB200_OK;
+}
+
+extern "C" int pb200_batch_launch(pb200_ctx* ctx, pb200_batch* b) {
+  ENTER(ctx);
+  if (!b) return PB200_ERR_INVALID;
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  ctx->timing.launches = 0;
+  CUDA_TRY(ctx, cudaMemsetAsync(b->d_counts.p, 0, size_t(b->n_queries) * 8, ctx->stream));
+  return launch_eval(ctx, b->bd, b->bd.progs, b->n_queries, b->n_shards, b->cp.may_need_staging,
+                     static_cast<unsigned long long*>(b->d_counts.p), 1, 0, nullptr, nullptr);
+}
+
+extern "C" int pb200_batch_device_counts(pb200_ctx* ctx, pb200_batch* b, void** device_counts) {
+  if (!ctx || !b || !device_counts) return PB200_ERR_INVALID;
+  *device_counts = b->d_counts.p;
+  return PB200_OK;
+}
+
+extern "C" int pb200_batch_fetch(pb200_ctx* ctx, pb200_batch* b, uint64_t* out_counts) {
+  ENTER(ctx);
+  if (!b || !out_counts) return PB200_ERR_INVALID;
+  TRY(ensure_pin(ctx, ctx->h_out, size_t(b->n_queries) * 8));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_out.p, b->d_counts.p, size_t(b->n_queries) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  std::memcpy(out_counts, ctx->h_out.p, size_t(b->n_queries) * 8);
+  return PB200_OK;
+}
+
+extern "C" int pb200_batch_free(pb200_ctx* ctx, pb200_batch* b) {
+  ENTER(ctx);
+  if (!b) return PB200_OK;
+  cudaStreamSynchronize(ctx->stream);
+  if (b->d_batch.p) cudaFree(b->d_batch.p);
+  if (b->d_counts.p) cudaFree(b->d_counts.p);
+  delete b;
+  return PB200_OK;
+}

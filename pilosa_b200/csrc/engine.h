@@ -1,0 +1,84 @@
+// Host-side engine state behind the C ABI (include/pilosa_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/pilosa_b200.h"
+#include "host_roaring.h"
+#include "layout.h"
+
+namespace pb200 {
+
+struct DevBuf {  // growable cudaMalloc-backed scratch
+  void* p = nullptr;
+  size_t cap = 0;
+};
+struct PinBuf {  // growable pinned host staging
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+struct Fragment {
+  void* blob = nullptr;  // one cudaMalloc: [row_ids | descs | payloads]
+  size_t blob_bytes = 0;
+  FragDev dev{};
+  size_t row_ids_off = 0, descs_off = 0, payload_off = 0;
+  uint64_t n_containers = 0, payload_bytes = 0;
+  bool all_bitmap = true;
+  std::vector<uint64_t> row_ids;     // ascending ids of the rows present
+  std::vector<uint64_t> row_counts;  // exact cardinality per present row
+  // TopN candidate order (rank cache, cache.go:136-288). Either handed over by the host
+  // (pb200_rank_set) or derived from exact row counts (count desc, id asc, 50000 entries).
+  std::vector<uint64_t> rank_ids, rank_counts;
+  bool rank_from_host = false;
+};
+
+struct Family {
+  std::unordered_map<uint64_t, Fragment> frags;
+  std::vector<FragDev> h_frags;  // indexed by shard
+  FragDev* d_frags = nullptr;
+  uint32_t cap = 0;
+  uint64_t n_not_all_bitmap = 0;  // fragments holding array/run containers
+};
+
+// A compiled batch of programs, ready for upload.
+struct Compiled {
+  std::vector<Prog> progs;
+  std::vector<Instr> instrs;
+  std::vector<Leaf> leaves;
+  struct PreTask {
+    int kind;             // 0 = BSI range -> temp slot, 1 = shift(temp a) -> temp b, 2 = eval sub-program -> temp slot
+    pb200_node node{};    // kind 0
+    uint32_t slot = 0, src_slot = 0;
+    Prog prog{};          // kind 2: sub-program (offsets into instrs / leaves)
+  };
+  std::vector<PreTask> pre;
+  uint32_t n_temp_slots = 0;
+  bool may_need_staging = false;  // some leaf family holds array/run containers (or temps)
+};
+
+}  // namespace pb200
+
+struct pb200_ctx {
+  int device = 0;
+  int sm_count = 148;
+  size_t budget = 0, used = 0;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::mutex mu;
+  std::string err;
+  std::vector<pb200::Family> families;
+  pb200::FamilyDev* d_families = nullptr;
+  uint32_t d_families_cap = 0;
+  bool families_dirty = true;
+  pb200::DevBuf d_batch, d_out, d_slow, d_temp, d_dense, d_dense_n, d_misc, d_topn, d_bsi;
+  pb200::PinBuf h_stage, h_out, h_algo;
+  bool mm_attr_set = false;
+  size_t pending_n_out = 0;      // split Count batch in flight (count_begin / count_end)
+  bool pending_launched = false;
+  pb200_timing timing{};
+};

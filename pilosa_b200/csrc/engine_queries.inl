@@ -1,0 +1,546 @@
+// Included by engine.cu: bitmap-returning calls, TopN, BSI aggregates.
+
+namespace {
+
+uint8_t* temp_slot(pb200_ctx* ctx, uint32_t slot, uint32_t n_shards) {
+  return static_cast<uint8_t*>(ctx->d_temp.p) + size_t(slot) * n_shards * kRowContainers * kBitmapBytes;
+}
+
+int launch_bsi_range(pb200_ctx* ctx, const BatchDev& bd, const pb200_node& nd, uint32_t n_shards, uint8_t* dense_out) {
+  BsiParams p{};
+  p.families = ctx->d_families; p.family = nd.family; p.bit_depth = nd.bit_depth;
+  p.shards = bd.shards; p.n_shards = n_shards;
+  p.bsi_op = nd.bsi_op; p.a = nd.a; p.b = nd.b;
+  p.dense_out = dense_out;
+  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 8);
+  const uint32_t items = n_shards * kRowContainers;
+  const uint32_t grid = std::min<uint32_t>(items, uint32_t(ctx->sm_count) * 8);
+  bsi_range_kernel<<<grid, kBsiThreads, 0, ctx->stream>>>(p);
+  ctx->timing.launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return PB200_OK;
+}
+
+int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_t n_shards) {
+  for (size_t i = 0; i < cp.pre.size(); i++) {
+    const auto& pt = cp.pre[i];
+    if (pt.kind == 0) {
+      TRY(launch_bsi_range(ctx, bd, pt.node, n_shards, temp_slot(ctx, pt.slot, n_shards)));
+    } else if (pt.kind == 2) {
+      TRY(launch_eval(ctx, bd, bd.progs + cp.progs.size() + i, 1, n_shards, true, nullptr, 0, 0, temp_slot(ctx, pt.slot, n_shards), nullptr));
+    } else {
+      const uint64_t n_words = uint64_t(n_shards) * kRowContainers * kBitmapWords;
+      const uint32_t grid = uint32_t(std::min<uint64_t>((n_words + 255) / 256, uint64_t(ctx->sm_count) * 16));
+      shift_rows_kernel<<<grid, 256, 0, ctx->stream>>>(temp_slot(ctx, pt.src_slot, n_shards), temp_slot(ctx, pt.slot, n_shards), n_shards);
+      ctx->timing.launches++;
+      CUDA_TRY(ctx, cudaGetLastError());
+    }
+  }
+  return PB200_OK;
+}
+
+// Compile one program and evaluate it into dense rows [n_shards][16][1024 words] at
+// ctx->d_dense with per-container cardinalities at ctx->d_dense_n. Leaves timing open:
+// the caller records ev1.
+int eval_dense(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards, BatchDev& bd) {
+  Compiled cp;
+  Compiler cc(ctx, cp);
+  if (!cc.compile(prog, n_nodes)) return fail(ctx, PB200_ERR_INVALID, cc.err);
+  TRY(sync_families(ctx));
+  TRY(upload_batch(ctx, cp, shards, n_shards, bd));
+  const size_t items = size_t(n_shards) * kRowContainers;
+  TRY(ensure_dev(ctx, ctx->d_dense, items * kBitmapBytes));
+  TRY(ensure_dev(ctx, ctx->d_dense_n, items * 4));
+  if (cp.n_temp_slots) TRY(ensure_dev(ctx, ctx->d_temp, size_t(cp.n_temp_slots) * items * kBitmapBytes));
+  TRY(run_pretasks(ctx, cp, bd, n_shards));
+  return launch_eval(ctx, bd, bd.progs, 1, n_shards, true, nullptr, 0, 0, static_cast<uint8_t*>(ctx->d_dense.p), static_cast<uint32_t*>(ctx->d_dense_n.p));
+}
+
+int eval_one_shard(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, std::vector<uint64_t>& words, std::vector<uint32_t>& ns) {
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  timing_begin(ctx);
+  BatchDev bd{};
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  TRY(eval_dense(ctx, prog, n_nodes, &shard, 1, bd));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  words.resize(size_t(kRowContainers) * kBitmapWords);
+  ns.resize(kRowContainers);
+  CUDA_TRY(ctx, cudaMemcpyAsync(words.data(), ctx->d_dense.p, words.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ns.data(), ctx->d_dense_n.p, ns.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  TRY(finish_call(ctx));
+  ctx->timing.d2h_bytes += words.size() * 8 + ns.size() * 4;
+  return PB200_OK;
+}
+
+}  // namespace
+
+extern "C" int pb200_eval(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, void* out, size_t cap, size_t* out_len) {
+  ENTER(ctx);
+  if (!out_len) return PB200_ERR_INVALID;
+  std::vector<uint64_t> words;
+  std::vector<uint32_t> ns;
+  TRY(eval_one_shard(ctx, prog, n_nodes, shard, words, ns));
+  // encode: containers optimize()d, keys shard*16 + c (fragment.go:629 OffsetRange re-keying)
+  std::vector<HostContainer> cs;
+  for (int c = 0; c < kRowContainers; c++) {
+    if (!ns[c]) continue;
+    HostContainer hc;
+    hc.key = shard * kRowContainers + c;
+    from_words(words.data() + size_t(c) * kBitmapWords, hc);
+    cs.push_back(std::move(hc));
+    cs.back().data = cs.back().owned.data();
+  }
+  std::vector<uint8_t> bytes;
+  serialize_containers(cs, bytes);
+  *out_len = bytes.size();
+  if (!out) return PB200_OK;
+  if (cap < bytes.size()) return fail(ctx, PB200_ERR_RANGE, "output buffer too small");
+  std::memcpy(out, bytes.data(), bytes.size());
+  return PB200_OK;
+}
+
+extern "C" int pb200_eval_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, uint64_t* out_cols, size_t cap, size_t* out_n) {
+  ENTER(ctx);
+  if (!out_n) return PB200_ERR_INVALID;
+  std::vector<uint64_t> words;
+  std::vector<uint32_t> ns;
+  TRY(eval_one_shard(ctx, prog, n_nodes, shard, words, ns));
+  size_t total = 0;
+  for (uint32_t n : ns) total += n;
+  *out_n = total;
+  if (!out_cols) return PB200_OK;
+  if (cap < total) return fail(ctx, PB200_ERR_RANGE, "output buffer too small");
+  size_t k = 0;
+  const uint64_t base = shard * PB200_SHARD_WIDTH;
+  for (size_t w = 0; w < words.size(); w++) {
+    uint64_t v = words[w];
+    while (v) { out_cols[k++] = base + w * 64 + __builtin_ctzll(v); v &= v - 1; }
+  }
+  return PB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// TopN
+// ---------------------------------------------------------------------------------------
+namespace {
+
+struct HPair { uint64_t id, count; };
+
+// Go's container/heap over pairHeap (cache.go:331-353: min-heap on Count). The order in
+// which fragment.top pops its results depends on these exact sift rules.
+struct PairHeap {
+  std::vector<HPair> a;
+  bool less(int i, int j) const { return a[i].count < a[j].count; }
+  void up(int j) { for (;;) { int i = (j - 1) / 2; if (i == j || !less(j, i)) break; std::swap(a[i], a[j]); j = i; } }
+  void down(int i0, int n) {
+    int i = i0;
+    for (;;) {
+      int j1 = 2 * i + 1;
+      if (j1 >= n || j1 < 0) break;
+      int j = j1;
+      if (int j2 = j1 + 1; j2 < n && less(j2, j1)) j = j2;
+      if (!less(j, i)) break;
+      std::swap(a[i], a[j]);
+      i = j;
+    }
+  }
+  void push(HPair p) { a.push_back(p); up(int(a.size()) - 1); }
+  HPair pop() { int n = int(a.size()) - 1; std::swap(a[0], a[n]); down(0, n); HPair p = a.back(); a.pop_back(); return p; }
+};
+
+void sort_pairs(std::vector<HPair>& p) {  // count desc; ties by ascending id (deterministic refinement of sort.Sort)
+  std::stable_sort(p.begin(), p.end(), [](const HPair& x, const HPair& y) { return x.count != y.count ? x.count > y.count : x.id < y.id; });
+}
+
+// fragment.top (fragment.go:1568-1700) over candidate pairs whose src-intersection counts
+// are already known (`isect[k]`, ignored when !has_src).
+std::vector<HPair> top_walk(const std::vector<HPair>& pairs, const uint32_t* isect, bool has_src, int n, uint64_t min_threshold,
+                            uint64_t tanimoto, uint64_t src_count) {
+  double min_tan = 0, max_tan = 0;
+  if (tanimoto > 0 && has_src) {
+    min_tan = double(src_count * tanimoto) / 100;
+    max_tan = double(src_count * 100) / double(tanimoto);
+  } else {
+    tanimoto = 0;
+  }
+  PairHeap results;
+  for (size_t k = 0; k < pairs.size(); k++) {
+    const uint64_t row_id = pairs[k].id, cnt = pairs[k].count;
+    if (cnt == 0) continue;
+    if (tanimoto > 0) { if (double(cnt) <= min_tan || double(cnt) >= max_tan) continue; }
+    else if (cnt < min_threshold) continue;
+    if (n == 0 || int(results.a.size()) < n) {
+      uint64_t count = has_src ? isect[k] : cnt;
+      if (count == 0) continue;
+      if (tanimoto > 0) {
+        double t = std::ceil(double(count * 100) / double(cnt + src_count - count));
+        if (t <= double(tanimoto)) continue;
+      } else if (count < min_threshold) continue;
+      results.push({row_id, count});
+      if (n > 0 && int(results.a.size()) == n && !has_src) break;
+      continue;
+    }
+    const uint64_t threshold = results.a[0].count;
+    if (threshold < min_threshold || cnt < threshold) break;
+    const uint64_t count = isect[k];
+    if (count < threshold) continue;
+    results.push({row_id, count});
+  }
+  std::vector<HPair> r(results.a.size());
+  size_t x = r.size(), i = 1;
+  while (!results.a.empty()) { r[x - i] = results.pop(); i++; }
+  return r;
+}
+
+uint64_t exact_row_count(const Fragment& f, uint64_t id) {
+  auto it = std::lower_bound(f.row_ids.begin(), f.row_ids.end(), id);
+  if (it == f.row_ids.end() || *it != id) return 0;
+  return f.row_counts[size_t(it - f.row_ids.begin())];
+}
+
+struct FragRankDev {  // lazily uploaded rank -> row-index table of one fragment
+  uint32_t* d = nullptr;
+  size_t n = 0;
+};
+
+// One TopN pass over `shards` (executor.go:905-930 executeTopNShards without the final sort):
+// per-shard fragment.top results.
+int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, uint32_t n_src_nodes, uint32_t n,
+              const uint64_t* ids, size_t n_ids, uint64_t min_threshold, uint64_t tanimoto, const uint64_t* shards,
+              uint32_t n_shards, std::vector<std::vector<HPair>>& per_shard) {
+  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
+  if (tanimoto > 100) return fail(ctx, PB200_ERR_INVALID, "Tanimoto Threshold is from 1 to 100 only");  // executor.go:988
+  if (min_threshold == 0) min_threshold = 1;  // defaultMinThreshold, executor.go:37,984
+  Family& fam = ctx->families[family];
+  const bool has_src = src_prog && n_src_nodes;
+  per_shard.assign(n_shards, {});
+  if (n_shards == 0) return PB200_OK;
+
+  // candidate pairs per shard (topBitmapPairs, fragment.go:1702-1738)
+  std::vector<std::vector<HPair>> cands(n_shards);
+  std::vector<const Fragment*> frs(n_shards, nullptr);
+  for (uint32_t s = 0; s < n_shards; s++) {
+    auto it = fam.frags.find(shards[s]);
+    if (it == fam.frags.end()) continue;
+    const Fragment& f = it->second;
+    frs[s] = &f;
+    auto& cd = cands[s];
+    if (n_ids == 0) {
+      cd.resize(f.rank_ids.size());
+      for (size_t k = 0; k < cd.size(); k++) cd[k] = {f.rank_ids[k], f.rank_counts[k]};
+    } else {
+      std::unordered_map<uint64_t, uint64_t> cache;
+      if (f.rank_from_host) for (size_t k = 0; k < f.rank_ids.size(); k++) cache[f.rank_ids[k]] = f.rank_counts[k];
+      for (size_t k = 0; k < n_ids; k++) {
+        uint64_t c = 0;
+        if (f.rank_from_host) { auto ci = cache.find(ids[k]); if (ci != cache.end()) c = ci->second; }
+        if (c == 0) c = exact_row_count(f, ids[k]);
+        if (c > 0) cd.push_back({ids[k], c});
+      }
+      sort_pairs(cd);
+    }
+  }
+
+  std::vector<uint32_t> isect;             // flattened per-candidate src intersection counts
+  std::vector<uint64_t> off(n_shards + 1, 0);
+  std::vector<uint64_t> src_counts(n_shards, 0);
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  timing_begin(ctx);
+  if (has_src) {
+    BatchDev bd{};
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    TRY(eval_dense(ctx, src_prog, n_src_nodes, shards, n_shards, bd));
+    // candidate tables on the device
+    for (uint32_t s = 0; s < n_shards; s++) off[s + 1] = off[s] + cands[s].size();
+    const uint64_t total = off[n_shards];
+    // layout in d_topn: [counts u32 x total][cand_off u64 x ns][rank_n u32 x ns][ptrs x ns][rowidx / ids ...]
+    size_t o_counts = 0;
+    size_t o_off = align_up(o_counts + total * 4, 16);
+    size_t o_n = o_off + size_t(n_shards) * 8;
+    size_t o_ptr = align_up(o_n + size_t(n_shards) * 4, 16);
+    size_t o_idx = o_ptr + size_t(n_shards) * 8;
+    size_t idx_bytes = n_ids ? n_ids * 8 : total * 4;
+    size_t total_bytes = o_idx + idx_bytes;
+    TRY(ensure_dev(ctx, ctx->d_topn, total_bytes));
+    TRY(ensure_pin(ctx, ctx->h_out, std::max<size_t>(total_bytes, size_t(n_shards) * kRowContainers * 4)));
+    uint8_t* h = static_cast<uint8_t*>(ctx->h_out.p);
+    uint8_t* d = static_cast<uint8_t*>(ctx->d_topn.p);
+    std::memcpy(h + o_off, off.data(), size_t(n_shards) * 8);
+    auto* hn = reinterpret_cast<uint32_t*>(h + o_n);
+    auto* hp = reinterpret_cast<const uint32_t**>(h + o_ptr);
+    if (n_ids) {
+      std::memcpy(h + o_idx, ids, n_ids * 8);
+      for (uint32_t s = 0; s < n_shards; s++) { hn[s] = 0; hp[s] = nullptr; }
+    } else {
+      auto* hidx = reinterpret_cast<uint32_t*>(h + o_idx);
+      for (uint32_t s = 0; s < n_shards; s++) {
+        hn[s] = uint32_t(cands[s].size());
+        hp[s] = reinterpret_cast<const uint32_t*>(d + o_idx) + off[s];
+        const Fragment* f = frs[s];
+        for (size_t k = 0; k < cands[s].size(); k++) {
+          const uint64_t id = cands[s][k].id;
+          uint32_t ri;
+          if (f->dev.dense) ri = id < f->dev.nrows ? uint32_t(id) : 0xffffffffu;
+          else {
+            auto it = std::lower_bound(f->row_ids.begin(), f->row_ids.end(), id);
+            ri = (it != f->row_ids.end() && *it == id) ? uint32_t(it - f->row_ids.begin()) : 0xffffffffu;
+          }
+          hidx[off[s] + k] = ri;
+        }
+      }
+    }
+    CUDA_TRY(ctx, cudaMemcpyAsync(d + o_off, h + o_off, total_bytes - o_off, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->timing.h2d_bytes += total_bytes - o_off;
+    const size_t n_counts = n_ids ? size_t(n_shards) * n_ids : total;
+    if (n_ids) TRY(ensure_dev(ctx, ctx->d_bsi, n_counts * 4));
+    uint32_t* d_counts = n_ids ? static_cast<uint32_t*>(ctx->d_bsi.p) : reinterpret_cast<uint32_t*>(d + o_counts);
+    CUDA_TRY(ctx, cudaMemsetAsync(d_counts, 0, std::max<size_t>(n_counts * 4, 4), ctx->stream));
+    TopnParams tp{};
+    tp.families = ctx->d_families; tp.family = family; tp.shards = bd.shards; tp.n_shards = n_shards;
+    tp.src_dense = static_cast<const uint8_t*>(ctx->d_dense.p);
+    tp.rank_rowidx = reinterpret_cast<const uint32_t* const*>(d + o_ptr);
+    tp.rank_n = reinterpret_cast<const uint32_t*>(d + o_n);
+    tp.cand_off = reinterpret_cast<const uint64_t*>(d + o_off);
+    tp.ids = n_ids ? reinterpret_cast<const uint64_t*>(d + o_idx) : nullptr;
+    tp.n_ids = uint32_t(n_ids);
+    tp.counts = d_counts;
+    tp.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 8);
+    if (n_counts) {
+      const uint32_t items = n_shards * kRowContainers;
+      const uint32_t grid = std::min<uint32_t>(items, uint32_t(ctx->sm_count) * 8);
+      topn_count_kernel<<<grid, kTopnThreads, 0, ctx->stream>>>(tp);
+      ctx->timing.launches++;
+      CUDA_TRY(ctx, cudaGetLastError());
+    }
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    isect.resize(std::max<size_t>(n_counts, 1));
+    std::vector<uint32_t> dn(size_t(n_shards) * kRowContainers);
+    if (n_counts) CUDA_TRY(ctx, cudaMemcpyAsync(isect.data(), d_counts, n_counts * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(dn.data(), ctx->d_dense_n.p, dn.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    TRY(finish_call(ctx));
+    ctx->timing.d2h_bytes += n_counts * 4 + dn.size() * 4;
+    for (uint32_t s = 0; s < n_shards; s++)
+      for (int c = 0; c < kRowContainers; c++) src_counts[s] += dn[size_t(s) * kRowContainers + c];
+  }
+
+  // per-shard selection walk
+  std::vector<uint32_t> tmp;
+  for (uint32_t s = 0; s < n_shards; s++) {
+    if (!frs[s]) continue;
+    const uint32_t* is = nullptr;
+    if (has_src) {
+      if (n_ids) {
+        // device counts are laid out in `ids` order; candidates were re-sorted by count
+        tmp.resize(cands[s].size());
+        std::unordered_map<uint64_t, uint32_t> pos;
+        for (size_t k = 0; k < n_ids; k++) pos.emplace(ids[k], uint32_t(k));
+        for (size_t k = 0; k < cands[s].size(); k++) tmp[k] = isect[size_t(s) * n_ids + pos[cands[s][k].id]];
+        is = tmp.data();
+      } else {
+        is = isect.data() + off[s];
+      }
+    }
+    per_shard[s] = top_walk(cands[s], is, has_src, n_ids ? 0 : int(n), min_threshold, tanimoto, src_counts[s]);
+  }
+  return PB200_OK;
+}
+
+std::vector<HPair> merge_pairs(const std::vector<std::vector<HPair>>& per_shard) {  // Pairs.Add (cache.go:356-374) + sort
+  std::unordered_map<uint64_t, uint64_t> m;
+  for (auto& v : per_shard) for (auto& p : v) m[p.id] += p.count;
+  std::vector<HPair> out;
+  out.reserve(m.size());
+  for (auto& kv : m) out.push_back({kv.first, kv.second});
+  std::sort(out.begin(), out.end(), [](const HPair& x, const HPair& y) { return x.id < y.id; });
+  sort_pairs(out);
+  return out;
+}
+
+int write_pairs(pb200_ctx* ctx, const std::vector<HPair>& v, pb200_pair* out, size_t cap, size_t* n_out) {
+  if (!n_out) return PB200_ERR_INVALID;
+  *n_out = v.size();
+  if (v.size() > cap) return fail(ctx, PB200_ERR_RANGE, "pair buffer too small");
+  for (size_t i = 0; i < v.size(); i++) { out[i].id = v[i].id; out[i].count = v[i].count; }
+  return PB200_OK;
+}
+
+}  // namespace
+
+extern "C" int pb200_topn_shard(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, uint32_t n_src_nodes, uint32_t n,
+                                const uint64_t* ids, size_t n_ids, uint64_t min_threshold, uint64_t tanimoto_threshold,
+                                uint64_t shard, pb200_pair* out, size_t cap, size_t* n_out) {
+  ENTER(ctx);
+  if (n_ids && !ids) return PB200_ERR_INVALID;
+  std::vector<std::vector<HPair>> per;
+  TRY(topn_pass(ctx, family, src_prog, n_src_nodes, n, ids, n_ids, min_threshold, tanimoto_threshold, &shard, 1, per));
+  return write_pairs(ctx, per[0], out, cap, n_out);
+}
+
+extern "C" int pb200_topn(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, uint32_t n_src_nodes, uint32_t n,
+                          const uint64_t* ids, size_t n_ids, uint64_t min_threshold, uint64_t tanimoto_threshold, uint32_t flags,
+                          const uint64_t* shards, uint32_t n_shards, pb200_pair* out, size_t cap, size_t* n_out) {
+  ENTER(ctx);
+  if (n_ids && !ids) return PB200_ERR_INVALID;
+  TRY(validate_shards(ctx, shards, n_shards));
+  std::vector<std::vector<HPair>> per;
+  TRY(topn_pass(ctx, family, src_prog, n_src_nodes, n, ids, n_ids, min_threshold, tanimoto_threshold, shards, n_shards, per));
+  std::vector<HPair> pairs = merge_pairs(per);
+  if (pairs.empty() || n_ids > 0 || (flags & PB200_TOPN_REMOTE)) return write_pairs(ctx, pairs, out, cap, n_out);  // executor.go:884-887
+  // second pass with the candidate ids of pass 1 (executor.go:889-902)
+  pb200_timing t1 = ctx->timing;
+  std::vector<uint64_t> ids2;
+  for (auto& p : pairs) ids2.push_back(p.id);
+  std::sort(ids2.begin(), ids2.end());
+  TRY(topn_pass(ctx, family, src_prog, n_src_nodes, n, ids2.data(), ids2.size(), min_threshold, tanimoto_threshold, shards, n_shards, per));
+  ctx->timing.kernel_ms += t1.kernel_ms; ctx->timing.algo_bytes += t1.algo_bytes; ctx->timing.launches += t1.launches;
+  ctx->timing.h2d_bytes += t1.h2d_bytes; ctx->timing.d2h_bytes += t1.d2h_bytes;
+  std::vector<HPair> trimmed = merge_pairs(per);
+  if (n != 0 && n < trimmed.size()) trimmed.resize(n);
+  return write_pairs(ctx, trimmed, out, cap, n_out);
+}
+
+// ---------------------------------------------------------------------------------------
+// BSI aggregates
+// ---------------------------------------------------------------------------------------
+namespace {
+
+// Prepares the optional filter of a BSI aggregate: a plain Row() leaf is used in place,
+// anything else is evaluated into temp slot 0.
+int bsi_prepare(pb200_ctx* ctx, pb200_family fam, uint32_t bit_depth, const pb200_node* filt, uint32_t nf, const uint64_t* shards,
+                uint32_t n_shards, BsiParams& p, BatchDev& bd) {
+  if (fam >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
+  if (bit_depth > 63) return fail(ctx, PB200_ERR_INVALID, "bit depth > 63");
+  TRY(validate_shards(ctx, shards, n_shards));
+  Compiled cp;
+  Compiler cc(ctx, cp);
+  const bool has_filter = filt && nf;
+  bool direct = false;
+  if (has_filter) {
+    if (!cc.compile(filt, nf)) return fail(ctx, PB200_ERR_INVALID, cc.err);
+    direct = cp.pre.empty() && cp.progs[0].n_instr == 1 && cp.leaves[cp.progs[0].leaf_off + cp.instrs[cp.progs[0].instr_off].leaf].kind != L_TEMP;
+  }
+  TRY(sync_families(ctx));
+  TRY(upload_batch(ctx, cp, shards, n_shards, bd));
+  p = BsiParams{};
+  p.families = ctx->d_families; p.family = fam; p.bit_depth = bit_depth;
+  p.shards = bd.shards; p.n_shards = n_shards;
+  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 8);
+  if (has_filter) {
+    p.has_filter = 1;
+    if (direct) {
+      p.filter = cp.leaves[cp.progs[0].leaf_off + cp.instrs[cp.progs[0].instr_off].leaf];
+    } else {
+      // evaluate into one extra temp slot placed after the program's own temps
+      const uint32_t slot = cp.n_temp_slots;
+      TRY(ensure_dev(ctx, ctx->d_temp, size_t(slot + 1) * n_shards * kRowContainers * kBitmapBytes));
+      TRY(run_pretasks(ctx, cp, bd, n_shards));
+      TRY(launch_eval(ctx, bd, bd.progs, 1, n_shards, true, nullptr, 0, 0, temp_slot(ctx, slot, n_shards), nullptr));
+      p.filter.kind = L_TEMP; p.filter.family = slot; p.filter.row = 0;
+    }
+    p.temp_base = static_cast<const uint8_t*>(ctx->d_temp.p);
+  }
+  return PB200_OK;
+}
+
+int bsi_minmax_impl(pb200_ctx* ctx, pb200_family fam, uint32_t bit_depth, const pb200_node* filt, uint32_t nf, int is_max,
+                    const uint64_t* shards, uint32_t n_shards, std::vector<int64_t>& vals, std::vector<uint64_t>& counts) {
+  vals.assign(n_shards, 0);
+  counts.assign(n_shards, 0);
+  if (n_shards == 0) return PB200_OK;
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  timing_begin(ctx);
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  BsiParams p; BatchDev bd{};
+  TRY(bsi_prepare(ctx, fam, bit_depth, filt, nf, shards, n_shards, p, bd));
+  TRY(ensure_dev(ctx, ctx->d_bsi, size_t(n_shards) * 16));
+  p.is_max = is_max ? 1 : 0;
+  p.mm_val = static_cast<long long*>(ctx->d_bsi.p);
+  p.mm_count = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_bsi.p) + size_t(n_shards) * 8);
+  const int smem = kRowContainers * kBitmapBytes;
+  if (!ctx->mm_attr_set) { CUDA_TRY(ctx, cudaFuncSetAttribute(bsi_minmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); ctx->mm_attr_set = true; }
+  const uint32_t grid = std::min<uint32_t>(n_shards, uint32_t(ctx->sm_count) * 4);
+  bsi_minmax_kernel<<<grid, kMmThreads, smem, ctx->stream>>>(p);
+  ctx->timing.launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(vals.data(), p.mm_val, size_t(n_shards) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(counts.data(), p.mm_count, size_t(n_shards) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  TRY(finish_call(ctx));
+  ctx->timing.d2h_bytes += size_t(n_shards) * 16;
+  return PB200_OK;
+}
+
+int bsi_minmax_reduce(pb200_ctx* ctx, pb200_family fam, uint32_t bit_depth, const pb200_node* filt, uint32_t nf, int is_max,
+                      const uint64_t* shards, uint32_t n_shards, int64_t* out_val, uint64_t* out_count) {
+  if (!out_val || !out_count) return PB200_ERR_INVALID;
+  std::vector<int64_t> vals; std::vector<uint64_t> counts;
+  TRY(bsi_minmax_impl(ctx, fam, bit_depth, filt, nf, is_max, shards, n_shards, vals, counts));
+  // ValCount.smaller / larger (executor.go:3010-3029), folded in shard-list order
+  int64_t v = 0; uint64_t c = 0;
+  for (uint32_t s = 0; s < n_shards; s++) {
+    const bool take = c == 0 || ((is_max ? vals[s] > v : vals[s] < v) && counts[s] > 0);
+    if (take) { v = vals[s]; c = counts[s]; }
+  }
+  if (c == 0) v = 0;  // executor.go:470-472,506-508
+  *out_val = v; *out_count = c;
+  return PB200_OK;
+}
+
+}  // namespace
+
+extern "C" int pb200_bsi_sum(pb200_ctx* ctx, pb200_family bsi_family, uint32_t bit_depth, const pb200_node* filter_prog, uint32_t n_filter_nodes,
+                             uint32_t flags, const uint64_t* shards, uint32_t n_shards, int64_t* out_sum, uint64_t* out_count) {
+  ENTER(ctx);
+  if (!out_sum || !out_count) return PB200_ERR_INVALID;
+  *out_sum = 0; *out_count = 0;
+  if (n_shards == 0) return PB200_OK;
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  timing_begin(ctx);
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  BsiParams p; BatchDev bd{};
+  TRY(bsi_prepare(ctx, bsi_family, bit_depth, filter_prog, n_filter_nodes, shards, n_shards, p, bd));
+  const size_t n_acc = 2 * size_t(kMaxDepth) + 1;
+  TRY(ensure_dev(ctx, ctx->d_bsi, n_acc * 8));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_bsi.p, 0, n_acc * 8, ctx->stream));
+  p.strict = (flags & PB200_SUM_STRICT) ? 1 : 0;
+  p.sum_acc = static_cast<unsigned long long*>(ctx->d_bsi.p);
+  const uint32_t items = n_shards * kRowContainers;
+  const uint32_t grid = std::min<uint32_t>(items, uint32_t(ctx->sm_count) * 6);
+  bsi_sum_kernel<<<grid, kBsiThreads, 0, ctx->stream>>>(p);
+  ctx->timing.launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  std::vector<unsigned long long> acc(n_acc);
+  CUDA_TRY(ctx, cudaMemcpyAsync(acc.data(), ctx->d_bsi.p, n_acc * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  TRY(finish_call(ctx));
+  ctx->timing.d2h_bytes += n_acc * 8;
+  // sum = SUM_i 2^i * (|B_i & prow| - |B_i & nrow|) in wrapping 64-bit arithmetic (fragment.go:1130-1138)
+  uint64_t sum = 0;
+  for (uint32_t i = 0; i < bit_depth; i++) sum += (uint64_t(1) << i) * acc[1 + 2 * i] - (uint64_t(1) << i) * acc[2 + 2 * i];
+  *out_count = acc[0];
+  *out_sum = acc[0] ? int64_t(sum) : 0;  // executor.go:438-440: {0,0} when count is 0
+  return PB200_OK;
+}
+
+extern "C" int pb200_bsi_min(pb200_ctx* ctx, pb200_family bsi_family, uint32_t bit_depth, const pb200_node* filter_prog, uint32_t n_filter_nodes,
+                             const uint64_t* shards, uint32_t n_shards, int64_t* out_val, uint64_t* out_count) {
+  ENTER(ctx);
+  return bsi_minmax_reduce(ctx, bsi_family, bit_depth, filter_prog, n_filter_nodes, 0, shards, n_shards, out_val, out_count);
+}
+
+extern "C" int pb200_bsi_max(pb200_ctx* ctx, pb200_family bsi_family, uint32_t bit_depth, const pb200_node* filter_prog, uint32_t n_filter_nodes,
+                             const uint64_t* shards, uint32_t n_shards, int64_t* out_val, uint64_t* out_count) {
+  ENTER(ctx);
+  return bsi_minmax_reduce(ctx, bsi_family, bit_depth, filter_prog, n_filter_nodes, 1, shards, n_shards, out_val, out_count);
+}
+
+extern "C" int pb200_bsi_minmax_shards(pb200_ctx* ctx, pb200_family bsi_family, uint32_t bit_depth, const pb200_node* filter_prog, uint32_t n_filter_nodes,
+                                       int is_max, const uint64_t* shards, uint32_t n_shards, int64_t* out_vals, uint64_t* out_counts) {
+  ENTER(ctx);
+  if (n_shards && (!out_vals || !out_counts)) return PB200_ERR_INVALID;
+  std::vector<int64_t> vals; std::vector<uint64_t> counts;
+  TRY(bsi_minmax_impl(ctx, bsi_family, bit_depth, filter_prog, n_filter_nodes, is_max, shards, n_shards, vals, counts));
+  std::copy(vals.begin(), vals.end(), out_vals);
+  std::copy(counts.begin(), counts.end(), out_counts);
+  return PB200_OK;
+}

@@ -1,0 +1,408 @@
+// CUDA kernels (sm_100a) for the per-shard bitmap query hot path. No tensor cores: the
+// work is HBM-bound integer/bit arithmetic (AND/OR/XOR/ANDNOT + popcount), so the design
+// rules are 128-bit coalesced loads, enough bytes in flight per SM, shared-memory staging
+// for array/run containers and grids sized in multiples of the SM count.
+//
+// Work decomposition: one ITEM = (query q, shard s, container column c) = the <= N
+// containers (one per operand row) that share key&15 == c in one shard — the unit
+// roaring.Bitmap.Intersect/Union/... merge-join on (roaring.go:593-941). Because every
+// row of a fragment occupies exactly 16 consecutive container keys, the merge-join
+// degenerates to a 16-slot gather from the row tables (layout.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "layout.h"
+
+namespace pb200 {
+
+struct EvalParams {
+  const FamilyDev* families;
+  uint32_t n_families;
+  const Prog* progs;
+  const Instr* instrs;
+  const Leaf* leaves;
+  const uint64_t* shards;
+  uint32_t n_shards;
+  uint32_t n_queries;
+  const uint8_t* temp_base;        // dense temp rows: ((slot * n_shards + s) * 16 + c) * 8192
+  unsigned long long* out_counts;  // out[q * out_qstride + s * out_sstride] += popcount (may be null)
+  uint32_t out_qstride, out_sstride;
+  uint8_t* dense_out;              // optional: ((q * n_shards + s) * 16 + c) * 8192 bytes of result words
+  uint32_t* dense_n;               // optional: cardinality per (q, s, c)
+  uint32_t* slow_list;             // scratch: items the fast kernel defers to the staged kernel
+  uint32_t* slow_count;
+  unsigned long long* algo_bytes;  // accumulated algorithmic bytes (payload + 16 B / container)
+};
+
+// ---------------------------------------------------------------------------------------
+// leaf resolution: (family, row) x shard x column -> ContainerDesc. Replaces
+// Holder.fragment (holder.go:496) + fragment.row -> Bitmap.OffsetRange (roaring.go:535).
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ ContainerDesc resolve_leaf(const EvalParams& p, const Leaf& lf, uint32_t s, uint32_t c) {
+  ContainerDesc d;
+  d.addr = 0; d.n = 0; d.meta = 0;
+  if (lf.kind == L_ZERO) return d;
+  if (lf.kind == L_TEMP) {
+    d.addr = reinterpret_cast<uint64_t>(p.temp_base) + ((uint64_t(lf.family) * p.n_shards + s) * kRowContainers + c) * kBitmapBytes;
+    d.n = 1;  // unknown, non-zero
+    d.meta = make_meta(kBitmap, kBitmapWords);
+    return d;
+  }
+  if (lf.family >= p.n_families) return d;
+  const FamilyDev fam = p.families[lf.family];
+  const uint64_t shard = p.shards[s];
+  if (shard >= fam.cap) return d;
+  const FragDev f = fam.frags[shard];
+  if (f.nrows == 0) return d;
+  uint64_t idx;
+  if (f.dense) {
+    if (lf.row >= f.nrows) return d;
+    idx = lf.row;
+  } else {
+    uint32_t lo = 0, hi = f.nrows;
+    while (lo < hi) {
+      uint32_t mid = (lo + hi) >> 1;
+      if (f.row_ids[mid] < lf.row) lo = mid + 1; else hi = mid;
+    }
+    if (lo >= f.nrows || f.row_ids[lo] != lf.row) return d;
+    idx = lo;
+  }
+  return f.rows[idx * kRowContainers + c];
+}
+
+__device__ __forceinline__ bool is_const_or_bitmap(const ContainerDesc& d) {
+  return d.n == 0 || d.n == kFullN || desc_type(d) == kBitmap;
+}
+
+__device__ __forceinline__ uint32_t desc_algo_bytes(const ContainerDesc& d) {
+  if (d.n == 0) return 0;
+  uint32_t t = desc_type(d), l = desc_len(d);
+  return 16u + (t == kBitmap ? uint32_t(kBitmapBytes) : t == kArray ? l * 2u : l * 4u);
+}
+
+__device__ __forceinline__ uint4 ldg128(const void* p) {
+  return __ldg(reinterpret_cast<const uint4*>(p));
+}
+// streaming load: operand payloads are read once per query — do not let them evict the
+// descriptor tables from L1/L2 (ld.global.nc.L1::no_allocate).
+__device__ __forceinline__ uint4 ldg128_stream(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint32_t popc128(const uint4& v) {
+  return __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);
+}
+__device__ __forceinline__ uint4 and128(const uint4& a, const uint4& b) { return make_uint4(a.x & b.x, a.y & b.y, a.z & b.z, a.w & b.w); }
+__device__ __forceinline__ uint4 or128(const uint4& a, const uint4& b) { return make_uint4(a.x | b.x, a.y | b.y, a.z | b.z, a.w | b.w); }
+__device__ __forceinline__ uint4 xor128(const uint4& a, const uint4& b) { return make_uint4(a.x ^ b.x, a.y ^ b.y, a.z ^ b.z, a.w ^ b.w); }
+__device__ __forceinline__ uint4 andnot128(const uint4& a, const uint4& b) { return make_uint4(a.x & ~b.x, a.y & ~b.y, a.z & ~b.z, a.w & ~b.w); }
+
+__device__ __forceinline__ uint4 apply_op(uint8_t op, const uint4& acc, const uint4& v) {
+  switch (op) {
+    case I_AND_LEAF: case I_AND_STACK: return and128(acc, v);
+    case I_OR_LEAF: case I_OR_STACK: return or128(acc, v);
+    case I_XOR_LEAF: case I_XOR_STACK: return xor128(acc, v);
+    case I_ANDNOT_LEAF: return andnot128(acc, v);   // acc \ leaf
+    case I_RANDNOT_LEAF: return andnot128(v, acc);  // leaf \ acc
+    case I_ANDNOT_STACK: return andnot128(v, acc);  // v = popped LEFT operand: left \ acc
+    default: return acc;
+  }
+}
+
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+constexpr int kFastWarps = 8;  // warps per CTA in the fast kernel
+constexpr int kUnroll = 4;     // 128-bit chunks evaluated together per lane
+
+// ---------------------------------------------------------------------------------------
+// K1 / K6-fast: one WARP per item. Handles every item whose operand containers are all
+// bitmap, empty or full: the program is evaluated word-parallel straight out of global
+// memory with 128-bit loads (16 chunks per lane per container), popcounted and
+// warp-reduced; one atomicAdd per item. Items with array/run operands are appended to
+// the slow list for eval_staged_kernel. Also covers intersectionCountBitmapBitmap
+// (roaring.go:3212, :5061) and the full/empty shortcuts (roaring.go:3079-3087).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kFastWarps * 32) eval_fast_kernel(EvalParams p) {
+  __shared__ ContainerDesc s_desc[kFastWarps][kMaxLeaves];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint64_t n_items = uint64_t(p.n_queries) * p.n_shards * kRowContainers;
+  const uint64_t warp_stride = uint64_t(gridDim.x) * kFastWarps;
+  unsigned long long bytes_acc = 0;
+
+  for (uint64_t item = uint64_t(blockIdx.x) * kFastWarps + warp; item < n_items; item += warp_stride) {
+    const uint32_t c = uint32_t(item & 15);
+    const uint64_t qs = item >> 4;
+    const uint32_t s = uint32_t(qs % p.n_shards);
+    const uint32_t q = uint32_t(qs / p.n_shards);
+    const Prog pg = p.progs[q];
+    const Instr* ins = p.instrs + pg.instr_off;
+
+    // resolve leaves (lane l -> leaf l)
+    bool ok = true;
+    uint32_t bytes = 0;
+    if (lane < pg.n_leaves) {
+      ContainerDesc d = resolve_leaf(p, p.leaves[pg.leaf_off + lane], s, c);
+      s_desc[warp][lane] = d;
+      ok = is_const_or_bitmap(d);
+      bytes = desc_algo_bytes(d);
+    }
+    const bool all_ok = __all_sync(0xffffffffu, ok);
+    bytes = warp_sum(bytes);
+    if (lane == 0) bytes_acc += bytes;
+    __syncwarp();
+
+    if (!all_ok) {
+      if (lane == 0) p.slow_list[atomicAdd(p.slow_count, 1u)] = uint32_t(item);
+      __syncwarp();
+      continue;
+    }
+
+    uint32_t cnt = 0;
+    const bool want_dense = p.dense_out != nullptr;
+    uint8_t* dout = want_dense ? p.dense_out + item * kBitmapBytes : nullptr;
+
+    if (!want_dense && pg.n_instr == 1) {
+      // Count(Row): cardinality straight from the descriptor (roaring.go:405 Count = sum of n).
+      // (L_TEMP leaves carry no cardinality, so they take the generic path.)
+      const ContainerDesc d = s_desc[warp][ins[0].leaf];
+      if (!(d.n == 1 && desc_type(d) == kBitmap && p.leaves[pg.leaf_off + ins[0].leaf].kind == L_TEMP)) {
+        if (lane == 0 && p.out_counts && d.n) atomicAdd(p.out_counts + uint64_t(q) * p.out_qstride + uint64_t(s) * p.out_sstride, (unsigned long long)d.n);
+        __syncwarp();
+        continue;
+      }
+    }
+
+    if (!want_dense && pg.n_instr == 2 && ins[1].op == I_AND_LEAF) {
+      // ---- 2-operand intersect: the headline Count(Intersect(Row, Row)) path ----
+      const ContainerDesc a = s_desc[warp][ins[0].leaf], b = s_desc[warp][ins[1].leaf];
+      const bool a_temp = p.leaves[pg.leaf_off + ins[0].leaf].kind == L_TEMP;
+      const bool b_temp = p.leaves[pg.leaf_off + ins[1].leaf].kind == L_TEMP;
+      if (a.n == 0 || b.n == 0) { __syncwarp(); continue; }
+      if (a.n == kFullN && !b_temp) cnt = (lane == 0) ? b.n : 0;        // roaring.go:3079
+      else if (b.n == kFullN && !a_temp) cnt = (lane == 0) ? a.n : 0;   // roaring.go:3082
+      else {
+        const uint4* pa = reinterpret_cast<const uint4*>(a.addr) + lane;
+        const uint4* pb = reinterpret_cast<const uint4*>(b.addr) + lane;
+        const bool fa = a.n == kFullN, fb = b.n == kFullN;
+        const uint4 ones = make_uint4(~0u, ~0u, ~0u, ~0u);
+#pragma unroll
+        for (int k0 = 0; k0 < 16; k0 += 8) {
+          uint4 va[8], vb[8];
+#pragma unroll
+          for (int k = 0; k < 8; k++) va[k] = fa ? ones : ldg128_stream(pa + (k0 + k) * 32);
+#pragma unroll
+          for (int k = 0; k < 8; k++) vb[k] = fb ? ones : ldg128_stream(pb + (k0 + k) * 32);
+#pragma unroll
+          for (int k = 0; k < 8; k++) cnt += popc128(and128(va[k], vb[k]));
+        }
+      }
+    } else {
+      // ---- generic accumulator machine over bitmap / constant leaves ----
+      for (int k0 = 0; k0 < 16; k0 += kUnroll) {
+        uint4 acc[kUnroll];
+        uint4 stack[kMaxStack][kUnroll];
+        int sp = 0;
+        bool live = false;
+        for (uint32_t i = 0; i < pg.n_instr; i++) {
+          const Instr in = ins[i];
+          uint4 v[kUnroll];
+          if (in.op <= I_RANDNOT_LEAF) {
+            const ContainerDesc d = s_desc[warp][in.leaf];
+            if (d.n == 0) {
+#pragma unroll
+              for (int k = 0; k < kUnroll; k++) v[k] = make_uint4(0, 0, 0, 0);
+            } else if (d.n == kFullN && desc_type(d) != kBitmap) {
+#pragma unroll
+              for (int k = 0; k < kUnroll; k++) v[k] = make_uint4(~0u, ~0u, ~0u, ~0u);
+            } else {
+              const uint4* ptr = reinterpret_cast<const uint4*>(d.addr) + lane;
+#pragma unroll
+              for (int k = 0; k < kUnroll; k++) v[k] = ldg128_stream(ptr + (k0 + k) * 32);
+            }
+            if (in.op == I_LOAD) {
+              if (live) {
+#pragma unroll
+                for (int k = 0; k < kUnroll; k++) stack[sp][k] = acc[k];
+                sp++;
+              }
+#pragma unroll
+              for (int k = 0; k < kUnroll; k++) acc[k] = v[k];
+              live = true;
+            } else {
+#pragma unroll
+              for (int k = 0; k < kUnroll; k++) acc[k] = apply_op(in.op, acc[k], v[k]);
+            }
+          } else {
+            sp--;
+#pragma unroll
+            for (int k = 0; k < kUnroll; k++) acc[k] = apply_op(in.op, acc[k], stack[sp][k]);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < kUnroll; k++) {
+          cnt += popc128(acc[k]);
+          if (want_dense) reinterpret_cast<uint4*>(dout)[lane + (k0 + k) * 32] = acc[k];
+        }
+      }
+    }
+    cnt = warp_sum(cnt);
+    if (lane == 0) {
+      if (p.out_counts && cnt) atomicAdd(p.out_counts + uint64_t(q) * p.out_qstride + uint64_t(s) * p.out_sstride, (unsigned long long)cnt);
+      if (p.dense_n) p.dense_n[item] = cnt;
+    }
+    __syncwarp();
+  }
+  if (lane == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+}
+
+// ---------------------------------------------------------------------------------------
+// shared-memory staging of array / run containers (K2-K5 generalised): a container is
+// expanded into a window [w0, w0 + nwords) of 64-bit words in shared memory, after which
+// every 3x3 type pair and every op of roaring.go:3078-4957 is the same word-parallel
+// boolean function. The whole CTA cooperates; the window must be pre-zeroed.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void stage_container(const ContainerDesc& d, uint32_t* win32, uint32_t w0, uint32_t nwords,
+                                                int tid, int nthreads) {
+  const uint32_t lo = w0 * 64, hi = (w0 + nwords) * 64;  // value range [lo, hi)
+  const uint32_t type = desc_type(d), len = desc_len(d);
+  if (type == kArray) {
+    const uint16_t* a = reinterpret_cast<const uint16_t*>(d.addr);
+    uint32_t b = 0, e = len;
+    if (lo > 0) {  // lower_bound(lo)
+      uint32_t l = 0, h = len;
+      while (l < h) { uint32_t m = (l + h) >> 1; if (a[m] < lo) l = m + 1; else h = m; }
+      b = l;
+    }
+    for (uint32_t i = b + tid; i < e; i += nthreads) {
+      uint32_t v = a[i];
+      if (v >= hi) break;
+      v -= lo;
+      atomicOr(&win32[v >> 5], 1u << (v & 31));
+    }
+  } else if (type == kRun) {
+    const ushort2* r = reinterpret_cast<const ushort2*>(d.addr);
+    uint32_t b = 0;
+    if (lo > 0) {  // first run with last >= lo
+      uint32_t l = 0, h = len;
+      while (l < h) { uint32_t m = (l + h) >> 1; if (r[m].y < lo) l = m + 1; else h = m; }
+      b = l;
+    }
+    for (uint32_t i = b + tid; i < len; i += nthreads) {
+      ushort2 iv = r[i];
+      uint32_t s = iv.x, l = iv.y;
+      if (s >= hi) break;
+      if (s < lo) s = lo;
+      if (l >= hi) l = hi - 1;
+      s -= lo; l -= lo;
+      uint32_t ws = s >> 5, we = l >> 5;
+      uint32_t ms = ~0u << (s & 31), me = ~0u >> (31 - (l & 31));
+      if (ws == we) atomicOr(&win32[ws], ms & me);
+      else {
+        atomicOr(&win32[ws], ms);
+        for (uint32_t k = ws + 1; k < we; k++) win32[k] = ~0u;  // interior words belong to this run only
+        atomicOr(&win32[we], me);
+      }
+    }
+  }
+}
+
+constexpr int kStagedThreads = 256;
+constexpr int kSlotWords = 4096;  // 32 KiB of staging windows per CTA
+
+// ---------------------------------------------------------------------------------------
+// K6-staged: one CTA per deferred item. Array/run operands are staged into shared-memory
+// windows (all of them at once; the column is processed in passes when more than four
+// need staging), then the accumulator machine runs word-parallel over bitmap (global),
+// staged (shared) and constant operands.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kStagedThreads) eval_staged_kernel(EvalParams p) {
+  __shared__ ContainerDesc s_desc[kMaxLeaves];
+  __shared__ int s_slot[kMaxLeaves];
+  __shared__ int s_nslots;
+  __shared__ uint32_t s_red[kStagedThreads / 32];
+  __shared__ __align__(16) uint64_t s_win[kSlotWords];
+  const int tid = threadIdx.x;
+  const uint32_t n_slow = *p.slow_count;
+
+  for (uint32_t it = blockIdx.x; it < n_slow; it += gridDim.x) {
+    const uint64_t item = p.slow_list[it];
+    const uint32_t c = uint32_t(item & 15);
+    const uint64_t qs = item >> 4;
+    const uint32_t s = uint32_t(qs % p.n_shards);
+    const uint32_t q = uint32_t(qs / p.n_shards);
+    const Prog pg = p.progs[q];
+    const Instr* ins = p.instrs + pg.instr_off;
+
+    __syncthreads();  // previous item fully consumed
+    if (tid < pg.n_leaves) s_desc[tid] = resolve_leaf(p, p.leaves[pg.leaf_off + tid], s, c);
+    __syncthreads();
+    if (tid == 0) {
+      int ns = 0;
+      for (uint32_t l = 0; l < pg.n_leaves; l++) s_slot[l] = is_const_or_bitmap(s_desc[l]) ? -1 : ns++;
+      s_nslots = ns;
+    }
+    __syncthreads();
+    const int nslots = s_nslots;
+    uint32_t chunk = kBitmapWords;
+    while (chunk * nslots > kSlotWords) chunk >>= 1;  // nslots <= 32 -> chunk >= 128
+
+    uint32_t cnt = 0;
+    uint8_t* dout = p.dense_out ? p.dense_out + item * kBitmapBytes : nullptr;
+    for (uint32_t w0 = 0; w0 < kBitmapWords; w0 += chunk) {
+      // zero + stage
+      for (uint32_t i = tid; i < chunk * nslots / 2; i += kStagedThreads) reinterpret_cast<uint4*>(s_win)[i] = make_uint4(0, 0, 0, 0);
+      __syncthreads();
+      for (uint32_t l = 0; l < pg.n_leaves; l++)
+        if (s_slot[l] >= 0) stage_container(s_desc[l], reinterpret_cast<uint32_t*>(s_win + s_slot[l] * chunk), w0, chunk, tid, kStagedThreads);
+      __syncthreads();
+      // evaluate: chunk/2 uint4 per operand
+      for (uint32_t j = tid; j < chunk / 2; j += kStagedThreads) {
+        uint4 acc = make_uint4(0, 0, 0, 0);
+        uint4 stack[kMaxStack];
+        int sp = 0;
+        bool live = false;
+        for (uint32_t i = 0; i < pg.n_instr; i++) {
+          const Instr in = ins[i];
+          if (in.op <= I_RANDNOT_LEAF) {
+            const ContainerDesc d = s_desc[in.leaf];
+            uint4 v;
+            if (d.n == 0) v = make_uint4(0, 0, 0, 0);
+            else if (s_slot[in.leaf] >= 0) v = reinterpret_cast<const uint4*>(s_win + s_slot[in.leaf] * chunk)[j];
+            else if (d.n == kFullN && desc_type(d) != kBitmap) v = make_uint4(~0u, ~0u, ~0u, ~0u);
+            else v = ldg128_stream(reinterpret_cast<const uint4*>(d.addr) + w0 / 2 + j);
+            if (in.op == I_LOAD) {
+              if (live) stack[sp++] = acc;
+              acc = v;
+              live = true;
+            } else {
+              acc = apply_op(in.op, acc, v);
+            }
+          } else {
+            acc = apply_op(in.op, acc, stack[--sp]);
+          }
+        }
+        cnt += popc128(acc);
+        if (dout) reinterpret_cast<uint4*>(dout)[w0 / 2 + j] = acc;
+      }
+      __syncthreads();
+    }
+    cnt = warp_sum(cnt);
+    if ((tid & 31) == 0) s_red[tid >> 5] = cnt;
+    __syncthreads();
+    if (tid == 0) {
+      uint32_t tot = 0;
+      for (int w = 0; w < kStagedThreads / 32; w++) tot += s_red[w];
+      if (p.out_counts && tot) atomicAdd(p.out_counts + uint64_t(q) * p.out_qstride + uint64_t(s) * p.out_sstride, (unsigned long long)tot);
+      if (p.dense_n) p.dense_n[item] = tot;
+    }
+  }
+}
+
+}  // namespace pb200

@@ -1,0 +1,287 @@
+"""ctypes binding of libpilosa_b200.so (include/pilosa_b200.h).
+
+There is no fallback of any kind: if the shared library is missing or a declared symbol is
+not exported, ``load_library`` raises; if no CUDA device is usable ``Engine()`` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+from typing import List, Optional, Sequence, Tuple
+
+from .abi import Node, Pair, Timing, u64_array
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpilosa_b200.so")
+HEADER_PATH = os.path.join(_HERE, "..", "include", "pilosa_b200.h")
+
+
+class EngineError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"pb200 status {status}: {msg}")
+        self.status = status
+
+
+def declared_symbols() -> List[str]:
+    """Every function the public header declares (used by the ABI-completeness test)."""
+    src = open(HEADER_PATH).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(pb200_[a-z0-9_]+)\s*\(", src)))
+
+
+_lib: Optional[C.CDLL] = None
+
+
+def load_library() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python __graft_entry__.py` "
+            "(nvcc -gencode arch=compute_100a,code=sm_100a). pilosa_b200 has no CPU fallback."
+        )
+    L = C.CDLL(LIB_PATH)
+    missing = [s for s in declared_symbols() if not hasattr(L, s)]
+    if missing:
+        raise ImportError(f"{LIB_PATH} does not export: {missing}")
+    vp, sz = C.c_void_p, C.c_size_t
+    u64p, i64p, u32p = C.POINTER(C.c_uint64), C.POINTER(C.c_int64), C.POINTER(C.c_uint32)
+    np_, pp = C.POINTER(Node), C.POINTER(Pair)
+    u32, u64, i32 = C.c_uint32, C.c_uint64, C.c_int
+    sig = {
+        "pb200_init": (i32, [i32, sz, C.POINTER(vp)]),
+        "pb200_shutdown": (i32, [vp]),
+        "pb200_strerror": (C.c_char_p, [i32]),
+        "pb200_last_error": (C.c_char_p, [vp]),
+        "pb200_abi_version": (i32, []),
+        "pb200_set_stream": (i32, [vp, vp]),
+        "pb200_family_create": (i32, [vp, u32p]),
+        "pb200_frag_load": (i32, [vp, u32, u64, C.c_char_p, sz]),
+        "pb200_frag_apply": (i32, [vp, u32, u64, u64p, sz, u64p, sz]),
+        "pb200_frag_drop": (i32, [vp, u32, u64]),
+        "pb200_rank_set": (i32, [vp, u32, u64, u64p, u64p, sz]),
+        "pb200_frag_stat": (i32, [vp, u32, u64, u64p, u64p, u64p]),
+        "pb200_count": (i32, [vp, np_, u32, u64p, u32, u64p]),
+        "pb200_count_batch": (i32, [vp, np_, u32p, u32, u64p, u32, u64p]),
+        "pb200_count_shards": (i32, [vp, np_, u32, u64p, u32, u64p]),
+        "pb200_count_batch_begin": (i32, [vp, np_, u32p, u32, u64p, u32]),
+        "pb200_count_batch_device": (i32, [vp, C.POINTER(vp)]),
+        "pb200_count_batch_end": (i32, [vp, u64p]),
+        "pb200_batch_prepare": (i32, [vp, np_, u32p, u32, u64p, u32, C.POINTER(vp)]),
+        "pb200_batch_launch": (i32, [vp, vp]),
+        "pb200_batch_device_counts": (i32, [vp, vp, C.POINTER(vp)]),
+        "pb200_batch_fetch": (i32, [vp, vp, u64p]),
+        "pb200_batch_free": (i32, [vp, vp]),
+        "pb200_eval": (i32, [vp, np_, u32, u64, C.c_char_p, sz, C.POINTER(sz)]),
+        "pb200_eval_columns": (i32, [vp, np_, u32, u64, u64p, sz, C.POINTER(sz)]),
+        "pb200_topn": (i32, [vp, u32, np_, u32, u32, u64p, sz, u64, u64, u32, u64p, u32, pp, sz, C.POINTER(sz)]),
+        "pb200_topn_shard": (i32, [vp, u32, np_, u32, u32, u64p, sz, u64, u64, u64, pp, sz, C.POINTER(sz)]),
+        "pb200_bsi_sum": (i32, [vp, u32, u32, np_, u32, u32, u64p, u32, i64p, u64p]),
+        "pb200_bsi_min": (i32, [vp, u32, u32, np_, u32, u64p, u32, i64p, u64p]),
+        "pb200_bsi_max": (i32, [vp, u32, u32, np_, u32, u64p, u32, i64p, u64p]),
+        "pb200_bsi_minmax_shards": (i32, [vp, u32, u32, np_, u32, i32, u64p, u32, i64p, u64p]),
+        "pb200_last_timing": (i32, [vp, C.POINTER(Timing)]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype, fn.argtypes = res, args
+    _lib = L
+    return L
+
+
+class Engine:
+    """One context bound to one CUDA device (pb200_ctx)."""
+
+    def __init__(self, device: int = 0, hbm_budget_bytes: int = 0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.pb200_init(device, hbm_budget_bytes, C.byref(h))
+        if rc != 0:
+            raise EngineError(rc, f"pb200_init(device={device}) failed: {self.lib.pb200_strerror(rc).decode()} "
+                                  "(a CUDA device is required; there is no CPU fallback)")
+        self._h = h
+        self.device = device
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self.lib.pb200_shutdown(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc: int) -> None:
+        if rc != 0:
+            raise EngineError(rc, f"{self.lib.pb200_strerror(rc).decode()}: {self.lib.pb200_last_error(self._h).decode()}")
+
+    # ---- fragments ----
+    def set_stream(self, cuda_stream: int) -> None:
+        self._check(self.lib.pb200_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    def family_create(self) -> int:
+        out = C.c_uint32()
+        self._check(self.lib.pb200_family_create(self._h, C.byref(out)))
+        return out.value
+
+    def frag_load(self, fam: int, shard: int, data) -> None:
+        """data: bytes, or any object with .ptr/.size (synth.FragBytes) passed without a copy."""
+        if hasattr(data, "ptr"):
+            self._check(self.lib.pb200_frag_load(self._h, fam, shard, C.cast(C.c_void_p(data.ptr), C.c_char_p), data.size))
+        else:
+            self._check(self.lib.pb200_frag_load(self._h, fam, shard, data, len(data)))
+
+    def frag_apply(self, fam: int, shard: int, set_pos: Sequence[int] = (), clear_pos: Sequence[int] = ()) -> None:
+        self._check(self.lib.pb200_frag_apply(self._h, fam, shard, u64_array(set_pos), len(set_pos), u64_array(clear_pos), len(clear_pos)))
+
+    def frag_drop(self, fam: int, shard: int) -> None:
+        self._check(self.lib.pb200_frag_drop(self._h, fam, shard))
+
+    def rank_set(self, fam: int, shard: int, row_ids: Sequence[int], counts: Sequence[int]) -> None:
+        assert len(row_ids) == len(counts)
+        self._check(self.lib.pb200_rank_set(self._h, fam, shard, u64_array(row_ids), u64_array(counts), len(row_ids)))
+
+    def frag_stat(self, fam: int, shard: int) -> Tuple[int, int, int]:
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._check(self.lib.pb200_frag_stat(self._h, fam, shard, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    # ---- queries ----
+    def count(self, prog, shards: Sequence[int]) -> int:
+        out = C.c_uint64()
+        self._check(self.lib.pb200_count(self._h, prog, len(prog), u64_array(shards), len(shards), C.byref(out)))
+        return out.value
+
+    def count_shards(self, prog, shards: Sequence[int]) -> List[int]:
+        out = (C.c_uint64 * max(1, len(shards)))()
+        self._check(self.lib.pb200_count_shards(self._h, prog, len(prog), u64_array(shards), len(shards), out))
+        return list(out[: len(shards)])
+
+    def count_batch(self, progs: Sequence, shards: Sequence[int]) -> List[int]:
+        """progs: list of Node arrays."""
+        total = sum(len(p) for p in progs)
+        flat = (Node * max(1, total))()
+        off = (C.c_uint32 * (len(progs) + 1))()
+        k = 0
+        for i, p in enumerate(progs):
+            off[i] = k
+            for nd in p:
+                flat[k] = nd
+                k += 1
+        off[len(progs)] = k
+        return self.count_batch_raw(flat, off, len(progs), u64_array(shards), len(shards))
+
+    def count_batch_raw(self, flat, off, n_queries: int, shards_arr, n_shards: int, out=None) -> List[int]:
+        """Zero-marshalling variant for the bench: ctypes arrays prepared once by the caller."""
+        out = out if out is not None else (C.c_uint64 * max(1, n_queries))()
+        self._check(self.lib.pb200_count_batch(self._h, flat, off, n_queries, shards_arr, n_shards, out))
+        return out
+
+    # ---- split / prepared Count batches (multi-GPU reduce, device-resident serving loop) ----
+    @staticmethod
+    def pack_programs(progs: Sequence):
+        """Concatenate Node arrays into the (flat, prog_off) pair the batch entry points take."""
+        total = sum(len(p) for p in progs)
+        flat = (Node * max(1, total))()
+        off = (C.c_uint32 * (len(progs) + 1))()
+        k = 0
+        for i, p in enumerate(progs):
+            off[i] = k
+            for nd in p:
+                flat[k] = nd
+                k += 1
+        off[len(progs)] = k
+        return flat, off
+
+    def count_batch_begin(self, flat, off, n_queries: int, shards_arr, n_shards: int) -> None:
+        self._check(self.lib.pb200_count_batch_begin(self._h, flat, off, n_queries, shards_arr, n_shards))
+
+    def count_batch_device(self) -> int:
+        p = C.c_void_p()
+        self._check(self.lib.pb200_count_batch_device(self._h, C.byref(p)))
+        return p.value or 0
+
+    def count_batch_end(self, out) -> None:
+        self._check(self.lib.pb200_count_batch_end(self._h, out))
+
+    def batch_prepare(self, flat, off, n_queries: int, shards_arr, n_shards: int):
+        b = C.c_void_p()
+        self._check(self.lib.pb200_batch_prepare(self._h, flat, off, n_queries, shards_arr, n_shards, C.byref(b)))
+        return b
+
+    def batch_launch(self, b) -> None:
+        self._check(self.lib.pb200_batch_launch(self._h, b))
+
+    def batch_device_counts(self, b) -> int:
+        p = C.c_void_p()
+        self._check(self.lib.pb200_batch_device_counts(self._h, b, C.byref(p)))
+        return p.value or 0
+
+    def batch_fetch(self, b, out) -> None:
+        self._check(self.lib.pb200_batch_fetch(self._h, b, out))
+
+    def batch_free(self, b) -> None:
+        self._check(self.lib.pb200_batch_free(self._h, b))
+
+    def eval_roaring(self, prog, shard: int) -> bytes:
+        n = C.c_size_t()
+        self._check(self.lib.pb200_eval(self._h, prog, len(prog), shard, None, 0, C.byref(n)))
+        buf = C.create_string_buffer(max(1, n.value))
+        self._check(self.lib.pb200_eval(self._h, prog, len(prog), shard, buf, n.value, C.byref(n)))
+        return buf.raw[: n.value]
+
+    def eval_columns(self, prog, shard: int) -> List[int]:
+        n = C.c_size_t()
+        self._check(self.lib.pb200_eval_columns(self._h, prog, len(prog), shard, None, 0, C.byref(n)))
+        buf = (C.c_uint64 * max(1, n.value))()
+        self._check(self.lib.pb200_eval_columns(self._h, prog, len(prog), shard, buf, n.value, C.byref(n)))
+        return list(buf[: n.value])
+
+    def _pairs(self, fn, *args, cap=1 << 16):
+        out = (Pair * cap)()
+        n = C.c_size_t()
+        self._check(fn(*args, out, cap, C.byref(n)))
+        return [(out[i].id, out[i].count) for i in range(n.value)]
+
+    def topn(self, fam, src_prog, n, shards, ids=(), min_threshold=0, tanimoto=0, remote=False):
+        sp, ns = (src_prog, len(src_prog)) if src_prog is not None else (None, 0)
+        return self._pairs(self.lib.pb200_topn, self._h, fam, sp, ns, n, u64_array(ids) if ids else None, len(ids),
+                           min_threshold, tanimoto, 1 if remote else 0, u64_array(shards), len(shards))
+
+    def topn_shard(self, fam, src_prog, n, shard, ids=(), min_threshold=0, tanimoto=0):
+        sp, ns = (src_prog, len(src_prog)) if src_prog is not None else (None, 0)
+        return self._pairs(self.lib.pb200_topn_shard, self._h, fam, sp, ns, n, u64_array(ids) if ids else None, len(ids),
+                           min_threshold, tanimoto, shard)
+
+    def bsi_sum(self, fam, bit_depth, filter_prog, shards, flags=0):
+        fp, nf = (filter_prog, len(filter_prog)) if filter_prog is not None else (None, 0)
+        s, c = C.c_int64(), C.c_uint64()
+        self._check(self.lib.pb200_bsi_sum(self._h, fam, bit_depth, fp, nf, flags, u64_array(shards), len(shards), C.byref(s), C.byref(c)))
+        return s.value, c.value
+
+    def bsi_min(self, fam, bit_depth, filter_prog, shards):
+        fp, nf = (filter_prog, len(filter_prog)) if filter_prog is not None else (None, 0)
+        v, c = C.c_int64(), C.c_uint64()
+        self._check(self.lib.pb200_bsi_min(self._h, fam, bit_depth, fp, nf, u64_array(shards), len(shards), C.byref(v), C.byref(c)))
+        return v.value, c.value
+
+    def bsi_max(self, fam, bit_depth, filter_prog, shards):
+        fp, nf = (filter_prog, len(filter_prog)) if filter_prog is not None else (None, 0)
+        v, c = C.c_int64(), C.c_uint64()
+        self._check(self.lib.pb200_bsi_max(self._h, fam, bit_depth, fp, nf, u64_array(shards), len(shards), C.byref(v), C.byref(c)))
+        return v.value, c.value
+
+    def bsi_minmax_shards(self, fam, bit_depth, filter_prog, shards, is_max):
+        fp, nf = (filter_prog, len(filter_prog)) if filter_prog is not None else (None, 0)
+        v, c = (C.c_int64 * max(1, len(shards)))(), (C.c_uint64 * max(1, len(shards)))()
+        self._check(self.lib.pb200_bsi_minmax_shards(self._h, fam, bit_depth, fp, nf, int(is_max), u64_array(shards), len(shards), v, c))
+        return list(v[: len(shards)]), list(c[: len(shards)])
+
+    def last_timing(self) -> Timing:
+        t = Timing()
+        self._check(self.lib.pb200_last_timing(self._h, C.byref(t)))
+        return t

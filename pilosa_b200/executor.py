@@ -1,0 +1,272 @@
+"""Host-side mirror of the reference's executor for the hot path (executor.go).
+
+``Executor`` keeps the reference's call surface — Count / Row / TopN / Sum / Min / Max over a
+list of shards — and delegates every per-shard computation to a *backend* exposing the C-ABI
+methods (``pilosa_b200.engine.Engine`` in production). It owns only what stays on the host
+in the reference too: field metadata, BSI predicate re-basing (field.go:1526-1567,
+executor.go:1536-1665) and the cross-device reduce (executor.go:2458-2611 mapReduce).
+
+Multi-GPU: one process per GPU; shard ``s`` lives on rank ``s % world``;
+each rank evaluates its own shards and only the tiny partials are exchanged with
+``torch.distributed`` (NCCL over NVLink on the GPU box, gloo in the CPU tests):
+Count/Sum -> all-reduce(sum); Min/Max -> all-gather of (val, count, position) triples and
+the ValCount.smaller/larger rule; TopN -> all-gather of the pass-1 pairs, Pairs.Add, then
+pass 2 with the merged candidate ids. Bitmap-returning calls need no exchange.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+from . import abi
+from .abi import Call, flatten
+
+EXISTENCE_FIELD = "exists"  # index.go existenceFieldName
+
+
+@dataclass
+class BsiGroup:  # field.go:1505-1512
+    min: int = 0
+    max: int = 0
+    base: int = 0
+    bit_depth: int = 0
+
+    def bit_depth_min(self) -> int:  # field.go:1579
+        return self.base - (1 << self.bit_depth) + 1
+
+    def bit_depth_max(self) -> int:  # field.go:1584
+        return self.base + (1 << self.bit_depth) - 1
+
+    def base_value(self, op: int, value: int) -> Tuple[int, bool]:  # field.go:1526-1552
+        mn, mx = self.bit_depth_min(), self.bit_depth_max()
+        bv = 0
+        if op in (abi.BSI_GT, abi.BSI_GTE):
+            if value > mx:
+                return 0, True
+            if value > mn:
+                bv = value - self.base
+        elif op in (abi.BSI_LT, abi.BSI_LTE):
+            if value < mn:
+                return 0, True
+            bv = (mx - self.base) if value > mx else (value - self.base)
+        elif op in (abi.BSI_EQ, abi.BSI_NEQ):
+            if value < mn or value > mx:
+                return 0, True
+            bv = value - self.base
+        return bv, False
+
+    def base_value_between(self, lo: int, hi: int) -> Tuple[int, int, bool]:  # field.go:1555-1569
+        mn, mx = self.bit_depth_min(), self.bit_depth_max()
+        if hi < mn or lo > mx:
+            return 0, 0, True
+        return max(lo, mn) - self.base, min(hi, mx) - self.base, False
+
+
+def bit_depth(v: int) -> int:  # field.go:1606-1613
+    for i in range(63):
+        if v < (1 << i):
+            return i
+    return 63
+
+
+def bit_depth_int64(v: int) -> int:  # field.go:1616-1621
+    return bit_depth(-v if v < 0 else v)
+
+
+@dataclass
+class Field:
+    name: str
+    type: str = "set"  # set | int
+    families: Dict[str, int] = field(default_factory=dict)  # view -> family handle
+    bsig: Optional[BsiGroup] = None
+
+
+class Executor:
+    def __init__(self, backend, rank: int = 0, world: int = 1, group=None):
+        self.be = backend
+        self.rank, self.world, self.group = rank, world, group
+        self.fields: Dict[str, Field] = {}
+
+    # ---- schema / loading (host bookkeeping; holder.go / field.go stay in Go) ----
+    def create_field(self, name: str, type: str = "set", min: int = 0, max: int = 0) -> Field:
+        f = Field(name, type)
+        if type == "int":
+            # field.go:1047-1066: BitDepth from the declared range, Base 0 for new fields
+            f.bsig = BsiGroup(min=min, max=max, base=0, bit_depth=builtins_max(bit_depth_int64(min), bit_depth_int64(max)))
+            f.families["bsig_" + name] = self.be.family_create()
+        else:
+            f.families["standard"] = self.be.family_create()
+        self.fields[name] = f
+        return f
+
+    def family(self, field_name: str, view: str = "standard") -> int:
+        f = self.fields.get(field_name)
+        if f is None:
+            raise KeyError(f"field not found: {field_name}")  # ErrFieldNotFound
+        if view not in f.families:
+            f.families[view] = self.be.family_create()
+        return f.families[view]
+
+    def owns(self, shard: int) -> bool:
+        return shard % self.world == self.rank
+
+    def load_fragment(self, field_name: str, shard: int, data, view: Optional[str] = None) -> bool:
+        """Loads the fragment on this rank if it owns the shard (shard % world == rank)."""
+        if not self.owns(shard):
+            return False
+        f = self.fields[field_name]
+        view = view or ("bsig_" + field_name if f.type == "int" else "standard")
+        self.be.frag_load(self.family(field_name, view), shard, data)
+        return True
+
+    def local_shards(self, shards: Sequence[int]) -> List[int]:
+        return [s for s in shards if self.owns(s)]
+
+    # ---- call-tree helpers ----
+    def row_range(self, field_name: str, op: int, value: Optional[int] = None, value2: Optional[int] = None) -> Call:
+        """Row(field <op> value): executeRowBSIGroupShard's host-side pre-checks
+        (executor.go:1536-1665) reduced to a Range / NotNull / Empty leaf."""
+        f = self.fields[field_name]
+        g = f.bsig
+        if g is None:
+            raise KeyError("bsiGroup not found")  # ErrBSIGroupNotFound
+        rng = lambda o, a=0, b=0: Call("Range", field_name=field_name, bsi_op=o, a=a, b=b, bit_depth=g.bit_depth)  # noqa: E731
+        if op == abi.BSI_NEQ and value is None:  # != null
+            return rng(abi.BSI_NOTNULL)
+        if op == abi.BSI_BETWEEN:
+            lo, hi, oor = g.base_value_between(value, value2)
+            if oor:
+                return abi.Empty()
+            if value <= g.min and value2 >= g.max:
+                return rng(abi.BSI_NOTNULL)
+            return rng(abi.BSI_BETWEEN, lo, hi)
+        bv, oor = g.base_value(op, value)
+        if oor and op != abi.BSI_NEQ:
+            return abi.Empty()
+        if ((op == abi.BSI_LT and value > g.max) or (op == abi.BSI_LTE and value >= g.max) or
+                (op == abi.BSI_GT and value < g.min) or (op == abi.BSI_GTE and value <= g.min)):
+            return rng(abi.BSI_NOTNULL)
+        if oor and op == abi.BSI_NEQ:
+            return rng(abi.BSI_NOTNULL)
+        return rng(op, bv)
+
+    def program(self, call: Call):
+        return flatten(call, lambda fld, view: self.family(fld, view))
+
+    # ---- collectives ----
+    def _allreduce_ints(self, vals: List[int]) -> List[int]:
+        if self.world == 1:
+            return vals
+        import torch
+        import torch.distributed as dist
+
+        dev = "cuda" if dist.get_backend(self.group) == "nccl" else "cpu"
+        t = torch.tensor(vals, dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return [int(x) for x in t.tolist()]
+
+    def _allgather(self, obj):
+        if self.world == 1:
+            return [obj]
+        import torch.distributed as dist
+
+        out = [None] * self.world
+        dist.all_gather_object(out, obj, group=self.group)
+        return out
+
+    # ---- queries (executor.go) ----
+    def count(self, call: Call, shards: Sequence[int]) -> int:  # executeCount :1793
+        local = self.local_shards(shards)
+        n = self.be.count(self.program(call), local) if local else 0
+        return _u64(self._allreduce_ints([_i64(n)])[0])
+
+    def count_batch(self, calls: Sequence[Call], shards: Sequence[int]) -> List[int]:
+        local = self.local_shards(shards)
+        vals = [int(v) for v in self.be.count_batch([self.program(c) for c in calls], local)[: len(calls)]] if local else [0] * len(calls)
+        return [_u64(v) for v in self._allreduce_ints([_i64(v) for v in vals])]
+
+    def row_columns(self, call: Call, shards: Sequence[int]) -> List[int]:
+        """Row.Columns() of a bitmap call over shards (rank-local shards only; results stay sharded)."""
+        prog = self.program(call)
+        cols: List[int] = []
+        for s in self.local_shards(sorted(shards)):
+            cols += self.be.eval_columns(prog, s)
+        return cols
+
+    def sum(self, field_name: str, shards: Sequence[int], filter_call: Optional[Call] = None) -> Tuple[int, int]:  # executeSum :409
+        f = self.fields[field_name]
+        local = self.local_shards(shards)
+        fp = self.program(filter_call) if filter_call is not None else None
+        s, c = self.be.bsi_sum(self.family(field_name, "bsig_" + field_name), f.bsig.bit_depth, fp, local) if local else (0, 0)
+        s, c = self._allreduce_ints([s, c])
+        if c == 0:
+            return 0, 0
+        return _wrap_i64(s + c * f.bsig.base), c  # executor.go:718
+
+    def _minmax(self, field_name: str, shards: Sequence[int], filter_call: Optional[Call], is_max: bool) -> Tuple[int, int]:
+        f = self.fields[field_name]
+        local = [(i, s) for i, s in enumerate(shards) if self.owns(s)]
+        fp = self.program(filter_call) if filter_call is not None else None
+        best = None  # (val, count, position in the caller's shard list)
+        if local:
+            vals, counts = self.be.bsi_minmax_shards(self.family(field_name, "bsig_" + field_name), f.bsig.bit_depth, fp,
+                                                    [s for _, s in local], is_max)
+            for (pos, _), v, c in zip(local, vals, counts):
+                if c == 0:
+                    continue
+                if best is None or (v > best[0] if is_max else v < best[0]):
+                    best = (v, c, pos)
+        cands = [b for b in self._allgather(best) if b is not None]
+        if not cands:
+            return 0, 0
+        # ValCount.smaller/larger folded in shard-list order: the first shard attaining the extreme wins
+        cands.sort(key=lambda b: ((-b[0] if is_max else b[0]), b[2]))
+        v, c, _ = cands[0]
+        return v + f.bsig.base, c  # executor.go:759,797
+
+    def min(self, field_name, shards, filter_call=None):  # executeMin :445
+        return self._minmax(field_name, shards, filter_call, False)
+
+    def max(self, field_name, shards, filter_call=None):  # executeMax :481
+        return self._minmax(field_name, shards, filter_call, True)
+
+    def topn(self, field_name: str, shards: Sequence[int], n: int = 0, src: Optional[Call] = None, ids: Sequence[int] = (),
+             threshold: int = 0, tanimoto: int = 0) -> List[Tuple[int, int]]:  # executeTopN :863
+        fam = self.family(field_name)
+        sp = self.program(src) if src is not None else None
+        local = self.local_shards(shards)
+        if self.world == 1:
+            return self.be.topn(fam, sp, n, local, ids=list(ids), min_threshold=threshold, tanimoto=tanimoto)
+        p1 = self.be.topn(fam, sp, n, local, ids=list(ids), min_threshold=threshold, tanimoto=tanimoto, remote=True) if local else []
+        pairs = _merge_pairs(self._allgather(p1))
+        if not pairs or ids:
+            return pairs
+        ids2 = sorted(i for i, _ in pairs)
+        p2 = self.be.topn(fam, sp, n, local, ids=ids2, min_threshold=threshold, tanimoto=tanimoto, remote=True) if local else []
+        out = _merge_pairs(self._allgather(p2))
+        return out[:n] if n else out
+
+
+def builtins_max(a, b):
+    return a if a > b else b
+
+
+def _merge_pairs(lists) -> List[Tuple[int, int]]:  # Pairs.Add cache.go:356 + sort (count desc, id asc)
+    m: Dict[int, int] = {}
+    for lst in lists:
+        for i, c in lst or []:
+            m[i] = m.get(i, 0) + c
+    return sorted(m.items(), key=lambda kv: (-kv[1], kv[0]))
+
+
+def _i64(v: int) -> int:
+    return v - (1 << 64) if v >= (1 << 63) else v
+
+
+def _u64(v: int) -> int:
+    return v & ((1 << 64) - 1)
+
+
+def _wrap_i64(v: int) -> int:
+    v &= (1 << 64) - 1
+    return v - (1 << 64) if v >= (1 << 63) else v

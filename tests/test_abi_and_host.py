@@ -1,0 +1,207 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol the header declares,
+the product refuses to run without a CUDA device (no fallback), and the host logic
+(program flattening, BSI predicate re-basing, synthetic generator, file format)."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import pytest
+
+import oracle
+from pilosa_b200 import abi, synth
+from pilosa_b200.abi import Difference, Intersect, Not, Row, Union, Xor
+from pilosa_b200.executor import BsiGroup, Executor, bit_depth, bit_depth_int64
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from pilosa_b200 import engine
+
+    lib = engine.load_library()
+    syms = engine.declared_symbols()
+    assert len(syms) >= 24
+    for s in syms:
+        assert hasattr(lib, s), s
+    assert lib.pb200_abi_version() == 1
+    assert lib.pb200_strerror(0) == b"ok"
+    # the shared object itself (nm): every declared symbol is an exported text symbol
+    out = subprocess.check_output(["nm", "-D", "--defined-only", engine.LIB_PATH]).decode()
+    exported = {line.split()[-1] for line in out.splitlines() if " T " in line}
+    assert set(syms) <= exported
+
+
+def test_no_cpu_fallback():
+    """Without a CUDA device pb200_init must fail loudly; with one it must succeed."""
+    import torch
+
+    from pilosa_b200.engine import Engine, EngineError
+
+    if torch.cuda.is_available():
+        Engine(0).close()
+    else:
+        with pytest.raises(EngineError, match="no CPU fallback"):
+            Engine(0)
+
+
+def test_product_never_imports_oracle():
+    bad = []
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "pilosa_b200")):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".inl")):
+                src = open(os.path.join(dirpath, fn)).read()
+                for line in src.splitlines():
+                    s = line.strip()
+                    if fn == "selftest.py":
+                        continue  # smoke(): the oracle is the checker there, by contract
+                    if s.startswith(("import oracle", "from oracle")) or "oracle/" in s and "#include" in s:
+                        bad.append((fn, s))
+    assert not bad, bad
+
+
+def test_flatten_post_order():
+    fams = {}
+    prog = abi.flatten(Difference(Row("a", 1), Union(Row("b", 2), Row("c", 3))), lambda f, v: fams.setdefault((f, v), len(fams)))
+    ops = [(n.op, n.family, n.row, n.nargs) for n in prog]
+    assert ops == [(abi.OP_ROW, 0, 1, 0), (abi.OP_ROW, 1, 2, 0), (abi.OP_ROW, 2, 3, 0), (abi.OP_UNION, 0, 0, 2), (abi.OP_DIFFERENCE, 0, 0, 2)]
+    prog = abi.flatten(Not(Row("a", 1)), lambda f, v: 7)
+    assert [(n.op, n.family) for n in prog] == [(abi.OP_ROW, 7), (abi.OP_NOT, 7)]
+
+
+# field_internal_test.go:31-157 — baseValue / baseValueBetween tables, restated for Base -100/0/100
+def test_bsi_group_base_value_tables():
+    # the three groups and both tables are the literal rows of field_internal_test.go:31-157
+    b0 = BsiGroup(min=-1000, max=1000, base=-100, bit_depth=10)
+    b1 = BsiGroup(min=-255, max=255, base=0, bit_depth=8)
+    b2 = BsiGroup(min=-(1 << 63), max=(1 << 63) - 1, base=100, bit_depth=11)
+    LT, GT, EQ = abi.BSI_LT, abi.BSI_GT, abi.BSI_EQ
+    cases = [
+        (b0, LT, 5, 105, False), (b0, LT, -8, 92, False), (b0, LT, -108, -8, False), (b0, LT, 1005, 1023, False), (b0, LT, 0, 100, False),
+        (b1, LT, 5, 5, False), (b1, LT, -8, -8, False), (b1, LT, 1005, 255, False), (b1, LT, 0, 0, False),
+        (b2, LT, 5, -95, False), (b2, LT, -8, -108, False), (b2, LT, 105, 5, False), (b2, LT, 1105, 1005, False),
+        (b0, GT, -5, 95, False), (b0, GT, 5, 105, False), (b0, GT, 905, 1005, False), (b0, GT, 0, 100, False),
+        (b1, GT, 5, 5, False), (b1, GT, -8, -8, False), (b1, GT, 1005, 0, True), (b1, GT, 0, 0, False),
+        (b2, GT, 5, -95, False), (b2, GT, -8, -108, False), (b2, GT, 105, 5, False), (b2, GT, 1105, 1005, False),
+        (b0, EQ, -105, -5, False), (b0, EQ, 5, 105, False), (b0, EQ, 905, 1005, False), (b0, EQ, 0, 100, False),
+        (b1, EQ, 5, 5, False), (b1, EQ, -8, -8, False), (b1, EQ, 1005, 0, True), (b1, EQ, 0, 0, False),
+        (b2, EQ, 5, -95, False), (b2, EQ, -8, -108, False), (b2, EQ, 105, 5, False), (b2, EQ, 1105, 1005, False),
+    ]
+    for g, op, val, exp, oor in cases:
+        assert g.base_value(op, val) == (exp, oor), (g.base, op, val)
+        assert oracle.base_value(g.base, g.bit_depth, op, val) == (exp, oor)
+    between = [
+        (b0, -205, -105, -105, -5, False), (b0, -105, 80, -5, 180, False), (b0, 5, 20, 105, 120, False),
+        (b0, 20, 1005, 120, 1023, False), (b0, 1005, 2000, 0, 0, True),
+        (b1, -105, -5, -105, -5, False), (b1, -5, 20, -5, 20, False), (b1, 5, 20, 5, 20, False),
+        (b1, 20, 1005, 20, 255, False), (b1, 1005, 2000, 0, 0, True),
+        (b2, 5, 95, -95, -5, False), (b2, 95, 120, -5, 20, False), (b2, 105, 120, 5, 20, False),
+        (b2, 120, 1105, 20, 1005, False), (b2, 1105, 2000, 1005, 1900, False),
+    ]
+    for g, lo, hi, elo, ehi, oor in between:
+        assert g.base_value_between(lo, hi) == (elo, ehi, oor), (g.base, lo, hi)
+        assert oracle.base_value_between(g.base, g.bit_depth, lo, hi) == (elo, ehi, oor)
+    # field.go:1606-1621
+    assert [bit_depth(v) for v in (0, 1, 2, 3, 4, 255, 256, (1 << 31) - 1, 1 << 31)] == [0, 1, 2, 2, 3, 8, 9, 31, 32]
+    assert bit_depth_int64(-(1 << 31)) == 32 and oracle.lib().orc_bit_depth_i64(-(1 << 31)) == 32
+
+
+def test_synth_is_seeded_and_canonical():
+    a, b = synth.mixed(3, 0, 2).bytes(), synth.mixed(3, 0, 2).bytes()
+    assert a == b
+    assert synth.mixed(4, 0, 2).bytes() != a
+    bm = oracle.Bitmap.deserialize(a)
+    types = {t for _, t, _ in bm.containers()}
+    assert types == {oracle.ARRAY, oracle.BITMAP, oracle.RUN}
+    # canonical: re-serialising through the oracle's optimize() is the identity
+    assert bm.serialize(optimize=True) == a
+    dense = oracle.Bitmap.deserialize(synth.bernoulli(0, 1, 1, 0.10).bytes())
+    assert all(t == oracle.BITMAP for _, t, _ in dense.containers()) and len(dense.containers()) == 16
+    assert abs(dense.count() - 0.1 * (1 << 20)) < 3000
+    sparse = oracle.Bitmap.deserialize(synth.bernoulli(0, 1, 1, 1e-4).bytes())
+    assert all(t in (oracle.ARRAY, oracle.RUN) for _, t, _ in sparse.containers()) and 40 < sparse.count() < 200
+    pos = [5, 70000, (3 << 20) + 9, (3 << 20) + 10]
+    assert oracle.Bitmap.deserialize(synth.from_positions(pos).bytes()).slice() == pos
+
+
+def test_executor_host_logic_with_oracle_backend():
+    ex = Executor(oracle.Oracle(workers=2))
+    ex.create_field("f")
+    ex.create_field("v", type="int", min=-1000, max=1000)
+    assert ex.fields["v"].bsig.bit_depth == 10
+    for s in (0, 1):
+        ex.load_fragment("f", s, synth.bernoulli(s, 0, 3, 0.05))
+        ex.load_fragment("v", s, synth.bsi(s, bit_depth=10, vmin=-1000, vmax=1000, density=0.2))
+    a, b = ex.count(Row("f", 0), [0, 1]), ex.count(Row("f", 1), [0, 1])
+    i, u, x = (ex.count(op(Row("f", 0), Row("f", 1)), [0, 1]) for op in (Intersect, Union, Xor))
+    assert u == a + b - i and x == u - i and ex.count(Difference(Row("f", 0), Row("f", 1)), [0, 1]) == a - i
+    s, c = ex.sum("v", [0, 1])
+    assert c == ex.count(ex.row_range("v", abi.BSI_NEQ, None), [0, 1])
+    lt, ge = ex.count(ex.row_range("v", abi.BSI_LT, 17), [0, 1]), ex.count(ex.row_range("v", abi.BSI_GTE, 17), [0, 1])
+    assert lt + ge == c
+    assert ex.row_range("v", abi.BSI_GT, 5000).name == "Empty"             # executor.go:1640
+    assert ex.row_range("v", abi.BSI_LT, 5000).bsi_op == abi.BSI_NOTNULL    # executor.go:1652
+    assert ex.row_range("v", abi.BSI_BETWEEN, -1000, 1000).bsi_op == abi.BSI_NOTNULL  # :1620
+    mn, mx = ex.min("v", [0, 1]), ex.max("v", [0, 1])
+    assert mn[0] <= mx[0] and mn[1] >= 1 and mx[1] >= 1
+
+
+_DIST_WORKER = r"""
+import os, sys
+sys.path.insert(0, {root!r})
+import torch.distributed as dist
+import oracle
+from pilosa_b200 import abi, synth
+from pilosa_b200.abi import Intersect, Row, Union
+from pilosa_b200.executor import Executor
+
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:{port}", rank=int(sys.argv[1]), world_size=2)
+rank = dist.get_rank()
+shards = list(range(6))
+def build(rank, world):
+    ex = Executor(oracle.Oracle(workers=1), rank=rank, world=world)
+    ex.create_field("f"); ex.create_field("z"); ex.create_field("v", type="int", min=-500, max=500)
+    for s in shards:
+        ex.load_fragment("f", s, synth.bernoulli(s, 0, 3, 0.05))
+        ex.load_fragment("z", s, synth.zipf(s, n_rows=60, k=2))
+        ex.load_fragment("v", s, synth.bsi(s, bit_depth=9, vmin=-500, vmax=500, density=0.01))
+    return ex
+ex2 = build(rank, 2)            # sharded over two ranks
+ex1 = build(0, 1)               # everything on one rank: the expected answers
+src = Intersect(Row("f", 0), Row("f", 1))
+checks = [
+    (ex2.count(src, shards), ex1.count(src, shards)),
+    (ex2.count_batch([src, Union(Row("f", 0), Row("f", 2))], shards), ex1.count_batch([src, Union(Row("f", 0), Row("f", 2))], shards)),
+    (ex2.sum("v", shards), ex1.sum("v", shards)),
+    (ex2.sum("v", shards, Row("f", 1)), ex1.sum("v", shards, Row("f", 1))),
+    (ex2.min("v", shards), ex1.min("v", shards)),
+    (ex2.max("v", shards), ex1.max("v", shards)),
+    (ex2.topn("z", shards, n=5), ex1.topn("z", shards, n=5)),
+    (ex2.topn("z", shards, n=5, src=src), ex1.topn("z", shards, n=5, src=src)),
+    (ex2.topn("z", shards, n=5, src=src, ids=[1, 2, 3]), ex1.topn("z", shards, n=5, src=src, ids=[1, 2, 3])),
+    (ex2.count(ex2.row_range("v", abi.BSI_GT, 0), shards), ex1.count(ex1.row_range("v", abi.BSI_GT, 0), shards)),
+]
+for i, (got, exp) in enumerate(checks):
+    assert got == exp, (i, got, exp)
+assert sorted(ex2.local_shards(shards)) == [s for s in shards if s % 2 == rank]
+dist.barrier()
+dist.destroy_process_group()
+print("rank", rank, "ok")
+"""
+
+
+def test_two_rank_gloo_shard_partition(tmp_path):
+    """world_size-2 gloo run of the shard partition + partial merge: Count/Sum
+    all-reduce, Min/Max triple gather, TopN two-pass merge equal the single-rank answers."""
+    import socket
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    script = tmp_path / "worker.py"
+    script.write_text(_DIST_WORKER.format(root=ROOT, port=port))
+    procs = [subprocess.Popen([sys.executable, str(script), str(r)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT) for r in range(2)]
+    outs = [p.communicate(timeout=300)[0].decode() for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+        assert "ok" in o

@@ -1,0 +1,225 @@
+"""Parity tests proper: the CUDA engine, called through the C ABI, against the CPU oracle on
+the same seeded inputs (bit-exact: all integer work). Run on the B200 box with -m gpu."""
+import random
+
+import pytest
+
+import oracle
+from pilosa_b200 import abi, synth
+from pilosa_b200.abi import Difference, Empty, Intersect, Not, Row, Shift, Union, Xor
+from pilosa_b200.executor import Executor
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pair():
+    """Engine + oracle executors over the same small synthetic index (C1/C2/C3/C4/C5 shapes)."""
+    from pilosa_b200.engine import Engine
+
+    eng = Engine(0)
+    orc = oracle.Oracle(workers=8)
+    g, c = Executor(eng), Executor(orc)
+    shards = [0, 1, 2, 5]  # shard 3/4 absent on purpose (missing fragments)
+    for ex in (g, c):
+        ex.create_field("f")        # dense bernoulli rows (bitmap containers)
+        ex.create_field("m")        # mixed array/bitmap/run containers
+        ex.create_field("sp")       # sparse p=1e-4 (arrays / short runs)
+        ex.create_field("z")        # zipf ranked field
+        ex.create_field("exists")   # existence field for Not()
+        ex.create_field("v", type="int", min=-(1 << 31), max=(1 << 31) - 1)
+        ex.create_field("w", type="int", min=0, max=1000)
+    for s in shards:
+        frs = {
+            "f": synth.bernoulli(s, 0, 6, 0.10),
+            "m": synth.mixed(s, 0, 8),
+            "sp": synth.bernoulli(s, 0, 4, 1e-4),
+            "z": synth.zipf(s, n_rows=300, k=4),
+            "exists": synth.bernoulli(s, 0, 1, 0.9),
+            "v": synth.bsi(s, bit_depth=32, density=0.7),
+            "w": synth.bsi(s, bit_depth=10, vmin=0, vmax=1000, density=0.01),
+        }
+        for name, fb in frs.items():
+            for ex in (g, c):
+                ex.load_fragment(name, s, fb)
+    yield g, c, shards + [3]  # query shard 3 too: no fragment anywhere
+    eng.close()
+
+
+CALLS = [
+    Intersect(Row("f", 1), Row("f", 2)),                                   # C1: bitmap x bitmap
+    Intersect(Row("f", 1), Row("f", 2), Row("f", 3)),
+    Union(Row("m", 0), Row("m", 1), Row("m", 2), Row("m", 3)),             # C2
+    Difference(Row("m", 0), Row("m", 1), Row("m", 2), Row("m", 3)),
+    Xor(Row("m", 0), Row("m", 1), Row("m", 2), Row("m", 3)),
+    Intersect(Row("sp", 1), Row("sp", 2)),                                  # C5: sparse
+    Intersect(Row("sp", 0), Row("m", 5)),
+    Intersect(Row("m", 4), Row("f", 0)),
+    Union(Row("sp", 0), Row("sp", 1), Row("sp", 2), Row("sp", 3)),
+    Row("m", 6),
+    Row("f", 99),                                                           # missing row
+    Intersect(Row("f", 1), Row("f", 99)),
+    Union(Row("f", 99), Row("m", 1)),
+    Difference(Row("m", 1), Row("f", 99)),
+    Intersect(Union(Row("m", 0), Row("f", 1)), Union(Row("m", 2), Row("sp", 3))),      # bushy: stack
+    Difference(Row("f", 0), Union(Row("m", 1), Row("m", 2))),
+    Xor(Intersect(Row("m", 0), Row("m", 1)), Difference(Row("m", 2), Row("m", 3)), Row("f", 5)),
+    Union(Intersect(Row("m", 0), Row("m", 1)), Intersect(Row("m", 2), Row("m", 3)), Intersect(Row("m", 4), Row("m", 5))),
+    Not(Row("m", 1)),
+    Not(Intersect(Row("f", 1), Row("m", 2))),
+    Union(),
+    Xor(),
+    Empty(),
+    Intersect(Row("m", 7)),
+]
+
+
+@pytest.mark.parametrize("idx", range(len(CALLS)))
+def test_count_matches_oracle(pair, idx):
+    g, c, shards = pair
+    call = CALLS[idx]
+    assert g.count(call, shards) == c.count(call, shards), repr(call)
+
+
+def test_count_per_shard_and_batch(pair):
+    g, c, shards = pair
+    for call in CALLS[:8]:
+        assert g.be.count_shards(g.program(call), shards) == c.be.count_shards(c.program(call), shards)
+    got = g.count_batch(CALLS, shards)
+    exp = [c.count(call, shards) for call in CALLS]
+    assert got == exp
+
+
+def test_count_edge_shard_lists(pair):
+    g, c, _ = pair
+    call = Intersect(Row("f", 1), Row("f", 2))
+    assert g.count(call, []) == 0
+    assert g.count(call, [3]) == 0            # no fragment
+    assert g.count(call, [10 ** 6]) == 0      # beyond the family table
+    assert g.count(call, [2, 2]) == 2 * g.count(call, [2])  # duplicates are independent map jobs
+
+
+def test_random_trees(pair):
+    g, c, shards = pair
+    rnd = random.Random(7)
+    leaves = [("f", r) for r in range(6)] + [("m", r) for r in range(8)] + [("sp", r) for r in range(4)] + [("f", 77)]
+
+    def tree(depth):
+        if depth == 0 or rnd.random() < 0.3:
+            f, r = rnd.choice(leaves)
+            return Row(f, r)
+        op = rnd.choice([Intersect, Union, Difference, Xor])
+        return op(*[tree(depth - 1) for _ in range(rnd.randint(1, 3))])
+
+    n_ok = 0
+    for _ in range(60):
+        t = tree(3)
+        try:
+            got = g.count(t, shards)
+        except Exception as e:  # only the documented limits may be hit
+            assert "too" in str(e), str(e)
+            continue
+        assert got == c.count(t, shards), repr(t)
+        n_ok += 1
+    assert n_ok > 40
+
+
+def test_eval_columns_and_roaring(pair):
+    g, c, shards = pair
+    for call in [CALLS[0], CALLS[2], CALLS[3], CALLS[4], CALLS[5], CALLS[14], CALLS[18]]:
+        for s in (0, 5, 3):
+            gp, cp = g.program(call), c.program(call)
+            assert g.be.eval_columns(gp, s) == c.be.eval_columns(cp, s), (repr(call), s)
+            assert g.be.eval_roaring(gp, s) == c.be.eval_roaring(cp, s), (repr(call), s)
+
+
+def test_topn(pair):
+    g, c, shards = pair
+    src = Intersect(Row("f", 1), Row("f", 2))
+    for kw in (dict(n=10), dict(n=10, src=src), dict(n=50, src=Row("m", 1)), dict(n=0, src=src), dict(n=5, src=src, threshold=30),
+               dict(n=3, src=Row("sp", 1)), dict(n=10, src=src, ids=[1, 5, 7, 250, 9999]), dict(n=10, ids=[3, 4, 299]),
+               dict(n=5, src=src, tanimoto=1), dict(n=5, src=Row("z", 3), tanimoto=30)):
+        assert g.topn("z", shards, **kw) == c.topn("z", shards, **kw), kw
+    # single shard, exact fragment.top order (heap pop order)
+    for s in (0, 5):
+        gp, cp = g.program(src), c.program(src)
+        assert g.be.topn_shard(g.family("z"), gp, 7, s) == c.be.topn_shard(c.family("z"), cp, 7, s)
+        assert g.be.topn_shard(g.family("z"), None, 7, s) == c.be.topn_shard(c.family("z"), None, 7, s)
+
+
+def test_bsi_sum_min_max(pair):
+    g, c, shards = pair
+    filt = Row("f", 1)
+    filt2 = Intersect(Row("f", 1), Row("m", 2))
+    for fld in ("v", "w"):
+        for f in (None, filt, filt2, Row("f", 99)):
+            assert g.sum(fld, shards, f) == c.sum(fld, shards, f), (fld, repr(f))
+            assert g.min(fld, shards, f) == c.min(fld, shards, f), (fld, repr(f))
+            assert g.max(fld, shards, f) == c.max(fld, shards, f), (fld, repr(f))
+    # strict flag (opt-in deviation from the reference quirk) agrees with the oracle's strict mode
+    fam, prog = g.family("v", "bsig_v"), g.program(filt)
+    assert g.be.bsi_sum(fam, 32, prog, shards, flags=abi.SUM_STRICT) == c.be.bsi_sum(c.family("v", "bsig_v"), 32, c.program(filt), shards, flags=abi.SUM_STRICT)
+
+
+def test_bsi_range(pair):
+    g, c, shards = pair
+    ops = [abi.BSI_EQ, abi.BSI_NEQ, abi.BSI_LT, abi.BSI_LTE, abi.BSI_GT, abi.BSI_GTE]
+    for x in (0, 1, -1, 12345, -12345, 1 << 30, -(1 << 30), (1 << 31) - 1, -(1 << 31), 5 * 10 ** 9):
+        for op in ops:
+            assert g.count(g.row_range("v", op, x), shards) == c.count(c.row_range("v", op, x), shards), (op, x)
+    for lo, hi in ((0, 100), (-100, 100), (-5000, -10), (-(1 << 31), (1 << 31) - 1), (10, 5), (1 << 29, 1 << 30)):
+        assert g.count(g.row_range("v", abi.BSI_BETWEEN, lo, hi), shards) == c.count(c.row_range("v", abi.BSI_BETWEEN, lo, hi), shards)
+    assert g.count(g.row_range("v", abi.BSI_NEQ, None), shards) == c.count(c.row_range("v", abi.BSI_NEQ, None), shards)
+    # sparse small-depth field: array/run planes exercise the staged plane loads
+    for x in (0, 1, 500, 999, 1000, 1001, -1):
+        for op in ops:
+            assert g.count(g.row_range("w", op, x), shards) == c.count(c.row_range("w", op, x), shards), ("w", op, x)
+    # range leaf inside a larger tree, and materialised
+    call = Intersect(Row("f", 1), g.row_range("v", abi.BSI_GT, 0))
+    ccall = Intersect(Row("f", 1), c.row_range("v", abi.BSI_GT, 0))
+    assert g.count(call, shards) == c.count(ccall, shards)
+    assert g.be.eval_columns(g.program(call), 1) == c.be.eval_columns(c.program(ccall), 1)
+
+
+def test_frag_apply_and_reload(pair):
+    g, c, shards = pair
+    fam_g, fam_c = g.family("sp"), c.family("sp")
+    rnd = random.Random(3)
+    sets = [r * (1 << 20) + rnd.randrange(1 << 20) for r in (0, 1, 1, 2, 9) for _ in range(40)]
+    clears = sets[::5] + [3 * (1 << 20) + 17]
+    g.be.frag_apply(fam_g, 1, sets, clears)
+    for p in sets:
+        c.be.set_bit(fam_c, 1, p >> 20, p & ((1 << 20) - 1) | (1 << 20))
+    for p in clears:
+        c.be.clear_bit(fam_c, 1, p >> 20, p & ((1 << 20) - 1) | (1 << 20))
+    for call in (Row("sp", 1), Intersect(Row("sp", 1), Row("sp", 2)), Row("sp", 9), Union(Row("sp", 0), Row("sp", 9))):
+        assert g.count(call, [1]) == c.count(call, [1])
+        assert g.be.eval_columns(g.program(call), 1) == c.be.eval_columns(c.program(call), 1)
+
+
+def test_ops_log_replay_on_load(pair):
+    g, c, _ = pair
+    base = synth.bernoulli(7, 0, 2, 0.001).bytes()
+    ops = oracle.encode_op(0, [5]) + oracle.encode_op(2, [1 << 20, (1 << 20) + 70000, 900000]) + oracle.encode_op(1, [5]) + \
+        oracle.encode_op(3, [900000, 12])
+    for ex in (g, c):
+        ex.create_field("ol")
+        ex.load_fragment("ol", 7, base + ops)
+    for call in (Row("ol", 0), Row("ol", 1), Intersect(Row("ol", 0), Row("ol", 1))):
+        assert g.be.eval_columns(g.program(call), 7) == c.be.eval_columns(c.program(call), 7)
+
+
+def test_error_behaviour(pair):
+    from pilosa_b200.engine import EngineError
+
+    g, _, shards = pair
+    with pytest.raises(EngineError, match="empty Intersect"):
+        g.count(Intersect(), shards)
+    with pytest.raises(EngineError, match="empty Difference"):
+        g.count(Difference(), shards)
+    with pytest.raises(EngineError):
+        g.be.frag_load(g.family("f"), 0, b"\x00\x01\x02")
+    with pytest.raises(EngineError, match="magic"):
+        g.be.frag_load(g.family("f"), 0, b"\x00" * 64)
+    # a failed load leaves the resident fragment intact
+    assert g.count(Row("f", 1), [0]) > 0
