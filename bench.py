@@ -66,8 +66,33 @@ class ClockSampler:
         self.idx = gpu_index
         self.proc = None
         self.lines = []
+        self.nvml = None
+        self._stop = False
+        self._samples = []
+
+    def _nvml_loop(self):
+        import pynvml as nv
+
+        h = nv.nvmlDeviceGetHandleByIndex(self.idx)
+        bits = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        while not self._stop:
+            sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            self._samples.append((sm, mx, [k for k, b in bits.items() if r & b]))
+            time.sleep(0.002)
 
     def start(self):
+        try:  # NVML polling every ~2 ms: the timed region is only tens of milliseconds long
+            import pynvml as nv
+
+            nv.nvmlInit()
+            self.nvml = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.nvml.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.idx)],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -80,6 +105,13 @@ class ClockSampler:
             self.lines.append(ln.strip())
 
     def stop(self):
+        if self.nvml is not None:
+            self._stop = True
+            self.nvml.join(timeout=2)
+            sm = [s[0] for s in self._samples]
+            reasons = sorted({r for s in self._samples for r in s[2]})
+            return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self._samples[0][1] if self._samples else None,
+                    "reasons": reasons, "samples": len(sm), "source": "nvml, 2 ms period, timed region only"}
         if self.proc:
             self.proc.terminate()
             try:
@@ -351,6 +383,13 @@ def main():
     algo_bytes = B * len(shards) * 16 * 2 * (8192 + 16)   # per launch per GPU (payload + 16 B/container)
     peak, peak_src = peaks()
     achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9
+    traffic, traffic_src = None, None
+    try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
+        prof = json.load(open(os.path.join(ROOT, "profiles", "r01_eval_fast_summary.json")))
+        if B == 1024 and len(shards) == SHARDS_PER_GPU:
+            traffic, traffic_src = prof["traffic_bytes_per_launch"], "profiles/r01_eval_fast_summary.json (" + prof["command"] + ")"
+    except Exception:
+        pass
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
@@ -359,7 +398,7 @@ def main():
                 "ms_per_step": 1e3 * e2e_s / args.steps},
         "gpu_launches": args.steps * 2 * int(max(1, tm.launches)),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "kernel": "eval_fast_kernel (K1: 128-bit AND + popcount over bitmap container pairs)",
                      "algo_bytes_per_launch": algo_bytes, "peak_source": peak_src,
                      "note": "achieved = algorithmic bytes per launch / mean launch duration from CUDA events over the timed region "
