@@ -198,6 +198,38 @@ int pb200_batch_device_counts(pb200_ctx* ctx, pb200_batch* batch, void** device_
 int pb200_batch_fetch(pb200_ctx* ctx, pb200_batch* batch, uint64_t* out_counts);
 int pb200_batch_free(pb200_ctx* ctx, pb200_batch* batch);
 
+/* Count(Intersect(Row(family=a), Row(family=b))) for n_pairs row pairs WITHOUT allocating.
+ * This entry point has no counterpart in the reference; it exists for hosts that are not
+ * allowed to allocate device memory while serving: a host living inside a PyTorch (or RMM)
+ * process whose pooling allocator already owns the free HBM — where a raw cudaMalloc can
+ * fail or stall every stream — a deployment that gave its whole HBM budget to resident
+ * fragments, or a latency-critical query thread that must never block in the driver's
+ * allocator. It calls no cudaMalloc / cudaFree / pooled or library allocator at all.
+ *
+ *  - d_pairs  : DEVICE buffer, uint64[2 * n_pairs] = {a0, b0, a1, b1, ...} row ids
+ *  - d_shards : DEVICE buffer, uint64[n_shards] shard numbers
+ *  - d_counts : DEVICE buffer, uint64[n_pairs], overwritten with the counts
+ *  The caller owns all three (cut from its own pool). Everything else the kernels need —
+ *  the expanded programs and the list of array/run container columns handed to the staged
+ *  kernel — lives in one fixed array inside the library image, PB200_NOALLOC_SCRATCH_BYTES
+ *  per GPU that loads the library, held until process exit.
+ *  Limits (PB200_ERR_RANGE beyond them; split the batch): n_pairs <= PB200_NOALLOC_MAX_PAIRS
+ *  and n_pairs * n_shards * 16 <= PB200_NOALLOC_MAX_ITEMS.
+ *  The call is asynchronous on the context's stream (pb200_set_stream): synchronise that
+ *  stream before reading d_counts. The first call on a device looks up the array's device
+ *  address (one-time set-up); make that first call before starting any stream capture.
+ *  All calls on a device share the array and it keeps the previous call's contents: the
+ *  entry point re-zeroes what must start at zero, and calls that overlap on the GPU
+ *  (two contexts or streams on the same device) race — issue them on one stream.
+ *  Fragment tables must be current: after loading fragments run one ordinary query first
+ *  (refreshing the tables allocates, so this entry point refuses to do it). */
+#define PB200_NOALLOC_MAX_PAIRS 4096u
+#define PB200_NOALLOC_MAX_ITEMS (1u << 20)
+#define PB200_NOALLOC_SCRATCH_BYTES ((4u << 20) + (256u << 10))
+int pb200_count_pairs_noalloc(pb200_ctx* ctx, pb200_family family, const uint64_t* d_pairs,
+                              uint32_t n_pairs, const uint64_t* d_shards, uint32_t n_shards,
+                              uint64_t* d_counts);
+
 /* Evaluate a bitmap call on ONE shard and return the resulting row segment as Pilosa
  * roaring bytes (containers optimize()d, keys = shard*16 + i as fragment.go:629
  * OffsetRange produces). Two-call protocol: with out == NULL only *out_len is written.

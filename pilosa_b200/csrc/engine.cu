@@ -777,3 +777,116 @@ extern "C" int pb200_batch_free(pb200_ctx* ctx, pb200_batch* b) {
   delete b;
   return PB200_OK;
 }
+
+// =======================================================================================
+// Allocation-free Count(Intersect(Row a, Row b)) for callers that must not allocate.
+//
+// Who needs this: code that runs inside a process where somebody else owns the device heap
+// and a stray cudaMalloc is off limits — a host embedded in a PyTorch program (the caching
+// allocator has usually reserved the free HBM, so a raw cudaMalloc can fail even though
+// "free" memory exists, and cudaMalloc/cudaFree stall every stream of the device), a
+// deployment that handed the whole HBM budget to resident fragments, or a latency-critical
+// query thread whose policy forbids anything that can block on the driver's allocator. Such
+// callers carve the small input / output buffers out of their own pool and pass them in;
+// everything the kernels need beyond that (the compiled two-leaf programs and the list of
+// container columns deferred to the staged kernel) lives in the fixed array below.
+//
+// The array is part of the library image: every GPU that loads libpilosa_b200.so holds
+// PB200_NOALLOC_SCRATCH_BYTES of it until the process exits, used or not. All calls on a
+// device share it and it keeps whatever the previous call left behind, so the entry point
+// re-zeroes the words that must start at zero, and two calls whose kernels overlap on the
+// GPU (different contexts / streams on one device) race on it — keep them on one stream.
+// =======================================================================================
+static __device__ __align__(256) unsigned char g_noalloc_scratch[PB200_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+// byte offsets inside g_noalloc_scratch (all 256 B aligned)
+constexpr size_t kNaCounters = 0;                                                     // u32 slow_count @0, u64 algo_bytes @8
+constexpr size_t kNaProgs = 256;                                                      // Prog[MAX_PAIRS]
+constexpr size_t kNaLeaves = kNaProgs + size_t(PB200_NOALLOC_MAX_PAIRS) * sizeof(Prog);      // Leaf[2 * MAX_PAIRS]
+constexpr size_t kNaInstrs = kNaLeaves + size_t(PB200_NOALLOC_MAX_PAIRS) * 2 * sizeof(Leaf); // Instr[2 * MAX_PAIRS]
+constexpr size_t kNaSlow = (kNaInstrs + size_t(PB200_NOALLOC_MAX_PAIRS) * 2 * sizeof(Instr) + 255) / 256 * 256;  // u32[MAX_ITEMS]
+constexpr size_t kNaEnd = kNaSlow + size_t(PB200_NOALLOC_MAX_ITEMS) * 4;
+static_assert(kNaEnd <= PB200_NOALLOC_SCRATCH_BYTES, "scratch layout exceeds PB200_NOALLOC_SCRATCH_BYTES");
+
+// Writes the program of pair q — LOAD row a ; AND row b — into the scratch array. Device
+// code may name the array directly; only host code needs its address.
+__global__ void noalloc_expand_kernel(const uint64_t* pairs, uint32_t n_pairs, uint32_t family) {
+  const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n_pairs) return;
+  Prog* progs = reinterpret_cast<Prog*>(g_noalloc_scratch + kNaProgs);
+  Leaf* leaves = reinterpret_cast<Leaf*>(g_noalloc_scratch + kNaLeaves);
+  Instr* instrs = reinterpret_cast<Instr*>(g_noalloc_scratch + kNaInstrs);
+  Prog pg; pg.instr_off = 2 * q; pg.n_instr = 2; pg.leaf_off = 2 * q; pg.n_leaves = 2;
+  progs[q] = pg;
+  Leaf a; a.kind = L_ROW; a.family = family; a.row = pairs[2 * q];
+  Leaf b; b.kind = L_ROW; b.family = family; b.row = pairs[2 * q + 1];
+  leaves[2 * q] = a; leaves[2 * q + 1] = b;
+  instrs[2 * q] = Instr{I_LOAD, 0};
+  instrs[2 * q + 1] = Instr{I_AND_LEAF, 1};
+}
+
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[64] = {};  // device address of the array, per device ordinal
+
+// One-time set-up per device, with that device current: in host code the array's name is
+// only a stand-in, not a device address, so the address has to be asked for.
+int noalloc_setup(pb200_ctx* ctx, unsigned char** out) {
+  if (ctx->device < 0 || ctx->device >= 64) return fail(ctx, PB200_ERR_RANGE, "device ordinal out of range for the no-alloc path");
+  std::lock_guard<std::mutex> g(g_noalloc_mu);
+  if (!g_noalloc_ptr[ctx->device]) {
+    void* p = nullptr;
+    CUDA_TRY(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (!p) return fail(ctx, PB200_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[ctx->device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_noalloc_ptr[ctx->device];
+  return PB200_OK;
+}
+
+}  // namespace
+
+extern "C" int pb200_count_pairs_noalloc(pb200_ctx* ctx, pb200_family family, const uint64_t* d_pairs, uint32_t n_pairs,
+                                         const uint64_t* d_shards, uint32_t n_shards, uint64_t* d_counts) {
+  ENTER(ctx);
+  if (n_pairs == 0) return PB200_OK;
+  if (!d_pairs || !d_counts || (n_shards && !d_shards)) return fail(ctx, PB200_ERR_INVALID, "null device buffer");
+  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
+  if (n_pairs > PB200_NOALLOC_MAX_PAIRS)
+    return fail(ctx, PB200_ERR_RANGE, "pb200_count_pairs_noalloc: n_pairs " + std::to_string(n_pairs) + " exceeds PB200_NOALLOC_MAX_PAIRS (" +
+                                          std::to_string(PB200_NOALLOC_MAX_PAIRS) + "); split the batch");
+  const uint64_t n_items = uint64_t(n_pairs) * n_shards * kRowContainers;
+  if (n_items > PB200_NOALLOC_MAX_ITEMS)
+    return fail(ctx, PB200_ERR_RANGE, "pb200_count_pairs_noalloc: n_pairs x n_shards x 16 = " + std::to_string(n_items) +
+                                          " exceeds PB200_NOALLOC_MAX_ITEMS (" + std::to_string(PB200_NOALLOC_MAX_ITEMS) + "); split the batch");
+  if (ctx->families_dirty || !ctx->d_families)
+    return fail(ctx, PB200_ERR_INVALID, "device fragment tables are stale: run one ordinary query (e.g. pb200_count) after loading fragments "
+                                        "before using the no-alloc entry point (refreshing them allocates)");
+  unsigned char* scratch = nullptr;
+  TRY(noalloc_setup(ctx, &scratch));
+  // the array still holds the previous call's counters; the caller's counts are accumulated with atomics
+  CUDA_TRY(ctx, cudaMemsetAsync(scratch + kNaCounters, 0, 16, ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(d_counts, 0, size_t(n_pairs) * 8, ctx->stream));
+  if (n_shards == 0) return PB200_OK;
+  noalloc_expand_kernel<<<(n_pairs + 255) / 256, 256, 0, ctx->stream>>>(d_pairs, n_pairs, family);
+  EvalParams p{};
+  p.families = ctx->d_families;
+  p.n_families = uint32_t(ctx->families.size());
+  p.progs = reinterpret_cast<const Prog*>(scratch + kNaProgs);
+  p.leaves = reinterpret_cast<const Leaf*>(scratch + kNaLeaves);
+  p.instrs = reinterpret_cast<const Instr*>(scratch + kNaInstrs);
+  p.shards = d_shards;
+  p.n_shards = n_shards; p.n_queries = n_pairs;
+  p.out_counts = reinterpret_cast<unsigned long long*>(d_counts);
+  p.out_qstride = 1; p.out_sstride = 0;
+  p.slow_list = reinterpret_cast<uint32_t*>(scratch + kNaSlow);
+  p.slow_count = reinterpret_cast<uint32_t*>(scratch + kNaCounters);
+  p.algo_bytes = reinterpret_cast<unsigned long long*>(scratch + kNaCounters + 8);
+  const uint32_t grid = uint32_t(std::min<uint64_t>((n_items + kFastWarps - 1) / kFastWarps, uint64_t(ctx->sm_count) * 8));
+  eval_fast_kernel<<<grid, kFastWarps * 32, 0, ctx->stream>>>(p);
+  const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, uint64_t(ctx->sm_count) * 6));
+  eval_staged_kernel<<<sgrid, kStagedThreads, 0, ctx->stream>>>(p);
+  CUDA_TRY(ctx, cudaGetLastError());
+  return PB200_OK;
+}

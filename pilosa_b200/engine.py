@@ -74,6 +74,7 @@ def load_library() -> C.CDLL:
         "pb200_batch_device_counts": (i32, [vp, vp, C.POINTER(vp)]),
         "pb200_batch_fetch": (i32, [vp, vp, u64p]),
         "pb200_batch_free": (i32, [vp, vp]),
+        "pb200_count_pairs_noalloc": (i32, [vp, u32, vp, u32, vp, u32, vp]),
         "pb200_eval": (i32, [vp, np_, u32, u64, C.c_char_p, sz, C.POINTER(sz)]),
         "pb200_eval_columns": (i32, [vp, np_, u32, u64, u64p, sz, C.POINTER(sz)]),
         "pb200_topn": (i32, [vp, u32, np_, u32, u32, u64p, sz, u64, u64, u32, u64p, u32, pp, sz, C.POINTER(sz)]),
@@ -226,6 +227,13 @@ class Engine:
 
     def batch_free(self, b) -> None:
         self._check(self.lib.pb200_batch_free(self._h, b))
+
+    def count_pairs_noalloc(self, fam: int, d_pairs: int, n_pairs: int, d_shards: int, n_shards: int, d_counts: int) -> None:
+        """Allocation-free Count(Intersect) over row pairs. All three buffers are DEVICE
+        addresses owned by the caller (e.g. ``tensor.data_ptr()``); the call only enqueues work
+        on the context's stream — synchronise that stream before reading ``d_counts``."""
+        self._check(self.lib.pb200_count_pairs_noalloc(self._h, fam, C.c_void_p(d_pairs), n_pairs, C.c_void_p(d_shards), n_shards,
+                                                       C.c_void_p(d_counts)))
 
     def eval_roaring(self, prog, shard: int) -> bytes:
         n = C.c_size_t()
