@@ -79,6 +79,7 @@ def lib() -> C.CDLL:
         "orc_frag_set_bit": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64]),
         "orc_frag_clear_bit": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64]),
         "orc_frag_set_value": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int64]),
+        "orc_frag_clear_value": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int64]),
         "orc_frag_value": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32, i64p]),
         "orc_frag_cache_config": (None, [vp, C.c_uint32, C.c_uint64, C.c_int, C.c_uint32]),
         "orc_frag_recalculate_cache": (None, [vp, C.c_uint32, C.c_uint64]),
@@ -319,6 +320,9 @@ class Oracle:
 
     def set_value(self, fam, shard, col, bit_depth, value) -> bool:
         return bool(lib().orc_frag_set_value(self._h, fam, shard, col, bit_depth, value))
+
+    def clear_value(self, fam, shard, col, bit_depth, value) -> bool:
+        return bool(lib().orc_frag_clear_value(self._h, fam, shard, col, bit_depth, value))
 
     def value(self, fam, shard, col, bit_depth):
         out = C.c_int64()

@@ -199,6 +199,9 @@ int orc_frag_clear_bit(void* h, uint32_t fam, uint64_t shard, uint64_t row, uint
 int orc_frag_set_value(void* h, uint32_t fam, uint64_t shard, uint64_t col, uint32_t bit_depth, int64_t v) {
   return ((Orc*)h)->holder.fragment(fam, shard, true)->set_value(col, bit_depth, v);
 }
+int orc_frag_clear_value(void* h, uint32_t fam, uint64_t shard, uint64_t col, uint32_t bit_depth, int64_t v) {
+  return ((Orc*)h)->holder.fragment(fam, shard, true)->clear_value(col, bit_depth, v);
+}
 int orc_frag_value(void* h, uint32_t fam, uint64_t shard, uint64_t col, uint32_t bit_depth, int64_t* out) {
   Fragment* f = ((Orc*)h)->holder.fragment(fam, shard);
   return f ? f->value(col, bit_depth, out) : 0;

@@ -274,6 +274,19 @@ struct Fragment {
     else changed |= clear_bit(kBsiSignBit, col);
     return changed;
   }
+  // fragment.go:926-929 clearValue -> setValueBase(clear = true): magnitude bits follow
+  // `value`, then the exists and sign bits are cleared (:1008-1030)
+  bool clear_value(uint64_t col, unsigned bit_depth, int64_t value) {
+    bool changed = false;
+    uint64_t uvalue = value < 0 ? uint64_t(-value) : uint64_t(value);
+    for (unsigned i = 0; i < bit_depth; i++) {
+      if (uvalue & (uint64_t(1) << i)) changed |= set_bit(kBsiOffsetBit + i, col);
+      else changed |= clear_bit(kBsiOffsetBit + i, col);
+    }
+    changed |= clear_bit(kBsiExistsBit, col);
+    changed |= clear_bit(kBsiSignBit, col);
+    return changed;
+  }
   // fragment.go:893-924
   bool value(uint64_t col, unsigned bit_depth, int64_t* out) const {
     if (!storage.contains_value(pos(kBsiExistsBit, col))) return false;

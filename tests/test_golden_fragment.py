@@ -1,0 +1,287 @@
+"""Known-answer tests of the reference's fragment / executor tests, restated. Each test runs
+against the CPU oracle (pins the oracle, `-m "not gpu"`) and against the CUDA engine through
+the C ABI (`-m gpu`), with the expected values being the literals of the Go tests cited."""
+import pytest
+
+from pilosa_b200 import abi
+from pilosa_b200.abi import Difference, Intersect, Not, Row, Union, Xor
+
+from world import SW, World
+
+BACKENDS = ["oracle", pytest.param("gpu", marks=pytest.mark.gpu)]
+
+
+@pytest.fixture(params=BACKENDS)
+def w(request):
+    world = World(request.param)
+    yield world
+    world.close()
+
+
+def _bsi(w, values, bit_depth=16, name="v"):
+    w.create_field(name, type="int", min=-(1 << bit_depth) + 1, max=(1 << bit_depth) - 1)
+    assert w.cpu.fields[name].bsig.bit_depth == bit_depth
+    for col, v in values:
+        w.set_value(name, col, v)
+
+
+# ---- fragment_internal_test.go:373-423 TestFragment_Sum ----
+def test_fragment_sum(w):
+    _bsi(w, [(1000, 382), (2000, 300), (3000, 2818), (4000, 300)])
+    assert w.frag_sum("v") == (3800, 4)
+    assert w.frag_sum("v", w.new_row(2000, 4000, 5000)) == (600, 2)
+    w.clear_value("v", 1000, 23)
+    assert w.frag_sum("v") == (3800 - 382, 3)
+
+
+# ---- fragment_internal_test.go:426-499 TestFragment_MinMax ----
+def test_fragment_min_max(w):
+    _bsi(w, [(1000, 382), (2000, 300), (3000, 2818), (4000, 300), (5000, 2818), (6000, 2817), (7000, 0)])
+    mins = [(None, 0, 1), ((2000, 4000, 5000), 300, 2), ((2000, 4000), 300, 2), ((1,), 0, 0), ((1000,), 382, 1), ((7000,), 0, 1)]
+    maxs = [(None, 2818, 2), ((2000, 4000, 5000), 2818, 1), ((2000, 4000), 300, 2), ((1,), 0, 0), ((1000,), 382, 1), ((7000,), 0, 1)]
+    for cols, exp, cnt in mins:
+        f = w.new_row(*cols) if cols else None
+        assert w.frag_minmax("v", False, f) == (exp, cnt), ("min", cols)
+    for cols, exp, cnt in maxs:
+        f = w.new_row(*cols) if cols else None
+        assert w.frag_minmax("v", True, f) == (exp, cnt), ("max", cols)
+
+
+# ---- fragment_internal_test.go:502-694 TestFragment_Range ----
+def test_fragment_range_eq_neq(w):
+    _bsi(w, [(1000, 382), (2000, 300), (3000, 2818), (4000, 300)])
+    assert w.frag_range("v", abi.BSI_EQ, 300) == [2000, 4000]
+    assert w.frag_range("v", abi.BSI_NEQ, 300) == [1000, 3000]
+
+
+def test_fragment_range_lt_gt_between(w):
+    _bsi(w, [(1000, 382), (2000, 300), (3000, 2817), (4000, 301), (5000, 1), (6000, 0)])
+    assert w.frag_range("v", abi.BSI_LT, 301) == [2000, 5000, 6000]
+    assert w.frag_range("v", abi.BSI_LT, 300) == [5000, 6000]
+    assert w.frag_range("v", abi.BSI_LTE, 301) == [2000, 4000, 5000, 6000]
+    assert w.frag_range("v", abi.BSI_LTE, 300) == [2000, 5000, 6000]
+    assert w.frag_range("v", abi.BSI_GT, 300) == [1000, 3000, 4000]
+    assert w.frag_range("v", abi.BSI_GT, 301) == [1000, 3000]
+    assert w.frag_range("v", abi.BSI_GTE, 300) == [1000, 2000, 3000, 4000]
+    assert w.frag_range("v", abi.BSI_GTE, 301) == [1000, 3000, 4000]
+    assert w.frag_range("v", abi.BSI_BETWEEN, 300, 2817) == [1000, 2000, 3000, 4000]
+    assert w.frag_range("v", abi.BSI_BETWEEN, 301, 2817) == [1000, 3000, 4000]
+    assert w.frag_range("v", abi.BSI_BETWEEN, 301, 2816) == [1000, 4000]
+    assert w.frag_range("v", abi.BSI_BETWEEN, 300, 2816) == [1000, 2000, 4000]
+
+
+# ---- fragment_internal_test.go:959-979 TestFragment_Top ----
+def test_fragment_top(w):
+    w.create_field("f")
+    w.set_bits("f", 100, 1, 3, 200)
+    w.set_bits("f", 101, 1)
+    w.set_bits("f", 102, 1, 2)
+    w.recalculate_cache("f")
+    assert w.frag_top("f", n=2) == [(100, 3), (102, 2)]
+
+
+# ---- fragment_internal_test.go:1017-1042 TestFragment_TopN_Intersect ----
+def test_fragment_topn_intersect(w):
+    w.create_field("f")
+    src = w.new_row(1, 2, 3)
+    w.set_bits("f", 100, 1, 10, 11, 12)
+    w.set_bits("f", 101, 1, 2, 3, 4)
+    w.set_bits("f", 102, 1, 2, 4, 5, 6)
+    w.set_bits("f", 103, 1000, 1001, 1002)
+    w.recalculate_cache("f")
+    assert w.frag_top("f", n=3, src=src) == [(101, 3), (102, 2), (100, 1)]
+
+
+# ---- fragment_internal_test.go:1044-1094 TestFragment_TopN_Intersect_Large ----
+def test_fragment_topn_intersect_large(w):
+    w.create_field("f")
+    src = w.new_row(*range(980, 1000))
+    fam = w._fam("f")
+    w.orc.cache_config(fam, 0, False, 50000)
+    for i in range(1000):
+        for j in range(i):
+            w.orc.set_bit(fam, 0, i, j)
+    w.recalculate_cache("f")
+    assert w.frag_top("f", n=10, src=src) == [(999 - k, 19 - k) for k in range(10)]
+
+
+# ---- fragment_internal_test.go:1096-1113 TestFragment_TopN_IDs ----
+def test_fragment_topn_ids(w):
+    w.create_field("f")
+    w.set_bits("f", 100, 1, 2, 3)
+    w.set_bits("f", 101, 4, 5, 6, 7)
+    w.set_bits("f", 102, 8, 9, 10, 11, 12)
+    w._touch("f", 0)
+    assert w.frag_top("f", row_ids=[100, 101, 200]) == [(101, 4), (100, 3)]
+
+
+# ---- fragment_internal_test.go:1115-1131 TestFragment_TopN_NopCache (host never asks the engine:
+# executor.go:978 rejects TopN on cache-less fields, so this one pins the oracle only) ----
+def test_fragment_topn_nop_cache():
+    w = World("oracle")
+    w.create_field("f", cache_none=True)
+    w.set_bits("f", 100, 1, 2, 3)
+    w.set_bits("f", 101, 4, 5, 6, 7)
+    assert w.frag_top("f", row_ids=[100, 101, 200]) == []
+
+
+# ---- fragment_internal_test.go:1135-1195 TestFragment_TopN_CacheSize ----
+def test_fragment_topn_cache_size(w):
+    w.create_field("f", cache_size=3)
+    w.set_bits("f", 100, 1, 2, 3)
+    w.set_bits("f", 101, 4, 5, 6, 7)
+    w.set_bits("f", 102, 8, 9, 10, 11, 12)
+    w.set_bits("f", 103, 8, 9, 10, 11, 12, 13)
+    w.set_bits("f", 104, 8, 9, 10, 11, 12, 13, 14)
+    w.set_bits("f", 105, 10, 11)
+    w.recalculate_cache("f")
+    assert w.frag_top("f", n=5) == [(104, 7), (103, 6), (102, 5)]
+
+
+# ---- executor_test.go:136-508: Difference / Intersect / Union / Xor / Count over two shards ----
+def _two_shard_rows(w):
+    w.create_field("general")
+    w.set_bits("general", 10, 3, SW + 1)
+    w.set_bits("general", 10, SW + 2)
+    w.set_bits("general", 11, 2, SW + 2)
+    return [0, 1]
+
+
+def test_executor_difference_literal(w):
+    # TestExecutor_Execute_Difference/RowIDColumnID (executor_test.go:136-152), literal
+    w.create_field("general")
+    w.set_bits("general", 10, 1, 2, 3)
+    w.set_bits("general", 11, 2, 4)
+    assert w.ex.row_columns(Difference(Row("general", 10), Row("general", 11)), [0]) == [1, 3]
+
+
+def test_executor_set_ops(w):
+    # same shapes as TestExecutor_Execute_Intersect/Union/Xor/Count (executor_test.go:214-508): two rows over two
+    # shards; expected columns derived by hand from the set definitions
+    shards = _two_shard_rows(w)
+    ex = w.ex
+    r10, r11 = Row("general", 10), Row("general", 11)
+    assert ex.row_columns(Difference(r10, r11), shards) == [3, SW + 1]
+    assert ex.row_columns(Intersect(r10, r11), shards) == [SW + 2]
+    assert ex.row_columns(Union(r10, r11), shards) == [2, 3, SW + 1, SW + 2]
+    assert ex.row_columns(Xor(r10, r11), shards) == [2, 3, SW + 1]
+    assert ex.count(r10, shards) == 3
+    assert ex.count(Union(), shards) == 0 and ex.row_columns(Xor(), shards) == []  # empty Union/Xor = empty row
+    with pytest.raises(Exception, match="empty Intersect"):
+        ex.count(Intersect(), shards)
+
+
+# ---- executor_test.go:2759-2833 TestExecutor_Execute_Not ----
+def test_executor_not(w):
+    w.create_field("exists")
+    w.create_field("f")
+    for col in (1, 2, 3, SW + 1):
+        w.set_bit("exists", 0, col)
+    w.set_bits("f", 10, 3, SW + 1)
+    w.set_bits("f", 11, 2)
+    ex = w.ex
+    assert ex.row_columns(Not(Row("f", 10)), [0, 1]) == [1, 2]
+    assert ex.row_columns(Not(Row("f", 11)), [0, 1]) == [1, 3, SW + 1]
+    assert ex.row_columns(Not(Union(Row("f", 10), Row("f", 11))), [0, 1]) == [1]
+    assert ex.row_columns(Not(Row("f", 99)), [0, 1]) == [1, 2, 3, SW + 1]
+
+
+# ---- executor_test.go:895-1215 TopN across two shards ----
+def test_executor_topn_two_shards(w):
+    w.create_field("f")
+    w.create_field("other")
+    # TestExecutor_Execute_TopN/RowIDColumnID (:895-935): literal Set() calls and expected pairs
+    w.set_bits("f", 0, 0, 1, SW, SW + 2, 5 * SW + 100)
+    w.set_bits("f", 10, 0, SW)
+    w.set_bits("f", 20, SW)
+    w.set_bits("other", 0, 0)
+    for s in (0, 1, 5):
+        w.recalculate_cache("f", s)
+    assert w.ex.topn("f", [0, 1, 5], n=2) == [(0, 5), (10, 2)]
+
+
+def test_executor_topn_src(w):
+    # TestExecutor_Execute_TopN_Src (:1180-1215): literal bits and expected pairs
+    w.create_field("f")
+    w.create_field("other")
+    w.set_bits("f", 0, 0, 1, SW)
+    w.set_bits("f", 10, SW, SW + 1)
+    w.set_bits("f", 20, SW, SW + 1, SW + 2)
+    w.set_bits("other", 100, SW, SW + 1, SW + 2)
+    for s in (0, 1):
+        w.recalculate_cache("f", s)
+    assert w.ex.topn("f", [0, 1], n=3, src=Row("other", 100)) == [(20, 3), (10, 2), (0, 1)]
+
+
+# ---- executor_test.go:1516-1633 Sum, :1262-1417 Min/Max (two shards, negatives) ----
+def test_executor_sum_min_max(w):
+    # TestExecutor_Execute_Sum/ColumnID (:1516-1565): literal Set() calls, Sum = 200/5, filtered 80/2
+    w.create_field("x")
+    w.create_field("foo", type="int", min=-990, max=1000)
+    w.set_bits("x", 0, 0, SW + 1)
+    for col, v in [(0, 20), (SW, 30), (SW + 2, 40), (5 * SW + 100, 50), (SW + 1, 60)]:
+        w.set_value("foo", col, v)
+    ex = w.ex
+    shards = [0, 1, 5]
+    assert ex.sum("foo", shards) == (200, 5)
+    assert ex.sum("foo", shards, Row("x", 0)) == (80, 2)
+    assert ex.sum("foo", shards, Row("x", 7)) == (0, 0)                  # executor.go:438-440
+    assert ex.min("foo", [4]) == (0, 0)
+
+
+def test_executor_min_max(w):
+    # TestExecutor_Execute_MinMax/ColumnID (:1262-1325) + the Max table of the ColumnKey variant (:1385-1410)
+    w.create_field("x")
+    w.create_field("f", type="int", min=-1100, max=1000)
+    w.set_bits("x", 0, 0, 3, SW + 1)
+    w.set_bits("x", 1, 1)
+    w.set_bits("x", 2, SW + 2)
+    for col, v in [(0, 20), (1, -5), (2, -5), (3, 10), (SW, 30), (SW + 2, 40), (5 * SW + 100, 50), (SW + 1, 60)]:
+        w.set_value("f", col, v)
+    ex = w.ex
+    shards = [0, 1, 5]
+    for filt, exp, cnt in [(None, -5, 2), (Row("x", 0), 10, 1), (Row("x", 1), -5, 1), (Row("x", 2), 40, 1)]:
+        assert ex.min("f", shards, filt) == (exp, cnt), ("min", repr(filt))
+    for filt, exp, cnt in [(None, 60, 1), (Row("x", 0), 60, 1), (Row("x", 1), -5, 1), (Row("x", 2), 40, 1)]:
+        assert ex.max("f", shards, filt) == (exp, cnt), ("max", repr(filt))
+
+
+# ---- executor_test.go:1977-2168 TestExecutor_Execute_Row_BSIGroup (one shard + edges) ----
+def test_executor_row_bsigroup(w):
+    w.create_field("foo", type="int", min=-990, max=1000)
+    w.create_field("edge", type="int", min=-900, max=1000)
+    foo = [(50, 20), (SW, 20), (SW + 5, 30), (2, -10), (SW + 2, 60), (7, 0)]
+    for col, v in foo:
+        w.set_value("foo", col, v)
+    for col, v in [(1, -100), (2, -900), (3, 1000), (4, 1)]:
+        w.set_value("edge", col, v)
+    ex = w.ex
+    sh = [0, 1]
+
+    def q(field, op, a=None, b=None):
+        return ex.row_columns(ex.row_range(field, op, a, b), sh)
+
+    by_val = lambda pred: sorted(c for c, v in foo if pred(v))  # noqa: E731
+    assert q("foo", abi.BSI_EQ, 20) == by_val(lambda v: v == 20)
+    assert q("foo", abi.BSI_NEQ, 20) == by_val(lambda v: v != 20)
+    assert q("foo", abi.BSI_LT, 30) == by_val(lambda v: v < 30)
+    assert q("foo", abi.BSI_LTE, 30) == by_val(lambda v: v <= 30)
+    assert q("foo", abi.BSI_GT, 20) == by_val(lambda v: v > 20)
+    assert q("foo", abi.BSI_GTE, 20) == by_val(lambda v: v >= 20)
+    assert q("foo", abi.BSI_GT, -11) == by_val(lambda v: v > -11)
+    assert q("foo", abi.BSI_LT, -5) == by_val(lambda v: v < -5)
+    assert q("foo", abi.BSI_BETWEEN, 0, 30) == by_val(lambda v: 0 <= v <= 30)
+    assert q("foo", abi.BSI_BETWEEN, -20, 20) == by_val(lambda v: -20 <= v <= 20)
+    assert q("foo", abi.BSI_NEQ, None) == by_val(lambda v: True)                  # != null
+    # out-of-range edges (executor.go:1640-1660)
+    assert q("foo", abi.BSI_GT, 5000) == []
+    assert q("foo", abi.BSI_LT, -5000) == []
+    assert q("foo", abi.BSI_LT, 5000) == by_val(lambda v: True)                   # notNull
+    assert q("foo", abi.BSI_GTE, -5000) == by_val(lambda v: True)
+    assert q("foo", abi.BSI_EQ, 5000) == []
+    assert q("foo", abi.BSI_NEQ, 5000) == by_val(lambda v: True)
+    assert q("foo", abi.BSI_BETWEEN, 2000, 3000) == []
+    assert q("foo", abi.BSI_BETWEEN, -5000, 5000) == by_val(lambda v: True)
+    assert q("edge", abi.BSI_GTE, -900) == [1, 2, 3, 4]
+    assert q("edge", abi.BSI_LTE, 1000) == [1, 2, 3, 4]
+    assert q("edge", abi.BSI_EQ, -900) == [2] and q("edge", abi.BSI_EQ, 1000) == [3]
