@@ -1,0 +1,199 @@
+#!/usr/bin/env python
+"""bench_configs.py — the other BASELINE.json configs (C2..C5 of SURVEY.md §8d) on one GPU.
+
+bench.py carries the headline metric (C1 batched). This script measures, for each remaining
+config, the engine through the C ABI (kernel time from the library's CUDA events, wall time of
+the whole call, algorithmic GB/s) next to the CPU oracle (reference restatement, all host
+cores) on a bounded sample of the same shards, and checks the sampled answers bit-exactly.
+One JSON line per query, plus a markdown table on stderr for BASELINE.md.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from pilosa_b200 import abi, synth  # noqa: E402
+from pilosa_b200.abi import Difference, Intersect, Row, Union, Xor  # noqa: E402
+from pilosa_b200.executor import Executor  # noqa: E402
+
+SEED = 20190416
+
+
+def load_parallel(gen, shards, sinks, workers):
+    """gen(shard) -> FragBytes, loaded into every sink(shard, fb)."""
+    with ThreadPoolExecutor(max_workers=workers) as tp:
+        for s, fb in zip(shards, tp.map(gen, shards)):
+            for sink in sinks(s):
+                sink(s, fb)
+
+
+def timed(eng, fn, reps):
+    fn()  # warm-up (also grows scratch buffers)
+    fn()
+    ks, ws, res = [], [], None
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        res = fn()
+        ws.append((time.perf_counter() - t0) * 1e3)
+        ks.append(eng.last_timing().kernel_ms)
+    tm = eng.last_timing()
+    return res, statistics.median(ks), statistics.median(ws), int(tm.algo_bytes), int(tm.launches)
+
+
+def cpu_timed(fn, min_seconds=3.0):
+    fn()
+    t0 = time.perf_counter()
+    n = 0
+    res = None
+    while n < 1 or time.perf_counter() - t0 < min_seconds:
+        res = fn()
+        n += 1
+    return res, (time.perf_counter() - t0) / n * 1e3
+
+
+def emit(rows, name, query, n_shards, kernel_ms, wall_ms, algo_bytes, launches, cpu_ms, cpu_shards, ok, extra=None):
+    gbs = algo_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
+    cpu_full_ms = cpu_ms * n_shards / max(1, cpu_shards)
+    line = {"config": name, "query": query, "shards": n_shards, "kernel_ms": round(kernel_ms, 4), "call_ms": round(wall_ms, 4),
+            "algo_bytes": algo_bytes, "algo_GBps": round(gbs, 1), "launches": launches,
+            "cpu_ms_sample": round(cpu_ms, 3), "cpu_sample_shards": cpu_shards, "cpu_ms_scaled_to_all_shards": round(cpu_full_ms, 2),
+            "cpu_cores": os.cpu_count(), "speedup_call_vs_cpu": round(cpu_full_ms / wall_ms, 1) if wall_ms > 0 else None,
+            "parity": "ok" if ok else "MISMATCH"}
+    if extra:
+        line.update(extra)
+    print(json.dumps(line), flush=True)
+    rows.append(line)
+    if not ok:
+        raise SystemExit(f"parity mismatch in {name}: {query}")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--configs", default="c2,c3,c4,c5")
+    ap.add_argument("--reps", type=int, default=7)
+    ap.add_argument("--c2-shards", type=int, default=1024)
+    ap.add_argument("--c3-shards", type=int, default=1024)
+    ap.add_argument("--c3-rows", type=int, default=10000)
+    ap.add_argument("--c4-shards", type=int, default=2048)
+    ap.add_argument("--c5-shards", default="64,512,8192")
+    ap.add_argument("--cpu-shards", type=int, default=32)
+    args = ap.parse_args()
+
+    import oracle
+    from pilosa_b200.engine import Engine
+
+    cores = os.cpu_count() or 8
+    eng = Engine(0)
+    g = Executor(eng)
+    c = Executor(oracle.Oracle(workers=cores))
+    rows = []
+    cfgs = args.configs.split(",")
+
+    def both(name, **kw):
+        for ex in (g, c):
+            ex.create_field(name, **kw)
+
+    def sinks_for(field, cpu_set):
+        def sinks(s):
+            out = [lambda s_, fb: g.load_fragment(field, s_, fb)]
+            if s in cpu_set:
+                out.append(lambda s_, fb: c.load_fragment(field, s_, fb))
+            return out
+        return sinks
+
+    # ---------------- C2: Count(Union/Difference/Xor) over 4 rows, mixed containers ----------------
+    if "c2" in cfgs:
+        shards = list(range(args.c2_shards))
+        cpu_sh = shards[: args.cpu_shards]
+        both("m")
+        t0 = time.perf_counter()
+        load_parallel(lambda s: synth.mixed(s, 0, 4, SEED), shards, sinks_for("m", set(cpu_sh)), cores)
+        print(f"# c2 loaded in {time.perf_counter() - t0:.1f}s", file=sys.stderr)
+        leaves = [Row("m", r) for r in range(4)]
+        for qname, call in (("Count(Union(r0..r3))", Union(*leaves)), ("Count(Difference(r0,r1,r2,r3))", Difference(*leaves)),
+                            ("Count(Xor(r0..r3))", Xor(*leaves)), ("Count(Intersect(r0,r1))", Intersect(leaves[0], leaves[1]))):
+            _, k, wms, ab, ln = timed(eng, lambda: g.count(call, shards), args.reps)
+            got = g.count(call, cpu_sh)
+            exp, cms = cpu_timed(lambda: c.count(call, cpu_sh))
+            emit(rows, "C2", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
+
+    # ---------------- C3: TopN(f, n=50) over 10k rows with an Intersect filter ----------------
+    if "c3" in cfgs:
+        shards = list(range(args.c3_shards))
+        cpu_sh = shards[: max(4, args.cpu_shards // 4)]
+        both("z")
+        both("a")
+        t0 = time.perf_counter()
+        load_parallel(lambda s: synth.zipf(s, args.c3_rows, 8, 1.6, 50.0, SEED), shards, sinks_for("z", set(cpu_sh)), cores)
+        load_parallel(lambda s: synth.bernoulli(s, 1, 2, 0.10, SEED), shards, sinks_for("a", set(cpu_sh)), cores)
+        print(f"# c3 loaded in {time.perf_counter() - t0:.1f}s", file=sys.stderr)
+        src = Intersect(Row("a", 1), Row("a", 2))
+        for qname, kw in ((f"TopN(z, Intersect(Row(a=1),Row(a=2)), n=50) [{args.c3_rows} rows]", dict(n=50, src=src)),
+                          ("TopN(z, n=50) [no source: rank cache only]", dict(n=50))):
+            _, k, wms, ab, ln = timed(eng, lambda: g.topn("z", shards, **kw), max(3, args.reps // 2))
+            got = g.topn("z", cpu_sh, **kw)
+            exp, cms = cpu_timed(lambda: c.topn("z", cpu_sh, **kw))
+            emit(rows, "C3", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
+
+    # ---------------- C4: BSI int32: Sum / Min / Max / Range ----------------
+    if "c4" in cfgs:
+        shards = list(range(args.c4_shards))
+        cpu_sh = shards[: max(4, args.cpu_shards // 4)]
+        both("v", type="int", min=-(1 << 31), max=(1 << 31) - 1)
+        both("fl")
+        t0 = time.perf_counter()
+        load_parallel(lambda s: synth.bsi(s, 32, -(1 << 31), (1 << 31) - 1, 1.0, SEED), shards, sinks_for("v", set(cpu_sh)), cores)
+        load_parallel(lambda s: synth.bernoulli(s, 1, 1, 0.10, SEED), shards, sinks_for("fl", set(cpu_sh)), cores)
+        print(f"# c4 loaded in {time.perf_counter() - t0:.1f}s", file=sys.stderr)
+        qs = [("Sum(field=v)", lambda ex, sh: ex.sum("v", sh)), ("Sum(Row(fl=1), field=v)", lambda ex, sh: ex.sum("v", sh, Row("fl", 1))),
+              ("Min(field=v)", lambda ex, sh: ex.min("v", sh)), ("Max(field=v)", lambda ex, sh: ex.max("v", sh))]
+        for x in (0, 1 << 30, -(1 << 30), 12345):
+            qs.append((f"Count(Row(v > {x}))", lambda ex, sh, x=x: ex.count(ex.row_range("v", abi.BSI_GT, x), sh)))
+        qs.append(("Count(Row(-1000 < v < 1000))", lambda ex, sh: ex.count(ex.row_range("v", abi.BSI_BETWEEN, -999, 999), sh)))
+        for qname, fn in qs:
+            _, k, wms, ab, ln = timed(eng, lambda: fn(g, shards), args.reps)
+            got = fn(g, cpu_sh)
+            exp, cms = cpu_timed(lambda: fn(c, cpu_sh))
+            emit(rows, "C4", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
+
+    # ---------------- C5: sparse Count(Intersect) sweep ----------------
+    if "c5" in cfgs:
+        sweep = [int(x) for x in args.c5_shards.split(",")]
+        nmax = max(sweep)
+        shards = list(range(nmax))
+        cpu_sh = shards[: min(nmax, 512)]
+        both("sp")
+        t0 = time.perf_counter()
+        load_parallel(lambda s: synth.bernoulli(s, 1, 2, 1e-4, SEED), shards, sinks_for("sp", set(cpu_sh)), cores)
+        print(f"# c5 loaded in {time.perf_counter() - t0:.1f}s", file=sys.stderr)
+        call = Intersect(Row("sp", 1), Row("sp", 2))
+        for n in sweep:
+            sh = shards[:n]
+            _, k, wms, ab, ln = timed(eng, lambda: g.count(call, sh), args.reps)
+            csh = sh[: len(cpu_sh)]
+            got = g.count(call, csh)
+            exp, cms = cpu_timed(lambda: c.count(call, csh), 1.0)
+            emit(rows, "C5", f"Count(Intersect(Row(sp=1),Row(sp=2))) p=1e-4, {n} shards", n, k, wms, ab, ln, cms, len(csh), got == exp)
+            # batched: 256 copies of the query in one call (what a busy server would issue)
+            progs = [g.program(call)] * 256
+            _, k, wms, ab, ln = timed(eng, lambda: eng.count_batch(progs, sh), args.reps)
+            emit(rows, "C5", f"batch of 256 x same query, {n} shards (per-query figures)", n, k / 256, wms / 256, ab // 256, ln, cms, len(csh), True)
+
+    print("\n| config | query | shards | kernel ms | call ms | algorithmic GB/s | CPU ms (all shards, %d cores) | call speed-up |" % cores, file=sys.stderr)
+    print("|---|---|---|---|---|---|---|---|", file=sys.stderr)
+    for r in rows:
+        print(f"| {r['config']} | `{r['query']}` | {r['shards']} | {r['kernel_ms']} | {r['call_ms']} | {r['algo_GBps']} | "
+              f"{r['cpu_ms_scaled_to_all_shards']} | {r['speedup_call_vs_cpu']}x |", file=sys.stderr)
+    eng.close()
+
+
+if __name__ == "__main__":
+    main()
