@@ -4,8 +4,12 @@
 #include "engine.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <thread>
 
 #include "kernels.cuh"
 #include "kernels_bsi.cuh"
@@ -121,7 +125,10 @@ extern "C" int pb200_init(int device, size_t hbm_budget_bytes, pb200_ctx** out) 
 
 static void free_fragment(Fragment& f) {
   if (f.blob) cudaFree(f.blob);
+  if (f.d_rank) cudaFree(f.d_rank);
   f.blob = nullptr;
+  f.d_rank = nullptr;
+  f.d_rank_valid = false;
 }
 
 extern "C" int pb200_shutdown(pb200_ctx* ctx) {
@@ -352,6 +359,7 @@ extern "C" int pb200_rank_set(pb200_ctx* ctx, pb200_family family, uint64_t shar
   it->second.rank_ids.assign(row_ids, row_ids + n);
   it->second.rank_counts.assign(counts, counts + n);
   it->second.rank_from_host = true;
+  it->second.d_rank_valid = false;  // rebuilt on the next TopN
   return PB200_OK;
 }
 

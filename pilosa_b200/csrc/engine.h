@@ -35,6 +35,8 @@ struct Fragment {
   // (pb200_rank_set) or derived from exact row counts (count desc, id asc, 50000 entries).
   std::vector<uint64_t> rank_ids, rank_counts;
   bool rank_from_host = false;
+  uint32_t* d_rank = nullptr;  // device copy of the rank order as row-table indices (TopN)
+  bool d_rank_valid = false;
 };
 
 struct Family {
@@ -77,7 +79,8 @@ struct pb200_ctx {
   bool families_dirty = true;
   pb200::DevBuf d_batch, d_out, d_slow, d_temp, d_dense, d_dense_n, d_misc, d_topn, d_bsi;
   pb200::PinBuf h_stage, h_out, h_algo;
-  bool mm_attr_set = false;
+  bool mm_attr_set = false, topn_attr_set = false;
+  const uint64_t* dense_shards_dev = nullptr;  // shard list of the source rows currently in d_dense (TopN pass 1 -> 2)
   size_t pending_n_out = 0;      // split Count batch in flight (count_begin / count_end)
   bool pending_launched = false;
   pb200_timing timing{};

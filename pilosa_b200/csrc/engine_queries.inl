@@ -152,10 +152,30 @@ void sort_pairs(std::vector<HPair>& p) {  // count desc; ties by ascending id (d
   std::stable_sort(p.begin(), p.end(), [](const HPair& x, const HPair& y) { return x.count != y.count ? x.count > y.count : x.id < y.id; });
 }
 
-// fragment.top (fragment.go:1568-1700) over candidate pairs whose src-intersection counts
-// are already known (`isect[k]`, ignored when !has_src).
-std::vector<HPair> top_walk(const std::vector<HPair>& pairs, const uint32_t* isect, bool has_src, int n, uint64_t min_threshold,
-                            uint64_t tanimoto, uint64_t src_count) {
+// Host-side shard loop on a few threads (the reference runs its per-shard jobs on a worker
+// pool of NumCPU goroutines, executor.go:83-107; the selection walks are independent per shard).
+template <class F>
+void parallel_shards(uint32_t n, F&& fn) {
+  unsigned hw = std::thread::hardware_concurrency();
+  unsigned nt = std::min<unsigned>(hw ? hw : 4, 8);
+  if (n < 256 || nt < 2) { for (uint32_t s = 0; s < n; s++) fn(s); return; }
+  std::vector<std::thread> th;
+  std::atomic<uint32_t> next{0};
+  for (unsigned t = 0; t < nt; t++)
+    th.emplace_back([&] {
+      for (;;) {
+        uint32_t b = next.fetch_add(32);
+        if (b >= n) break;
+        for (uint32_t s = b; s < std::min(n, b + 32); s++) fn(s);
+      }
+    });
+  for (auto& t : th) t.join();
+}
+
+// fragment.top (fragment.go:1568-1700) over candidates (ids[k], cached counts[k]) whose
+// src-intersection counts are already known (`isect[k]`, ignored when !has_src).
+std::vector<HPair> top_walk(const uint64_t* ids, const uint64_t* counts, size_t n_pairs, const uint32_t* isect, bool has_src, int n,
+                            uint64_t min_threshold, uint64_t tanimoto, uint64_t src_count) {
   double min_tan = 0, max_tan = 0;
   if (tanimoto > 0 && has_src) {
     min_tan = double(src_count * tanimoto) / 100;
@@ -164,8 +184,8 @@ std::vector<HPair> top_walk(const std::vector<HPair>& pairs, const uint32_t* ise
     tanimoto = 0;
   }
   PairHeap results;
-  for (size_t k = 0; k < pairs.size(); k++) {
-    const uint64_t row_id = pairs[k].id, cnt = pairs[k].count;
+  for (size_t k = 0; k < n_pairs; k++) {
+    const uint64_t row_id = ids[k], cnt = counts[k];
     if (cnt == 0) continue;
     if (tanimoto > 0) { if (double(cnt) <= min_tan || double(cnt) >= max_tan) continue; }
     else if (cnt < min_threshold) continue;
@@ -198,16 +218,34 @@ uint64_t exact_row_count(const Fragment& f, uint64_t id) {
   return f.row_counts[size_t(it - f.row_ids.begin())];
 }
 
-struct FragRankDev {  // lazily uploaded rank -> row-index table of one fragment
-  uint32_t* d = nullptr;
-  size_t n = 0;
-};
+// Device copy of a fragment's rank order as row-table indices; built when the rank list
+// changes (load / pb200_rank_set), reused by every TopN call.
+int ensure_rank_table(pb200_ctx* ctx, Fragment& f) {
+  if (f.d_rank_valid) return PB200_OK;
+  if (f.d_rank) { CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream)); CUDA_TRY(ctx, cudaFree(f.d_rank)); f.d_rank = nullptr; }
+  const size_t n = f.rank_ids.size();
+  if (n) {
+    std::vector<uint32_t> idx(n);
+    for (size_t k = 0; k < n; k++) {
+      const uint64_t id = f.rank_ids[k];
+      if (f.dev.dense) idx[k] = id < f.dev.nrows ? uint32_t(id) : 0xffffffffu;
+      else {
+        auto it = std::lower_bound(f.row_ids.begin(), f.row_ids.end(), id);
+        idx[k] = (it != f.row_ids.end() && *it == id) ? uint32_t(it - f.row_ids.begin()) : 0xffffffffu;
+      }
+    }
+    CUDA_TRY(ctx, cudaMalloc(&f.d_rank, n * 4));
+    CUDA_TRY(ctx, cudaMemcpy(f.d_rank, idx.data(), n * 4, cudaMemcpyHostToDevice));
+  }
+  f.d_rank_valid = true;
+  return PB200_OK;
+}
 
 // One TopN pass over `shards` (executor.go:905-930 executeTopNShards without the final sort):
 // per-shard fragment.top results.
 int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, uint32_t n_src_nodes, uint32_t n,
               const uint64_t* ids, size_t n_ids, uint64_t min_threshold, uint64_t tanimoto, const uint64_t* shards,
-              uint32_t n_shards, std::vector<std::vector<HPair>>& per_shard) {
+              uint32_t n_shards, std::vector<std::vector<HPair>>& per_shard, bool reuse_src = false) {
   if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
   if (tanimoto > 100) return fail(ctx, PB200_ERR_INVALID, "Tanimoto Threshold is from 1 to 100 only");  // executor.go:988
   if (min_threshold == 0) min_threshold = 1;  // defaultMinThreshold, executor.go:37,984
@@ -215,143 +253,163 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
   const bool has_src = src_prog && n_src_nodes;
   per_shard.assign(n_shards, {});
   if (n_shards == 0) return PB200_OK;
+  static const bool trace = getenv("PB200_TRACE") != nullptr;
+  auto t_start = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!trace) return;
+    auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "[pb200 topn] %-18s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_start).count());
+    t_start = now;
+  };
 
-  // candidate pairs per shard (topBitmapPairs, fragment.go:1702-1738)
-  std::vector<std::vector<HPair>> cands(n_shards);
-  std::vector<const Fragment*> frs(n_shards, nullptr);
+  std::vector<Fragment*> frs(n_shards, nullptr);
   for (uint32_t s = 0; s < n_shards; s++) {
     auto it = fam.frags.find(shards[s]);
-    if (it == fam.frags.end()) continue;
-    const Fragment& f = it->second;
-    frs[s] = &f;
-    auto& cd = cands[s];
-    if (n_ids == 0) {
-      cd.resize(f.rank_ids.size());
-      for (size_t k = 0; k < cd.size(); k++) cd[k] = {f.rank_ids[k], f.rank_counts[k]};
-    } else {
+    if (it != fam.frags.end()) frs[s] = &it->second;
+  }
+  // explicit ids: candidate pairs per shard (topBitmapPairs, fragment.go:1702-1738), sorted by count
+  std::vector<std::vector<uint64_t>> id_ids, id_counts;
+  std::vector<std::vector<uint32_t>> id_pos;  // position of each sorted candidate in the caller's `ids`
+  if (n_ids) {
+    id_ids.resize(n_shards); id_counts.resize(n_shards); id_pos.resize(n_shards);
+    parallel_shards(n_shards, [&](uint32_t s) {
+      if (!frs[s]) return;
+      const Fragment& f = *frs[s];
       std::unordered_map<uint64_t, uint64_t> cache;
       if (f.rank_from_host) for (size_t k = 0; k < f.rank_ids.size(); k++) cache[f.rank_ids[k]] = f.rank_counts[k];
+      std::vector<std::pair<HPair, uint32_t>> cd;
       for (size_t k = 0; k < n_ids; k++) {
         uint64_t c = 0;
         if (f.rank_from_host) { auto ci = cache.find(ids[k]); if (ci != cache.end()) c = ci->second; }
         if (c == 0) c = exact_row_count(f, ids[k]);
-        if (c > 0) cd.push_back({ids[k], c});
+        if (c > 0) cd.push_back({{ids[k], c}, uint32_t(k)});
       }
-      sort_pairs(cd);
-    }
+      std::stable_sort(cd.begin(), cd.end(), [](const auto& x, const auto& y) {
+        return x.first.count != y.first.count ? x.first.count > y.first.count : x.first.id < y.first.id;
+      });
+      for (auto& e : cd) { id_ids[s].push_back(e.first.id); id_counts[s].push_back(e.first.count); id_pos[s].push_back(e.second); }
+    });
   }
 
-  std::vector<uint32_t> isect;             // flattened per-candidate src intersection counts
+  lap("candidates");
   std::vector<uint64_t> off(n_shards + 1, 0);
   std::vector<uint64_t> src_counts(n_shards, 0);
+  const uint32_t* isect = nullptr;
   TRY(ensure_dev(ctx, ctx->d_misc, 64));
   timing_begin(ctx);
   if (has_src) {
+    for (uint32_t s = 0; s < n_shards; s++) {
+      if (frs[s] && !n_ids) TRY(ensure_rank_table(ctx, *frs[s]));
+      off[s + 1] = off[s] + ((frs[s] && !n_ids) ? frs[s]->rank_ids.size() : 0);
+    }
     BatchDev bd{};
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    TRY(eval_dense(ctx, src_prog, n_src_nodes, shards, n_shards, bd));
-    // candidate tables on the device
-    for (uint32_t s = 0; s < n_shards; s++) off[s + 1] = off[s] + cands[s].size();
+    if (reuse_src && ctx->dense_shards_dev) {
+      bd.shards = ctx->dense_shards_dev;  // pass 2: the source rows of pass 1 are still resident in d_dense
+    } else {
+      TRY(eval_dense(ctx, src_prog, n_src_nodes, shards, n_shards, bd));
+      ctx->dense_shards_dev = bd.shards;
+    }
     const uint64_t total = off[n_shards];
-    // layout in d_topn: [counts u32 x total][cand_off u64 x ns][rank_n u32 x ns][ptrs x ns][rowidx / ids ...]
-    size_t o_counts = 0;
-    size_t o_off = align_up(o_counts + total * 4, 16);
+    const size_t n_counts = n_ids ? size_t(n_shards) * n_ids : size_t(total);
+    // d_topn: [cand_off u64 x ns][rank_n u32 x ns][ptrs x ns][ids u64 x n_ids] ; counts in d_bsi
+    size_t o_off = 0;
     size_t o_n = o_off + size_t(n_shards) * 8;
     size_t o_ptr = align_up(o_n + size_t(n_shards) * 4, 16);
-    size_t o_idx = o_ptr + size_t(n_shards) * 8;
-    size_t idx_bytes = n_ids ? n_ids * 8 : total * 4;
-    size_t total_bytes = o_idx + idx_bytes;
+    size_t o_ids = o_ptr + size_t(n_shards) * 8;
+    size_t total_bytes = o_ids + n_ids * 8;
     TRY(ensure_dev(ctx, ctx->d_topn, total_bytes));
-    TRY(ensure_pin(ctx, ctx->h_out, std::max<size_t>(total_bytes, size_t(n_shards) * kRowContainers * 4)));
-    uint8_t* h = static_cast<uint8_t*>(ctx->h_out.p);
+    TRY(ensure_pin(ctx, ctx->h_stage, total_bytes));
+    TRY(ensure_dev(ctx, ctx->d_bsi, std::max<size_t>(n_counts, 1) * 4));
+    TRY(ensure_pin(ctx, ctx->h_out, std::max<size_t>(n_counts, 1) * 4 + size_t(n_shards) * kRowContainers * 4));
+    uint8_t* h = static_cast<uint8_t*>(ctx->h_stage.p);
     uint8_t* d = static_cast<uint8_t*>(ctx->d_topn.p);
     std::memcpy(h + o_off, off.data(), size_t(n_shards) * 8);
     auto* hn = reinterpret_cast<uint32_t*>(h + o_n);
     auto* hp = reinterpret_cast<const uint32_t**>(h + o_ptr);
-    if (n_ids) {
-      std::memcpy(h + o_idx, ids, n_ids * 8);
-      for (uint32_t s = 0; s < n_shards; s++) { hn[s] = 0; hp[s] = nullptr; }
-    } else {
-      auto* hidx = reinterpret_cast<uint32_t*>(h + o_idx);
-      for (uint32_t s = 0; s < n_shards; s++) {
-        hn[s] = uint32_t(cands[s].size());
-        hp[s] = reinterpret_cast<const uint32_t*>(d + o_idx) + off[s];
-        const Fragment* f = frs[s];
-        for (size_t k = 0; k < cands[s].size(); k++) {
-          const uint64_t id = cands[s][k].id;
-          uint32_t ri;
-          if (f->dev.dense) ri = id < f->dev.nrows ? uint32_t(id) : 0xffffffffu;
-          else {
-            auto it = std::lower_bound(f->row_ids.begin(), f->row_ids.end(), id);
-            ri = (it != f->row_ids.end() && *it == id) ? uint32_t(it - f->row_ids.begin()) : 0xffffffffu;
-          }
-          hidx[off[s] + k] = ri;
-        }
-      }
+    uint32_t max_cand = uint32_t(n_ids);
+    for (uint32_t s = 0; s < n_shards; s++) {
+      const bool use = frs[s] && !n_ids;
+      hn[s] = use ? uint32_t(frs[s]->rank_ids.size()) : 0;
+      hp[s] = use ? frs[s]->d_rank : nullptr;
+      max_cand = std::max(max_cand, hn[s]);
     }
-    CUDA_TRY(ctx, cudaMemcpyAsync(d + o_off, h + o_off, total_bytes - o_off, cudaMemcpyHostToDevice, ctx->stream));
-    ctx->timing.h2d_bytes += total_bytes - o_off;
-    const size_t n_counts = n_ids ? size_t(n_shards) * n_ids : total;
-    if (n_ids) TRY(ensure_dev(ctx, ctx->d_bsi, n_counts * 4));
-    uint32_t* d_counts = n_ids ? static_cast<uint32_t*>(ctx->d_bsi.p) : reinterpret_cast<uint32_t*>(d + o_counts);
-    CUDA_TRY(ctx, cudaMemsetAsync(d_counts, 0, std::max<size_t>(n_counts * 4, 4), ctx->stream));
+    if (n_ids) std::memcpy(h + o_ids, ids, n_ids * 8);
+    CUDA_TRY(ctx, cudaMemcpyAsync(d, h, total_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->timing.h2d_bytes += total_bytes;
+    uint32_t* d_counts = static_cast<uint32_t*>(ctx->d_bsi.p);
     TopnParams tp{};
     tp.families = ctx->d_families; tp.family = family; tp.shards = bd.shards; tp.n_shards = n_shards;
     tp.src_dense = static_cast<const uint8_t*>(ctx->d_dense.p);
+    tp.src_n = static_cast<const uint32_t*>(ctx->d_dense_n.p);
     tp.rank_rowidx = reinterpret_cast<const uint32_t* const*>(d + o_ptr);
     tp.rank_n = reinterpret_cast<const uint32_t*>(d + o_n);
     tp.cand_off = reinterpret_cast<const uint64_t*>(d + o_off);
-    tp.ids = n_ids ? reinterpret_cast<const uint64_t*>(d + o_idx) : nullptr;
+    tp.ids = n_ids ? reinterpret_cast<const uint64_t*>(d + o_ids) : nullptr;
     tp.n_ids = uint32_t(n_ids);
+    tp.chunk = 2048;
+    tp.chunks_per_shard = std::max<uint32_t>(1, (max_cand + tp.chunk - 1) / tp.chunk);
     tp.counts = d_counts;
     tp.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 8);
     if (n_counts) {
-      const uint32_t items = n_shards * kRowContainers;
-      const uint32_t grid = std::min<uint32_t>(items, uint32_t(ctx->sm_count) * 8);
-      topn_count_kernel<<<grid, kTopnThreads, 0, ctx->stream>>>(tp);
+      if (!ctx->topn_attr_set) {
+        CUDA_TRY(ctx, cudaFuncSetAttribute(topn_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopnSmem));
+        ctx->topn_attr_set = true;
+      }
+      const uint64_t items = uint64_t(n_shards) * tp.chunks_per_shard;
+      const uint32_t grid = uint32_t(std::min<uint64_t>(items, uint64_t(ctx->sm_count) * 4));
+      topn_count_kernel<<<grid, kTopnThreads, kTopnSmem, ctx->stream>>>(tp);
       ctx->timing.launches++;
       CUDA_TRY(ctx, cudaGetLastError());
     }
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-    isect.resize(std::max<size_t>(n_counts, 1));
-    std::vector<uint32_t> dn(size_t(n_shards) * kRowContainers);
-    if (n_counts) CUDA_TRY(ctx, cudaMemcpyAsync(isect.data(), d_counts, n_counts * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_TRY(ctx, cudaMemcpyAsync(dn.data(), ctx->d_dense_n.p, dn.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t* h_counts = static_cast<uint32_t*>(ctx->h_out.p);
+    uint32_t* h_dn = h_counts + std::max<size_t>(n_counts, 1);
+    if (n_counts) CUDA_TRY(ctx, cudaMemcpyAsync(h_counts, d_counts, n_counts * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_dn, ctx->d_dense_n.p, size_t(n_shards) * kRowContainers * 4, cudaMemcpyDeviceToHost, ctx->stream));
     TRY(finish_call(ctx));
-    ctx->timing.d2h_bytes += n_counts * 4 + dn.size() * 4;
+    ctx->timing.d2h_bytes += n_counts * 4 + size_t(n_shards) * kRowContainers * 4;
     for (uint32_t s = 0; s < n_shards; s++)
-      for (int c = 0; c < kRowContainers; c++) src_counts[s] += dn[size_t(s) * kRowContainers + c];
+      for (int c = 0; c < kRowContainers; c++) src_counts[s] += h_dn[size_t(s) * kRowContainers + c];
+    isect = h_counts;
+    lap("device + copies");
   }
 
-  // per-shard selection walk
-  std::vector<uint32_t> tmp;
-  for (uint32_t s = 0; s < n_shards; s++) {
-    if (!frs[s]) continue;
-    const uint32_t* is = nullptr;
-    if (has_src) {
-      if (n_ids) {
-        // device counts are laid out in `ids` order; candidates were re-sorted by count
-        tmp.resize(cands[s].size());
-        std::unordered_map<uint64_t, uint32_t> pos;
-        for (size_t k = 0; k < n_ids; k++) pos.emplace(ids[k], uint32_t(k));
-        for (size_t k = 0; k < cands[s].size(); k++) tmp[k] = isect[size_t(s) * n_ids + pos[cands[s][k].id]];
+  // per-shard selection walk (host: sequential, data-dependent, a few thousand steps per shard)
+  parallel_shards(n_shards, [&](uint32_t s) {
+    if (!frs[s]) return;
+    const Fragment& f = *frs[s];
+    if (n_ids) {
+      std::vector<uint32_t> tmp;
+      const uint32_t* is = nullptr;
+      if (has_src) {  // device counts are laid out in `ids` order; candidates were re-sorted by count
+        tmp.resize(id_ids[s].size());
+        for (size_t k = 0; k < tmp.size(); k++) tmp[k] = isect[size_t(s) * n_ids + id_pos[s][k]];
         is = tmp.data();
-      } else {
-        is = isect.data() + off[s];
       }
+      per_shard[s] = top_walk(id_ids[s].data(), id_counts[s].data(), id_ids[s].size(), is, has_src, 0, min_threshold, tanimoto, src_counts[s]);
+    } else {
+      per_shard[s] = top_walk(f.rank_ids.data(), f.rank_counts.data(), f.rank_ids.size(), has_src ? isect + off[s] : nullptr, has_src,
+                              int(n), min_threshold, tanimoto, src_counts[s]);
     }
-    per_shard[s] = top_walk(cands[s], is, has_src, n_ids ? 0 : int(n), min_threshold, tanimoto, src_counts[s]);
-  }
+  });
+  lap("selection walk");
   return PB200_OK;
 }
 
 std::vector<HPair> merge_pairs(const std::vector<std::vector<HPair>>& per_shard) {  // Pairs.Add (cache.go:356-374) + sort
-  std::unordered_map<uint64_t, uint64_t> m;
-  for (auto& v : per_shard) for (auto& p : v) m[p.id] += p.count;
+  std::vector<HPair> all;
+  size_t total = 0;
+  for (auto& v : per_shard) total += v.size();
+  all.reserve(total);
+  for (auto& v : per_shard) all.insert(all.end(), v.begin(), v.end());
+  std::sort(all.begin(), all.end(), [](const HPair& x, const HPair& y) { return x.id < y.id; });
   std::vector<HPair> out;
-  out.reserve(m.size());
-  for (auto& kv : m) out.push_back({kv.first, kv.second});
-  std::sort(out.begin(), out.end(), [](const HPair& x, const HPair& y) { return x.id < y.id; });
+  for (size_t i = 0; i < all.size();) {  // sum the counts of equal ids
+    HPair acc = all[i++];
+    while (i < all.size() && all[i].id == acc.id) acc.count += all[i++].count;
+    out.push_back(acc);
+  }
   sort_pairs(out);
   return out;
 }
@@ -391,7 +449,9 @@ extern "C" int pb200_topn(pb200_ctx* ctx, pb200_family family, const pb200_node*
   std::vector<uint64_t> ids2;
   for (auto& p : pairs) ids2.push_back(p.id);
   std::sort(ids2.begin(), ids2.end());
-  TRY(topn_pass(ctx, family, src_prog, n_src_nodes, n, ids2.data(), ids2.size(), min_threshold, tanimoto_threshold, shards, n_shards, per));
+  TRY(topn_pass(ctx, family, src_prog, n_src_nodes, n, ids2.data(), ids2.size(), min_threshold, tanimoto_threshold, shards, n_shards, per,
+                /*reuse_src=*/true));
+  ctx->dense_shards_dev = nullptr;
   ctx->timing.kernel_ms += t1.kernel_ms; ctx->timing.algo_bytes += t1.algo_bytes; ctx->timing.launches += t1.launches;
   ctx->timing.h2d_bytes += t1.h2d_bytes; ctx->timing.d2h_bytes += t1.d2h_bytes;
   std::vector<HPair> trimmed = merge_pairs(per);

@@ -1,9 +1,16 @@
 // K7 — TopN: one source row x many candidate rows -> intersection counts.
 // Replaces the hot loop of fragment.top (fragment.go:1599-1689): Src.intersectionCount(f.row(id))
 // for every ranked row, i.e. roaring.intersectionCount (roaring.go:3078-3215) over 16
-// container pairs per row. One CTA owns (shard, container column): the source column is
-// staged once in shared memory as an 8 KiB bitmap, then each warp streams candidate
-// containers against it (array: bit probes; bitmap: AND+popc; run: masked range popcount).
+// container pairs per row.
+//
+// One CTA owns (shard, chunk of candidate rows) and stages the WHOLE 128 KiB source row
+// (16 container columns) in shared memory once. A half-warp then owns one candidate row:
+// lane c handles container c, so the 16 descriptors of a row (256 B) and — because the
+// loader stores a row's containers back to back — its payloads are read as contiguous
+// streams, and the 16 per-container counts are combined with shuffles into one plain
+// store (no atomics: a row belongs to exactly one half-warp). Small arrays / run lists
+// (the bulk of a Zipf-distributed field) are probed lane-serially; containers that are
+// large (bitmaps, long arrays, many runs) are handed to the whole warp afterwards.
 #pragma once
 #include "kernels.cuh"
 
@@ -14,19 +21,26 @@ struct TopnParams {
   uint32_t family;
   const uint64_t* shards;
   uint32_t n_shards;
-  const uint8_t* src_dense;      // dense source rows: (s * 16 + c) * 8192 (never null: no-src TopN needs no kernel)
-  // candidate rows: either per-shard rank lists (row indices into the fragment's row table)
+  const uint8_t* src_dense;            // dense source rows: (s * 16 + c) * 8192
+  const uint32_t* src_n;               // cardinality per (s, c) of the source (skip empty columns)
+  // candidate rows: per-shard rank tables (row indices into the fragment's row table) ...
   const uint32_t* const* rank_rowidx;  // [n_shards] device pointers (null when the shard has no fragment)
   const uint32_t* rank_n;              // [n_shards]
   const uint64_t* cand_off;            // [n_shards] offset of shard s in `counts`
   // ... or one explicit id list shared by all shards (pass 2, fragment.go:1573)
   const uint64_t* ids;
   uint32_t n_ids;
-  uint32_t* counts;                    // [sum rank_n] or [n_shards * n_ids]
+  uint32_t chunk;                      // candidates per CTA
+  uint32_t chunks_per_shard;
+  uint32_t* counts;                    // [sum rank_n] or [n_shards * n_ids]; every entry is written
   unsigned long long* algo_bytes;
 };
 
-constexpr int kTopnThreads = 256;
+constexpr int kTopnThreads = 1024;
+constexpr int kTopnSmallArray = 128; // arrays up to this many values are probed by a single lane
+constexpr int kTopnSmallRuns = 8;
+constexpr int kTopnIlp = 2;         // independent candidate rows per lane per iteration
+constexpr int kTopnSmem = kRowContainers * kBitmapBytes;  // 128 KiB source row
 
 __device__ __forceinline__ uint32_t popc_range_smem(const uint64_t* w, uint32_t s, uint32_t l) {  // inclusive [s, l]
   uint32_t ws = s >> 6, we = l >> 6;
@@ -37,93 +51,202 @@ __device__ __forceinline__ uint32_t popc_range_smem(const uint64_t* w, uint32_t 
   return n;
 }
 
-__global__ void __launch_bounds__(kTopnThreads) topn_count_kernel(TopnParams p) {
-  __shared__ __align__(16) uint64_t s_src[kBitmapWords];
-  __shared__ uint32_t s_any;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const uint32_t n_items = p.n_shards * kRowContainers;
+// Quarter-warp (8 lanes) intersection count of one large container against a staged source
+// column: 8 lanes x 16 B = one 128 B line per step, two steps in flight. Four containers are
+// processed concurrently per warp. `ql` is the lane index inside the quarter (0..7); the
+// result is valid in every lane of the quarter.
+__device__ __forceinline__ uint32_t topn_big_q(const ContainerDesc& d, const uint64_t* src, int ql, bool active) {
+  uint32_t cnt = 0;
+  if (active) {
+    const uint32_t type = desc_type(d), len = desc_len(d);
+    const uint32_t* src32 = reinterpret_cast<const uint32_t*>(src);
+    if (type == kArray) {  // intersectionCountArrayBitmap, roaring.go:3197 — 8 values per 128-bit load
+      const uint4* a4 = reinterpret_cast<const uint4*>(d.addr);
+      const uint32_t nvec = (len + 7) >> 3;  // the tail vector is padded by the loader; masked below
+      for (uint32_t i = ql; i < nvec; i += 16) {
+        const uint4 va = ldg128_stream(a4 + i);
+        const bool two = i + 8 < nvec;
+        const uint4 vb = two ? ldg128_stream(a4 + i + 8) : make_uint4(0, 0, 0, 0);
+        const uint32_t wa[4] = {va.x, va.y, va.z, va.w}, wb[4] = {vb.x, vb.y, vb.z, vb.w};
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+          const uint32_t x = wa[t] & 0xffff, y = wa[t] >> 16, x2 = wb[t] & 0xffff, y2 = wb[t] >> 16;
+          const uint32_t bx = (src32[x >> 5] >> (x & 31)) & 1u, by = (src32[y >> 5] >> (y & 31)) & 1u;
+          const uint32_t bx2 = (src32[x2 >> 5] >> (x2 & 31)) & 1u, by2 = (src32[y2 >> 5] >> (y2 & 31)) & 1u;
+          const uint32_t e = i * 8 + 2 * t, e2 = (i + 8) * 8 + 2 * t;
+          cnt += (e < len ? bx : 0u) + (e + 1 < len ? by : 0u);
+          cnt += (two && e2 < len ? bx2 : 0u) + (two && e2 + 1 < len ? by2 : 0u);
+        }
+      }
+    } else if (type == kBitmap) {  // intersectionCountBitmapBitmap, roaring.go:3212
+      const uint4* b = reinterpret_cast<const uint4*>(d.addr);
+      const uint4* m4 = reinterpret_cast<const uint4*>(src);
+#pragma unroll 4
+      for (int j = ql; j < kBitmapWords / 2; j += 8) cnt += popc128(and128(ldg128_stream(b + j), m4[j]));
+    } else {  // intersectionCountBitmapRun, roaring.go:3189 (bitmapCountRange per run)
+      const ushort2* r = reinterpret_cast<const ushort2*>(d.addr);
+      for (uint32_t i = ql; i < len; i += 8) { ushort2 iv = r[i]; cnt += popc_range_smem(src, iv.x, iv.y); }
+    }
+  }
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  return cnt;
+}
+
+__global__ void __launch_bounds__(kTopnThreads, 1) topn_count_kernel(TopnParams p) {
+  extern __shared__ __align__(16) uint64_t s_src[];  // [16][1024]
+  __shared__ uint32_t s_srcn[kRowContainers];
+  const int tid = threadIdx.x, lane = tid & 31, hw = tid >> 4, sub = tid & 15;  // hw: half-warp index in the CTA
+  const uint32_t n_items = p.n_shards * p.chunks_per_shard;
   unsigned long long bytes_acc = 0;
 
   for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
-    const uint32_t s = item >> 4, c = item & 15;
-    const FamilyDev fam = p.families[p.family];
-    const uint64_t shard = p.shards[s];
-    __syncthreads();
-    if (tid == 0) s_any = 0;
-    __syncthreads();
-    if (shard >= fam.cap) continue;
-    const FragDev f = fam.frags[shard];
-    if (f.nrows == 0) continue;
-    // stage the source column; skip everything when it is empty (intersect with nothing)
-    const uint4* src = reinterpret_cast<const uint4*>(p.src_dense + (uint64_t(s) * kRowContainers + c) * kBitmapBytes);
-    uint32_t any = 0;
-    for (int j = tid; j < kBitmapWords / 2; j += kTopnThreads) {
-      uint4 v = ldg128(src + j);
-      reinterpret_cast<uint4*>(s_src)[j] = v;
-      any |= v.x | v.y | v.z | v.w;
-    }
-    if (any) s_any = 1;
-    __syncthreads();
-    if (!s_any) continue;
-
+    const uint32_t s = item / p.chunks_per_shard, ch = item % p.chunks_per_shard;
     const bool by_rank = p.ids == nullptr;
     const uint32_t n_cand = by_rank ? p.rank_n[s] : p.n_ids;
-    const uint32_t* rowidx = by_rank ? p.rank_rowidx[s] : nullptr;
+    const uint32_t k0 = ch * p.chunk;
+    if (k0 >= n_cand) continue;
+    const uint32_t k1 = min(n_cand, k0 + p.chunk);
     uint32_t* out = p.counts + (by_rank ? p.cand_off[s] : uint64_t(s) * p.n_ids);
+    const FamilyDev fam = p.families[p.family];
+    const uint64_t shard = p.shards[s];
+    FragDev f{};
+    if (shard < fam.cap) f = fam.frags[shard];
 
-    for (uint32_t k = warp; k < n_cand; k += kTopnThreads / 32) {
-      uint64_t idx;
-      if (by_rank) { idx = rowidx[k]; if (idx == 0xffffffffull) continue; }
-      else {
-        const uint64_t id = p.ids[k];
-        if (f.dense) { if (id >= f.nrows) continue; idx = id; }
-        else {
-          uint32_t lo = 0, hi = f.nrows;
-          while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if (f.row_ids[mid] < id) lo = mid + 1; else hi = mid; }
-          if (lo >= f.nrows || f.row_ids[lo] != id) continue;
-          idx = lo;
-        }
-      }
-      const ContainerDesc d = f.rows[idx * kRowContainers + c];
-      if (d.n == 0) continue;
-      const uint32_t type = desc_type(d), len = desc_len(d);
-      uint32_t cnt = 0;
-      if (type == kArray) {  // intersectionCountArrayBitmap, roaring.go:3197
-        const uint16_t* a = reinterpret_cast<const uint16_t*>(d.addr);
-        // 8 values (16 B) per lane per step
-        const uint32_t nvec = len >> 3;
-        const uint4* a4 = reinterpret_cast<const uint4*>(a);
-        for (uint32_t i = lane; i < nvec; i += 32) {
-          uint4 v = ldg128_stream(a4 + i);
-          uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    __syncthreads();  // previous item done with the staged source
+    if (tid < kRowContainers) s_srcn[tid] = p.src_n[s * kRowContainers + tid];
+    __syncthreads();
+    uint32_t any = 0;
 #pragma unroll
-          for (int t = 0; t < 4; t++) {
-            uint32_t x = w[t] & 0xffff, y = w[t] >> 16;
-            cnt += uint32_t(s_src[x >> 6] >> (x & 63)) & 1u;
-            cnt += uint32_t(s_src[y >> 6] >> (y & 63)) & 1u;
+    for (int c = 0; c < kRowContainers; c++) any |= s_srcn[c];
+    if (f.nrows == 0 || any == 0) {  // nothing can intersect: zero this chunk's counts
+      for (uint32_t k = k0 + tid; k < k1; k += kTopnThreads) out[k] = 0;
+      continue;
+    }
+    // stage the non-empty source columns
+    for (int c = 0; c < kRowContainers; c++) {
+      if (s_srcn[c] == 0) continue;
+      const uint4* src = reinterpret_cast<const uint4*>(p.src_dense + (uint64_t(s) * kRowContainers + c) * kBitmapBytes);
+      for (int j = tid; j < kBitmapWords / 2; j += kTopnThreads) reinterpret_cast<uint4*>(s_src + c * kBitmapWords)[j] = ldg128(src + j);
+    }
+    if (tid < kRowContainers && s_srcn[tid]) bytes_acc += kBitmapBytes;
+    __syncthreads();
+
+    const uint32_t* rowidx = by_rank ? p.rank_rowidx[s] : nullptr;
+    const uint64_t* my_src = s_src + sub * kBitmapWords;
+    const uint32_t* my_src32 = reinterpret_cast<const uint32_t*>(my_src);
+    const bool col_live = s_srcn[sub] != 0;
+    // Every warp iteration covers 2 x kTopnIlp candidate rows: one per half-warp, kTopnIlp
+    // independent rows per lane so that the descriptor -> payload -> probe chains of
+    // different rows overlap (the probes are shared-memory-latency bound otherwise).
+    constexpr uint32_t kStride = kTopnThreads / 16;
+    for (uint32_t kb = k0 + (hw & ~1u); kb < k1; kb += kStride * kTopnIlp) {
+      ContainerDesc d[kTopnIlp];
+      uint32_t kk[kTopnIlp], cnt[kTopnIlp];
+      bool valid[kTopnIlp], small_arr[kTopnIlp], big[kTopnIlp];
+      uint4 v0[kTopnIlp];
+#pragma unroll
+      for (int u = 0; u < kTopnIlp; u++) {
+        kk[u] = kb + u * kStride + (hw & 1u);
+        valid[u] = kk[u] < k1;
+        uint64_t idx = ~0ull;
+        if (valid[u]) {
+          if (by_rank) { const uint32_t ri = rowidx[kk[u]]; if (ri != 0xffffffffu) idx = ri; }
+          else {
+            const uint64_t id = p.ids[kk[u]];
+            if (f.dense) { if (id < f.nrows) idx = id; }
+            else {
+              uint32_t lo = 0, hi = f.nrows;
+              while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if (f.row_ids[mid] < id) lo = mid + 1; else hi = mid; }
+              if (lo < f.nrows && f.row_ids[lo] == id) idx = lo;
+            }
           }
         }
-        for (uint32_t i = (nvec << 3) + lane; i < len; i += 32) { uint32_t x = a[i]; cnt += uint32_t(s_src[x >> 6] >> (x & 63)) & 1u; }
-      } else if (type == kBitmap) {  // intersectionCountBitmapBitmap, roaring.go:3212
-        const uint4* b = reinterpret_cast<const uint4*>(d.addr);
-#pragma unroll 4
-        for (int j = lane; j < kBitmapWords / 2; j += 32) {
-          uint4 v = ldg128_stream(b + j);
-          uint4 m = reinterpret_cast<const uint4*>(s_src)[j];
-          cnt += popc128(and128(v, m));
-        }
-      } else {  // intersectionCountBitmapRun, roaring.go:3189 (bitmapCountRange per run)
-        const ushort2* r = reinterpret_cast<const ushort2*>(d.addr);
-        for (uint32_t i = lane; i < len; i += 32) { ushort2 iv = r[i]; cnt += popc_range_smem(s_src, iv.x, iv.y); }
+        d[u].addr = 0; d[u].n = 0; d[u].meta = 0;
+        if (idx != ~0ull) d[u] = f.rows[idx * kRowContainers + sub];
+        if (!col_live) d[u].n = 0;  // empty source column: no intersection, no loads
       }
-      cnt = warp_sum(cnt);
-      if (lane == 0) {
-        if (cnt) atomicAdd(out + k, cnt);
-        bytes_acc += desc_algo_bytes(d);
+#pragma unroll
+      for (int u = 0; u < kTopnIlp; u++) {  // first 8 values of every small array: one 128-bit load each, all in flight
+        const uint32_t type = desc_type(d[u]), len = desc_len(d[u]);
+        small_arr[u] = d[u].n && type == kArray && len <= kTopnSmallArray;
+        big[u] = d[u].n && !small_arr[u] && !(type == kRun && len <= kTopnSmallRuns);
+        v0[u] = make_uint4(0, 0, 0, 0);
+        if (small_arr[u]) v0[u] = ldg128_stream(reinterpret_cast<const uint4*>(d[u].addr));
+        if (d[u].n) bytes_acc += desc_algo_bytes(d[u]);
+        cnt[u] = 0;
+      }
+#pragma unroll
+      for (int u = 0; u < kTopnIlp; u++) {
+        const uint32_t len = small_arr[u] ? desc_len(d[u]) : 0;
+        const uint32_t w[4] = {v0[u].x, v0[u].y, v0[u].z, v0[u].w};
+#pragma unroll
+        for (int t = 0; t < 4; t++) {  // unconditional 32-bit probes (any u16 is a valid index), masked afterwards
+          const uint32_t x = w[t] & 0xffff, y = w[t] >> 16;
+          const uint32_t bx = (my_src32[x >> 5] >> (x & 31)) & 1u, by = (my_src32[y >> 5] >> (y & 31)) & 1u;
+          cnt[u] += (2 * t < len ? bx : 0u) + (2 * t + 1 < len ? by : 0u);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kTopnIlp; u++) {
+        if (small_arr[u]) {
+          const uint32_t len = desc_len(d[u]);
+          const uint4* a4 = reinterpret_cast<const uint4*>(d[u].addr);
+          for (uint32_t i = 8; i < len; i += 8) {  // payloads are 16 B aligned and padded by the loader
+            const uint4 v = ldg128_stream(a4 + (i >> 3));
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+              const uint32_t x = w[t] & 0xffff, y = w[t] >> 16;
+              const uint32_t bx = (my_src32[x >> 5] >> (x & 31)) & 1u, by = (my_src32[y >> 5] >> (y & 31)) & 1u;
+              cnt[u] += (i + 2 * t < len ? bx : 0u) + (i + 2 * t + 1 < len ? by : 0u);
+            }
+          }
+        } else if (d[u].n && !big[u]) {  // short run list
+          const ushort2* r = reinterpret_cast<const ushort2*>(d[u].addr);
+          const uint32_t len = desc_len(d[u]);
+          for (uint32_t i = 0; i < len; i++) { ushort2 iv = r[i]; cnt[u] += popc_range_smem(my_src, iv.x, iv.y); }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kTopnIlp; u++) {
+        // large containers: four at a time, one per quarter-warp
+        uint32_t big_mask = __ballot_sync(0xffffffffu, big[u]);
+        while (big_mask) {
+          // the q-th lowest set bit of big_mask is served by quarter q
+          uint32_t m = big_mask;
+          int pick = -1;
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            const int b = m ? __ffs(m) - 1 : -1;
+            if (b >= 0) m &= m - 1;
+            if (q == (lane >> 3)) pick = b;
+          }
+          big_mask = m;
+          const int from = pick >= 0 ? pick : lane;
+          ContainerDesc bd;
+          bd.addr = __shfl_sync(0xffffffffu, d[u].addr, from);
+          bd.n = __shfl_sync(0xffffffffu, d[u].n, from);
+          bd.meta = __shfl_sync(0xffffffffu, d[u].meta, from);
+          const uint32_t c = topn_big_q(bd, s_src + (from & 15) * kBitmapWords, lane & 7, pick >= 0);
+          // route the quarter's result back to the lane that owns the container
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            const int owner = __shfl_sync(0xffffffffu, pick, q * 8);
+            const uint32_t val = __shfl_sync(0xffffffffu, c, q * 8);
+            if (owner == lane) cnt[u] = val;
+          }
+        }
+        // sum the 16 lanes of each half-warp
+        uint32_t cc = cnt[u];
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) cc += __shfl_xor_sync(0xffffffffu, cc, o);
+        if (valid[u] && sub == 0) out[kk[u]] = cc;
       }
     }
-    if (tid == 0) bytes_acc += kBitmapBytes;  // the source column
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) bytes_acc += __shfl_xor_sync(0xffffffffu, bytes_acc, o);
   if (lane == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
 }
 
