@@ -355,20 +355,31 @@ def main():
         # ---- leg 2: end to end through the C ABI with host buffers ----
         out_e2e = (C.c_uint64 * B)()
 
-        def step_e2e(i):
+        def begin(i):
             fl, off = batches[i]
-            eng.count_batch_begin(fl, off, B, shards_arr, len(shards))   # host programs -> pinned -> H2D, kernel
-            if world > 1:
-                t = torch.as_tensor(DevArray(eng.count_batch_device(), B), device="cuda")
-                dist.all_reduce(t, op=dist.ReduceOp.SUM)
-            eng.count_batch_end(out_e2e)                                   # D2H + wait
+            eng.count_batch_begin(fl, off, B, shards_arr, len(shards))   # host programs -> pinned -> H2D, kernels (async)
 
-        for i in range(args.warmup):
-            step_e2e(i)
+        def run_e2e(idx):
+            """Every step: programs host->device, kernel, counts device->host. On one GPU the host
+            prepares step i+1 while step i runs (two batches in flight); with N GPUs the NCCL
+            all-reduce of the device-resident counts sits between _begin and _end."""
+            if world == 1:
+                begin(idx[0])
+                for n in range(len(idx)):
+                    if n + 1 < len(idx):
+                        begin(idx[n + 1])
+                    eng.count_batch_end(out_e2e)                           # D2H on the copy stream + wait
+            else:
+                for i in idx:
+                    begin(i)
+                    t = torch.as_tensor(DevArray(eng.count_batch_device(), B), device="cuda")
+                    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+                    eng.count_batch_end(out_e2e)
+
+        run_e2e(list(range(args.warmup)))
         barrier()
         t0 = time.perf_counter()
-        for i in range(args.warmup, n_batches):
-            step_e2e(i)
+        run_e2e(list(range(args.warmup, n_batches)))
         torch.cuda.synchronize()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
         barrier()

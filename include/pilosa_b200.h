@@ -151,6 +151,14 @@ int pb200_frag_drop(pb200_ctx* ctx, pb200_family family, uint64_t shard);
 int pb200_rank_set(pb200_ctx* ctx, pb200_family family, uint64_t shard,
                    const uint64_t* row_ids, const uint64_t* counts, size_t n);
 
+/* Host-only validation of fragment-file bytes with the loader's own parser (snapshot + ops
+ * log replay), without a context or a GPU: the checks pb200_frag_load performs before it
+ * touches the device. Returns PB200_OK or PB200_ERR_FORMAT; the reference's counterpart is
+ * the error path of roaring.go:1562-1653 unmarshalPilosaRoaring. Optional outputs: number of
+ * non-empty containers and total cardinality; `err`/`err_cap` receive the message. */
+int pb200_host_check_roaring(const void* roaring_bytes, size_t len, uint64_t* n_containers,
+                             uint64_t* n_bits, char* err, size_t err_cap);
+
 /* Number of rows / containers / payload bytes resident for a fragment (diagnostics). */
 int pb200_frag_stat(pb200_ctx* ctx, pb200_family family, uint64_t shard,
                     uint64_t* n_rows, uint64_t* n_containers, uint64_t* payload_bytes);
@@ -174,11 +182,16 @@ int pb200_count_batch(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* p
 int pb200_count_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
                        const uint64_t* shards, uint32_t n_shards, uint64_t* out_per_shard);
 
-/* Split form of pb200_count_batch for hosts that merge across GPUs: _begin compiles,
- * uploads and launches asynchronously; between the two calls the per-query partial counts
- * are resident in HBM at *device_counts (uint64[n_queries]) where an NCCL all-reduce over
- * NVLink can sum them in place (the reduceFn of executor.go:1813 across devices); _end
- * copies them to the host and waits. One batch may be in flight per context. */
+/* Split form of pb200_count_batch: _begin compiles, uploads and launches asynchronously;
+ * _end copies the counts of the OLDEST batch in flight to the host (on a separate copy
+ * stream) and waits for them. Two uses:
+ *  - pipelining: up to two batches may be in flight per context, so a host calls
+ *    _begin(i+1) before _end(i) and its compile/upload work overlaps the kernels of batch i;
+ *  - merging across GPUs: with ONE batch in flight, the per-query partial counts are
+ *    resident in HBM at *device_counts (uint64[n_queries], the most recently begun batch)
+ *    where an NCCL all-reduce over NVLink, enqueued on the context's stream, sums them in
+ *    place (the reduceFn of executor.go:1813 across devices); _end then waits for that
+ *    work too. Do not issue another _begin between a collective and its _end. */
 int pb200_count_batch_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off,
                             uint32_t n_queries, const uint64_t* shards, uint32_t n_shards);
 int pb200_count_batch_device(pb200_ctx* ctx, void** device_counts);

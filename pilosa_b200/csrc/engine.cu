@@ -142,10 +142,20 @@ extern "C" int pb200_shutdown(pb200_ctx* ctx) {
       if (fam.d_frags) cudaFree(fam.d_frags);
     }
     if (ctx->d_families) cudaFree(ctx->d_families);
-    for (DevBuf* b : {&ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi})
+    for (DevBuf* b : {&ctx->d_slow_descs, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi})
       if (b->p) cudaFree(b->p);
-    for (PinBuf* b : {&ctx->h_stage, &ctx->h_out, &ctx->h_algo})
+    for (PinBuf* b : {&ctx->h_stage, &ctx->h_out, &ctx->h_algo, &ctx->h_topn})
       if (b->p) cudaFreeHost(b->p);
+    for (auto& sl : ctx->slots) {
+      if (sl.d_batch.p) cudaFree(sl.d_batch.p);
+      if (sl.d_out.p) cudaFree(sl.d_out.p);
+      if (sl.h_stage.p) cudaFreeHost(sl.h_stage.p);
+      if (sl.h_out.p) cudaFreeHost(sl.h_out.p);
+      if (sl.k0) cudaEventDestroy(sl.k0);
+      if (sl.k1) cudaEventDestroy(sl.k1);
+      if (sl.done) cudaEventDestroy(sl.done);
+    }
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -275,6 +285,23 @@ static int upload_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const st
   fam.h_frags[shard] = nf.dev;
   CUDA_TRY(ctx, cudaMemcpy(fam.d_frags + shard, &nf.dev, sizeof(FragDev), cudaMemcpyHostToDevice));
   fam.frags.emplace(shard, std::move(nf));
+  return PB200_OK;
+}
+
+extern "C" int pb200_host_check_roaring(const void* roaring_bytes, size_t len, uint64_t* n_containers, uint64_t* n_bits, char* err,
+                                        size_t err_cap) {
+  std::vector<HostContainer> cs;
+  std::string msg;
+  if (!roaring_bytes && len) return PB200_ERR_INVALID;
+  const bool ok = parse_fragment(static_cast<const uint8_t*>(roaring_bytes), len, cs, msg);
+  if (err && err_cap) { std::snprintf(err, err_cap, "%s", ok ? "" : msg.c_str()); }
+  if (!ok) return PB200_ERR_FORMAT;
+  FragImage img;
+  if (!build_image(cs, img, msg)) { if (err && err_cap) std::snprintf(err, err_cap, "%s", msg.c_str()); return PB200_ERR_FORMAT; }
+  uint64_t bits = 0;
+  for (auto& c : cs) bits += c.n;
+  if (n_containers) *n_containers = img.n_containers;
+  if (n_bits) *n_bits = bits;
   return PB200_OK;
 }
 
@@ -550,9 +577,23 @@ int upload_batch(pb200_ctx* ctx, const Compiled& cp, const uint64_t* shards, uin
   return PB200_OK;
 }
 
+// Persistent grids are sized to exactly the number of CTAs that can be resident (SMs x CTAs
+// per SM from the occupancy calculator): a grid larger than that runs a second, thinner wave.
+template <class K>
+uint32_t resident_ctas(pb200_ctx* ctx, int slot, K kernel, int block, size_t dyn_smem) {
+  if (ctx->occ[slot] == 0) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, block, dyn_smem) != cudaSuccess || n < 1) n = 1;
+    ctx->occ[slot] = n;
+  }
+  return uint32_t(ctx->sm_count) * uint32_t(ctx->occ[slot]);
+}
+enum { OCC_FAST = 0, OCC_STAGED, OCC_RANGE, OCC_SUM, OCC_MM, OCC_TOPN };
+
 // Launches the fast + staged kernels for `n_queries` programs starting at `progs`.
 int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards, bool staging,
-                unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, uint8_t* dense_out, uint32_t* dense_n) {
+                unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, uint8_t* dense_out, uint32_t* dense_n,
+                uint32_t max_leaves = kMaxLeaves) {
   const uint64_t n_items = uint64_t(n_queries) * n_shards * kRowContainers;
   if (n_items == 0) return PB200_OK;
   if (n_items >= (1ull << 32)) return fail(ctx, PB200_ERR_RANGE, "batch too large: queries x shards x 16 must be < 2^32");
@@ -570,14 +611,21 @@ int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t 
   p.dense_out = dense_out; p.dense_n = dense_n;
   p.slow_list = static_cast<uint32_t*>(ctx->d_slow.p);
   p.slow_count = static_cast<uint32_t*>(ctx->d_misc.p);
-  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 8);
+  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + ctx->algo_off);
+  // descriptors of deferred items travel from the fast to the staged kernel when they fit a modest scratch budget
+  const uint64_t desc_bytes = n_items * uint64_t(max_leaves) * sizeof(ContainerDesc);
+  if (staging && desc_bytes <= (256ull << 20)) {
+    TRY(ensure_dev(ctx, ctx->d_slow_descs, size_t(desc_bytes)));
+    p.slow_descs = static_cast<ContainerDesc*>(ctx->d_slow_descs.p);
+    p.slow_desc_stride = max_leaves;
+  }
   CUDA_TRY(ctx, cudaMemsetAsync(p.slow_count, 0, 4, ctx->stream));
   const uint64_t want = (n_items + kFastWarps - 1) / kFastWarps;
-  const uint32_t grid = uint32_t(std::min<uint64_t>(want, uint64_t(ctx->sm_count) * 8));
+  const uint32_t grid = uint32_t(std::min<uint64_t>(want, resident_ctas(ctx, OCC_FAST, eval_fast_kernel, kFastWarps * 32, 0)));
   eval_fast_kernel<<<grid, kFastWarps * 32, 0, ctx->stream>>>(p);
   ctx->timing.launches++;
   if (staging) {
-    const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, uint64_t(ctx->sm_count) * 6));
+    const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, resident_ctas(ctx, OCC_STAGED, eval_staged_kernel, kStagedThreads, 0)));
     eval_staged_kernel<<<sgrid, kStagedThreads, 0, ctx->stream>>>(p);
     ctx->timing.launches++;
   }
@@ -610,6 +658,13 @@ int finish_call(pb200_ctx* ctx) {
   return PB200_OK;
 }
 
+uint32_t max_leaves_of(const Compiled& cp) {
+  uint32_t m = 1;
+  for (auto& pg : cp.progs) m = std::max(m, pg.n_leaves);
+  for (auto& pt : cp.pre) m = std::max(m, pt.prog.n_leaves);
+  return m;
+}
+
 // Compiles a batch of post-order programs.
 int compile_batch(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries, Compiled& cp) {
   Compiler cc(ctx, cp);
@@ -622,46 +677,112 @@ int compile_batch(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_
 }
 
 // First half of a Count call: compile, upload, launch (asynchronous on the stream). The
-// counts stay in ctx->d_out until count_end fetches them.
+// counts stay in the slot's device buffer until count_end fetches them. Up to two batches
+// may be in flight: the host prepares batch i+1 while the kernels of batch i run.
 int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries, const uint64_t* shards,
                 uint32_t n_shards, bool per_shard) {
   TRY(validate_shards(ctx, shards, n_shards));
+  if (ctx->n_pending >= 2) return fail(ctx, PB200_ERR_INVALID, "two Count batches already in flight: call pb200_count_batch_end first");
+  const int si = (ctx->head + ctx->n_pending) & 1;
+  CountSlot& sl = ctx->slots[si];
+  if (!sl.k0) {
+    CUDA_TRY(ctx, cudaEventCreate(&sl.k0)); CUDA_TRY(ctx, cudaEventCreate(&sl.k1));
+    CUDA_TRY(ctx, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+  }
+  if (!ctx->copy_stream) CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
   const size_t n_out = per_shard ? size_t(n_queries) * n_shards : n_queries;
-  ctx->pending_n_out = n_out;
-  ctx->pending_launched = false;
-  TRY(ensure_dev(ctx, ctx->d_out, std::max<size_t>(n_out, 1) * 8));
-  TRY(ensure_pin(ctx, ctx->h_out, std::max<size_t>(n_out, 1) * 8));
+  sl.n_out = n_out;
+  sl.launched = false;
+  sl.seq = ++ctx->begin_seq;
+  std::swap(ctx->d_out, sl.d_out);  // ensure_* work on the context's named buffers
+  int rc = ensure_dev(ctx, ctx->d_out, std::max<size_t>(n_out, 1) * 8);
+  std::swap(ctx->d_out, sl.d_out);
+  TRY(rc);
+  std::swap(ctx->h_out, sl.h_out);
+  rc = ensure_pin(ctx, ctx->h_out, std::max<size_t>(n_out, 1) * 8 + 8);
+  std::swap(ctx->h_out, sl.h_out);
+  TRY(rc);
   TRY(ensure_dev(ctx, ctx->d_misc, 64));
-  timing_begin(ctx);
-  if (n_queries == 0) return PB200_OK;
-  if (n_shards == 0) { CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_out.p, 0, n_out * 8, ctx->stream)); ctx->pending_launched = true; CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream)); CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream)); return PB200_OK; }
-  Compiled cp;
-  TRY(compile_batch(ctx, progs, prog_off, n_queries, cp));
-  TRY(sync_families(ctx));
-  BatchDev bd{};
-  TRY(upload_batch(ctx, cp, shards, n_shards, bd));
-  if (cp.n_temp_slots) TRY(ensure_dev(ctx, ctx->d_temp, size_t(cp.n_temp_slots) * n_shards * kRowContainers * kBitmapBytes));
-  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-  CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_out.p, 0, n_out * 8, ctx->stream));
-  TRY(run_pretasks(ctx, cp, bd, n_shards));
-  TRY(launch_eval(ctx, bd, bd.progs, n_queries, n_shards, cp.may_need_staging, static_cast<unsigned long long*>(ctx->d_out.p),
-                  per_shard ? n_shards : 1, per_shard ? 1 : 0, nullptr, nullptr));
-  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-  ctx->pending_launched = true;
+  ctx->timing = pb200_timing{};
+  ctx->algo_off = 16 + 8 * size_t(si);
+  CUDA_TRY(ctx, cudaMemsetAsync(static_cast<uint8_t*>(ctx->d_misc.p) + ctx->algo_off, 0, 8, ctx->stream));
+  ctx->n_pending++;
+  unsigned long long* d_out = static_cast<unsigned long long*>(sl.d_out.p);
+  CUDA_TRY(ctx, cudaEventRecord(sl.k0, ctx->stream));
+  if (n_queries != 0 && n_shards == 0) CUDA_TRY(ctx, cudaMemsetAsync(d_out, 0, n_out * 8, ctx->stream));
+  if (n_queries != 0 && n_shards != 0) {
+    Compiled cp;
+    rc = compile_batch(ctx, progs, prog_off, n_queries, cp);
+    if (rc != PB200_OK) { ctx->n_pending--; return rc; }
+    // Count(Row(v <op> x)) with nothing around it: let the comparator kernel count, skip the dense row
+    for (uint32_t q = 0; q < n_queries; q++) {
+      const Prog& pg = cp.progs[q];
+      if (pg.n_instr != 1) continue;
+      Leaf& lf = cp.leaves[pg.leaf_off + cp.instrs[pg.instr_off].leaf];
+      if (lf.kind != L_TEMP) continue;
+      for (auto& pt : cp.pre)
+        if (pt.kind == 0 && pt.slot == lf.family) {
+          pt.count_only = true;
+          pt.count_out = d_out + (per_shard ? size_t(q) * n_shards : q);
+          pt.count_sstride = per_shard ? 1 : 0;
+          lf.kind = L_ZERO;  // the evaluator adds nothing for this query
+          break;
+        }
+    }
+    rc = sync_families(ctx);
+    BatchDev bd{};
+    if (rc == PB200_OK) {
+      std::swap(ctx->d_batch, sl.d_batch); std::swap(ctx->h_stage, sl.h_stage);  // this slot's own upload buffers
+      rc = upload_batch(ctx, cp, shards, n_shards, bd);
+      std::swap(ctx->d_batch, sl.d_batch); std::swap(ctx->h_stage, sl.h_stage);
+    }
+    bool need_temp = false;
+    for (auto& pt : cp.pre) need_temp |= !(pt.kind == 0 && pt.count_only);
+    if (rc == PB200_OK && need_temp) rc = ensure_dev(ctx, ctx->d_temp, size_t(cp.n_temp_slots) * n_shards * kRowContainers * kBitmapBytes);
+    if (rc == PB200_OK && cudaMemsetAsync(d_out, 0, n_out * 8, ctx->stream) != cudaSuccess) rc = fail(ctx, PB200_ERR_CUDA, "cudaMemsetAsync(counts) failed");
+    if (rc == PB200_OK) rc = run_pretasks(ctx, cp, bd, n_shards);
+    if (rc == PB200_OK)
+      rc = launch_eval(ctx, bd, bd.progs, n_queries, n_shards, cp.may_need_staging, d_out, per_shard ? n_shards : 1, per_shard ? 1 : 0,
+                       nullptr, nullptr, max_leaves_of(cp));
+    if (rc != PB200_OK) { ctx->n_pending--; ctx->algo_off = 8; return rc; }
+  }
+  ctx->algo_off = 8;
+  CUDA_TRY(ctx, cudaEventRecord(sl.k1, ctx->stream));
+  CUDA_TRY(ctx, cudaEventRecord(sl.done, ctx->stream));
+  sl.launched = true;
   return PB200_OK;
 }
 
-// Second half: device -> host copy of the counts and the single stream wait.
+// Device pointer of the counts of the most recently begun batch (for in-place collectives).
+void* count_device_ptr(pb200_ctx* ctx) {
+  if (ctx->n_pending == 0) return nullptr;
+  return ctx->slots[(ctx->head + ctx->n_pending - 1) & 1].d_out.p;
+}
+
+// Second half, oldest batch first: device -> host copy of the counts on the copy stream, so
+// that a younger batch already queued on the compute stream keeps the GPU busy meanwhile.
 int count_end(pb200_ctx* ctx, uint64_t* out) {
-  const size_t n_out = ctx->pending_n_out;
-  if (n_out == 0) return PB200_OK;
-  if (!out) return PB200_ERR_INVALID;
-  if (!ctx->pending_launched) return fail(ctx, PB200_ERR_INVALID, "no Count batch in flight");
-  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_out.p, ctx->d_out.p, n_out * 8, cudaMemcpyDeviceToHost, ctx->stream));
-  TRY(finish_call(ctx));
-  std::memcpy(out, ctx->h_out.p, n_out * 8);
-  ctx->timing.d2h_bytes += n_out * 8;
-  ctx->pending_launched = false;
+  if (ctx->n_pending == 0) return fail(ctx, PB200_ERR_INVALID, "no Count batch in flight");
+  CountSlot& sl = ctx->slots[ctx->head];
+  const size_t n_out = sl.n_out;
+  if (n_out && !out) return PB200_ERR_INVALID;
+  // Nothing younger queued: re-record `done` now so that work the host enqueued on the compute
+  // stream after _begin (an NCCL all-reduce of the device-resident counts) is waited for too.
+  if (ctx->n_pending == 1) CUDA_TRY(ctx, cudaEventRecord(sl.done, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copy_stream, sl.done, 0));
+  uint8_t* h = static_cast<uint8_t*>(sl.h_out.p);
+  if (n_out) CUDA_TRY(ctx, cudaMemcpyAsync(h, sl.d_out.p, n_out * 8, cudaMemcpyDeviceToHost, ctx->copy_stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(h + std::max<size_t>(n_out, 1) * 8, static_cast<uint8_t*>(ctx->d_misc.p) + 16 + 8 * size_t(ctx->head), 8,
+                                cudaMemcpyDeviceToHost, ctx->copy_stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->copy_stream));
+  float ms = 0;
+  if (cudaEventElapsedTime(&ms, sl.k0, sl.k1) == cudaSuccess) ctx->timing.kernel_ms = ms;
+  std::memcpy(&ctx->timing.algo_bytes, h + std::max<size_t>(n_out, 1) * 8, 8);
+  if (n_out) std::memcpy(out, h, n_out * 8);
+  ctx->timing.d2h_bytes = n_out * 8 + 8;
+  sl.launched = false;
+  ctx->head ^= 1;
+  ctx->n_pending--;
   return PB200_OK;
 }
 
@@ -707,8 +828,8 @@ extern "C" int pb200_count_batch_begin(pb200_ctx* ctx, const pb200_node* progs, 
 extern "C" int pb200_count_batch_device(pb200_ctx* ctx, void** device_counts) {
   ENTER(ctx);
   if (!device_counts) return PB200_ERR_INVALID;
-  *device_counts = ctx->d_out.p;
-  return PB200_OK;
+  *device_counts = count_device_ptr(ctx);
+  return *device_counts ? PB200_OK : fail(ctx, PB200_ERR_INVALID, "no Count batch in flight");
 }
 
 extern "C" int pb200_count_batch_end(pb200_ctx* ctx, uint64_t* out_counts) {
@@ -757,7 +878,7 @@ extern "C" int pb200_batch_launch(pb200_ctx* ctx, pb200_batch* b) {
   ctx->timing.launches = 0;
   CUDA_TRY(ctx, cudaMemsetAsync(b->d_counts.p, 0, size_t(b->n_queries) * 8, ctx->stream));
   return launch_eval(ctx, b->bd, b->bd.progs, b->n_queries, b->n_shards, b->cp.may_need_staging,
-                     static_cast<unsigned long long*>(b->d_counts.p), 1, 0, nullptr, nullptr);
+                     static_cast<unsigned long long*>(b->d_counts.p), 1, 0, nullptr, nullptr, max_leaves_of(b->cp));
 }
 
 extern "C" int pb200_batch_device_counts(pb200_ctx* ctx, pb200_batch* b, void** device_counts) {

@@ -57,10 +57,24 @@ struct Compiled {
     pb200_node node{};    // kind 0
     uint32_t slot = 0, src_slot = 0;
     Prog prog{};          // kind 2: sub-program (offsets into instrs / leaves)
+    bool count_only = false;              // kind 0 feeding a bare Count(): count in the comparator kernel
+    unsigned long long* count_out = nullptr;
+    uint32_t count_sstride = 0;
   };
   std::vector<PreTask> pre;
   uint32_t n_temp_slots = 0;
   bool may_need_staging = false;  // some leaf family holds array/run containers (or temps)
+};
+
+// One Count batch in flight (pb200_count_batch_begin .. _end). Two slots let a host compile and
+// upload batch i+1 while the kernels of batch i run; results leave on a separate copy stream.
+struct CountSlot {
+  DevBuf d_batch, d_out;
+  PinBuf h_stage, h_out;
+  cudaEvent_t k0 = nullptr, k1 = nullptr, done = nullptr;
+  size_t n_out = 0;
+  bool launched = false;
+  uint64_t seq = 0;  // begin order
 };
 
 }  // namespace pb200
@@ -77,11 +91,16 @@ struct pb200_ctx {
   pb200::FamilyDev* d_families = nullptr;
   uint32_t d_families_cap = 0;
   bool families_dirty = true;
+  pb200::DevBuf d_slow_descs;
   pb200::DevBuf d_batch, d_out, d_slow, d_temp, d_dense, d_dense_n, d_misc, d_topn, d_bsi;
-  pb200::PinBuf h_stage, h_out, h_algo;
+  pb200::PinBuf h_stage, h_out, h_algo, h_topn;
   bool mm_attr_set = false, topn_attr_set = false;
+  int occ[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // resident CTAs per SM of each persistent kernel (occupancy calculator)
   const uint64_t* dense_shards_dev = nullptr;  // shard list of the source rows currently in d_dense (TopN pass 1 -> 2)
-  size_t pending_n_out = 0;      // split Count batch in flight (count_begin / count_end)
-  bool pending_launched = false;
+  pb200::CountSlot slots[2];     // split Count batches in flight (count_begin / count_end), oldest first
+  int n_pending = 0, head = 0;   // ring of pending slots
+  uint64_t begin_seq = 0;
+  cudaStream_t copy_stream = nullptr;
+  size_t algo_off = 8;           // byte offset in d_misc of the algorithmic-bytes counter the next kernels add to
   pb200_timing timing{};
 };

@@ -6,16 +6,18 @@ uint8_t* temp_slot(pb200_ctx* ctx, uint32_t slot, uint32_t n_shards) {
   return static_cast<uint8_t*>(ctx->d_temp.p) + size_t(slot) * n_shards * kRowContainers * kBitmapBytes;
 }
 
-int launch_bsi_range(pb200_ctx* ctx, const BatchDev& bd, const pb200_node& nd, uint32_t n_shards, uint8_t* dense_out) {
+int launch_bsi_range(pb200_ctx* ctx, const BatchDev& bd, const pb200_node& nd, uint32_t n_shards, uint8_t* dense_out,
+                     unsigned long long* count_out = nullptr, uint32_t count_sstride = 0) {
   BsiParams p{};
+  p.count_out = count_out; p.count_sstride = count_sstride;
   p.families = ctx->d_families; p.family = nd.family; p.bit_depth = nd.bit_depth;
   p.shards = bd.shards; p.n_shards = n_shards;
   p.bsi_op = nd.bsi_op; p.a = nd.a; p.b = nd.b;
   p.dense_out = dense_out;
-  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 8);
+  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + ctx->algo_off);
   const uint32_t items = n_shards * kRowContainers;
-  const uint32_t grid = std::min<uint32_t>(items, uint32_t(ctx->sm_count) * 8);
-  bsi_range_kernel<<<grid, kBsiThreads, 0, ctx->stream>>>(p);
+  const uint32_t grid = std::min<uint32_t>(items, resident_ctas(ctx, OCC_RANGE, bsi_range_kernel, kBsiThreads, kRingBytes));
+  bsi_range_kernel<<<grid, kBsiThreads, kRingBytes, ctx->stream>>>(p);
   ctx->timing.launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   return PB200_OK;
@@ -25,7 +27,10 @@ int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_
   for (size_t i = 0; i < cp.pre.size(); i++) {
     const auto& pt = cp.pre[i];
     if (pt.kind == 0) {
-      TRY(launch_bsi_range(ctx, bd, pt.node, n_shards, temp_slot(ctx, pt.slot, n_shards)));
+      if (pt.count_only)  // Count(Row(v <op> x)): popcount in the comparator kernel, nothing materialised
+        TRY(launch_bsi_range(ctx, bd, pt.node, n_shards, nullptr, pt.count_out, pt.count_sstride));
+      else
+        TRY(launch_bsi_range(ctx, bd, pt.node, n_shards, temp_slot(ctx, pt.slot, n_shards)));
     } else if (pt.kind == 2) {
       TRY(launch_eval(ctx, bd, bd.progs + cp.progs.size() + i, 1, n_shards, true, nullptr, 0, 0, temp_slot(ctx, pt.slot, n_shards), nullptr));
     } else {
@@ -319,10 +324,10 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
     size_t o_ids = o_ptr + size_t(n_shards) * 8;
     size_t total_bytes = o_ids + n_ids * 8;
     TRY(ensure_dev(ctx, ctx->d_topn, total_bytes));
-    TRY(ensure_pin(ctx, ctx->h_stage, total_bytes));
+    TRY(ensure_pin(ctx, ctx->h_topn, total_bytes));  // not h_stage: the program upload issued above may still be reading it
     TRY(ensure_dev(ctx, ctx->d_bsi, std::max<size_t>(n_counts, 1) * 4));
     TRY(ensure_pin(ctx, ctx->h_out, std::max<size_t>(n_counts, 1) * 4 + size_t(n_shards) * kRowContainers * 4));
-    uint8_t* h = static_cast<uint8_t*>(ctx->h_stage.p);
+    uint8_t* h = static_cast<uint8_t*>(ctx->h_topn.p);
     uint8_t* d = static_cast<uint8_t*>(ctx->d_topn.p);
     std::memcpy(h + o_off, off.data(), size_t(n_shards) * 8);
     auto* hn = reinterpret_cast<uint32_t*>(h + o_n);
@@ -357,7 +362,7 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
         ctx->topn_attr_set = true;
       }
       const uint64_t items = uint64_t(n_shards) * tp.chunks_per_shard;
-      const uint32_t grid = uint32_t(std::min<uint64_t>(items, uint64_t(ctx->sm_count) * 4));
+      const uint32_t grid = uint32_t(std::min<uint64_t>(items, resident_ctas(ctx, OCC_TOPN, topn_count_kernel, kTopnThreads, kTopnSmem)));
       topn_count_kernel<<<grid, kTopnThreads, kTopnSmem, ctx->stream>>>(tp);
       ctx->timing.launches++;
       CUDA_TRY(ctx, cudaGetLastError());
@@ -518,7 +523,7 @@ int bsi_minmax_impl(pb200_ctx* ctx, pb200_family fam, uint32_t bit_depth, const 
   p.mm_count = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_bsi.p) + size_t(n_shards) * 8);
   const int smem = kRowContainers * kBitmapBytes;
   if (!ctx->mm_attr_set) { CUDA_TRY(ctx, cudaFuncSetAttribute(bsi_minmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); ctx->mm_attr_set = true; }
-  const uint32_t grid = std::min<uint32_t>(n_shards, uint32_t(ctx->sm_count) * 4);
+  const uint32_t grid = std::min<uint32_t>(n_shards, resident_ctas(ctx, OCC_MM, bsi_minmax_kernel, kMmThreads, smem));
   bsi_minmax_kernel<<<grid, kMmThreads, smem, ctx->stream>>>(p);
   ctx->timing.launches++;
   CUDA_TRY(ctx, cudaGetLastError());
@@ -565,8 +570,8 @@ extern "C" int pb200_bsi_sum(pb200_ctx* ctx, pb200_family bsi_family, uint32_t b
   p.strict = (flags & PB200_SUM_STRICT) ? 1 : 0;
   p.sum_acc = static_cast<unsigned long long*>(ctx->d_bsi.p);
   const uint32_t items = n_shards * kRowContainers;
-  const uint32_t grid = std::min<uint32_t>(items, uint32_t(ctx->sm_count) * 6);
-  bsi_sum_kernel<<<grid, kBsiThreads, 0, ctx->stream>>>(p);
+  const uint32_t grid = std::min<uint32_t>(items, resident_ctas(ctx, OCC_SUM, bsi_sum_kernel, kBsiThreads, kRingBytes));
+  bsi_sum_kernel<<<grid, kBsiThreads, kRingBytes, ctx->stream>>>(p);
   ctx->timing.launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));

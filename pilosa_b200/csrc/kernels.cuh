@@ -32,6 +32,8 @@ struct EvalParams {
   uint32_t* dense_n;               // optional: cardinality per (q, s, c)
   uint32_t* slow_list;             // scratch: items the fast kernel defers to the staged kernel
   uint32_t* slow_count;
+  ContainerDesc* slow_descs;       // scratch (optional): resolved descriptors of deferred items, [slot][slow_desc_stride]
+  uint32_t slow_desc_stride;
   unsigned long long* algo_bytes;  // accumulated algorithmic bytes (payload + 16 B / container)
 };
 
@@ -113,9 +115,92 @@ __device__ __forceinline__ uint4 apply_op(uint8_t op, const uint4& acc, const ui
 }
 
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
+  // (REDUX.SUM via __reduce_add_sync was measured: no gain for Sum, 10 % slower Min/Max)
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
+}
+
+// ---------------------------------------------------------------------------------------
+// K2-K5 (count form), warp-level: |a AND b| when the smaller operand is a short array or a
+// short run list. Lanes take the elements (runs) of the small side and test them against
+// the other container where it lies: bitmap -> one word probe (intersectionCountArrayBitmap
+// roaring.go:3197 / BitmapRun :3189), array -> binary search (ArrayArray :3115, ArrayRun
+// :3138), runs -> binary search + interval overlap (RunRun :3156). Returns kNotSparse when
+// the pair should be staged instead. The result is uniform across the warp.
+// ---------------------------------------------------------------------------------------
+constexpr uint32_t kNotSparse = 0xffffffffu;
+constexpr uint32_t kSparseArrayMax = 1024;  // elements of the probing side
+constexpr uint32_t kSparseRunMax = 256;     // runs of the probing side
+
+__device__ __forceinline__ bool in_bitmap(uint64_t addr, uint32_t v) {
+  return (__ldg(reinterpret_cast<const unsigned long long*>(addr) + (v >> 6)) >> (v & 63)) & 1ull;
+}
+__device__ __forceinline__ bool in_array(uint64_t addr, uint32_t len, uint32_t v) {
+  const uint16_t* a = reinterpret_cast<const uint16_t*>(addr);
+  uint32_t lo = 0, hi = len;
+  while (lo < hi) { const uint32_t m = (lo + hi) >> 1; if (__ldg(a + m) < v) lo = m + 1; else hi = m; }
+  return lo < len && __ldg(a + lo) == v;
+}
+// index of the first run whose last >= v (len if none)
+__device__ __forceinline__ uint32_t run_lower(const ushort2* r, uint32_t len, uint32_t v) {
+  uint32_t lo = 0, hi = len;
+  while (lo < hi) { const uint32_t m = (lo + hi) >> 1; if (__ldg(r + m).y < v) lo = m + 1; else hi = m; }
+  return lo;
+}
+__device__ __forceinline__ uint32_t popc_range_global(uint64_t addr, uint32_t s, uint32_t l) {  // inclusive [s, l]
+  const unsigned long long* w = reinterpret_cast<const unsigned long long*>(addr);
+  const uint32_t ws = s >> 6, we = l >> 6;
+  const unsigned long long ms = ~0ull << (s & 63), me = ~0ull >> (63 - (l & 63));
+  if (ws == we) return __popcll(__ldg(w + ws) & ms & me);
+  uint32_t n = __popcll(__ldg(w + ws) & ms) + __popcll(__ldg(w + we) & me);
+  for (uint32_t k = ws + 1; k < we; k++) n += __popcll(__ldg(w + k));
+  return n;
+}
+
+__device__ __noinline__ uint32_t sparse_pair_icount(ContainerDesc a, ContainerDesc b, int lane) {
+  if (a.n == 0 || b.n == 0) return 0;
+  if (a.n == kFullN) return b.n;  // roaring.go:3079-3084
+  if (b.n == kFullN) return a.n;
+  uint32_t ta = desc_type(a), tb = desc_type(b);
+  // make `a` the probing (small) side: prefer an array, then a run list; the smaller one on ties
+  const bool a_probe = ta != kBitmap, b_probe = tb != kBitmap;
+  if (!a_probe && !b_probe) return kNotSparse;
+  if (!a_probe || (b_probe && ((tb == kArray && ta != kArray) || (tb == ta && desc_len(b) < desc_len(a))))) {
+    const ContainerDesc t = a; a = b; b = t;
+    ta = desc_type(a); tb = desc_type(b);
+  }
+  const uint32_t la = desc_len(a), lb = desc_len(b);
+  uint32_t cnt = 0;
+  if (ta == kArray) {
+    if (la > kSparseArrayMax) return kNotSparse;
+    const uint16_t* arr = reinterpret_cast<const uint16_t*>(a.addr);
+    for (uint32_t i = lane; i < la; i += 32) {
+      const uint32_t v = __ldg(arr + i);
+      bool hit;
+      if (tb == kBitmap) hit = in_bitmap(b.addr, v);
+      else if (tb == kArray) hit = in_array(b.addr, lb, v);
+      else { const ushort2* r = reinterpret_cast<const ushort2*>(b.addr); const uint32_t j = run_lower(r, lb, v); hit = j < lb && __ldg(r + j).x <= v; }
+      cnt += hit ? 1u : 0u;
+    }
+  } else {  // a is a run list
+    if (la > kSparseRunMax) return kNotSparse;
+    if (tb == kBitmap && a.n > 16384) return kNotSparse;  // long runs over a bitmap: streaming beats probing
+    const ushort2* ra = reinterpret_cast<const ushort2*>(a.addr);
+    for (uint32_t i = lane; i < la; i += 32) {
+      const ushort2 iv = __ldg(ra + i);
+      if (tb == kBitmap) cnt += popc_range_global(b.addr, iv.x, iv.y);
+      else {  // run x run: overlaps with every run of b that reaches into [start, last]
+        const ushort2* rb = reinterpret_cast<const ushort2*>(b.addr);
+        for (uint32_t j = run_lower(rb, lb, iv.x); j < lb; j++) {
+          const ushort2 o = __ldg(rb + j);
+          if (o.x > iv.y) break;
+          cnt += min(uint32_t(iv.y), uint32_t(o.y)) - max(uint32_t(iv.x), uint32_t(o.x)) + 1;
+        }
+      }
+    }
+  }
+  return warp_sum(cnt);
 }
 
 constexpr int kFastWarps = 8;  // warps per CTA in the fast kernel
@@ -158,14 +243,48 @@ __global__ void __launch_bounds__(kFastWarps * 32) eval_fast_kernel(EvalParams p
     if (lane == 0) bytes_acc += bytes;
     __syncwarp();
 
+    const bool want_dense = p.dense_out != nullptr;
     if (!all_ok) {
-      if (lane == 0) p.slow_list[atomicAdd(p.slow_count, 1u)] = uint32_t(item);
+      // K2-K5 in-warp: a two-operand count whose smaller side is a short array / run list needs
+      // no staging — membership probes (or interval overlaps) plus the cardinalities give
+      // |a AND b|, and |a OR b|, |a XOR b|, |a ANDNOT b| follow from it.
+      bool done = false;
+      if (!want_dense && pg.n_instr == 2 && ins[0].op == I_LOAD && ins[1].op >= I_AND_LEAF && ins[1].op <= I_ANDNOT_LEAF &&
+          p.leaves[pg.leaf_off + ins[0].leaf].kind != L_TEMP && p.leaves[pg.leaf_off + ins[1].leaf].kind != L_TEMP) {
+        const ContainerDesc a = s_desc[warp][ins[0].leaf], b = s_desc[warp][ins[1].leaf];
+        const uint32_t ic = sparse_pair_icount(a, b, lane);
+        if (ic != kNotSparse) {
+          uint32_t r;
+          switch (ins[1].op) {
+            case I_AND_LEAF: r = ic; break;
+            case I_OR_LEAF: r = a.n + b.n - ic; break;
+            case I_XOR_LEAF: r = a.n + b.n - 2 * ic; break;
+            default: r = a.n - ic; break;  // I_ANDNOT_LEAF
+          }
+          if (lane == 0 && p.out_counts && r) atomicAdd(p.out_counts + uint64_t(q) * p.out_qstride + uint64_t(s) * p.out_sstride, (unsigned long long)r);
+          done = true;
+        }
+      } else if (!want_dense && pg.n_instr == 1 && p.leaves[pg.leaf_off + ins[0].leaf].kind != L_TEMP) {
+        // Count(Row) of an array / run container: the cardinality is in the descriptor
+        const ContainerDesc d = s_desc[warp][ins[0].leaf];
+        if (lane == 0 && p.out_counts && d.n) atomicAdd(p.out_counts + uint64_t(q) * p.out_qstride + uint64_t(s) * p.out_sstride, (unsigned long long)d.n);
+        done = true;
+      }
+      if (!done) {
+        // defer to the staged kernel; hand it the descriptors already resolved here so it does
+        // not repeat the shard -> fragment -> row-table pointer chase
+        uint32_t slot = 0;
+        if (lane == 0) { slot = atomicAdd(p.slow_count, 1u); p.slow_list[slot] = uint32_t(item); }
+        if (p.slow_descs) {
+          slot = __shfl_sync(0xffffffffu, slot, 0);
+          if (lane < pg.n_leaves) p.slow_descs[uint64_t(slot) * p.slow_desc_stride + lane] = s_desc[warp][lane];
+        }
+      }
       __syncwarp();
       continue;
     }
 
     uint32_t cnt = 0;
-    const bool want_dense = p.dense_out != nullptr;
     uint8_t* dout = want_dense ? p.dense_out + item * kBitmapBytes : nullptr;
 
     if (!want_dense && pg.n_instr == 1) {
@@ -280,11 +399,32 @@ __device__ __forceinline__ void stage_container(const ContainerDesc& d, uint32_t
       while (l < h) { uint32_t m = (l + h) >> 1; if (a[m] < lo) l = m + 1; else h = m; }
       b = l;
     }
-    for (uint32_t i = b + tid; i < e; i += nthreads) {
-      uint32_t v = a[i];
-      if (v >= hi) break;
-      v -= lo;
-      atomicOr(&win32[v >> 5], 1u << (v & 31));
+    if (hi < 65536u) {  // lower_bound(hi)
+      uint32_t l = b, h = len;
+      while (l < h) { uint32_t m = (l + h) >> 1; if (a[m] < hi) l = m + 1; else h = m; }
+      e = l;
+    }
+    // Each thread takes a contiguous segment of the sorted array and assembles whole 32-bit
+    // words in a register: words strictly inside its segment are owned by this thread alone
+    // (plain stores); only the first and last word can be shared with a neighbouring
+    // thread (shared-memory atomics cost ~2 cycles per lane, so they are kept to two).
+    const uint32_t n = e - b;
+    const uint32_t per = (n + nthreads - 1) / nthreads;
+    const uint32_t i0 = b + tid * per, i1 = min(e, i0 + per);
+    if (per && i0 < i1) {
+      uint32_t cur_w = (uint32_t(a[i0]) - lo) >> 5, cur_bits = 0;
+      bool first = true;
+#pragma unroll 4
+      for (uint32_t i = i0; i < i1; i++) {
+        const uint32_t v = uint32_t(__ldg(a + i)) - lo, w = v >> 5;
+        if (w != cur_w) {
+          if (first) { atomicOr(&win32[cur_w], cur_bits); first = false; }
+          else win32[cur_w] = cur_bits;
+          cur_w = w; cur_bits = 0;
+        }
+        cur_bits |= 1u << (v & 31);
+      }
+      atomicOr(&win32[cur_w], cur_bits);
     }
   } else if (type == kRun) {
     const ushort2* r = reinterpret_cast<const ushort2*>(d.addr);
@@ -294,21 +434,48 @@ __device__ __forceinline__ void stage_container(const ContainerDesc& d, uint32_t
       while (l < h) { uint32_t m = (l + h) >> 1; if (r[m].y < lo) l = m + 1; else h = m; }
       b = l;
     }
-    for (uint32_t i = b + tid; i < len; i += nthreads) {
-      ushort2 iv = r[i];
-      uint32_t s = iv.x, l = iv.y;
-      if (s >= hi) break;
-      if (s < lo) s = lo;
-      if (l >= hi) l = hi - 1;
-      s -= lo; l -= lo;
-      uint32_t ws = s >> 5, we = l >> 5;
-      uint32_t ms = ~0u << (s & 31), me = ~0u >> (31 - (l & 31));
-      if (ws == we) atomicOr(&win32[ws], ms & me);
-      else {
-        atomicOr(&win32[ws], ms);
-        for (uint32_t k = ws + 1; k < we; k++) win32[k] = ~0u;  // interior words belong to this run only
-        atomicOr(&win32[we], me);
+    uint32_t e = len;
+    if (hi < 65536u) {  // first run with start >= hi
+      uint32_t l = b, h = len;
+      while (l < h) { uint32_t m = (l + h) >> 1; if (r[m].x < hi) l = m + 1; else h = m; }
+      e = l;
+    }
+    // Same scheme as for arrays: a contiguous segment of the (sorted, disjoint) run list per
+    // thread, whole words assembled in a register; only the segment's first and last word
+    // can be shared with a neighbouring thread and need an atomic.
+    const uint32_t n = e - b;
+    const uint32_t per = (n + nthreads - 1) / nthreads;
+    const uint32_t i0 = b + tid * per, i1 = min(e, i0 + per);
+    if (per && i0 < i1) {
+      uint32_t cur_w = 0xffffffffu, cur_bits = 0;
+      bool first = true;
+      auto emit = [&](uint32_t w, uint32_t bits) {
+        if (w != cur_w) {
+          if (cur_w != 0xffffffffu) {
+            if (first) { atomicOr(&win32[cur_w], cur_bits); first = false; }
+            else win32[cur_w] = cur_bits;
+          }
+          cur_w = w; cur_bits = 0;
+        }
+        cur_bits |= bits;
+      };
+#pragma unroll 2
+      for (uint32_t i = i0; i < i1; i++) {
+        const ushort2 iv = __ldg(r + i);
+        uint32_t s = iv.x, l = iv.y;
+        if (s < lo) s = lo;
+        if (l >= hi) l = hi - 1;
+        s -= lo; l -= lo;
+        const uint32_t ws = s >> 5, we = l >> 5;
+        const uint32_t ms = ~0u << (s & 31), me = ~0u >> (31 - (l & 31));
+        if (ws == we) emit(ws, ms & me);
+        else {
+          emit(ws, ms);
+          for (uint32_t k = ws + 1; k < we; k++) emit(k, ~0u);
+          emit(we, me);
+        }
       }
+      atomicOr(&win32[cur_w], cur_bits);
     }
   }
 }
@@ -327,9 +494,13 @@ __global__ void __launch_bounds__(kStagedThreads) eval_staged_kernel(EvalParams 
   __shared__ int s_slot[kMaxLeaves];
   __shared__ int s_nslots;
   __shared__ uint32_t s_red[kStagedThreads / 32];
+  __shared__ unsigned long long s_base[kMaxLeaves];
+  __shared__ uint32_t s_stride[kMaxLeaves];
+  __shared__ __align__(16) uint4 s_const[2];
   __shared__ __align__(16) uint64_t s_win[kSlotWords];
   const int tid = threadIdx.x;
   const uint32_t n_slow = *p.slow_count;
+  if (tid == 0) { s_const[0] = make_uint4(0, 0, 0, 0); s_const[1] = make_uint4(~0u, ~0u, ~0u, ~0u); }
 
   for (uint32_t it = blockIdx.x; it < n_slow; it += gridDim.x) {
     const uint64_t item = p.slow_list[it];
@@ -341,14 +512,24 @@ __global__ void __launch_bounds__(kStagedThreads) eval_staged_kernel(EvalParams 
     const Instr* ins = p.instrs + pg.instr_off;
 
     __syncthreads();  // previous item fully consumed
-    if (tid < pg.n_leaves) s_desc[tid] = resolve_leaf(p, p.leaves[pg.leaf_off + tid], s, c);
-    __syncthreads();
-    if (tid == 0) {
-      int ns = 0;
-      for (uint32_t l = 0; l < pg.n_leaves; l++) s_slot[l] = is_const_or_bitmap(s_desc[l]) ? -1 : ns++;
-      s_nslots = ns;
+    if (tid < 32) {  // warp 0: descriptors + staging-slot assignment (n_leaves <= 32)
+      ContainerDesc d; d.addr = 0; d.n = 0; d.meta = 0;
+      if (tid < pg.n_leaves) {
+        d = p.slow_descs ? p.slow_descs[uint64_t(it) * p.slow_desc_stride + tid] : resolve_leaf(p, p.leaves[pg.leaf_off + tid], s, c);
+        s_desc[tid] = d;
+      }
+      const bool need = tid < pg.n_leaves && !is_const_or_bitmap(d);
+      const uint32_t mask = __ballot_sync(0xffffffffu, need);
+      if (tid < pg.n_leaves) s_slot[tid] = need ? int(__popc(mask & ((1u << tid) - 1u))) : -1;
+      if (tid == 0) s_nslots = __popc(mask);
     }
     __syncthreads();
+    // pull the bitmap operands towards L2 while the array / run operands are being staged
+    for (uint32_t l = 0; l < pg.n_leaves; l++) {
+      const ContainerDesc d = s_desc[l];
+      if (d.n != 0 && desc_type(d) == kBitmap && tid < kBitmapBytes / 128)
+        asm volatile("prefetch.global.L2 [%0];" :: "l"(d.addr + uint64_t(tid) * 128));
+    }
     const int nslots = s_nslots;
     uint32_t chunk = kBitmapWords;
     while (chunk * nslots > kSlotWords) chunk >>= 1;  // nslots <= 32 -> chunk >= 128
@@ -362,34 +543,54 @@ __global__ void __launch_bounds__(kStagedThreads) eval_staged_kernel(EvalParams 
       for (uint32_t l = 0; l < pg.n_leaves; l++)
         if (s_slot[l] >= 0) stage_container(s_desc[l], reinterpret_cast<uint32_t*>(s_win + s_slot[l] * chunk), w0, chunk, tid, kStagedThreads);
       __syncthreads();
-      // evaluate: chunk/2 uint4 per operand
-      for (uint32_t j = tid; j < chunk / 2; j += kStagedThreads) {
-        uint4 acc = make_uint4(0, 0, 0, 0);
-        uint4 stack[kMaxStack];
+      // operand sources for this pass, as (generic address, stride): global bitmap words, a staged
+      // shared-memory window, or a 16 B constant (all zeros / all ones) read with stride 0
+      if (tid < pg.n_leaves) {
+        const ContainerDesc d = s_desc[tid];
+        unsigned long long base; uint32_t stride = 16;
+        if (d.n == 0) { base = reinterpret_cast<unsigned long long>(&s_const[0]); stride = 0; }
+        else if (s_slot[tid] >= 0) base = reinterpret_cast<unsigned long long>(s_win + s_slot[tid] * chunk);
+        else if (d.n == kFullN && desc_type(d) != kBitmap) { base = reinterpret_cast<unsigned long long>(&s_const[1]); stride = 0; }
+        else base = d.addr + uint64_t(w0) * 8;
+        s_base[tid] = base; s_stride[tid] = stride;
+      }
+      __syncthreads();
+      // evaluate: the instruction loop is outermost so that each decode serves both of the
+      // thread's 128-bit chunks (chunk/2 uint4 per operand, kStagedThreads apart)
+      for (uint32_t j0 = tid; j0 < chunk / 2; j0 += 2 * kStagedThreads) {
+        const uint32_t j1 = j0 + kStagedThreads;
+        const bool two = j1 < chunk / 2;
+        uint4 acc0 = make_uint4(0, 0, 0, 0), acc1 = acc0;
+        uint4 stack0[kMaxStack], stack1[kMaxStack];
         int sp = 0;
         bool live = false;
         for (uint32_t i = 0; i < pg.n_instr; i++) {
           const Instr in = ins[i];
           if (in.op <= I_RANDNOT_LEAF) {
-            const ContainerDesc d = s_desc[in.leaf];
-            uint4 v;
-            if (d.n == 0) v = make_uint4(0, 0, 0, 0);
-            else if (s_slot[in.leaf] >= 0) v = reinterpret_cast<const uint4*>(s_win + s_slot[in.leaf] * chunk)[j];
-            else if (d.n == kFullN && desc_type(d) != kBitmap) v = make_uint4(~0u, ~0u, ~0u, ~0u);
-            else v = ldg128_stream(reinterpret_cast<const uint4*>(d.addr) + w0 / 2 + j);
+            const unsigned long long base = s_base[in.leaf];
+            const uint32_t stride = s_stride[in.leaf];
+            const uint4 v0 = *reinterpret_cast<const uint4*>(base + uint64_t(j0) * stride);
+            const uint4 v1 = two ? *reinterpret_cast<const uint4*>(base + uint64_t(j1) * stride) : make_uint4(0, 0, 0, 0);
             if (in.op == I_LOAD) {
-              if (live) stack[sp++] = acc;
-              acc = v;
+              if (live) { stack0[sp] = acc0; stack1[sp] = acc1; sp++; }
+              acc0 = v0; acc1 = v1;
               live = true;
             } else {
-              acc = apply_op(in.op, acc, v);
+              acc0 = apply_op(in.op, acc0, v0);
+              acc1 = apply_op(in.op, acc1, v1);
             }
           } else {
-            acc = apply_op(in.op, acc, stack[--sp]);
+            --sp;
+            acc0 = apply_op(in.op, acc0, stack0[sp]);
+            acc1 = apply_op(in.op, acc1, stack1[sp]);
           }
         }
-        cnt += popc128(acc);
-        if (dout) reinterpret_cast<uint4*>(dout)[w0 / 2 + j] = acc;
+        cnt += popc128(acc0);
+        if (dout) reinterpret_cast<uint4*>(dout)[w0 / 2 + j0] = acc0;
+        if (two) {
+          cnt += popc128(acc1);
+          if (dout) reinterpret_cast<uint4*>(dout)[w0 / 2 + j1] = acc1;
+        }
       }
       __syncthreads();
     }

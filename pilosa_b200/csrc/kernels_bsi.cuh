@@ -5,8 +5,64 @@
 // held in registers replaces ~3 x bitDepth materialised Row operations per shard.
 #pragma once
 #include "kernels.cuh"
+#include "tma.cuh"
 
 namespace pb200 {
+
+// ---------------------------------------------------------------------------------------
+// Plane ring: the container columns a BSI kernel consumes one after the other (E, S, filter,
+// B_i ...) are streamed through a ring of kRingDepth 8 KiB shared-memory slots by the bulk
+// copy engine. One thread issues cp.async.bulk for plane q + kRingDepth as soon as plane q
+// has been consumed, so kRingDepth x 8 KiB per CTA are always in flight however many
+// registers the comparator state needs. Bitmap containers take the TMA path; array / run
+// containers are staged into their slot by the CTA; empty / full containers are constants.
+// ---------------------------------------------------------------------------------------
+constexpr int kRingDepth = 4;
+constexpr int kRingBytes = kRingDepth * kBitmapBytes;
+
+struct PlaneRing {
+  uint8_t* ring;     // kRingDepth x 8 KiB, 128 B aligned
+  uint64_t* full;    // kRingDepth mbarriers (count 1 + transaction bytes)
+  uint32_t phase;    // expected parity per slot (bit s), tracked identically by every thread
+
+  __device__ __forceinline__ static bool by_tma(const ContainerDesc& d) { return d.n != 0 && desc_type(d) == kBitmap; }
+
+  // thread 0 only: start the copy of plane sequence number q
+  __device__ __forceinline__ void issue(const ContainerDesc& d, uint32_t q) {
+    if (!by_tma(d)) return;
+    const uint32_t slot = q % kRingDepth;
+    fence_proxy_async();  // earlier generic-proxy traffic on this slot is ordered before the async write
+    mbar_arrive_expect_tx(&full[slot], kBitmapBytes);
+    tma_load_1d(ring + slot * kBitmapBytes, reinterpret_cast<const void*>(d.addr), kBitmapBytes, &full[slot]);
+  }
+
+  // whole CTA: this thread's PER chunks of plane q. The caller must __syncthreads() before
+  // thread 0 re-issues into the same slot.
+  template <int NT, int PER>
+  __device__ __forceinline__ void take(const ContainerDesc& d, uint32_t q, int tid, uint4 (&v)[PER]) {
+    const uint32_t slot = q % kRingDepth;
+    uint4* win = reinterpret_cast<uint4*>(ring + slot * kBitmapBytes);
+    if (d.n == 0) {
+#pragma unroll
+      for (int k = 0; k < PER; k++) v[k] = make_uint4(0, 0, 0, 0);
+    } else if (desc_type(d) == kBitmap) {
+      mbar_wait(&full[slot], (phase >> slot) & 1u);
+      phase ^= 1u << slot;
+#pragma unroll
+      for (int k = 0; k < PER; k++) v[k] = win[tid + k * NT];
+    } else if (d.n == kFullN) {
+#pragma unroll
+      for (int k = 0; k < PER; k++) v[k] = make_uint4(~0u, ~0u, ~0u, ~0u);
+    } else {
+      for (int j = tid; j < kBitmapWords / 2; j += NT) win[j] = make_uint4(0, 0, 0, 0);
+      __syncthreads();
+      stage_container(d, reinterpret_cast<uint32_t*>(win), 0, kBitmapWords, tid, NT);
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < PER; k++) v[k] = win[tid + k * NT];
+    }
+  }
+};
 
 constexpr int kBsiThreads = 256;  // one CTA per (shard, container column): 2 x uint4 per thread
 constexpr int kMaxDepth = 64;
@@ -24,7 +80,9 @@ struct BsiParams {
   // range
   uint32_t bsi_op;
   int64_t a, b;
-  uint8_t* dense_out;    // range result rows: (s * 16 + c) * 8192
+  uint8_t* dense_out;    // range result rows: (s * 16 + c) * 8192 (null: count only)
+  unsigned long long* count_out;  // optional: count_out[s * count_sstride] += |result| (Count(Row(v <op> x)) without materialising)
+  uint32_t count_sstride;
   // sum
   uint32_t strict;
   unsigned long long* sum_acc;  // [0] = count, [1 + 2i] = popcount(B_i & prow), [2 + 2i] = popcount(B_i & nrow)
@@ -182,27 +240,57 @@ __device__ __forceinline__ unsigned long long uabs64(long long v) { return v < 0
 
 __global__ void __launch_bounds__(kBsiThreads) bsi_range_kernel(BsiParams p) {
   constexpr int PER = 2;
-  __shared__ __align__(16) uint64_t s_win[kBitmapWords];
+  extern __shared__ __align__(128) uint8_t s_ring[];
+  __shared__ __align__(8) uint64_t s_full[kRingDepth];
+  __shared__ ContainerDesc s_pd[kMaxDepth + 2];  // planes in consumption order: E, S, B_{d-1} .. B_0
   const int tid = threadIdx.x;
   const uint32_t n_items = p.n_shards * kRowContainers;
   unsigned long long bytes_acc = 0;
+  PlaneRing pr;
+  pr.ring = s_ring; pr.full = s_full; pr.phase = 0;
+  if (tid == 0) {
+    for (int i = 0; i < kRingDepth; i++) mbar_init(&s_full[i], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  uint32_t q0 = 0;  // planes consumed so far by this CTA (ring sequence numbers run across items)
+  const uint32_t n_planes = p.bsi_op == PB200_BSI_NOTNULL ? 1u : p.bit_depth + 2u;
+
   for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
     const uint32_t s = item >> 4, c = item & 15;
-    uint4* out = reinterpret_cast<uint4*>(p.dense_out + uint64_t(item) * kBitmapBytes);
+    uint4* out = p.dense_out ? reinterpret_cast<uint4*>(p.dense_out + uint64_t(item) * kBitmapBytes) : nullptr;
+    uint32_t cnt = 0;
     const FamilyDev fam = p.families[p.family];
     const uint64_t shard = p.shards[s];
     FragDev f{};
     if (shard < fam.cap) f = fam.frags[shard];
+    if (tid < int(n_planes)) {
+      const uint64_t row = tid < 2 ? uint64_t(tid) : uint64_t(2 + (p.bit_depth - 1 - (tid - 2)));
+      const ContainerDesc d = bsi_row_desc(f, row, c);
+      s_pd[tid] = d;
+      bytes_acc += desc_algo_bytes(d);
+    }
+    __syncthreads();
+    if (tid == 0)
+      for (uint32_t j = 0; j < n_planes && j < uint32_t(kRingDepth); j++) pr.issue(s_pd[j], q0 + j);
+
     uint4 E[PER], S[PER], res[PER];
-    const ContainerDesc dE = bsi_row_desc(f, 0, c), dS = bsi_row_desc(f, 1, c);
-    load_column<kBsiThreads, PER>(dE, s_win, tid, E);
-    if (tid == 0) bytes_acc += desc_algo_bytes(dE) + desc_algo_bytes(dS);
+    pr.take<kBsiThreads, PER>(s_pd[0], q0 + 0, tid, E);
+    __syncthreads();
+    if (tid == 0 && uint32_t(kRingDepth) < n_planes) pr.issue(s_pd[kRingDepth], q0 + kRingDepth);
     if (p.bsi_op == PB200_BSI_NOTNULL) {
 #pragma unroll
-      for (int k = 0; k < PER; k++) out[tid + k * kBsiThreads] = E[k];
+      for (int k = 0; k < PER; k++) { if (out) out[tid + k * kBsiThreads] = E[k]; cnt += popc128(E[k]); }
+      if (p.count_out) {
+        cnt = warp_sum(cnt);
+        if ((tid & 31) == 0 && cnt) atomicAdd(p.count_out + uint64_t(s) * p.count_sstride, (unsigned long long)cnt);
+      }
+      q0 += n_planes;
       continue;
     }
-    load_column<kBsiThreads, PER>(dS, s_win, tid, S);
+    pr.take<kBsiThreads, PER>(s_pd[1], q0 + 1, tid, S);
+    __syncthreads();
+    if (tid == 0 && 1u + kRingDepth < n_planes) pr.issue(s_pd[1 + kRingDepth], q0 + 1 + kRingDepth);
     uint4 pos[PER], neg[PER];
 #pragma unroll
     for (int k = 0; k < PER; k++) { pos[k] = andnot128(E[k], S[k]); neg[k] = and128(E[k], S[k]); }
@@ -232,14 +320,17 @@ __global__ void __launch_bounds__(kBsiThreads) bsi_range_kernel(BsiParams p) {
         else { m0.init(M_LTU, pos, ub, 0, true); m1.init(M_LTU, neg, ua, 0, true); combine = 4; }
         break;
     }
+    // magnitude planes MSB -> LSB through the ring
     for (int i = int(p.bit_depth) - 1; i >= 0; i--) {
-      const ContainerDesc dB = bsi_row_desc(f, 2 + i, c);
+      const uint32_t j = 2u + uint32_t(int(p.bit_depth) - 1 - i);
       uint4 row[PER];
-      load_column<kBsiThreads, PER>(dB, s_win, tid, row);
-      if (tid == 0) bytes_acc += desc_algo_bytes(dB);
+      pr.take<kBsiThreads, PER>(s_pd[j], q0 + j, tid, row);
+      __syncthreads();  // every thread has read slot (q0 + j) % depth: it may be refilled
+      if (tid == 0 && j + kRingDepth < n_planes) pr.issue(s_pd[j + kRingDepth], q0 + j + kRingDepth);
       m0.step(i, row);
       m1.step(i, row);
     }
+    q0 += n_planes;
 #pragma unroll
     for (int k = 0; k < PER; k++) {
       switch (combine) {
@@ -249,10 +340,18 @@ __global__ void __launch_bounds__(kBsiThreads) bsi_range_kernel(BsiParams p) {
         case 3: res[k] = or128(pos[k], m0.f[k]); break;
         default: res[k] = or128(m0.f[k], m1.f[k]); break;
       }
-      out[tid + k * kBsiThreads] = res[k];
+      if (out) out[tid + k * kBsiThreads] = res[k];
+      cnt += popc128(res[k]);
     }
+    if (p.count_out) {
+      cnt = warp_sum(cnt);
+      if ((tid & 31) == 0 && cnt) atomicAdd(p.count_out + uint64_t(s) * p.count_sstride, (unsigned long long)cnt);
+    }
+    __syncthreads();  // s_pd is rewritten by the next item
   }
-  if (tid == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) bytes_acc += __shfl_xor_sync(0xffffffffu, bytes_acc, o);
+  if ((tid & 31) == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -263,12 +362,23 @@ __global__ void __launch_bounds__(kBsiThreads) bsi_range_kernel(BsiParams p) {
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBsiThreads) bsi_sum_kernel(BsiParams p) {
   constexpr int PER = 2;
-  __shared__ __align__(16) uint64_t s_win[kBitmapWords];
+  extern __shared__ __align__(128) uint8_t s_ring[];
+  __shared__ __align__(8) uint64_t s_full[kRingDepth];
+  __shared__ ContainerDesc s_pd[kMaxDepth + 3];  // planes in consumption order: E, [filter], S, B_0 .. B_{d-1}
   __shared__ unsigned long long s_acc[2 * kMaxDepth + 1];
   const int tid = threadIdx.x, lane = tid & 31;
   for (int i = tid; i < 2 * kMaxDepth + 1; i += kBsiThreads) s_acc[i] = 0;
+  PlaneRing pr;
+  pr.ring = s_ring; pr.full = s_full; pr.phase = 0;
+  if (tid == 0) {
+    for (int i = 0; i < kRingDepth; i++) mbar_init(&s_full[i], 1);
+    mbar_fence_init();
+  }
   __syncthreads();
   const uint32_t n_items = p.n_shards * kRowContainers;
+  const uint32_t nf = p.has_filter ? 1u : 0u;
+  const uint32_t n_planes = p.bit_depth + 2u + nf;
+  uint32_t q0 = 0;
   unsigned long long bytes_acc = 0;
   for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
     const uint32_t s = item >> 4, c = item & 15;
@@ -277,19 +387,35 @@ __global__ void __launch_bounds__(kBsiThreads) bsi_sum_kernel(BsiParams p) {
     FragDev f{};
     if (shard < fam.cap) f = fam.frags[shard];
     if (f.nrows == 0) continue;  // no fragment: ValCount{} (executor.go:709-711)
+    __syncthreads();             // s_pd of the previous item fully consumed
+    if (tid < int(n_planes)) {
+      ContainerDesc d;
+      if (tid == 0) d = bsi_row_desc(f, 0, c);
+      else if (nf && tid == 1) d = filter_desc(p, s, c);
+      else if (tid == int(1 + nf)) d = bsi_row_desc(f, 1, c);
+      else d = bsi_row_desc(f, 2 + (tid - 2 - nf), c);
+      s_pd[tid] = d;
+      bytes_acc += desc_algo_bytes(d);
+    }
+    __syncthreads();
+    if (tid == 0)
+      for (uint32_t j = 0; j < n_planes && j < uint32_t(kRingDepth); j++) pr.issue(s_pd[j], q0 + j);
+    uint32_t j = 0;
+    auto next_plane = [&](uint4 (&v)[PER]) {
+      pr.take<kBsiThreads, PER>(s_pd[j], q0 + j, tid, v);
+      __syncthreads();  // slot consumed by every thread: refill it
+      if (tid == 0 && j + kRingDepth < n_planes) pr.issue(s_pd[j + kRingDepth], q0 + j + kRingDepth);
+      j++;
+    };
     uint4 cons[PER], nrow[PER], prow[PER];
-    const ContainerDesc dE = bsi_row_desc(f, 0, c), dS = bsi_row_desc(f, 1, c);
-    load_column<kBsiThreads, PER>(dE, s_win, tid, cons);
-    if (p.has_filter) {
-      const ContainerDesc dF = filter_desc(p, s, c);
+    next_plane(cons);
+    if (nf) {
       uint4 fl[PER];
-      load_column<kBsiThreads, PER>(dF, s_win, tid, fl);
-      if (tid == 0) bytes_acc += desc_algo_bytes(dF);
+      next_plane(fl);
 #pragma unroll
       for (int k = 0; k < PER; k++) cons[k] = and128(cons[k], fl[k]);
     }
-    load_column<kBsiThreads, PER>(dS, s_win, tid, nrow);
-    if (tid == 0) bytes_acc += desc_algo_bytes(dE) + desc_algo_bytes(dS);
+    next_plane(nrow);
     uint32_t cnt = 0;
 #pragma unroll
     for (int k = 0; k < PER; k++) {
@@ -300,11 +426,8 @@ __global__ void __launch_bounds__(kBsiThreads) bsi_sum_kernel(BsiParams p) {
     cnt = warp_sum(cnt);
     if (lane == 0 && cnt) atomicAdd(&s_acc[0], (unsigned long long)cnt);
     for (uint32_t i = 0; i < p.bit_depth; i++) {
-      const ContainerDesc dB = bsi_row_desc(f, 2 + i, c);
-      if (dB.n == 0) continue;
       uint4 row[PER];
-      load_column<kBsiThreads, PER>(dB, s_win, tid, row);
-      if (tid == 0) bytes_acc += desc_algo_bytes(dB);
+      next_plane(row);
       uint32_t pc = 0, nc = 0;
 #pragma unroll
       for (int k = 0; k < PER; k++) { pc += popc128(and128(row[k], prow[k])); nc += popc128(and128(row[k], nrow[k])); }
@@ -314,11 +437,14 @@ __global__ void __launch_bounds__(kBsiThreads) bsi_sum_kernel(BsiParams p) {
         if (nc) atomicAdd(&s_acc[2 + 2 * i], (unsigned long long)nc);
       }
     }
+    q0 += n_planes;
   }
   __syncthreads();
   for (uint32_t i = tid; i < 2 * p.bit_depth + 1; i += kBsiThreads)
     if (s_acc[i]) atomicAdd(p.sum_acc + i, s_acc[i]);
-  if (tid == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) bytes_acc += __shfl_xor_sync(0xffffffffu, bytes_acc, o);
+  if (lane == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
 }
 
 // ---------------------------------------------------------------------------------------

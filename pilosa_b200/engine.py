@@ -62,6 +62,7 @@ def load_library() -> C.CDLL:
         "pb200_frag_apply": (i32, [vp, u32, u64, u64p, sz, u64p, sz]),
         "pb200_frag_drop": (i32, [vp, u32, u64]),
         "pb200_rank_set": (i32, [vp, u32, u64, u64p, u64p, sz]),
+        "pb200_host_check_roaring": (i32, [C.c_char_p, sz, u64p, u64p, C.c_char_p, sz]),
         "pb200_frag_stat": (i32, [vp, u32, u64, u64p, u64p, u64p]),
         "pb200_count": (i32, [vp, np_, u32, u64p, u32, u64p]),
         "pb200_count_batch": (i32, [vp, np_, u32p, u32, u64p, u32, u64p]),
@@ -90,6 +91,18 @@ def load_library() -> C.CDLL:
         fn.restype, fn.argtypes = res, args
     _lib = L
     return L
+
+
+def host_check_roaring(data: bytes) -> Tuple[int, int]:
+    """Validate fragment-file bytes with the loader's parser, no GPU needed.
+    Returns (non-empty containers, total bits) or raises EngineError(PB200_ERR_FORMAT)."""
+    lib = load_library()
+    nc, nb = C.c_uint64(), C.c_uint64()
+    err = C.create_string_buffer(256)
+    rc = lib.pb200_host_check_roaring(data, len(data), C.byref(nc), C.byref(nb), err, 256)
+    if rc != 0:
+        raise EngineError(rc, err.value.decode() or lib.pb200_strerror(rc).decode())
+    return nc.value, nb.value
 
 
 class Engine:

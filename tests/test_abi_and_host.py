@@ -205,3 +205,33 @@ def test_two_rank_gloo_shard_partition(tmp_path):
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
         assert "ok" in o
+
+
+def test_host_loader_parser_matches_oracle_and_survives_fuzz():
+    """The loader's own parser (snapshot + ops-log replay, no GPU) agrees with the oracle's
+    restatement of unmarshalPilosaRoaring on valid files and rejects malformed ones cleanly."""
+    import random
+
+    from pilosa_b200.engine import EngineError, host_check_roaring
+
+    good = synth.mixed(0, 0, 3).bytes()
+    ops = oracle.encode_op(0, [5]) + oracle.encode_op(2, [70000, 1 << 21, (1 << 21) + 9]) + oracle.encode_op(1, [5]) + oracle.encode_op(3, [12])
+    for blob in (good, good + ops, synth.bernoulli(2, 0, 2, 0.1).bytes(), synth.bernoulli(2, 0, 2, 1e-4).bytes() + ops):
+        ref = oracle.Bitmap.deserialize(blob)
+        nc, nb = host_check_roaring(blob)
+        assert nb == ref.count() and nc == len(ref.containers())
+    for blob, msg in ((b"", "too small"), (b"\x00" * 32, "magic"), (good[:40], "truncated"), (good + b"\x09" * 13, "unknown op type"),
+                      (good + oracle.encode_op(0, [5])[:-1] + b"\x00", "checksum")):
+        with pytest.raises(EngineError, match=msg):
+            host_check_roaring(blob)
+    rnd = random.Random(2)
+    rejected = 0
+    for _ in range(400):
+        b = bytearray(good if rnd.random() < 0.5 else good[: rnd.randrange(8, len(good))])
+        for _ in range(rnd.randrange(1, 8)):
+            b[rnd.randrange(min(len(b), 800))] = rnd.randrange(256)
+        try:
+            host_check_roaring(bytes(b))
+        except EngineError:
+            rejected += 1
+    assert rejected > 200  # and, above all, no crash
