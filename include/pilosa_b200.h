@@ -67,7 +67,9 @@ enum pb200_op {
   PB200_OP_XOR = 5,        /* executeXorShard executor.go:1715; Row.Xor row.go:133                 */
   PB200_OP_NOT = 6,        /* executeNotShard executor.go:1737-1768: family = existence field,
                               row = 0, one operand: exists.row(0) \ operand                         */
-  PB200_OP_SHIFT = 7,      /* executeShiftShard executor.go:1771; Bitmap.Shift roaring.go:944 (n=1)*/
+  PB200_OP_SHIFT = 7,      /* executeShiftShard executor.go:1771; Bitmap.Shift roaring.go:944 (one step; nest for n>1,
+                              at most 64 deep). The bit leaving the shard's last column is kept under container key
+                              (shard+1)*16 of the same segment, as roaring.go:970-974 does. */
   PB200_OP_BSI_RANGE = 8,  /* fragment.rangeOp / rangeBetween / notNull fragment.go:1271-1534      */
   PB200_OP_EMPTY = 9       /* NewRow(): used by hosts for out-of-range BSI predicates
                               (executor.go:1611,1641) and Union()/Xor() with no children           */

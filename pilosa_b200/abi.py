@@ -105,10 +105,14 @@ def Not(child: Call, existence_field: str = "exists") -> Call:
     return Call("Not", [child], field_name=existence_field)
 
 
-def Shift(child: Call, n: int = 1) -> Call:
-    if n != 1:
-        raise ValueError("cannot shift by a value other than 1")  # roaring.go:945
-    return Call("Shift", [child])
+def Shift(child: Call, n: int = 0) -> Call:
+    """Shift(row, n=): Row.Shift (row.go:217-239) applies the one-step roaring shift n times; a missing
+    n is 0 (executor.go:1772, IntArg of an absent key) and returns the row unchanged."""
+    if n < 0:
+        raise ValueError("cannot shift by negative values")  # row.go:219
+    for _ in range(n):
+        child = Call("Shift", [child])
+    return child
 
 
 def Empty() -> Call:

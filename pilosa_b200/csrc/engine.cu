@@ -142,7 +142,7 @@ extern "C" int pb200_shutdown(pb200_ctx* ctx) {
       if (fam.d_frags) cudaFree(fam.d_frags);
     }
     if (ctx->d_families) cudaFree(ctx->d_families);
-    for (DevBuf* b : {&ctx->d_slow_descs, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi})
+    for (DevBuf* b : {&ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi})
       if (b->p) cudaFree(b->p);
     for (PinBuf* b : {&ctx->h_stage, &ctx->h_out, &ctx->h_algo, &ctx->h_topn})
       if (b->p) cudaFreeHost(b->p);
@@ -645,6 +645,9 @@ void timing_begin(pb200_ctx* ctx) {
 
 // Runs the pre-tasks (BSI range / shift / sub-expression temps) of a compiled batch.
 int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_t n_shards);
+bool has_shift(const Compiled& cp);
+int launch_overflow(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards,
+                    unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, unsigned long long* ovf_out);
 
 // Ends a query call: fetches the algorithmic-byte counter with the other results, waits for
 // the stream once, and reads the kernel time between the ev0/ev1 events.
@@ -744,6 +747,8 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
     if (rc == PB200_OK)
       rc = launch_eval(ctx, bd, bd.progs, n_queries, n_shards, cp.may_need_staging, d_out, per_shard ? n_shards : 1, per_shard ? 1 : 0,
                        nullptr, nullptr, max_leaves_of(cp));
+    if (rc == PB200_OK && has_shift(cp))  // bits shifted past a shard's last column count too (roaring.go:970-974)
+      rc = launch_overflow(ctx, bd, bd.progs, n_queries, n_shards, d_out, per_shard ? n_shards : 1, per_shard ? 1 : 0, nullptr);
     if (rc != PB200_OK) { ctx->n_pending--; ctx->algo_off = 8; return rc; }
   }
   ctx->algo_off = 8;

@@ -91,7 +91,9 @@ struct pb200_ctx {
   pb200::FamilyDev* d_families = nullptr;
   uint32_t d_families_cap = 0;
   bool families_dirty = true;
-  pb200::DevBuf d_slow_descs;
+  pb200::DevBuf d_slow_descs, d_ovf;
+  bool dense_has_ovf = false;                      // the rows in d_dense carry Shift overflow words
+  unsigned long long* dense_ovf_dev = nullptr;
   pb200::DevBuf d_batch, d_out, d_slow, d_temp, d_dense, d_dense_n, d_misc, d_topn, d_bsi;
   pb200::PinBuf h_stage, h_out, h_algo, h_topn;
   bool mm_attr_set = false, topn_attr_set = false;

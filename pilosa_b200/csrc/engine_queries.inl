@@ -23,7 +23,35 @@ int launch_bsi_range(pb200_ctx* ctx, const BatchDev& bd, const pb200_node& nd, u
   return PB200_OK;
 }
 
+bool has_shift(const Compiled& cp) {
+  for (auto& pt : cp.pre) if (pt.kind == 1) return true;
+  return false;
+}
+
+unsigned long long* ovf_slot(pb200_ctx* ctx, uint32_t slot, uint32_t n_shards) {
+  return static_cast<unsigned long long*>(ctx->d_ovf.p) + size_t(slot) * n_shards;
+}
+
+// Overflow words (see shift_overflow_kernel) of `n_queries` programs: added to the counts and / or stored.
+int launch_overflow(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards,
+                    unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, unsigned long long* ovf_out) {
+  OverflowParams op{};
+  op.progs = progs; op.instrs = bd.instrs; op.leaves = bd.leaves; op.n_queries = n_queries; op.n_shards = n_shards;
+  op.ovf = static_cast<const unsigned long long*>(ctx->d_ovf.p);
+  op.out_counts = out_counts; op.out_qstride = qstride; op.out_sstride = sstride; op.ovf_out = ovf_out;
+  const uint64_t n = uint64_t(n_queries) * n_shards;
+  eval_overflow_kernel<<<uint32_t((n + 127) / 128), 128, 0, ctx->stream>>>(op);
+  ctx->timing.launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return PB200_OK;
+}
+
 int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_t n_shards) {
+  if (has_shift(cp)) {  // overflow words of every temp slot (+1 for a result), zero unless a shift sets them
+    const size_t bytes = size_t(cp.n_temp_slots + 1) * n_shards * 8;
+    TRY(ensure_dev(ctx, ctx->d_ovf, bytes));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_ovf.p, 0, bytes, ctx->stream));
+  }
   for (size_t i = 0; i < cp.pre.size(); i++) {
     const auto& pt = cp.pre[i];
     if (pt.kind == 0) {
@@ -33,11 +61,14 @@ int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_
         TRY(launch_bsi_range(ctx, bd, pt.node, n_shards, temp_slot(ctx, pt.slot, n_shards)));
     } else if (pt.kind == 2) {
       TRY(launch_eval(ctx, bd, bd.progs + cp.progs.size() + i, 1, n_shards, true, nullptr, 0, 0, temp_slot(ctx, pt.slot, n_shards), nullptr));
+      if (has_shift(cp)) TRY(launch_overflow(ctx, bd, bd.progs + cp.progs.size() + i, 1, n_shards, nullptr, 0, 0, ovf_slot(ctx, pt.slot, n_shards)));
     } else {
       const uint64_t n_words = uint64_t(n_shards) * kRowContainers * kBitmapWords;
       const uint32_t grid = uint32_t(std::min<uint64_t>((n_words + 255) / 256, uint64_t(ctx->sm_count) * 16));
       shift_rows_kernel<<<grid, 256, 0, ctx->stream>>>(temp_slot(ctx, pt.src_slot, n_shards), temp_slot(ctx, pt.slot, n_shards), n_shards);
-      ctx->timing.launches++;
+      shift_overflow_kernel<<<(n_shards + 127) / 128, 128, 0, ctx->stream>>>(temp_slot(ctx, pt.src_slot, n_shards), ovf_slot(ctx, pt.src_slot, n_shards),
+                                                                            ovf_slot(ctx, pt.slot, n_shards), n_shards);
+      ctx->timing.launches += 2;
       CUDA_TRY(ctx, cudaGetLastError());
     }
   }
@@ -58,10 +89,16 @@ int eval_dense(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const u
   TRY(ensure_dev(ctx, ctx->d_dense_n, items * 4));
   if (cp.n_temp_slots) TRY(ensure_dev(ctx, ctx->d_temp, size_t(cp.n_temp_slots) * items * kBitmapBytes));
   TRY(run_pretasks(ctx, cp, bd, n_shards));
+  ctx->dense_has_ovf = has_shift(cp);
+  if (ctx->dense_has_ovf) {
+    ctx->dense_ovf_dev = ovf_slot(ctx, cp.n_temp_slots, n_shards);
+    TRY(launch_overflow(ctx, bd, bd.progs, 1, n_shards, nullptr, 0, 0, ctx->dense_ovf_dev));
+  }
   return launch_eval(ctx, bd, bd.progs, 1, n_shards, true, nullptr, 0, 0, static_cast<uint8_t*>(ctx->d_dense.p), static_cast<uint32_t*>(ctx->d_dense_n.p));
 }
 
-int eval_one_shard(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, std::vector<uint64_t>& words, std::vector<uint32_t>& ns) {
+int eval_one_shard(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, std::vector<uint64_t>& words, std::vector<uint32_t>& ns,
+                   uint64_t* overflow) {
   TRY(ensure_dev(ctx, ctx->d_misc, 64));
   timing_begin(ctx);
   BatchDev bd{};
@@ -72,6 +109,8 @@ int eval_one_shard(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uin
   ns.resize(kRowContainers);
   CUDA_TRY(ctx, cudaMemcpyAsync(words.data(), ctx->d_dense.p, words.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(ns.data(), ctx->d_dense_n.p, ns.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  *overflow = 0;
+  if (ctx->dense_has_ovf) CUDA_TRY(ctx, cudaMemcpyAsync(overflow, ctx->dense_ovf_dev, 8, cudaMemcpyDeviceToHost, ctx->stream));
   TRY(finish_call(ctx));
   ctx->timing.d2h_bytes += words.size() * 8 + ns.size() * 4;
   return PB200_OK;
@@ -84,7 +123,8 @@ extern "C" int pb200_eval(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nod
   if (!out_len) return PB200_ERR_INVALID;
   std::vector<uint64_t> words;
   std::vector<uint32_t> ns;
-  TRY(eval_one_shard(ctx, prog, n_nodes, shard, words, ns));
+  uint64_t overflow = 0;
+  TRY(eval_one_shard(ctx, prog, n_nodes, shard, words, ns, &overflow));
   // encode: containers optimize()d, keys shard*16 + c (fragment.go:629 OffsetRange re-keying)
   std::vector<HostContainer> cs;
   for (int c = 0; c < kRowContainers; c++) {
@@ -92,6 +132,15 @@ extern "C" int pb200_eval(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nod
     HostContainer hc;
     hc.key = shard * kRowContainers + c;
     from_words(words.data() + size_t(c) * kBitmapWords, hc);
+    cs.push_back(std::move(hc));
+    cs.back().data = cs.back().owned.data();
+  }
+  if (overflow) {  // bits a Shift carried past the shard's last column: container key (shard+1)*16 (roaring.go:970-974)
+    std::vector<uint64_t> w(kBitmapWords, 0);
+    w[0] = overflow;
+    HostContainer hc;
+    hc.key = (shard + 1) * kRowContainers;
+    from_words(w.data(), hc);
     cs.push_back(std::move(hc));
     cs.back().data = cs.back().owned.data();
   }
@@ -109,8 +158,9 @@ extern "C" int pb200_eval_columns(pb200_ctx* ctx, const pb200_node* prog, uint32
   if (!out_n) return PB200_ERR_INVALID;
   std::vector<uint64_t> words;
   std::vector<uint32_t> ns;
-  TRY(eval_one_shard(ctx, prog, n_nodes, shard, words, ns));
-  size_t total = 0;
+  uint64_t overflow = 0;
+  TRY(eval_one_shard(ctx, prog, n_nodes, shard, words, ns, &overflow));
+  size_t total = size_t(__builtin_popcountll(overflow));
   for (uint32_t n : ns) total += n;
   *out_n = total;
   if (!out_cols) return PB200_OK;
@@ -121,6 +171,7 @@ extern "C" int pb200_eval_columns(pb200_ctx* ctx, const pb200_node* prog, uint32
     uint64_t v = words[w];
     while (v) { out_cols[k++] = base + w * 64 + __builtin_ctzll(v); v &= v - 1; }
   }
+  for (uint64_t v = overflow; v; v &= v - 1) out_cols[k++] = base + PB200_SHARD_WIDTH + __builtin_ctzll(v);
   return PB200_OK;
 }
 

@@ -608,9 +608,11 @@ __global__ void __launch_bounds__(kMmThreads) bsi_minmax_kernel(BsiParams p) {
 
 // ---------------------------------------------------------------------------------------
 // Shift by one with carry across containers (roaring.go:944-977, :4374-4388) on dense rows:
-// out = (in << 1) | carry_in; the carry out of column 15 would leave the shard and is
-// dropped exactly like Row.Shift per-shard semantics of the bitmap (the reference appends
-// a container at key+1, i.e. the next shard's range; per-shard execution cannot see it).
+// out = (in << 1) | carry_in. The bit carried out of the shard's last column is not lost:
+// Bitmap.Shift appends it as a container at key+1 (roaring.go:970-974), which inside a
+// per-shard row segment is the first container of the NEXT shard's key range. That
+// container is modelled as one 64-bit "overflow word" per (temp slot, shard): bit k =
+// column (shard + 1) * 2^20 + k, enough for 64 nested shifts.
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) shift_rows_kernel(const uint8_t* in, uint8_t* out, uint32_t n_shards) {
   const uint64_t n_words = uint64_t(n_shards) * kRowContainers * kBitmapWords;
@@ -621,6 +623,59 @@ __global__ void __launch_bounds__(256) shift_rows_kernel(const uint8_t* in, uint
     const uint64_t prev = in_row == 0 ? 0 : a[w - 1];
     o[w] = (a[w] << 1) | (prev >> 63);
   }
+}
+
+// overflow word of a shifted row: the operand's own overflow container shifted by one, plus
+// the carry out of the operand's last word
+__global__ void shift_overflow_kernel(const uint8_t* in, const unsigned long long* ovf_in, unsigned long long* ovf_out, uint32_t n_shards) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_shards) return;
+  const uint64_t* a = reinterpret_cast<const uint64_t*>(in) + (uint64_t(s) + 1) * kRowContainers * kBitmapWords - 1;
+  ovf_out[s] = (ovf_in[s] << 1) | (*a >> 63);
+}
+
+// The accumulator machine over overflow words only: leaves that are temp rows contribute
+// their overflow word, every stored row contributes 0 (a fragment has no container in the
+// next shard's key range), so Intersect drops the overflow, Union / Xor / Difference keep it —
+// exactly what the roaring merge-joins do with a key that exists on one side only
+// (roaring.go:593-941). One thread per (query, shard).
+struct OverflowParams {
+  const Prog* progs; const Instr* instrs; const Leaf* leaves;
+  uint32_t n_queries, n_shards;
+  const unsigned long long* ovf;   // [slot][n_shards]
+  unsigned long long* out_counts;  // optional: += popcount at [q * qstride + s * sstride]
+  uint32_t out_qstride, out_sstride;
+  unsigned long long* ovf_out;     // optional: result word per (q, s)
+};
+
+__global__ void eval_overflow_kernel(OverflowParams p) {
+  const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= uint64_t(p.n_queries) * p.n_shards) return;
+  const uint32_t q = uint32_t(i / p.n_shards), s = uint32_t(i % p.n_shards);
+  const Prog pg = p.progs[q];
+  unsigned long long acc = 0, stack[kMaxStack];
+  int sp = 0;
+  bool live = false;
+  for (uint32_t k = 0; k < pg.n_instr; k++) {
+    const Instr in = p.instrs[pg.instr_off + k];
+    unsigned long long v;
+    if (in.op <= I_RANDNOT_LEAF) {
+      const Leaf lf = p.leaves[pg.leaf_off + in.leaf];
+      v = lf.kind == L_TEMP ? p.ovf[uint64_t(lf.family) * p.n_shards + s] : 0ull;
+      if (in.op == I_LOAD) { if (live) stack[sp++] = acc; acc = v; live = true; continue; }
+    } else {
+      v = stack[--sp];
+    }
+    switch (in.op) {
+      case I_AND_LEAF: case I_AND_STACK: acc &= v; break;
+      case I_OR_LEAF: case I_OR_STACK: acc |= v; break;
+      case I_XOR_LEAF: case I_XOR_STACK: acc ^= v; break;
+      case I_ANDNOT_LEAF: acc &= ~v; break;
+      default: acc = v & ~acc; break;  // I_RANDNOT_LEAF, I_ANDNOT_STACK: left \ acc
+    }
+  }
+  if (p.ovf_out) p.ovf_out[i] = acc;
+  if (p.out_counts && acc) atomicAdd(p.out_counts + uint64_t(q) * p.out_qstride + uint64_t(s) * p.out_sstride, (unsigned long long)__popcll(acc));
 }
 
 }  // namespace pb200

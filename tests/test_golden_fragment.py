@@ -4,7 +4,7 @@ the C ABI (`-m gpu`), with the expected values being the literals of the Go test
 import pytest
 
 from pilosa_b200 import abi
-from pilosa_b200.abi import Difference, Intersect, Not, Row, Union, Xor
+from pilosa_b200.abi import Difference, Intersect, Not, Row, Shift, Union, Xor
 
 from world import SW, World
 
@@ -285,3 +285,50 @@ def test_executor_row_bsigroup(w):
     assert q("edge", abi.BSI_GTE, -900) == [1, 2, 3, 4]
     assert q("edge", abi.BSI_LTE, 1000) == [1, 2, 3, 4]
     assert q("edge", abi.BSI_EQ, -900) == [2] and q("edge", abi.BSI_EQ, 1000) == [3]
+
+
+# ---- executor_test.go:3999-4085 TestExecutor_Execute_Shift ----
+def test_executor_shift_bit0_and_container_boundary(w):
+    w.create_field("general")
+    w.set_bit("general", 10, 0)
+    w.set_bit("general", 11, 65535)
+    assert w.ex.row_columns(Shift(Row("general", 10), n=1), [0]) == [1]
+    assert w.ex.row_columns(Shift(Shift(Row("general", 10), n=1), n=1), [0]) == [2]
+    assert w.ex.row_columns(Shift(Row("general", 11), n=1), [0]) == [65536]
+
+
+def test_executor_shift_shard_boundary(w):
+    w.create_field("general")
+    orig = [1, SW - 1, SW + 1]
+    w.set_bits("general", 10, *orig)
+    assert w.ex.row_columns(Shift(Row("general", 10), n=1), [0, 1]) == [2, SW, SW + 2]
+    assert w.ex.row_columns(Shift(Row("general", 10), n=2), [0, 1]) == [3, SW + 1, SW + 3]
+    assert w.ex.row_columns(Shift(Shift(Row("general", 10))), [0, 1]) == orig  # n defaults to 0
+    assert w.ex.count(Shift(Row("general", 10), n=1), [0, 1]) == 3
+
+
+def test_executor_shift_shard_boundary_no_create(w):
+    w.create_field("general")
+    w.set_bits("general", 10, SW - 2, SW - 1, SW, SW + 2)
+    assert w.ex.row_columns(Shift(Row("general", 10), n=1), [0, 1]) == [SW - 1, SW, SW + 1, SW + 3]
+    assert w.ex.row_columns(Shift(Shift(Row("general", 10), n=1), n=1), [0, 1]) == [SW, SW + 1, SW + 2, SW + 4]
+    assert w.ex.count(Shift(Shift(Row("general", 10), n=1), n=1), [0, 1]) == 4
+
+
+# The carried bit lives under the next shard's container key inside the SAME segment
+# (roaring.go:970-974), so set ops see it only against other shifted rows: Intersect with a
+# stored row drops it, Union / Xor / Difference keep it (row.go:106-213 work per segment).
+def test_shift_overflow_in_set_ops(w):
+    w.create_field("general")
+    w.set_bits("general", 1, 5, SW - 1)
+    w.set_bits("general", 2, 6, SW - 1, SW)
+    w.set_bits("general", 3, 5, SW - 2, SW - 1)
+    s1, s3 = Shift(Row("general", 1), n=1), Shift(Row("general", 3), n=1)
+    for call, shards in [(Intersect(s1, Row("general", 2)), [0, 1]), (Union(s1, Row("general", 2)), [0, 1]), (Union(s1, Row("general", 2)), [0]),
+                         (Xor(s1, s3), [0, 1]), (Difference(s3, s1), [0]), (Difference(Row("general", 2), s1), [0, 1]),
+                         (Intersect(s1, s3), [0]), (Shift(Union(s1, s3), n=3), [0]), (Xor(Shift(s3, n=1), s1), [0])]:
+        got = w.ex.row_columns(call, shards)
+        assert got == w.cpu.row_columns(call, shards), repr(call)
+        assert w.ex.count(call, shards) == len(got), repr(call)
+    assert w.ex.row_columns(Intersect(s1, s3), [0]) == [6, SW]
+    assert w.ex.row_columns(Union(s1, Row("general", 2)), [0, 1]) == [6, SW - 1, SW, SW]  # both segments hold column SW
