@@ -475,6 +475,7 @@ struct Compiler {
     leaf_base = uint32_t(out.leaves.size());
     tree.clear();
     std::vector<int> st;
+    uint32_t n_shifts = 0;
     for (uint32_t k = 0; k < n; k++) {
       const pb200_node& nd = nodes[k];
       switch (nd.op) {
@@ -519,6 +520,7 @@ struct Compiler {
         }
         case PB200_OP_SHIFT: {
           if (st.empty()) { err = "Shift() requires an input row"; return false; }  // executor.go:1777
+          if (++n_shifts > 64) { err = "too many Shift steps in one call (limit 64: the carried bits live in one 64-bit word per shard)"; return false; }
           // materialise the operand, then shift it by one with carry across containers
           Compiled::PreTask ev; ev.kind = 2; ev.slot = out.n_temp_slots++;
           // The operand's leaves sit in [leaf_base, now): compile it as its own program over the same table.

@@ -249,6 +249,8 @@ def test_error_behaviour(pair):
         g.count(Intersect(), shards)
     with pytest.raises(EngineError, match="empty Difference"):
         g.count(Difference(), shards)
+    with pytest.raises(EngineError, match="too many Shift"):
+        g.count(Shift(Row("f", 1), n=65), shards)
     with pytest.raises(EngineError):
         g.be.frag_load(g.family("f"), 0, b"\x00\x01\x02")
     with pytest.raises(EngineError, match="magic"):
