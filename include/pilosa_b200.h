@@ -67,8 +67,8 @@ enum pb200_op {
   PB200_OP_XOR = 5,        /* executeXorShard executor.go:1715; Row.Xor row.go:133                 */
   PB200_OP_NOT = 6,        /* executeNotShard executor.go:1737-1768: family = existence field,
                               row = 0, one operand: exists.row(0) \ operand                         */
-  PB200_OP_SHIFT = 7,      /* executeShiftShard executor.go:1771; Bitmap.Shift roaring.go:944 (one step; nest for n>1,
-                              at most 64 deep). The bit leaving the shard's last column is kept under container key
+  PB200_OP_SHIFT = 7,      /* executeShiftShard executor.go:1771; Bitmap.Shift roaring.go:944 (one step; nest for n>1;
+                              each step is a leaf of the call, so at most 31 deep). The bit leaving the shard's last column is kept under container key
                               (shard+1)*16 of the same segment, as roaring.go:970-974 does. */
   PB200_OP_BSI_RANGE = 8,  /* fragment.rangeOp / rangeBetween / notNull fragment.go:1271-1534      */
   PB200_OP_EMPTY = 9       /* NewRow(): used by hosts for out-of-range BSI predicates
@@ -251,6 +251,19 @@ int pb200_count_pairs_noalloc(pb200_ctx* ctx, pb200_family family, const uint64_
  * Replaces executor.go:654-680 executeBitmapCallShard for bitmap-returning calls. */
 int pb200_eval(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard,
                void* out, size_t cap, size_t* out_len);
+
+/* The same for ALL local shards of a bitmap-returning call in one launch sequence: what
+ * executor.mapperLocal (executor.go:2576) + executeBitmapCallShard (:654) produce before
+ * Row.Merge (:595-602), one row segment per shard. The segments are typed (Container.optimize,
+ * roaring.go:2289-2338) and serialised ON THE DEVICE; `out` receives the per-shard Pilosa
+ * roaring streams packed back to back in shard-list order, stream i at
+ * out + out_off[i] with length out_off[i+1] - out_off[i] (out_off: n_shards + 1 entries, may be
+ * NULL). A shard without data yields the 8-byte empty stream. With out == NULL only *out_len
+ * (and out_off) are written; if cap is too small PB200_ERR_RANGE is returned with the needed
+ * size in *out_len. Upper bound for sizing: n_shards * (128 KiB + 536) bytes. */
+int pb200_eval_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
+                      const uint64_t* shards, uint32_t n_shards, void* out, size_t cap,
+                      uint64_t* out_off, size_t* out_len);
 
 /* Evaluate a bitmap call on one shard into the sorted list of absolute column ids
  * (row.go:302-327 Row.Columns). Two-call protocol as above (cap in elements). */

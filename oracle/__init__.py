@@ -374,6 +374,9 @@ class Oracle:
         _check(lib().orc_eval_roaring(self._h, prog, len(prog), shard, buf, n.value, C.byref(n)))
         return buf.raw[: n.value]
 
+    def eval_roaring_shards(self, prog, shards) -> list:
+        return [self.eval_roaring(prog, s) for s in shards]
+
     def _pairs(self, fn, *args, cap=1 << 16):
         out = (Pair * cap)()
         n = C.c_size_t()

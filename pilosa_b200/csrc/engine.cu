@@ -14,6 +14,7 @@
 #include "kernels.cuh"
 #include "kernels_bsi.cuh"
 #include "kernels_topn.cuh"
+#include "kernels_rows.cuh"
 
 using namespace pb200;
 
@@ -142,7 +143,7 @@ extern "C" int pb200_shutdown(pb200_ctx* ctx) {
       if (fam.d_frags) cudaFree(fam.d_frags);
     }
     if (ctx->d_families) cudaFree(ctx->d_families);
-    for (DevBuf* b : {&ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi})
+    for (DevBuf* b : {&ctx->d_rows, &ctx->d_rows_off, &ctx->d_rows_meta, &ctx->d_rows_item_off, &ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi})
       if (b->p) cudaFree(b->p);
     for (PinBuf* b : {&ctx->h_stage, &ctx->h_out, &ctx->h_algo, &ctx->h_topn})
       if (b->p) cudaFreeHost(b->p);

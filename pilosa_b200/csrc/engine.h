@@ -92,6 +92,7 @@ struct pb200_ctx {
   uint32_t d_families_cap = 0;
   bool families_dirty = true;
   pb200::DevBuf d_slow_descs, d_ovf;
+  pb200::DevBuf d_rows, d_rows_off, d_rows_meta, d_rows_item_off;  // K11: serialised result rows (kernels_rows.cuh)
   bool dense_has_ovf = false;                      // the rows in d_dense carry Shift overflow words
   unsigned long long* dense_ovf_dev = nullptr;
   pb200::DevBuf d_batch, d_out, d_slow, d_temp, d_dense, d_dense_n, d_misc, d_topn, d_bsi;

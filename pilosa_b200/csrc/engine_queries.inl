@@ -118,39 +118,73 @@ int eval_one_shard(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uin
 
 }  // namespace
 
+namespace {
+
+// K11: evaluate one program over the shards and serialise every shard's row on the device
+// (kernels_rows.cuh). Leaves ctx->d_rows (packed streams) and ctx->d_rows_off
+// ([n_shards + 1] u64 stream offsets) filled, in stream order.
+int eval_rows_device(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards) {
+  BatchDev bd{};
+  TRY(eval_dense(ctx, prog, n_nodes, shards, n_shards, bd));
+  const uint32_t items = n_shards * kRowContainers;
+  TRY(ensure_dev(ctx, ctx->d_rows_meta, size_t(items) * 4));
+  TRY(ensure_dev(ctx, ctx->d_rows_item_off, size_t(items) * 8));
+  TRY(ensure_dev(ctx, ctx->d_rows_off, size_t(n_shards + 1) * 8));
+  // worst case: every container a bitmap, plus headers and a small overflow container per shard
+  TRY(ensure_dev(ctx, ctx->d_rows, size_t(items) * kBitmapBytes + size_t(n_shards) * (8 + 17 * 16 + 256)));
+  const uint64_t* dense = static_cast<const uint64_t*>(ctx->d_dense.p);
+  const uint32_t* dense_n = static_cast<const uint32_t*>(ctx->d_dense_n.p);
+  uint32_t* meta = static_cast<uint32_t*>(ctx->d_rows_meta.p);
+  unsigned long long* item_off = static_cast<unsigned long long*>(ctx->d_rows_item_off.p);
+  rows_classify_kernel<<<std::min<uint32_t>((items + 7) / 8, uint32_t(ctx->sm_count) * 8), 256, 0, ctx->stream>>>(dense, dense_n, items, meta);
+  rows_layout_kernel<<<1, 1024, 0, ctx->stream>>>(meta, dense_n, bd.shards, ctx->dense_has_ovf ? ctx->dense_ovf_dev : nullptr, n_shards,
+                                                  static_cast<uint8_t*>(ctx->d_rows.p), static_cast<unsigned long long*>(ctx->d_rows_off.p), item_off);
+  rows_emit_kernel<<<std::min<uint32_t>(items, uint32_t(ctx->sm_count) * 8), kRowsEmitThreads, 0, ctx->stream>>>(dense, meta, item_off, items,
+                                                                                                            static_cast<uint8_t*>(ctx->d_rows.p));
+  ctx->timing.launches += 3;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return PB200_OK;
+}
+
+int eval_shards_impl(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards,
+                     void* out, size_t cap, uint64_t* out_off, size_t* out_len) {
+  if (!out_len) return PB200_ERR_INVALID;
+  TRY(validate_shards(ctx, shards, n_shards));
+  *out_len = 0;
+  if (n_shards == 0) { if (out_off) out_off[0] = 0; return PB200_OK; }
+  if (n_shards > (1u << 24)) return fail(ctx, PB200_ERR_RANGE, "too many shards in one call");
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  timing_begin(ctx);
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  TRY(eval_rows_device(ctx, prog, n_nodes, shards, n_shards));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  std::vector<uint64_t> local_off;
+  uint64_t* off = out_off;
+  if (!off) { local_off.resize(size_t(n_shards) + 1); off = local_off.data(); }
+  CUDA_TRY(ctx, cudaMemcpyAsync(off, ctx->d_rows_off.p, size_t(n_shards + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  const size_t total = size_t(off[n_shards]);
+  *out_len = total;
+  ctx->timing.d2h_bytes += size_t(n_shards + 1) * 8;
+  if (out) {
+    if (cap < total) { finish_call(ctx); return fail(ctx, PB200_ERR_RANGE, "output buffer too small"); }
+    CUDA_TRY(ctx, cudaMemcpyAsync(out, ctx->d_rows.p, total, cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->timing.d2h_bytes += total;
+  }
+  return finish_call(ctx);
+}
+
+}  // namespace
+
 extern "C" int pb200_eval(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, void* out, size_t cap, size_t* out_len) {
   ENTER(ctx);
-  if (!out_len) return PB200_ERR_INVALID;
-  std::vector<uint64_t> words;
-  std::vector<uint32_t> ns;
-  uint64_t overflow = 0;
-  TRY(eval_one_shard(ctx, prog, n_nodes, shard, words, ns, &overflow));
-  // encode: containers optimize()d, keys shard*16 + c (fragment.go:629 OffsetRange re-keying)
-  std::vector<HostContainer> cs;
-  for (int c = 0; c < kRowContainers; c++) {
-    if (!ns[c]) continue;
-    HostContainer hc;
-    hc.key = shard * kRowContainers + c;
-    from_words(words.data() + size_t(c) * kBitmapWords, hc);
-    cs.push_back(std::move(hc));
-    cs.back().data = cs.back().owned.data();
-  }
-  if (overflow) {  // bits a Shift carried past the shard's last column: container key (shard+1)*16 (roaring.go:970-974)
-    std::vector<uint64_t> w(kBitmapWords, 0);
-    w[0] = overflow;
-    HostContainer hc;
-    hc.key = (shard + 1) * kRowContainers;
-    from_words(w.data(), hc);
-    cs.push_back(std::move(hc));
-    cs.back().data = cs.back().owned.data();
-  }
-  std::vector<uint8_t> bytes;
-  serialize_containers(cs, bytes);
-  *out_len = bytes.size();
-  if (!out) return PB200_OK;
-  if (cap < bytes.size()) return fail(ctx, PB200_ERR_RANGE, "output buffer too small");
-  std::memcpy(out, bytes.data(), bytes.size());
-  return PB200_OK;
+  return eval_shards_impl(ctx, prog, n_nodes, &shard, 1, out, cap, nullptr, out_len);
+}
+
+extern "C" int pb200_eval_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards,
+                                 void* out, size_t cap, uint64_t* out_off, size_t* out_len) {
+  ENTER(ctx);
+  return eval_shards_impl(ctx, prog, n_nodes, shards, n_shards, out, cap, out_off, out_len);
 }
 
 extern "C" int pb200_eval_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, uint64_t* out_cols, size_t cap, size_t* out_n) {

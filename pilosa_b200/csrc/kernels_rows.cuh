@@ -1,0 +1,221 @@
+// K11: bitmap-returning calls. The dense result rows of eval_dense
+// ([shard][16 containers][1024 words] + cardinalities) are turned ON THE DEVICE into what the
+// reference hands back per shard — a roaring bitmap whose containers carry the canonical type
+// of Container.optimize (roaring.go:2289-2338) — already laid out as the Pilosa roaring byte
+// stream (roaring.go:1044-1122: cookie, keyN, {key u64, type u16, n-1 u16}*, offset u32*,
+// payloads; run payload = u16 count + {start,last}*), so that the host copies compact bytes
+// instead of 128 KiB of words per shard and never re-scans them.
+//
+//   rows_classify_kernel  warp per container: count runs (bitmapCountRuns roaring.go:2249), pick type
+//   rows_layout_kernel    one CTA: stream sizes, exclusive scan over shards, headers, offsets
+//   rows_emit_kernel      CTA per container: array / run / bitmap payload
+#pragma once
+#include "layout.h"
+
+namespace pb200 {
+
+constexpr uint32_t kRowsEmitThreads = 256;
+
+__device__ __forceinline__ uint32_t rows_payload_bytes(uint32_t meta) {
+  const uint32_t type = meta & 3u, len = meta >> 2;
+  return type == kArray ? len * 2 : type == kRun ? 2 + len * 4 : type == kBitmap ? kBitmapBytes : 0;
+}
+
+// Container.optimize's choice from (n, runs): run if runs <= 2048 && runs <= n/2; else array if n < 4096;
+// else bitmap; n == 0 -> nil. Returned as type | len << 2.
+__device__ __forceinline__ uint32_t rows_pick_type(uint32_t n, uint32_t runs) {
+  if (n == 0) return kNil;
+  if (runs <= 2048 && runs <= n / 2) return kRun | (runs << 2);
+  if (n < 4096) return kArray | (n << 2);
+  return kBitmap | (uint32_t(kBitmapWords) << 2);
+}
+
+__global__ void __launch_bounds__(256) rows_classify_kernel(const uint64_t* __restrict__ dense, const uint32_t* __restrict__ dense_n,
+                                                            uint32_t n_items, uint32_t* __restrict__ meta) {
+  const uint32_t lane = threadIdx.x & 31, warps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t item = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; item < n_items; item += warps) {
+    const uint32_t n = dense_n[item];
+    if (n == 0 || n == 65536) {  // nil / full (one run)
+      if (lane == 0) meta[item] = rows_pick_type(n, n ? 1 : 0);
+      continue;
+    }
+    const uint4* src = reinterpret_cast<const uint4*>(dense + uint64_t(item) * kBitmapWords);
+    uint32_t starts = 0, carry = 0;  // carry: top bit of the word before this iteration's first word
+    #pragma unroll 4
+    for (int it = 0; it < 16; it++) {
+      const uint4 v = src[it * 32 + lane];
+      const uint64_t w0 = uint64_t(v.x) | (uint64_t(v.y) << 32), w1 = uint64_t(v.z) | (uint64_t(v.w) << 32);
+      const uint32_t top1 = uint32_t(w1 >> 63);
+      uint32_t prev = __shfl_up_sync(0xffffffffu, top1, 1);
+      if (lane == 0) prev = carry;
+      starts += __popcll(w0 & ~((w0 << 1) | prev)) + __popcll(w1 & ~((w1 << 1) | (w0 >> 63)));
+      carry = __shfl_sync(0xffffffffu, top1, 31);
+    }
+    #pragma unroll
+    for (int o = 16; o; o >>= 1) starts += __shfl_xor_sync(0xffffffffu, starts, o);
+    if (lane == 0) meta[item] = rows_pick_type(n, starts);
+  }
+}
+
+__device__ __forceinline__ void rows_put16(uint8_t* p, uint32_t v) { *reinterpret_cast<uint16_t*>(p) = uint16_t(v); }
+__device__ __forceinline__ void rows_put32(uint8_t* p, uint32_t v) { rows_put16(p, v); rows_put16(p + 2, v >> 16); }
+__device__ __forceinline__ void rows_put64(uint8_t* p, uint64_t v) { rows_put32(p, uint32_t(v)); rows_put32(p + 4, uint32_t(v >> 32)); }
+
+// One CTA of 1024 threads, a thread per shard (chunks of 1024 with a running total): stream
+// size = 8 + 16 * keyN + payloads; streams are packed back to back (all sizes are even, so
+// every field stays 2-byte aligned). `ovf` (optional) is the Shift overflow word per shard:
+// a 17th container under key (shard + 1) * 16, small enough to be written right here.
+__global__ void __launch_bounds__(1024) rows_layout_kernel(const uint32_t* __restrict__ meta, const uint32_t* __restrict__ dense_n,
+                                                           const uint64_t* __restrict__ shards, const unsigned long long* __restrict__ ovf,
+                                                           uint32_t n_shards, uint8_t* __restrict__ out, unsigned long long* __restrict__ shard_off,
+                                                           unsigned long long* __restrict__ item_off) {
+  __shared__ unsigned long long warp_tot[32];
+  __shared__ unsigned long long running;
+  const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) running = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < n_shards; base += 1024) {
+    const uint32_t s = base + threadIdx.x;
+    uint32_t keyn = 0, pay = 0, ometa = 0;
+    unsigned long long ow = 0;
+    if (s < n_shards) {
+      for (int c = 0; c < kRowContainers; c++) {
+        const uint32_t m = meta[s * kRowContainers + c];
+        if (m & 3u) { keyn++; pay += rows_payload_bytes(m); }
+      }
+      ow = ovf ? ovf[s] : 0ull;
+      if (ow) {
+        ometa = rows_pick_type(__popcll(ow), __popcll(ow & ~(ow << 1)));
+        keyn++; pay += rows_payload_bytes(ometa);
+      }
+    }
+    const unsigned long long size = s < n_shards ? 8ull + 16ull * keyn + pay : 0ull;
+    unsigned long long x = size;  // inclusive scan over the chunk
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) warp_tot[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+      unsigned long long t = warp_tot[lane], z = t;
+      #pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, z, o); if (lane >= o) z += y; }
+      warp_tot[lane] = z - t;  // exclusive
+    }
+    __syncthreads();
+    const unsigned long long start = running + warp_tot[wid] + x - size;
+    if (s < n_shards) {
+      shard_off[s] = start;
+      uint8_t* p = out + start;
+      rows_put32(p, 12348u);  // magic, storage version 0, no flags (roaring.go:1056)
+      rows_put32(p + 4, keyn);
+      uint8_t* hdr = p + 8;
+      uint8_t* offs = p + 8 + 12ull * keyn;
+      uint32_t off = 8 + 16 * keyn;
+      const uint64_t shard = shards[s];
+      for (int c = 0; c < kRowContainers; c++) {
+        const uint32_t item = s * kRowContainers + c, m = meta[item];
+        if (!(m & 3u)) continue;
+        rows_put64(hdr, shard * kRowContainers + c);
+        rows_put16(hdr + 8, m & 3u);
+        rows_put16(hdr + 10, dense_n[item] - 1);
+        hdr += 12;
+        rows_put32(offs, off); offs += 4;
+        item_off[item] = start + off;
+        off += rows_payload_bytes(m);
+      }
+      if (ow) {
+        rows_put64(hdr, (shard + 1) * kRowContainers);
+        rows_put16(hdr + 8, ometa & 3u);
+        rows_put16(hdr + 10, __popcll(ow) - 1);
+        rows_put32(offs, off);
+        uint8_t* q = p + off;
+        if ((ometa & 3u) == kArray) {
+          for (unsigned long long v = ow; v; v &= v - 1) { rows_put16(q, __ffsll((long long)v) - 1); q += 2; }
+        } else {  // run (a bitmap needs n >= 4096)
+          rows_put16(q, ometa >> 2); q += 2;
+          unsigned long long st = ow & ~(ow << 1), en = ow & ~(ow >> 1);
+          for (; st; st &= st - 1, en &= en - 1) { rows_put16(q, __ffsll((long long)st) - 1); rows_put16(q + 2, __ffsll((long long)en) - 1); q += 4; }
+        }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 1023) running += warp_tot[31] + x;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) shard_off[n_shards] = running;
+}
+
+// CTA per non-empty container; thread t owns words 4t .. 4t+3.
+__global__ void __launch_bounds__(kRowsEmitThreads) rows_emit_kernel(const uint64_t* __restrict__ dense, const uint32_t* __restrict__ meta,
+                                                                     const unsigned long long* __restrict__ item_off, uint32_t n_items,
+                                                                     uint8_t* __restrict__ out) {
+  __shared__ uint32_t warp_tot[kRowsEmitThreads / 32];
+  const uint32_t t = threadIdx.x, lane = t & 31, wid = t >> 5;
+  for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const uint32_t m = meta[item], type = m & 3u;
+    if (type == kNil) continue;
+    const uint64_t* w = dense + uint64_t(item) * kBitmapWords;
+    uint8_t* dst = out + item_off[item];
+    if (type == kBitmap) {
+      const uint64_t a = reinterpret_cast<uint64_t>(dst);
+      if ((a & 15) == 0) {
+        const uint4* s4 = reinterpret_cast<const uint4*>(w); uint4* d4 = reinterpret_cast<uint4*>(dst);
+        for (uint32_t i = t; i < kBitmapBytes / 16; i += kRowsEmitThreads) d4[i] = s4[i];
+      } else if ((a & 7) == 0) {
+        uint64_t* d8 = reinterpret_cast<uint64_t*>(dst);
+        for (uint32_t i = t; i < kBitmapWords; i += kRowsEmitThreads) d8[i] = w[i];
+      } else if ((a & 3) == 0) {
+        const uint32_t* s2 = reinterpret_cast<const uint32_t*>(w); uint32_t* d2 = reinterpret_cast<uint32_t*>(dst);
+        for (uint32_t i = t; i < kBitmapBytes / 4; i += kRowsEmitThreads) d2[i] = s2[i];
+      } else {
+        const uint16_t* s1 = reinterpret_cast<const uint16_t*>(w); uint16_t* d1 = reinterpret_cast<uint16_t*>(dst);
+        for (uint32_t i = t; i < kBitmapBytes / 2; i += kRowsEmitThreads) d1[i] = s1[i];
+      }
+      continue;
+    }
+    const ulonglong2 lo = reinterpret_cast<const ulonglong2*>(w)[2 * t], hi = reinterpret_cast<const ulonglong2*>(w)[2 * t + 1];
+    const uint64_t v[4] = {lo.x, lo.y, hi.x, hi.y};
+    uint64_t sm[4], em[4];  // array: sm = the words; run: run-start and run-end masks
+    uint32_t cnt = 0;       // array: bits; run: starts | ends << 16
+    if (type == kArray) {
+      #pragma unroll
+      for (int i = 0; i < 4; i++) { sm[i] = v[i]; cnt += __popcll(v[i]); }
+    } else {
+      uint64_t prev_top = t ? w[4 * t - 1] >> 63 : 0ull;
+      const uint64_t next_low = t + 1 < kRowsEmitThreads ? w[4 * t + 4] & 1ull : 0ull;
+      #pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const uint64_t nl = i < 3 ? v[i + 1] & 1ull : next_low;
+        sm[i] = v[i] & ~((v[i] << 1) | prev_top);
+        em[i] = v[i] & ~((v[i] >> 1) | (nl << 63));
+        prev_top = v[i] >> 63;
+        cnt += __popcll(sm[i]) + (uint32_t(__popcll(em[i])) << 16);
+      }
+    }
+    uint32_t x = cnt;  // block exclusive scan (both halves at once: at most 4096 / 2048 per half)
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    __syncthreads();  // warp_tot of the previous item is no longer read
+    if (lane == 31) warp_tot[wid] = x;
+    __syncthreads();
+    uint32_t pre = x - cnt;
+    for (uint32_t i = 0; i < wid; i++) pre += warp_tot[i];
+    if (type == kArray) {
+      uint16_t* d = reinterpret_cast<uint16_t*>(dst) + pre;
+      #pragma unroll
+      for (int i = 0; i < 4; i++)
+        for (uint64_t b = sm[i]; b; b &= b - 1) *d++ = uint16_t((4 * t + i) * 64 + __ffsll((long long)b) - 1);
+    } else {
+      if (t == 0) *reinterpret_cast<uint16_t*>(dst) = uint16_t(m >> 2);
+      uint16_t* ds = reinterpret_cast<uint16_t*>(dst + 2) + 2 * (pre & 0xffffu);
+      uint16_t* de = reinterpret_cast<uint16_t*>(dst + 2) + 2 * (pre >> 16) + 1;
+      #pragma unroll
+      for (int i = 0; i < 4; i++) {
+        for (uint64_t b = sm[i]; b; b &= b - 1) { *ds = uint16_t((4 * t + i) * 64 + __ffsll((long long)b) - 1); ds += 2; }
+        for (uint64_t b = em[i]; b; b &= b - 1) { *de = uint16_t((4 * t + i) * 64 + __ffsll((long long)b) - 1); de += 2; }
+      }
+    }
+  }
+}
+
+}  // namespace pb200

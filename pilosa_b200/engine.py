@@ -78,6 +78,7 @@ def load_library() -> C.CDLL:
         "pb200_count_pairs_noalloc": (i32, [vp, u32, vp, u32, vp, u32, vp]),
         "pb200_eval": (i32, [vp, np_, u32, u64, C.c_char_p, sz, C.POINTER(sz)]),
         "pb200_eval_columns": (i32, [vp, np_, u32, u64, u64p, sz, C.POINTER(sz)]),
+        "pb200_eval_shards": (i32, [vp, np_, u32, u64p, u32, vp, sz, u64p, C.POINTER(sz)]),
         "pb200_topn": (i32, [vp, u32, np_, u32, u32, u64p, sz, u64, u64, u32, u64p, u32, pp, sz, C.POINTER(sz)]),
         "pb200_topn_shard": (i32, [vp, u32, np_, u32, u32, u64p, sz, u64, u64, u64, pp, sz, C.POINTER(sz)]),
         "pb200_bsi_sum": (i32, [vp, u32, u32, np_, u32, u32, u64p, u32, i64p, u64p]),
@@ -116,6 +117,7 @@ class Engine:
             raise EngineError(rc, f"pb200_init(device={device}) failed: {self.lib.pb200_strerror(rc).decode()} "
                                   "(a CUDA device is required; there is no CPU fallback)")
         self._h = h
+        self._rows_buf = None
         self.device = device
 
     def close(self) -> None:
@@ -254,6 +256,21 @@ class Engine:
         buf = C.create_string_buffer(max(1, n.value))
         self._check(self.lib.pb200_eval(self._h, prog, len(prog), shard, buf, n.value, C.byref(n)))
         return buf.raw[: n.value]
+
+    def eval_roaring_shards(self, prog, shards: Sequence[int]) -> List[bytes]:
+        """One row segment (Pilosa roaring bytes) per shard, typed and serialised on the device."""
+        ns = len(shards)
+        if ns == 0:
+            return []
+        cap = ns * (131072 + 536)
+        if self._rows_buf is None or len(self._rows_buf) < cap:
+            self._rows_buf = bytearray(cap)
+        buf = (C.c_char * cap).from_buffer(self._rows_buf)
+        off = (C.c_uint64 * (ns + 1))()
+        n = C.c_size_t()
+        self._check(self.lib.pb200_eval_shards(self._h, prog, len(prog), u64_array(shards), ns, buf, cap, off, C.byref(n)))
+        mv = memoryview(self._rows_buf)
+        return [bytes(mv[off[i]: off[i + 1]]) for i in range(ns)]
 
     def eval_columns(self, prog, shard: int) -> List[int]:
         n = C.c_size_t()

@@ -193,6 +193,13 @@ class Executor:
             cols += self.be.eval_columns(prog, s)
         return cols
 
+    def row_segments(self, call: Call, shards: Sequence[int]) -> List[Tuple[int, bytes]]:
+        """executeBitmapCall (executor.go:604-652) before the coordinator's Row.Merge: one
+        (shard, Pilosa roaring bytes) segment per rank-local shard, in ascending shard order; the
+        result stays sharded across ranks (no exchange for bitmap-returning calls)."""
+        local = self.local_shards(sorted(shards))
+        return list(zip(local, self.be.eval_roaring_shards(self.program(call), local)))
+
     def sum(self, field_name: str, shards: Sequence[int], filter_call: Optional[Call] = None) -> Tuple[int, int]:  # executeSum :409
         f = self.fields[field_name]
         local = self.local_shards(shards)

@@ -133,6 +133,26 @@ def test_eval_columns_and_roaring(pair):
             assert g.be.eval_roaring(gp, s) == c.be.eval_roaring(cp, s), (repr(call), s)
 
 
+def test_row_segments_serialised_on_device(pair):
+    """pb200_eval_shards (K11): every shard's result typed by Container.optimize and serialised by the
+    device kernels must equal, byte for byte, the oracle's serialisation of the reference result."""
+    g, c, shards = pair
+    ex = Row("exists", 0)
+    calls = [CALLS[i] for i in (0, 2, 3, 4, 5, 6, 8, 9, 10, 14, 16, 18, 20, 22)]
+    calls += [Shift(ex, n=1), Shift(Union(Row("m", 1), ex), n=3), Xor(Shift(ex, n=2), Row("sp", 1)), Not(Row("exists", 0)),
+              g.row_range("v", abi.BSI_GT, 0), g.row_range("w", abi.BSI_BETWEEN, 10, 500), Intersect(Row("sp", 0), g.row_range("v", abi.BSI_LT, -5))]
+    kinds = set()
+    for call in calls:
+        got = g.row_segments(call, shards + [5, 0])   # duplicates: independent map jobs
+        exp = c.row_segments(call, shards + [5, 0])
+        assert got == exp, repr(call)
+        for _, b in got:
+            keyn = int.from_bytes(b[4:8], "little")
+            kinds |= {int.from_bytes(b[8 + 12 * k + 8: 8 + 12 * k + 10], "little") for k in range(keyn)}
+    assert kinds == {1, 2, 3}  # array, bitmap and run containers all came out of the device path
+    assert g.row_segments(calls[0], []) == []
+
+
 def test_shift_with_carry_out_of_the_shard(pair):
     """Shift (executor.go:1771, row.go:217, roaring.go:944): the bit leaving column 2^20-1 stays in the
     shard's segment under the next shard's container key and takes part in counts, set ops and the
@@ -249,8 +269,9 @@ def test_error_behaviour(pair):
         g.count(Intersect(), shards)
     with pytest.raises(EngineError, match="empty Difference"):
         g.count(Difference(), shards)
-    with pytest.raises(EngineError, match="too many Shift"):
+    with pytest.raises(EngineError, match="too many"):  # every step adds a temp-row leaf: the 32-leaf limit comes first
         g.count(Shift(Row("f", 1), n=65), shards)
+    assert g.count(Shift(Row("f", 1), n=31), shards) > 0
     with pytest.raises(EngineError):
         g.be.frag_load(g.family("f"), 0, b"\x00\x01\x02")
     with pytest.raises(EngineError, match="magic"):
