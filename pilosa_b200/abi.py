@@ -154,4 +154,6 @@ def flatten(call: Call, family_of: Callable[[str, str], int]) -> "C.Array[Node]"
 
 
 def u64_array(vals: Sequence[int]) -> "C.Array[C.c_uint64]":
+    if isinstance(vals, C.Array):  # prepared once by the caller (a 8192-entry list costs ~1 ms to convert)
+        return vals
     return (C.c_uint64 * len(vals))(*vals)

@@ -257,20 +257,25 @@ class Engine:
         self._check(self.lib.pb200_eval(self._h, prog, len(prog), shard, buf, n.value, C.byref(n)))
         return buf.raw[: n.value]
 
-    def eval_roaring_shards(self, prog, shards: Sequence[int]) -> List[bytes]:
-        """One row segment (Pilosa roaring bytes) per shard, typed and serialised on the device."""
+    def eval_shards_raw(self, prog, shards: Sequence[int]):
+        """pb200_eval_shards into a reused host buffer: (buffer, offsets[n_shards + 1])."""
         ns = len(shards)
-        if ns == 0:
-            return []
-        cap = ns * (131072 + 536)
+        cap = max(1, ns) * (131072 + 536)
         if self._rows_buf is None or len(self._rows_buf) < cap:
             self._rows_buf = bytearray(cap)
         buf = (C.c_char * cap).from_buffer(self._rows_buf)
         off = (C.c_uint64 * (ns + 1))()
         n = C.c_size_t()
-        self._check(self.lib.pb200_eval_shards(self._h, prog, len(prog), u64_array(shards), ns, buf, cap, off, C.byref(n)))
-        mv = memoryview(self._rows_buf)
-        return [bytes(mv[off[i]: off[i + 1]]) for i in range(ns)]
+        self._check(self.lib.pb200_eval_shards(self._h, prog, len(prog), u64_array(shards) if ns else None, ns, buf, cap, off, C.byref(n)))
+        return self._rows_buf, off
+
+    def eval_roaring_shards(self, prog, shards: Sequence[int]) -> List[bytes]:
+        """One row segment (Pilosa roaring bytes) per shard, typed and serialised on the device."""
+        if not shards:
+            return []
+        buf, off = self.eval_shards_raw(prog, shards)
+        mv = memoryview(buf)
+        return [bytes(mv[off[i]: off[i + 1]]) for i in range(len(shards))]
 
     def eval_columns(self, prog, shard: int) -> List[int]:
         n = C.c_size_t()
