@@ -591,7 +591,7 @@ uint32_t resident_ctas(pb200_ctx* ctx, int slot, K kernel, int block, size_t dyn
   }
   return uint32_t(ctx->sm_count) * uint32_t(ctx->occ[slot]);
 }
-enum { OCC_FAST = 0, OCC_STAGED, OCC_RANGE, OCC_SUM, OCC_MM, OCC_TOPN };
+enum { OCC_FAST = 0, OCC_STAGED, OCC_SUM, OCC_MM, OCC_TOPN };
 
 // Launches the fast + staged kernels for `n_queries` programs starting at `progs`.
 int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards, bool staging,

@@ -97,7 +97,9 @@ struct pb200_ctx {
   unsigned long long* dense_ovf_dev = nullptr;
   pb200::DevBuf d_batch, d_out, d_slow, d_temp, d_dense, d_dense_n, d_misc, d_topn, d_bsi;
   pb200::PinBuf h_stage, h_out, h_algo, h_topn;
-  bool mm_attr_set = false, topn_attr_set = false;
+  bool topn_attr_set = false, sum_attr_set = false, mm_attr_set = false;
+  uint32_t range_attr_set = 0;  // per instantiation of bsi_range_pipe_kernel
+  int occ_range[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   int occ[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // resident CTAs per SM of each persistent kernel (occupancy calculator)
   const uint64_t* dense_shards_dev = nullptr;  // shard list of the source rows currently in d_dense (TopN pass 1 -> 2)
   pb200::CountSlot slots[2];     // split Count batches in flight (count_begin / count_end), oldest first

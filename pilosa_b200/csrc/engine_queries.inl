@@ -6,6 +6,23 @@ uint8_t* temp_slot(pb200_ctx* ctx, uint32_t slot, uint32_t n_shards) {
   return static_cast<uint8_t*>(ctx->d_temp.p) + size_t(slot) * n_shards * kRowContainers * kBitmapBytes;
 }
 
+template <class K>
+int launch_range_pipe(pb200_ctx* ctx, int slot, K kernel, const BsiParams& p, uint32_t items) {
+  constexpr int smem = (kPipeStages + 1) * kBitmapBytes;
+  if (!(ctx->range_attr_set & (1u << slot))) {
+    CUDA_TRY(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ctx->range_attr_set |= 1u << slot;
+  }
+  if (ctx->occ_range[slot] == 0) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kPipeThreads, smem) != cudaSuccess || n < 1) n = 1;
+    ctx->occ_range[slot] = n;
+  }
+  const uint32_t grid = std::min<uint32_t>(items, uint32_t(ctx->sm_count) * uint32_t(ctx->occ_range[slot]));
+  kernel<<<grid, kPipeThreads, smem, ctx->stream>>>(p);
+  return PB200_OK;
+}
+
 int launch_bsi_range(pb200_ctx* ctx, const BatchDev& bd, const pb200_node& nd, uint32_t n_shards, uint8_t* dense_out,
                      unsigned long long* count_out = nullptr, uint32_t count_sstride = 0) {
   BsiParams p{};
@@ -16,8 +33,22 @@ int launch_bsi_range(pb200_ctx* ctx, const BatchDev& bd, const pb200_node& nd, u
   p.dense_out = dense_out;
   p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + ctx->algo_off);
   const uint32_t items = n_shards * kRowContainers;
-  const uint32_t grid = std::min<uint32_t>(items, resident_ctas(ctx, OCC_RANGE, bsi_range_kernel, kBsiThreads, kRingBytes));
-  bsi_range_kernel<<<grid, kBsiThreads, kRingBytes, ctx->stream>>>(p);
+  {
+    const RangePlan plan = range_plan(p.bsi_op, p.a, p.b);
+    int rc = PB200_ERR_INVALID;
+#define PB200_RANGE_CASE(slot, K0, K1, CB) \
+    if (plan.k0 == K0 && plan.k1 == K1 && plan.combine == CB) rc = launch_range_pipe(ctx, slot, bsi_range_kernel<K0, K1, CB>, p, items);
+    PB200_RANGE_CASE(0, M_EQ, M_NONE, 0)
+    PB200_RANGE_CASE(1, M_EQ, M_NONE, 1)
+    PB200_RANGE_CASE(2, M_LTU, M_NONE, 2)
+    PB200_RANGE_CASE(3, M_LTU, M_NONE, 3)
+    PB200_RANGE_CASE(4, M_GTU, M_NONE, 0)
+    PB200_RANGE_CASE(5, M_BETWEENU, M_NONE, 0)
+    PB200_RANGE_CASE(6, M_LTU, M_LTU, 4)
+    PB200_RANGE_CASE(7, M_NONE, M_NONE, 5)
+#undef PB200_RANGE_CASE
+    if (rc != PB200_OK) return rc == PB200_ERR_INVALID ? fail(ctx, rc, "unknown BSI range op") : rc;
+  }
   ctx->timing.launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   return PB200_OK;
@@ -400,6 +431,7 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
       TRY(eval_dense(ctx, src_prog, n_src_nodes, shards, n_shards, bd));
       ctx->dense_shards_dev = bd.shards;
     }
+    if (trace) { cudaStreamSynchronize(ctx->stream); lap("  rank tables + src"); }
     const uint64_t total = off[n_shards];
     const size_t n_counts = n_ids ? size_t(n_shards) * n_ids : size_t(total);
     // d_topn: [cand_off u64 x ns][rank_n u32 x ns][ptrs x ns][ids u64 x n_ids] ; counts in d_bsi
@@ -453,6 +485,7 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
       CUDA_TRY(ctx, cudaGetLastError());
     }
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    if (trace) { cudaStreamSynchronize(ctx->stream); lap("  count kernel"); }
     uint32_t* h_counts = static_cast<uint32_t*>(ctx->h_out.p);
     uint32_t* h_dn = h_counts + std::max<size_t>(n_counts, 1);
     if (n_counts) CUDA_TRY(ctx, cudaMemcpyAsync(h_counts, d_counts, n_counts * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -602,20 +635,27 @@ int bsi_minmax_impl(pb200_ctx* ctx, pb200_family fam, uint32_t bit_depth, const 
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
   BsiParams p; BatchDev bd{};
   TRY(bsi_prepare(ctx, fam, bit_depth, filt, nf, shards, n_shards, p, bd));
-  TRY(ensure_dev(ctx, ctx->d_bsi, size_t(n_shards) * 16));
+  const uint32_t items = n_shards * kRowContainers;
+  TRY(ensure_dev(ctx, ctx->d_bsi, size_t(n_shards) * 16 + size_t(items) * sizeof(MmRec)));
   p.is_max = is_max ? 1 : 0;
   p.mm_val = static_cast<long long*>(ctx->d_bsi.p);
   p.mm_count = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_bsi.p) + size_t(n_shards) * 8);
-  const int smem = kRowContainers * kBitmapBytes;
-  if (!ctx->mm_attr_set) { CUDA_TRY(ctx, cudaFuncSetAttribute(bsi_minmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); ctx->mm_attr_set = true; }
-  const uint32_t grid = std::min<uint32_t>(n_shards, resident_ctas(ctx, OCC_MM, bsi_minmax_kernel, kMmThreads, smem));
-  bsi_minmax_kernel<<<grid, kMmThreads, smem, ctx->stream>>>(p);
-  ctx->timing.launches++;
+  MmRec* recs = reinterpret_cast<MmRec*>(static_cast<uint8_t*>(ctx->d_bsi.p) + size_t(n_shards) * 16);
+  {
+    constexpr int smem = (kPipeStages + 1) * kBitmapBytes;
+    if (!ctx->mm_attr_set) { CUDA_TRY(ctx, cudaFuncSetAttribute(bsi_minmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); ctx->mm_attr_set = true; }
+    const uint32_t grid = std::min<uint32_t>(items, resident_ctas(ctx, OCC_MM, bsi_minmax_kernel, kPipeThreads, smem));
+    bsi_minmax_kernel<<<grid, kPipeThreads, smem, ctx->stream>>>(p, recs);
+  }
+  bsi_minmax_combine_kernel<<<(n_shards + 127) / 128, 128, 0, ctx->stream>>>(p, recs);
+  ctx->timing.launches += 2;
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(vals.data(), p.mm_val, size_t(n_shards) * 8, cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(counts.data(), p.mm_count, size_t(n_shards) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  TRY(ensure_pin(ctx, ctx->h_out, size_t(n_shards) * 16));  // values then counts, contiguous on the device too
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_out.p, p.mm_val, size_t(n_shards) * 16, cudaMemcpyDeviceToHost, ctx->stream));
   TRY(finish_call(ctx));
+  std::memcpy(vals.data(), ctx->h_out.p, size_t(n_shards) * 8);
+  std::memcpy(counts.data(), static_cast<const uint8_t*>(ctx->h_out.p) + size_t(n_shards) * 8, size_t(n_shards) * 8);
   ctx->timing.d2h_bytes += size_t(n_shards) * 16;
   return PB200_OK;
 }
@@ -655,8 +695,12 @@ extern "C" int pb200_bsi_sum(pb200_ctx* ctx, pb200_family bsi_family, uint32_t b
   p.strict = (flags & PB200_SUM_STRICT) ? 1 : 0;
   p.sum_acc = static_cast<unsigned long long*>(ctx->d_bsi.p);
   const uint32_t items = n_shards * kRowContainers;
-  const uint32_t grid = std::min<uint32_t>(items, resident_ctas(ctx, OCC_SUM, bsi_sum_kernel, kBsiThreads, kRingBytes));
-  bsi_sum_kernel<<<grid, kBsiThreads, kRingBytes, ctx->stream>>>(p);
+  {
+    constexpr int smem = (kPipeStages + 1) * kBitmapBytes;
+    if (!ctx->sum_attr_set) { CUDA_TRY(ctx, cudaFuncSetAttribute(bsi_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); ctx->sum_attr_set = true; }
+    const uint32_t grid = std::min<uint32_t>(items, resident_ctas(ctx, OCC_SUM, bsi_sum_kernel, kPipeThreads, smem));
+    bsi_sum_kernel<<<grid, kPipeThreads, smem, ctx->stream>>>(p);
+  }
   ctx->timing.launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));

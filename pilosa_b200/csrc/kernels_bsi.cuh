@@ -9,62 +9,6 @@
 
 namespace pb200 {
 
-// ---------------------------------------------------------------------------------------
-// Plane ring: the container columns a BSI kernel consumes one after the other (E, S, filter,
-// B_i ...) are streamed through a ring of kRingDepth 8 KiB shared-memory slots by the bulk
-// copy engine. One thread issues cp.async.bulk for plane q + kRingDepth as soon as plane q
-// has been consumed, so kRingDepth x 8 KiB per CTA are always in flight however many
-// registers the comparator state needs. Bitmap containers take the TMA path; array / run
-// containers are staged into their slot by the CTA; empty / full containers are constants.
-// ---------------------------------------------------------------------------------------
-constexpr int kRingDepth = 4;
-constexpr int kRingBytes = kRingDepth * kBitmapBytes;
-
-struct PlaneRing {
-  uint8_t* ring;     // kRingDepth x 8 KiB, 128 B aligned
-  uint64_t* full;    // kRingDepth mbarriers (count 1 + transaction bytes)
-  uint32_t phase;    // expected parity per slot (bit s), tracked identically by every thread
-
-  __device__ __forceinline__ static bool by_tma(const ContainerDesc& d) { return d.n != 0 && desc_type(d) == kBitmap; }
-
-  // thread 0 only: start the copy of plane sequence number q
-  __device__ __forceinline__ void issue(const ContainerDesc& d, uint32_t q) {
-    if (!by_tma(d)) return;
-    const uint32_t slot = q % kRingDepth;
-    fence_proxy_async();  // earlier generic-proxy traffic on this slot is ordered before the async write
-    mbar_arrive_expect_tx(&full[slot], kBitmapBytes);
-    tma_load_1d(ring + slot * kBitmapBytes, reinterpret_cast<const void*>(d.addr), kBitmapBytes, &full[slot]);
-  }
-
-  // whole CTA: this thread's PER chunks of plane q. The caller must __syncthreads() before
-  // thread 0 re-issues into the same slot.
-  template <int NT, int PER>
-  __device__ __forceinline__ void take(const ContainerDesc& d, uint32_t q, int tid, uint4 (&v)[PER]) {
-    const uint32_t slot = q % kRingDepth;
-    uint4* win = reinterpret_cast<uint4*>(ring + slot * kBitmapBytes);
-    if (d.n == 0) {
-#pragma unroll
-      for (int k = 0; k < PER; k++) v[k] = make_uint4(0, 0, 0, 0);
-    } else if (desc_type(d) == kBitmap) {
-      mbar_wait(&full[slot], (phase >> slot) & 1u);
-      phase ^= 1u << slot;
-#pragma unroll
-      for (int k = 0; k < PER; k++) v[k] = win[tid + k * NT];
-    } else if (d.n == kFullN) {
-#pragma unroll
-      for (int k = 0; k < PER; k++) v[k] = make_uint4(~0u, ~0u, ~0u, ~0u);
-    } else {
-      for (int j = tid; j < kBitmapWords / 2; j += NT) win[j] = make_uint4(0, 0, 0, 0);
-      __syncthreads();
-      stage_container(d, reinterpret_cast<uint32_t*>(win), 0, kBitmapWords, tid, NT);
-      __syncthreads();
-#pragma unroll
-      for (int k = 0; k < PER; k++) v[k] = win[tid + k * NT];
-    }
-  }
-};
-
-constexpr int kBsiThreads = 256;  // one CTA per (shard, container column): 2 x uint4 per thread
 constexpr int kMaxDepth = 64;
 
 struct BsiParams {
@@ -107,33 +51,6 @@ __device__ __forceinline__ ContainerDesc bsi_row_desc(const FragDev& f, uint64_t
   return f.rows[idx * kRowContainers + c];
 }
 
-// Block-cooperative load of a whole container column as words: thread t receives uint4 #t
-// and #(t + nthreads) ... of the 512 uint4. Array/run containers are staged through the
-// shared window `win` (8 KiB). All threads of the CTA must call with the same descriptor.
-template <int NT, int PER>
-__device__ __forceinline__ void load_column(const ContainerDesc& d, uint64_t* win, int tid, uint4 (&v)[PER]) {
-  static_assert(NT * PER == kBitmapWords / 2, "column = 512 uint4");
-  if (d.n == 0) {
-#pragma unroll
-    for (int k = 0; k < PER; k++) v[k] = make_uint4(0, 0, 0, 0);
-  } else if (desc_type(d) == kBitmap) {
-    const uint4* ptr = reinterpret_cast<const uint4*>(d.addr) + tid;
-#pragma unroll
-    for (int k = 0; k < PER; k++) v[k] = ldg128_stream(ptr + k * NT);
-  } else if (d.n == kFullN) {
-#pragma unroll
-    for (int k = 0; k < PER; k++) v[k] = make_uint4(~0u, ~0u, ~0u, ~0u);
-  } else {
-    __syncthreads();  // window free
-    for (int j = tid; j < kBitmapWords / 2; j += NT) reinterpret_cast<uint4*>(win)[j] = make_uint4(0, 0, 0, 0);
-    __syncthreads();
-    stage_container(d, reinterpret_cast<uint32_t*>(win), 0, kBitmapWords, tid, NT);
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < PER; k++) v[k] = reinterpret_cast<const uint4*>(win)[tid + k * NT];
-  }
-}
-
 __device__ __forceinline__ ContainerDesc filter_desc(const BsiParams& p, uint32_t s, uint32_t c) {
   EvalParams ep{};
   ep.families = p.families; ep.n_families = 0xffffffffu; ep.shards = p.shards; ep.n_shards = p.n_shards; ep.temp_base = p.temp_base;
@@ -147,20 +64,24 @@ __device__ __forceinline__ ContainerDesc filter_desc(const BsiParams& p, uint32_
 // ---------------------------------------------------------------------------------------
 enum MachKind : int { M_NONE = 0, M_EQ, M_LTU, M_GTU, M_BETWEENU };
 
-template <int PER>
+// `kind` is a compile-time constant in the pipe kernel (KIND != M_DYNAMIC), so the unused keep rows
+// and branches disappear and the comparator fits 3 CTAs per SM; M_DYNAMIC keeps it a run-time field.
+constexpr int M_DYNAMIC = -1;
+template <int PER, int KIND = M_DYNAMIC>
 struct Mach {
-  int kind = M_NONE;
+  int kind_rt = M_NONE;
   unsigned long long p1 = 0, p2 = 0;
   bool allow_eq = false, leading = true, done = false;
   uint4 f[PER], k1[PER], k2[PER];
 
   __device__ __forceinline__ void init(int kd, const uint4 (&filter)[PER], unsigned long long a, unsigned long long b, bool eq) {
-    kind = kd; p1 = a; p2 = b; allow_eq = eq; leading = true; done = false;
+    kind_rt = kd; p1 = a; p2 = b; allow_eq = eq; leading = true; done = false;
 #pragma unroll
     for (int k = 0; k < PER; k++) { f[k] = filter[k]; k1[k] = make_uint4(0, 0, 0, 0); k2[k] = make_uint4(0, 0, 0, 0); }
   }
   // one plane, MSB -> LSB; on completion the result is in f[]
   __device__ __forceinline__ void step(int i, const uint4 (&row)[PER]) {
+    const int kind = KIND == M_DYNAMIC ? kind_rt : KIND;
     if (kind == M_NONE || done) return;
     const bool bit1 = (p1 >> i) & 1ull;
     if (kind == M_EQ) {
@@ -238,372 +159,483 @@ struct Mach {
 
 __device__ __forceinline__ unsigned long long uabs64(long long v) { return v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v; }
 
-__global__ void __launch_bounds__(kBsiThreads) bsi_range_kernel(BsiParams p) {
-  constexpr int PER = 2;
-  extern __shared__ __align__(128) uint8_t s_ring[];
-  __shared__ __align__(8) uint64_t s_full[kRingDepth];
-  __shared__ ContainerDesc s_pd[kMaxDepth + 2];  // planes in consumption order: E, S, B_{d-1} .. B_0
-  const int tid = threadIdx.x;
-  const uint32_t n_items = p.n_shards * kRowContainers;
-  unsigned long long bytes_acc = 0;
-  PlaneRing pr;
-  pr.ring = s_ring; pr.full = s_full; pr.phase = 0;
-  if (tid == 0) {
-    for (int i = 0; i < kRingDepth; i++) mbar_init(&s_full[i], 1);
-    mbar_fence_init();
+// ---------------------------------------------------------------------------------------
+// K9: Min / Max (fragment.go:1145-1168 min, :1189-1210 max, :1171-1186 minUnsigned,
+// :1213-1225 maxUnsigned). The reference descends the bit planes MSB -> LSB over the whole
+// shard, one Row op + Count per plane. (value, count) of an extreme is a plain set function,
+// so it decomposes: every SLICE of columns (what one consumer warp holds of a container
+// column: 8192 columns) finds its own extreme and how many columns attain it, and slices
+// combine by "better value wins, equal values add their counts". The per-plane decision is
+// therefore a warp vote instead of a block-wide reduction over the shard. Both searches the
+// sign split can ask for run side by side:
+//   A = maxUnsigned over {negatives for Min | positives for Max}   (wins if any such column exists)
+//   B = minUnsigned over {positives for Min | negatives for Max}
+// bsi_minmax_kernel writes one record per (shard, container column); bsi_minmax_combine_kernel
+// folds the 16 records of a shard.
+// ---------------------------------------------------------------------------------------
+struct MmRec { unsigned long long magA, cntA, magB, cntB; };
+
+__device__ __forceinline__ bool mm_nz(const uint4& v) { return (v.x | v.y | v.z | v.w) != 0; }
+
+// One thread per shard: fold the 16 column records, apply the sign rule of fragment.min / max.
+__global__ void bsi_minmax_combine_kernel(BsiParams p, const MmRec* __restrict__ recs) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= p.n_shards) return;
+  MmRec r{0, 0, ~0ull, 0};
+  for (int c = 0; c < kRowContainers; c++) {
+    const MmRec x = recs[s * kRowContainers + c];
+    if (x.cntA) { if (x.magA > r.magA || !r.cntA) { r.magA = x.magA; r.cntA = x.cntA; } else if (x.magA == r.magA) r.cntA += x.cntA; }
+    if (x.cntB) { if (x.magB < r.magB || !r.cntB) { r.magB = x.magB; r.cntB = x.cntB; } else if (x.magB == r.magB) r.cntB += x.cntB; }
   }
-  __syncthreads();
-  uint32_t q0 = 0;  // planes consumed so far by this CTA (ring sequence numbers run across items)
-  const uint32_t n_planes = p.bsi_op == PB200_BSI_NOTNULL ? 1u : p.bit_depth + 2u;
-
-  for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
-    const uint32_t s = item >> 4, c = item & 15;
-    uint4* out = p.dense_out ? reinterpret_cast<uint4*>(p.dense_out + uint64_t(item) * kBitmapBytes) : nullptr;
-    uint32_t cnt = 0;
-    const FamilyDev fam = p.families[p.family];
-    const uint64_t shard = p.shards[s];
-    FragDev f{};
-    if (shard < fam.cap) f = fam.frags[shard];
-    if (tid < int(n_planes)) {
-      const uint64_t row = tid < 2 ? uint64_t(tid) : uint64_t(2 + (p.bit_depth - 1 - (tid - 2)));
-      const ContainerDesc d = bsi_row_desc(f, row, c);
-      s_pd[tid] = d;
-      bytes_acc += desc_algo_bytes(d);
-    }
-    __syncthreads();
-    if (tid == 0)
-      for (uint32_t j = 0; j < n_planes && j < uint32_t(kRingDepth); j++) pr.issue(s_pd[j], q0 + j);
-
-    uint4 E[PER], S[PER], res[PER];
-    pr.take<kBsiThreads, PER>(s_pd[0], q0 + 0, tid, E);
-    __syncthreads();
-    if (tid == 0 && uint32_t(kRingDepth) < n_planes) pr.issue(s_pd[kRingDepth], q0 + kRingDepth);
-    if (p.bsi_op == PB200_BSI_NOTNULL) {
-#pragma unroll
-      for (int k = 0; k < PER; k++) { if (out) out[tid + k * kBsiThreads] = E[k]; cnt += popc128(E[k]); }
-      if (p.count_out) {
-        cnt = warp_sum(cnt);
-        if ((tid & 31) == 0 && cnt) atomicAdd(p.count_out + uint64_t(s) * p.count_sstride, (unsigned long long)cnt);
-      }
-      q0 += n_planes;
-      continue;
-    }
-    pr.take<kBsiThreads, PER>(s_pd[1], q0 + 1, tid, S);
-    __syncthreads();
-    if (tid == 0 && 1u + kRingDepth < n_planes) pr.issue(s_pd[1 + kRingDepth], q0 + 1 + kRingDepth);
-    uint4 pos[PER], neg[PER];
-#pragma unroll
-    for (int k = 0; k < PER; k++) { pos[k] = andnot128(E[k], S[k]); neg[k] = and128(E[k], S[k]); }
-
-    Mach<PER> m0, m1;
-    int combine = 0;  // 0: m0 ; 1: E \ m0 ; 2: S | m0 ; 3: pos | m0 ; 4: m0 | m1
-    const long long a = p.a, b = p.b;
-    const unsigned long long ua = uabs64(a), ub = uabs64(b);
-    switch (p.bsi_op) {
-      case PB200_BSI_EQ: m0.init(M_EQ, a < 0 ? neg : pos, ua, 0, false); break;
-      case PB200_BSI_NEQ: m0.init(M_EQ, a < 0 ? neg : pos, ua, 0, false); combine = 1; break;
-      case PB200_BSI_LT: case PB200_BSI_LTE: {
-        const bool eq = p.bsi_op == PB200_BSI_LTE;
-        if ((a >= 0 && eq) || (a >= -1 && !eq)) { m0.init(M_LTU, pos, ua, 0, eq); combine = 2; }
-        else m0.init(M_GTU, neg, ua, 0, eq);
-        break;
-      }
-      case PB200_BSI_GT: case PB200_BSI_GTE: {
-        const bool eq = p.bsi_op == PB200_BSI_GTE;
-        if ((a >= 0 && eq) || (a >= -1 && !eq)) m0.init(M_GTU, pos, ua, 0, eq);
-        else { m0.init(M_LTU, neg, ua, 0, eq); combine = 3; }
-        break;
-      }
-      default:  // BETWEEN
-        if (a >= 0) m0.init(M_BETWEENU, pos, ua, ub, true);
-        else if (b < 0) m0.init(M_BETWEENU, neg, ub, ua, true);
-        else { m0.init(M_LTU, pos, ub, 0, true); m1.init(M_LTU, neg, ua, 0, true); combine = 4; }
-        break;
-    }
-    // magnitude planes MSB -> LSB through the ring
-    for (int i = int(p.bit_depth) - 1; i >= 0; i--) {
-      const uint32_t j = 2u + uint32_t(int(p.bit_depth) - 1 - i);
-      uint4 row[PER];
-      pr.take<kBsiThreads, PER>(s_pd[j], q0 + j, tid, row);
-      __syncthreads();  // every thread has read slot (q0 + j) % depth: it may be refilled
-      if (tid == 0 && j + kRingDepth < n_planes) pr.issue(s_pd[j + kRingDepth], q0 + j + kRingDepth);
-      m0.step(i, row);
-      m1.step(i, row);
-    }
-    q0 += n_planes;
-#pragma unroll
-    for (int k = 0; k < PER; k++) {
-      switch (combine) {
-        case 0: res[k] = m0.f[k]; break;
-        case 1: res[k] = andnot128(E[k], m0.f[k]); break;
-        case 2: res[k] = or128(S[k], m0.f[k]); break;
-        case 3: res[k] = or128(pos[k], m0.f[k]); break;
-        default: res[k] = or128(m0.f[k], m1.f[k]); break;
-      }
-      if (out) out[tid + k * kBsiThreads] = res[k];
-      cnt += popc128(res[k]);
-    }
-    if (p.count_out) {
-      cnt = warp_sum(cnt);
-      if ((tid & 31) == 0 && cnt) atomicAdd(p.count_out + uint64_t(s) * p.count_sstride, (unsigned long long)cnt);
-    }
-    __syncthreads();  // s_pd is rewritten by the next item
+  long long val = 0;
+  unsigned long long count = 0;
+  if (p.bit_depth != 0) {  // with no planes the reference's loops never assign count (fragment.go:1171,1213): (0, 0)
+    if (r.cntA) { val = p.is_max ? (long long)r.magA : -(long long)r.magA; count = r.cntA; }
+    else if (r.cntB) { val = p.is_max ? -(long long)r.magB : (long long)r.magB; count = r.cntB; }
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) bytes_acc += __shfl_xor_sync(0xffffffffu, bytes_acc, o);
-  if ((tid & 31) == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+  p.mm_val[s] = val;
+  p.mm_count[s] = count;
 }
 
 // ---------------------------------------------------------------------------------------
+// Plane pipe (K8 / K9 / K10). The container columns a BSI kernel consumes one after the other
+// (E, S, filter, B_i ...) are 8 KiB contiguous blocks, so they are moved by the bulk copy
+// engine (TMA, SASS UBLKCP) instead of by the threads that compute on them. One PRODUCER warp
+// issues the cp.async.bulk copies of an item's planes into a ring of kPipeStages 8 KiB
+// slots, gated per slot by an `empty` mbarrier; eight CONSUMER warps wait on the slot's
+// `full` mbarrier (transaction bytes), take their 2 x 16 B, and release the slot with one
+// mbarrier arrive per warp. No block-wide barrier separates planes, so the warps drift by
+// up to kPipeStages planes and kPipeStages x 8 KiB per CTA stay in flight whatever the
+// consumers' register footprint is. Items with an array / run plane (sparse BSI data) take
+// a synchronous path among the consumers (named barrier 1).
+// ---------------------------------------------------------------------------------------
+constexpr int kPipeStages = 7;  // 3 CTAs / SM: 3 x (7 slots + 1 staging window) x 8 KiB + static < 227 KiB
+constexpr int kPipeConsumers = 256;                 // 8 warps x 32 lanes x 2 uint4 = 8 KiB
+constexpr int kPipeThreads = kPipeConsumers + 32;   // + the producer warp
+
+__device__ __forceinline__ void consumers_sync() { asm volatile("bar.sync 1, %0;" :: "n"(kPipeConsumers) : "memory"); }
+
+struct PlanePipe {
+  uint8_t* ring;
+  uint64_t* full;    // [kPipeStages], count 1 + tx bytes
+  uint64_t* empty;   // [kPipeStages], count = consumer warps
+  uint32_t seq = 0;  // TMA planes issued (producer) / taken (consumer) so far; both sides count alike
+
+  __device__ __forceinline__ static bool by_tma(const ContainerDesc& d) { return d.n != 0 && desc_type(d) == kBitmap; }
+
+  __device__ __forceinline__ void init(int tid) {
+    if (tid == 0) {
+      for (int i = 0; i < kPipeStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], kPipeConsumers / 32); }
+      mbar_fence_init();
+    }
+  }
+  // producer lane: copy plane d into the next slot once its previous contents have been released
+  __device__ __forceinline__ void produce(const ContainerDesc& d) {
+    if (!by_tma(d)) return;
+    const uint32_t slot = seq % kPipeStages, use = seq / kPipeStages;
+    if (use) mbar_wait(&empty[slot], (use - 1) & 1u);
+    fence_proxy_async();
+    mbar_arrive_expect_tx(&full[slot], kBitmapBytes);
+    tma_load_1d(ring + slot * kBitmapBytes, reinterpret_cast<const void*>(d.addr), kBitmapBytes, &full[slot]);
+    seq++;
+  }
+  // consumer thread t (0..255): its two chunks of a streamable plane
+  __device__ __forceinline__ void take(const ContainerDesc& d, int t, uint4 (&v)[2]) {
+    if (d.n == 0) { v[0] = v[1] = make_uint4(0, 0, 0, 0); return; }
+    if (desc_type(d) != kBitmap) { v[0] = v[1] = make_uint4(~0u, ~0u, ~0u, ~0u); return; }  // full run
+    const uint32_t slot = seq % kPipeStages, use = seq / kPipeStages;
+    mbar_wait(&full[slot], use & 1u);
+    const uint4* win = reinterpret_cast<const uint4*>(ring + slot * kBitmapBytes);
+    v[0] = win[t]; v[1] = win[t + kPipeConsumers];
+    __syncwarp();
+    if ((t & 31) == 0) mbar_arrive(&empty[slot]);
+    seq++;
+  }
+};
+
+// any plane on the synchronous path (consumers only): array / run containers are expanded into `win` first
+__device__ __forceinline__ void pipe_plane_sync(const ContainerDesc& d, int t, uint64_t* win, uint4 (&v)[2]) {
+  if (d.n == 0) { v[0] = v[1] = make_uint4(0, 0, 0, 0); return; }
+  if (d.n == kFullN) { v[0] = v[1] = make_uint4(~0u, ~0u, ~0u, ~0u); return; }
+  if (desc_type(d) == kBitmap) {
+    v[0] = ldg128_stream(reinterpret_cast<const uint4*>(d.addr) + t);
+    v[1] = ldg128_stream(reinterpret_cast<const uint4*>(d.addr) + t + kPipeConsumers);
+    return;
+  }
+  consumers_sync();  // window free
+  reinterpret_cast<uint4*>(win)[t] = make_uint4(0, 0, 0, 0);
+  reinterpret_cast<uint4*>(win)[t + kPipeConsumers] = make_uint4(0, 0, 0, 0);
+  consumers_sync();
+  stage_container(d, reinterpret_cast<uint32_t*>(win), 0, kBitmapWords, t, kPipeConsumers);
+  consumers_sync();
+  v[0] = reinterpret_cast<const uint4*>(win)[t]; v[1] = reinterpret_cast<const uint4*>(win)[t + kPipeConsumers];
+}
+
+// Item feed: the producer warp also resolves the descriptor table of every item (three
+// dependent global loads) one item AHEAD of the consumers, double-buffered and handed over
+// through mbarriers, so the pipe never drains at an item boundary and the consumer warps
+// touch global memory only for results.
+struct ItemFeed {
+  static constexpr int kMaxPlanes = kMaxDepth + 3;
+  ContainerDesc (*pd)[kMaxPlanes];  // [2][kMaxPlanes], planes in consumption order
+  int* mode;                        // [2]: 0 skip, 1 streamed through the pipe, 2 synchronous path
+  uint64_t* ready;                  // [2], count 32 (producer lanes)
+  uint64_t* free_;                  // [2], count = consumer warps
+  __device__ __forceinline__ void init(int tid) {
+    if (tid == 0) {
+      for (int i = 0; i < 2; i++) { mbar_init(&ready[i], 32); mbar_init(&free_[i], kPipeConsumers / 32); }
+      mbar_fence_init();
+    }
+  }
+  // producer warp: wait until buffer (it & 1) is free again
+  __device__ __forceinline__ int begin_fill(uint32_t it) {
+    const int buf = it & 1; const uint32_t use = it >> 1;
+    if (use) mbar_wait(&free_[buf], (use - 1) & 1u);
+    return buf;
+  }
+  __device__ __forceinline__ void publish(int buf, int m, int lane) {
+    if (lane == 0) mode[buf] = m;
+    __syncwarp();
+    mbar_arrive(&ready[buf]);
+  }
+  // consumer threads
+  __device__ __forceinline__ int acquire(uint32_t it) {
+    const int buf = it & 1;
+    mbar_wait(&ready[buf], (it >> 1) & 1u);
+    return buf;
+  }
+  __device__ __forceinline__ void release(int buf, int lane) {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&free_[buf]);
+  }
+};
+
 // K8: Sum. consider = E [& filter]; count = |consider|; nrow = S (unfiltered: the reference
 // quirk, fragment.go:1118,1134; `strict` masks it with consider); prow = consider \ nrow;
-// per plane popcount(B_i & prow), popcount(B_i & nrow). Persistent CTAs accumulate in
-// shared memory and flush 2*depth+1 atomics once.
-// ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBsiThreads) bsi_sum_kernel(BsiParams p) {
-  constexpr int PER = 2;
-  extern __shared__ __align__(128) uint8_t s_ring[];
-  __shared__ __align__(8) uint64_t s_full[kRingDepth];
-  __shared__ ContainerDesc s_pd[kMaxDepth + 3];  // planes in consumption order: E, [filter], S, B_0 .. B_{d-1}
-  __shared__ unsigned long long s_acc[2 * kMaxDepth + 1];
-  const int tid = threadIdx.x, lane = tid & 31;
-  for (int i = tid; i < 2 * kMaxDepth + 1; i += kBsiThreads) s_acc[i] = 0;
-  PlaneRing pr;
-  pr.ring = s_ring; pr.full = s_full; pr.phase = 0;
-  if (tid == 0) {
-    for (int i = 0; i < kRingDepth; i++) mbar_init(&s_full[i], 1);
-    mbar_fence_init();
+// per plane popcount(B_i & prow), popcount(B_i & nrow), accumulated per consumer warp in shared
+// memory and flushed with 2*depth+1 atomics per CTA at the end.
+// Planes in consumption order: E, [filter], S, B_0 .. B_{d-1}.
+__global__ void __launch_bounds__(kPipeThreads) bsi_sum_kernel(BsiParams p) {
+  extern __shared__ __align__(128) uint8_t s_ring[];  // kPipeStages slots, then an 8 KiB staging window
+  __shared__ __align__(8) uint64_t s_full[kPipeStages], s_empty[kPipeStages], s_ready[2], s_free[2];
+  __shared__ ContainerDesc s_pd[2][ItemFeed::kMaxPlanes];
+  __shared__ int s_mode[2];
+  __shared__ uint32_t s_acc[kPipeConsumers / 32][2 * kMaxDepth + 1];  // per consumer warp: no atomics
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  uint64_t* s_win = reinterpret_cast<uint64_t*>(s_ring + kPipeStages * kBitmapBytes);
+  for (int i = tid; i < (kPipeConsumers / 32) * (2 * kMaxDepth + 1); i += kPipeThreads) (&s_acc[0][0])[i] = 0;
+  PlanePipe pp;
+  pp.ring = s_ring; pp.full = s_full; pp.empty = s_empty;
+  pp.init(tid);
+  ItemFeed feed;
+  feed.pd = s_pd; feed.mode = s_mode; feed.ready = s_ready; feed.free_ = s_free;
+  feed.init(tid);
+  __syncthreads();
+  const uint32_t depth = p.bit_depth, nf = p.has_filter ? 1u : 0u, n_planes = depth + 2 + nf;
+  const uint32_t n_items = p.n_shards * kRowContainers;
+  uint32_t it = 0;
+  if (tid >= kPipeConsumers) {  // ---- producer warp ----
+    unsigned long long bytes_acc = 0;
+    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
+      const uint32_t s = item / kRowContainers, c = item % kRowContainers;
+      const FamilyDev fam = p.families[p.family];
+      const uint64_t shard = p.shards[s];
+      FragDev f{};
+      if (shard < fam.cap) f = fam.frags[shard];
+      const int buf = feed.begin_fill(it);
+      int mode = f.nrows ? 1 : 0;  // no fragment: ValCount{} (executor.go:709-711)
+      bool sparse = false;
+      if (mode) {
+        for (uint32_t j = lane; j < n_planes; j += 32) {
+          ContainerDesc d;
+          if (j == 0) d = bsi_row_desc(f, 0, c);
+          else if (nf && j == 1) d = filter_desc(p, s, c);
+          else if (j == 1 + nf) d = bsi_row_desc(f, 1, c);
+          else d = bsi_row_desc(f, 2 + (j - 2 - nf), c);
+          s_pd[buf][j] = d;
+          bytes_acc += desc_algo_bytes(d);
+          sparse |= !is_const_or_bitmap(d);
+        }
+        if (__any_sync(0xffffffffu, sparse)) mode = 2;
+      }
+      feed.publish(buf, mode, lane);
+      if (mode == 1 && lane == 0)
+        for (uint32_t j = 0; j < n_planes; j++) pp.produce(s_pd[buf][j]);
+    }
+    if (bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+  } else {  // ---- consumer warps ----
+    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
+      const int buf = feed.acquire(it);
+      const int mode = s_mode[buf];
+      if (mode) {
+        const ContainerDesc* pd = s_pd[buf];
+        uint32_t j = 0;
+        auto next_plane = [&](uint4 (&v)[2]) {
+          if (mode == 1) pp.take(pd[j], tid, v); else pipe_plane_sync(pd[j], tid, s_win, v);
+          j++;
+        };
+        uint4 cons[2], nrow[2], prow[2];
+        next_plane(cons);
+        if (nf) {
+          uint4 fl[2];
+          next_plane(fl);
+          cons[0] = and128(cons[0], fl[0]); cons[1] = and128(cons[1], fl[1]);
+        }
+        next_plane(nrow);
+        if (p.strict) { nrow[0] = and128(nrow[0], cons[0]); nrow[1] = and128(nrow[1], cons[1]); }
+        prow[0] = andnot128(cons[0], nrow[0]); prow[1] = andnot128(cons[1], nrow[1]);
+        const uint32_t cnt = warp_sum(popc128(cons[0]) + popc128(cons[1]));
+        if (lane == 0) s_acc[wid][0] += cnt;
+        for (uint32_t i = 0; i < depth; i++) {
+          uint4 row[2];
+          next_plane(row);
+          // popcount(B_i & prow) in the low half, popcount(B_i & nrow) in the high half (<= 8192 each per warp)
+          const uint32_t both = warp_sum((popc128(and128(row[0], prow[0])) + popc128(and128(row[1], prow[1]))) |
+                                         ((popc128(and128(row[0], nrow[0])) + popc128(and128(row[1], nrow[1]))) << 16));
+          if (lane == 0) { s_acc[wid][1 + 2 * i] += both & 0xffffu; s_acc[wid][2 + 2 * i] += both >> 16; }
+        }
+      }
+      feed.release(buf, lane);
+    }
   }
   __syncthreads();
-  const uint32_t n_items = p.n_shards * kRowContainers;
-  const uint32_t nf = p.has_filter ? 1u : 0u;
-  const uint32_t n_planes = p.bit_depth + 2u + nf;
-  uint32_t q0 = 0;
-  unsigned long long bytes_acc = 0;
-  for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
-    const uint32_t s = item >> 4, c = item & 15;
-    const FamilyDev fam = p.families[p.family];
-    const uint64_t shard = p.shards[s];
-    FragDev f{};
-    if (shard < fam.cap) f = fam.frags[shard];
-    if (f.nrows == 0) continue;  // no fragment: ValCount{} (executor.go:709-711)
-    __syncthreads();             // s_pd of the previous item fully consumed
-    if (tid < int(n_planes)) {
-      ContainerDesc d;
-      if (tid == 0) d = bsi_row_desc(f, 0, c);
-      else if (nf && tid == 1) d = filter_desc(p, s, c);
-      else if (tid == int(1 + nf)) d = bsi_row_desc(f, 1, c);
-      else d = bsi_row_desc(f, 2 + (tid - 2 - nf), c);
-      s_pd[tid] = d;
-      bytes_acc += desc_algo_bytes(d);
+  for (int i = tid; i < int(2 * depth + 1); i += kPipeThreads) {
+    unsigned long long tot = 0;
+    for (int w = 0; w < kPipeConsumers / 32; w++) tot += s_acc[w][i];
+    if (tot) atomicAdd(p.sum_acc + i, tot);
+  }
+}
+
+// How a predicate maps onto the unsigned machines (fragment.go:1271-1534): machine kinds for the
+// positive / negative side and how their results combine. Shared by the host (which picks the kernel
+// instantiation) and the device (which picks filters and magnitudes).
+//   combine 0: m0 ; 1: E \ m0 ; 2: S | m0 ; 3: pos | m0 ; 4: m0 | m1 ; 5: E (notNull)
+struct RangePlan { int k0, k1, combine; };
+__host__ __device__ inline RangePlan range_plan(uint32_t op, long long a, long long b) {
+  switch (op) {
+    case PB200_BSI_NOTNULL: return {M_NONE, M_NONE, 5};
+    case PB200_BSI_EQ: return {M_EQ, M_NONE, 0};
+    case PB200_BSI_NEQ: return {M_EQ, M_NONE, 1};
+    case PB200_BSI_LT: case PB200_BSI_LTE: {
+      const bool eq = op == PB200_BSI_LTE;
+      if ((a >= 0 && eq) || (a >= -1 && !eq)) return {M_LTU, M_NONE, 2};
+      return {M_GTU, M_NONE, 0};
     }
-    __syncthreads();
-    if (tid == 0)
-      for (uint32_t j = 0; j < n_planes && j < uint32_t(kRingDepth); j++) pr.issue(s_pd[j], q0 + j);
+    case PB200_BSI_GT: case PB200_BSI_GTE: {
+      const bool eq = op == PB200_BSI_GTE;
+      if ((a >= 0 && eq) || (a >= -1 && !eq)) return {M_GTU, M_NONE, 0};
+      return {M_LTU, M_NONE, 3};
+    }
+    default:  // BETWEEN
+      if (a >= 0 || b < 0) return {M_BETWEENU, M_NONE, 0};
+      return {M_LTU, M_LTU, 4};
+  }
+}
+
+// K10. Planes in consumption order: E, S, B_{d-1} .. B_0. One instantiation per (machines, combine).
+template <int K0, int K1, int COMBINE>
+__global__ void __launch_bounds__(kPipeThreads, 3) bsi_range_kernel(BsiParams p) {
+  extern __shared__ __align__(128) uint8_t s_ring[];  // kPipeStages slots, then an 8 KiB staging window
+  __shared__ __align__(8) uint64_t s_full[kPipeStages], s_empty[kPipeStages], s_ready[2], s_free[2];
+  __shared__ ContainerDesc s_pd[2][ItemFeed::kMaxPlanes];
+  __shared__ int s_mode[2];
+  const int tid = threadIdx.x, lane = tid & 31;
+  uint64_t* s_win = reinterpret_cast<uint64_t*>(s_ring + kPipeStages * kBitmapBytes);
+  PlanePipe pp;
+  pp.ring = s_ring; pp.full = s_full; pp.empty = s_empty;
+  pp.init(tid);
+  ItemFeed feed;
+  feed.pd = s_pd; feed.mode = s_mode; feed.ready = s_ready; feed.free_ = s_free;
+  feed.init(tid);
+  __syncthreads();
+  const uint32_t depth = p.bit_depth;
+  const uint32_t n_planes = COMBINE == 5 ? 1u : depth + 2u;
+  const uint32_t n_items = p.n_shards * kRowContainers;
+  uint32_t it = 0;
+  if (tid >= kPipeConsumers) {  // ---- producer warp ----
+    unsigned long long bytes_acc = 0;
+    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
+      const uint32_t s = item / kRowContainers, c = item % kRowContainers;
+      const FamilyDev fam = p.families[p.family];
+      const uint64_t shard = p.shards[s];
+      FragDev f{};
+      if (shard < fam.cap) f = fam.frags[shard];
+      const int buf = feed.begin_fill(it);
+      bool sparse = false;
+      for (uint32_t j = lane; j < n_planes; j += 32) {
+        const uint64_t row = j < 2 ? uint64_t(j) : uint64_t(2 + (depth - 1 - (j - 2)));
+        const ContainerDesc d = bsi_row_desc(f, row, c);  // no fragment: empty planes, the result row is zero
+        s_pd[buf][j] = d;
+        bytes_acc += desc_algo_bytes(d);
+        sparse |= !is_const_or_bitmap(d);
+      }
+      const int mode = __any_sync(0xffffffffu, sparse) ? 2 : 1;
+      feed.publish(buf, mode, lane);
+      if (mode == 1 && lane == 0)
+        for (uint32_t j = 0; j < n_planes; j++) pp.produce(s_pd[buf][j]);
+    }
+    if (bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+    return;
+  }
+  // ---- consumer warps ----
+  for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
+    const uint32_t s = item / kRowContainers;
+    uint4* out = p.dense_out ? reinterpret_cast<uint4*>(p.dense_out + uint64_t(item) * kBitmapBytes) : nullptr;
+    const int buf = feed.acquire(it);
+    const int mode = s_mode[buf];
+    const ContainerDesc* pd = s_pd[buf];
     uint32_t j = 0;
-    auto next_plane = [&](uint4 (&v)[PER]) {
-      pr.take<kBsiThreads, PER>(s_pd[j], q0 + j, tid, v);
-      __syncthreads();  // slot consumed by every thread: refill it
-      if (tid == 0 && j + kRingDepth < n_planes) pr.issue(s_pd[j + kRingDepth], q0 + j + kRingDepth);
+    auto next_plane = [&](uint4 (&v)[2]) {
+      if (mode == 1) pp.take(pd[j], tid, v); else pipe_plane_sync(pd[j], tid, s_win, v);
       j++;
     };
-    uint4 cons[PER], nrow[PER], prow[PER];
-    next_plane(cons);
-    if (nf) {
-      uint4 fl[PER];
-      next_plane(fl);
+    uint4 E[2], res[2];
+    next_plane(E);
+    if (COMBINE == 5) {
+      res[0] = E[0]; res[1] = E[1];
+    } else {
+      uint4 S[2], pos[2], neg[2];
+      next_plane(S);
 #pragma unroll
-      for (int k = 0; k < PER; k++) cons[k] = and128(cons[k], fl[k]);
-    }
-    next_plane(nrow);
-    uint32_t cnt = 0;
+      for (int k = 0; k < 2; k++) { pos[k] = andnot128(E[k], S[k]); neg[k] = and128(E[k], S[k]); }
+      Mach<2, K0> m0;
+      Mach<2, K1> m1;
+      const long long a = p.a, b = p.b;
+      const unsigned long long ua = uabs64(a), ub = uabs64(b);
+      const bool eq = p.bsi_op == PB200_BSI_LTE || p.bsi_op == PB200_BSI_GTE;
+      if (K0 == M_EQ) m0.init(K0, a < 0 ? neg : pos, ua, 0, false);
+      else if (K1 == M_LTU) { m0.init(K0, pos, ub, 0, true); m1.init(K1, neg, ua, 0, true); }  // BETWEEN across zero
+      else if (K0 == M_BETWEENU) { if (a >= 0) m0.init(K0, pos, ua, ub, true); else m0.init(K0, neg, ub, ua, true); }
+      else if (COMBINE == 2) m0.init(K0, pos, ua, 0, eq);   // LT / LTE with a non-negative bound
+      else if (COMBINE == 3) m0.init(K0, neg, ua, 0, eq);   // GT / GTE with a negative bound
+      else if (p.bsi_op == PB200_BSI_LT || p.bsi_op == PB200_BSI_LTE) m0.init(K0, neg, ua, 0, eq);  // M_GTU over the negatives
+      else m0.init(K0, pos, ua, 0, eq);                                                              // M_GTU over the positives
+      for (int i = int(depth) - 1; i >= 0; i--) {  // every plane is taken, so that both sides of the pipe count alike
+        uint4 row[2];
+        next_plane(row);
+        m0.step(i, row);
+        if (K1 != M_NONE) m1.step(i, row);
+      }
 #pragma unroll
-    for (int k = 0; k < PER; k++) {
-      if (p.strict) nrow[k] = and128(nrow[k], cons[k]);
-      prow[k] = andnot128(cons[k], nrow[k]);
-      cnt += popc128(cons[k]);
-    }
-    cnt = warp_sum(cnt);
-    if (lane == 0 && cnt) atomicAdd(&s_acc[0], (unsigned long long)cnt);
-    for (uint32_t i = 0; i < p.bit_depth; i++) {
-      uint4 row[PER];
-      next_plane(row);
-      uint32_t pc = 0, nc = 0;
-#pragma unroll
-      for (int k = 0; k < PER; k++) { pc += popc128(and128(row[k], prow[k])); nc += popc128(and128(row[k], nrow[k])); }
-      pc = warp_sum(pc); nc = warp_sum(nc);
-      if (lane == 0) {
-        if (pc) atomicAdd(&s_acc[1 + 2 * i], (unsigned long long)pc);
-        if (nc) atomicAdd(&s_acc[2 + 2 * i], (unsigned long long)nc);
+      for (int k = 0; k < 2; k++) {
+        if (COMBINE == 0) res[k] = m0.f[k];
+        else if (COMBINE == 1) res[k] = andnot128(E[k], m0.f[k]);
+        else if (COMBINE == 2) res[k] = or128(S[k], m0.f[k]);
+        else if (COMBINE == 3) res[k] = or128(pos[k], m0.f[k]);
+        else res[k] = or128(m0.f[k], m1.f[k]);
       }
     }
-    q0 += n_planes;
-  }
-  __syncthreads();
-  for (uint32_t i = tid; i < 2 * p.bit_depth + 1; i += kBsiThreads)
-    if (s_acc[i]) atomicAdd(p.sum_acc + i, s_acc[i]);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) bytes_acc += __shfl_xor_sync(0xffffffffu, bytes_acc, o);
-  if (lane == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
-}
-
-// ---------------------------------------------------------------------------------------
-// K9: Min / Max. One CTA per shard (1024 threads x 8 uint4 = the whole 128 KiB row state in
-// registers); per plane one block-wide popcount decides whether the candidate set shrinks
-// (fragment.go:1171-1186 minUnsigned, :1213-1225 maxUnsigned, :1145-1168 min, :1189-1210 max).
-// ---------------------------------------------------------------------------------------
-constexpr int kMmThreads = 1024;
-
-__device__ __forceinline__ unsigned long long block_sum_1024(uint32_t v, unsigned long long* s_red, int tid) {
-  v = warp_sum(v);
-  __syncthreads();
-  if ((tid & 31) == 0) s_red[tid >> 5] = v;
-  __syncthreads();
-  unsigned long long tot = 0;
-#pragma unroll
-  for (int w = 0; w < kMmThreads / 32; w++) tot += s_red[w];
-  return tot;
-}
-
-// Column c of the row is handled by threads [64c, 64c+64): 8 uint4 each.
-__device__ __forceinline__ void load_row_1024(const FragDev& f, uint64_t row, uint64_t* win16, int tid, uint4 (&v)[8],
-                                              unsigned long long& bytes_acc) {
-  const int c = tid >> 6, t = tid & 63;
-  const ContainerDesc d = bsi_row_desc(f, row, c);
-  if (t == 0) bytes_acc += desc_algo_bytes(d);
-  // staging (rare for BSI planes): every column has its own 8 KiB window
-  const bool need_stage = d.n != 0 && d.n != kFullN && desc_type(d) != kBitmap;
-  const int any_stage = __syncthreads_or(need_stage);
-  if (any_stage) {
-    uint64_t* win = win16 + size_t(c) * kBitmapWords;
-    for (int j = t; j < kBitmapWords / 2; j += 64) reinterpret_cast<uint4*>(win)[j] = make_uint4(0, 0, 0, 0);
-    __syncthreads();
-    if (need_stage) stage_container(d, reinterpret_cast<uint32_t*>(win), 0, kBitmapWords, t, 64);
-    __syncthreads();
-  }
-  if (d.n == 0) {
-#pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = make_uint4(0, 0, 0, 0);
-  } else if (desc_type(d) == kBitmap) {
-    const uint4* ptr = reinterpret_cast<const uint4*>(d.addr) + t;
-#pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = ldg128_stream(ptr + k * 64);
-  } else if (d.n == kFullN) {
-#pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = make_uint4(~0u, ~0u, ~0u, ~0u);
-  } else {
-    const uint4* win = reinterpret_cast<const uint4*>(win16 + size_t(c) * kBitmapWords);
-#pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = win[t + k * 64];
-  }
-  if (any_stage) __syncthreads();
-}
-
-__global__ void __launch_bounds__(kMmThreads) bsi_minmax_kernel(BsiParams p) {
-  extern __shared__ __align__(16) uint64_t s_win16[];  // 16 x 8 KiB staging windows
-  __shared__ unsigned long long s_red[kMmThreads / 32];
-  const int tid = threadIdx.x;
-  unsigned long long bytes_acc = 0;
-  for (uint32_t s = blockIdx.x; s < p.n_shards; s += gridDim.x) {
-    const FamilyDev fam = p.families[p.family];
-    const uint64_t shard = p.shards[s];
-    FragDev f{};
-    if (shard < fam.cap) f = fam.frags[shard];
-    long long val = 0;
-    unsigned long long count = 0;
-    if (f.nrows != 0) {
-      uint4 cons[8], tmp[8];
-      load_row_1024(f, 0, s_win16, tid, cons, bytes_acc);
-      if (p.has_filter) {
-        // the filter row: resolve per column like any leaf
-        const int c = tid >> 6, t = tid & 63;
-        const ContainerDesc dF = filter_desc(p, s, c);
-        if (t == 0) bytes_acc += desc_algo_bytes(dF);
-        const bool need_stage = dF.n != 0 && dF.n != kFullN && desc_type(dF) != kBitmap;
-        const int any_stage = __syncthreads_or(need_stage);
-        uint64_t* win = s_win16 + size_t(c) * kBitmapWords;
-        if (any_stage) {
-          for (int j = t; j < kBitmapWords / 2; j += 64) reinterpret_cast<uint4*>(win)[j] = make_uint4(0, 0, 0, 0);
-          __syncthreads();
-          if (need_stage) stage_container(dF, reinterpret_cast<uint32_t*>(win), 0, kBitmapWords, t, 64);
-          __syncthreads();
-        }
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-          uint4 fv;
-          if (dF.n == 0) fv = make_uint4(0, 0, 0, 0);
-          else if (desc_type(dF) == kBitmap) fv = ldg128_stream(reinterpret_cast<const uint4*>(dF.addr) + t + k * 64);
-          else if (dF.n == kFullN) fv = make_uint4(~0u, ~0u, ~0u, ~0u);
-          else fv = reinterpret_cast<const uint4*>(win)[t + k * 64];
-          cons[k] = and128(cons[k], fv);
-        }
-        if (any_stage) __syncthreads();
-      }
-      uint32_t c0 = 0;
-#pragma unroll
-      for (int k = 0; k < 8; k++) c0 += popc128(cons[k]);
-      const unsigned long long n_cons = block_sum_1024(c0, s_red, tid);
-      if (n_cons != 0) {
-        load_row_1024(f, 1, s_win16, tid, tmp, bytes_acc);  // sign row
-        // which unsigned search, over which candidate set?
-        uint32_t cs = 0;
-        if (!p.is_max) {
-#pragma unroll
-          for (int k = 0; k < 8; k++) cs += popc128(and128(tmp[k], cons[k]));  // negatives present?
-        } else {
-#pragma unroll
-          for (int k = 0; k < 8; k++) cs += popc128(andnot128(cons[k], tmp[k]));  // positives present?
-        }
-        const unsigned long long n_side = block_sum_1024(cs, s_red, tid);
-        bool use_max_unsigned, negate;
-        uint4 filt[8];
-        if (!p.is_max) {
-          if (n_side) { use_max_unsigned = true; negate = true;
-#pragma unroll
-            for (int k = 0; k < 8; k++) filt[k] = and128(tmp[k], cons[k]);
-          } else { use_max_unsigned = false; negate = false;
-#pragma unroll
-            for (int k = 0; k < 8; k++) filt[k] = cons[k];
-          }
-        } else {
-          if (!n_side) { use_max_unsigned = false; negate = true;
-#pragma unroll
-            for (int k = 0; k < 8; k++) filt[k] = cons[k];
-          } else { use_max_unsigned = true; negate = false;
-#pragma unroll
-            for (int k = 0; k < 8; k++) filt[k] = andnot128(cons[k], tmp[k]);
-          }
-        }
-        unsigned long long mag = 0;
-        for (int i = int(p.bit_depth) - 1; i >= 0; i--) {
-          load_row_1024(f, 2 + i, s_win16, tid, tmp, bytes_acc);
-          uint32_t pc = 0;
-#pragma unroll
-          for (int k = 0; k < 8; k++) {
-            tmp[k] = use_max_unsigned ? and128(tmp[k], filt[k]) : andnot128(filt[k], tmp[k]);
-            pc += popc128(tmp[k]);
-          }
-          count = block_sum_1024(pc, s_red, tid);
-          if (count > 0) {
-            if (use_max_unsigned) mag += 1ull << i;
-#pragma unroll
-            for (int k = 0; k < 8; k++) filt[k] = tmp[k];
-          } else {
-            if (!use_max_unsigned) mag += 1ull << i;
-            if (i == 0) {
-              uint32_t fc = 0;
-#pragma unroll
-              for (int k = 0; k < 8; k++) fc += popc128(filt[k]);
-              count = block_sum_1024(fc, s_red, tid);
-            }
-          }
-        }
-        val = negate ? -(long long)mag : (long long)mag;
-      }
+    feed.release(buf, lane);
+    if (out) { out[tid] = res[0]; out[tid + kPipeConsumers] = res[1]; }
+    if (p.count_out) {
+      const uint32_t cnt = warp_sum(popc128(res[0]) + popc128(res[1]));
+      if (lane == 0 && cnt) atomicAdd(p.count_out + uint64_t(s) * p.count_sstride, (unsigned long long)cnt);
     }
-    if (tid == 0) { p.mm_val[s] = val; p.mm_count[s] = count; }
   }
-  if ((tid & 63) == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+}
+
+// K9 (see the slice decomposition above). Planes in consumption order: E, [filter], S, B_{d-1} .. B_0.
+__global__ void __launch_bounds__(kPipeThreads, 3) bsi_minmax_kernel(BsiParams p, MmRec* __restrict__ recs) {
+  extern __shared__ __align__(128) uint8_t s_ring[];  // kPipeStages slots, then an 8 KiB staging window
+  __shared__ __align__(8) uint64_t s_full[kPipeStages], s_empty[kPipeStages], s_ready[2], s_free[2];
+  __shared__ ContainerDesc s_pd[2][ItemFeed::kMaxPlanes];
+  __shared__ int s_mode[2];
+  __shared__ MmRec s_rec[kPipeConsumers / 32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  uint64_t* s_win = reinterpret_cast<uint64_t*>(s_ring + kPipeStages * kBitmapBytes);
+  PlanePipe pp;
+  pp.ring = s_ring; pp.full = s_full; pp.empty = s_empty;
+  pp.init(tid);
+  ItemFeed feed;
+  feed.pd = s_pd; feed.mode = s_mode; feed.ready = s_ready; feed.free_ = s_free;
+  feed.init(tid);
+  __syncthreads();
+  const uint32_t depth = p.bit_depth, nf = p.has_filter ? 1u : 0u, n_planes = depth + 2 + nf;
+  const uint32_t n_items = p.n_shards * kRowContainers;
+  uint32_t it = 0;
+  if (tid >= kPipeConsumers) {  // ---- producer warp ----
+    unsigned long long bytes_acc = 0;
+    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
+      const uint32_t s = item / kRowContainers, c = item % kRowContainers;
+      const FamilyDev fam = p.families[p.family];
+      const uint64_t shard = p.shards[s];
+      FragDev f{};
+      if (shard < fam.cap) f = fam.frags[shard];
+      const int buf = feed.begin_fill(it);
+      int mode = f.nrows ? 1 : 0;
+      bool sparse = false;
+      if (mode) {
+        for (uint32_t j = lane; j < n_planes; j += 32) {
+          ContainerDesc d;
+          if (j == 0) d = bsi_row_desc(f, 0, c);
+          else if (nf && j == 1) d = filter_desc(p, s, c);
+          else if (j == 1 + nf) d = bsi_row_desc(f, 1, c);
+          else d = bsi_row_desc(f, 2 + (depth - 1 - (j - 2 - nf)), c);
+          s_pd[buf][j] = d;
+          bytes_acc += desc_algo_bytes(d);
+          sparse |= !is_const_or_bitmap(d);
+        }
+        if (__any_sync(0xffffffffu, sparse)) mode = 2;
+      }
+      feed.publish(buf, mode, lane);
+      if (mode == 1 && lane == 0)
+        for (uint32_t j = 0; j < n_planes; j++) pp.produce(s_pd[buf][j]);
+    }
+    if (bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+    return;
+  }
+  // ---- consumer warps ----
+  for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, it++) {
+    const int buf = feed.acquire(it);
+    const int mode = s_mode[buf];
+    MmRec mine{0, 0, ~0ull, 0};
+    if (mode) {
+      const ContainerDesc* pd = s_pd[buf];
+      uint32_t j = 0;
+      auto next_plane = [&](uint4 (&v)[2]) {
+        if (mode == 1) pp.take(pd[j], tid, v); else pipe_plane_sync(pd[j], tid, s_win, v);
+        j++;
+      };
+      uint4 cons[2], sign[2];
+      next_plane(cons);
+      if (nf) {
+        uint4 fl[2];
+        next_plane(fl);
+        cons[0] = and128(cons[0], fl[0]); cons[1] = and128(cons[1], fl[1]);
+      }
+      next_plane(sign);
+      uint4 A[2], B[2];  // A: maxUnsigned candidates, B: minUnsigned candidates (see K9 above)
+#pragma unroll
+      for (int k = 0; k < 2; k++) {
+        const uint4 neg = and128(cons[k], sign[k]), pos = andnot128(cons[k], sign[k]);
+        A[k] = p.is_max ? pos : neg;
+        B[k] = p.is_max ? neg : pos;
+      }
+      unsigned long long magA = 0, magB = 0;
+      for (int i = int(depth) - 1; i >= 0; i--) {
+        uint4 v[2];
+        next_plane(v);
+        const uint4 x0 = and128(A[0], v[0]), x1 = and128(A[1], v[1]);
+        const uint4 y0 = andnot128(B[0], v[0]), y1 = andnot128(B[1], v[1]);
+        if (__any_sync(0xffffffffu, mm_nz(x0) || mm_nz(x1))) { A[0] = x0; A[1] = x1; magA |= 1ull << i; }   // maxUnsigned :1216-1220
+        if (__any_sync(0xffffffffu, mm_nz(y0) || mm_nz(y1))) { B[0] = y0; B[1] = y1; } else magB |= 1ull << i;  // minUnsigned :1174-1180
+      }
+      mine = MmRec{magA, warp_sum(popc128(A[0]) + popc128(A[1])), magB, warp_sum(popc128(B[0]) + popc128(B[1]))};
+    }
+    feed.release(buf, lane);
+    consumers_sync();  // s_rec of the previous item has been folded
+    if (lane == 0) s_rec[wid] = mine;
+    consumers_sync();
+    if (tid == 0) {  // fold the column's 8 slices
+      MmRec r{0, 0, ~0ull, 0};
+      for (int w = 0; w < kPipeConsumers / 32; w++) {
+        const MmRec x = s_rec[w];
+        if (x.cntA) { if (x.magA > r.magA || !r.cntA) { r.magA = x.magA; r.cntA = x.cntA; } else if (x.magA == r.magA) r.cntA += x.cntA; }
+        if (x.cntB) { if (x.magB < r.magB || !r.cntB) { r.magB = x.magB; r.cntB = x.cntB; } else if (x.magB == r.magB) r.cntB += x.cntB; }
+      }
+      recs[item] = r;
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------
