@@ -265,6 +265,51 @@ int pb200_eval_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
                       const uint64_t* shards, uint32_t n_shards, void* out, size_t cap,
                       uint64_t* out_off, size_t* out_len);
 
+/* ---- Rows / GroupBy --------------------------------------------- */
+
+/* Rows(field[, previous=][, column=][, limit=]) over the local shards: executeRows /
+ * executeRowsShard (executor.go:1277-1441) = fragment.rows (fragment.go:2668-2712) with
+ * filterColumn / filterWithLimit (:2606-2629) per shard, merged by RowIDs.merge (:1043-1069).
+ * `start` is previous + 1 (0 when absent); `limit` is UINT64_MAX when absent. A row exists in a
+ * shard when it has a non-empty container there (what a snapshotted fragment holds). With
+ * PB200_ROWS_COLUMN only the shard holding `column` can contribute (:1405-1409). Time-quantum
+ * views are merged by the host (one call per view). */
+#define PB200_ROWS_COLUMN 1u
+int pb200_rows(pb200_ctx* ctx, pb200_family family, uint64_t start, uint32_t flags, uint64_t column,
+               uint64_t limit, const uint64_t* shards, uint32_t n_shards, uint64_t* out_rows,
+               size_t cap, size_t* n_out);
+
+/* GroupBy(Rows(f0), Rows(f1), ..., filter=, limit=): executeGroupBy's map-reduce
+ * (executor.go:1071-1137), executeGroupByShard (:1236-1275), groupByIterator (:3060-3230)
+ * and mergeGroupCounts (:1166-1200) for the local shards. Every shard walks the cross
+ * product of its rows in ascending (f0, f1, ...) order and keeps its first `limit` groups
+ * with a non-zero count; shards are merged in shard-list order (equal groups add up, at
+ * most `limit` kept). `offset` and the final limit are the caller's (:1139-1157). The counts
+ * |filter & r0 & r1 & ...| of ALL combinations come from the device in one pass (the same kernel
+ * as TopN: a prefix row per shard staged in shared memory against the last field's rows); only
+ * the iterator's bookkeeping (`previous` seek / wrap rules :3121-3153) runs on the host.
+ * child.rows (optional, ascending): the result of a Rows() child that carried limit= or
+ * column= and was therefore executed first (:1105-1116) -> filterWithRows (fragment.go:2636).
+ * Limits: 1..4 fields; (product of candidate rows) x shards <= 2^27 counts per call.
+ * One deviation: with >= 3 fields the reference's nextAtIdx can spin for ever once the first
+ * field is exhausted (:3167-3191); this implementation ends the iteration there. */
+#define PB200_GROUPBY_MAX_FIELDS 4
+typedef struct pb200_groupby_child {
+  pb200_family family;   /* standard view of the field                                   */
+  uint32_t has_previous; /* Rows(previous=) present                                      */
+  uint64_t previous;
+  const uint64_t* rows;  /* pre-executed Rows() result, or NULL                          */
+  uint64_t n_rows;
+} pb200_groupby_child;   /* 32 bytes */
+typedef struct pb200_group {
+  uint64_t rows[PB200_GROUPBY_MAX_FIELDS]; /* row id per field, unused entries 0         */
+  uint64_t count;
+} pb200_group;           /* 40 bytes */
+int pb200_groupby(pb200_ctx* ctx, const pb200_groupby_child* children, uint32_t n_children,
+                  const pb200_node* filter_prog, uint32_t n_filter_nodes, uint64_t limit,
+                  const uint64_t* shards, uint32_t n_shards, pb200_group* out, size_t cap,
+                  size_t* n_out);
+
 /* Evaluate a bitmap call on one shard into the sorted list of absolute column ids
  * (row.go:302-327 Row.Columns). Two-call protocol as above (cap in elements). */
 int pb200_eval_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard,

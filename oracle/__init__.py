@@ -90,6 +90,8 @@ def lib() -> C.CDLL:
         "orc_count_shards": (C.c_int, [vp, np_, C.c_uint32, u64p, C.c_uint32, C.c_int, u64p]),
         "orc_eval_columns": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, u64p, sz, C.POINTER(sz)]),
         "orc_eval_roaring": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, C.c_char_p, sz, C.POINTER(sz)]),
+        "orc_rows": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, u64p, C.c_uint32, u64p, sz, C.POINTER(sz)]),
+        "orc_groupby": (C.c_int, [vp, C.c_void_p, C.c_uint32, np_, C.c_uint32, C.c_uint64, u64p, C.c_uint32, C.c_void_p, sz, C.POINTER(sz)]),
         "orc_topn": (C.c_int, [vp, C.c_uint32, np_, C.c_uint32, C.c_uint32, u64p, sz, C.c_uint64, C.c_uint64, C.c_uint32, u64p,
                                C.c_uint32, C.POINTER(Pair), sz, C.POINTER(sz)]),
         "orc_topn_shard": (C.c_int, [vp, C.c_uint32, np_, C.c_uint32, C.c_uint32, u64p, sz, C.c_uint64, C.c_uint64,
@@ -392,6 +394,31 @@ class Oracle:
         sp, ns = (src_prog, len(src_prog)) if src_prog is not None else (None, 0)
         return self._pairs(lib().orc_topn_shard, self._h, fam, sp, ns, n, u64_array(ids) if ids else None, len(ids),
                            min_threshold, tanimoto, shard)
+
+    def rows(self, fam, shards, start=0, column=None, limit=None):
+        from pilosa_b200.abi import NO_LIMIT, ROWS_COLUMN
+        cap = 1 << 16
+        while True:
+            out, n = (C.c_uint64 * cap)(), C.c_size_t()
+            _check(lib().orc_rows(self._h, fam, start, 0 if column is None else ROWS_COLUMN, column or 0,
+                                  NO_LIMIT if limit is None else limit, u64_array(shards), len(shards), out, cap, C.byref(n)))
+            if n.value <= cap:
+                return list(out[: n.value])
+            cap = n.value
+
+    def groupby(self, children, filter_prog, limit, shards):
+        """children: [(family, previous or None, rows or None)]; returns [((row ids), count)]."""
+        from pilosa_b200.abi import NO_LIMIT, Group, pack_groupby_children, unpack_groups
+        arr, keep = pack_groupby_children(children)
+        fp, nf = (filter_prog, len(filter_prog)) if filter_prog is not None else (None, 0)
+        cap = 1 << 14
+        while True:
+            out, n = (Group * cap)(), C.c_size_t()
+            _check(lib().orc_groupby(self._h, arr, len(children), fp, nf, NO_LIMIT if limit is None else limit,
+                                     u64_array(shards), len(shards), out, cap, C.byref(n)))
+            if n.value <= cap:
+                return unpack_groups(out, n.value, len(children))
+            cap = n.value
 
     def bsi_sum(self, fam, bit_depth, filter_prog, shards, flags=0):
         fp, nf = (filter_prog, len(filter_prog)) if filter_prog is not None else (None, 0)

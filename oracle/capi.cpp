@@ -280,6 +280,33 @@ int orc_topn_shard(void* h, uint32_t fam, const pb200_node* src, uint32_t nsrc, 
     for (size_t i = 0; i < r.size() && i < cap; i++) out[i] = {r[i].id, r[i].count};
   });
 }
+int orc_rows(void* h, uint32_t fam, uint64_t start, uint32_t flags, uint64_t column, uint64_t limit, const uint64_t* shards, uint32_t ns,
+             uint64_t* out, size_t cap, size_t* n_out) {
+  return guard([&] {
+    auto r = ((Orc*)h)->exec.rows(fam, start, (flags & PB200_ROWS_COLUMN) != 0, column, limit != ~0ull, limit, vec(shards, ns));
+    *n_out = r.size();
+    for (size_t i = 0; i < r.size() && i < cap; i++) out[i] = r[i];
+  });
+}
+int orc_groupby(void* h, const pb200_groupby_child* ch, uint32_t nch, const pb200_node* filt, uint32_t nf, uint64_t limit,
+                const uint64_t* shards, uint32_t ns, pb200_group* out, size_t cap, size_t* n_out) {
+  return guard([&] {
+    if (nch > PB200_GROUPBY_MAX_FIELDS) throw std::runtime_error("too many GroupBy fields");
+    std::vector<Executor::GroupByChild> c(nch);
+    for (uint32_t i = 0; i < nch; i++) {
+      c[i].fam = ch[i].family; c[i].has_prev = ch[i].has_previous != 0; c[i].prev = ch[i].previous;
+      if (ch[i].rows) c[i].child_rows.assign(ch[i].rows, ch[i].rows + ch[i].n_rows);
+    }
+    auto r = ((Orc*)h)->exec.group_by(c, filt, nf, limit, vec(shards, ns));
+    *n_out = r.size();
+    for (size_t i = 0; i < r.size() && i < cap; i++) {
+      pb200_group g{};
+      for (size_t j = 0; j < r[i].rows.size(); j++) g.rows[j] = r[i].rows[j];
+      g.count = r[i].count;
+      out[i] = g;
+    }
+  });
+}
 int orc_bsi_sum(void* h, uint32_t fam, uint32_t bit_depth, const pb200_node* filt, uint32_t nf, uint32_t flags,
                 const uint64_t* shards, uint32_t ns, int64_t* out_sum, uint64_t* out_count) {
   return guard([&] {

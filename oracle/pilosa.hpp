@@ -248,6 +248,46 @@ struct Fragment {
       n += N(it->second);
     return n;
   }
+  // fragment.rows (fragment.go:2668-2712) with the filters of :2606-2657 applied in the order the
+  // callers build them: filterColumn, filterWithRows, filterWithLimit (last, :2608-2611).
+  struct RowsOpts {
+    uint64_t start = 0;
+    bool has_column = false; uint64_t column = 0;
+    const std::vector<uint64_t>* in_rows = nullptr;  // filterWithRows (ascending)
+    bool has_limit = false; uint64_t limit = 0;
+  };
+  std::vector<uint64_t> rows(const RowsOpts& o) const {
+    std::vector<uint64_t> out;
+    uint64_t last_row = ~0ull, limit = o.limit;
+    size_t loc = 0;
+    for (auto it = storage.cs.lower_bound(o.start * 16); it != storage.cs.end(); ++it) {
+      if (!it->second || N(it->second) == 0) continue;  // nil containers are skipped by the iterator (containers_slice.go:239-254)
+      const uint64_t key = it->first, vrow = key >> 4;
+      if (vrow == last_row) continue;
+      bool add = true, done = false;
+      if (o.has_column) {  // filterColumn :2622
+        const uint64_t col_id = o.column % kShardWidth;
+        const uint64_t col_key = (vrow * kShardWidth + col_id) >> 16;
+        add = col_key == key && contains(it->second, uint16_t(col_id & 0xffff));
+      }
+      if (add && o.in_rows) {  // filterWithRows :2636
+        const auto& r = *o.in_rows;
+        if (loc >= r.size()) { add = false; done = true; }
+        else {
+          loc = size_t(std::lower_bound(r.begin() + loc, r.end(), vrow) - r.begin());
+          if (loc >= r.size()) { add = false; done = true; }
+          else if (r[loc] == vrow) { if (loc == r.size() - 1) done = true; }
+          else add = false;
+        }
+      }
+      if (add && o.has_limit) {  // filterWithLimit :2612
+        if (limit > 0) limit--; else { add = false; done = true; }
+      }
+      if (add) { last_row = vrow; out.push_back(vrow); }
+      if (done) return out;
+    }
+    return out;
+  }
   bool set_bit(uint64_t row_id, uint64_t col) {  // :680-724
     bool changed = storage.direct_add(pos(row_id, col));
     if (!changed) return false;
@@ -749,6 +789,175 @@ struct Executor {
     auto trimmed = topn_shards(fam, src, nsrc, n, ids2, min_threshold, tanimoto, shards);
     if (n != 0 && n < trimmed.size()) trimmed.resize(n);
     return trimmed;
+  }
+
+  // RowIDs.merge (executor.go:1043-1069)
+  static std::vector<uint64_t> rowids_merge(const std::vector<uint64_t>& a, const std::vector<uint64_t>& b, uint64_t limit) {
+    std::vector<uint64_t> r;
+    size_t i = 0, j = 0;
+    while (i < a.size() && j < b.size() && r.size() < limit) {
+      if (a[i] < b[j]) r.push_back(a[i++]);
+      else if (a[i] > b[j]) r.push_back(b[j++]);
+      else { r.push_back(b[j]); i++; j++; }
+    }
+    while (i < a.size() && r.size() < limit) r.push_back(a[i++]);
+    while (j < b.size() && r.size() < limit) r.push_back(b[j++]);
+    return r;
+  }
+  // executeRows / executeRowsShard (executor.go:1277-1441), standard view only (time views stay on the host)
+  std::vector<uint64_t> rows(uint32_t fam, uint64_t start, bool has_column, uint64_t column, bool has_limit, uint64_t limit,
+                             const std::vector<uint64_t>& shards) const {
+    const uint64_t lim = has_limit ? limit : ~0ull;
+    auto per = map_shards<std::vector<uint64_t>>(shards, [&](uint64_t shard) -> std::vector<uint64_t> {
+      Fragment* f = holder->fragment(fam, shard);
+      if (!f) return {};
+      if (has_column && column / kShardWidth != shard) return {};  // :1405-1409
+      Fragment::RowsOpts o;
+      o.start = start; o.has_column = has_column; o.column = column; o.has_limit = has_limit; o.limit = limit;
+      return f->rows(o);
+    });
+    std::vector<uint64_t> acc;
+    for (auto& v : per) acc = rowids_merge(acc, v, lim);
+    return acc;
+  }
+
+  // ---- GroupBy (executor.go:1071-1275, groupByIterator :3060-3230, rowIterator fragment.go:2759-2791) ----
+  struct GroupCount { std::vector<uint64_t> rows; uint64_t count = 0; };
+  struct GroupByChild {
+    uint32_t fam = 0;
+    bool has_prev = false; uint64_t prev = 0;
+    std::vector<uint64_t> child_rows;  // pre-executed Rows(limit= / column=); empty = no filterWithRows (:3118-3120)
+  };
+  struct RowIter {  // fragment.go:2759-2791
+    const Fragment* f = nullptr;
+    std::vector<uint64_t> ids;
+    size_t cur = 0;
+    bool wrap = false;
+    void seek(uint64_t row_id) { cur = size_t(std::lower_bound(ids.begin(), ids.end(), row_id) - ids.begin()); }
+    bool next(uint64_t* id, bool* wrapped) {
+      *wrapped = false;
+      if (cur >= ids.size()) {
+        if (!wrap || ids.empty()) { *wrapped = true; return false; }
+        seek(0);
+        *wrapped = true;
+      }
+      *id = ids[cur++];
+      return true;
+    }
+  };
+  struct GroupByIter {
+    std::vector<RowIter> its;
+    std::vector<Row> rows;
+    std::vector<uint64_t> ids;
+    const Row* filter = nullptr;
+    bool done = false;
+    void set_row(size_t i, uint64_t id) {  // the three cases of nextAtIdx :3180-3186
+      Row nr = its[i].f->row(id);
+      if (i == 0 && filter) rows[i] = nr.intersect(*filter);
+      else if (i == 0 || i == rows.size() - 1) rows[i] = nr;
+      else rows[i] = nr.intersect(rows[i - 1]);
+      ids[i] = id;
+    }
+    void next_at(size_t i) {  // :3167-3191
+      for (;;) {
+        uint64_t id; bool wrapped;
+        if (!its[i].next(&id, &wrapped)) { done = true; return; }
+        if (wrapped && i != 0) next_at(i - 1);
+        // The reference keeps looping here after the recursion has set done; with >= 3 fields and no
+        // non-empty row left at this level that loop never ends (the iterator wraps for ever). Stop instead.
+        if (done) return;
+        set_row(i, id);
+        if (rows[i].count() != 0) break;
+      }
+    }
+    bool next(GroupCount* out) {  // :3193-3230
+      uint64_t count;
+      for (;;) {
+        if (done) return false;
+        const size_t k = rows.size();
+        count = k == 1 ? rows[0].count() : rows[k - 1].intersection_count(rows[k - 2]);
+        if (count == 0) { next_at(k - 1); continue; }
+        break;
+      }
+      out->rows = ids;
+      out->count = count;
+      next_at(rows.size() - 1);
+      return true;
+    }
+  };
+  std::vector<GroupCount> group_by_shard(const std::vector<GroupByChild>& ch, const pb200_node* filt, uint32_t nf, uint64_t limit,
+                                         uint64_t shard) const {
+    Row filter_row;
+    GroupByIter g;
+    if (filt && nf) { filter_row = eval_shard(filt, nf, shard); g.filter = &filter_row; }
+    const size_t k = ch.size();
+    g.its.resize(k); g.rows.resize(k); g.ids.assign(k, 0);
+    bool ignore_prev = false;
+    for (size_t i = 0; i < k; i++) {  // newGroupByIterator :3086-3165
+      Fragment* f = holder->fragment(ch[i].fam, shard);
+      if (!f) return {};  // "this whole shard doesn't have all it needs to continue"
+      Fragment::RowsOpts o;
+      if (!ch[i].child_rows.empty()) o.in_rows = &ch[i].child_rows;
+      g.its[i].f = f; g.its[i].ids = f->rows(o); g.its[i].wrap = i != 0;
+      uint64_t prev = ch[i].prev;
+      if (ch[i].has_prev && !ignore_prev) {
+        if (i == k - 1) prev++;
+        g.its[i].seek(prev);
+      }
+      uint64_t id; bool wrapped;
+      if (!g.its[i].next(&id, &wrapped)) { g.done = true; break; }
+      g.rows[i] = f->row(id); g.ids[i] = id;
+      if (ch[i].has_prev && id != prev) ignore_prev = true;
+      if (wrapped) {
+        bool dead = false;
+        for (size_t j = i; j-- > 0;) {
+          uint64_t id2; bool w2;
+          if (!g.its[j].next(&id2, &w2)) { dead = true; break; }
+          g.rows[j] = g.its[j].f->row(id2); g.ids[j] = id2;
+          if (!w2) break;
+        }
+        if (dead) { g.done = true; break; }
+      }
+    }
+    if (!g.done) {
+      if (g.filter && k > 0) g.rows[0] = g.rows[0].intersect(*g.filter);
+      for (size_t i = 1; i + 1 < k; i++) g.rows[i] = g.rows[i].intersect(g.rows[i - 1]);
+    }
+    std::vector<GroupCount> results;  // executeGroupByShard :1262-1274
+    GroupCount gc;
+    while (results.size() < limit && g.next(&gc))
+      if (gc.count > 0) results.push_back(gc);
+    return results;
+  }
+  static int group_compare(const GroupCount& a, const GroupCount& b) {  // :1203-1214
+    for (size_t i = 0; i < a.rows.size(); i++) {
+      if (a.rows[i] < b.rows[i]) return -1;
+      if (a.rows[i] > b.rows[i]) return 1;
+    }
+    return 0;
+  }
+  static std::vector<GroupCount> merge_group_counts(std::vector<GroupCount> a, const std::vector<GroupCount>& b, uint64_t limit) {  // :1166-1200
+    limit = std::min<uint64_t>(limit, a.size() + b.size());
+    std::vector<GroupCount> ret;
+    size_t i = 0, j = 0;
+    while (i < a.size() && j < b.size() && ret.size() < limit) {
+      const int c = group_compare(a[i], b[j]);
+      if (c < 0) ret.push_back(a[i++]);
+      else if (c == 0) { a[i].count += b[j].count; ret.push_back(a[i]); i++; j++; }
+      else ret.push_back(b[j++]);
+    }
+    for (; i < a.size() && ret.size() < limit; i++) ret.push_back(a[i]);
+    for (; j < b.size() && ret.size() < limit; j++) ret.push_back(b[j]);
+    return ret;
+  }
+  // executeGroupBy's map-reduce (:1122-1137); offset / final limit are applied by the caller (:1139-1157)
+  std::vector<GroupCount> group_by(const std::vector<GroupByChild>& ch, const pb200_node* filt, uint32_t nf, uint64_t limit,
+                                   const std::vector<uint64_t>& shards) const {
+    if (ch.empty()) throw std::runtime_error("need at least one child call");
+    auto per = map_shards<std::vector<GroupCount>>(shards, [&](uint64_t shard) { return group_by_shard(ch, filt, nf, limit, shard); });
+    std::vector<GroupCount> acc;
+    for (auto& v : per) acc = merge_group_counts(acc, v, limit);
+    return acc;
   }
 
   // executor.go:409-442 + 683-721 (Base is added by the caller)

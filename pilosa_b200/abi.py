@@ -42,6 +42,44 @@ class Pair(C.Structure):
     _fields_ = [("id", C.c_uint64), ("count", C.c_uint64)]
 
 
+GROUPBY_MAX_FIELDS = 4
+NO_LIMIT = (1 << 64) - 1
+ROWS_COLUMN = 1
+
+
+class GroupByChild(C.Structure):
+    """pb200_groupby_child — one Rows() child of a GroupBy (executor.go:1091-1118)."""
+
+    _fields_ = [("family", C.c_uint32), ("has_previous", C.c_uint32), ("previous", C.c_uint64),
+                ("rows", C.POINTER(C.c_uint64)), ("n_rows", C.c_uint64)]
+
+
+class Group(C.Structure):
+    """pb200_group — GroupCount (executor.go:1160-1164) with row ids only."""
+
+    _fields_ = [("rows", C.c_uint64 * GROUPBY_MAX_FIELDS), ("count", C.c_uint64)]
+
+
+def pack_groupby_children(children):
+    """children: [(family, previous or None, rows list or None)] -> (ctypes array, keep-alive list)."""
+    arr = (GroupByChild * max(1, len(children)))()
+    keep = []
+    for i, (fam, prev, rows) in enumerate(children):
+        arr[i].family = fam
+        arr[i].has_previous = 0 if prev is None else 1
+        arr[i].previous = 0 if prev is None else prev
+        if rows:
+            a = (C.c_uint64 * len(rows))(*rows)
+            keep.append(a)
+            arr[i].rows = C.cast(a, C.POINTER(C.c_uint64))
+            arr[i].n_rows = len(rows)
+    return arr, keep
+
+
+def unpack_groups(out, n, k):
+    return [(tuple(out[i].rows[j] for j in range(k)), out[i].count) for i in range(n)]
+
+
 class Timing(C.Structure):
     _fields_ = [
         ("kernel_ms", C.c_double),

@@ -413,9 +413,12 @@ struct TNode {
   std::vector<int> kids;
 };
 
+constexpr uint32_t kOpInternalTemp = 0x100;  // leaf = dense temp row slot `row`; engine-internal (GroupBy), refused from the C ABI
+
 struct Compiler {
   pb200_ctx* ctx;
   Compiled& out;
+  bool internal_ok = false;
   uint32_t leaf_base = 0;
   std::vector<TNode> tree;
   std::string err;
@@ -485,6 +488,10 @@ struct Compiler {
           st.push_back(leaf_node(add_leaf(L_ROW, nd.family, nd.row)));
           break;
         case PB200_OP_EMPTY: st.push_back(leaf_node(add_leaf(L_ZERO, 0, 0))); break;
+        case kOpInternalTemp:
+          if (!internal_ok) { err = "unknown op " + std::to_string(nd.op); return false; }
+          st.push_back(leaf_node(add_leaf(L_TEMP, uint32_t(nd.row), 0)));
+          break;
         case PB200_OP_BSI_RANGE: {
           if (nd.family >= ctx->families.size()) { err = "unknown family in BSI range"; return false; }
           if (nd.bsi_op < PB200_BSI_EQ || nd.bsi_op > PB200_BSI_NOTNULL) { err = "invalid range operation"; return false; }
@@ -672,8 +679,9 @@ uint32_t max_leaves_of(const Compiled& cp) {
 }
 
 // Compiles a batch of post-order programs.
-int compile_batch(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries, Compiled& cp) {
+int compile_batch(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries, Compiled& cp, bool internal_ok = false) {
   Compiler cc(ctx, cp);
+  cc.internal_ok = internal_ok;
   for (uint32_t q = 0; q < n_queries; q++) {
     const uint32_t b = prog_off[q], e = prog_off[q + 1];
     if (e < b) return fail(ctx, PB200_ERR_INVALID, "prog_off not ascending");
@@ -804,6 +812,7 @@ int count_impl(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off
 }  // namespace
 
 #include "engine_queries.inl"
+#include "engine_groupby.inl"
 
 extern "C" int pb200_count(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards, uint64_t* out_count) {
   ENTER(ctx);

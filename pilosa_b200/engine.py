@@ -78,6 +78,8 @@ def load_library() -> C.CDLL:
         "pb200_count_pairs_noalloc": (i32, [vp, u32, vp, u32, vp, u32, vp]),
         "pb200_eval": (i32, [vp, np_, u32, u64, C.c_char_p, sz, C.POINTER(sz)]),
         "pb200_eval_columns": (i32, [vp, np_, u32, u64, u64p, sz, C.POINTER(sz)]),
+        "pb200_rows": (i32, [vp, u32, u64, u32, u64, u64, u64p, u32, u64p, sz, C.POINTER(sz)]),
+        "pb200_groupby": (i32, [vp, vp, u32, np_, u32, u64, u64p, u32, vp, sz, C.POINTER(sz)]),
         "pb200_eval_shards": (i32, [vp, np_, u32, u64p, u32, vp, sz, u64p, C.POINTER(sz)]),
         "pb200_topn": (i32, [vp, u32, np_, u32, u32, u64p, sz, u64, u64, u32, u64p, u32, pp, sz, C.POINTER(sz)]),
         "pb200_topn_shard": (i32, [vp, u32, np_, u32, u32, u64p, sz, u64, u64, u64, pp, sz, C.POINTER(sz)]),
@@ -276,6 +278,35 @@ class Engine:
         buf, off = self.eval_shards_raw(prog, shards)
         mv = memoryview(buf)
         return [bytes(mv[off[i]: off[i + 1]]) for i in range(len(shards))]
+
+    def rows(self, fam, shards, start=0, column=None, limit=None) -> List[int]:
+        from .abi import NO_LIMIT, ROWS_COLUMN
+        cap = 1 << 16
+        while True:
+            out, n = (C.c_uint64 * cap)(), C.c_size_t()
+            rc = self.lib.pb200_rows(self._h, fam, start, 0 if column is None else ROWS_COLUMN, column or 0,
+                                     NO_LIMIT if limit is None else limit, u64_array(shards), len(shards), out, cap, C.byref(n))
+            if rc == -6 and n.value > cap:  # PB200_ERR_RANGE: retry with the size the call reported
+                cap = n.value
+                continue
+            self._check(rc)
+            return list(out[: n.value])
+
+    def groupby(self, children, filter_prog, limit, shards):
+        """children: [(family, previous or None, rows or None)]; returns [((row ids), count)]."""
+        from .abi import NO_LIMIT, Group, pack_groupby_children, unpack_groups
+        arr, keep = pack_groupby_children(children)
+        fp, nf = (filter_prog, len(filter_prog)) if filter_prog is not None else (None, 0)
+        cap = 1 << 14
+        while True:
+            out, n = (Group * cap)(), C.c_size_t()
+            rc = self.lib.pb200_groupby(self._h, arr, len(children), fp, nf, NO_LIMIT if limit is None else limit,
+                                        u64_array(shards), len(shards), out, cap, C.byref(n))
+            if rc == -6 and n.value > cap:
+                cap = n.value
+                continue
+            self._check(rc)
+            return unpack_groups(out, n.value, len(children))
 
     def eval_columns(self, prog, shard: int) -> List[int]:
         n = C.c_size_t()

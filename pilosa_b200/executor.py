@@ -19,7 +19,7 @@ from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
 
 from . import abi
-from .abi import Call, flatten
+from .abi import SHARD_WIDTH, Call, flatten
 
 EXISTENCE_FIELD = "exists"  # index.go existenceFieldName
 
@@ -252,6 +252,62 @@ class Executor:
         p2 = self.be.topn(fam, sp, n, local, ids=ids2, min_threshold=threshold, tanimoto=tanimoto, remote=True) if local else []
         out = _merge_pairs(self._allgather(p2))
         return out[:n] if n else out
+
+
+    def rows(self, field_name: str, shards: Sequence[int], previous: Optional[int] = None, limit: Optional[int] = None,
+             column: Optional[int] = None) -> List[int]:  # executeRows :1277 (standard view)
+        if column is not None:
+            shards = [column // SHARD_WIDTH]  # :1291-1293
+        local = self.local_shards(shards)
+        start = 0 if previous is None else previous + 1
+        mine = self.be.rows(self.family(field_name), local, start=start, column=column, limit=limit) if local else []
+        if self.world == 1:
+            return mine
+        merged = sorted(set().union(*[set(x or []) for x in self._allgather(mine)]))  # RowIDs.merge :1043
+        return merged if limit is None else merged[:limit]
+
+    def group_by(self, children: Sequence["RowsCall"], shards: Sequence[int], filter_call: Optional[Call] = None,
+                 limit: Optional[int] = None, offset: Optional[int] = None) -> List[Tuple[Tuple[int, ...], int]]:
+        """executeGroupBy (executor.go:1071-1158): [((row id per field), count)] in ascending group order."""
+        if not children:
+            raise ValueError("need at least one child call")  # :1073
+        packed = []
+        for ch in children:
+            for name in (ch.field,):
+                if name not in self.fields:
+                    raise KeyError("field not found")  # ErrFieldNotFound :3104
+            pre = None
+            if ch.limit is not None or ch.column is not None:  # executed cluster-wide first (:1105-1116)
+                pre = self.rows(ch.field, shards, previous=ch.previous, limit=ch.limit, column=ch.column)
+                if not pre:
+                    return []
+            packed.append((self.family(ch.field), ch.previous, pre))
+        fp = self.program(filter_call) if filter_call is not None else None
+        local = self.local_shards(shards)
+        mine = self.be.groupby(packed, fp, limit, local) if local else []
+        if self.world > 1:  # mergeGroupCounts :1166 over the ranks' partial lists
+            acc: Dict[Tuple[int, ...], int] = {}
+            for lst in self._allgather(mine):
+                for g, c in lst or []:
+                    acc[g] = acc.get(g, 0) + c
+            mine = sorted(acc.items())
+            if limit is not None:
+                mine = mine[:limit]
+        if offset is not None and offset < len(mine):  # :1140-1146
+            mine = mine[offset:]
+        if limit is not None and limit < len(mine):    # :1148-1156
+            mine = mine[:limit]
+        return mine
+
+
+@dataclass
+class RowsCall:
+    """A Rows() child of GroupBy / a Rows query: Rows(field[, previous=][, limit=][, column=])."""
+
+    field: str
+    previous: Optional[int] = None
+    limit: Optional[int] = None
+    column: Optional[int] = None
 
 
 def builtins_max(a, b):

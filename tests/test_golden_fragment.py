@@ -332,3 +332,83 @@ def test_shift_overflow_in_set_ops(w):
         assert w.ex.count(call, shards) == len(got), repr(call)
     assert w.ex.row_columns(Intersect(s1, s3), [0]) == [6, SW]
     assert w.ex.row_columns(Union(s1, Row("general", 2)), [0, 1]) == [6, SW - 1, SW, SW]  # both segments hold column SW
+
+
+# ---- executor_test.go:3244-3284 TestExecutor_Execute_Rows ----
+def _import_bits(w, field, bits):
+    if field not in w.cpu.fields:
+        w.create_field(field)
+    for row, col in bits:
+        w.set_bit(field, row, col)
+
+
+def test_executor_rows(w):
+    _import_bits(w, "general", [(10, 0), (10, SW + 1), (11, 2), (11, SW + 2), (12, 2), (12, SW + 2), (13, 3)])
+    sh = [0, 1]
+    assert w.ex.rows("general", sh) == [10, 11, 12, 13]
+    assert w.ex.rows("general", sh, limit=2) == [10, 11]
+    assert w.ex.rows("general", sh, previous=10, limit=2) == [11, 12]
+    assert w.ex.rows("general", sh, column=2) == [11, 12]
+    assert w.ex.rows("general", sh, column=SW + 2, limit=1) == [11]
+    assert w.ex.rows("general", sh, previous=13) == []
+    assert w.ex.rows("general", [7]) == []
+
+
+# ---- executor_test.go:3568-3890 TestExecutor_Execute_GroupBy ----
+def test_executor_group_by(w):
+    from pilosa_b200.executor import RowsCall as R
+
+    sh = [0, 1, 2, 3]
+    _import_bits(w, "general", [(10, 0), (10, 1), (10, SW + 1), (11, 2), (11, SW + 2), (12, 2), (12, SW + 2)])
+    _import_bits(w, "sub", [(100, 0), (100, 1), (100, 3), (100, SW + 1), (110, 2), (110, 0)])
+    with pytest.raises(ValueError, match="need at least one child call"):
+        w.ex.group_by([], sh)
+    with pytest.raises(KeyError):
+        w.ex.group_by([R("missing")], sh)
+    basic = [((10, 100), 3), ((10, 110), 1), ((11, 110), 1), ((12, 110), 1)]
+    assert w.ex.group_by([R("general"), R("sub")], sh) == basic
+    assert w.ex.group_by([R("general"), R("sub")], sh, filter_call=Row("general", 10)) == basic[:2]   # "Filter"
+    assert w.ex.group_by([R("general", previous=10)], sh) == [((11,), 2), ((12,), 2)]                 # "check field offset no limit"
+    assert w.ex.group_by([R("general", previous=10)], sh, limit=1) == [((11,), 2)]                    # "check field offset limit"
+    assert w.ex.group_by([R("general")], sh, filter_call=Row("sub", 110)) == [((10,), 1), ((11,), 1), ((12,), 1)]
+    # limit already trims the reduce (executor.go:1076-1081,1129), offset is applied to what is left (:1140-1146)
+    assert w.ex.group_by([R("general"), R("sub")], sh, offset=1, limit=2) == basic[1:2]
+    assert w.ex.group_by([R("general"), R("sub")], sh, offset=1) == basic[1:]
+
+    _import_bits(w, "a", [(0, 1), (1, SW + 1)])
+    _import_bits(w, "b", [(0, SW + 1), (1, 1)])
+    assert w.ex.group_by([R("a"), R("b")], sh, limit=1) == [((0, 1), 1)]                              # "tricky data"
+
+    same = [(0, 0), (0, 1), (0, 2), (1, 1), (2, 0), (2, 2), (3, 3)]
+    for f in ("wa", "wb", "wc"):
+        _import_bits(w, f, same)
+    assert w.ex.group_by([R("wa"), R("wb"), R("wc", previous=1)], sh, limit=3) == \
+        [((0, 0, 2), 2), ((0, 1, 0), 1), ((0, 1, 1), 1)]                                              # "test wrapping with previous"
+    assert w.ex.group_by([R("wa", previous=3), R("wb", previous=3), R("wc", previous=3)], sh, limit=3) == []   # "previous is last result"
+    assert w.ex.group_by([R("wa"), R("wb", previous=2), R("wc", previous=2)], sh, limit=1) == [((1, 0, 0), 1)]  # "test wrapping multiple"
+
+    m = [(0, 0), (1, SW), (2, 0), (3, SW)]
+    _import_bits(w, "ma", m)
+    _import_bits(w, "mb", m)
+    assert w.ex.group_by([R("ma"), R("mb")], sh, limit=5) == [((0, 0), 1), ((0, 2), 1), ((1, 1), 1), ((1, 3), 1), ((2, 0), 1)]
+    assert w.ex.group_by([R("ma"), R("mb", limit=2)], sh, limit=5) == [((0, 0), 1), ((1, 1), 1), ((2, 0), 1), ((3, 1), 1)]
+    assert w.ex.group_by([R("ma"), R("mb", column=SW)], sh, limit=5) == [((1, 1), 1), ((1, 3), 1), ((3, 1), 1), ((3, 3), 1)]
+
+    n = [(0, 0), (0, SW), (1, 0), (1, SW)]
+    _import_bits(w, "na", n)
+    _import_bits(w, "nb", n)
+    assert w.ex.group_by([R("na"), R("nb")], sh) == [((0, 0), 2), ((0, 1), 2), ((1, 0), 2), ((1, 1), 2)]   # "same rows in different shards"
+
+    pp = [(0, 0), (1, 0), (2, 0), (3, 0), (3, 91000), (3, SW), (3, SW * 2), (3, SW * 3)]
+    for f in ("ppa", "ppb", "ppc"):
+        _import_bits(w, f, pp)
+    total = w.ex.group_by([R("ppa"), R("ppb"), R("ppc")], sh, limit=3)                                # paging with previous
+    res = total
+    while len(total) < 64:
+        last = res[-1][0]
+        res = w.ex.group_by([R("ppa", previous=last[0]), R("ppb", previous=last[1]), R("ppc", previous=last[2])], sh, limit=3)
+        assert res, "paging stalled"
+        total += res
+    exp = [((i // 16, (i % 16) // 4, i % 4), 1) for i in range(64)]
+    exp[63] = ((3, 3, 3), 5)
+    assert total == exp

@@ -185,6 +185,48 @@ def test_shift_with_carry_out_of_the_shard(pair):
     assert g.min("v", shards, src) == c.min("v", shards, src)
 
 
+def test_rows(pair):
+    g, c, shards = pair
+    col = (5 << 20) + 12345
+    for fld in ("f", "m", "sp", "z", "exists"):
+        for kw in (dict(), dict(limit=3), dict(previous=2), dict(previous=1, limit=2), dict(column=777), dict(column=col), dict(column=col, limit=5),
+                   dict(previous=10 ** 9), dict(limit=0)):
+            assert g.rows(fld, shards, **kw) == c.rows(fld, shards, **kw), (fld, kw)
+
+
+def test_group_by(pair):
+    """GroupBy (executor.go:1071-1275, :3060-3230): every combination counted on the device, iterator rules
+    replayed on the host, against the oracle's literal restatement of the nested iterator."""
+    from pilosa_b200.executor import RowsCall as R
+
+    g, c, shards = pair
+    flt = Intersect(Row("exists", 0), Union(Row("f", 1), Row("m", 2)))
+    cases = [
+        ([R("f")], {}), ([R("f")], dict(filter_call=flt)), ([R("m")], dict(filter_call=Row("sp", 1), limit=3)),
+        ([R("f"), R("m")], {}), ([R("f"), R("m")], dict(filter_call=flt)), ([R("f"), R("m")], dict(limit=7)),
+        ([R("m"), R("sp")], dict(filter_call=Row("f", 0))), ([R("sp"), R("sp")], {}),
+        ([R("z", limit=12), R("f")], dict(limit=40)), ([R("f"), R("z", previous=100, limit=9)], {}),
+        ([R("f", previous=2), R("m", previous=3)], dict(limit=10)), ([R("f", previous=5), R("m", previous=7)], {}),
+        ([R("f", previous=77), R("m")], {}), ([R("m", column=(2 << 20) + 5), R("f")], {}),
+        ([R("f"), R("m"), R("sp")], {}), ([R("f"), R("m"), R("sp")], dict(filter_call=flt, limit=25)),
+        ([R("f", previous=1), R("m", previous=7), R("sp", previous=3)], dict(limit=6)),
+        ([R("f", previous=1), R("m", previous=2), R("sp", previous=1)], dict(filter_call=Row("exists", 0))),
+        ([R("sp"), R("f"), R("m"), R("sp")], dict(limit=50)),
+        ([R("f"), R("m")], dict(filter_call=g.row_range("v", abi.BSI_GT, 0))),
+        ([R("f"), R("m")], dict(filter_call=Row("f", 99))),      # empty filter
+        ([R("f"), R("w")], {}),                                   # int field: its standard view has no fragments
+    ]
+    nonempty = 0
+    for children, kw in cases:
+        fams_ok = all(ch.field in g.fields for ch in children)
+        if not fams_ok:
+            continue
+        got = g.group_by(children, shards, **kw)
+        assert got == c.group_by(children, shards, **kw), (children, kw)
+        nonempty += bool(got)
+    assert nonempty >= 15
+
+
 def test_topn(pair):
     g, c, shards = pair
     src = Intersect(Row("f", 1), Row("f", 2))
