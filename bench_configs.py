@@ -77,7 +77,8 @@ def emit(rows, name, query, n_shards, kernel_ms, wall_ms, algo_bytes, launches, 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--configs", default="c1,c2,c3,c4,c5")
+    ap.add_argument("--configs", default="c1,c2,c3,c4,c5,gb")
+    ap.add_argument("--gb-shards", type=int, default=256)
     ap.add_argument("--reps", type=int, default=7)
     ap.add_argument("--c2-shards", type=int, default=1024)
     ap.add_argument("--c3-shards", type=int, default=1024)
@@ -213,6 +214,25 @@ def main():
             flat, off = eng.pack_programs([prog] * 256)
             _, k, wms, ab, ln = timed(eng, lambda: eng.count_batch_raw(flat, off, 256, sh_arr, n), args.reps)
             emit(rows, "C5", f"batch of 256 x same query, {n} shards (per-query figures)", n, k / 256, wms / 256, ab // 256, ln, cms, len(csh), True)
+
+    # ---------------- GB: GroupBy over two / three set fields ----------------
+    if "gb" in cfgs:
+        from pilosa_b200.executor import RowsCall as R
+        shards = list(range(args.gb_shards))
+        cpu_sh = shards[: max(4, args.cpu_shards // 4)]
+        for name, nrows, p_ in (("ga", 16, 0.10), ("gb", 64, 0.02), ("gc", 8, 0.25)):
+            both(name)
+            load_parallel(lambda s, nrows=nrows, p_=p_, name=name: synth.bernoulli(s, 0, nrows, p_, SEED + len(name) + nrows), shards,
+                          sinks_for(name, set(cpu_sh)), cores)
+        both("gf")
+        load_parallel(lambda s: synth.bernoulli(s, 1, 1, 0.5, SEED + 99), shards, sinks_for("gf", set(cpu_sh)), cores)
+        for qname, ch, kw in (("GroupBy(Rows(ga), Rows(gb)) [16 x 64 groups]", [R("ga"), R("gb")], {}),
+                              ("GroupBy(Rows(ga), Rows(gb), filter=Row(gf=1))", [R("ga"), R("gb")], dict(filter_call=Row("gf", 1))),
+                              ("GroupBy(Rows(gc), Rows(ga), Rows(gb)) [8 x 16 x 64 groups]", [R("gc"), R("ga"), R("gb")], {})):
+            _, k, wms, ab, ln = timed(eng, lambda: g.group_by(ch, shards, **kw), max(3, args.reps // 2))
+            got = g.group_by(ch, cpu_sh, **kw)
+            exp, cms = cpu_timed(lambda: c.group_by(ch, cpu_sh, **kw))
+            emit(rows, "GB", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp, {"groups": len(got)})
 
     print("\n| config | query | shards | kernel ms | call ms | algorithmic GB/s | CPU ms (all shards, %d cores) | call speed-up |" % cores, file=sys.stderr)
     print("|---|---|---|---|---|---|---|---|", file=sys.stderr)
