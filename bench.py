@@ -362,7 +362,7 @@ def main():
         def run_e2e(idx):
             """Every step: programs host->device, kernel, counts device->host. On one GPU the host
             prepares step i+1 while step i runs (two batches in flight); with N GPUs the NCCL
-            all-reduce of the device-resident counts sits between _begin and _end."""
+            all-reduce of the device-resident counts is queued right behind each batch's kernel."""
             if world == 1:
                 begin(idx[0])
                 for n in range(len(idx)):
@@ -370,10 +370,14 @@ def main():
                         begin(idx[n + 1])
                     eng.count_batch_end(out_e2e)                           # D2H on the copy stream + wait
             else:
-                for i in idx:
+                def begin_reduce(i):
                     begin(i)
                     t = torch.as_tensor(DevArray(eng.count_batch_device(), B), device="cuda")
-                    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+                    dist.all_reduce(t, op=dist.ReduceOp.SUM)   # in place in HBM, queued behind the kernel
+                begin_reduce(idx[0])
+                for n in range(len(idx)):
+                    if n + 1 < len(idx):
+                        begin_reduce(idx[n + 1])                 # the next batch is queued before this one is fetched
                     eng.count_batch_end(out_e2e)
 
         run_e2e(list(range(args.warmup)))

@@ -189,11 +189,13 @@ int pb200_count_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
  * stream) and waits for them. Two uses:
  *  - pipelining: up to two batches may be in flight per context, so a host calls
  *    _begin(i+1) before _end(i) and its compile/upload work overlaps the kernels of batch i;
- *  - merging across GPUs: with ONE batch in flight, the per-query partial counts are
- *    resident in HBM at *device_counts (uint64[n_queries], the most recently begun batch)
- *    where an NCCL all-reduce over NVLink, enqueued on the context's stream, sums them in
- *    place (the reduceFn of executor.go:1813 across devices); _end then waits for that
- *    work too. Do not issue another _begin between a collective and its _end. */
+ *  - merging across GPUs: the per-query partial counts of the most recently begun batch are
+ *    resident in HBM at *device_counts (uint64[n_queries]) where an NCCL all-reduce over
+ *    NVLink, enqueued on the context's stream right after _device, sums them in place (the
+ *    reduceFn of executor.go:1813 across devices). Work queued on the context's stream
+ *    between _device and the next _begin / _end call belongs to that batch: its _end waits
+ *    for it too, so the two uses combine (_begin, _device + all-reduce, _begin, _device +
+ *    all-reduce, _end, ...). */
 int pb200_count_batch_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off,
                             uint32_t n_queries, const uint64_t* shards, uint32_t n_shards);
 int pb200_count_batch_device(pb200_ctx* ctx, void** device_counts);

@@ -697,8 +697,12 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
                 uint32_t n_shards, bool per_shard) {
   TRY(validate_shards(ctx, shards, n_shards));
   if (ctx->n_pending >= 2) return fail(ctx, PB200_ERR_INVALID, "two Count batches already in flight: call pb200_count_batch_end first");
+  // The older batch's device counts were handed out: whatever the caller queued on the compute stream since
+  // (an in-place NCCL all-reduce) belongs to that batch, so its `done` moves behind it before new work is queued.
+  if (ctx->n_pending == 1 && ctx->slots[ctx->head].external) CUDA_TRY(ctx, cudaEventRecord(ctx->slots[ctx->head].done, ctx->stream));
   const int si = (ctx->head + ctx->n_pending) & 1;
   CountSlot& sl = ctx->slots[si];
+  sl.external = false;
   if (!sl.k0) {
     CUDA_TRY(ctx, cudaEventCreate(&sl.k0)); CUDA_TRY(ctx, cudaEventCreate(&sl.k1));
     CUDA_TRY(ctx, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
@@ -846,7 +850,9 @@ extern "C" int pb200_count_batch_device(pb200_ctx* ctx, void** device_counts) {
   ENTER(ctx);
   if (!device_counts) return PB200_ERR_INVALID;
   *device_counts = count_device_ptr(ctx);
-  return *device_counts ? PB200_OK : fail(ctx, PB200_ERR_INVALID, "no Count batch in flight");
+  if (!*device_counts) return fail(ctx, PB200_ERR_INVALID, "no Count batch in flight");
+  ctx->slots[(ctx->head + ctx->n_pending - 1) & 1].external = true;
+  return PB200_OK;
 }
 
 extern "C" int pb200_count_batch_end(pb200_ctx* ctx, uint64_t* out_counts) {

@@ -74,6 +74,7 @@ struct CountSlot {
   cudaEvent_t k0 = nullptr, k1 = nullptr, done = nullptr;
   size_t n_out = 0;
   bool launched = false;
+  bool external = false;  // the caller took the device counts (pb200_count_batch_device) and may have queued work on them
   uint64_t seq = 0;  // begin order
 };
 

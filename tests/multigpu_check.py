@@ -60,6 +60,18 @@ def main():
         checks.append((f"count(v>{x})", g.count(g.row_range("v", abi.BSI_GT, x), shards), c.count(c.row_range("v", abi.BSI_GT, x), shards)))
     for kw in (dict(n=10), dict(n=10, src=src), dict(n=5, src=Row("m", 1), threshold=3), dict(n=10, src=src, ids=[1, 2, 3, 399])):
         checks.append((f"topn/{kw}", g.topn("z", shards, **kw), c.topn("z", shards, **kw)))
+    from pilosa_b200.executor import RowsCall as R
+    for kw in (dict(), dict(limit=3), dict(previous=1, limit=2), dict(column=(3 << 20) + 17)):
+        checks.append((f"rows/{kw}", g.rows("z", shards, **kw), c.rows("z", shards, **kw)))
+    for ch, kw in (([R("f"), R("m")], {}), ([R("f"), R("m")], dict(filter_call=src, limit=5)), ([R("z", limit=6), R("f")], {}),
+                   ([R("f", previous=1), R("m", previous=2)], {}), ([R("f"), R("m"), R("f")], dict(limit=20))):
+        checks.append((f"groupby/{ch}/{kw}", g.group_by(ch, shards, **kw), c.group_by(ch, shards, **kw)))
+    # bitmap-returning calls stay sharded: every rank checks its own segments against the oracle's
+    from pilosa_b200.abi import Shift
+    for call in (src, Union(Row("m", 0), Row("f", 1)), Shift(Row("f", 1), n=1), g.row_range("v", abi.BSI_LT, -5)):
+        mine = g.row_segments(call, shards)
+        exp = [(s, b) for s, b in c.row_segments(call, shards) if s % world == rank]
+        checks.append((f"segments/{call!r}", mine, exp))
     bad = [(n, a, b) for n, a, b in checks if a != b]
     ok = torch.tensor([0 if bad else 1], device="cuda")
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
