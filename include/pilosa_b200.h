@@ -144,6 +144,17 @@ int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t shard,
                      const uint64_t* set_pos, size_t n_set,
                      const uint64_t* clear_pos, size_t n_clear);
 
+/* Union (clear = 0) or subtract (clear = 1) a serialized roaring bitmap of fragment positions
+ * (row * 2^20 + column % 2^20) into the resident fragment and report how many bits changed:
+ * fragment.importRoaring (fragment.go:2243) -> Bitmap.ImportRoaringBits (roaring.go:1463-1558).
+ * `data` is either Pilosa roaring (with ops log) or the OFFICIAL roaring format with 16-bit
+ * keys that /import-roaring receives (readOfficialHeader .. readWithRuns roaring.go:5075-5245;
+ * run payloads are start:length there). The fragment is created if the shard had none. The
+ * rank-cache recount (fragment.go:2080-2095) stays with the Go side, which follows up with
+ * pb200_rank_set. */
+int pb200_frag_import_roaring(pb200_ctx* ctx, pb200_family family, uint64_t shard,
+                              const void* data, size_t len, int clear, int64_t* changed);
+
 /* fragment.go:574 closeStorage / drop of a fragment. */
 int pb200_frag_drop(pb200_ctx* ctx, pb200_family family, uint64_t shard);
 

@@ -90,6 +90,8 @@ def lib() -> C.CDLL:
         "orc_count_shards": (C.c_int, [vp, np_, C.c_uint32, u64p, C.c_uint32, C.c_int, u64p]),
         "orc_eval_columns": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, u64p, sz, C.POINTER(sz)]),
         "orc_eval_roaring": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, C.c_char_p, sz, C.POINTER(sz)]),
+        "orc_frag_drop": (C.c_int, [vp, C.c_uint32, C.c_uint64]),
+        "orc_frag_import_roaring": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_char_p, sz, C.c_int, C.POINTER(C.c_int64)]),
         "orc_rows": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, u64p, C.c_uint32, u64p, sz, C.POINTER(sz)]),
         "orc_groupby": (C.c_int, [vp, C.c_void_p, C.c_uint32, np_, C.c_uint32, C.c_uint64, u64p, C.c_uint32, C.c_void_p, sz, C.POINTER(sz)]),
         "orc_topn": (C.c_int, [vp, C.c_uint32, np_, C.c_uint32, C.c_uint32, u64p, sz, C.c_uint64, C.c_uint64, C.c_uint32, u64p,
@@ -394,6 +396,14 @@ class Oracle:
         sp, ns = (src_prog, len(src_prog)) if src_prog is not None else (None, 0)
         return self._pairs(lib().orc_topn_shard, self._h, fam, sp, ns, n, u64_array(ids) if ids else None, len(ids),
                            min_threshold, tanimoto, shard)
+
+    def frag_drop(self, fam, shard) -> None:
+        _check(lib().orc_frag_drop(self._h, fam, shard))
+
+    def frag_import_roaring(self, fam, shard, data: bytes, clear: bool = False) -> int:
+        n = C.c_int64()
+        _check(lib().orc_frag_import_roaring(self._h, fam, shard, data, len(data), int(clear), C.byref(n)))
+        return n.value
 
     def rows(self, fam, shards, start=0, column=None, limit=None):
         from pilosa_b200.abi import NO_LIMIT, ROWS_COLUMN

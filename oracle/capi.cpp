@@ -141,8 +141,8 @@ size_t orc_bitmap_serialize(void* b, int do_optimize, uint8_t* out, size_t cap) 
   if (out && cap >= v.size()) std::copy(v.begin(), v.end(), out);
   return v.size();
 }
-void* orc_bitmap_deserialize(const uint8_t* data, size_t len) {
-  try { return new Bitmap(deserialize(data, len)); }
+void* orc_bitmap_deserialize(const uint8_t* data, size_t len) {  // Bitmap.UnmarshalBinary: either format
+  try { return new Bitmap(unmarshal_binary(data, len)); }
   catch (const std::exception& e) { g_err = e.what(); return nullptr; }
 }
 // append an op record (typ 0..3) to a byte buffer held by the caller: returns encoded bytes
@@ -278,6 +278,31 @@ int orc_topn_shard(void* h, uint32_t fam, const pb200_node* src, uint32_t nsrc, 
     auto r = ((Orc*)h)->exec.topn_shard(fam, src, nsrc, n, vec(ids, nids), min_threshold, tanimoto, shard);
     *n_out = r.size();
     for (size_t i = 0; i < r.size() && i < cap; i++) out[i] = {r[i].id, r[i].count};
+  });
+}
+// fragment.importRoaring (fragment.go:2243-2330): ImportRoaringBits into storage, then the rank cache
+// entries of the touched rows are refreshed from exact counts (:2080-2095)
+int orc_frag_drop(void* h, uint32_t fam, uint64_t shard) {
+  return guard([&] {
+    auto& fams = ((Orc*)h)->holder.families;
+    if (fam >= fams.size()) throw std::runtime_error("unknown family");
+    fams[fam].erase(shard);
+  });
+}
+int orc_frag_import_roaring(void* h, uint32_t fam, uint64_t shard, const uint8_t* data, size_t len, int clear, int64_t* changed) {
+  return guard([&] {
+    Fragment* f = ((Orc*)h)->holder.fragment(fam, shard, true);
+    Bitmap other = unmarshal_binary(data, len);
+    const int64_t n = import_roaring_bits(f->storage, data, len, clear != 0);
+    if (changed) *changed = n;
+    uint64_t last = ~0ull;
+    for (auto& kv : other.cs) {
+      const uint64_t row = kv.first >> 4;
+      if (row == last) continue;
+      last = row;
+      if (!f->cache_none) f->cache.add(row, f->row_count(row));
+      if (row > f->max_row_id) f->max_row_id = row;
+    }
   });
 }
 int orc_rows(void* h, uint32_t fam, uint64_t start, uint32_t flags, uint64_t column, uint64_t limit, const uint64_t* shards, uint32_t ns,

@@ -1427,16 +1427,119 @@ template <class T> inline T get_le(const uint8_t* p) {
 
 Bitmap deserialize(const uint8_t* data, size_t len);
 
-// ImportRoaringBits (roaring.go:1463-1558) restricted to what the ops log needs:
-// set or clear every bit of an embedded Pilosa-format bitmap.
-inline void import_roaring_bits(Bitmap& b, const uint8_t* data, size_t len, bool clear) {
-  Bitmap other = deserialize(data, len);
+Bitmap unmarshal_official(const uint8_t* data, size_t len);
+
+// Bitmap.UnmarshalBinary (roaring.go:5133-5179): Pilosa format by its magic number, else the
+// official roaring format.
+inline Bitmap unmarshal_binary(const uint8_t* data, size_t len) {
+  if (len >= 2 && get_le<uint16_t>(data) == kMagicNumber) return deserialize(data, len);
+  return unmarshal_official(data, len);
+}
+
+// ImportRoaringBits (roaring.go:1463-1558): set or clear every bit of a serialized bitmap (either
+// format); returns the number of bits that changed.
+inline int64_t import_roaring_bits(Bitmap& b, const uint8_t* data, size_t len, bool clear) {
+  Bitmap other = unmarshal_binary(data, len);
+  int64_t changed = 0;
   for (auto& kv : other.cs) {
     if (!kv.second) continue;
     CPtr cur = b.get(kv.first);
+    const int64_t before = N(cur);
+    if (clear && before == 0) continue;  // :1493-1495
     CPtr res = clear ? difference(cur, kv.second) : (cur ? union_(cur, kv.second) : kv.second);
-    if (N(res) > 0) b.cs[kv.first] = res; else b.cs.erase(kv.first);
+    const int64_t after = N(res);
+    changed += clear ? before - after : after - before;
+    if (after > 0) b.cs[kv.first] = res; else b.cs.erase(kv.first);
   }
+  return changed;
+}
+
+// readOfficialHeader + readOffsets / readWithRuns (roaring.go:5075-5245): the standard 32-bit roaring
+// serialization (16-bit container keys). Error texts are the reference's; reads that would panic in Go
+// (slice bounds) are reported as "... truncated".
+inline Bitmap unmarshal_official(const uint8_t* data, size_t len) {
+  constexpr uint32_t kCookieNoRuns = 12346, kCookieRuns = 12347;
+  Bitmap b;
+  if (len < 8) throw std::runtime_error("reading roaring header: buffer too small, expecting at least 8 bytes, was " + std::to_string(len));
+  const uint32_t cookie = get_le<uint32_t>(data);
+  size_t pos = 4;
+  uint32_t size = 0;
+  bool have_runs = false;
+  const uint8_t* is_run = nullptr;
+  if (cookie == kCookieNoRuns) {
+    size = get_le<uint32_t>(data + pos);
+    pos += 4;
+  } else if ((cookie & 0xffff) == kCookieRuns) {
+    have_runs = true;
+    size = uint32_t(uint16_t(cookie >> 16)) + 1;
+    const size_t nb = (size + 7) / 8;
+    if (pos + nb > len) throw std::runtime_error("reading roaring header: malformed bitmap, is-run bitmap overruns buffer at " + std::to_string(pos + nb));
+    is_run = data + pos;
+    pos += nb;
+  } else {
+    throw std::runtime_error("reading roaring header: did not find expected serialCookie in header");
+  }
+  const size_t header = pos;
+  if (size > (1u << 16)) throw std::runtime_error("reading roaring header: it is logically impossible to have more than (1<<16) containers");
+  if (pos + 4 * size_t(size) >= len)
+    throw std::runtime_error("reading roaring header: malformed bitmap, key-cardinality slice overruns buffer at " + std::to_string(pos + 4 * size_t(size)));
+  pos += 4 * size_t(size);
+  struct Hdr { uint64_t key; int type; int32_t card; };
+  std::vector<Hdr> hdr(size);
+  for (uint32_t i = 0; i < size; i++) {
+    const uint8_t* p = data + header + size_t(i) * 4;
+    const int32_t card = int32_t(get_le<uint16_t>(p + 2)) + 1;
+    int type = card < 4096 ? kArray : kBitmap;  // ArrayMaxSize, :5091-5097
+    if (is_run && (is_run[i / 8] & (1u << (i % 8)))) type = kRun;
+    hdr[i] = {get_le<uint16_t>(p), type, card};
+  }
+  auto put_array = [&](const Hdr& h, size_t off) {
+    if (off + size_t(h.card) * 2 > len) throw std::runtime_error("array payload truncated");
+    auto c = std::make_shared<Container>();
+    c->type = kArray; c->n = h.card; c->array.resize(h.card);
+    for (int32_t k = 0; k < h.card; k++) c->array[k] = get_le<uint16_t>(data + off + size_t(k) * 2);
+    b.cs[h.key] = c;
+  };
+  auto put_bitmap = [&](const Hdr& h, size_t off) {
+    if (off + kBitmapN * 8 > len) throw std::runtime_error("bitmap payload truncated");
+    auto c = std::make_shared<Container>();
+    c->type = kBitmap; c->n = h.card; c->bitmap.resize(kBitmapN);
+    std::memcpy(c->bitmap.data(), data + off, kBitmapN * 8);
+    b.cs[h.key] = c;
+  };
+  if (!have_runs) {  // readOffsets :5181-5211
+    for (uint32_t i = 0; i < size; i++) {
+      if (pos + size_t(i) * 4 + 4 > len) throw std::runtime_error("reading offsets from official roaring format: offset incomplete: len=" + std::to_string(len - pos - size_t(i) * 4));
+      const uint32_t off = get_le<uint32_t>(data + pos + size_t(i) * 4);
+      if (off >= len) throw std::runtime_error("reading offsets from official roaring format: offset out of bounds: off=" + std::to_string(off) + ", len=" + std::to_string(len));
+      if (hdr[i].type == kArray) put_array(hdr[i], off); else put_bitmap(hdr[i], off);
+    }
+  } else {           // readWithRuns :5213-5245: payloads back to back, no offset section
+    if (len < pos + 2) throw std::runtime_error("reading offsets from official roaring format: offset incomplete: len=" + std::to_string(len));
+    for (uint32_t i = 0; i < size; i++) {
+      const Hdr& h = hdr[i];
+      if (h.type == kRun) {
+        if (pos + 2 > len) throw std::runtime_error("run header truncated");
+        const uint16_t rc = get_le<uint16_t>(data + pos);
+        if (pos + 2 + size_t(rc) * 4 > len) throw std::runtime_error("run payload truncated");
+        auto c = std::make_shared<Container>();
+        c->type = kRun; c->n = h.card; c->runs.resize(rc);
+        for (uint16_t k = 0; k < rc; k++) {  // start:length -> start:last
+          const uint16_t st = get_le<uint16_t>(data + pos + 2 + size_t(k) * 4), ln = get_le<uint16_t>(data + pos + 4 + size_t(k) * 4);
+          c->runs[k] = {st, uint16_t(st + ln)};
+        }
+        b.cs[h.key] = c;
+        pos += 2 + size_t(rc) * 4;
+      } else if (h.type == kArray) {
+        put_array(h, pos);
+        pos += size_t(h.card) * 2;
+      } else {
+        put_bitmap(h, pos);
+        pos += kBitmapN * 8;
+      }
+    }
+  }
+  return b;
 }
 
 // unmarshalPilosaRoaring (:1562-1653) — throws std::runtime_error with the

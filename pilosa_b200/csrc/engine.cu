@@ -294,7 +294,7 @@ extern "C" int pb200_host_check_roaring(const void* roaring_bytes, size_t len, u
   std::vector<HostContainer> cs;
   std::string msg;
   if (!roaring_bytes && len) return PB200_ERR_INVALID;
-  const bool ok = parse_fragment(static_cast<const uint8_t*>(roaring_bytes), len, cs, msg);
+  const bool ok = parse_any(static_cast<const uint8_t*>(roaring_bytes), len, cs, msg);
   if (err && err_cap) { std::snprintf(err, err_cap, "%s", ok ? "" : msg.c_str()); }
   if (!ok) return PB200_ERR_FORMAT;
   FragImage img;
@@ -353,6 +353,34 @@ extern "C" int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t sh
   for (auto& c : cs) m.emplace(c.key, std::move(c));
   if (n_set) apply_bits(m, set_pos, n_set, true);
   if (n_clear) apply_bits(m, clear_pos, n_clear, false);
+  cs.clear();
+  for (auto& kv : m) {
+    cs.push_back(std::move(kv.second));
+    if (!cs.back().owned.empty()) cs.back().data = cs.back().owned.data();
+  }
+  return upload_fragment(ctx, fam, shard, cs);
+}
+
+extern "C" int pb200_frag_import_roaring(pb200_ctx* ctx, pb200_family family, uint64_t shard, const void* data, size_t len, int clear,
+                                         int64_t* changed) {
+  ENTER(ctx);
+  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
+  if (!data) return fail(ctx, PB200_ERR_INVALID, "no roaring bitmap provided");  // roaring.go:1464
+  std::vector<HostContainer> other;
+  std::string err;
+  if (!parse_any(static_cast<const uint8_t*>(data), len, other, err)) return fail(ctx, PB200_ERR_FORMAT, err);
+  for (auto& c : other)
+    if ((c.key >> 4) >= (1ull << 44)) return fail(ctx, PB200_ERR_FORMAT, "container key out of range");
+  Family& fam = ctx->families[family];
+  std::vector<uint8_t> blob;
+  std::vector<HostContainer> cs;
+  auto it = fam.frags.find(shard);
+  if (it != fam.frags.end()) TRY(download_containers(ctx, it->second, blob, cs));
+  std::map<uint64_t, HostContainer> m;
+  for (auto& c : cs) m.emplace(c.key, std::move(c));
+  const int64_t n = merge_containers(m, other, clear != 0);
+  if (changed) *changed = n;
+  if (n == 0 && it != fam.frags.end()) return PB200_OK;  // nothing to rewrite
   cs.clear();
   for (auto& kv : m) {
     cs.push_back(std::move(kv.second));

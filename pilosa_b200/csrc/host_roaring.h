@@ -189,7 +189,107 @@ inline bool parse_snapshot(const uint8_t* data, size_t len, std::vector<HostCont
   return true;
 }
 
+// The official (32-bit, 16-bit container keys) roaring serialization that Bitmap.UnmarshalBinary also
+// accepts (readOfficialHeader / readOffsets / readWithRuns, roaring.go:5075-5245): cookie 12346 = arrays
+// and bitmaps with an offset section; cookie 12347 | (n-1) << 16 = is-run bitmap, payloads back to back,
+// runs stored as start:length. Error texts are the reference's; out-of-range reads become "... truncated".
+inline bool parse_official(const uint8_t* data, size_t len, std::vector<HostContainer>& out, std::string& err) {
+  out.clear();
+  if (len < 8) { err = "reading roaring header: buffer too small, expecting at least 8 bytes, was " + std::to_string(len); return false; }
+  const uint32_t cookie = rd<uint32_t>(data);
+  size_t pos = 4;
+  uint64_t size = 0;
+  const uint8_t* is_run = nullptr;
+  if (cookie == 12346) {
+    size = rd<uint32_t>(data + pos);
+    pos += 4;
+  } else if ((cookie & 0xffff) == 12347) {
+    size = uint64_t(uint16_t(cookie >> 16)) + 1;
+    const size_t nb = size_t(size + 7) / 8;
+    if (pos + nb > len) { err = "reading roaring header: malformed bitmap, is-run bitmap overruns buffer at " + std::to_string(pos + nb); return false; }
+    is_run = data + pos;
+    pos += nb;
+  } else {
+    err = "reading roaring header: did not find expected serialCookie in header"; return false;
+  }
+  const size_t header = pos;
+  if (size > (1u << 16)) { err = "reading roaring header: it is logically impossible to have more than (1<<16) containers"; return false; }
+  if (pos + 4 * size >= len) { err = "reading roaring header: malformed bitmap, key-cardinality slice overruns buffer at " + std::to_string(pos + 4 * size); return false; }
+  pos += size_t(4 * size);
+  out.resize(size_t(size));
+  for (uint64_t i = 0; i < size; i++) {
+    HostContainer& c = out[i];
+    c.key = rd<uint16_t>(data + header + i * 4);
+    c.n = uint32_t(rd<uint16_t>(data + header + i * 4 + 2)) + 1;
+    c.type = c.n < 4096 ? kArray : kBitmap;
+    if (is_run && (is_run[i / 8] & (1u << (i % 8)))) c.type = kRun;
+    if (i > 0 && out[i - 1].key >= c.key) { err = "container keys not strictly ascending"; return false; }
+  }
+  for (uint64_t i = 0; i < size; i++) {
+    HostContainer& c = out[i];
+    size_t off = pos;
+    if (!is_run) {
+      if (pos + i * 4 + 4 > len) { err = "reading offsets from official roaring format: offset incomplete: len=" + std::to_string(len - pos - i * 4); return false; }
+      off = rd<uint32_t>(data + pos + i * 4);
+      if (off >= len) { err = "reading offsets from official roaring format: offset out of bounds: off=" + std::to_string(off) + ", len=" + std::to_string(len); return false; }
+    }
+    if (c.type == kRun) {
+      if (off + 2 > len) { err = "run header truncated"; return false; }
+      c.len = rd<uint16_t>(data + off);
+      if (off + 2 + size_t(c.len) * 4 > len) { err = "run payload truncated"; return false; }
+      c.owned.resize(size_t(c.len) * 4);
+      for (uint32_t k = 0; k < c.len; k++) {  // start:length -> start:last
+        const uint16_t st = rd<uint16_t>(data + off + 2 + k * 4), last = uint16_t(st + rd<uint16_t>(data + off + 4 + k * 4));
+        std::memcpy(&c.owned[k * 4], &st, 2); std::memcpy(&c.owned[k * 4 + 2], &last, 2);
+      }
+      c.data = c.owned.data();
+      pos = off + 2 + size_t(c.len) * 4;
+    } else if (c.type == kArray) {
+      c.len = c.n;
+      if (off + size_t(c.len) * 2 > len) { err = "array payload truncated"; return false; }
+      c.data = data + off;
+      if (is_run) pos = off + size_t(c.len) * 2;
+    } else {
+      c.len = kBitmapWords;
+      if (off + kBitmapBytes > len) { err = "bitmap payload truncated"; return false; }
+      c.data = data + off;
+      if (is_run) pos = off + kBitmapBytes;
+    }
+  }
+  return true;
+}
+
 bool parse_fragment(const uint8_t* data, size_t len, std::vector<HostContainer>& out, std::string& err);
+
+// Bitmap.UnmarshalBinary (roaring.go:5133-5179): Pilosa format (with its ops log) by the magic number, else official.
+inline bool parse_any(const uint8_t* data, size_t len, std::vector<HostContainer>& out, std::string& err) {
+  if (len >= 2 && rd<uint16_t>(data) == 12348) return parse_fragment(data, len, out, err);
+  return parse_official(data, len, out, err);
+}
+
+// ImportRoaringBits (roaring.go:1463-1558) on the host copy: OR (or AND-NOT) every container of `other`
+// into the map; returns the number of bits that changed.
+inline int64_t merge_containers(std::map<uint64_t, HostContainer>& m, const std::vector<HostContainer>& other, bool clear) {
+  std::vector<uint64_t> w(kBitmapWords), w2(kBitmapWords);
+  int64_t changed = 0;
+  for (auto& oc : other) {
+    if (oc.n == 0) continue;
+    auto it = m.find(oc.key);
+    if (it == m.end()) {
+      if (clear) continue;
+      it = m.emplace(oc.key, HostContainer{}).first; it->second.key = oc.key;
+    }
+    const int64_t before = it->second.n;
+    to_words(it->second, w.data());
+    to_words(oc, w2.data());
+    for (int k = 0; k < kBitmapWords; k++) w[k] = clear ? (w[k] & ~w2[k]) : (w[k] | w2[k]);
+    from_words(w.data(), it->second);
+    changed += clear ? before - int64_t(it->second.n) : int64_t(it->second.n) - before;
+    if (it->second.n == 0) m.erase(it);
+  }
+  return changed;
+}
+
 
 // Replays the ops log (roaring.go:1627-1650) on top of the snapshot containers.
 inline bool replay_ops(const uint8_t* buf, size_t rem, std::map<uint64_t, HostContainer>& m, std::string& err) {
@@ -224,20 +324,8 @@ inline bool replay_ops(const uint8_t* buf, size_t rem, std::map<uint64_t, HostCo
       }
       case 4: case 5: {  // embedded roaring bitmap: set / clear all of its bits (roaring.go:1463-1558)
         std::vector<HostContainer> other;
-        if (!parse_fragment(buf + 17, value, other, err)) return false;
-        std::vector<uint64_t> w(kBitmapWords), w2(kBitmapWords);
-        for (auto& oc : other) {
-          auto it = m.find(oc.key);
-          if (it == m.end()) {
-            if (typ == 5) continue;
-            it = m.emplace(oc.key, HostContainer{}).first; it->second.key = oc.key;
-          }
-          to_words(it->second, w.data());
-          to_words(oc, w2.data());
-          for (int k = 0; k < kBitmapWords; k++) w[k] = typ == 4 ? (w[k] | w2[k]) : (w[k] & ~w2[k]);
-          from_words(w.data(), it->second);
-          if (it->second.n == 0) m.erase(it);
-        }
+        if (!parse_any(buf + 17, value, other, err)) return false;
+        merge_containers(m, other, typ == 5);
         break;
       }
     }

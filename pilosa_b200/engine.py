@@ -78,6 +78,7 @@ def load_library() -> C.CDLL:
         "pb200_count_pairs_noalloc": (i32, [vp, u32, vp, u32, vp, u32, vp]),
         "pb200_eval": (i32, [vp, np_, u32, u64, C.c_char_p, sz, C.POINTER(sz)]),
         "pb200_eval_columns": (i32, [vp, np_, u32, u64, u64p, sz, C.POINTER(sz)]),
+        "pb200_frag_import_roaring": (i32, [vp, u32, u64, C.c_char_p, sz, i32, C.POINTER(C.c_int64)]),
         "pb200_rows": (i32, [vp, u32, u64, u32, u64, u64, u64p, u32, u64p, sz, C.POINTER(sz)]),
         "pb200_groupby": (i32, [vp, vp, u32, np_, u32, u64, u64p, u32, vp, sz, C.POINTER(sz)]),
         "pb200_eval_shards": (i32, [vp, np_, u32, u64p, u32, vp, sz, u64p, C.POINTER(sz)]),
@@ -155,6 +156,12 @@ class Engine:
 
     def frag_apply(self, fam: int, shard: int, set_pos: Sequence[int] = (), clear_pos: Sequence[int] = ()) -> None:
         self._check(self.lib.pb200_frag_apply(self._h, fam, shard, u64_array(set_pos), len(set_pos), u64_array(clear_pos), len(clear_pos)))
+
+    def frag_import_roaring(self, fam: int, shard: int, data: bytes, clear: bool = False) -> int:
+        """fragment.importRoaring: union / subtract a serialized bitmap (Pilosa or official format); returns bits changed."""
+        n = C.c_int64()
+        self._check(self.lib.pb200_frag_import_roaring(self._h, fam, shard, data, len(data), int(clear), C.byref(n)))
+        return n.value
 
     def frag_drop(self, fam: int, shard: int) -> None:
         self._check(self.lib.pb200_frag_drop(self._h, fam, shard))

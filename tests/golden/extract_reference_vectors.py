@@ -176,6 +176,26 @@ def roaring_tables():
     print("roaring_tables:", {k: len(v) for k, v in out.items()})
 
 
+def official_roaring():
+    """TestUnmarshalRoaringWithNoErrors / WithErrors (roaring/roaring_internal_test.go:3359-3435): the hex
+    literals, the expected counts / error texts, and the bytes of the external fixture the test reads."""
+    src = open(os.path.join(REF, "roaring/roaring_internal_test.go")).read()
+    body = src[src.index("func TestUnmarshalRoaringWithNoErrors"):src.index("func BenchmarkUnionBitmapBitmapInPlace")]
+    ok = []
+    for m in re.finditer(r'roaringData:\s*"([0-9A-Fa-f]+)",\s*count:\s*(\d+),\s*expectedBits:\s*"\[([^\]]*)\]"', body):
+        ok.append({"hex": m.group(1), "count": int(m.group(2)), "bits": [int(x) for x in m.group(3).split()]})
+    m = re.search(r'roaringFileName:\s*"([^"]+)",\s*count:\s*(\d+)', body)
+    blob = open(os.path.join(REF, "roaring", m.group(1)), "rb").read()
+    ok.append({"hex": blob.hex(), "count": int(m.group(2)), "bits": None, "file": m.group(1)})
+    bad = []
+    for m in re.finditer(r'hexString:\s*"([0-9A-Fa-f]+)",(?:\s*expectedError:\s*"([^"]*)",)?', body):
+        bad.append({"hex": m.group(1), "error": m.group(2)})
+    with open(os.path.join(OUT, "official_roaring.json"), "w") as f:
+        json.dump({"source": "roaring/roaring_internal_test.go:3359-3435", "ok": ok, "errors": bad}, f, indent=0)
+    print("official_roaring.json:", len(ok), "valid images,", len(bad), "header cases")
+
+
 if __name__ == "__main__":
+    official_roaring()
     container_combinations()
     roaring_tables()

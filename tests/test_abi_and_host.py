@@ -220,7 +220,7 @@ def test_host_loader_parser_matches_oracle_and_survives_fuzz():
         ref = oracle.Bitmap.deserialize(blob)
         nc, nb = host_check_roaring(blob)
         assert nb == ref.count() and nc == len(ref.containers())
-    for blob, msg in ((b"", "too small"), (b"\x00" * 32, "magic"), (good[:40], "truncated"), (good + b"\x09" * 13, "unknown op type"),
+    for blob, msg in ((b"", "too small"), (b"\x00" * 32, "serialCookie"), (b"\x3c\x30\x01\x00" + b"\x00" * 28, "wrong roaring version"), (good[:40], "truncated"), (good + b"\x09" * 13, "unknown op type"),
                       (good + oracle.encode_op(0, [5])[:-1] + b"\x00", "checksum")):
         with pytest.raises(EngineError, match=msg):
             host_check_roaring(blob)
@@ -235,3 +235,77 @@ def test_host_loader_parser_matches_oracle_and_survives_fuzz():
         except EngineError:
             rejected += 1
     assert rejected > 200  # and, above all, no crash
+
+
+def _official_roaring(containers, with_runs=False):
+    """Encoder for the OFFICIAL roaring format (the /import-roaring payload): containers = [(key16, kind, payload)]
+    with kind 'a' (sorted values), 'b' (1024 words) or 'r' ([(start, last)], needs with_runs)."""
+    import struct
+
+    n = len(containers)
+    def card(kind, p):
+        return len(p) if kind == "a" else sum(bin(w).count("1") for w in p) if kind == "b" else sum(l - s + 1 for s, l in p)
+    def body(kind, p):
+        if kind == "a":
+            return struct.pack(f"<{len(p)}H", *p)
+        if kind == "b":
+            return struct.pack("<1024Q", *p)
+        return struct.pack("<H", len(p)) + b"".join(struct.pack("<HH", s, l - s) for s, l in p)
+    hdr = b"".join(struct.pack("<HH", k, card(kind, p) - 1) for k, kind, p in containers)
+    bodies = [body(kind, p) for _, kind, p in containers]
+    if with_runs:
+        bits = bytearray((n + 7) // 8)
+        for i, (_, kind, _) in enumerate(containers):
+            if kind == "r":
+                bits[i // 8] |= 1 << (i % 8)
+        return struct.pack("<I", 12347 | ((n - 1) << 16)) + bytes(bits) + hdr + b"".join(bodies)
+    out = struct.pack("<II", 12346, n) + hdr
+    off = len(out) + 4 * n
+    offs = []
+    for b in bodies:
+        offs.append(off)
+        off += len(b)
+    return out + struct.pack(f"<{n}I", *offs) + b"".join(bodies)
+
+
+def test_official_roaring_format_golden_vectors():
+    """TestUnmarshalRoaringWithNoErrors / WithErrors (roaring_internal_test.go:3359-3435): the oracle's
+    UnmarshalBinary and the loader's host parser read the reference's serialized images alike."""
+    import json
+
+    from pilosa_b200.engine import EngineError, host_check_roaring
+
+    g = json.load(open(os.path.join(ROOT, "tests", "golden", "official_roaring.json")))
+    for case in g["ok"]:
+        blob = bytes.fromhex(case["hex"])
+        bm = oracle.Bitmap.deserialize(blob)
+        assert bm.count() == case["count"]
+        if case["bits"] is not None:
+            assert bm.slice() == case["bits"]
+        assert host_check_roaring(blob)[1] == case["count"]
+    for case in g["errors"]:
+        blob = bytes.fromhex(case["hex"])
+        if case["error"] is None:  # a Pilosa-format image with no containers: fine
+            assert oracle.Bitmap.deserialize(blob).count() == 0 and host_check_roaring(blob) == (0, 0)
+            continue
+        with pytest.raises(oracle.OracleError) as e1:
+            oracle.Bitmap.deserialize(blob)
+        assert str(e1.value) == case["error"]
+        with pytest.raises(EngineError) as e2:
+            host_check_roaring(blob)
+        assert case["error"] in str(e2.value)
+    # our own encoder against both parsers: arrays + bitmap with offsets; runs (start:length) without
+    words = [0] * 1024
+    for v in range(0, 65536, 7):
+        words[v >> 6] |= 1 << (v & 63)
+    a = _official_roaring([(0, "a", [1, 5, 70]), (3, "b", words), (9, "a", list(range(100, 4000, 3)))])
+    r = _official_roaring([(0, "r", [(1, 10), (100, 65535)]), (2, "a", [7]), (5, "b", words)], with_runs=True)
+    for blob in (a, r):
+        bm = oracle.Bitmap.deserialize(blob)
+        assert host_check_roaring(blob) == (len(bm.containers()), bm.count())
+    assert oracle.Bitmap.deserialize(r).slice()[:12] == list(range(1, 11)) + [100, 101]
+    for cut in (9, 20, len(a) - 1, len(a) - 9000):  # truncations are errors in both, never a crash
+        with pytest.raises(oracle.OracleError):
+            oracle.Bitmap.deserialize(a[:cut])
+        with pytest.raises(EngineError):
+            host_check_roaring(a[:cut])

@@ -291,6 +291,38 @@ def test_frag_apply_and_reload(pair):
         assert g.be.eval_columns(g.program(call), 1) == c.be.eval_columns(c.program(call), 1)
 
 
+def test_import_roaring(pair):
+    """pb200_frag_import_roaring = fragment.importRoaring (fragment.go:2243) -> ImportRoaringBits (roaring.go:1463):
+    official-format and Pilosa-format payloads, set and clear, changed counts, new shard, then queries agree."""
+    from test_abi_and_host import _official_roaring
+
+    g, c, shards = pair
+    rnd = random.Random(11)
+    words = [rnd.getrandbits(64) & rnd.getrandbits(64) for _ in range(1024)]
+    # fragment positions row * 2^20 + col: container key = row * 16 + (col >> 16); rows 2 and 40 of field "m"
+    official = _official_roaring([(2 * 16 + 1, "a", sorted(rnd.sample(range(65536), 900))), (2 * 16 + 3, "b", words),
+                                  (40 * 16 + 0, "a", [0, 1, 65535])])
+    with_runs = _official_roaring([(2 * 16 + 1, "r", [(10, 5000), (60000, 65535)]), (5 * 16 + 15, "a", [3, 9])], with_runs=True)
+    pilosa_fmt = synth.mixed(0, 2, 2).bytes()  # rows 2..3 in Pilosa format
+    fm_g, fm_c = g.family("m"), c.family("m")
+    for shard, blob, clear in ((0, official, False), (0, with_runs, False), (1, pilosa_fmt, False), (0, with_runs, True),
+                               (2, official, True), (9, official, False), (0, official, False)):
+        assert g.be.frag_import_roaring(fm_g, shard, blob, clear) == c.be.frag_import_roaring(fm_c, shard, blob, clear), (shard, clear)
+    sh = shards + [9]
+    for call in (Row("m", 2), Row("m", 40), Union(Row("m", 2), Row("m", 5)), Xor(Row("m", 2), Row("m", 3), Row("f", 1))):
+        assert g.count(call, sh) == c.count(call, sh), repr(call)
+        assert g.row_segments(call, sh) == c.row_segments(call, sh), repr(call)
+    assert g.rows("m", sh) == c.rows("m", sh)
+    from pilosa_b200.engine import EngineError
+    with pytest.raises(EngineError, match="serialCookie"):
+        g.be.frag_import_roaring(fm_g, 0, b"\x01\x02\x03\x04\x05\x06\x07\x08\x09")
+    # undo, so that later tests see the original fixture
+    for ex in (g, c):
+        for s_ in (0, 1, 2):
+            ex.load_fragment("m", s_, synth.mixed(s_, 0, 8))
+        ex.be.frag_drop(ex.family("m"), 9)
+
+
 def test_ops_log_replay_on_load(pair):
     g, c, _ = pair
     base = synth.bernoulli(7, 0, 2, 0.001).bytes()
