@@ -73,7 +73,8 @@ def test_file_format_round_trip_and_ops_log():
     # corrupted checksum / bad magic are rejected with the reference's messages
     bad = bytearray(data + oracle.encode_op(0, [9]))
     bad[-1] ^= 0xFF
-    for blob, msg in ((bytes(bad), "checksum"), (b"\x00" * 16, "magic number"), (b"\x01\x02", "too small")):
+    for blob, msg in ((bytes(bad), "checksum"), (b"\x3c\x30\x01\x00" + b"\x00" * 12, "wrong roaring version"),
+                      (b"\x00" * 16, "serialCookie"), (b"\x01\x02", "too small")):
         try:
             Bitmap.deserialize(blob)
             raise AssertionError("expected failure: " + msg)
