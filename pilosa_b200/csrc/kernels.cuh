@@ -404,27 +404,32 @@ __device__ __forceinline__ void stage_container(const ContainerDesc& d, uint32_t
       while (l < h) { uint32_t m = (l + h) >> 1; if (a[m] < hi) l = m + 1; else h = m; }
       e = l;
     }
-    // Each thread takes a contiguous segment of the sorted array and assembles whole 32-bit
-    // words in a register: words strictly inside its segment are owned by this thread alone
-    // (plain stores); only the first and last word can be shared with a neighbouring
-    // thread (shared-memory atomics cost ~2 cycles per lane, so they are kept to two).
-    const uint32_t n = e - b;
-    const uint32_t per = (n + nthreads - 1) / nthreads;
-    const uint32_t i0 = b + tid * per, i1 = min(e, i0 + per);
-    if (per && i0 < i1) {
-      uint32_t cur_w = (uint32_t(a[i0]) - lo) >> 5, cur_bits = 0;
-      bool first = true;
-#pragma unroll 4
-      for (uint32_t i = i0; i < i1; i++) {
-        const uint32_t v = uint32_t(__ldg(a + i)) - lo, w = v >> 5;
-        if (w != cur_w) {
-          if (first) { atomicOr(&win32[cur_w], cur_bits); first = false; }
-          else win32[cur_w] = cur_bits;
-          cur_w = w; cur_bits = 0;
-        }
-        cur_bits |= 1u << (v & 31);
+    // Eight consecutive values per thread and step (one 16-byte load when aligned); a thread's values that
+    // fall into the same 32-bit word are merged in registers before the shared-memory atomicOr.
+    for (uint32_t i = b + tid * 8; i < e; i += nthreads * 8) {
+      uint32_t cur_w = 0xffffffffu, cur_bits = 0;
+      const uint32_t m = min(8u, e - i);
+      uint32_t vals[8];
+      if (m == 8 && ((reinterpret_cast<uintptr_t>(a + i) & 15) == 0)) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(a + i));
+        vals[0] = q.x & 0xffff; vals[1] = q.x >> 16; vals[2] = q.y & 0xffff; vals[3] = q.y >> 16;
+        vals[4] = q.z & 0xffff; vals[5] = q.z >> 16; vals[6] = q.w & 0xffff; vals[7] = q.w >> 16;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; k++) vals[k] = k < int(m) ? uint32_t(__ldg(a + i + k)) : 0u;
       }
-      atomicOr(&win32[cur_w], cur_bits);
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        if (k < int(m)) {
+          const uint32_t v = vals[k] - lo, w = v >> 5;
+          if (w != cur_w) {
+            if (cur_w != 0xffffffffu) atomicOr(&win32[cur_w], cur_bits);
+            cur_w = w; cur_bits = 0;
+          }
+          cur_bits |= 1u << (v & 31);
+        }
+      }
+      if (cur_w != 0xffffffffu) atomicOr(&win32[cur_w], cur_bits);
     }
   } else if (type == kRun) {
     const ushort2* r = reinterpret_cast<const ushort2*>(d.addr);
@@ -440,42 +445,34 @@ __device__ __forceinline__ void stage_container(const ContainerDesc& d, uint32_t
       while (l < h) { uint32_t m = (l + h) >> 1; if (r[m].x < hi) l = m + 1; else h = m; }
       e = l;
     }
-    // Same scheme as for arrays: a contiguous segment of the (sorted, disjoint) run list per
-    // thread, whole words assembled in a register; only the segment's first and last word
-    // can be shared with a neighbouring thread and need an atomic.
-    const uint32_t n = e - b;
-    const uint32_t per = (n + nthreads - 1) / nthreads;
-    const uint32_t i0 = b + tid * per, i1 = min(e, i0 + per);
-    if (per && i0 < i1) {
-      uint32_t cur_w = 0xffffffffu, cur_bits = 0;
-      bool first = true;
-      auto emit = [&](uint32_t w, uint32_t bits) {
-        if (w != cur_w) {
-          if (cur_w != 0xffffffffu) {
-            if (first) { atomicOr(&win32[cur_w], cur_bits); first = false; }
-            else win32[cur_w] = cur_bits;
-          }
-          cur_w = w; cur_bits = 0;
-        }
-        cur_bits |= bits;
-      };
-#pragma unroll 2
-      for (uint32_t i = i0; i < i1; i++) {
+    // One run per thread (coalesced loads of the run list). The two edge words of a run can be shared with
+    // a neighbouring run: shared-memory atomicOr. The words strictly inside a run belong to that run alone
+    // (runs are disjoint and not adjacent): plain stores — by the owning thread when there are few, by the
+    // whole warp (coalesced, run after run) when a long run has hundreds of them.
+    const int lane = tid & 31;
+    for (uint32_t base = b; base < e; base += nthreads) {  // warp-uniform trip count: nthreads is a multiple of 32
+      const uint32_t i = base + tid;
+      uint32_t ws = 0, we = 0;
+      if (i < e) {
         const ushort2 iv = __ldg(r + i);
         uint32_t s = iv.x, l = iv.y;
         if (s < lo) s = lo;
         if (l >= hi) l = hi - 1;
         s -= lo; l -= lo;
-        const uint32_t ws = s >> 5, we = l >> 5;
+        ws = s >> 5; we = l >> 5;
         const uint32_t ms = ~0u << (s & 31), me = ~0u >> (31 - (l & 31));
-        if (ws == we) emit(ws, ms & me);
-        else {
-          emit(ws, ms);
-          for (uint32_t k = ws + 1; k < we; k++) emit(k, ~0u);
-          emit(we, me);
-        }
+        if (ws == we) atomicOr(&win32[ws], ms & me);
+        else { atomicOr(&win32[ws], ms); atomicOr(&win32[we], me); }
       }
-      atomicOr(&win32[cur_w], cur_bits);
+      const bool long_run = we > ws + 1 + 16;  // short interiors: by the owning thread; long ones: by the warp
+      if (!long_run) for (uint32_t k = ws + 1; k < we; k++) win32[k] = ~0u;
+      uint32_t todo = __ballot_sync(0xffffffffu, long_run);
+      while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint32_t k0 = __shfl_sync(0xffffffffu, ws, src) + 1, k1 = __shfl_sync(0xffffffffu, we, src);
+        for (uint32_t k = k0 + lane; k < k1; k += 32) win32[k] = ~0u;
+      }
     }
   }
 }
