@@ -130,6 +130,7 @@ static void free_fragment(Fragment& f) {
   f.blob = nullptr;
   f.d_rank = nullptr;
   f.d_rank_valid = false;
+  f.rank_pos_valid = false;
 }
 
 extern "C" int pb200_shutdown(pb200_ctx* ctx) {
@@ -416,6 +417,7 @@ extern "C" int pb200_rank_set(pb200_ctx* ctx, pb200_family family, uint64_t shar
   it->second.rank_counts.assign(counts, counts + n);
   it->second.rank_from_host = true;
   it->second.d_rank_valid = false;  // rebuilt on the next TopN
+  it->second.rank_pos_valid = false;
   return PB200_OK;
 }
 

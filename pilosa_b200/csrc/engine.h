@@ -37,6 +37,8 @@ struct Fragment {
   bool rank_from_host = false;
   uint32_t* d_rank = nullptr;  // device copy of the rank order as row-table indices (TopN)
   bool d_rank_valid = false;
+  std::vector<uint32_t> rank_pos_of_row;  // rank position of row_ids[j] (0xffffffff: not ranked); host index for TopN pass 2
+  bool rank_pos_valid = false;
 };
 
 struct Family {

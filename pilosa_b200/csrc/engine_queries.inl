@@ -364,9 +364,73 @@ int ensure_rank_table(pb200_ctx* ctx, Fragment& f) {
 
 // One TopN pass over `shards` (executor.go:905-930 executeTopNShards without the final sort):
 // per-shard fragment.top results.
+// What pass 1 of a two-pass TopN leaves behind for pass 2 of the same call: the exact intersection count of
+// EVERY ranked row of every shard is already on the host, so pass 2 (the same counts for the merged candidate
+// ids, executor.go:889-902) is a lookup instead of a second trip over the head rows.
+struct TopnCarry {
+  bool valid = false;
+  std::vector<uint64_t> off;         // shard s owns isect[off[s] .. off[s+1]) in rank order
+  const uint32_t* isect = nullptr;   // pinned host buffer of pass 1 (ctx->h_out)
+  std::vector<uint64_t> src_counts;  // |source row| per shard (Tanimoto)
+};
+
+void ensure_rank_pos(Fragment& f) {
+  if (f.rank_pos_valid) return;
+  f.rank_pos_of_row.assign(f.row_ids.size(), 0xffffffffu);
+  for (size_t p = 0; p < f.rank_ids.size(); p++) {
+    auto it = std::lower_bound(f.row_ids.begin(), f.row_ids.end(), f.rank_ids[p]);
+    if (it != f.row_ids.end() && *it == f.rank_ids[p]) f.rank_pos_of_row[size_t(it - f.row_ids.begin())] = uint32_t(p);
+  }
+  f.rank_pos_valid = true;
+}
+
+// Pass 2 from pass 1's counts. Returns false (nothing written) when some candidate row exists in a shard
+// but is not in that shard's rank table: the regular device pass handles that case.
+bool topn_pass2_from_carry(pb200_ctx* ctx, pb200_family family, const uint64_t* ids, size_t n_ids, uint64_t min_threshold,
+                           uint64_t tanimoto, const uint64_t* shards, uint32_t n_shards, const TopnCarry& carry,
+                           std::vector<std::vector<HPair>>& per_shard) {
+  Family& fam = ctx->families[family];
+  std::vector<Fragment*> frs(n_shards, nullptr), todo;
+  for (uint32_t s = 0; s < n_shards; s++) {
+    auto it = fam.frags.find(shards[s]);
+    if (it == fam.frags.end()) continue;
+    frs[s] = &it->second;
+    if (!it->second.rank_pos_valid) todo.push_back(&it->second);
+  }
+  std::sort(todo.begin(), todo.end());
+  todo.erase(std::unique(todo.begin(), todo.end()), todo.end());
+  parallel_shards(uint32_t(todo.size()), [&](uint32_t i) { ensure_rank_pos(*todo[i]); });
+  std::atomic<bool> miss{false};
+  std::vector<std::vector<HPair>> out(n_shards);
+  parallel_shards(n_shards, [&](uint32_t s) {
+    if (!frs[s] || miss.load(std::memory_order_relaxed)) return;
+    const Fragment& f = *frs[s];
+    struct Cand { uint64_t id, count; uint32_t isect; };
+    std::vector<Cand> cd;
+    for (size_t k = 0; k < n_ids; k++) {
+      const auto it = std::lower_bound(f.row_ids.begin(), f.row_ids.end(), ids[k]);
+      if (it == f.row_ids.end() || *it != ids[k]) continue;  // the shard does not have this row
+      const size_t j = size_t(it - f.row_ids.begin());
+      const uint32_t pos = f.rank_pos_of_row[j];
+      if (pos == 0xffffffffu) { miss.store(true, std::memory_order_relaxed); return; }
+      uint64_t c = f.rank_from_host ? f.rank_counts[pos] : f.row_counts[j];
+      if (c == 0) c = f.row_counts[j];
+      if (c > 0) cd.push_back({ids[k], c, carry.isect[carry.off[s] + pos]});
+    }
+    std::stable_sort(cd.begin(), cd.end(), [](const Cand& x, const Cand& y) { return x.count != y.count ? x.count > y.count : x.id < y.id; });
+    std::vector<uint64_t> cid(cd.size()), cc(cd.size());
+    std::vector<uint32_t> ci(cd.size());
+    for (size_t k = 0; k < cd.size(); k++) { cid[k] = cd[k].id; cc[k] = cd[k].count; ci[k] = cd[k].isect; }
+    out[s] = top_walk(cid.data(), cc.data(), cid.size(), ci.data(), true, 0, min_threshold, tanimoto, carry.src_counts[s]);
+  });
+  if (miss.load()) return false;
+  per_shard.swap(out);
+  return true;
+}
+
 int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, uint32_t n_src_nodes, uint32_t n,
               const uint64_t* ids, size_t n_ids, uint64_t min_threshold, uint64_t tanimoto, const uint64_t* shards,
-              uint32_t n_shards, std::vector<std::vector<HPair>>& per_shard, bool reuse_src = false) {
+              uint32_t n_shards, std::vector<std::vector<HPair>>& per_shard, bool reuse_src = false, TopnCarry* carry = nullptr) {
   if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
   if (tanimoto > 100) return fail(ctx, PB200_ERR_INVALID, "Tanimoto Threshold is from 1 to 100 only");  // executor.go:988
   if (min_threshold == 0) min_threshold = 1;  // defaultMinThreshold, executor.go:37,984
@@ -496,6 +560,7 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
       for (int c = 0; c < kRowContainers; c++) src_counts[s] += h_dn[size_t(s) * kRowContainers + c];
     isect = h_counts;
     lap("device + copies");
+    if (carry && !n_ids) { carry->valid = true; carry->off = off; carry->isect = h_counts; carry->src_counts = src_counts; }
   }
 
   // per-shard selection walk (host: sequential, data-dependent, a few thousand steps per shard)
@@ -521,18 +586,14 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
 }
 
 std::vector<HPair> merge_pairs(const std::vector<std::vector<HPair>>& per_shard) {  // Pairs.Add (cache.go:356-374) + sort
-  std::vector<HPair> all;
-  size_t total = 0;
-  for (auto& v : per_shard) total += v.size();
-  all.reserve(total);
-  for (auto& v : per_shard) all.insert(all.end(), v.begin(), v.end());
-  std::sort(all.begin(), all.end(), [](const HPair& x, const HPair& y) { return x.id < y.id; });
+  // the shards mostly report the same few ids: sum them in a hash map, then sort only the distinct ones
+  std::unordered_map<uint64_t, uint64_t> sum;
+  sum.reserve(1024);
+  for (auto& v : per_shard)
+    for (auto& p : v) sum[p.id] += p.count;
   std::vector<HPair> out;
-  for (size_t i = 0; i < all.size();) {  // sum the counts of equal ids
-    HPair acc = all[i++];
-    while (i < all.size() && all[i].id == acc.id) acc.count += all[i++].count;
-    out.push_back(acc);
-  }
+  out.reserve(sum.size());
+  for (auto& kv : sum) out.push_back({kv.first, kv.second});
   sort_pairs(out);
   return out;
 }
@@ -564,7 +625,8 @@ extern "C" int pb200_topn(pb200_ctx* ctx, pb200_family family, const pb200_node*
   if (n_ids && !ids) return PB200_ERR_INVALID;
   TRY(validate_shards(ctx, shards, n_shards));
   std::vector<std::vector<HPair>> per;
-  TRY(topn_pass(ctx, family, src_prog, n_src_nodes, n, ids, n_ids, min_threshold, tanimoto_threshold, shards, n_shards, per));
+  TopnCarry carry;
+  TRY(topn_pass(ctx, family, src_prog, n_src_nodes, n, ids, n_ids, min_threshold, tanimoto_threshold, shards, n_shards, per, false, &carry));
   std::vector<HPair> pairs = merge_pairs(per);
   if (pairs.empty() || n_ids > 0 || (flags & PB200_TOPN_REMOTE)) return write_pairs(ctx, pairs, out, cap, n_out);  // executor.go:884-887
   // second pass with the candidate ids of pass 1 (executor.go:889-902)
@@ -572,11 +634,14 @@ extern "C" int pb200_topn(pb200_ctx* ctx, pb200_family family, const pb200_node*
   std::vector<uint64_t> ids2;
   for (auto& p : pairs) ids2.push_back(p.id);
   std::sort(ids2.begin(), ids2.end());
-  TRY(topn_pass(ctx, family, src_prog, n_src_nodes, n, ids2.data(), ids2.size(), min_threshold, tanimoto_threshold, shards, n_shards, per,
-                /*reuse_src=*/true));
+  const uint64_t thr = min_threshold ? min_threshold : 1;  // defaultMinThreshold, as topn_pass applies it
+  if (!(carry.valid && topn_pass2_from_carry(ctx, family, ids2.data(), ids2.size(), thr, tanimoto_threshold, shards, n_shards, carry, per))) {
+    TRY(topn_pass(ctx, family, src_prog, n_src_nodes, n, ids2.data(), ids2.size(), min_threshold, tanimoto_threshold, shards, n_shards, per,
+                  /*reuse_src=*/true));
+    ctx->timing.kernel_ms += t1.kernel_ms; ctx->timing.algo_bytes += t1.algo_bytes; ctx->timing.launches += t1.launches;
+    ctx->timing.h2d_bytes += t1.h2d_bytes; ctx->timing.d2h_bytes += t1.d2h_bytes;
+  }
   ctx->dense_shards_dev = nullptr;
-  ctx->timing.kernel_ms += t1.kernel_ms; ctx->timing.algo_bytes += t1.algo_bytes; ctx->timing.launches += t1.launches;
-  ctx->timing.h2d_bytes += t1.h2d_bytes; ctx->timing.d2h_bytes += t1.d2h_bytes;
   std::vector<HPair> trimmed = merge_pairs(per);
   if (n != 0 && n < trimmed.size()) trimmed.resize(n);
   return write_pairs(ctx, trimmed, out, cap, n_out);

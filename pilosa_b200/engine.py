@@ -288,7 +288,7 @@ class Engine:
 
     def rows(self, fam, shards, start=0, column=None, limit=None) -> List[int]:
         from .abi import NO_LIMIT, ROWS_COLUMN
-        cap = 1 << 16
+        cap = 1 << 10
         while True:
             out, n = (C.c_uint64 * cap)(), C.c_size_t()
             rc = self.lib.pb200_rows(self._h, fam, start, 0 if column is None else ROWS_COLUMN, column or 0,
@@ -304,13 +304,13 @@ class Engine:
         from .abi import NO_LIMIT, Group, pack_groupby_children, unpack_groups
         arr, keep = pack_groupby_children(children)
         fp, nf = (filter_prog, len(filter_prog)) if filter_prog is not None else (None, 0)
-        cap = 1 << 14
+        cap = getattr(self, "_gb_cap", 1 << 10)
         while True:
             out, n = (Group * cap)(), C.c_size_t()
             rc = self.lib.pb200_groupby(self._h, arr, len(children), fp, nf, NO_LIMIT if limit is None else limit,
                                         u64_array(shards), len(shards), out, cap, C.byref(n))
             if rc == -6 and n.value > cap:
-                cap = n.value
+                cap = self._gb_cap = n.value  # remembered: the retry runs the query again
                 continue
             self._check(rc)
             return unpack_groups(out, n.value, len(children))
@@ -322,11 +322,16 @@ class Engine:
         self._check(self.lib.pb200_eval_columns(self._h, prog, len(prog), shard, buf, n.value, C.byref(n)))
         return list(buf[: n.value])
 
-    def _pairs(self, fn, *args, cap=1 << 16):
-        out = (Pair * cap)()
-        n = C.c_size_t()
-        self._check(fn(*args, out, cap, C.byref(n)))
-        return [(out[i].id, out[i].count) for i in range(n.value)]
+    def _pairs(self, fn, *args, cap=1 << 10):
+        while True:  # small buffer first (allocating a big ctypes array costs more than a TopN call)
+            out = (Pair * cap)()
+            n = C.c_size_t()
+            rc = fn(*args, out, cap, C.byref(n))
+            if rc == -6 and n.value > cap:  # PB200_ERR_RANGE: *n_out holds the size needed
+                cap = n.value
+                continue
+            self._check(rc)
+            return [(out[i].id, out[i].count) for i in range(n.value)]
 
     def topn(self, fam, src_prog, n, shards, ids=(), min_threshold=0, tanimoto=0, remote=False):
         sp, ns = (src_prog, len(src_prog)) if src_prog is not None else (None, 0)
