@@ -75,6 +75,15 @@ def emit(rows, name, query, n_shards, kernel_ms, wall_ms, algo_bytes, launches, 
         raise SystemExit(f"parity mismatch in {name}: {query}")
 
 
+def prop(rows, config, name, ok, detail=""):
+    """A size-independent identity checked on the GPU results at the config's FULL size (the oracle only
+    covers a shard sample there)."""
+    line = {"config": config, "property": name, "ok": bool(ok), "detail": detail}
+    print(json.dumps(line), flush=True)
+    if not ok:
+        raise SystemExit(f"property violated in {config}: {name} {detail}")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="c1,c2,c3,c4,c5,gb")
@@ -142,6 +151,18 @@ def main():
             exp, cms = cpu_timed(lambda: c.count(call, cpu_sh))
             emit(rows, "C2", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
 
+        if "c2" in cfgs:
+            a, b = leaves[0], leaves[1]
+            ca, cb = g.count(a, shards), g.count(b, shards)
+            ci, cu, cx, cd = (g.count(op(a, b), shards) for op in (Intersect, Union, Xor, Difference))
+            prop(rows, "C2", "|a|+|b| = |a or b| + |a and b|", ca + cb == cu + ci, f"{ca}+{cb} vs {cu}+{ci}")
+            prop(rows, "C2", "|a xor b| = |a or b| - |a and b|", cx == cu - ci)
+            prop(rows, "C2", "|a - b| = |a| - |a and b|", cd == ca - ci)
+            per = eng.count_shards(g.program(Union(*leaves)), shards)
+            prop(rows, "C2", "sum of per-shard counts = count over all shards", sum(per) == g.count(Union(*leaves), shards))
+            u4, x4 = g.count(Union(*leaves), shards), g.count(Xor(*leaves), shards)
+            prop(rows, "C2", "Xor(r0..r3) <= Union(r0..r3) <= sum of rows", x4 <= u4 <= sum(g.count(l, shards) for l in leaves))
+
     # ---------------- C3: TopN(f, n=50) over 10k rows with an Intersect filter ----------------
     if "c3" in cfgs:
         shards = list(range(args.c3_shards))
@@ -159,6 +180,14 @@ def main():
             got = g.topn("z", cpu_sh, **kw)
             exp, cms = cpu_timed(lambda: c.topn("z", cpu_sh, **kw))
             emit(rows, "C3", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
+
+        if "c3" in cfgs:
+            top = g.topn("z", shards, n=50, src=src)
+            exact = g.count_batch([Intersect(src, Row("z", i)) for i, _ in top], shards)
+            prop(rows, "C3", "TopN counts = Count(Intersect(src, Row)) of the returned ids", [c_ for _, c_ in top] == exact)
+            prop(rows, "C3", "TopN result sorted by count desc", all(top[i][1] >= top[i + 1][1] for i in range(len(top) - 1)))
+            again = g.topn("z", shards, n=50, src=src, ids=[i for i, _ in top])
+            prop(rows, "C3", "TopN(ids = its own result) returns the same pairs", sorted(again) == sorted(top))
 
     # ---------------- C4: BSI int32: Sum / Min / Max / Range ----------------
     if "c4" in cfgs:
@@ -180,6 +209,22 @@ def main():
             got = fn(g, cpu_sh)
             exp, cms = cpu_timed(lambda: fn(c, cpu_sh))
             emit(rows, "C4", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
+        nn = g.count(g.row_range("v", abi.BSI_NEQ, None), shards)  # not null
+        for x in (0, 12345, -(1 << 30)):
+            gt, le = g.count(g.row_range("v", abi.BSI_GT, x), shards), g.count(g.row_range("v", abi.BSI_LTE, x), shards)
+            eq, ne = g.count(g.row_range("v", abi.BSI_EQ, x), shards), g.count(g.row_range("v", abi.BSI_NEQ, x), shards)
+            prop(rows, "C4", f"count(v > {x}) + count(v <= {x}) = count(v != null)", gt + le == nn, f"{gt}+{le} vs {nn}")
+            prop(rows, "C4", f"count(v == {x}) + count(v != {x}) = count(v != null)", eq + ne == nn)
+        (mn, _), (mx, _) = g.min("v", shards), g.max("v", shards)
+        prop(rows, "C4", "count(v < Min) = 0 and count(v > Max) = 0",
+             g.count(g.row_range("v", abi.BSI_LT, mn), shards) == 0 and g.count(g.row_range("v", abi.BSI_GT, mx), shards) == 0)
+        s_all, c_all = g.sum("v", shards)
+        s_f, c_f = g.be.bsi_sum(g.family("v", "bsig_v"), 32, g.program(Row("fl", 1)), shards, flags=1)        # strict: filter applies to negatives too
+        s_n, c_n = g.be.bsi_sum(g.family("v", "bsig_v"), 32, g.program(Difference(g.row_range("v", abi.BSI_NEQ, None), Row("fl", 1))), shards, flags=1)
+        prop(rows, "C4", "Sum(filter) + Sum(not filter) = Sum(all) (strict sums), counts too", s_f + s_n == s_all and c_f + c_n == c_all == nn)
+        bw = g.count(g.row_range("v", abi.BSI_BETWEEN, -999, 999), shards)
+        prop(rows, "C4", "count(-1000 < v < 1000) = count(v < 1000) - count(v <= -1000)",
+             bw == g.count(g.row_range("v", abi.BSI_LT, 1000), shards) - g.count(g.row_range("v", abi.BSI_LTE, -1000), shards))
         # materialised Row(v > x): every shard's result typed + serialised on the device (K11), packed streams copied
         # to the host (the D2H of ~128 KiB per shard dominates the call; kernel ms is evaluation + serialisation)
         for x in (0, 12345, (1 << 31) - 4096):
