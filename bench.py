@@ -338,7 +338,8 @@ def main():
         for i in range(args.warmup):
             step_resident(i)
         barrier()
-        sampler.start()
+        if rank == 0:  # one poller per box: concurrent NVML queries from every rank serialise in the driver
+            sampler.start()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record(stream)
         for i in range(args.warmup, n_batches):
@@ -387,7 +388,7 @@ def main():
         torch.cuda.synchronize()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
         barrier()
-        clocks = sampler.stop()
+        clocks = sampler.stop() if rank == 0 else None
         tm = eng.last_timing()
         assert list(out_e2e) == last_resident, "resident and e2e legs disagree"
 
