@@ -390,8 +390,8 @@ __global__ void __launch_bounds__(kPipeThreads) bsi_sum_kernel(BsiParams p) {
           uint4 row[2];
           next_plane(row);
           // popcount(B_i & prow) in the low half, popcount(B_i & nrow) in the high half (<= 8192 each per warp)
-          const uint32_t both = warp_sum((popc128(and128(row[0], prow[0])) + popc128(and128(row[1], prow[1]))) |
-                                         ((popc128(and128(row[0], nrow[0])) + popc128(and128(row[1], nrow[1]))) << 16));
+          const uint32_t both = __reduce_add_sync(0xffffffffu, (popc128(and128(row[0], prow[0])) + popc128(and128(row[1], prow[1]))) |
+                                                  ((popc128(and128(row[0], nrow[0])) + popc128(and128(row[1], nrow[1]))) << 16));  // one REDUX
           if (lane == 0) { s_acc[wid][1 + 2 * i] += both & 0xffffu; s_acc[wid][2 + 2 * i] += both >> 16; }
         }
       }
