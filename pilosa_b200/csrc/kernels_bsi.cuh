@@ -219,7 +219,13 @@ struct PlanePipe {
   uint8_t* ring;
   uint64_t* full;    // [kPipeStages], count 1 + tx bytes
   uint64_t* empty;   // [kPipeStages], count = consumer warps
-  uint32_t seq = 0;  // TMA planes issued (producer) / taken (consumer) so far; both sides count alike
+  // position in the ring, advanced alike by the producer (planes issued) and the consumers (planes taken):
+  // slot index, lap parity, and whether the first lap is over (the producer need not wait for `empty` before)
+  uint32_t slot = 0, lap = 0;
+  bool lapped = false;
+  __device__ __forceinline__ void advance() {
+    if (++slot == kPipeStages) { slot = 0; lap ^= 1u; lapped = true; }
+  }
 
   __device__ __forceinline__ static bool by_tma(const ContainerDesc& d) { return d.n != 0 && desc_type(d) == kBitmap; }
 
@@ -232,24 +238,22 @@ struct PlanePipe {
   // producer lane: copy plane d into the next slot once its previous contents have been released
   __device__ __forceinline__ void produce(const ContainerDesc& d) {
     if (!by_tma(d)) return;
-    const uint32_t slot = seq % kPipeStages, use = seq / kPipeStages;
-    if (use) mbar_wait(&empty[slot], (use - 1) & 1u);
+    if (lapped) mbar_wait(&empty[slot], lap ^ 1u);  // the slot's previous use has been released by all consumer warps
     fence_proxy_async();
     mbar_arrive_expect_tx(&full[slot], kBitmapBytes);
     tma_load_1d(ring + slot * kBitmapBytes, reinterpret_cast<const void*>(d.addr), kBitmapBytes, &full[slot]);
-    seq++;
+    advance();
   }
   // consumer thread t (0..255): its two chunks of a streamable plane
   __device__ __forceinline__ void take(const ContainerDesc& d, int t, uint4 (&v)[2]) {
     if (d.n == 0) { v[0] = v[1] = make_uint4(0, 0, 0, 0); return; }
     if (desc_type(d) != kBitmap) { v[0] = v[1] = make_uint4(~0u, ~0u, ~0u, ~0u); return; }  // full run
-    const uint32_t slot = seq % kPipeStages, use = seq / kPipeStages;
-    mbar_wait(&full[slot], use & 1u);
+    mbar_wait(&full[slot], lap);
     const uint4* win = reinterpret_cast<const uint4*>(ring + slot * kBitmapBytes);
     v[0] = win[t]; v[1] = win[t + kPipeConsumers];
     __syncwarp();
     if ((t & 31) == 0) mbar_arrive(&empty[slot]);
-    seq++;
+    advance();
   }
 };
 
