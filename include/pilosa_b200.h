@@ -278,6 +278,14 @@ int pb200_eval_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
                       const uint64_t* shards, uint32_t n_shards, void* out, size_t cap,
                       uint64_t* out_off, size_t* out_len);
 
+/* Page-lock a caller-owned host buffer (cudaHostRegister) so that result copies into it — the
+ * packed streams of pb200_eval_shards are 128 KiB per dense shard — run as direct DMA at PCIe
+ * speed instead of through the driver's pageable staging. Optional: every entry point also works
+ * with ordinary memory. A Go host registers its reusable result arena once (the memory must not
+ * move: C.malloc or an mmap, not a GC-managed slice). No reference counterpart. */
+int pb200_host_register(pb200_ctx* ctx, void* ptr, size_t len);
+int pb200_host_unregister(pb200_ctx* ctx, void* ptr);
+
 /* ---- Rows / GroupBy --------------------------------------------- */
 
 /* Rows(field[, previous=][, column=][, limit=]) over the local shards: executeRows /

@@ -362,6 +362,21 @@ extern "C" int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t sh
   return upload_fragment(ctx, fam, shard, cs);
 }
 
+extern "C" int pb200_host_register(pb200_ctx* ctx, void* ptr, size_t len) {
+  ENTER(ctx);
+  if (!ptr || !len) return PB200_ERR_INVALID;
+  CUDA_TRY(ctx, cudaHostRegister(ptr, len, cudaHostRegisterDefault));
+  return PB200_OK;
+}
+
+extern "C" int pb200_host_unregister(pb200_ctx* ctx, void* ptr) {
+  ENTER(ctx);
+  if (!ptr) return PB200_ERR_INVALID;
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CUDA_TRY(ctx, cudaHostUnregister(ptr));
+  return PB200_OK;
+}
+
 extern "C" int pb200_frag_import_roaring(pb200_ctx* ctx, pb200_family family, uint64_t shard, const void* data, size_t len, int clear,
                                          int64_t* changed) {
   ENTER(ctx);

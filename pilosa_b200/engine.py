@@ -79,6 +79,8 @@ def load_library() -> C.CDLL:
         "pb200_eval": (i32, [vp, np_, u32, u64, C.c_char_p, sz, C.POINTER(sz)]),
         "pb200_eval_columns": (i32, [vp, np_, u32, u64, u64p, sz, C.POINTER(sz)]),
         "pb200_frag_import_roaring": (i32, [vp, u32, u64, C.c_char_p, sz, i32, C.POINTER(C.c_int64)]),
+        "pb200_host_register": (i32, [vp, vp, sz]),
+        "pb200_host_unregister": (i32, [vp, vp]),
         "pb200_rows": (i32, [vp, u32, u64, u32, u64, u64, u64p, u32, u64p, sz, C.POINTER(sz)]),
         "pb200_groupby": (i32, [vp, vp, u32, np_, u32, u64, u64p, u32, vp, sz, C.POINTER(sz)]),
         "pb200_eval_shards": (i32, [vp, np_, u32, u64p, u32, vp, sz, u64p, C.POINTER(sz)]),
@@ -123,8 +125,16 @@ class Engine:
         self._rows_buf = None
         self.device = device
 
+    def _release_rows_buf(self) -> None:
+        if getattr(self, "_rows_pinned", False) and getattr(self, "_h", None):
+            self.lib.pb200_host_unregister(self._h, C.addressof(self._rows_c))
+        self._rows_pinned = False
+        self._rows_c = None
+        self._rows_buf = None
+
     def close(self) -> None:
         if getattr(self, "_h", None):
+            self._release_rows_buf()
             self.lib.pb200_shutdown(self._h)
             self._h = None
 
@@ -271,8 +281,12 @@ class Engine:
         ns = len(shards)
         cap = max(1, ns) * (131072 + 536)
         if self._rows_buf is None or len(self._rows_buf) < cap:
+            self._release_rows_buf()
             self._rows_buf = bytearray(cap)
-        buf = (C.c_char * cap).from_buffer(self._rows_buf)
+            self._rows_c = (C.c_char * cap).from_buffer(self._rows_buf)
+            # page-locked once: the packed streams then arrive by direct DMA (pb200_host_register)
+            self._rows_pinned = self.lib.pb200_host_register(self._h, C.addressof(self._rows_c), cap) == 0
+        buf = self._rows_c
         off = (C.c_uint64 * (ns + 1))()
         n = C.c_size_t()
         self._check(self.lib.pb200_eval_shards(self._h, prog, len(prog), u64_array(shards) if ns else None, ns, buf, cap, off, C.byref(n)))
