@@ -151,6 +151,21 @@ def main():
             exp, cms = cpu_timed(lambda: c.count(call, cpu_sh))
             emit(rows, "C2", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
 
+        # the same queries with PB200_OPT_DENSIFY_MIN_BYTES = 1024 (second context: large arrays / runs kept as bitmaps)
+        eng_d = Engine(0)
+        eng_d.set_option(Engine.OPT_DENSIFY_MIN_BYTES, 1024)
+        gd = Executor(eng_d)
+        gd.create_field("m")
+        load_parallel(lambda s: synth.mixed(s, 0, 4, SEED), shards, lambda s: [lambda s_, fb: gd.load_fragment("m", s_, fb)], cores)
+        hbm = [sum(e.frag_stat(x.family("m"), s)[2] for s in shards) for e, x in ((eng, g), (eng_d, gd))]
+        for qname, call in (("Count(Union(r0..r3))", Union(*leaves)), ("Count(Difference(r0,r1,r2,r3))", Difference(*leaves)),
+                            ("Count(Xor(r0..r3))", Xor(*leaves)), ("Count(Intersect(r0,r1))", Intersect(leaves[0], leaves[1]))):
+            _, k, wms, ab, ln = timed(eng_d, lambda: gd.count(call, shards), args.reps)
+            same = gd.count(call, shards) == g.count(call, shards)
+            exp, cms = cpu_timed(lambda: c.count(call, cpu_sh), 1.0)
+            emit(rows, "C2", qname + " [densify >= 1024 B]", len(shards), k, wms, ab, ln, cms, len(cpu_sh), same and gd.count(call, cpu_sh) == exp,
+                 {"hbm_payload_bytes": hbm[1], "hbm_payload_bytes_as_loaded": hbm[0]})
+        eng_d.close()
         if "c2" in cfgs:
             a, b = leaves[0], leaves[1]
             ca, cb = g.count(a, shards), g.count(b, shards)

@@ -278,6 +278,16 @@ int pb200_eval_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
                       const uint64_t* shards, uint32_t n_shards, void* out, size_t cap,
                       uint64_t* out_off, size_t* out_len);
 
+/* Context options. No reference counterpart.
+ * PB200_OPT_DENSIFY_MIN_BYTES (default 0 = off): fragments loaded or rewritten AFTER the call keep
+ * array / run containers whose file payload is at least `value` bytes (<= 8192) as 8 KiB bitmaps
+ * in HBM. Results are unchanged; set-op calls over such containers take the streaming bitmap
+ * kernel instead of the shared-memory expansion (about 2x on the mixed-container config at
+ * value = 1024) at the price of HBM capacity (at most 8192 / value times the payload).
+ * pb200_last_timing().algo_bytes keeps counting the reference's encoding. */
+#define PB200_OPT_DENSIFY_MIN_BYTES 1u
+int pb200_set_option(pb200_ctx* ctx, uint32_t option, uint64_t value);
+
 /* Page-lock a caller-owned host buffer (cudaHostRegister) so that result copies into it — the
  * packed streams of pb200_eval_shards are 128 KiB per dense shard — run as direct DMA at PCIe
  * speed instead of through the driver's pageable staging. Optional: every entry point also works

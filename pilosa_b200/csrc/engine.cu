@@ -246,7 +246,7 @@ static void default_rank(Fragment& f) {
 static int upload_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const std::vector<HostContainer>& cs) {
   FragImage img;
   std::string err;
-  if (!build_image(cs, img, err)) return fail(ctx, PB200_ERR_FORMAT, err);
+  if (!build_image(cs, img, err, ctx->densify_min_bytes)) return fail(ctx, PB200_ERR_FORMAT, err);
   if (ctx->budget && ctx->used + img.blob.size() > ctx->budget) return fail(ctx, PB200_ERR_NOMEM, "HBM budget exhausted");
   TRY(family_grow(ctx, fam, shard));
   void* blob = nullptr;
@@ -360,6 +360,17 @@ extern "C" int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t sh
     if (!cs.back().owned.empty()) cs.back().data = cs.back().owned.data();
   }
   return upload_fragment(ctx, fam, shard, cs);
+}
+
+extern "C" int pb200_set_option(pb200_ctx* ctx, uint32_t option, uint64_t value) {
+  ENTER(ctx);
+  switch (option) {
+    case PB200_OPT_DENSIFY_MIN_BYTES:
+      if (value > kBitmapBytes) return fail(ctx, PB200_ERR_INVALID, "densify threshold above 8192 bytes");
+      ctx->densify_min_bytes = uint32_t(value);
+      return PB200_OK;
+    default: return fail(ctx, PB200_ERR_INVALID, "unknown option");
+  }
 }
 
 extern "C" int pb200_host_register(pb200_ctx* ctx, void* ptr, size_t len) {

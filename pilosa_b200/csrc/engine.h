@@ -100,6 +100,7 @@ struct pb200_ctx {
   unsigned long long* dense_ovf_dev = nullptr;
   pb200::DevBuf d_batch, d_out, d_slow, d_temp, d_dense, d_dense_n, d_misc, d_topn, d_bsi;
   pb200::PinBuf h_stage, h_out, h_algo, h_topn;
+  uint32_t densify_min_bytes = 0;  // PB200_OPT_DENSIFY_MIN_BYTES (0 = containers stay as loaded)
   bool topn_attr_set = false, sum_attr_set = false, mm_attr_set = false;
   uint32_t range_attr_set = 0;  // per instantiation of bsi_range_pipe_kernel
   int occ_range[8] = {0, 0, 0, 0, 0, 0, 0, 0};

@@ -383,7 +383,12 @@ struct FragImage {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-inline bool build_image(const std::vector<HostContainer>& cs, FragImage& img, std::string& err) {
+// densify_min_bytes > 0: array / run containers whose payload is at least that large are stored as 8 KiB
+// bitmaps (HBM capacity traded for the streaming path of the evaluator); 0 keeps every container as loaded.
+inline bool build_image(const std::vector<HostContainer>& cs, FragImage& img, std::string& err, uint32_t densify_min_bytes = 0) {
+  auto densify = [&](const HostContainer& c) {
+    return densify_min_bytes && c.n && c.n != kFullN && (c.type == kArray || c.type == kRun) && payload_bytes(c.type, c.len) >= densify_min_bytes;
+  };
   // rows present
   img.row_ids.clear(); img.row_counts.clear();
   for (auto& c : cs) {
@@ -406,8 +411,9 @@ inline bool build_image(const std::vector<HostContainer>& cs, FragImage& img, st
   img.payload_off = off;
   size_t psize = 0;
   for (auto& c : cs) {
-    psize = align_up(psize, c.type == kBitmap ? 128 : 16);
-    psize += payload_bytes(c.type, c.len);
+    const bool dz = densify(c);
+    psize = align_up(psize, c.type == kBitmap || dz ? 128 : 16);
+    psize += dz ? kBitmapBytes : payload_bytes(c.type, c.len);
   }
   img.blob.assign(off + align_up(psize, 128) + 128, 0);  // +128: kernels may over-read a 16 B tail
   if (!img.dense) std::memcpy(img.blob.data() + img.row_ids_off, img.row_ids.data(), img.row_ids.size() * 8);
@@ -420,16 +426,23 @@ inline bool build_image(const std::vector<HostContainer>& cs, FragImage& img, st
     uint64_t row = c.key >> 4;
     while (img.row_ids[ri] != row) ri++;
     size_t slot = (img.dense ? size_t(row) : ri) * kRowContainers + (c.key & 15);
-    p = align_up(p, c.type == kBitmap ? 128 : 16);
+    const bool dz = densify(c);
+    p = align_up(p, c.type == kBitmap || dz ? 128 : 16);
     uint32_t pb = payload_bytes(c.type, c.len);
-    std::memcpy(img.blob.data() + p, c.data, pb);
     descs[slot].addr = p;
     descs[slot].n = c.n;
-    descs[slot].meta = make_meta(c.type, c.len);
+    if (dz) {
+      to_words(c, reinterpret_cast<uint64_t*>(img.blob.data() + p));  // 128 B aligned inside the blob
+      descs[slot].meta = make_meta_densified(pb);
+      pb = kBitmapBytes;
+    } else {
+      std::memcpy(img.blob.data() + p, c.data, pb);
+      descs[slot].meta = make_meta(c.type, c.len);
+    }
     p += pb;
     img.n_containers++;
     img.payload_bytes += pb;
-    if (!(c.type == kBitmap || c.n == kFullN)) img.all_bitmap = false;
+    if (!(c.type == kBitmap || dz || c.n == kFullN)) img.all_bitmap = false;
   }
   return true;
 }

@@ -79,6 +79,7 @@ __device__ __forceinline__ bool is_const_or_bitmap(const ContainerDesc& d) {
 
 __device__ __forceinline__ uint32_t desc_algo_bytes(const ContainerDesc& d) {
   if (d.n == 0) return 0;
+  if (desc_densified(d)) return 16u + desc_file_bytes(d);  // algorithmic bytes follow the reference's encoding
   uint32_t t = desc_type(d), l = desc_len(d);
   return 16u + (t == kBitmap ? uint32_t(kBitmapBytes) : t == kArray ? l * 2u : l * 4u);
 }

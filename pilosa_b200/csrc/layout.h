@@ -18,13 +18,20 @@ struct __attribute__((aligned(16))) ContainerDesc {
   uint64_t addr;  // device address of the payload: array = n x u16 sorted; bitmap = 1024 x u64;
                   // run = len x {u16 start, u16 last}. 16 B aligned (bitmaps 128 B aligned).
   uint32_t n;     // cardinality, 0..65536 (0 = nil container)
-  uint32_t meta;  // bits 0-1: CType; bits 2-31: len (array: n, run: number of runs, bitmap: 1024)
+  uint32_t meta;  // bits 0-1: CType; bits 2-14: len (array: n, run: number of runs, bitmap: 1024);
+                  // bit 31: stored as a bitmap although the file held an array / run (load-time densify
+                  // option), bits 15-30 then keep the file encoding's payload bytes for the byte accounting
 };
 static_assert(sizeof(ContainerDesc) == 16, "ContainerDesc must be 16 B");
 
 __host__ __device__ inline uint32_t desc_type(const ContainerDesc& d) { return d.meta & 3u; }
-__host__ __device__ inline uint32_t desc_len(const ContainerDesc& d) { return d.meta >> 2; }
+__host__ __device__ inline uint32_t desc_len(const ContainerDesc& d) { return (d.meta >> 2) & 0x1fffu; }
 __host__ __device__ inline uint32_t make_meta(uint32_t type, uint32_t len) { return type | (len << 2); }
+__host__ __device__ inline bool desc_densified(const ContainerDesc& d) { return (d.meta >> 31) != 0; }
+__host__ __device__ inline uint32_t desc_file_bytes(const ContainerDesc& d) { return (d.meta >> 15) & 0xffffu; }
+__host__ __device__ inline uint32_t make_meta_densified(uint32_t file_payload_bytes) {
+  return make_meta(2u /* kBitmap */, 1024u) | (file_payload_bytes << 15) | 0x80000000u;
+}
 
 // One fragment = all rows of one (field, view) for one shard (fragment.go:100-140).
 // rows[i*16 + c] is container c of the i-th row; replaces the B+tree keyed by

@@ -79,6 +79,7 @@ def load_library() -> C.CDLL:
         "pb200_eval": (i32, [vp, np_, u32, u64, C.c_char_p, sz, C.POINTER(sz)]),
         "pb200_eval_columns": (i32, [vp, np_, u32, u64, u64p, sz, C.POINTER(sz)]),
         "pb200_frag_import_roaring": (i32, [vp, u32, u64, C.c_char_p, sz, i32, C.POINTER(C.c_int64)]),
+        "pb200_set_option": (i32, [vp, u32, u64]),
         "pb200_host_register": (i32, [vp, vp, sz]),
         "pb200_host_unregister": (i32, [vp, vp]),
         "pb200_rows": (i32, [vp, u32, u64, u32, u64, u64, u64p, u32, u64p, sz, C.POINTER(sz)]),
@@ -124,6 +125,11 @@ class Engine:
         self._h = h
         self._rows_buf = None
         self.device = device
+
+    OPT_DENSIFY_MIN_BYTES = 1
+
+    def set_option(self, option: int, value: int) -> None:
+        self._check(self.lib.pb200_set_option(self._h, option, value))
 
     def _release_rows_buf(self) -> None:
         if getattr(self, "_rows_pinned", False) and getattr(self, "_h", None):

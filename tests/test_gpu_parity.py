@@ -323,6 +323,42 @@ def test_import_roaring(pair):
         ex.be.frag_drop(ex.family("m"), 9)
 
 
+def test_densify_option_changes_layout_not_results():
+    """PB200_OPT_DENSIFY_MIN_BYTES: large array / run containers kept as bitmaps in HBM; every result and the
+    algorithmic byte count stay what they are without it."""
+    from pilosa_b200.engine import Engine
+
+    shards = [0, 1, 2]
+    calls = [Union(*[Row("m", r) for r in range(4)]), Difference(*[Row("m", r) for r in range(4)]), Xor(Row("m", 0), Row("m", 5), Row("sp", 1)),
+             Intersect(Row("m", 1), Row("sp", 0)), Not(Row("m", 2)), Shift(Row("m", 3), n=1)]
+    res = []
+    for thr in (0, 512):
+        eng = Engine(0)
+        if thr:
+            eng.set_option(Engine.OPT_DENSIFY_MIN_BYTES, thr)
+        ex = Executor(eng)
+        for name in ("m", "sp", "z", "exists"):
+            ex.create_field(name)
+        for s in shards:
+            ex.load_fragment("m", s, synth.mixed(s, 0, 8))
+            ex.load_fragment("sp", s, synth.bernoulli(s, 0, 4, 1e-4))
+            ex.load_fragment("z", s, synth.zipf(s, n_rows=200, k=4))
+            ex.load_fragment("exists", s, synth.bernoulli(s, 0, 1, 0.9))
+        out = [ex.count(c_, shards) for c_ in calls]
+        algo = eng.last_timing().algo_bytes
+        out.append([ex.row_segments(c_, shards) for c_ in calls[:3]])
+        out.append(ex.topn("z", shards, n=10, src=Row("m", 1)))
+        out.append(ex.group_by([__import__("pilosa_b200.executor", fromlist=["RowsCall"]).RowsCall("m")], shards, filter_call=Row("z", 3)))
+        eng.frag_apply(ex.family("m"), 0, set_pos=[5, (1 << 20) * 3 + 77], clear_pos=[(1 << 20) + 9])  # rewrite goes through the option too
+        out.append(ex.count(calls[0], shards))
+        res.append((out, algo, eng.frag_stat(ex.family("m"), 0), eng.frag_stat(ex.family("sp"), 0)))
+        eng.close()
+    (plain, algo0, m0, sp0), (dense, algo1, m1, sp1) = res
+    assert plain == dense
+    assert algo0 == algo1                      # byte accounting follows the reference's encoding
+    assert m1[2] > m0[2] and sp1[2] == sp0[2]  # payload bytes: mixed field grew, the tiny arrays stayed
+
+
 def test_ops_log_replay_on_load(pair):
     g, c, _ = pair
     base = synth.bernoulli(7, 0, 2, 0.001).bytes()
