@@ -412,3 +412,64 @@ def test_executor_group_by(w):
     exp = [((i // 16, (i % 16) // 4, i % 4), 1) for i in range(64)]
     exp[63] = ((3, 3, 3), 5)
     assert total == exp
+
+
+# ---- fragment_internal_test.go:1463-1509 TestFragment_Tanimoto / TestFragment_Zero_Tanimoto ----
+def test_fragment_tanimoto(w):
+    w.create_field("f")
+    src = w.new_row(1, 2, 3)
+    w.set_bits("f", 100, 1, 3, 2, 200)
+    w.set_bits("f", 101, 1, 3)
+    w.set_bits("f", 102, 1, 2, 10, 12)
+    w.recalculate_cache("f")
+    assert w.frag_top("f", src=src, tanimoto=50) == [(100, 3), (101, 2)]
+    assert w.frag_top("f", src=src, tanimoto=0) == [(100, 3), (101, 2), (102, 2)]
+
+
+# ---- fragment_internal_test.go:2634-2712 TestFragment_RowsIteration ----
+def test_fragment_rows_iteration(w):
+    w.create_field("f")
+    for i in range(100, 200):
+        w.set_bit("f", i, i % 2)
+    assert w.frag_rows("f") == list(range(100, 200))
+    assert w.frag_rows("f", column=1) == list(range(101, 200, 2))
+    w.create_field("g")
+    w.set_bit("g", 1, 66000)
+    w.set_bit("g", 2, 66000)
+    w.set_bit("g", 2, 166000)
+    assert w.frag_rows("g") == [1, 2] and w.frag_rows("g", column=66000) == [1, 2]
+    w.create_field("h")   # "combinations", thinned out: every new bit keeps both listings complete
+    expected = []
+    for r in range(1, 10000, 1100):
+        expected.append(r)
+        for c in range(1, SW - 1, 210000):
+            w.set_bit("h", r, c)
+            assert w.frag_rows("h") == expected
+            assert w.frag_rows("h", column=c) == expected
+
+
+# ---- fragment_internal_test.go:2715-2760 TestFragment_RoaringImport ----
+def test_fragment_roaring_import(w):
+    import oracle
+
+    tests = [[[0], [1]],
+             [[0, 65535, 65536, 65537, 65538, 65539, 130000], [1000, 67000, 130000]],
+             [[0, 65535, 65536, 65537, 65538, 65539, 130000], [0, 65535, 65536, 65537, 65538, 65539, 130000]],
+             [[0, 65535, 65536, (1 << 20) + 1, (1 << 20) * 2 + 1], [1, (1 << 20) + 2, (1 << 20) * 2 + 2]]]
+    for i, test in enumerate(tests):
+        name = f"imp{i}"
+        w.create_field(name)
+        w.set_bit(name, 9, 9)  # the fragment exists on both sides before the first import
+        seen = set()
+        for positions in test:
+            changed = w.import_roaring(name, 0, oracle.Bitmap(*positions).serialize(), False)
+            assert changed == len(set(positions) - seen)
+            seen |= set(positions)
+            by_row = {}
+            for p in sorted(seen):  # calcExpected: position -> (row, column)
+                by_row.setdefault(p >> 20, []).append(p & (SW - 1))
+            for row, cols in by_row.items():
+                assert w.ex.row_columns(Row(name, row), [0]) == cols, (i, row)
+        removed = w.import_roaring(name, 0, oracle.Bitmap(*test[0]).serialize(), True)  # and clearing them again
+        assert removed == len(set(test[0]))
+        assert sum(w.ex.count(Row(name, r), [0]) for r in range(3)) == len(seen - set(test[0]))

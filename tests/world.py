@@ -153,3 +153,16 @@ class World:
         bd = bit_depth if bit_depth is not None else ex.fields[field].bsig.bit_depth
         call = abi.Call("Range", field_name=field, bsi_op=op, a=a, b=b, bit_depth=bd)
         return ex.be.eval_columns(ex.program(call), shard)
+
+    def frag_rows(self, field: str, shard: int = 0, start: int = 0, column: Optional[int] = None, limit: Optional[int] = None) -> List[int]:
+        """fragment.rows(start, filters...) of one shard."""
+        ex = self.ex
+        return ex.be.rows(ex.family(field), [shard], start=start, column=column, limit=limit)
+
+    def import_roaring(self, field: str, shard: int, data: bytes, clear: bool = False) -> int:
+        """fragment.importRoaring on the oracle AND, independently, on the engine's resident copy."""
+        self.sync()
+        n = self.orc.frag_import_roaring(self.cpu.family(field, self._view(field)), shard, data, clear)
+        if self.gpu:
+            assert self.eng.frag_import_roaring(self.gpu.family(field, self._view(field)), shard, data, clear) == n
+        return n
