@@ -122,6 +122,20 @@ class Executor:
     def local_shards(self, shards: Sequence[int]) -> List[int]:
         return [s for s in shards if self.owns(s)]
 
+    def _local(self, shards: Sequence[int]):
+        """local_shards(); a shard list passed as a TUPLE is marshalled to the C array once and cached
+        (converting 8192 Python ints costs more than the query they address)."""
+        if not isinstance(shards, tuple):
+            return self.local_shards(shards)
+        cache = self.__dict__.setdefault("_local_cache", {})
+        hit = cache.get(shards)
+        if hit is None:
+            if len(cache) >= 32:
+                cache.clear()
+            lst = self.local_shards(shards)
+            hit = cache[shards] = abi.u64_array(lst) if lst else lst
+        return hit
+
     # ---- call-tree helpers ----
     def row_range(self, field_name: str, op: int, value: Optional[int] = None, value2: Optional[int] = None) -> Call:
         """Row(field <op> value): executeRowBSIGroupShard's host-side pre-checks
@@ -176,13 +190,13 @@ class Executor:
 
     # ---- queries (executor.go) ----
     def count(self, call: Call, shards: Sequence[int]) -> int:  # executeCount :1793
-        local = self.local_shards(shards)
-        n = self.be.count(self.program(call), local) if local else 0
+        local = self._local(shards)
+        n = self.be.count(self.program(call), local) if len(local) else 0
         return _u64(self._allreduce_ints([_i64(n)])[0])
 
     def count_batch(self, calls: Sequence[Call], shards: Sequence[int]) -> List[int]:
-        local = self.local_shards(shards)
-        vals = [int(v) for v in self.be.count_batch([self.program(c) for c in calls], local)[: len(calls)]] if local else [0] * len(calls)
+        local = self._local(shards)
+        vals = [int(v) for v in self.be.count_batch([self.program(c) for c in calls], local)[: len(calls)]] if len(local) else [0] * len(calls)
         return [_u64(v) for v in self._allreduce_ints([_i64(v) for v in vals])]
 
     def row_columns(self, call: Call, shards: Sequence[int]) -> List[int]:
