@@ -153,7 +153,7 @@ import torch.distributed as dist
 import oracle
 from pilosa_b200 import abi, synth
 from pilosa_b200.abi import Intersect, Row, Union
-from pilosa_b200.executor import Executor
+from pilosa_b200.executor import Executor, RowsCall as R
 
 dist.init_process_group("gloo", init_method="tcp://127.0.0.1:{port}", rank=int(sys.argv[1]), world_size=2)
 rank = dist.get_rank()
@@ -180,6 +180,14 @@ checks = [
     (ex2.topn("z", shards, n=5, src=src), ex1.topn("z", shards, n=5, src=src)),
     (ex2.topn("z", shards, n=5, src=src, ids=[1, 2, 3]), ex1.topn("z", shards, n=5, src=src, ids=[1, 2, 3])),
     (ex2.count(ex2.row_range("v", abi.BSI_GT, 0), shards), ex1.count(ex1.row_range("v", abi.BSI_GT, 0), shards)),
+    (ex2.count(src, tuple(shards)), ex1.count(src, tuple(shards))),      # tuple shard lists: cached marshalling
+    (ex2.count(src, tuple(shards)), ex1.count(src, shards)),
+    (ex2.rows("z", shards), ex1.rows("z", shards)),
+    (ex2.rows("z", shards, previous=3, limit=4), ex1.rows("z", shards, previous=3, limit=4)),
+    (ex2.rows("z", shards, column=(3 << 20) + 5), ex1.rows("z", shards, column=(3 << 20) + 5)),
+    (ex2.group_by([R("f"), R("z", limit=5)], shards), ex1.group_by([R("f"), R("z", limit=5)], shards)),
+    (ex2.group_by([R("f"), R("f")], shards, filter_call=Row("z", 1), limit=4), ex1.group_by([R("f"), R("f")], shards, filter_call=Row("z", 1), limit=4)),
+    (ex2.row_segments(src, shards), [(s_, b_) for s_, b_ in ex1.row_segments(src, shards) if s_ % 2 == rank]),
 ]
 for i, (got, exp) in enumerate(checks):
     assert got == exp, (i, got, exp)
