@@ -317,3 +317,16 @@ def test_official_roaring_format_golden_vectors():
             oracle.Bitmap.deserialize(a[:cut])
         with pytest.raises(EngineError):
             host_check_roaring(a[:cut])
+
+
+def test_plain_c_host_builds_and_fails_loudly_without_a_gpu():
+    """examples/count_c.c is a C (not C++) translation unit over include/pilosa_b200.h: it must compile with gcc,
+    link against the library alone, and — like every product path — refuse to run without a CUDA device."""
+    exe = os.path.join(ROOT, "examples", "count_c")
+    assert os.path.exists(exe), "make -C pilosa_b200/csrc builds it"
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu test")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert r.returncode != 0 and "pb200_init" in r.stderr and "C host ok" not in r.stdout

@@ -388,3 +388,13 @@ def test_error_behaviour(pair):
         g.be.frag_load(g.family("f"), 0, b"\x00" * 64)
     # a failed load leaves the resident fragment intact
     assert g.count(Row("f", 1), [0]) > 0
+
+
+def test_plain_c_host_runs():
+    """The C example (no Python, no torch in the process) drives load / count / eval_shards / TopN through the C ABI."""
+    import os
+    import subprocess
+
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples", "count_c")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "C host ok" in r.stdout, r.stdout + r.stderr
