@@ -76,9 +76,10 @@ def bit_depth_int64(v: int) -> int:  # field.go:1616-1621
 @dataclass
 class Field:
     name: str
-    type: str = "set"  # set | int
+    type: str = "set"  # set | int | time
     families: Dict[str, int] = field(default_factory=dict)  # view -> family handle
     bsig: Optional[BsiGroup] = None
+    time_quantum: str = ""  # "YMDH" subset for time fields (time.go:29-58)
 
 
 class Executor:
@@ -88,8 +89,8 @@ class Executor:
         self.fields: Dict[str, Field] = {}
 
     # ---- schema / loading (host bookkeeping; holder.go / field.go stay in Go) ----
-    def create_field(self, name: str, type: str = "set", min: int = 0, max: int = 0) -> Field:
-        f = Field(name, type)
+    def create_field(self, name: str, type: str = "set", min: int = 0, max: int = 0, time_quantum: str = "") -> Field:
+        f = Field(name, type, time_quantum=time_quantum)
         if type == "int":
             # field.go:1047-1066: BitDepth from the declared range, Base 0 for new fields
             f.bsig = BsiGroup(min=min, max=max, base=0, bit_depth=builtins_max(bit_depth_int64(min), bit_depth_int64(max)))
@@ -137,6 +138,25 @@ class Executor:
         return hit
 
     # ---- call-tree helpers ----
+    def row_time(self, field_name: str, row: int, from_time, to_time) -> Call:
+        """Row(f=row, from=, to=) on a time field (executeRowShard, executor.go:1501-1531): the union of the row
+        over the time-quantum views that tile [from, to) (viewsByTimeRange, time.go:104-181). Views the field does
+        not have are skipped, as the reference skips a view without a fragment (:1519-1522); the result is Empty
+        without a quantum or without any such view. The union is an ordinary n-ary Union of Row leaves, one per
+        view family, so it counts against the 32 leaves of a call."""
+        from .timeviews import VIEW_STANDARD, views_by_time_range
+
+        f = self.fields.get(field_name)
+        if f is None:
+            raise KeyError(f"field not found: {field_name}")
+        if not f.time_quantum:
+            return Call("Empty")
+        rows = [Call("Row", field_name=field_name, row=row, view=v)
+                for v in views_by_time_range(VIEW_STANDARD, from_time, to_time, f.time_quantum) if v in f.families]
+        if not rows:
+            return Call("Empty")
+        return rows[0] if len(rows) == 1 else Call("Union", rows)
+
     def row_range(self, field_name: str, op: int, value: Optional[int] = None, value2: Optional[int] = None) -> Call:
         """Row(field <op> value): executeRowBSIGroupShard's host-side pre-checks
         (executor.go:1536-1665) reduced to a Range / NotNull / Empty leaf."""

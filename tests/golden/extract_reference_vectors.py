@@ -195,7 +195,23 @@ def official_roaring():
     print("official_roaring.json:", len(ok), "valid images,", len(bad), "header cases")
 
 
+def time_views():
+    """TestViewsByTimeRange (time_internal_test.go:87-160): (start, end, quantum) -> view names."""
+    src = open(os.path.join(REF, "time_internal_test.go")).read()
+    body = src[src.index("func TestViewsByTimeRange"):]
+    body = body[:body.index("\nfunc ", 10)]
+    cases = []
+    pat = re.compile(r'viewsByTimeRange\("F", mustParseTime\("([^"]+)"\), mustParseTime\("([^"]+)"\), mustParseTimeQuantum\("([A-Z]+)"\)\)\s*'
+                     r'if !reflect.DeepEqual\(a, \[\]string\{([^}]*)\}\)', re.S)
+    for m in pat.finditer(body):
+        cases.append({"start": m.group(1), "end": m.group(2), "quantum": m.group(3), "views": re.findall(r'"([^"]+)"', m.group(4))})
+    with open(os.path.join(OUT, "time_views.json"), "w") as f:
+        json.dump({"source": "time_internal_test.go:87-160 TestViewsByTimeRange", "cases": cases}, f, indent=0)
+    print("time_views.json:", len(cases), "cases")
+
+
 if __name__ == "__main__":
+    time_views()
     official_roaring()
     container_combinations()
     roaring_tables()

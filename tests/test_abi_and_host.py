@@ -330,3 +330,36 @@ def test_plain_c_host_builds_and_fails_loudly_without_a_gpu():
         pytest.skip("GPU present: covered by the gpu test")
     r = subprocess.run([exe], capture_output=True, text=True, timeout=60)
     assert r.returncode != 0 and "pb200_init" in r.stderr and "C host ok" not in r.stdout
+
+
+def test_time_quantum_views_golden_table_and_row_time():
+    """viewsByTimeRange (time.go:104-181) against the table of TestViewsByTimeRange (time_internal_test.go:87-160),
+    and the Row(from=, to=) composition of executor.go:1501-1531 on the host side."""
+    import json
+    from datetime import datetime
+
+    from pilosa_b200.timeviews import views_by_time, views_by_time_range
+
+    g = json.load(open(os.path.join(ROOT, "tests", "golden", "time_views.json")))
+    assert len(g["cases"]) == 13
+    ts = lambda s: datetime.strptime(s, "%Y-%m-%d %H:%M")
+    for c in g["cases"]:
+        assert views_by_time_range("F", ts(c["start"]), ts(c["end"]), c["quantum"]) == c["views"], c["quantum"]
+    assert views_by_time("F", ts("2000-01-02 03:00"), "YMDH") == ["F_2000", "F_200001", "F_20000102", "F_2000010203"]  # TestViewsByTime, time_internal_test.go:68-84
+    assert views_by_time("F", ts("2000-01-02 03:00"), "D") == ["F_20000102"]
+    assert views_by_time_range("F", ts("2001-01-01 00:00"), ts("2001-01-01 00:00"), "YMDH") == []                       # empty range
+
+    ex = Executor(oracle.Oracle(workers=1))
+    ex.create_field("t", type="time", time_quantum="YMD")
+    ex.create_field("plain")
+    for v, seed in (("standard_2001", 1), ("standard_200012", 2), ("standard_20001130", 3), ("standard_2003", 4)):
+        ex.load_fragment("t", 0, synth.bernoulli(0, 0, 2, 0.01, seed), view=v)
+    full = ex.row_time("t", 1, ts("2000-11-28 00:00"), ts("2003-03-02 00:00"))
+    assert full.name == "Union" and [k.view for k in full.children] == ["standard_20001130", "standard_200012", "standard_2001"]
+    one = ex.row_time("t", 1, ts("2001-01-01 00:00"), ts("2002-01-01 00:00"))
+    assert one.name == "Row" and one.view == "standard_2001"
+    assert ex.row_time("t", 1, ts("1990-01-01 00:00"), ts("1991-01-01 00:00")).name == "Empty"   # no such views
+    assert ex.row_time("plain", 1, ts("2000-01-01 00:00"), ts("2003-01-01 00:00")).name == "Empty"  # no quantum (:1502-1505)
+    parts = [ex.count(abi.Call("Row", field_name="t", row=1, view=k.view), [0]) for k in full.children]
+    assert 0 < ex.count(full, [0]) <= sum(parts) and ex.count(full, [0]) >= max(parts)
+    assert ex.count(one, [0]) == parts[2]

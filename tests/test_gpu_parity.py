@@ -359,6 +359,46 @@ def test_densify_option_changes_layout_not_results():
     assert m1[2] > m0[2] and sp1[2] == sp0[2]  # payload bytes: mixed field grew, the tiny arrays stayed
 
 
+def test_time_range_rows():
+    """Row(f=r, from=, to=) on a time field (executor.go:1501-1531): the union over the quantum views, engine vs oracle."""
+    from datetime import datetime
+
+    from pilosa_b200.engine import Engine
+
+    eng = Engine(0)
+    g, c = Executor(eng), Executor(oracle.Oracle(workers=4))
+    shards = [0, 1, 3]
+    views = ["standard_2000112822", "standard_2000112823", "standard_20001129", "standard_200012", "standard_2001", "standard_200201",
+             "standard_2002030100", "standard_1999", "standard"]
+    for ex in (g, c):
+        ex.create_field("t", type="time", time_quantum="YMDH")
+        ex.create_field("f")
+    for s in shards:
+        for i, v in enumerate(views):
+            if s == 3 and i % 3 == 0:
+                continue  # some views have no fragment in some shards (:1519-1522)
+            fb = synth.mixed(s, 0, 3, 100 + i) if i % 2 else synth.bernoulli(s, 0, 3, 0.02, 100 + i)
+            for ex in (g, c):
+                ex.load_fragment("t", s, fb, view=v)
+        for ex in (g, c):
+            ex.load_fragment("f", s, synth.bernoulli(s, 0, 2, 0.1))
+    t = lambda s_: datetime.strptime(s_, "%Y-%m-%d %H:%M")
+    ranges = [("2000-11-28 22:00", "2002-03-01 03:00"), ("2000-11-28 23:00", "2000-11-30 00:00"), ("2001-01-01 00:00", "2002-01-01 00:00"),
+              ("1990-01-01 00:00", "1991-01-01 00:00"), ("2000-12-01 00:00", "2002-02-01 00:00")]
+    seen = set()
+    for a, b in ranges:
+        for row in (0, 2):
+            gc, cc = g.row_time("t", row, t(a), t(b)), c.row_time("t", row, t(a), t(b))
+            assert repr(gc) == repr(cc)
+            seen.add(gc.name)
+            assert g.count(gc, shards) == c.count(cc, shards), (a, b, row)
+            assert g.row_segments(gc, shards) == c.row_segments(cc, shards), (a, b, row)
+            both = Intersect(gc, Row("f", 1))
+            assert g.count(both, shards) == c.count(Intersect(cc, Row("f", 1)), shards)
+    assert seen == {"Union", "Row", "Empty"}
+    eng.close()
+
+
 def test_ops_log_replay_on_load(pair):
     g, c, _ = pair
     base = synth.bernoulli(7, 0, 2, 0.001).bytes()
