@@ -123,7 +123,7 @@ def main():
     # Launch/latency-bound: 4 MiB of operands stay L2-resident when the same pair is repeated, so
     # the GB/s figure here is an L2 number, labelled as such; the HBM-bound batched figure is bench.py's.
     if "c1" in cfgs:
-        shards = list(range(16))
+        shards = tuple(range(16))
         both("f")
         load_parallel(lambda s: synth.bernoulli(s, 0, 8, 0.10, SEED), shards, sinks_for("f", set(shards)), cores)
         call = Intersect(Row("f", 1), Row("f", 2))
@@ -137,7 +137,7 @@ def main():
 
     # ---------------- C2: Count(Union/Difference/Xor) over 4 rows, mixed containers ----------------
     if "c2" in cfgs:
-        shards = list(range(args.c2_shards))
+        shards = tuple(range(args.c2_shards))
         cpu_sh = shards[: args.cpu_shards]
         both("m")
         t0 = time.perf_counter()
@@ -180,7 +180,7 @@ def main():
 
     # ---------------- C3: TopN(f, n=50) over 10k rows with an Intersect filter ----------------
     if "c3" in cfgs:
-        shards = list(range(args.c3_shards))
+        shards = tuple(range(args.c3_shards))
         cpu_sh = shards[: max(4, args.cpu_shards // 4)]
         both("z")
         both("a")
@@ -206,7 +206,7 @@ def main():
 
     # ---------------- C4: BSI int32: Sum / Min / Max / Range ----------------
     if "c4" in cfgs:
-        shards = list(range(args.c4_shards))
+        shards = tuple(range(args.c4_shards))
         cpu_sh = shards[: max(4, args.cpu_shards // 4)]
         both("v", type="int", min=-(1 << 31), max=(1 << 31) - 1)
         both("fl")
@@ -255,7 +255,7 @@ def main():
     if "c5" in cfgs:
         sweep = [int(x) for x in args.c5_shards.split(",")]
         nmax = max(sweep)
-        shards = list(range(nmax))
+        shards = tuple(range(nmax))
         cpu_sh = shards[: min(nmax, 512)]
         both("sp")
         t0 = time.perf_counter()
@@ -278,7 +278,7 @@ def main():
     # ---------------- GB: GroupBy over two / three set fields ----------------
     if "gb" in cfgs:
         from pilosa_b200.executor import RowsCall as R
-        shards = list(range(args.gb_shards))
+        shards = tuple(range(args.gb_shards))
         cpu_sh = shards[: max(4, args.cpu_shards // 4)]
         for name, nrows, p_ in (("ga", 16, 0.10), ("gb", 64, 0.02), ("gc", 8, 0.25)):
             both(name)

@@ -264,9 +264,9 @@ class Executor:
 
     def sum(self, field_name: str, shards: Sequence[int], filter_call: Optional[Call] = None) -> Tuple[int, int]:  # executeSum :409
         f = self.fields[field_name]
-        local = self.local_shards(shards)
+        local = self._local(shards)
         fp = self.program(filter_call) if filter_call is not None else None
-        s, c = self.be.bsi_sum(self.family(field_name, "bsig_" + field_name), f.bsig.bit_depth, fp, local) if local else (0, 0)
+        s, c = self.be.bsi_sum(self.family(field_name, "bsig_" + field_name), f.bsig.bit_depth, fp, local) if len(local) else (0, 0)
         s, c = self._allreduce_ints([s, c])
         if c == 0:
             return 0, 0
@@ -274,13 +274,19 @@ class Executor:
 
     def _minmax(self, field_name: str, shards: Sequence[int], filter_call: Optional[Call], is_max: bool) -> Tuple[int, int]:
         f = self.fields[field_name]
-        local = [(i, s) for i, s in enumerate(shards) if self.owns(s)]
+        local = self._local(shards)
         fp = self.program(filter_call) if filter_call is not None else None
+        if self.world == 1:  # one rank: the library folds ValCount.smaller / larger itself, in shard-list order
+            if not len(local):
+                return 0, 0
+            fam = self.family(field_name, "bsig_" + field_name)
+            v, c = (self.be.bsi_max if is_max else self.be.bsi_min)(fam, f.bsig.bit_depth, fp, local)
+            return (v + f.bsig.base, c) if c else (0, 0)  # executor.go:759,797
+        positions = [i for i, s in enumerate(shards) if self.owns(s)]  # places of the local shards in the caller's list
         best = None  # (val, count, position in the caller's shard list)
-        if local:
-            vals, counts = self.be.bsi_minmax_shards(self.family(field_name, "bsig_" + field_name), f.bsig.bit_depth, fp,
-                                                    [s for _, s in local], is_max)
-            for (pos, _), v, c in zip(local, vals, counts):
+        if len(local):
+            vals, counts = self.be.bsi_minmax_shards(self.family(field_name, "bsig_" + field_name), f.bsig.bit_depth, fp, local, is_max)
+            for pos, v, c in zip(positions, vals, counts):
                 if c == 0:
                     continue
                 if best is None or (v > best[0] if is_max else v < best[0]):
@@ -304,15 +310,15 @@ class Executor:
              threshold: int = 0, tanimoto: int = 0) -> List[Tuple[int, int]]:  # executeTopN :863
         fam = self.family(field_name)
         sp = self.program(src) if src is not None else None
-        local = self.local_shards(shards)
+        local = self._local(shards)
         if self.world == 1:
             return self.be.topn(fam, sp, n, local, ids=list(ids), min_threshold=threshold, tanimoto=tanimoto)
-        p1 = self.be.topn(fam, sp, n, local, ids=list(ids), min_threshold=threshold, tanimoto=tanimoto, remote=True) if local else []
+        p1 = self.be.topn(fam, sp, n, local, ids=list(ids), min_threshold=threshold, tanimoto=tanimoto, remote=True) if len(local) else []
         pairs = _merge_pairs(self._allgather_pairs(p1))
         if not pairs or ids:
             return pairs
         ids2 = sorted(i for i, _ in pairs)
-        p2 = self.be.topn(fam, sp, n, local, ids=ids2, min_threshold=threshold, tanimoto=tanimoto, remote=True) if local else []
+        p2 = self.be.topn(fam, sp, n, local, ids=ids2, min_threshold=threshold, tanimoto=tanimoto, remote=True) if len(local) else []
         out = _merge_pairs(self._allgather_pairs(p2))
         return out[:n] if n else out
 
