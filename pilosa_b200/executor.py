@@ -137,6 +137,18 @@ class Executor:
             hit = cache[shards] = abi.u64_array(lst) if lst else lst
         return hit
 
+    def _local_positions(self, shards: Sequence[int]):
+        """Index of every local shard in the caller's list (cached for tuples, like _local)."""
+        if not isinstance(shards, tuple):
+            return [i for i, s in enumerate(shards) if self.owns(s)]
+        cache = self.__dict__.setdefault("_position_cache", {})
+        hit = cache.get(shards)
+        if hit is None:
+            if len(cache) >= 32:
+                cache.clear()
+            hit = cache[shards] = [i for i, s in enumerate(shards) if self.owns(s)]
+        return hit
+
     # ---- call-tree helpers ----
     def row_time(self, field_name: str, row: int, from_time, to_time) -> Call:
         """Row(f=row, from=, to=) on a time field (executeRowShard, executor.go:1501-1531): the union of the row
@@ -282,7 +294,7 @@ class Executor:
             fam = self.family(field_name, "bsig_" + field_name)
             v, c = (self.be.bsi_max if is_max else self.be.bsi_min)(fam, f.bsig.bit_depth, fp, local)
             return (v + f.bsig.base, c) if c else (0, 0)  # executor.go:759,797
-        positions = [i for i, s in enumerate(shards) if self.owns(s)]  # places of the local shards in the caller's list
+        positions = self._local_positions(shards)  # places of the local shards in the caller's list
         best = None  # (val, count, position in the caller's shard list)
         if len(local):
             vals, counts = self.be.bsi_minmax_shards(self.family(field_name, "bsig_" + field_name), f.bsig.bit_depth, fp, local, is_max)
