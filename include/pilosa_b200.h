@@ -149,9 +149,16 @@ int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t shard,
  * fragment.importRoaring (fragment.go:2243) -> Bitmap.ImportRoaringBits (roaring.go:1463-1558).
  * `data` is either Pilosa roaring (with ops log) or the OFFICIAL roaring format with 16-bit
  * keys that /import-roaring receives (readOfficialHeader .. readWithRuns roaring.go:5075-5245;
- * run payloads are start:length there). The fragment is created if the shard had none. The
- * rank-cache recount (fragment.go:2080-2095) stays with the Go side, which follows up with
- * pb200_rank_set. */
+ * run payloads are start:length there). The fragment is created if the shard had none.
+ * The rank-cache update of importRoaring (fragment.go:2258-2276) is done here as well: the engine
+ * keeps the fragment's rankCache entries and admission threshold (cache.go:136-288; seeded from the
+ * list pb200_rank_set handed over, else from the exact row counts, cut at
+ * PB200_OPT_RANK_CACHE_SIZE), moves the cached count of every changed row by its signed change
+ * (BulkAdd(row, Get(row) + changes), uint64 arithmetic, values below the threshold dropped) and
+ * re-ranks at once (Recalculate), so the next TopN walks the order the reference would. Ties rank
+ * by ascending id (the reference's sort leaves them unspecified). pb200_rank_get reads the
+ * ranking back for the Go cache; pb200_rank_set, pb200_frag_load and pb200_frag_apply replace it
+ * (the latter two by a fresh ranking of exact counts). */
 int pb200_frag_import_roaring(pb200_ctx* ctx, pb200_family family, uint64_t shard,
                               const void* data, size_t len, int clear, int64_t* changed);
 
@@ -163,6 +170,13 @@ int pb200_frag_drop(pb200_ctx* ctx, pb200_family family, uint64_t shard);
  * (row id, cached count) list of one fragment, in rank order. */
 int pb200_rank_set(pb200_ctx* ctx, pb200_family family, uint64_t shard,
                    const uint64_t* row_ids, const uint64_t* counts, size_t n);
+
+/* The fragment's current TopN candidate order, rank by rank: what rankCache.Top() (cache.go:288)
+ * holds after the engine's own import recount, the list of pb200_rank_set, or the default ranking
+ * of exact counts. *n receives the length; with row_ids == counts == NULL nothing else is written;
+ * PB200_ERR_RANGE when cap is too small. */
+int pb200_rank_get(pb200_ctx* ctx, pb200_family family, uint64_t shard,
+                   uint64_t* row_ids, uint64_t* counts, size_t cap, size_t* n);
 
 /* Host-only validation of fragment-file bytes with the loader's own parser (snapshot + ops
  * log replay), without a context or a GPU: the checks pb200_frag_load performs before it
@@ -286,6 +300,9 @@ int pb200_eval_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
  * value = 1024) at the price of HBM capacity (at most 8192 / value times the payload).
  * pb200_last_timing().algo_bytes keeps counting the reference's encoding. */
 #define PB200_OPT_DENSIFY_MIN_BYTES 1u
+/* PB200_OPT_RANK_CACHE_SIZE (default 50000 = DefaultCacheSize, field.go:47): entries the rank
+ * cache of a fragment keeps (rankCache.maxEntries); applies to rankings derived after the call. */
+#define PB200_OPT_RANK_CACHE_SIZE 2u
 int pb200_set_option(pb200_ctx* ctx, uint32_t option, uint64_t value);
 
 /* Page-lock a caller-owned host buffer (cudaHostRegister) so that result copies into it — the

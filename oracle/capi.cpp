@@ -293,16 +293,20 @@ int orc_frag_import_roaring(void* h, uint32_t fam, uint64_t shard, const uint8_t
   return guard([&] {
     Fragment* f = ((Orc*)h)->holder.fragment(fam, shard, true);
     Bitmap other = unmarshal_binary(data, len);
-    const int64_t n = import_roaring_bits(f->storage, data, len, clear != 0);
+    std::map<uint64_t, int64_t> row_set;
+    const int64_t n = import_roaring_bits(f->storage, data, len, clear != 0, &row_set);
     if (changed) *changed = n;
-    uint64_t last = ~0ull;
-    for (auto& kv : other.cs) {
-      const uint64_t row = kv.first >> 4;
-      if (row == last) continue;
-      last = row;
-      if (!f->cache_none) f->cache.add(row, f->row_count(row));
-      if (row > f->max_row_id) f->max_row_id = row;
+    for (auto& kv : other.cs)
+      if ((kv.first >> 4) > f->max_row_id) f->max_row_id = kv.first >> 4;
+    // fragment.importRoaring's cache update (fragment.go:2258-2276): the cached count of every row that
+    // changed moves by the signed change (uint64 arithmetic), then the ranking is rebuilt at once
+    bool any = false;
+    for (auto& kv : row_set) {
+      if (kv.second == 0 || f->cache_none) continue;
+      any = true;
+      f->cache.bulk_add(kv.first, f->cache.get(kv.first) + uint64_t(kv.second));
     }
+    if (any) f->cache.recalculate();
   });
 }
 int orc_rows(void* h, uint32_t fam, uint64_t start, uint32_t flags, uint64_t column, uint64_t limit, const uint64_t* shards, uint32_t ns,

@@ -196,6 +196,10 @@ struct RankCache {
     if (n < threshold_value && n > 0) return;
     entries[id] = n;
   }
+  void bulk_add(uint64_t id, uint64_t n) {  // :184-192 (no n > 0 exception: a count of 0 never replaces an entry once the threshold is 1)
+    if (n < threshold_value) return;
+    entries[id] = n;
+  }
   uint64_t get(uint64_t id) const { auto it = entries.find(id); return it == entries.end() ? 0 : it->second; }
   void recalculate() {  // :246-282
     std::vector<Pair> r;

@@ -1437,8 +1437,10 @@ inline Bitmap unmarshal_binary(const uint8_t* data, size_t len) {
 }
 
 // ImportRoaringBits (roaring.go:1463-1558): set or clear every bit of a serialized bitmap (either
-// format); returns the number of bits that changed.
-inline int64_t import_roaring_bits(Bitmap& b, const uint8_t* data, size_t len, bool clear) {
+// format); returns the number of bits that changed. `row_set`, when given, receives the signed
+// change per row of `row_size` containers (the rowSet result, :1484, :1498, :1514, :1524).
+inline int64_t import_roaring_bits(Bitmap& b, const uint8_t* data, size_t len, bool clear,
+                                   std::map<uint64_t, int64_t>* row_set = nullptr, uint64_t row_size = 16) {
   Bitmap other = unmarshal_binary(data, len);
   int64_t changed = 0;
   for (auto& kv : other.cs) {
@@ -1449,6 +1451,7 @@ inline int64_t import_roaring_bits(Bitmap& b, const uint8_t* data, size_t len, b
     CPtr res = clear ? difference(cur, kv.second) : (cur ? union_(cur, kv.second) : kv.second);
     const int64_t after = N(res);
     changed += clear ? before - after : after - before;
+    if (row_set && after != before) (*row_set)[kv.first / row_size] += after - before;
     if (after > 0) b.cs[kv.first] = res; else b.cs.erase(kv.first);
   }
   return changed;

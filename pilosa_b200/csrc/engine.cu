@@ -230,17 +230,51 @@ static int sync_families(pb200_ctx* ctx) {
   return PB200_OK;
 }
 
-static void default_rank(Fragment& f) {
-  // Exact row counts, count desc / id asc, trimmed to DefaultCacheSize = 50000 (field.go:47);
+static void default_rank(Fragment& f, uint32_t max_entries) {
+  // Exact row counts, count desc / id asc, trimmed to the cache size (DefaultCacheSize = 50000, field.go:47);
   // rows with count 0 never enter the cache.
   size_t n = f.row_ids.size();
   std::vector<uint32_t> order(n);
   for (size_t i = 0; i < n; i++) order[i] = uint32_t(i);
   std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return f.row_counts[a] > f.row_counts[b]; });
-  if (n > 50000) order.resize(50000);
+  if (n > max_entries) order.resize(max_entries);
   f.rank_ids.clear(); f.rank_counts.clear();
   for (uint32_t i : order) { f.rank_ids.push_back(f.row_ids[i]); f.rank_counts.push_back(f.row_counts[i]); }
   f.rank_from_host = false;
+}
+
+// rankCache.recalculate (cache.go:245-281) over the engine-held entries: rank by count (descending; ties by
+// ascending id, where the reference's sort.Sort leaves them unspecified), cut at the cache size, remember the
+// count at the cut as the admission threshold, and drop the cut entries once the map outgrows 1.1 x the size.
+// The ranking becomes the fragment's TopN candidate order.
+static void rank_recalculate(Fragment& f, uint32_t max_entries) {
+  auto& rs = f.rank_state;
+  std::vector<std::pair<uint64_t, uint64_t>> r(rs.entries.begin(), rs.entries.end());  // (id, count)
+  std::sort(r.begin(), r.end(), [](const std::pair<uint64_t, uint64_t>& a, const std::pair<uint64_t, uint64_t>& b) {
+    return a.second != b.second ? a.second > b.second : a.first < b.first;
+  });
+  size_t keep = r.size();
+  if (r.size() > max_entries) { rs.threshold_value = r[max_entries].second; keep = max_entries; }
+  else rs.threshold_value = 1;
+  if (rs.entries.size() > size_t(int(1.1 * double(max_entries))))  // thresholdFactor cache.go:31
+    for (size_t i = keep; i < r.size(); i++) rs.entries.erase(r[i].first);
+  f.rank_ids.resize(keep); f.rank_counts.resize(keep);
+  for (size_t i = 0; i < keep; i++) { f.rank_ids[i] = r[i].first; f.rank_counts[i] = r[i].second; }
+  f.rank_from_host = true;  // the cached counts are what TopN reports, as with a list handed over by the host
+  f.d_rank_valid = false;
+  f.rank_pos_valid = false;
+}
+
+// The cache as it stands before the first import recount: the list the host handed over (pb200_rank_set), else
+// every present row with its exact count, ranked once — what openCache + Recalculate leave (fragment.go:404-463).
+static void rank_state_build(Fragment& f, uint32_t max_entries) {
+  auto& rs = f.rank_state;
+  if (rs.live) return;
+  rs.entries.clear();
+  if (f.rank_from_host) for (size_t k = 0; k < f.rank_ids.size(); k++) rs.entries[f.rank_ids[k]] = f.rank_counts[k];
+  else for (size_t j = 0; j < f.row_ids.size(); j++) if (f.row_counts[j]) rs.entries[f.row_ids[j]] = f.row_counts[j];
+  rank_recalculate(f, max_entries);
+  rs.live = true;
 }
 
 static int upload_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const std::vector<HostContainer>& cs) {
@@ -272,7 +306,7 @@ static int upload_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const st
   nf.all_bitmap = img.all_bitmap;
   nf.row_ids = std::move(img.row_ids);
   nf.row_counts = std::move(img.row_counts);
-  default_rank(nf);
+  default_rank(nf, ctx->rank_cache_size);
 
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // no query may still read the old copy
   auto it = fam.frags.find(shard);
@@ -369,6 +403,10 @@ extern "C" int pb200_set_option(pb200_ctx* ctx, uint32_t option, uint64_t value)
       if (value > kBitmapBytes) return fail(ctx, PB200_ERR_INVALID, "densify threshold above 8192 bytes");
       ctx->densify_min_bytes = uint32_t(value);
       return PB200_OK;
+    case PB200_OPT_RANK_CACHE_SIZE:
+      if (value == 0 || value > 0xffffffffull) return fail(ctx, PB200_ERR_INVALID, "rank cache size out of range");
+      ctx->rank_cache_size = uint32_t(value);
+      return PB200_OK;
     default: return fail(ctx, PB200_ERR_INVALID, "unknown option");
   }
 }
@@ -405,15 +443,57 @@ extern "C" int pb200_frag_import_roaring(pb200_ctx* ctx, pb200_family family, ui
   if (it != fam.frags.end()) TRY(download_containers(ctx, it->second, blob, cs));
   std::map<uint64_t, HostContainer> m;
   for (auto& c : cs) m.emplace(c.key, std::move(c));
-  const int64_t n = merge_containers(m, other, clear != 0);
+  std::map<uint64_t, int64_t> row_set;
+  const int64_t n = merge_containers(m, other, clear != 0, &row_set);
   if (changed) *changed = n;
-  if (n == 0 && it != fam.frags.end()) return PB200_OK;  // nothing to rewrite
+  if (n == 0 && it != fam.frags.end()) return PB200_OK;  // nothing to rewrite, no row changed
   cs.clear();
   for (auto& kv : m) {
     cs.push_back(std::move(kv.second));
     if (!cs.back().owned.empty()) cs.back().data = cs.back().owned.data();
   }
-  return upload_fragment(ctx, fam, shard, cs);
+  // the rank cache outlives the rewrite of the device copy
+  Fragment::RankState st;
+  st.live = true;  // a fragment created by this import starts from an empty cache with threshold 0 (NewRankCache cache.go:158)
+  if (it != fam.frags.end()) {
+    rank_state_build(it->second, ctx->rank_cache_size);
+    st = std::move(it->second.rank_state);
+    it->second.rank_state = Fragment::RankState{};
+  }
+  const int rc = upload_fragment(ctx, fam, shard, cs);
+  it = fam.frags.find(shard);
+  if (it == fam.frags.end()) return rc;
+  Fragment& f = it->second;
+  f.rank_state = std::move(st);
+  if (rc != PB200_OK) return rc;  // the old copy is still in place, with its cache
+  // fragment.importRoaring (fragment.go:2258-2276): BulkAdd(row, Get(row) + changes) for every changed row
+  // (uint64 arithmetic; BulkAdd cache.go:184-192 drops a value below the threshold), then Recalculate.
+  for (auto& kv : row_set) {
+    if (kv.second == 0) continue;
+    auto e = f.rank_state.entries.find(kv.first);
+    const uint64_t v = (e == f.rank_state.entries.end() ? 0 : e->second) + uint64_t(kv.second);
+    if (v < f.rank_state.threshold_value) continue;
+    f.rank_state.entries[kv.first] = v;
+  }
+  rank_recalculate(f, ctx->rank_cache_size);
+  return PB200_OK;
+}
+
+extern "C" int pb200_rank_get(pb200_ctx* ctx, pb200_family family, uint64_t shard, uint64_t* row_ids, uint64_t* counts, size_t cap, size_t* n) {
+  ENTER(ctx);
+  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
+  if (!n) return PB200_ERR_INVALID;
+  auto it = ctx->families[family].frags.find(shard);
+  if (it == ctx->families[family].frags.end()) return fail(ctx, PB200_ERR_NOTFOUND, "no such fragment");
+  const Fragment& f = it->second;
+  *n = f.rank_ids.size();
+  if (!row_ids && !counts) return PB200_OK;
+  if (cap < f.rank_ids.size()) return fail(ctx, PB200_ERR_RANGE, "rank list larger than the buffer");
+  for (size_t k = 0; k < f.rank_ids.size(); k++) {
+    if (row_ids) row_ids[k] = f.rank_ids[k];
+    if (counts) counts[k] = f.rank_counts[k];
+  }
+  return PB200_OK;
 }
 
 extern "C" int pb200_frag_drop(pb200_ctx* ctx, pb200_family family, uint64_t shard) {
@@ -442,6 +522,7 @@ extern "C" int pb200_rank_set(pb200_ctx* ctx, pb200_family family, uint64_t shar
   it->second.rank_ids.assign(row_ids, row_ids + n);
   it->second.rank_counts.assign(counts, counts + n);
   it->second.rank_from_host = true;
+  it->second.rank_state = Fragment::RankState{};  // the host's list replaces whatever the import recount kept
   it->second.d_rank_valid = false;  // rebuilt on the next TopN
   it->second.rank_pos_valid = false;
   return PB200_OK;

@@ -39,6 +39,14 @@ struct Fragment {
   bool d_rank_valid = false;
   std::vector<uint32_t> rank_pos_of_row;  // rank position of row_ids[j] (0xffffffff: not ranked); host index for TopN pass 2
   bool rank_pos_valid = false;
+  // rankCache state (cache.go:136-288) for the import recount of fragment.importRoaring
+  // (fragment.go:2258-2276): id -> cached count and the admission threshold. Built on the first
+  // pb200_frag_import_roaring of the fragment, carried over every rewrite of its device copy.
+  struct RankState {
+    bool live = false;
+    uint64_t threshold_value = 0;
+    std::unordered_map<uint64_t, uint64_t> entries;
+  } rank_state;
 };
 
 struct Family {
@@ -101,6 +109,7 @@ struct pb200_ctx {
   pb200::DevBuf d_batch, d_out, d_slow, d_temp, d_dense, d_dense_n, d_misc, d_topn, d_bsi;
   pb200::PinBuf h_stage, h_out, h_algo, h_topn;
   uint32_t densify_min_bytes = 0;  // PB200_OPT_DENSIFY_MIN_BYTES (0 = containers stay as loaded)
+  uint32_t rank_cache_size = 50000;  // PB200_OPT_RANK_CACHE_SIZE (field.go:47 DefaultCacheSize)
   bool topn_attr_set = false, sum_attr_set = false, mm_attr_set = false;
   uint32_t range_attr_set = 0;  // per instantiation of bsi_range_pipe_kernel
   int occ_range[8] = {0, 0, 0, 0, 0, 0, 0, 0};

@@ -268,8 +268,10 @@ inline bool parse_any(const uint8_t* data, size_t len, std::vector<HostContainer
 }
 
 // ImportRoaringBits (roaring.go:1463-1558) on the host copy: OR (or AND-NOT) every container of `other`
-// into the map; returns the number of bits that changed.
-inline int64_t merge_containers(std::map<uint64_t, HostContainer>& m, const std::vector<HostContainer>& other, bool clear) {
+// into the map; returns the number of bits that changed and, in `row_set` when given, the signed change per
+// row (its rowSet result: key / 16 containers per row).
+inline int64_t merge_containers(std::map<uint64_t, HostContainer>& m, const std::vector<HostContainer>& other, bool clear,
+                                std::map<uint64_t, int64_t>* row_set = nullptr) {
   std::vector<uint64_t> w(kBitmapWords), w2(kBitmapWords);
   int64_t changed = 0;
   for (auto& oc : other) {
@@ -285,6 +287,7 @@ inline int64_t merge_containers(std::map<uint64_t, HostContainer>& m, const std:
     for (int k = 0; k < kBitmapWords; k++) w[k] = clear ? (w[k] & ~w2[k]) : (w[k] | w2[k]);
     from_words(w.data(), it->second);
     changed += clear ? before - int64_t(it->second.n) : int64_t(it->second.n) - before;
+    if (row_set && int64_t(it->second.n) != before) (*row_set)[oc.key >> 4] += int64_t(it->second.n) - before;
     if (it->second.n == 0) m.erase(it);
   }
   return changed;

@@ -62,6 +62,7 @@ def load_library() -> C.CDLL:
         "pb200_frag_apply": (i32, [vp, u32, u64, u64p, sz, u64p, sz]),
         "pb200_frag_drop": (i32, [vp, u32, u64]),
         "pb200_rank_set": (i32, [vp, u32, u64, u64p, u64p, sz]),
+        "pb200_rank_get": (i32, [vp, u32, u64, u64p, u64p, sz, C.POINTER(sz)]),
         "pb200_host_check_roaring": (i32, [C.c_char_p, sz, u64p, u64p, C.c_char_p, sz]),
         "pb200_frag_stat": (i32, [vp, u32, u64, u64p, u64p, u64p]),
         "pb200_count": (i32, [vp, np_, u32, u64p, u32, u64p]),
@@ -127,6 +128,7 @@ class Engine:
         self.device = device
 
     OPT_DENSIFY_MIN_BYTES = 1
+    OPT_RANK_CACHE_SIZE = 2
 
     def set_option(self, option: int, value: int) -> None:
         self._check(self.lib.pb200_set_option(self._h, option, value))
@@ -181,6 +183,14 @@ class Engine:
 
     def frag_drop(self, fam: int, shard: int) -> None:
         self._check(self.lib.pb200_frag_drop(self._h, fam, shard))
+
+    def rank_get(self, fam: int, shard: int) -> Tuple[List[int], List[int]]:
+        """The fragment's TopN candidate order (rankCache.Top(), cache.go:288): (row ids, cached counts)."""
+        n = C.c_size_t()
+        self._check(self.lib.pb200_rank_get(self._h, fam, shard, None, None, 0, C.byref(n)))
+        ids, cnt = (C.c_uint64 * max(1, n.value))(), (C.c_uint64 * max(1, n.value))()
+        self._check(self.lib.pb200_rank_get(self._h, fam, shard, ids, cnt, n.value, C.byref(n)))
+        return list(ids[: n.value]), list(cnt[: n.value])
 
     def rank_set(self, fam: int, shard: int, row_ids: Sequence[int], counts: Sequence[int]) -> None:
         assert len(row_ids) == len(counts)

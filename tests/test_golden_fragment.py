@@ -473,3 +473,43 @@ def test_fragment_roaring_import(w):
         removed = w.import_roaring(name, 0, oracle.Bitmap(*test[0]).serialize(), True)  # and clearing them again
         assert removed == len(set(test[0]))
         assert sum(w.ex.count(Row(name, r), [0]) for r in range(3)) == len(seen - set(test[0]))
+
+
+# ---- fragment.importRoaring's cache update (fragment.go:2258-2276) — no reference test looks at the cache after an
+# import, so the expectations below are worked out by hand from that code and rankCache (cache.go:184-192 BulkAdd,
+# :245-281 recalculate) for a cache of 4 entries (thresholdBuffer = int(1.1 * 4) = 4). Pins the oracle; the engine's
+# own rank-cache state is compared with the oracle step by step in test_gpu_parity.py::test_import_roaring_rank_recount.
+def test_import_roaring_cache_update_by_hand():
+    import oracle
+
+    def frag(rows):
+        return oracle.Bitmap(*sorted(r * SW + c for r, cols in rows.items() for c in cols)).serialize()
+
+    orc = oracle.Oracle(workers=1)
+    fam = orc.family_create()
+    orc.cache_config(fam, 0, False, 4)
+    # rows 0..7 with 10, 17, .. 59 bits; openCache + Recalculate: top 4 ranked, threshold = count of the 5th (row 3: 31),
+    # 8 entries > 4 -> the unranked ones leave the map
+    orc.frag_load(fam, 0, frag({r: range(10 + 7 * r) for r in range(8)}))
+    assert orc.rankings(fam, 0) == ([7, 6, 5, 4], [59, 52, 45, 38])
+    steps = [
+        # cached row 5: 45 + 20
+        ({5: range(1000, 1020)}, False, 20, ([5, 7, 6, 4], [65, 59, 52, 38])),
+        # row 1 is not cached: Get() = 0, 0 + 5 < 31 -> BulkAdd drops it
+        ({1: range(1000, 1005)}, False, 5, ([5, 7, 6, 4], [65, 59, 52, 38])),
+        # row 2 is not cached either: 0 + 60 >= 31 -> enters with 60 (it holds 84 bits); 5 entries: threshold = 38, row 4 leaves
+        ({2: range(1000, 1060)}, False, 60, ([5, 2, 7, 6], [65, 60, 59, 52])),
+        # a new row of 200 bits: threshold = 52, row 6 leaves the map
+        ({30: range(200)}, False, 200, ([30, 5, 2, 7], [200, 65, 60, 59])),
+        # ... cleared again: 200 - 200 = 0 < 52 -> dropped by BulkAdd, the cached 200 stays
+        ({30: range(200)}, True, 200, ([30, 5, 2, 7], [200, 65, 60, 59])),
+        # clear on uncached row 0: 0 + uint64(-3) wraps and passes the threshold; threshold = 59, row 7 leaves
+        ({0: range(3)}, True, 3, ([0, 30, 5, 2], [2**64 - 3, 200, 65, 60])),
+        # bits already set: no row changed, no Recalculate
+        ({5: range(5)}, False, 0, ([0, 30, 5, 2], [2**64 - 3, 200, 65, 60])),
+        # row 6 left the map two steps ago: 0 - 20 wraps as well
+        ({6: range(20)}, True, 20, ([0, 6, 30, 5], [2**64 - 3, 2**64 - 20, 200, 65])),
+    ]
+    for rows, clear, changed, ranking in steps:
+        assert orc.frag_import_roaring(fam, 0, frag(rows), clear) == changed
+        assert orc.rankings(fam, 0) == ranking

@@ -323,6 +323,64 @@ def test_import_roaring(pair):
         ex.be.frag_drop(ex.family("m"), 9)
 
 
+def test_import_roaring_rank_recount():
+    """The rank-cache update of fragment.importRoaring (fragment.go:2258-2276) on the engine's own rankCache state
+    (cache.go:136-288): BulkAdd(row, Get(row) + changes) + Recalculate after every import, with a cache of 4 entries so
+    that the admission threshold, the 1.1 x trim of the entries, a count that stays stale because 0 is below the
+    threshold, and the uint64 wrap of a clear on an uncached row all happen. After every step the ranking
+    (pb200_rank_get = rankCache.Top()) and TopN with and without a source row equal the oracle's."""
+    from pilosa_b200.engine import Engine
+
+    def frag(rows):  # {row: [cols]} -> Pilosa roaring bytes of shard 0
+        return oracle.Bitmap(*sorted(r * (1 << 20) + c for r, cols in rows.items() for c in cols)).serialize()
+
+    eng, orc = Engine(0), oracle.Oracle(workers=2)
+    try:
+        g, c = Executor(eng), Executor(orc)
+        for ex in (g, c):
+            ex.create_field("t")
+            ex.create_field("s")
+        fg, fc = g.family("t"), c.family("t")
+        eng.set_option(Engine.OPT_RANK_CACHE_SIZE, 4)
+        orc.cache_config(fc, 0, False, 4)
+        rnd = random.Random(5)
+        base = {r: sorted(rnd.sample(range(70000), 10 + 7 * r)) for r in range(8)}  # counts 10, 17, .. 59: rows 4..7 are cached
+        src = frag({0: list(range(0, 70000, 3))})
+        for ex in (g, c):
+            ex.load_fragment("t", 0, frag(base))
+            ex.load_fragment("s", 0, src)
+
+        def check(step):
+            assert eng.rank_get(fg, 0) == orc.rankings(fc, 0), step
+            for n in (0, 2, 3):
+                assert g.topn("t", [0], n=n) == c.topn("t", [0], n=n), (step, n)
+                assert g.topn("t", [0], n=n, src=Row("s", 0)) == c.topn("t", [0], n=n, src=Row("s", 0)), (step, n)
+
+        check("load")
+        assert eng.rank_get(fg, 0)[0] == [7, 6, 5, 4]
+        steps = [
+            ("cached row grows", {5: list(range(100000, 100020))}, False),
+            ("uncached row, below the threshold: dropped", {1: list(range(200000, 200005))}, False),
+            ("uncached row, above the threshold: enters with the CHANGE as its count", {2: list(range(300000, 300060))}, False),
+            ("new row", {30: list(range(0, 400, 2))}, False),
+            ("top row cleared completely: 0 is below the threshold, the old count stays", {30: list(range(0, 400, 2))}, True),
+            ("clear on an uncached row: Get() = 0 minus the change wraps", {0: base[0][:3]}, True),
+            ("bits that are already set: nothing changes", {7: base[7][:5]}, False),
+            ("partial clear of a cached row", {6: base[6][:20]}, True),
+        ]
+        for name, rows, clear in steps:
+            blob = frag(rows)
+            assert eng.frag_import_roaring(fg, 0, blob, clear) == orc.frag_import_roaring(fc, 0, blob, clear), name
+            check(name)
+        ids, counts = eng.rank_get(fg, 0)
+        assert counts[0] == (1 << 64) - 3 and ids[0] == 0  # the wrapped count leads the ranking, as it would in the reference
+        # a list handed over by the host replaces the engine's state
+        eng.rank_set(fg, 0, [3, 4], [9, 8])
+        assert eng.rank_get(fg, 0) == ([3, 4], [9, 8])
+    finally:
+        eng.close()
+
+
 def test_densify_option_changes_layout_not_results():
     """PB200_OPT_DENSIFY_MIN_BYTES: large array / run containers kept as bitmaps in HBM; every result and the
     algorithmic byte count stay what they are without it."""
