@@ -139,7 +139,11 @@ int pb200_frag_load(pb200_ctx* ctx, pb200_family family, uint64_t shard,
 
 /* Write-path coherence: apply set/clear of storage positions (pos = row*2^20 + col%2^20)
  * to the device copy; hook for fragment.go:680-779 (set/clearBit), :2051 importPositions,
- * :2243 importRoaring. Clears are applied after sets. */
+ * :2243 importRoaring. Clears are applied after sets. The rank cache follows importPositions
+ * (:2080-2093): the cached count of every row a position names is re-read from the rewritten
+ * fragment (BulkAdd: dropped when below the admission threshold, so an emptied row keeps its old
+ * count as in the reference), then the ranking is rebuilt; see pb200_frag_import_roaring for the
+ * cache state the engine keeps. */
 int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t shard,
                      const uint64_t* set_pos, size_t n_set,
                      const uint64_t* clear_pos, size_t n_clear);
@@ -157,8 +161,8 @@ int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t shard,
  * (BulkAdd(row, Get(row) + changes), uint64 arithmetic, values below the threshold dropped) and
  * re-ranks at once (Recalculate), so the next TopN walks the order the reference would. Ties rank
  * by ascending id (the reference's sort leaves them unspecified). pb200_rank_get reads the
- * ranking back for the Go cache; pb200_rank_set, pb200_frag_load and pb200_frag_apply replace it
- * (the latter two by a fresh ranking of exact counts). */
+ * ranking back for the Go cache; pb200_rank_set replaces it with the host's list and
+ * pb200_frag_load with a fresh ranking of exact counts. */
 int pb200_frag_import_roaring(pb200_ctx* ctx, pb200_family family, uint64_t shard,
                               const void* data, size_t len, int clear, int64_t* changed);
 

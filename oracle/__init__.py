@@ -92,6 +92,7 @@ def lib() -> C.CDLL:
         "orc_eval_roaring": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, C.c_char_p, sz, C.POINTER(sz)]),
         "orc_frag_drop": (C.c_int, [vp, C.c_uint32, C.c_uint64]),
         "orc_frag_import_roaring": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_char_p, sz, C.c_int, C.POINTER(C.c_int64)]),
+        "orc_frag_import_positions": (C.c_int, [vp, C.c_uint32, C.c_uint64, u64p, sz, u64p, sz, C.POINTER(C.c_int64)]),
         "orc_rows": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, u64p, C.c_uint32, u64p, sz, C.POINTER(sz)]),
         "orc_groupby": (C.c_int, [vp, C.c_void_p, C.c_uint32, np_, C.c_uint32, C.c_uint64, u64p, C.c_uint32, C.c_void_p, sz, C.POINTER(sz)]),
         "orc_topn": (C.c_int, [vp, C.c_uint32, np_, C.c_uint32, C.c_uint32, u64p, sz, C.c_uint64, C.c_uint64, C.c_uint32, u64p,
@@ -399,6 +400,12 @@ class Oracle:
 
     def frag_drop(self, fam, shard) -> None:
         _check(lib().orc_frag_drop(self._h, fam, shard))
+
+    def frag_import_positions(self, fam, shard, set_pos=(), clear_pos=()) -> int:
+        """fragment.importPositions (fragment.go:2051-2098): AddN / RemoveN + the rank-cache recount of the rows named."""
+        n = C.c_int64()
+        _check(lib().orc_frag_import_positions(self._h, fam, shard, u64_array(set_pos), len(set_pos), u64_array(clear_pos), len(clear_pos), C.byref(n)))
+        return n.value
 
     def frag_import_roaring(self, fam, shard, data: bytes, clear: bool = False) -> int:
         n = C.c_int64()

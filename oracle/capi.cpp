@@ -289,6 +289,14 @@ int orc_frag_drop(void* h, uint32_t fam, uint64_t shard) {
     fams[fam].erase(shard);
   });
 }
+int orc_frag_import_positions(void* h, uint32_t fam, uint64_t shard, const uint64_t* set, size_t n_set, const uint64_t* clear, size_t n_clear,
+                              int64_t* changed) {
+  return guard([&] {
+    Fragment* f = ((Orc*)h)->holder.fragment(fam, shard, true);
+    const int64_t n = f->import_positions(set, n_set, clear, n_clear);
+    if (changed) *changed = n;
+  });
+}
 int orc_frag_import_roaring(void* h, uint32_t fam, uint64_t shard, const uint8_t* data, size_t len, int clear, int64_t* changed) {
   return guard([&] {
     Fragment* f = ((Orc*)h)->holder.fragment(fam, shard, true);

@@ -8,6 +8,7 @@
 #include <cmath>
 #include <functional>
 #include <mutex>
+#include <set>
 #include <thread>
 #include <unordered_map>
 
@@ -304,6 +305,21 @@ struct Fragment {
     if (!changed) return false;
     if (!cache_none) cache.add(row_id, row_count(row_id));
     return true;
+  }
+  // importPositions (fragment.go:2051-2098): storage.AddN(set), storage.RemoveN(clear), then the cache count of
+  // every row named by a position is re-read from storage (BulkAdd, :2080-2090) and the ranking rebuilt (:2093).
+  // Positions are fragment positions (row * ShardWidth + column % ShardWidth). Returns the bits changed.
+  int64_t import_positions(const uint64_t* set, size_t n_set, const uint64_t* clear, size_t n_clear) {
+    int64_t changed = 0;
+    std::set<uint64_t> row_set;
+    for (size_t i = 0; i < n_set; i++) { changed += storage.direct_add(set[i]); row_set.insert(set[i] / kShardWidth); }
+    for (size_t i = 0; i < n_clear; i++) { changed += storage.direct_remove(clear[i]); row_set.insert(clear[i] / kShardWidth); }
+    for (uint64_t row : row_set) {
+      if (!cache_none) cache.bulk_add(row, row_count(row));
+      if (row > max_row_id && row_count(row)) max_row_id = row;
+    }
+    if (!cache_none) cache.recalculate();
+    return changed;
   }
   // fragment.go:975-1040 setValueBase (sign-magnitude, exists row last)
   bool set_value(uint64_t col, unsigned bit_depth, int64_t value) {

@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <set>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -374,6 +375,34 @@ static int download_containers(pb200_ctx* ctx, const Fragment& f, std::vector<ui
   return PB200_OK;
 }
 
+// Replace the device copy of a fragment by `cs` and bring its rank cache along: the rankCache state (built on first
+// use) is carried over the rewrite, `update` applies the write's BulkAdd calls to it, then Recalculate.
+template <class Update>
+static int rewrite_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const std::vector<HostContainer>& cs, Update&& update) {
+  Fragment::RankState st;
+  st.live = true;  // a fragment created by this write starts from an empty cache with threshold 0 (NewRankCache cache.go:158)
+  auto it = fam.frags.find(shard);
+  if (it != fam.frags.end()) {
+    rank_state_build(it->second, ctx->rank_cache_size);
+    st = std::move(it->second.rank_state);
+    it->second.rank_state = Fragment::RankState{};
+  }
+  const int rc = upload_fragment(ctx, fam, shard, cs);
+  it = fam.frags.find(shard);
+  if (it == fam.frags.end()) return rc;
+  Fragment& f = it->second;
+  f.rank_state = std::move(st);
+  if (rc != PB200_OK) return rc;  // the old copy is still in place, with its cache
+  update(f);
+  rank_recalculate(f, ctx->rank_cache_size);
+  return PB200_OK;
+}
+
+static void rank_bulk_add(Fragment& f, uint64_t id, uint64_t n) {  // rankCache.BulkAdd cache.go:184-192
+  if (n < f.rank_state.threshold_value) return;
+  f.rank_state.entries[id] = n;
+}
+
 extern "C" int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t shard, const uint64_t* set_pos, size_t n_set,
                                 const uint64_t* clear_pos, size_t n_clear) {
   ENTER(ctx);
@@ -393,7 +422,17 @@ extern "C" int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t sh
     cs.push_back(std::move(kv.second));
     if (!cs.back().owned.empty()) cs.back().data = cs.back().owned.data();
   }
-  return upload_fragment(ctx, fam, shard, cs);
+  // importPositions' recount (fragment.go:2080-2093): the cached count of every row a position names is re-read
+  // from storage (BulkAdd), then Recalculate
+  std::set<uint64_t> row_set;
+  for (size_t i = 0; i < n_set; i++) row_set.insert(set_pos[i] >> 20);
+  for (size_t i = 0; i < n_clear; i++) row_set.insert(clear_pos[i] >> 20);
+  return rewrite_fragment(ctx, fam, shard, cs, [&](Fragment& f) {
+    for (uint64_t row : row_set) {
+      const auto r = std::lower_bound(f.row_ids.begin(), f.row_ids.end(), row);
+      rank_bulk_add(f, row, (r != f.row_ids.end() && *r == row) ? f.row_counts[size_t(r - f.row_ids.begin())] : 0);
+    }
+  });
 }
 
 extern "C" int pb200_set_option(pb200_ctx* ctx, uint32_t option, uint64_t value) {
@@ -452,31 +491,15 @@ extern "C" int pb200_frag_import_roaring(pb200_ctx* ctx, pb200_family family, ui
     cs.push_back(std::move(kv.second));
     if (!cs.back().owned.empty()) cs.back().data = cs.back().owned.data();
   }
-  // the rank cache outlives the rewrite of the device copy
-  Fragment::RankState st;
-  st.live = true;  // a fragment created by this import starts from an empty cache with threshold 0 (NewRankCache cache.go:158)
-  if (it != fam.frags.end()) {
-    rank_state_build(it->second, ctx->rank_cache_size);
-    st = std::move(it->second.rank_state);
-    it->second.rank_state = Fragment::RankState{};
-  }
-  const int rc = upload_fragment(ctx, fam, shard, cs);
-  it = fam.frags.find(shard);
-  if (it == fam.frags.end()) return rc;
-  Fragment& f = it->second;
-  f.rank_state = std::move(st);
-  if (rc != PB200_OK) return rc;  // the old copy is still in place, with its cache
   // fragment.importRoaring (fragment.go:2258-2276): BulkAdd(row, Get(row) + changes) for every changed row
-  // (uint64 arithmetic; BulkAdd cache.go:184-192 drops a value below the threshold), then Recalculate.
-  for (auto& kv : row_set) {
-    if (kv.second == 0) continue;
-    auto e = f.rank_state.entries.find(kv.first);
-    const uint64_t v = (e == f.rank_state.entries.end() ? 0 : e->second) + uint64_t(kv.second);
-    if (v < f.rank_state.threshold_value) continue;
-    f.rank_state.entries[kv.first] = v;
-  }
-  rank_recalculate(f, ctx->rank_cache_size);
-  return PB200_OK;
+  // (uint64 arithmetic), then Recalculate
+  return rewrite_fragment(ctx, fam, shard, cs, [&](Fragment& f) {
+    for (auto& kv : row_set) {
+      if (kv.second == 0) continue;
+      const auto e = f.rank_state.entries.find(kv.first);
+      rank_bulk_add(f, kv.first, (e == f.rank_state.entries.end() ? 0 : e->second) + uint64_t(kv.second));
+    }
+  });
 }
 
 extern "C" int pb200_rank_get(pb200_ctx* ctx, pb200_family family, uint64_t shard, uint64_t* row_ids, uint64_t* counts, size_t cap, size_t* n) {

@@ -513,3 +513,19 @@ def test_import_roaring_cache_update_by_hand():
     for rows, clear, changed, ranking in steps:
         assert orc.frag_import_roaring(fam, 0, frag(rows), clear) == changed
         assert orc.rankings(fam, 0) == ranking
+    # importPositions (fragment.go:2051-2098, the bulkImport path): the rows named by the positions get their count
+    # re-read from storage. The map holds {0, 6, 30, 5} and the threshold is 60 (row 2's cached count when it left).
+    W3, W20 = 2**64 - 3, 2**64 - 20
+    pos_steps = [
+        # row 2 really holds 84 bits: one more = 85 >= 60 -> back in; threshold = 65, row 5 leaves
+        ([2 * SW + 5000], [], 1, ([0, 6, 30, 2], [W3, W20, 200, 85])),
+        # the last 7 bits of row 0 cleared: count 0 < 65 -> dropped, the wrapped count stays; 4 entries: threshold = 1
+        ([], [c for c in range(3, 10)], 7, ([0, 6, 30, 2], [W3, W20, 200, 85])),
+        # rows 1 and 6 named: both re-read (23 and 31 bits), row 6 loses its wrapped count; threshold = 23, row 1 leaves
+        ([1 * SW + 9000], [6 * SW + 20], 2, ([0, 30, 2, 6], [W3, 200, 85, 31])),
+        # a position that is already set still names its row: row 7 (59 bits) is re-read and enters
+        ([7 * SW + 0], [], 0, ([0, 30, 2, 7], [W3, 200, 85, 59])),
+    ]
+    for set_pos, clear_pos, changed, ranking in pos_steps:
+        assert orc.frag_import_positions(fam, 0, set_pos, clear_pos) == changed
+        assert orc.rankings(fam, 0) == ranking

@@ -374,6 +374,20 @@ def test_import_roaring_rank_recount():
             check(name)
         ids, counts = eng.rank_get(fg, 0)
         assert counts[0] == (1 << 64) - 3 and ids[0] == 0  # the wrapped count leads the ranking, as it would in the reference
+        # pb200_frag_apply = importPositions (fragment.go:2051-2098): the rows the positions name are re-read (:2080-2093)
+        SWd = 1 << 20
+        pos_steps = [
+            ("uncached row re-read: enters with its real count", [2 * SWd + 5000], []),
+            ("row emptied: 0 is below the threshold, the cached count stays", [], [r_ * SWd + c_ for r_, c_ in ((0, c_) for c_ in base[0][3:])]),
+            ("two rows named, one loses its wrapped count", [1 * SWd + 9000], [6 * SWd + base[6][20]]),
+            ("a bit that is already set still names its row", [7 * SWd + base[7][0]], []),
+            ("new row by positions", [77 * SWd + c_ for c_ in range(0, 900, 3)], []),
+        ]
+        for name, set_pos, clear_pos in pos_steps:
+            eng.frag_apply(fg, 0, set_pos, clear_pos)
+            orc.frag_import_positions(fc, 0, set_pos, clear_pos)
+            check(name)
+            assert g.count(Union(*[Row("t", r_) for r_ in range(8)]), [0]) == c.count(Union(*[Row("t", r_) for r_ in range(8)]), [0])
         # a list handed over by the host replaces the engine's state
         eng.rank_set(fg, 0, [3, 4], [9, 8])
         assert eng.rank_get(fg, 0) == ([3, 4], [9, 8])
