@@ -296,6 +296,19 @@ int pb200_eval_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
                       const uint64_t* shards, uint32_t n_shards, void* out, size_t cap,
                       uint64_t* out_off, size_t* out_len);
 
+/* The same result as the protobuf the HTTP / internal client answer carries: the `Columns` field
+ * of internal.Row (internal/public.proto: repeated uint64 Columns = 1) exactly as the generated
+ * marshaller writes it (internal/public.pb.go:745-766, reached from encodeRow / encodeQueryResponse,
+ * encoding/proto/proto.go:408-457): tag 0x0A, varint(payload length), every column id of
+ * Row.Columns() (row.go:302-327) as a varint — segment by segment in shard-list order (pass the
+ * shards ascending, as Row.Merge keeps them). An empty row yields 0 bytes (the field is omitted).
+ * Sized and written ON THE DEVICE over all the local shards of the call; Go appends its Attrs /
+ * Keys fields (tags 0x12 / 0x1A) behind these bytes to complete the message. With out == NULL only
+ * *out_len is written; PB200_ERR_RANGE with the needed size in *out_len when cap is too small. */
+int pb200_eval_proto_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes,
+                             const uint64_t* shards, uint32_t n_shards, void* out, size_t cap,
+                             size_t* out_len);
+
 /* Context options. No reference counterpart.
  * PB200_OPT_DENSIFY_MIN_BYTES (default 0 = off): fragments loaded or rewritten AFTER the call keep
  * array / run containers whose file payload is at least `value` bytes (<= 8192) as 8 KiB bitmaps

@@ -90,6 +90,7 @@ def lib() -> C.CDLL:
         "orc_count_shards": (C.c_int, [vp, np_, C.c_uint32, u64p, C.c_uint32, C.c_int, u64p]),
         "orc_eval_columns": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, u64p, sz, C.POINTER(sz)]),
         "orc_eval_roaring": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, C.c_char_p, sz, C.POINTER(sz)]),
+        "orc_eval_proto_columns": (C.c_int, [vp, np_, C.c_uint32, u64p, C.c_uint32, C.c_char_p, sz, C.POINTER(sz)]),
         "orc_frag_drop": (C.c_int, [vp, C.c_uint32, C.c_uint64]),
         "orc_frag_import_roaring": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_char_p, sz, C.c_int, C.POINTER(C.c_int64)]),
         "orc_frag_import_positions": (C.c_int, [vp, C.c_uint32, C.c_uint64, u64p, sz, u64p, sz, C.POINTER(C.c_int64)]),
@@ -377,6 +378,15 @@ class Oracle:
         _check(lib().orc_eval_roaring(self._h, prog, len(prog), shard, None, 0, C.byref(n)))
         buf = C.create_string_buffer(max(1, n.value))
         _check(lib().orc_eval_roaring(self._h, prog, len(prog), shard, buf, n.value, C.byref(n)))
+        return buf.raw[: n.value]
+
+    def eval_proto_columns(self, prog, shards) -> bytes:
+        """The Columns field of internal.Row for the call's result over `shards` (public.pb.go:745-766)."""
+        n = C.c_size_t()
+        sh = u64_array(shards)
+        _check(lib().orc_eval_proto_columns(self._h, prog, len(prog), sh, len(shards), None, 0, C.byref(n)))
+        buf = C.create_string_buffer(max(1, n.value))
+        _check(lib().orc_eval_proto_columns(self._h, prog, len(prog), sh, len(shards), buf, n.value, C.byref(n)))
         return buf.raw[: n.value]
 
     def eval_roaring_shards(self, prog, shards) -> list:

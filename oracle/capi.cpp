@@ -253,6 +253,32 @@ int orc_eval_columns(void* h, const pb200_node* prog, uint32_t n, uint64_t shard
     if (out) std::copy(cols.begin(), cols.begin() + std::min(cap, cols.size()), out);
   });
 }
+// The `Columns` field of internal.Row as the generated marshaller writes it (internal/public.pb.go:745-766,
+// reached from encodeRow, encoding/proto/proto.go:408-457): tag 0x0A, varint(payload length), the columns as
+// base-128 varints; nothing at all for an empty row. Columns are Row.Columns() (row.go:302-327) of the call's
+// result, segment by segment in shard-list order (Row.Merge keeps the segments sorted by shard when the list is).
+int orc_eval_proto_columns(void* h, const pb200_node* prog, uint32_t n, const uint64_t* shards, uint32_t ns, uint8_t* out, size_t cap,
+                           size_t* out_len) {
+  return guard([&] {
+    std::vector<uint8_t> payload;
+    for (uint32_t i = 0; i < ns; i++) {
+      for (uint64_t num : ((Orc*)h)->exec.eval_shard(prog, n, shards[i]).columns()) {
+        while (num >= 0x80) { payload.push_back(uint8_t((num & 0x7f) | 0x80)); num >>= 7; }
+        payload.push_back(uint8_t(num));
+      }
+    }
+    std::vector<uint8_t> msg;
+    if (!payload.empty()) {
+      msg.push_back(0x0a);
+      uint64_t l = payload.size();
+      while (l >= 0x80) { msg.push_back(uint8_t((l & 0x7f) | 0x80)); l >>= 7; }
+      msg.push_back(uint8_t(l));
+      msg.insert(msg.end(), payload.begin(), payload.end());
+    }
+    *out_len = msg.size();
+    if (out && cap >= msg.size()) std::copy(msg.begin(), msg.end(), out);
+  });
+}
 // optimized Pilosa-roaring bytes of the shard's result segment
 int orc_eval_roaring(void* h, const pb200_node* prog, uint32_t n, uint64_t shard, uint8_t* out, size_t cap, size_t* out_len) {
   return guard([&] {

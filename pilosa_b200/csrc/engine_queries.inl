@@ -218,6 +218,53 @@ extern "C" int pb200_eval_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_
   return eval_shards_impl(ctx, prog, n_nodes, shards, n_shards, out, cap, out_off, out_len);
 }
 
+extern "C" int pb200_eval_proto_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards,
+                                        void* out, size_t cap, size_t* out_len) {
+  ENTER(ctx);
+  if (!out_len) return PB200_ERR_INVALID;
+  TRY(validate_shards(ctx, shards, n_shards));
+  *out_len = 0;
+  if (n_shards == 0) return PB200_OK;
+  if (n_shards > (1u << 24)) return fail(ctx, PB200_ERR_RANGE, "too many shards in one call");
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  timing_begin(ctx);
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  BatchDev bd{};
+  TRY(eval_dense(ctx, prog, n_nodes, shards, n_shards, bd));
+  const uint32_t n_slots = n_shards * kProtoSlots;
+  TRY(ensure_dev(ctx, ctx->d_rows_meta, size_t(n_slots) * 4));
+  TRY(ensure_dev(ctx, ctx->d_rows_item_off, size_t(n_slots) * 8));
+  const uint64_t* dense = static_cast<const uint64_t*>(ctx->d_dense.p);
+  const uint32_t* dense_n = static_cast<const uint32_t*>(ctx->d_dense_n.p);
+  const unsigned long long* ovf = ctx->dense_has_ovf ? ctx->dense_ovf_dev : nullptr;
+  uint32_t* sizes = static_cast<uint32_t*>(ctx->d_rows_meta.p);
+  unsigned long long* slot_off = static_cast<unsigned long long*>(ctx->d_rows_item_off.p);
+  unsigned long long* totals = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 16);
+  proto_size_kernel<<<std::min<uint32_t>((n_slots + 7) / 8, uint32_t(ctx->sm_count) * 8), kProtoThreads, 0, ctx->stream>>>(dense, dense_n, bd.shards, ovf,
+                                                                                                                   n_shards, sizes);
+  proto_layout_kernel<<<1, 1024, 0, ctx->stream>>>(sizes, n_slots, slot_off, totals);
+  ctx->timing.launches += 2;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  unsigned long long h_tot[2] = {0, 0};
+  CUDA_TRY(ctx, cudaMemcpyAsync(h_tot, totals, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->timing.d2h_bytes += 16;
+  const size_t total = size_t(h_tot[0]);
+  *out_len = total;
+  if (!out || total == 0) return finish_call(ctx);
+  if (cap < total) { finish_call(ctx); return fail(ctx, PB200_ERR_RANGE, "output buffer too small"); }
+  TRY(ensure_dev(ctx, ctx->d_rows, total));
+  proto_emit_kernel<<<std::min<uint32_t>(n_slots, uint32_t(ctx->sm_count) * 8), kProtoThreads, 0, ctx->stream>>>(
+      dense, sizes, slot_off, totals, bd.shards, ovf, n_shards, static_cast<uint8_t*>(ctx->d_rows.p));
+  ctx->timing.launches += 1;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(out, ctx->d_rows.p, total, cudaMemcpyDeviceToHost, ctx->stream));
+  ctx->timing.d2h_bytes += total;
+  return finish_call(ctx);
+}
+
 extern "C" int pb200_eval_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, uint64_t* out_cols, size_t cap, size_t* out_n) {
   ENTER(ctx);
   if (!out_n) return PB200_ERR_INVALID;

@@ -218,4 +218,126 @@ __global__ void __launch_bounds__(kRowsEmitThreads) rows_emit_kernel(const uint6
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// K12 — protobuf emission of a result row: the `Columns` field of internal.Row as the reference's
+// generated marshaller writes it (internal/public.pb.go:745-766, from encodeRow
+// encoding/proto/proto.go:408-457): tag 0x0A, varint(payload length), then every column id of
+// Row.Columns() (row.go:302-327) as a base-128 varint. Three launches over the dense rows the
+// evaluator left in HBM: sizes per (shard, container) slot, one scan, emission.
+// A slot is one of the 16 containers of a shard's row or, as the 17th, its Shift overflow word.
+// The varint length of a column id only changes at 2^7 and 2^14 (inside the first container of
+// shard 0, on 64-bit word boundaries) and at multiples of 2^20 beyond, so it is constant per word.
+// ---------------------------------------------------------------------------------------
+constexpr int kProtoSlots = kRowContainers + 1;
+constexpr int kProtoThreads = 256;
+
+__device__ __forceinline__ uint32_t varint_len(uint64_t x) { return x < 128 ? 1u : uint32_t(70 - __clzll((long long)x)) / 7u; }
+__device__ __forceinline__ uint8_t* put_varint(uint8_t* p, uint64_t x) {
+  while (x >= 0x80) { *p++ = uint8_t(x) | 0x80; x >>= 7; }
+  *p++ = uint8_t(x);
+  return p;
+}
+
+// A warp per slot: bytes its columns take as varints.
+__global__ void __launch_bounds__(kProtoThreads) proto_size_kernel(const uint64_t* __restrict__ dense, const uint32_t* __restrict__ dense_n,
+                                                                   const uint64_t* __restrict__ shards, const unsigned long long* __restrict__ ovf,
+                                                                   uint32_t n_shards, uint32_t* __restrict__ sizes) {
+  const uint32_t lane = threadIdx.x & 31, n_slots = n_shards * kProtoSlots;
+  const uint32_t warps = gridDim.x * (kProtoThreads / 32);
+  for (uint32_t slot = blockIdx.x * (kProtoThreads / 32) + (threadIdx.x >> 5); slot < n_slots; slot += warps) {
+    const uint32_t s = slot / kProtoSlots, c = slot % kProtoSlots;
+    uint32_t bytes = 0;
+    if (c == kRowContainers) {
+      if (lane == 0 && ovf)
+        for (unsigned long long v = ovf[s]; v; v &= v - 1) bytes += varint_len(((shards[s] + 1) << 20) + uint32_t(__ffsll((long long)v) - 1));
+    } else {
+      const uint32_t item = s * kRowContainers + c;
+      if (dense_n[item]) {
+        const uint64_t* w = dense + size_t(item) * kBitmapWords;
+        const uint64_t base = (shards[s] << 20) + (uint64_t(c) << 16);
+        for (uint32_t i = lane; i < kBitmapWords; i += 32) bytes += uint32_t(__popcll(w[i])) * varint_len(base + i * 64);
+      }
+    }
+    bytes = warp_sum(bytes);
+    if (lane == 0) sizes[slot] = bytes;
+  }
+}
+
+// One CTA: exclusive scan of the slot sizes (payload-relative offsets); totals[0] = message length
+// (0 for an empty row: the field is omitted), totals[1] = length of tag + length prefix.
+__global__ void __launch_bounds__(1024) proto_layout_kernel(const uint32_t* __restrict__ sizes, uint32_t n_slots,
+                                                            unsigned long long* __restrict__ slot_off, unsigned long long* __restrict__ totals) {
+  __shared__ unsigned long long warp_tot[32];
+  __shared__ unsigned long long running;
+  const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) running = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < n_slots; base += 1024) {
+    const uint32_t i = base + threadIdx.x;
+    const unsigned long long size = i < n_slots ? sizes[i] : 0ull;
+    unsigned long long x = size;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) warp_tot[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+      unsigned long long t = warp_tot[lane], z = t;
+      #pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, z, o); if (lane >= o) z += y; }
+      warp_tot[lane] = z - t;
+    }
+    __syncthreads();
+    if (i < n_slots) slot_off[i] = running + warp_tot[wid] + x - size;
+    __syncthreads();
+    if (threadIdx.x == 1023) running += warp_tot[31] + x;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const unsigned long long payload = running;
+    const unsigned long long hdr = payload ? 1ull + varint_len(payload) : 0ull;
+    totals[0] = hdr + payload;
+    totals[1] = hdr;
+  }
+}
+
+// A CTA per slot: thread t owns words 4t .. 4t+3 of the container, a block scan places its bytes.
+__global__ void __launch_bounds__(kProtoThreads) proto_emit_kernel(const uint64_t* __restrict__ dense, const uint32_t* __restrict__ sizes,
+                                                                   const unsigned long long* __restrict__ slot_off,
+                                                                   const unsigned long long* __restrict__ totals, const uint64_t* __restrict__ shards,
+                                                                   const unsigned long long* __restrict__ ovf, uint32_t n_shards,
+                                                                   uint8_t* __restrict__ out) {
+  __shared__ uint32_t warp_tot[kProtoThreads / 32];
+  const uint32_t t = threadIdx.x, lane = t & 31, wid = t >> 5, n_slots = n_shards * kProtoSlots;
+  const unsigned long long hdr = totals[1];
+  if (blockIdx.x == 0 && t == 0 && hdr) { out[0] = 0x0a; put_varint(out + 1, totals[0] - hdr); }
+  for (uint32_t slot = blockIdx.x; slot < n_slots; slot += gridDim.x) {
+    if (sizes[slot] == 0) continue;  // uniform over the CTA
+    const uint32_t s = slot / kProtoSlots, c = slot % kProtoSlots;
+    uint8_t* dst = out + hdr + slot_off[slot];
+    if (c == kRowContainers) {
+      if (t == 0)
+        for (unsigned long long v = ovf[s]; v; v &= v - 1) dst = put_varint(dst, ((shards[s] + 1) << 20) + uint32_t(__ffsll((long long)v) - 1));
+      continue;
+    }
+    const uint64_t* w = dense + (size_t(s) * kRowContainers + c) * kBitmapWords + 4 * t;
+    const uint64_t base = (shards[s] << 20) + (uint64_t(c) << 16) + uint64_t(4 * t) * 64;
+    uint64_t word[4];
+    uint32_t bytes = 0;
+    #pragma unroll
+    for (int i = 0; i < 4; i++) { word[i] = w[i]; bytes += uint32_t(__popcll(word[i])) * varint_len(base + i * 64); }
+    uint32_t x = bytes;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    __syncthreads();  // warp_tot of the previous slot is no longer read
+    if (lane == 31) warp_tot[wid] = x;
+    __syncthreads();
+    uint32_t pre = x - bytes;
+    for (uint32_t i = 0; i < wid; i++) pre += warp_tot[i];
+    uint8_t* p = dst + pre;
+    #pragma unroll
+    for (int i = 0; i < 4; i++)
+      for (uint64_t b = word[i]; b; b &= b - 1) p = put_varint(p, base + i * 64 + uint32_t(__ffsll((long long)b) - 1));
+  }
+}
+
 }  // namespace pb200

@@ -86,6 +86,7 @@ def load_library() -> C.CDLL:
         "pb200_rows": (i32, [vp, u32, u64, u32, u64, u64, u64p, u32, u64p, sz, C.POINTER(sz)]),
         "pb200_groupby": (i32, [vp, vp, u32, np_, u32, u64, u64p, u32, vp, sz, C.POINTER(sz)]),
         "pb200_eval_shards": (i32, [vp, np_, u32, u64p, u32, vp, sz, u64p, C.POINTER(sz)]),
+        "pb200_eval_proto_columns": (i32, [vp, np_, u32, u64p, u32, vp, sz, C.POINTER(sz)]),
         "pb200_topn": (i32, [vp, u32, np_, u32, u32, u64p, sz, u64, u64, u32, u64p, u32, pp, sz, C.POINTER(sz)]),
         "pb200_topn_shard": (i32, [vp, u32, np_, u32, u32, u64p, sz, u64, u64, u64, pp, sz, C.POINTER(sz)]),
         "pb200_bsi_sum": (i32, [vp, u32, u32, np_, u32, u32, u64p, u32, i64p, u64p]),
@@ -307,6 +308,18 @@ class Engine:
         n = C.c_size_t()
         self._check(self.lib.pb200_eval_shards(self._h, prog, len(prog), u64_array(shards) if ns else None, ns, buf, cap, off, C.byref(n)))
         return self._rows_buf, off
+
+    def eval_proto_columns(self, prog, shards: Sequence[int]) -> bytes:
+        """The Columns field of internal.Row for the call's result over `shards`, encoded on the device."""
+        ns = len(shards)
+        sh = u64_array(shards) if ns else None
+        n = C.c_size_t()
+        self._check(self.lib.pb200_eval_proto_columns(self._h, prog, len(prog), sh, ns, None, 0, C.byref(n)))
+        if n.value == 0:
+            return b""
+        buf = C.create_string_buffer(n.value)
+        self._check(self.lib.pb200_eval_proto_columns(self._h, prog, len(prog), sh, ns, buf, n.value, C.byref(n)))
+        return buf.raw[: n.value]
 
     def eval_roaring_shards(self, prog, shards: Sequence[int]) -> List[bytes]:
         """One row segment (Pilosa roaring bytes) per shard, typed and serialised on the device."""

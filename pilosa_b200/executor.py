@@ -274,6 +274,11 @@ class Executor:
         local = self.local_shards(sorted(shards))
         return list(zip(local, self.be.eval_roaring_shards(self.program(call), local)))
 
+    def row_proto_columns(self, call: Call, shards: Sequence[int]) -> bytes:
+        """The `Columns` field of internal.Row for the rank-local part of a bitmap call's result, as the reference's
+        marshaller writes it (internal/public.pb.go:745-766 via encodeRow, encoding/proto/proto.go:408-457)."""
+        return self.be.eval_proto_columns(self.program(call), self.local_shards(sorted(shards)))
+
     def sum(self, field_name: str, shards: Sequence[int], filter_call: Optional[Call] = None) -> Tuple[int, int]:  # executeSum :409
         f = self.fields[field_name]
         local = self._local(shards)

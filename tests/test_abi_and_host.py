@@ -363,3 +363,40 @@ def test_time_quantum_views_golden_table_and_row_time():
     parts = [ex.count(abi.Call("Row", field_name="t", row=1, view=k.view), [0]) for k in full.children]
     assert 0 < ex.count(full, [0]) <= sum(parts) and ex.count(full, [0]) >= max(parts)
     assert ex.count(one, [0]) == parts[2]
+
+
+def test_oracle_proto_row_columns_against_protobuf():
+    """The oracle's restatement of internal.Row's marshaller for the Columns field (internal/public.pb.go:745-766):
+    a hand-encoded literal and google.protobuf's encoding of the same message (proto3 `repeated uint64 Columns = 1`,
+    packed) for column lists that cross every varint-length step below 2^29."""
+    from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+
+    from pilosa_b200.abi import Row
+    from pilosa_b200.executor import Executor
+
+    fdp = descriptor_pb2.FileDescriptorProto(name="public_min.proto", package="internal", syntax="proto3")
+    m = fdp.message_type.add(name="Row")
+    m.field.add(name="Columns", number=1, type=descriptor_pb2.FieldDescriptorProto.TYPE_UINT64, label=descriptor_pb2.FieldDescriptorProto.LABEL_REPEATED)
+    pool = descriptor_pool.DescriptorPool()
+    pool.Add(fdp)
+    RowMsg = message_factory.GetMessageClass(pool.FindMessageTypeByName("internal.Row"))
+
+    orc = oracle.Oracle(workers=1)
+    c = Executor(orc)
+    c.create_field("f")
+    fam = c.family("f")
+    for col in (1, 300, 1 << 20):
+        orc.set_bit(fam, col >> 20, 7, col)
+    # 1 -> 01; 300 -> AC 02; 2^20 -> 80 80 40; tag 0A, length 6
+    assert c.row_proto_columns(Row("f", 7), [0, 1]) == bytes([0x0A, 0x06, 0x01, 0xAC, 0x02, 0x80, 0x80, 0x40])
+    assert c.row_proto_columns(Row("f", 7), [1]) == bytes([0x0A, 0x03, 0x80, 0x80, 0x40])
+    assert c.row_proto_columns(Row("f", 8), [0, 1]) == b""  # len(m.Columns) == 0: nothing is written (:750)
+    cols = [0, 1, 127, 128, 16383, 16384, (1 << 20) - 1, 1 << 20, (1 << 21) - 1, 1 << 21, (255 << 20) + 5, (1 << 28) - 1, 1 << 28, (300 << 20) + 12345]
+    for col in cols:
+        orc.set_bit(fam, col >> 20, 9, col)
+    shards = sorted({col >> 20 for col in cols})
+    assert c.row_proto_columns(Row("f", 9), shards) == RowMsg(Columns=cols).SerializeToString()
+    many = list(range(0, 70000, 7))
+    for col in many:
+        orc.set_bit(fam, 0, 10, col)
+    assert c.row_proto_columns(Row("f", 10), [0]) == RowMsg(Columns=many).SerializeToString()  # 2-byte length prefix and beyond

@@ -395,6 +395,67 @@ def test_import_roaring_rank_recount():
         eng.close()
 
 
+def _row_message_class():
+    """internal.Row { repeated uint64 Columns = 1; } (internal/public.proto) built with google.protobuf: an independent
+    protobuf implementation to check the bytes against."""
+    from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+
+    fdp = descriptor_pb2.FileDescriptorProto(name="public_min.proto", package="internal", syntax="proto3")
+    m = fdp.message_type.add(name="Row")
+    m.field.add(name="Columns", number=1, type=descriptor_pb2.FieldDescriptorProto.TYPE_UINT64,
+                label=descriptor_pb2.FieldDescriptorProto.LABEL_REPEATED)
+    pool = descriptor_pool.DescriptorPool()
+    pool.Add(fdp)
+    return message_factory.GetMessageClass(pool.FindMessageTypeByName("internal.Row"))
+
+
+def test_proto_row_columns():
+    """pb200_eval_proto_columns: the Columns field of internal.Row sized and written on the device (K12) equals the
+    oracle's restatement of the generated marshaller (public.pb.go:745-766) and google.protobuf's encoding of the same
+    column list: shard 0 (1-, 2- and 3-byte varints inside one container), shards on both sides of 2^21 and 2^28, a
+    dense and a sparse row, set operations, a BSI range, Shift with its carry into the next shard, an empty row."""
+    from pilosa_b200.engine import Engine
+
+    RowMsg = _row_message_class()
+    eng, orc = Engine(0), oracle.Oracle(workers=2)
+    try:
+        g, c = Executor(eng), Executor(orc)
+        shards = [0, 1, 2, 3, 255, 256, 70000]
+        for ex in (g, c):
+            ex.create_field("m")
+            ex.create_field("sp")
+            ex.create_field("v", type="int", min=-1000, max=1000)
+            for s in shards:
+                ex.load_fragment("m", s, synth.mixed(s, 0, 6))
+                ex.load_fragment("sp", s, synth.bernoulli(s, 0, 2, 2e-4))
+                ex.load_fragment("v", s, synth.bsi(s, 10, -1000, 1000, 0.02))
+        low = oracle.Bitmap(*([0, 1, 5, 127, 128, 129, 300, 16383, 16384, 16385, 65535, 65536, (1 << 20) - 1] + [(1 << 20) + x for x in (0, 127, 128)])).serialize()
+        for ex in (g, c):  # row 0 / row 1 of field "lo" in shard 0: the varint-length steps inside the first container
+            ex.create_field("lo")
+            ex.load_fragment("lo", 0, low)
+        calls = [Row("lo", 0), Union(Row("lo", 0), Row("lo", 1)), Row("sp", 0), Row("m", 1), Row("m", 3), Intersect(Row("m", 0), Row("m", 2)),
+                 Xor(Row("m", 1), Row("sp", 1)), Difference(Row("m", 4), Row("m", 5)), Row("sp", 1),
+                 g.row_range("v", abi.BSI_GT, 900), g.row_range("v", abi.BSI_BETWEEN, -5, 5),
+                 Shift(Row("m", 2), n=1), Shift(Row("sp", 0), n=3), Row("m", 99), Intersect(Row("sp", 0), Row("sp", 1))]
+        for call in calls:
+            for sh in (shards, [0], [255, 256], [3, 1], [70000]):
+                got = g.row_proto_columns(call, sh)
+                assert got == c.row_proto_columns(call, sh), (repr(call), sh)
+                cols = [x for s in sorted(sh) for x in g.be.eval_columns(g.program(call), s)]
+                assert got == RowMsg(Columns=cols).SerializeToString(), (repr(call), sh)
+        assert g.row_proto_columns(Row("m", 99), shards) == b""  # no columns: the field is omitted
+        assert g.row_proto_columns(Row("lo", 0), [0])[:2] == bytes([0x0A, len(g.row_proto_columns(Row("lo", 0), [0])) - 2])
+        import ctypes
+
+        p = g.program(Row("m", 1))
+        n = ctypes.c_size_t()
+        buf = ctypes.create_string_buffer(4)
+        rc = eng.lib.pb200_eval_proto_columns(eng._h, p, len(p), abi.u64_array([0]), 1, buf, 4, ctypes.byref(n))
+        assert rc == -6 and n.value == len(g.row_proto_columns(Row("m", 1), [0]))  # PB200_ERR_RANGE carries the needed size
+    finally:
+        eng.close()
+
+
 def test_densify_option_changes_layout_not_results():
     """PB200_OPT_DENSIFY_MIN_BYTES: large array / run containers kept as bitmaps in HBM; every result and the
     algorithmic byte count stay what they are without it."""
