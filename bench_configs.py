@@ -251,6 +251,17 @@ def main():
             exp, cms = cpu_timed(lambda: c.row_segments(call, cpu_sh))
             emit(rows, "C4", f"Row(v > {x}) materialised", len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp, {"result_bytes": out_bytes})
 
+        # the same kind of result as the protobuf the client answer carries: Columns of internal.Row, sized and
+        # varint-encoded on the device (K12), one message over all shards
+        for label, call in ((f"Row(v > {(1 << 31) - 4096})", g.row_range("v", abi.BSI_GT, (1 << 31) - 4096)),
+                            (f"Row(v > {(1 << 31) - (1 << 24)})", g.row_range("v", abi.BSI_GT, (1 << 31) - (1 << 24))),
+                            ("Row(-1000 < v < 1000)", g.row_range("v", abi.BSI_BETWEEN, -999, 999))):
+            prog, sh_arr = g.program(call), abi.u64_array(shards)
+            res, k, wms, ab, ln = timed(eng, lambda: eng.eval_proto_columns_raw(prog, sh_arr), max(3, args.reps // 2))
+            got = g.row_proto_columns(call, cpu_sh)
+            exp, cms = cpu_timed(lambda: c.row_proto_columns(call, cpu_sh))
+            emit(rows, "C4", f"{label} as protobuf Row.Columns", len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp, {"result_bytes": int(res[1])})
+
     # ---------------- C5: sparse Count(Intersect) sweep ----------------
     if "c5" in cfgs:
         sweep = [int(x) for x in args.c5_shards.split(",")]
@@ -274,6 +285,12 @@ def main():
             flat, off = eng.pack_programs([prog] * 256)
             _, k, wms, ab, ln = timed(eng, lambda: eng.count_batch_raw(flat, off, 256, sh_arr, n), args.reps)
             emit(rows, "C5", f"batch of 256 x same query, {n} shards (per-query figures)", n, k / 256, wms / 256, ab // 256, ln, cms, len(csh), True)
+
+        prog, sh_arr = g.program(Row("sp", 1)), abi.u64_array(shards)
+        res, k, wms, ab, ln = timed(eng, lambda: eng.eval_proto_columns_raw(prog, sh_arr), max(3, args.reps // 2))
+        got = g.row_proto_columns(Row("sp", 1), cpu_sh)
+        exp, cms = cpu_timed(lambda: c.row_proto_columns(Row("sp", 1), cpu_sh))
+        emit(rows, "C5", f"Row(sp=1) p=1e-4 as protobuf Row.Columns, {nmax} shards", nmax, k, wms, ab, ln, cms, len(cpu_sh), got == exp, {"result_bytes": int(res[1])})
 
     # ---------------- GB: GroupBy over two / three set fields ----------------
     if "gb" in cfgs:

@@ -144,6 +144,7 @@ class Engine:
     def close(self) -> None:
         if getattr(self, "_h", None):
             self._release_rows_buf()
+            self._release_proto_buf()
             self.lib.pb200_shutdown(self._h)
             self._h = None
 
@@ -309,17 +310,36 @@ class Engine:
         self._check(self.lib.pb200_eval_shards(self._h, prog, len(prog), u64_array(shards) if ns else None, ns, buf, cap, off, C.byref(n)))
         return self._rows_buf, off
 
-    def eval_proto_columns(self, prog, shards: Sequence[int]) -> bytes:
-        """The Columns field of internal.Row for the call's result over `shards`, encoded on the device."""
+    def _proto_alloc(self, cap: int) -> None:
+        self._release_proto_buf()
+        self._proto_buf = C.create_string_buffer(cap)
+        self._proto_pinned = self.lib.pb200_host_register(self._h, C.addressof(self._proto_buf), cap) == 0
+
+    def _release_proto_buf(self) -> None:
+        if getattr(self, "_proto_pinned", False) and getattr(self, "_h", None):
+            self.lib.pb200_host_unregister(self._h, C.addressof(self._proto_buf))
+        self._proto_pinned = False
+        self._proto_buf = None
+
+    def eval_proto_columns_raw(self, prog, shards: Sequence[int]):
+        """pb200_eval_proto_columns into a reused, page-locked host buffer: (buffer, length). One call when the
+        buffer is large enough; PB200_ERR_RANGE reports the size to grow it to."""
         ns = len(shards)
         sh = u64_array(shards) if ns else None
         n = C.c_size_t()
-        self._check(self.lib.pb200_eval_proto_columns(self._h, prog, len(prog), sh, ns, None, 0, C.byref(n)))
-        if n.value == 0:
-            return b""
-        buf = C.create_string_buffer(n.value)
-        self._check(self.lib.pb200_eval_proto_columns(self._h, prog, len(prog), sh, ns, buf, n.value, C.byref(n)))
-        return buf.raw[: n.value]
+        if getattr(self, "_proto_buf", None) is None:
+            self._proto_alloc(1 << 20)
+        rc = self.lib.pb200_eval_proto_columns(self._h, prog, len(prog), sh, ns, self._proto_buf, len(self._proto_buf), C.byref(n))
+        if rc == -6:  # PB200_ERR_RANGE
+            self._proto_alloc(n.value + n.value // 4)
+            rc = self.lib.pb200_eval_proto_columns(self._h, prog, len(prog), sh, ns, self._proto_buf, len(self._proto_buf), C.byref(n))
+        self._check(rc)
+        return self._proto_buf, n.value
+
+    def eval_proto_columns(self, prog, shards: Sequence[int]) -> bytes:
+        """The Columns field of internal.Row for the call's result over `shards`, encoded on the device."""
+        buf, n = self.eval_proto_columns_raw(prog, shards)
+        return C.string_at(buf, n)
 
     def eval_roaring_shards(self, prog, shards: Sequence[int]) -> List[bytes]:
         """One row segment (Pilosa roaring bytes) per shard, typed and serialised on the device."""
