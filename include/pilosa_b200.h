@@ -58,6 +58,9 @@ typedef uint32_t pb200_family;
  * A bitmap call tree (executor.go:654-680 executeBitmapCallShard) is passed flattened in
  * post order. N-ary nodes consume their `nargs` operands from the evaluation stack and
  * combine them as a LEFT FOLD in PQL order, exactly like executor.go:1668-1733,1003-1025.
+ * As in the reference, an n-ary node may have any number of operands: one device program holds
+ * 32 leaves, and a call with more is compiled with its wide operations over plain Row operands
+ * evaluated 32 rows at a time into dense temp rows first (same result, one extra pass per chunk).
  */
 enum pb200_op {
   PB200_OP_ROW = 1,        /* Row(f=row): fragment.row, fragment.go:600-641; executor.go:1444-1499 */

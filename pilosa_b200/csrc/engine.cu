@@ -633,10 +633,72 @@ struct Compiler {
     return true;
   }
 
-  // Compiles one post-order program; appends a Prog to out.progs.
+  // Compiles one post-order program; appends a Prog to out.progs. A call whose leaves do not fit one program
+  // (kMaxLeaves) is compiled a second time with its wide n-ary operations over plain rows evaluated chunk-wise
+  // into dense temp rows first — the reference has no limit on the operands of Union / Intersect / Xor /
+  // Difference (executor.go:1667-1735), and a time-range Row is such a Union over many views (:1501-1531).
   bool compile(const pb200_node* nodes, uint32_t n) {
+    const size_t s_leaves = out.leaves.size(), s_instrs = out.instrs.size(), s_pre = out.pre.size(), s_progs = out.progs.size();
+    const uint32_t s_slots = out.n_temp_slots;
+    split_min = 0;
+    if (compile_once(nodes, n)) return true;
+    if (err.rfind("too many leaves", 0) != 0 && err.rfind("expression too long", 0) != 0) return false;
+    out.leaves.resize(s_leaves); out.instrs.resize(s_instrs); out.pre.resize(s_pre); out.progs.resize(s_progs);
+    out.n_temp_slots = s_slots;
+    split_min = 3;
+    return compile_once(nodes, n);
+  }
+
+  uint32_t split_min = 0;  // 0: never; else n-ary operations over at least this many plain Row leaves go through temps
+  size_t pre_base = 0;     // first pre-task of the call being compiled
+
+  // The trailing operands that are plain Row leaves (and the tail of the leaf table) get leaf windows of their own
+  // below the call's window: one sub-program (the same operation, or Union for the subtrahends of a Difference)
+  // per chunk of kMaxLeaves into a temp slot, and the temps take their place as operands.
+  bool wide_split(const pb200_node& nd, std::vector<int>& st) {
+    const bool diff = nd.op == PB200_OP_DIFFERENCE;
+    const size_t n_rel = out.leaves.size() - leaf_base;
+    uint32_t m = 0;  // the longest run of trailing operands that are plain Row leaves at the tail of the leaf table
+    while (m < nd.nargs - (diff ? 1u : 0u) && m < n_rel) {
+      const TNode& tn = tree[st[st.size() - 1 - m]];
+      if (tn.op != 0 || tn.leaf != int(n_rel - 1 - m) || out.leaves[leaf_base + tn.leaf].kind != L_ROW) break;
+      m++;
+    }
+    if (m < 2) return false;
+    const uint32_t lead = nd.nargs - m;  // operands before the run stay operands (Difference: its minuend among them)
+    // [leaves of the call so far | m wide leaves] -> [m wide leaves | leaves of the call so far]: the call's window moves up by m
+    std::rotate(out.leaves.begin() + leaf_base, out.leaves.end() - m, out.leaves.end());
+    for (size_t p = pre_base; p < out.pre.size(); p++)
+      if (out.pre[p].kind == 2 && out.pre[p].prog.leaf_off == leaf_base) out.pre[p].prog.leaf_off += m;  // Shift operands compiled earlier
+    const uint32_t wide_base = leaf_base;
+    leaf_base += m;
+    st.resize(st.size() - m);
+    const uint8_t lop = nd.op == PB200_OP_INTERSECT ? I_AND_LEAF : nd.op == PB200_OP_XOR ? I_XOR_LEAF : I_OR_LEAF;
+    std::vector<int> temps;
+    for (uint32_t b = 0; b < m; b += uint32_t(kMaxLeaves)) {
+      const uint32_t cnt = std::min<uint32_t>(uint32_t(kMaxLeaves), m - b);
+      Compiled::PreTask ev; ev.kind = 2; ev.slot = out.n_temp_slots++;
+      ev.prog.instr_off = uint32_t(out.instrs.size()); ev.prog.n_instr = cnt;
+      ev.prog.leaf_off = wide_base + b; ev.prog.n_leaves = cnt;
+      out.instrs.push_back({I_LOAD, 0});
+      for (uint32_t j = 1; j < cnt; j++) out.instrs.push_back({lop, uint8_t(j)});
+      out.pre.push_back(ev);
+      temps.push_back(leaf_node(add_leaf(L_TEMP, ev.slot, 0)));
+    }
+    if (lead == 0 && temps.size() == 1) { st.push_back(temps[0]); return true; }
+    TNode t; t.op = nd.op;
+    t.kids.assign(st.end() - lead, st.end());
+    st.resize(st.size() - lead);
+    t.kids.insert(t.kids.end(), temps.begin(), temps.end());
+    tree.push_back(t);
+    st.push_back(int(tree.size() - 1));
+    return true;
+  }
+
+  bool compile_once(const pb200_node* nodes, uint32_t n) {
     if (!nodes || n == 0) { err = "empty program"; return false; }
     leaf_base = uint32_t(out.leaves.size());
+    pre_base = out.pre.size();
     tree.clear();
     std::vector<int> st;
     uint32_t n_shifts = 0;
@@ -670,6 +732,7 @@ struct Compiler {
           }
           if (st.size() < nd.nargs) { err = "malformed program: operand stack underflow"; return false; }
           if (nd.nargs == 1) break;  // identity
+          if (split_min && nd.nargs >= split_min && wide_split(nd, st)) break;
           TNode t; t.op = nd.op;
           t.kids.assign(st.end() - nd.nargs, st.end());
           st.resize(st.size() - nd.nargs);

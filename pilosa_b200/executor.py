@@ -155,7 +155,7 @@ class Executor:
         over the time-quantum views that tile [from, to) (viewsByTimeRange, time.go:104-181). Views the field does
         not have are skipped, as the reference skips a view without a fragment (:1519-1522); the result is Empty
         without a quantum or without any such view. The union is an ordinary n-ary Union of Row leaves, one per
-        view family, so it counts against the 32 leaves of a call."""
+        view family; beyond the 32 leaves of one device program the library evaluates it chunk-wise into temp rows."""
         from .timeviews import VIEW_STANDARD, views_by_time_range
 
         f = self.fields.get(field_name)

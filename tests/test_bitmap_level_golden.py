@@ -213,11 +213,12 @@ def test_engine_bitmap_level(gpu, case):
 
 @pytest.mark.gpu
 def test_engine_n_way_union_property(gpu):
-    """TestBitmap_UnionInPlaceProp :551-637 on the engine: the n-ary Union of up to 24 operands (the call's leaf budget
-    is 32) against the plain set union, values compared one by one."""
+    """TestBitmap_UnionInPlaceProp :551-637 on the engine: the n-ary Union of 2 .. 101 operands, as the reference draws
+    them (beyond 32 leaves the call is evaluated chunk-wise through temp rows), against the plain set union, values
+    compared one by one."""
     rnd = random.Random(20190416)
     for _ in range(12):
-        sets = [s for s in _prop_batches(rnd, rnd.randrange(23) + 2) if s]
+        sets = [s for s in _prop_batches(rnd, rnd.randrange(100) + 2) if s]
         if len(sets) < 2:
             continue
         operands = [sorted(s) for s in sets]

@@ -532,6 +532,69 @@ def test_time_range_rows():
     eng.close()
 
 
+def test_wide_nary_operations():
+    """The reference puts no limit on the operands of Union / Intersect / Xor / Difference (executor.go:1667-1735) and a
+    time-range Row is a Union over as many views as the range has (:1501-1531). A call whose leaves do not fit one
+    device program is compiled with its wide operations evaluated chunk-wise into dense temp rows; every result must
+    equal the oracle's, on the count, batch, per-shard, serialised-row and protobuf paths."""
+    from datetime import datetime
+
+    from pilosa_b200.engine import Engine
+
+    eng = Engine(0)
+    try:
+        g, c = Executor(eng), Executor(oracle.Oracle(workers=4))
+        shards = [0, 1, 2]
+        for ex in (g, c):
+            ex.create_field("w")   # 100 sparse rows
+            ex.create_field("d")   # 48 dense rows
+            ex.create_field("m")   # mixed containers
+            ex.create_field("t", type="time", time_quantum="H")
+            for s in shards:
+                ex.load_fragment("w", s, synth.bernoulli(s, 0, 100, 0.004))
+                ex.load_fragment("d", s, synth.bernoulli(s, 0, 48, 0.9))
+                ex.load_fragment("m", s, synth.mixed(s, 0, 8))
+        hours = [f"standard_200011{d:02d}{h:02d}" for d in (27, 28) for h in range(24)]  # 48 hourly views
+        for i, v in enumerate(hours):
+            for s in shards:
+                if (i + s) % 7 == 0:
+                    continue
+                fb = synth.bernoulli(s, 0, 2, 0.003, 500 + i)
+                for ex in (g, c):
+                    ex.load_fragment("t", s, fb, view=v)
+        W = lambda a, b: [Row("w", r) for r in range(a, b)]  # noqa: E731
+        D = lambda a, b: [Row("d", r) for r in range(a, b)]  # noqa: E731
+        calls = [
+            Union(*W(0, 100)), Xor(*W(0, 70)), Intersect(*D(0, 40)), Intersect(*D(0, 33)), Union(*W(0, 33)),
+            Difference(Row("m", 1), *W(0, 50)), Difference(Row("d", 0), *W(0, 100)),
+            Intersect(Row("m", 2), Union(*W(0, 50)), Xor(*W(50, 90))),
+            Union(Shift(Row("m", 3), n=1), *W(0, 60)),                      # a Shift operand compiled before the wide run
+            Union(Intersect(Row("m", 0), Row("m", 1)), *W(10, 75)),         # leading non-leaf operand stays an operand
+            Xor(Union(*W(0, 40)), Union(*W(30, 80)), Row("m", 4)),
+            Intersect(Union(*W(0, 100)), Row("d", 3)),
+            Difference(Union(*W(0, 64)), Union(*W(32, 96))),
+        ]
+        for call in calls:
+            assert g.count(call, shards) == c.count(call, shards), repr(call)[:80]
+            assert g.be.count_shards(g.program(call), shards) == c.be.count_shards(c.program(call), shards), repr(call)[:80]
+        assert g.count_batch(calls, shards) == c.count_batch(calls, shards)
+        assert g.count_batch(calls[:3] + [Row("m", 1)] + calls[7:9], shards) == c.count_batch(calls[:3] + [Row("m", 1)] + calls[7:9], shards)
+        for call in (calls[0], calls[5], calls[7], calls[8]):
+            assert g.row_segments(call, shards) == c.row_segments(call, shards), repr(call)[:80]
+            assert g.row_proto_columns(call, shards) == c.row_proto_columns(call, shards), repr(call)[:80]
+            assert g.row_columns(call, [1]) == c.row_columns(call, [1])
+        # a time range over 2 days of hourly views: 48 Row leaves in one Union
+        t0, t1 = datetime(2000, 11, 27, 0), datetime(2000, 11, 29, 0)
+        tr = g.row_time("t", 1, t0, t1)
+        assert repr(tr) == repr(c.row_time("t", 1, t0, t1)) and len(tr.children) > 32
+        assert g.count(tr, shards) == c.count(tr, shards) > 0
+        both = Intersect(tr, Row("d", 2))
+        assert g.count(both, shards) == c.count(both, shards)
+        assert g.row_segments(both, shards) == c.row_segments(both, shards)
+    finally:
+        eng.close()
+
+
 def test_ops_log_replay_on_load(pair):
     g, c, _ = pair
     base = synth.bernoulli(7, 0, 2, 0.001).bytes()
