@@ -72,6 +72,15 @@ def main():
         mine = g.row_segments(call, shards)
         exp = [(s, b) for s, b in c.row_segments(call, shards) if s % world == rank]
         checks.append((f"segments/{call!r}", mine, exp))
+    # the protobuf Columns field of the rank-local part of a result (serialized Row messages concatenate: the
+    # coordinator appends the ranks' bytes), and a Union wider than one device program, counted across ranks
+    for call in (src, Shift(Row("f", 1), n=1), g.row_range("v", abi.BSI_GT, 1 << 19)):
+        checks.append((f"proto/{call!r}", g.row_proto_columns(call, shards),
+                       c.be.eval_proto_columns(c.program(call), [s for s in sorted(shards) if s % world == rank])))
+    wide = Union(*[Row("z", r) for r in range(100)])
+    checks.append(("wide union", g.count(wide, shards), c.count(wide, shards)))
+    checks.append(("wide in a batch", g.count_batch([wide, src, Difference(Row("m", 0), *[Row("z", r) for r in range(40)])], shards),
+                   c.count_batch([wide, src, Difference(Row("m", 0), *[Row("z", r) for r in range(40)])], shards)))
     bad = [(n, a, b) for n, a, b in checks if a != b]
     ok = torch.tensor([0 if bad else 1], device="cuda")
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
