@@ -188,6 +188,9 @@ checks = [
     (ex2.group_by([R("f"), R("z", limit=5)], shards), ex1.group_by([R("f"), R("z", limit=5)], shards)),
     (ex2.group_by([R("f"), R("f")], shards, filter_call=Row("z", 1), limit=4), ex1.group_by([R("f"), R("f")], shards, filter_call=Row("z", 1), limit=4)),
     (ex2.row_segments(src, shards), [(s_, b_) for s_, b_ in ex1.row_segments(src, shards) if s_ % 2 == rank]),
+    # the protobuf Columns field of the rank-local part; a Union wider than one device program through the same merge
+    (ex2.row_proto_columns(src, shards), ex1.be.eval_proto_columns(ex1.program(src), [s_ for s_ in shards if s_ % 2 == rank])),
+    (ex2.count(Union(*[Row("z", r_) for r_ in range(60)]), shards), ex1.count(Union(*[Row("z", r_) for r_ in range(60)]), shards)),
 ]
 for i, (got, exp) in enumerate(checks):
     assert got == exp, (i, got, exp)
