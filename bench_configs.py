@@ -196,6 +196,18 @@ def main():
             exp, cms = cpu_timed(lambda: c.topn("z", cpu_sh, **kw))
             emit(rows, "C3", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
 
+        # n-ary operations wider than one device program (32 leaves): evaluated 32 rows at a time into temp rows
+        for lo, hi in ((0, 100), (1000, 1400)):
+            call = Union(*[Row("z", r) for r in range(lo, hi)])
+            _, k, wms, ab, ln = timed(eng, lambda: g.count(call, shards), max(3, args.reps // 2))
+            got = g.count(call, cpu_sh)
+            exp, cms = cpu_timed(lambda: c.count(call, cpu_sh))
+            emit(rows, "C3", f"Count(Union(Row(z={lo}) .. Row(z={hi - 1}))) [{hi - lo} operands]", len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
+        wide = Union(*[Row("z", r) for r in range(0, 64)])
+        prop(rows, "C3", "Count(Union of 64 rows) = sum over inclusion-exclusion halves: |A u B| = |A| + |B| - |A n B|",
+             g.count(wide, shards) == g.count(Union(*[Row("z", r) for r in range(32)]), shards) + g.count(Union(*[Row("z", r) for r in range(32, 64)]), shards)
+             - g.count(Intersect(Union(*[Row("z", r) for r in range(32)]), Union(*[Row("z", r) for r in range(32, 64)])), shards))
+
         if "c3" in cfgs:
             top = g.topn("z", shards, n=50, src=src)
             exact = g.count_batch([Intersect(src, Row("z", i)) for i, _ in top], shards)

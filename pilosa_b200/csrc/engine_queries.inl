@@ -77,6 +77,26 @@ int launch_overflow(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint3
   return PB200_OK;
 }
 
+// K13: one chunk of a wide Union (plain Row leaves only) into a dense temp row.
+int launch_union_rows(pb200_ctx* ctx, const BatchDev& bd, const Prog* prog, uint32_t n_shards, uint8_t* dense_out) {
+  const uint64_t n_items = uint64_t(n_shards) * kRowContainers;
+  if (n_items == 0) return PB200_OK;
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  EvalParams p{};
+  p.families = ctx->d_families;
+  p.n_families = uint32_t(ctx->families.size());
+  p.progs = prog; p.instrs = bd.instrs; p.leaves = bd.leaves; p.shards = bd.shards;
+  p.n_shards = n_shards; p.n_queries = 1;
+  p.temp_base = static_cast<const uint8_t*>(ctx->d_temp.p);
+  p.dense_out = dense_out;
+  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + ctx->algo_off);
+  const uint32_t grid = uint32_t(std::min<uint64_t>(n_items, uint64_t(ctx->sm_count) * 8));
+  union_rows_kernel<<<grid, kUnionThreads, 0, ctx->stream>>>(p);
+  ctx->timing.launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return PB200_OK;
+}
+
 int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_t n_shards) {
   if (has_shift(cp)) {  // overflow words of every temp slot (+1 for a result), zero unless a shift sets them
     const size_t bytes = size_t(cp.n_temp_slots + 1) * n_shards * 8;
@@ -91,8 +111,10 @@ int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_
       else
         TRY(launch_bsi_range(ctx, bd, pt.node, n_shards, temp_slot(ctx, pt.slot, n_shards)));
     } else if (pt.kind == 2) {
-      TRY(launch_eval(ctx, bd, bd.progs + cp.progs.size() + i, 1, n_shards, true, nullptr, 0, 0, temp_slot(ctx, pt.slot, n_shards), nullptr));
-      if (has_shift(cp)) TRY(launch_overflow(ctx, bd, bd.progs + cp.progs.size() + i, 1, n_shards, nullptr, 0, 0, ovf_slot(ctx, pt.slot, n_shards)));
+      if (pt.union_rows) TRY(launch_union_rows(ctx, bd, bd.progs + cp.progs.size() + i, n_shards, temp_slot(ctx, pt.slot, n_shards)));
+      else TRY(launch_eval(ctx, bd, bd.progs + cp.progs.size() + i, 1, n_shards, true, nullptr, 0, 0, temp_slot(ctx, pt.slot, n_shards), nullptr));
+      if (has_shift(cp) && !pt.union_rows)  // plain rows carry no overflow: the slot's word stays zero
+        TRY(launch_overflow(ctx, bd, bd.progs + cp.progs.size() + i, 1, n_shards, nullptr, 0, 0, ovf_slot(ctx, pt.slot, n_shards)));
     } else {
       const uint64_t n_words = uint64_t(n_shards) * kRowContainers * kBitmapWords;
       const uint32_t grid = uint32_t(std::min<uint64_t>((n_words + 255) / 256, uint64_t(ctx->sm_count) * 16));

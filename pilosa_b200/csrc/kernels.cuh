@@ -601,4 +601,64 @@ __global__ void __launch_bounds__(kStagedThreads) eval_staged_kernel(EvalParams 
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// K13 — Union of many plain rows into one dense temp row (the chunk sub-programs of a wide
+// n-ary Union, and of the subtrahends of a wide Difference): executeUnionShard's left fold
+// (executor.go:1693-1713) -> Row.Union -> roaring union (roaring.go:3420-3839) for any number
+// of operands at once. OR needs no operand kept apart, so every operand of a column is
+// accumulated into ONE 8 KiB shared-memory window — arrays and runs through the same
+// expansion the staged kernel uses, bitmaps word by word — and the window is written once.
+// One CTA per (shard, container column) item, persistent grid.
+// ---------------------------------------------------------------------------------------
+constexpr int kUnionThreads = 256;
+
+__global__ void __launch_bounds__(kUnionThreads) union_rows_kernel(EvalParams p) {
+  __shared__ __align__(16) uint32_t s_win[kBitmapWords * 2];
+  __shared__ ContainerDesc s_desc[kUnionThreads];  // a batch of operands: one descriptor lookup per thread
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const Prog pg = p.progs[0];
+  const uint32_t n_items = p.n_shards * kRowContainers;
+  unsigned long long bytes_acc = 0;
+  for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const uint32_t s = item / kRowContainers, c = item % kRowContainers;
+    __syncthreads();  // the previous item's window is no longer read
+    uint4* win4 = reinterpret_cast<uint4*>(s_win);
+    for (int j = tid; j < kBitmapWords / 2; j += kUnionThreads) win4[j] = make_uint4(0, 0, 0, 0);
+    for (uint32_t l0 = 0; l0 < pg.n_leaves; l0 += kUnionThreads) {  // any number of operands, a batch of descriptors at a time
+      const uint32_t nl = min(uint32_t(kUnionThreads), pg.n_leaves - l0);
+      if (tid < int(nl)) {
+        const ContainerDesc d = resolve_leaf(p, p.leaves[pg.leaf_off + l0 + tid], s, c);
+        s_desc[tid] = d;
+        bytes_acc += desc_algo_bytes(d);
+      }
+      __syncthreads();
+      // arrays (the bulk of a sparse field): a warp per operand, so that eight payload reads are in flight per CTA
+      // instead of one; their expansion uses shared-memory atomicOr only, so operands may overlap freely
+      for (uint32_t l = warp; l < nl; l += kUnionThreads / 32) {
+        const ContainerDesc d = s_desc[l];
+        if (d.n && desc_type(d) == kArray) stage_container(d, s_win, 0, kBitmapWords, lane, 32);
+      }
+      __syncthreads();
+      for (uint32_t l = 0; l < nl; l++) {  // bitmaps and runs: the whole CTA on one operand
+        const ContainerDesc d = s_desc[l];
+        if (d.n == 0 || desc_type(d) == kArray) continue;  // uniform over the CTA
+        if (desc_type(d) == kBitmap) {  // every thread owns the same words for every bitmap operand
+          const uint4* src = reinterpret_cast<const uint4*>(d.addr);
+          for (int j = tid; j < kBitmapWords / 2; j += kUnionThreads) win4[j] = or128(win4[j], ldg128_stream(src + j));
+        } else {
+          stage_container(d, s_win, 0, kBitmapWords, tid, kUnionThreads);
+        }
+        __syncthreads();  // plain stores of this operand before the atomics / read-modify-writes of the next one
+      }
+      __syncthreads();  // s_desc is rewritten by the next batch
+    }
+    __syncthreads();
+    uint4* dst = reinterpret_cast<uint4*>(p.dense_out + size_t(item) * kBitmapBytes);
+    for (int j = tid; j < kBitmapWords / 2; j += kUnionThreads) dst[j] = win4[j];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) bytes_acc += __shfl_xor_sync(0xffffffffu, bytes_acc, o);
+  if (lane == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+}
+
 }  // namespace pb200
