@@ -196,7 +196,7 @@ def main():
             exp, cms = cpu_timed(lambda: c.topn("z", cpu_sh, **kw))
             emit(rows, "C3", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
 
-        # n-ary operations wider than one device program (32 leaves): evaluated 32 rows at a time into temp rows
+        # n-ary operations wider than one device program (32 leaves): a Union of rows is one accumulating pass (K13)
         for lo, hi in ((0, 100), (1000, 1400)):
             call = Union(*[Row("z", r) for r in range(lo, hi)])
             _, k, wms, ab, ln = timed(eng, lambda: g.count(call, shards), max(3, args.reps // 2))

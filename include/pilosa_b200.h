@@ -60,7 +60,8 @@ typedef uint32_t pb200_family;
  * combine them as a LEFT FOLD in PQL order, exactly like executor.go:1668-1733,1003-1025.
  * As in the reference, an n-ary node may have any number of operands: one device program holds
  * 32 leaves, and a call with more is compiled with its wide operations over plain Row operands
- * evaluated 32 rows at a time into dense temp rows first (same result, one extra pass per chunk).
+ * evaluated into dense temp rows first (same result; a Union of rows in one extra pass whatever
+ * its width, Intersect / Xor in passes of 32 rows).
  */
 enum pb200_op {
   PB200_OP_ROW = 1,        /* Row(f=row): fragment.row, fragment.go:600-641; executor.go:1444-1499 */

@@ -653,8 +653,9 @@ struct Compiler {
   size_t pre_base = 0;     // first pre-task of the call being compiled
 
   // The trailing operands that are plain Row leaves (and the tail of the leaf table) get leaf windows of their own
-  // below the call's window: one sub-program (the same operation, or Union for the subtrahends of a Difference)
-  // per chunk of kMaxLeaves into a temp slot, and the temps take their place as operands.
+  // below the call's window and are evaluated into temp slots that take their place as operands: a Union (also the
+  // subtrahends of a Difference) as ONE sub-program of any width (union_rows_kernel), Intersect / Xor as one
+  // sub-program of the same operation per chunk of kMaxLeaves.
   bool wide_split(const pb200_node& nd, std::vector<int>& st) {
     const bool diff = nd.op == PB200_OP_DIFFERENCE;
     const size_t n_rel = out.leaves.size() - leaf_base;
