@@ -83,6 +83,8 @@ def lib() -> C.CDLL:
         "orc_frag_value": (C.c_int, [vp, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32, i64p]),
         "orc_frag_cache_config": (None, [vp, C.c_uint32, C.c_uint64, C.c_int, C.c_uint32]),
         "orc_frag_recalculate_cache": (None, [vp, C.c_uint32, C.c_uint64]),
+        "orc_frag_cache_add": (None, [vp, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64]),
+        "orc_frag_cache_len": (sz, [vp, C.c_uint32, C.c_uint64]),
         "orc_frag_rebuild_cache": (None, [vp, C.c_uint32, C.c_uint64]),
         "orc_frag_rankings": (sz, [vp, C.c_uint32, C.c_uint64, u64p, u64p, sz]),
         "orc_frag_serialize": (sz, [vp, C.c_uint32, C.c_uint64, C.c_char_p, sz]),
@@ -337,6 +339,12 @@ class Oracle:
 
     def cache_config(self, fam, shard, cache_none=False, max_entries=50000) -> None:
         lib().orc_frag_cache_config(self._h, fam, shard, int(cache_none), max_entries)
+
+    def cache_add(self, fam, shard, row_id: int, n: int) -> None:
+        lib().orc_frag_cache_add(self._h, fam, shard, row_id, n)
+
+    def cache_len(self, fam, shard) -> int:
+        return lib().orc_frag_cache_len(self._h, fam, shard)
 
     def recalculate_cache(self, fam, shard) -> None:
         lib().orc_frag_recalculate_cache(self._h, fam, shard)

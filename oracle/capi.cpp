@@ -211,6 +211,13 @@ void orc_frag_cache_config(void* h, uint32_t fam, uint64_t shard, int cache_none
   f->cache_none = cache_none != 0;
   f->cache.max_entries = max_entries;
 }
+void orc_frag_cache_add(void* h, uint32_t fam, uint64_t shard, uint64_t id, uint64_t n) {  // rankCache.Add cache.go:168-181
+  ((Orc*)h)->holder.fragment(fam, shard, true)->cache.add(id, n);
+}
+size_t orc_frag_cache_len(void* h, uint32_t fam, uint64_t shard) {  // rankCache.Len cache.go:202-206
+  Fragment* f = ((Orc*)h)->holder.fragment(fam, shard);
+  return f ? f->cache.entries.size() : 0;
+}
 void orc_frag_recalculate_cache(void* h, uint32_t fam, uint64_t shard) {
   Fragment* f = ((Orc*)h)->holder.fragment(fam, shard);
   if (f) f->recalculate_cache();

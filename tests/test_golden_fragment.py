@@ -529,3 +529,18 @@ def test_import_roaring_cache_update_by_hand():
     for set_pos, clear_pos, changed, ranking in pos_steps:
         assert orc.frag_import_positions(fam, 0, set_pos, clear_pos) == changed
         assert orc.rankings(fam, 0) == ranking
+
+
+# ---- cache_test.go:24-35 TestCache_Rank: 5 ids with the same count into a cache of 3; Recalculate cuts the entries ----
+def test_cache_rank():
+    import oracle
+
+    orc = oracle.Oracle(workers=1)
+    fam = orc.family_create()
+    cache_size = 3
+    orc.cache_config(fam, 0, False, cache_size)
+    for i in range(1, 2 * cache_size):
+        orc.cache_add(fam, 0, i, 3)
+    orc.recalculate_cache(fam, 0)
+    assert orc.cache_len(fam, 0) == cache_size
+    assert orc.rankings(fam, 0)[1] == [3, 3, 3]
