@@ -150,7 +150,7 @@ class Executor:
         return hit
 
     # ---- call-tree helpers ----
-    def row_time(self, field_name: str, row: int, from_time, to_time) -> Call:
+    def row_time(self, field_name: str, row: int, from_time=None, to_time=None) -> Call:
         """Row(f=row, from=, to=) on a time field (executeRowShard, executor.go:1501-1531): the union of the row
         over the time-quantum views that tile [from, to) (viewsByTimeRange, time.go:104-181). Views the field does
         not have are skipped, as the reference skips a view without a fragment (:1519-1522); the result is Empty
@@ -163,6 +163,12 @@ class Executor:
             raise KeyError(f"field not found: {field_name}")
         if not f.time_quantum:
             return Call("Empty")
+        if from_time is None:  # the zero time.Time (:1507-1508)
+            from datetime import datetime
+            from_time = datetime(1, 1, 1)
+        if to_time is None:    # "current time + 1 day, in order to account for timezone differences" (:1509-1512)
+            from datetime import datetime, timedelta
+            to_time = datetime.now() + timedelta(days=1)
         rows = [Call("Row", field_name=field_name, row=row, view=v)
                 for v in views_by_time_range(VIEW_STANDARD, from_time, to_time, f.time_quantum) if v in f.families]
         if not rows:

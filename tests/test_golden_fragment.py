@@ -213,6 +213,71 @@ def test_executor_topn_src(w):
     assert w.ex.topn("f", [0, 1], n=3, src=Row("other", 100)) == [(20, 3), (10, 2), (0, 1)]
 
 
+# ---- executor_test.go:1122-1143 TestExecutor_Execute_TopN_fill: the second pass refetches the winner's count in the
+# shard whose own top-1 was another row (executor.go:889-902) ----
+def test_executor_topn_fill(w):
+    w.create_field("f")
+    w.set_bits("f", 0, 0, 1, 2, SW)
+    w.set_bits("f", 1, SW + 2, SW)
+    for s in (0, 1):
+        w.recalculate_cache("f", s)
+    assert w.ex.topn("f", [0, 1], n=1) == [(0, 4)]
+
+
+# ---- executor_test.go:1146-1177 TestExecutor_Execute_TopN_fill_small: row 0 is nowhere a shard's top-1, yet wins ----
+def test_executor_topn_fill_small(w):
+    w.create_field("f")
+    w.set_bits("f", 0, 0, SW, 2 * SW, 3 * SW, 4 * SW)
+    w.set_bits("f", 1, 0, 1)
+    w.set_bits("f", 2, SW, SW + 1)
+    w.set_bits("f", 3, 2 * SW, 2 * SW + 1)
+    w.set_bits("f", 4, 3 * SW, 3 * SW + 1)
+    for s in range(5):
+        w.recalculate_cache("f", s)
+    assert w.ex.topn("f", [0, 1, 2, 3, 4], n=1) == [(0, 5)]
+
+
+# ---- executor_test.go:1635-1685 TestExecutor_Execute_Row_Range/RowIDColumnID: timestamped Set() calls on a YMDH time
+# field (each bit goes to the standard view and to the views of viewsByTime, time.go:91-101), Row(f=1, from=, to=) ----
+def test_executor_row_time_range(w):
+    from datetime import datetime, timedelta
+
+    from pilosa_b200.timeviews import views_by_time
+
+    for ex in w._execs():
+        ex.create_field("f", type="time", time_quantum="YMDH")
+    w._cache = getattr(w, "_cache", {})
+    w._cache["f"] = (False, 50000)
+    written = set()
+
+    def set_ts(col, row, ts):
+        for view in ["standard"] + views_by_time("standard", ts, "YMDH"):
+            w.orc.set_bit(w.cpu.family("f", view), 0, row, col)
+            w._dirty.add(("f", view, 0))
+            written.add(view)
+
+    ts = lambda s: datetime.strptime(s, "%Y-%m-%dT%H:%M")  # noqa: E731
+    for col, when in ((2, "1999-12-31T00:00"), (3, "2000-01-01T00:00"), (4, "2000-01-02T00:00"), (5, "2000-02-01T00:00"),
+                      (6, "2001-01-01T00:00"), (7, "2002-01-01T02:00")):
+        set_ts(col, 1, ts(when))
+    set_ts(8, 1, datetime.now() + timedelta(days=2))  # just outside the default end (now + 1 day)
+    set_ts(2, 1, ts("1999-12-30T00:00"))
+    set_ts(2, 1, ts("2002-02-01T00:00"))
+    set_ts(2, 10, ts("2001-01-01T00:00"))
+
+    def columns(frm, to):
+        ex = w.ex
+        return ex.row_columns(ex.row_time("f", 1, frm, to), [0])
+
+    assert columns(ts("1999-12-31T00:00"), ts("2002-01-01T03:00")) == [2, 3, 4, 5, 6, 7]   # Standard
+    assert columns(ts("1999-12-31T00:00"), None) == [2, 3, 4, 5, 6, 7]                      # From
+    assert columns(None, ts("2002-01-01T02:00")) == [2, 3, 4, 5, 6]                         # To
+    for view in sorted(written):  # Clear(2, f=1) clears the bit in the standard view and in the time views (Field.ClearBit, field.go:926-975)
+        w.orc.clear_bit(w.cpu.family("f", view), 0, 1, 2)
+        w._dirty.add(("f", view, 0))
+    assert columns(ts("1999-12-31T00:00"), ts("2002-01-01T03:00")) == [3, 4, 5, 6, 7]      # Clear
+
+
 # ---- executor_test.go:1516-1633 Sum, :1262-1417 Min/Max (two shards, negatives) ----
 def test_executor_sum_min_max(w):
     # TestExecutor_Execute_Sum/ColumnID (:1516-1565): literal Set() calls, Sum = 200/5, filtered 80/2
