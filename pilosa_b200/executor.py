@@ -80,6 +80,7 @@ class Field:
     families: Dict[str, int] = field(default_factory=dict)  # view -> family handle
     bsig: Optional[BsiGroup] = None
     time_quantum: str = ""  # "YMDH" subset for time fields (time.go:29-58)
+    no_standard_view: bool = False  # FieldOptions.NoStandardView: only the time views are written
 
 
 class Executor:
@@ -89,13 +90,14 @@ class Executor:
         self.fields: Dict[str, Field] = {}
 
     # ---- schema / loading (host bookkeeping; holder.go / field.go stay in Go) ----
-    def create_field(self, name: str, type: str = "set", min: int = 0, max: int = 0, time_quantum: str = "") -> Field:
-        f = Field(name, type, time_quantum=time_quantum)
+    def create_field(self, name: str, type: str = "set", min: int = 0, max: int = 0, time_quantum: str = "",
+                     no_standard_view: bool = False) -> Field:
+        f = Field(name, type, time_quantum=time_quantum, no_standard_view=no_standard_view)
         if type == "int":
             # field.go:1047-1066: BitDepth from the declared range, Base 0 for new fields
             f.bsig = BsiGroup(min=min, max=max, base=0, bit_depth=builtins_max(bit_depth_int64(min), bit_depth_int64(max)))
             f.families["bsig_" + name] = self.be.family_create()
-        else:
+        elif not no_standard_view:
             f.families["standard"] = self.be.family_create()
         self.fields[name] = f
         return f
@@ -347,12 +349,32 @@ class Executor:
 
 
     def rows(self, field_name: str, shards: Sequence[int], previous: Optional[int] = None, limit: Optional[int] = None,
-             column: Optional[int] = None) -> List[int]:  # executeRows :1277 (standard view)
+             column: Optional[int] = None, from_time=None, to_time=None) -> List[int]:  # executeRows :1277, executeRowsShard :1316-1441
         if column is not None:
             shards = [column // SHARD_WIDTH]  # :1291-1293
         local = self.local_shards(shards)
         start = 0 if previous is None else previous + 1
-        mine = self.be.rows(self.family(field_name), local, start=start, column=column, limit=limit) if local else []
+        f = self.fields[field_name]
+        views = ["standard"]
+        if f.type == "time" and (from_time is not None or to_time is not None or f.no_standard_view):  # :1340-1402
+            from .timeviews import min_max_views, time_of_view, views_by_time_range
+
+            if not f.time_quantum:
+                return []
+            mn, mx = min_max_views(list(f.families), f.time_quantum)
+            if not mn or not mx:
+                return []  # no time views yet
+            min_t, max_t = time_of_view(mn, False), time_of_view(mx, True)
+            from_time = min_t if from_time is None or from_time < min_t else from_time
+            to_time = max_t if to_time is None or to_time > max_t else to_time
+            views = views_by_time_range("standard", from_time, to_time, f.time_quantum)
+        mine: List[int] = []
+        for v in views:  # RowIDs.merge(viewRows, limit) over the views (:1430-1438): the smallest `limit` ids of the union
+            if v not in f.families or not local:
+                continue
+            mine = sorted(set(mine) | set(self.be.rows(f.families[v], local, start=start, column=column, limit=limit)))
+            if limit is not None:
+                mine = mine[:limit]
         if self.world == 1:
             return mine
         merged = sorted(set().union(*[set(x or []) for x in self._allgather(mine)]))  # RowIDs.merge :1043

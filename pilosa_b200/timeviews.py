@@ -96,3 +96,30 @@ def views_by_time_range(name: str, start: datetime, end: datetime, quantum: str)
         else:
             break
     return out
+
+
+def view_time_part(v: str) -> str:  # time.go:334-339: "standard_201901" -> "201901"
+    return v.split("_")[-1]
+
+
+def min_max_views(views, quantum: str):  # time.go:240-274
+    """The first and the last view (in string order) whose time part has the length of the quantum's LARGEST unit;
+    ("", "") when there is none."""
+    vs = sorted(views)
+    chars = 4 if "Y" in quantum else 6 if "M" in quantum else 8 if "D" in quantum else 10 if "H" in quantum else 0
+    hit = [v for v in vs if len(view_time_part(v)) == chars]
+    return (hit[0], hit[-1]) if hit else ("", "")
+
+
+def time_of_view(v: str, adj: bool):  # time.go:276-331; adj = the exclusive upper bound of the view's period
+    """None for "" (the zero time). ValueError with the reference's text for a name that is not a time view."""
+    if v == "":
+        return None
+    part = view_time_part(v)
+    fmt = {4: "%Y", 6: "%Y%m", 8: "%Y%m%d", 10: "%Y%m%d%H"}.get(len(part))
+    if fmt is None:
+        raise ValueError(f"invalid time format on view: {v}")
+    t = datetime.strptime(part, fmt)
+    if adj:
+        t = {4: lambda: _add_date(t, 1, 0, 0), 6: lambda: _add_month(t), 8: lambda: _add_date(t, 0, 0, 1), 10: lambda: t + timedelta(hours=1)}[len(part)]()
+    return t

@@ -403,3 +403,28 @@ def test_oracle_proto_row_columns_against_protobuf():
     for col in many:
         orc.set_bit(fam, 0, 10, col)
     assert c.row_proto_columns(Row("f", 10), [0]) == RowMsg(Columns=many).SerializeToString()  # 2-byte length prefix and beyond
+
+
+def test_min_max_views_and_time_of_view():
+    """TestMinMaxViews (time_internal_test.go:168-221) and TestTimeOfView (:223-293): the tables, literally."""
+    from datetime import datetime
+
+    from pilosa_b200.timeviews import min_max_views, time_of_view
+
+    for views, q, mn, mx in (([""], "Y", "", ""),
+                             (["std_2019", "std_2020", "std_202002", "std_202002", "std_2022"], "Y", "std_2019", "std_2022"),
+                             (["std_201902", "std_201901"], "M", "std_201901", "std_201902"),
+                             (["std_201902", "std_201901"], "D", "", ""),
+                             (["std_20190201"], "D", "std_20190201", "std_20190201"),
+                             (["foo", "bar"], "D", "", "")):
+        assert min_max_views(views, q) == (mn, mx), (views, q)
+    for view, exp, exp_adj in (("std_2019", datetime(2019, 1, 1), datetime(2020, 1, 1)),
+                               ("std_201902", datetime(2019, 2, 1), datetime(2019, 3, 1)),
+                               ("std_20190203", datetime(2019, 2, 3), datetime(2019, 2, 4)),
+                               ("std_2019020308", datetime(2019, 2, 3, 8), datetime(2019, 2, 3, 9))):
+        assert time_of_view(view, False) == exp and time_of_view(view, True) == exp_adj, view
+    for view in ("foo", "std_201902030801"):
+        for adj in (False, True):
+            with pytest.raises(ValueError, match=f"invalid time format on view: {view}"):
+                time_of_view(view, adj)
+    assert time_of_view("", False) is None  # the zero time (:280-282)

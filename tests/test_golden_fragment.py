@@ -278,6 +278,36 @@ def test_executor_row_time_range(w):
     assert columns(ts("1999-12-31T00:00"), ts("2002-01-01T03:00")) == [3, 4, 5, 6, 7]      # Clear
 
 
+# ---- executor_test.go:3286-3335 TestExecutor_Execute_RowsTime / RowsTimeEmpty: Rows(f, from=, to=) on a YMD time field
+# without a standard view (executeRowsShard :1340-1402: the range is clamped to the existing views) ----
+def test_executor_rows_time(w):
+    from datetime import datetime
+
+    from pilosa_b200.timeviews import views_by_time
+
+    for ex in w._execs():
+        ex.create_field("f", type="time", time_quantum="YMD", no_standard_view=True)
+        ex.create_field("x", type="time", time_quantum="YMD", no_standard_view=True)
+    w._cache = getattr(w, "_cache", {})
+    w._cache["f"] = (False, 50000)
+    ts = lambda s: datetime.strptime(s, "%Y-%m-%dT%H:%M")  # noqa: E731
+    for col, row, when in ((9, 1, "2001-01-01T00:00"), (9, 2, "2002-01-01T00:00"), (9, 3, "2003-01-01T00:00"), (9, 4, "2004-01-01T00:00"),
+                           (SW + 9, 13, "2003-02-02T00:00")):
+        for view in views_by_time("standard", ts(when), "YMD"):
+            w.orc.set_bit(w.cpu.family("f", view), col // SW, row, col)
+            w._dirty.add(("f", view, col // SW))
+    queries = [((ts("1999-12-31T00:00"), ts("2002-01-01T03:00")), [1]),
+               ((ts("2002-01-01T00:00"), ts("2004-01-01T00:00")), [2, 3, 13]),
+               ((ts("1990-01-01T00:00"), ts("1999-01-01T00:00")), []),
+               ((None, None), [1, 2, 3, 4, 13]),
+               ((ts("2002-01-01T00:00"), None), [2, 3, 4, 13]),
+               ((None, ts("2003-02-03T00:00")), [1, 2, 3, 13]),
+               ((ts("2002-01-01T00:00"), ts("2002-01-02T00:00")), [2])]
+    for (frm, to), expected in queries:
+        assert w.ex.rows("f", [0, 1], from_time=frm, to_time=to) == expected, (frm, to)
+    assert w.ex.rows("x", [0, 1], from_time=ts("1999-12-31T00:00"), to_time=ts("2002-01-01T03:00")) == []  # RowsTimeEmpty
+
+
 # ---- executor_test.go:1516-1633 Sum, :1262-1417 Min/Max (two shards, negatives) ----
 def test_executor_sum_min_max(w):
     # TestExecutor_Execute_Sum/ColumnID (:1516-1565): literal Set() calls, Sum = 200/5, filtered 80/2
