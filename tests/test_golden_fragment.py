@@ -186,6 +186,22 @@ def test_executor_not(w):
     assert ex.row_columns(Not(Row("f", 99)), [0, 1]) == [1, 2, 3, SW + 1]
 
 
+# ---- executor_test.go:2713-2757 TestExecutor_Execute_Existence and :2759-2785 TestExecutor_Execute_Not/RowIDColumnID:
+# the reference's own Set() calls (every set column also lands in the existence field) and expected columns ----
+def test_executor_not_literal(w):
+    w.create_field("exists")
+    w.create_field("f")
+    for col, row in ((3, 10), (SW + 1, 10), (SW + 2, 20)):
+        w.set_bit("f", row, col)
+        w.set_bit("exists", 0, col)
+    ex = w.ex
+    assert ex.row_columns(Row("f", 10), [0, 1]) == [3, SW + 1]
+    assert ex.row_columns(Not(Row("f", 10)), [0, 1]) == [SW + 2]
+    assert ex.row_columns(Not(Row("f", 20)), [0, 1]) == [3, SW + 1]
+    assert ex.row_columns(Not(Row("f", 0)), [0, 1]) == [3, SW + 1, SW + 2]
+    assert ex.row_columns(Not(Union(Row("f", 10), Row("f", 20))), [0, 1]) == []
+
+
 # ---- executor_test.go:895-1215 TopN across two shards ----
 def test_executor_topn_two_shards(w):
     w.create_field("f")
