@@ -655,3 +655,18 @@ def test_cache_rank():
     orc.recalculate_cache(fam, 0)
     assert orc.cache_len(fam, 0) == cache_size
     assert orc.rankings(fam, 0)[1] == [3, 3, 3]
+
+
+# ---- fragment_internal_test.go:2761-2833 TestFragment_RoaringImportTopN: bulkImport twice, then importRoaring, f.top()
+# after each step must rank every row by its new count — the rank-cache updates of :2080-2093 and :2258-2276 ----
+def test_fragment_roaring_import_topn(w):
+    import oracle
+
+    w.create_field("f")
+    pos = lambda rows, cols: [r * SW + c for r, c in zip(rows, cols)]  # noqa: E731
+    w.import_positions("f", 0, pos([4, 4, 4, 4], [0, 1, 2, 3]))
+    assert w.frag_top("f") == [(4, 4)]
+    w.import_positions("f", 0, pos([5, 5, 5, 5, 5], [0, 1, 2, 3, 4]))
+    assert w.frag_top("f") == [(5, 5), (4, 4)]
+    w.import_roaring("f", 0, oracle.Bitmap(0, 65535, 65536, (1 << 20) + 1, (1 << 20) + 2, (1 << 20) * 2 + 1).serialize())
+    assert w.frag_top("f") == [(5, 5), (4, 4), (0, 3), (1, 2), (2, 1)]

@@ -159,6 +159,13 @@ class World:
         ex = self.ex
         return ex.be.rows(ex.family(field), [shard], start=start, column=column, limit=limit)
 
+    def import_positions(self, field: str, shard: int, set_pos: Sequence[int] = (), clear_pos: Sequence[int] = ()) -> None:
+        """fragment.importPositions (the bulkImport path) on the oracle AND, independently, on the engine's resident copy."""
+        self.sync()
+        self.orc.frag_import_positions(self.cpu.family(field, self._view(field)), shard, list(set_pos), list(clear_pos))
+        if self.gpu:
+            self.eng.frag_apply(self.gpu.family(field, self._view(field)), shard, list(set_pos), list(clear_pos))
+
     def import_roaring(self, field: str, shard: int, data: bytes, clear: bool = False) -> int:
         """fragment.importRoaring on the oracle AND, independently, on the engine's resident copy."""
         self.sync()
