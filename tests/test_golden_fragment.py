@@ -670,3 +670,24 @@ def test_fragment_roaring_import_topn(w):
     assert w.frag_top("f") == [(5, 5), (4, 4)]
     w.import_roaring("f", 0, oracle.Bitmap(0, 65535, 65536, (1 << 20) + 1, (1 << 20) + 2, (1 << 20) * 2 + 1).serialize())
     assert w.frag_top("f") == [(5, 5), (4, 4), (0, 3), (1, 2), (2, 1)]
+
+
+# ---- fragment_internal_test.go:1570-1685 TestFragment_ImportSet: bulkImport of (row, column) pairs, then a bulkImport
+# with Clear; the table literally (importPositions = pb200_frag_apply on the engine) ----
+def test_fragment_import_set(w):
+    table = [
+        ([1, 1, 1, 1], [0, 1, 2, 3], {1: [0, 1, 2, 3]}, [], [], {1: [0, 1, 2, 3]}),
+        ([1, 1, 1, 1, 2, 2, 2, 2], [0, 1, 2, 3, 0, 1, 2, 3], {1: [0, 1, 2, 3], 2: [0, 1, 2, 3]}, [1, 1, 2], [1, 2, 3], {1: [0, 3], 2: [0, 1, 2]}),
+        ([1, 1, 1, 1, 2], [0, 1, 2, 3, 1], {1: [0, 1, 2, 3], 2: [1]}, [1, 1, 1, 1], [0, 1, 2, 3], {1: [], 2: [1]}),
+        ([1, 1, 1, 1, 2, 2, 1], [0, 1, 2, 3, 1, 8, 1], {1: [0, 1, 2, 3], 2: [1, 8]}, [1, 1], [0, 0], {1: [1, 2, 3], 2: [1, 8]}),
+        ([1, 2, 3], [8, 8, 8], {1: [8], 2: [8], 3: [8]}, [1, 2, 3], [9, 9, 9], {1: [8], 2: [8], 3: [8]}),
+    ]
+    for i, (set_rows, set_cols, set_exp, clr_rows, clr_cols, clr_exp) in enumerate(table):
+        name = f"is{i}"
+        w.create_field(name)
+        w.import_positions(name, 0, [r * SW + c for r, c in zip(set_rows, set_cols)])
+        for row, cols in set_exp.items():
+            assert w.ex.row_columns(Row(name, row), [0]) == cols, (i, "set", row)
+        w.import_positions(name, 0, [], [r * SW + c for r, c in zip(clr_rows, clr_cols)])
+        for row, cols in clr_exp.items():
+            assert w.ex.row_columns(Row(name, row), [0]) == cols, (i, "clear", row)
