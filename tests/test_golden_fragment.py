@@ -691,3 +691,32 @@ def test_fragment_import_set(w):
         w.import_positions(name, 0, [], [r * SW + c for r, c in zip(clr_rows, clr_cols)])
         for row, cols in clr_exp.items():
             assert w.ex.row_columns(Row(name, row), [0]) == cols, (i, "clear", row)
+
+
+# ---- fragment_internal_test.go:3099-3178 TestFragmentPositionsForValue: the BSI bit layout (exists row 0, sign row 1,
+# magnitude bit i in row 2 + i; fragment.go:934-972). Oracle only: a value written with setValue must leave exactly the
+# reference's toSet positions set and its toClear positions clear — the layout every BSI kernel reads. ----
+def test_fragment_positions_for_value():
+    import oracle
+
+    table = [  # (column, bit depth, value, toSet, toClear)
+        (0, 1, 0, [0], [SW, SW * 2]),
+        (0, 3, 0, [0], [SW * 1, SW * 2, SW * 3, SW * 4]),
+        (1, 3, 0, [1], [SW + 1, SW * 2 + 1, SW * 3 + 1, SW * 4 + 1]),
+        (0, 1, 1, [0, SW * 2], [SW]),
+        (0, 4, 10, [0, SW * 3, SW * 5], [SW * 1, SW * 2, SW * 4]),
+        (0, 5, 10, [0, SW * 3, SW * 5], [SW * 1, SW * 2, SW * 4, SW * 6]),
+    ]
+    for i, (col, depth, value, to_set, to_clear) in enumerate(table):
+        orc = oracle.Oracle(workers=1)
+        fam = orc.family_create()
+        for p in to_clear:  # pre-set what must be cleared, so that "clear" is observable
+            orc.set_bit(fam, 0, p // SW, p % SW)
+        orc.set_value(fam, 0, col, depth, value)
+        have = set(oracle.Bitmap.deserialize(orc.frag_serialize(fam, 0)).slice())
+        assert have == set(to_set), (i, sorted(have))
+    # a negative value sets the sign row as well (:953-957)
+    orc = oracle.Oracle(workers=1)
+    fam = orc.family_create()
+    orc.set_value(fam, 0, 7, 4, -10)
+    assert set(oracle.Bitmap.deserialize(orc.frag_serialize(fam, 0)).slice()) == {7, SW + 7, SW * 3 + 7, SW * 5 + 7}
