@@ -720,3 +720,42 @@ def test_fragment_positions_for_value():
     fam = orc.family_create()
     orc.set_value(fam, 0, 7, 4, -10)
     assert set(oracle.Bitmap.deserialize(orc.frag_serialize(fam, 0)).slice()) == {7, SW + 7, SW * 3 + 7, SW * 5 + 7}
+
+
+# ---- fragment_internal_test.go:222-368 TestFragment_SetValue (OK / Overwrite / Clear / NotExists / QuickCheck): the BSI
+# write path of the oracle, which every Sum / Min / Max / Range fixture of this suite is built with. Oracle only. ----
+def test_fragment_set_value():
+    import random
+
+    import oracle
+
+    def frag():
+        orc = oracle.Oracle(workers=1)
+        return orc, orc.family_create()
+
+    orc, fam = frag()                                   # OK
+    assert orc.set_value(fam, 0, 100, 16, 3829) is True
+    assert orc.value(fam, 0, 100, 16) == (3829, True)
+    assert orc.set_value(fam, 0, 100, 16, 3829) is False
+    orc, fam = frag()                                   # Overwrite
+    assert orc.set_value(fam, 0, 100, 16, 3829) is True
+    assert orc.set_value(fam, 0, 100, 16, 2028) is True
+    assert orc.value(fam, 0, 100, 16) == (2028, True)
+    orc, fam = frag()                                   # Clear
+    assert orc.set_value(fam, 0, 100, 16, 3829) is True
+    assert orc.clear_value(fam, 0, 100, 16, 2028) is True
+    assert orc.value(fam, 0, 100, 16) == (0, False)
+    orc, fam = frag()                                   # NotExists
+    assert orc.set_value(fam, 0, 100, 10, 20) is True
+    assert orc.value(fam, 0, 101, 11) == (0, False)
+    rnd = random.Random(222)                            # QuickCheck, with the reference's bounds
+    for _ in range(40):
+        depth, bit_n = rnd.randrange(62) + 1, rnd.randrange(99) + 1
+        orc, fam = frag()
+        want = {}
+        for _ in range(rnd.randrange(50)):
+            v = rnd.getrandbits(64) % (1 << depth)
+            want[v % bit_n] = v
+            orc.set_value(fam, 0, v % bit_n, depth, v)
+        for col, v in want.items():
+            assert orc.value(fam, 0, col, depth) == (v, True), (depth, col)
