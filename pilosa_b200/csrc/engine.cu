@@ -189,6 +189,7 @@ extern "C" int pb200_family_create(pb200_ctx* ctx, pb200_family* out) {
   if (!out) return PB200_ERR_INVALID;
   ctx->families.emplace_back();
   ctx->families_dirty = true;
+  ctx->generation++;
   *out = uint32_t(ctx->families.size() - 1);
   return PB200_OK;
 }
@@ -207,6 +208,7 @@ static int family_grow(pb200_ctx* ctx, Family& fam, uint64_t shard) {
   fam.d_frags = nd;
   fam.cap = ncap;
   ctx->families_dirty = true;
+  ctx->generation++;
   return PB200_OK;
 }
 
@@ -286,13 +288,16 @@ static int upload_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const st
   TRY(family_grow(ctx, fam, shard));
   void* blob = nullptr;
   CUDA_TRY(ctx, cudaMalloc(&blob, img.blob.size()));
+  struct BlobGuard {  // the new copy is released on every failure path below
+    void* p;
+    ~BlobGuard() { if (p) cudaFree(p); }
+  } guard{blob};
   // fix up payload addresses now that the base is known
   auto* descs = reinterpret_cast<ContainerDesc*>(img.blob.data() + img.descs_off);
   const uint64_t base = reinterpret_cast<uint64_t>(blob);
   for (size_t i = 0; i < size_t(img.nrows) * kRowContainers; i++)
     if (descs[i].n) descs[i].addr += base;
-  cudaError_t e = cudaMemcpy(blob, img.blob.data(), img.blob.size(), cudaMemcpyHostToDevice);
-  if (e != cudaSuccess) { cudaFree(blob); return fail(ctx, PB200_ERR_CUDA, std::string("cudaMemcpy fragment: ") + cudaGetErrorString(e)); }
+  CUDA_TRY(ctx, cudaMemcpy(blob, img.blob.data(), img.blob.size(), cudaMemcpyHostToDevice));
 
   Fragment nf;
   nf.blob = blob;
@@ -309,7 +314,11 @@ static int upload_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const st
   nf.row_counts = std::move(img.row_counts);
   default_rank(nf, ctx->rank_cache_size);
 
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // no query may still read the old copy
+  // Order: wait for the queries that may still read the old copy, point the device table at the new copy, and only
+  // then let go of the old one — a failure before that leaves the old fragment fully in place.
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpy(fam.d_frags + shard, &nf.dev, sizeof(FragDev), cudaMemcpyHostToDevice));
+  guard.p = nullptr;
   auto it = fam.frags.find(shard);
   if (it != fam.frags.end()) {
     if (!it->second.all_bitmap) fam.n_not_all_bitmap--;
@@ -320,8 +329,8 @@ static int upload_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const st
   ctx->used += nf.blob_bytes;
   if (!nf.all_bitmap) fam.n_not_all_bitmap++;
   fam.h_frags[shard] = nf.dev;
-  CUDA_TRY(ctx, cudaMemcpy(fam.d_frags + shard, &nf.dev, sizeof(FragDev), cudaMemcpyHostToDevice));
   fam.frags.emplace(shard, std::move(nf));
+  ctx->generation++;
   return PB200_OK;
 }
 
@@ -533,6 +542,7 @@ extern "C" int pb200_frag_drop(pb200_ctx* ctx, pb200_family family, uint64_t sha
   ctx->used -= it->second.blob_bytes;
   free_fragment(it->second);
   fam.frags.erase(it);
+  ctx->generation++;
   return PB200_OK;
 }
 
@@ -963,7 +973,7 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
   if (n_queries != 0 && n_shards != 0) {
     Compiled cp;
     rc = compile_batch(ctx, progs, prog_off, n_queries, cp);
-    if (rc != PB200_OK) { ctx->n_pending--; return rc; }
+    if (rc != PB200_OK) { ctx->n_pending--; ctx->algo_off = 8; return rc; }
     // Count(Row(v <op> x)) with nothing around it: let the comparator kernel count, skip the dense row
     for (uint32_t q = 0; q < n_queries; q++) {
       const Prog& pg = cp.progs[q];
@@ -1098,7 +1108,27 @@ struct pb200_batch {
   Compiled cp;
   BatchDev bd{};
   uint32_t n_queries = 0, n_shards = 0;
+  uint64_t generation = 0;  // ctx->generation the batch was last validated against
 };
+
+// A prepared batch outlives loads, writes and drops of the fragments it names. Its programs hold only (family, row)
+// leaves, so all that can go stale is (a) the device family table the launch passes to the kernels and (b) whether
+// some leaf family now holds array / run containers, i.e. whether the staged kernel and its scratch are needed.
+static int batch_revalidate(pb200_ctx* ctx, pb200_batch* b) {
+  TRY(sync_families(ctx));
+  if (b->generation == ctx->generation) return PB200_OK;
+  bool staging = false;
+  for (const Leaf& lf : b->cp.leaves) {
+    if (lf.kind == L_TEMP) staging = true;
+    else if (lf.kind == L_ROW) {
+      if (lf.family >= ctx->families.size()) return fail(ctx, PB200_ERR_INVALID, "prepared batch names a family that no longer exists");
+      if (ctx->families[lf.family].n_not_all_bitmap) staging = true;
+    }
+  }
+  b->cp.may_need_staging = staging;
+  b->generation = ctx->generation;
+  return PB200_OK;
+}
 
 extern "C" int pb200_batch_prepare(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries,
                                    const uint64_t* shards, uint32_t n_shards, pb200_batch** out) {
@@ -1122,6 +1152,7 @@ extern "C" int pb200_batch_prepare(pb200_ctx* ctx, const pb200_node* progs, cons
     return rc;
   }
   b->n_queries = n_queries; b->n_shards = n_shards;
+  b->generation = ctx->generation;
   *out = b;
   return PB200_OK;
 }
@@ -1129,6 +1160,7 @@ extern "C" int pb200_batch_prepare(pb200_ctx* ctx, const pb200_node* progs, cons
 extern "C" int pb200_batch_launch(pb200_ctx* ctx, pb200_batch* b) {
   ENTER(ctx);
   if (!b) return PB200_ERR_INVALID;
+  TRY(batch_revalidate(ctx, b));
   TRY(ensure_dev(ctx, ctx->d_misc, 64));
   ctx->timing.launches = 0;
   CUDA_TRY(ctx, cudaMemsetAsync(b->d_counts.p, 0, size_t(b->n_queries) * 8, ctx->stream));

@@ -103,6 +103,7 @@ struct pb200_ctx {
   pb200::FamilyDev* d_families = nullptr;
   uint32_t d_families_cap = 0;
   bool families_dirty = true;
+  uint64_t generation = 0;  // bumped by every load / write / drop / table growth: prepared batches re-validate against it
   pb200::DevBuf d_slow_descs, d_ovf;
   pb200::DevBuf d_rows, d_rows_off, d_rows_meta, d_rows_item_off;  // K11: serialised result rows (kernels_rows.cuh)
   bool dense_has_ovf = false;                      // the rows in d_dense carry Shift overflow words

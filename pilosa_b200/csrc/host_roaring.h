@@ -392,6 +392,10 @@ inline bool build_image(const std::vector<HostContainer>& cs, FragImage& img, st
   auto densify = [&](const HostContainer& c) {
     return densify_min_bytes && c.n && c.n != kFullN && (c.type == kArray || c.type == kRun) && payload_bytes(c.type, c.len) >= densify_min_bytes;
   };
+  // An array above ArrayMaxSize or a run list above runMaxSize is legal input (the reference's readers accept it,
+  // roaring.go:1562-1653, :5081-5245) but does not fit the descriptor's 13-bit length: such a container is stored as
+  // the bitmap Container.optimize would turn it into (roaring.go:2289-2338).
+  auto oversize = [](const HostContainer& c) { return (c.type == kArray && c.len > 4096) || (c.type == kRun && c.len > 2048); };
   // rows present
   img.row_ids.clear(); img.row_counts.clear();
   for (auto& c : cs) {
@@ -414,7 +418,7 @@ inline bool build_image(const std::vector<HostContainer>& cs, FragImage& img, st
   img.payload_off = off;
   size_t psize = 0;
   for (auto& c : cs) {
-    const bool dz = densify(c);
+    const bool dz = densify(c) || oversize(c);
     psize = align_up(psize, c.type == kBitmap || dz ? 128 : 16);
     psize += dz ? kBitmapBytes : payload_bytes(c.type, c.len);
   }
@@ -429,12 +433,17 @@ inline bool build_image(const std::vector<HostContainer>& cs, FragImage& img, st
     uint64_t row = c.key >> 4;
     while (img.row_ids[ri] != row) ri++;
     size_t slot = (img.dense ? size_t(row) : ri) * kRowContainers + (c.key & 15);
-    const bool dz = densify(c);
-    p = align_up(p, c.type == kBitmap || dz ? 128 : 16);
+    const bool ov = oversize(c);
+    const bool dz = !ov && densify(c);
+    p = align_up(p, c.type == kBitmap || dz || ov ? 128 : 16);
     uint32_t pb = payload_bytes(c.type, c.len);
     descs[slot].addr = p;
     descs[slot].n = c.n;
-    if (dz) {
+    if (ov) {
+      to_words(c, reinterpret_cast<uint64_t*>(img.blob.data() + p));
+      descs[slot].meta = make_meta(kBitmap, kBitmapWords);
+      pb = kBitmapBytes;
+    } else if (dz) {
       to_words(c, reinterpret_cast<uint64_t*>(img.blob.data() + p));  // 128 B aligned inside the blob
       descs[slot].meta = make_meta_densified(pb);
       pb = kBitmapBytes;
@@ -445,7 +454,7 @@ inline bool build_image(const std::vector<HostContainer>& cs, FragImage& img, st
     p += pb;
     img.n_containers++;
     img.payload_bytes += pb;
-    if (!(c.type == kBitmap || dz || c.n == kFullN)) img.all_bitmap = false;
+    if (!(c.type == kBitmap || dz || ov || c.n == kFullN)) img.all_bitmap = false;
   }
   return true;
 }
