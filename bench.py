@@ -42,8 +42,7 @@ P_DENSITY = 0.10
 SEED = 20190416
 METRIC = "count_intersect_queries_per_sec"
 UNIT = "queries/s"
-SAMPLE_ROWS = 64       # rows the CPU baseline holds (a bounded sample of the same index)
-SAMPLE_QUERIES = 256   # queries per CPU-baseline step
+CPU_SAMPLE_ROWS = 1024  # rows the CPU leg of the native arm holds: 16 shards x 1024 rows x 128 KiB = 2 GiB, far beyond any LLC
 
 
 def peaks():
@@ -80,7 +79,11 @@ class ClockSampler:
         while not self._stop:
             sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
             r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-            self._samples.append((sm, mx, [k for k, b in bits.items() if r & b]))
+            try:
+                pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+            except Exception:
+                pw = None
+            self._samples.append((sm, mx, [k for k, b in bits.items() if r & b], pw))
             time.sleep(0.002)
 
     def start(self):
@@ -110,7 +113,9 @@ class ClockSampler:
             self.nvml.join(timeout=2)
             sm = [s[0] for s in self._samples]
             reasons = sorted({r for s in self._samples for r in s[2]})
+            pw = [s[3] for s in self._samples if s[3] is not None]
             return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self._samples[0][1] if self._samples else None,
+                    "sm_mhz_min": min(sm) if sm else None, "power_w_max": max(pw) if pw else None,
                     "reasons": reasons, "samples": len(sm), "source": "nvml, 2 ms period, timed region only"}
         if self.proc:
             self.proc.terminate()
@@ -173,73 +178,111 @@ def pack_pairs(pairs, fam: int):
     return flat, off
 
 
-def sample_queries(rows: int):
-    rnd = random.Random(SEED + 1)
-    srows = sorted(rnd.sample(range(rows), min(SAMPLE_ROWS, rows)))
-    pairs = []
-    while len(pairs) < SAMPLE_QUERIES:
-        a, b = rnd.sample(srows, 2)
-        pairs.append((a, b))
-    return srows, pairs
+def mem_available_bytes() -> int:
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable:"):
+                return int(ln.split()[1]) * 1024
+    except OSError:
+        pass
+    return 0
 
 
-def cpu_leg(shards, rows: int, steps: int, warmup: int, min_seconds: float):
-    """Times the oracle (reference restatement) on the host cores: mode A (materialise then
-    count, what the reference does) and mode B (fused intersectionCount)."""
-    import oracle
-    from pilosa_b200 import synth
+class CpuArm:
+    """The reference's CPU path for this workload, restated (oracle/): an index over rows [0, rows_held) of the same
+    per-(shard, row, container) streams the GPU arm loads, a PERSISTENT worker pool of `cores` threads (executor.go:83-107),
+    and one step = the whole batch of Count(Intersect(Row, Row)) calls in flight together, i.e. batch x shards per-shard
+    jobs on that pool (what concurrent requests give the reference; executor.go:2576-2611).
+      mode A  executeCount as the reference runs it: materialise the intersection, then count (executor.go:1804-1810)
+      mode B  best-effort CPU: fused intersectionCount, nothing materialised (roaring.go:568-590)"""
 
-    cores = os.cpu_count() or 1
-    orc = oracle.Oracle(workers=cores)
-    fam = orc.family_create()
-    srows, pairs = sample_queries(rows)
-    with ThreadPoolExecutor(max_workers=min(cores, len(shards))) as tp:
-        frs = list(tp.map(lambda s: synth.bernoulli_rows(s, srows, P_DENSITY, SEED), shards))
-    for s, fb in zip(shards, frs):
-        orc.frag_load(fam, s, fb)
-    del frs
-    flat, off = pack_pairs(pairs, fam)
-    progs = [(type(flat[0]) * 3)(flat[3 * i], flat[3 * i + 1], flat[3 * i + 2]) for i in range(len(pairs))]
+    def __init__(self, shards, rows_held: int, batch: int, cores: int):
+        import oracle
+        from pilosa_b200 import synth
 
-    def run(fused: bool):
-        return [orc.count(p, shards, fused) for p in progs]
+        self.shards, self.rows_held, self.batch, self.cores = list(shards), rows_held, batch, cores
+        self.orc = oracle.Oracle(workers=cores)
+        self.fam = self.orc.family_create()
+        t0 = time.perf_counter()
 
-    for _ in range(max(1, warmup)):
-        counts = run(False)
-    t0 = time.perf_counter()
-    n_steps = 0
-    while n_steps < steps or (time.perf_counter() - t0) < min_seconds:
-        run(False)
-        n_steps += 1
-        if n_steps >= steps and min_seconds <= 0:
-            break
-    dt_a = time.perf_counter() - t0
-    t1 = time.perf_counter()
-    for _ in range(max(1, n_steps // 2)):
-        run(True)
-    dt_b = time.perf_counter() - t1
-    qa = n_steps * len(pairs) / dt_a
-    qb = max(1, n_steps // 2) * len(pairs) / dt_b
-    return {"value": qa, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{len(pairs)} queries/step over {len(srows)} of the {rows} rows x {len(shards)} shards, {n_steps} steps, "
-                      f"mode A (materialise then count, executor.go:1804); worker pool = {cores} threads",
-            "fused_intersection_count_value": qb, "seconds": dt_a}, pairs, counts
+        def gen(s):
+            fb = synth.bernoulli(s, 0, rows_held, P_DENSITY, SEED)
+            self.orc.frag_load(self.fam, s, fb)   # ctypes releases the GIL: shards are generated and parsed in parallel
+
+        with ThreadPoolExecutor(max_workers=max(1, min(cores, 8, len(self.shards)))) as tp:
+            list(tp.map(gen, self.shards))
+        self.build_s = time.perf_counter() - t0
+        self.sh = (C.c_uint64 * len(self.shards))(*self.shards)
+        self.index_bytes = len(self.shards) * rows_held * 16 * 8192
+
+    def step(self, pairs, fused: bool):
+        flat, off = pack_pairs(pairs, self.fam)
+        return self.orc.count_batch_raw(flat, off, len(pairs), self.sh, len(self.shards), fused)
+
+    def time_mode(self, batches, fused: bool, steps: int, min_seconds: float):
+        """(queries/s, steps run, seconds). Batches are cycled; packing the programs is outside the clock."""
+        packed = [pack_pairs(p, self.fam) for p in batches]
+        n, t0 = 0, time.perf_counter()
+        while n < steps or (time.perf_counter() - t0) < min_seconds:
+            fl, off = packed[n % len(packed)]
+            self.orc.count_batch_raw(fl, off, self.batch, self.sh, len(self.shards), fused)
+            n += 1
+        dt = time.perf_counter() - t0
+        return n * self.batch / dt, n, dt
+
+    def describe(self, qa, qb, n_steps, secs) -> dict:
+        per_q = len(self.shards) * 16 * 2 * (8192 + 16)
+        return {"value": qa, "unit": UNIT, "cores": self.cores, "kind": "port",
+                "sample": f"{self.batch} queries per step ({self.batch * len(self.shards)} per-shard jobs on a persistent pool of {self.cores} "
+                          f"threads) over rows [0,{self.rows_held}) x {len(self.shards)} shards = {self.index_bytes / 2**30:.1f} GiB held in RAM, "
+                          f"{n_steps} steps in {secs:.1f} s; value = mode A (materialise then count, executor.go:1804)",
+                "mode_a_materialise_then_count": qa, "mode_b_fused_intersection_count": qb,
+                "mode_a_algorithmic_gb_per_s": qa * per_q / 1e9, "mode_b_algorithmic_gb_per_s": qb * per_q / 1e9,
+                "index_build_s": self.build_s, "seconds": secs}
+
+
+def cpu_rows_held(rows: int, shards: int, want_all: bool) -> int:
+    """All rows of the GPU arm's index when the host has the memory for it (index + generator blobs), else a prefix."""
+    if want_all:
+        need = shards * rows * 16 * 8192
+        if mem_available_bytes() > 2.2 * need + (8 << 30):
+            return rows
+    return min(rows, CPU_SAMPLE_ROWS)
 
 
 def run_reference(args):
+    """--impl reference: the CPU arm alone, on this arm's config. Each step is the full batch of the GPU arm (same
+    generator, same seed, same pairs) when the whole index fits in host RAM; otherwise the batch is drawn over the
+    prefix of rows that is held, and `sample` says so."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    cores = os.cpu_count() or 1
     shards = list(range(SHARDS_PER_GPU))
-    cpu, pairs, _ = cpu_leg(shards, args.rows, args.steps, args.warmup, 0.0)
+    held = cpu_rows_held(args.rows, len(shards), True)
+    arm = CpuArm(shards, held, args.batch, cores)
+    batches = make_batches(args.warmup + args.steps, args.batch, held)
+    for i in range(args.warmup):
+        arm.step(batches[i], False)
+    qa, n, secs = arm.time_mode(batches[args.warmup:], False, args.steps, 0.0)
+    qb, _, _ = arm.time_mode(batches[args.warmup:], True, max(1, args.steps // 2), 0.0)
+    cpu = arm.describe(qa, qb, n, secs)
+    if args.cpu_scan:  # throughput against pool size: the pool, not thread start-up, is what is being timed
+        scan = {}
+        for w in sorted({1, 2, 4, max(1, cores // 2), cores}):
+            arm.orc.set_workers(w)
+            a, _, _ = arm.time_mode(batches[args.warmup:], False, 2, 0.0)
+            b, _, _ = arm.time_mode(batches[args.warmup:], True, 2, 0.0)
+            scan[str(w)] = {"mode_a": a, "mode_b": b}
+        cpu["workers_scan"] = scan
     line = {
-        "impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * len(pairs) / cpu["value"], "higher_is_better": True, "scaling": "weak",
+        "impl": "reference", "metric": METRIC, "value": qa, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * args.batch / qa, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": workload_config(args, 1) | {"reference_arm": "CPU restatement of the reference's Go path (oracle/, Go toolchain unavailable); "
-                                                               "each step = a bounded sample of the batch"},
+        "config": workload_config(args, 1),
         "cpu_baseline": cpu,
-        "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "e2e": {"value": qa, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "reference_arm": "CPU restatement of the reference's Go path (oracle/; the Go toolchain is not in this image), all host cores",
     }
     print(json.dumps(line), flush=True)
 
@@ -266,9 +309,11 @@ def main():
     ap.add_argument("--batch", type=int, default=1024)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-scan", action="store_true", help="reference arm: also time the pool at 1/2/4/P workers")
+    ap.add_argument("--sustained-seconds", type=float, default=2.0)
     args = ap.parse_args()
     if args.warmup < 3:
-        args.warmup = 3
+        raise SystemExit("bench.py: --warmup must be >= 3 (timing rule); got %d" % args.warmup)
 
     if args.impl == "reference":
         run_reference(args)
@@ -330,13 +375,26 @@ def main():
         prepared = [eng.batch_prepare(fl, off, B, shards_arr, len(shards)) for fl, off in batches]
         tens = [torch.as_tensor(DevArray(eng.batch_device_counts(b), B), device="cuda") for b in prepared] if world > 1 else None
 
+        # N > 1: the all-reduce(sum) of a batch's counts does not gate the next batch's kernel, so it is queued on a side
+        # stream behind an event recorded after the kernel; the launching stream goes straight on to the next batch.
+        side = torch.cuda.Stream() if world > 1 else None
+        ev_k = [torch.cuda.Event() for _ in prepared] if world > 1 else None
+
         def step_resident(i):
             eng.batch_launch(prepared[i])
             if world > 1:
-                dist.all_reduce(tens[i], op=dist.ReduceOp.SUM)
+                ev_k[i].record(stream)
+                side.wait_event(ev_k[i])
+                with torch.cuda.stream(side):
+                    dist.all_reduce(tens[i], op=dist.ReduceOp.SUM)
+
+        def join_side():
+            if world > 1:
+                stream.wait_stream(side)
 
         for i in range(args.warmup):
             step_resident(i)
+        join_side()
         barrier()
         if rank == 0:  # one poller per box: concurrent NVML queries from every rank serialise in the driver
             sampler.start()
@@ -344,12 +402,34 @@ def main():
         ev0.record(stream)
         for i in range(args.warmup, n_batches):
             step_resident(i)
+        join_side()                      # the last all-reduce is inside the timed region
         ev1.record(stream)
         barrier()
         ms_total = max_over_ranks(ev0.elapsed_time(ev1))
         out = (C.c_uint64 * B)()
         eng.batch_fetch(prepared[-1], out)
         last_resident = list(out)
+
+        # ---- leg 1b: the same resident loop held for >= --sustained-seconds (clocks and power settle; the 20-step
+        # figure above is a burst) ----
+        sustained = None
+        if args.sustained_seconds > 0:
+            n_sus = max(args.steps, int(args.sustained_seconds / max(1e-6, ms_total / args.steps * 1e-3)) + 1)
+            sus_sampler = ClockSampler(local_rank)
+            barrier()
+            if rank == 0:
+                sus_sampler.start()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record(stream)
+            for k in range(n_sus):
+                step_resident(k % len(prepared))
+            join_side()
+            s1.record(stream)
+            barrier()
+            sus_ms = max_over_ranks(s0.elapsed_time(s1))
+            sus_clocks = sus_sampler.stop() if rank == 0 else None
+            sustained = {"steps": n_sus, "seconds": sus_ms * 1e-3, "ms_per_step": sus_ms / n_sus,
+                         "value": B * world / (sus_ms / n_sus * 1e-3), "unit": UNIT, "clocks": sus_clocks}
         for b in prepared:
             eng.batch_free(b)
 
@@ -419,21 +499,29 @@ def main():
                      "algo_bytes_per_launch": algo_bytes, "peak_source": peak_src,
                      "note": "achieved = algorithmic bytes per launch / mean launch duration from CUDA events over the timed region "
                              "(includes the per-step 8 KiB count memset" + (" and the NCCL all-reduce of the counts" if world > 1 else "") + ")"},
+        "sustained": sustained,
         "columns_per_s": value * SHARDS_PER_GPU * (1 << 20) * 2,
         "global_queries_per_s": value / world,
         "index_build_s": t_build,
         "engine_algo_bytes_last_call": int(tm.algo_bytes),
     }
 
-    # ---- CPU baseline (rank 0, N = 1 only) + parity spot check against it ----
+    # ---- CPU baseline (rank 0, N = 1 only) + parity check against it ----
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu, pairs, cpu_counts = cpu_leg(shards, args.rows, 1, 1, args.cpu_seconds)
-        fl, off = pack_pairs(pairs, fam)
-        got = (C.c_uint64 * len(pairs))()
-        eng.count_batch_raw(fl, off, len(pairs), shards_arr, len(shards), got)
-        ok = list(got) == list(cpu_counts)
-        line["cpu_baseline"] = cpu
-        line["parity_check"] = "ok: %d sample queries bit-exact vs oracle" % len(pairs) if ok else "MISMATCH vs oracle"
+        cores = os.cpu_count() or 1
+        held = cpu_rows_held(args.rows, len(shards), False)
+        arm = CpuArm(shards, held, args.batch, cores)
+        cb = make_batches(4, args.batch, held)
+        cpu_counts = list(arm.step(cb[0], False))           # warm-up step; its counts are the parity reference
+        qa, n_a, secs_a = arm.time_mode(cb, False, 1, args.cpu_seconds * 0.6)
+        qb, _, _ = arm.time_mode(cb, True, 1, args.cpu_seconds * 0.4)
+        fl, off = pack_pairs(cb[0], fam)
+        got = (C.c_uint64 * args.batch)()
+        eng.count_batch_raw(fl, off, args.batch, shards_arr, len(shards), got)
+        ok = list(got) == cpu_counts
+        line["cpu_baseline"] = arm.describe(qa, qb, n_a, secs_a)
+        line["parity_check"] = "ok: %d queries (one full batch) bit-exact vs oracle" % args.batch if ok else "MISMATCH vs oracle"
+        del arm
         if not ok:
             print(json.dumps(line), flush=True)
             raise SystemExit("parity check against the oracle failed")

@@ -90,6 +90,7 @@ def lib() -> C.CDLL:
         "orc_frag_serialize": (sz, [vp, C.c_uint32, C.c_uint64, C.c_char_p, sz]),
         "orc_count": (C.c_int, [vp, np_, C.c_uint32, u64p, C.c_uint32, C.c_int, u64p]),
         "orc_count_shards": (C.c_int, [vp, np_, C.c_uint32, u64p, C.c_uint32, C.c_int, u64p]),
+        "orc_count_batch": (C.c_int, [vp, np_, C.POINTER(C.c_uint32), C.c_uint32, u64p, C.c_uint32, C.c_int, u64p]),
         "orc_eval_columns": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, u64p, sz, C.POINTER(sz)]),
         "orc_eval_roaring": (C.c_int, [vp, np_, C.c_uint32, C.c_uint64, C.c_char_p, sz, C.POINTER(sz)]),
         "orc_eval_proto_columns": (C.c_int, [vp, np_, C.c_uint32, u64p, C.c_uint32, C.c_char_p, sz, C.POINTER(sz)]),
@@ -373,6 +374,13 @@ class Oracle:
         out = (C.c_uint64 * max(1, len(shards)))()
         _check(lib().orc_count_shards(self._h, prog, len(prog), u64_array(shards), len(shards), int(fused), out))
         return list(out[: len(shards)])
+
+    def count_batch_raw(self, flat, off, n_queries: int, shards_arr, n_shards: int, fused=False, out=None):
+        """n_queries Count programs (flat pb200_node array + offsets) in flight together on the shared worker pool."""
+        if out is None:
+            out = (C.c_uint64 * max(1, n_queries))()
+        _check(lib().orc_count_batch(self._h, flat, off, n_queries, shards_arr, n_shards, int(fused), out))
+        return out
 
     def eval_columns(self, prog, shard: int) -> List[int]:
         n = C.c_size_t()

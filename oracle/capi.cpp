@@ -253,6 +253,14 @@ int orc_count_shards(void* h, const pb200_node* prog, uint32_t n, const uint64_t
     std::copy(v.begin(), v.end(), out);
   });
 }
+// n_queries Count calls in flight together on the shared worker pool (Executor::count_batch).
+int orc_count_batch(void* h, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries, const uint64_t* shards, uint32_t ns,
+                    int fused, uint64_t* out) {
+  return guard([&] {
+    auto v = ((Orc*)h)->exec.count_batch(progs, prog_off, n_queries, vec(shards, ns), fused != 0);
+    std::copy(v.begin(), v.end(), out);
+  });
+}
 int orc_eval_columns(void* h, const pb200_node* prog, uint32_t n, uint64_t shard, uint64_t* out, size_t cap, size_t* out_n) {
   return guard([&] {
     auto cols = ((Orc*)h)->exec.eval_shard(prog, n, shard).columns();

@@ -6,6 +6,8 @@
 #pragma once
 #include <atomic>
 #include <cmath>
+#include <condition_variable>
+#include <deque>
 #include <functional>
 #include <mutex>
 #include <set>
@@ -663,9 +665,85 @@ struct Holder {
   }
 };
 
+// The executor's worker pool (executor.go:83-107): NewExecutor starts workerPoolSize goroutines ONCE; each runs
+// worker() (:2604-2611), taking jobs off the shared `work` channel for as long as the executor lives. mapperLocal
+// (:2576-2601) pushes one job per shard onto that channel and then collects one response per job; jobs of different
+// requests interleave on the same workers. Restated with threads created once, a queue of job groups (one group =
+// the jobs one caller pushed) and a completion wait per group.
+class WorkerPool {
+ public:
+  explicit WorkerPool(int n) {
+    for (int i = 0; i < std::max(1, n); i++) threads_.emplace_back([this] { worker(); });
+  }
+  ~WorkerPool() {
+    { std::lock_guard<std::mutex> g(mu_); stop_ = true; }
+    cv_.notify_all();
+    for (auto& t : threads_) t.join();
+  }
+  int size() const { return (int)threads_.size(); }
+
+  // Pushes jobs fn(0) .. fn(n-1) and blocks until every one of them has reported back.
+  void run(size_t n, const std::function<void(size_t)>& fn) {
+    if (n == 0) return;
+    auto g = std::make_shared<Group>();
+    g->fn = &fn; g->n = n;
+    { std::lock_guard<std::mutex> lk(mu_); groups_.push_back(g); }
+    cv_.notify_all();
+    std::unique_lock<std::mutex> lk(g->mu);
+    g->cv.wait(lk, [&] { return g->done.load(std::memory_order_acquire) == n; });
+    if (g->err) std::rethrow_exception(g->err);
+  }
+
+ private:
+  struct Group {
+    const std::function<void(size_t)>* fn = nullptr;
+    size_t n = 0;
+    std::atomic<size_t> next{0}, done{0};
+    std::exception_ptr err;
+    std::mutex mu;
+    std::condition_variable cv;
+  };
+  void worker() {
+    std::shared_ptr<Group> g;
+    for (;;) {
+      if (!g) {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [&] { return stop_ || !groups_.empty(); });
+        if (stop_) return;
+        g = groups_.front();
+      }
+      const size_t i = g->next.fetch_add(1, std::memory_order_relaxed);
+      if (i >= g->n) {  // this group has no job left to hand out: retire it from the queue
+        std::lock_guard<std::mutex> lk(mu_);
+        if (!groups_.empty() && groups_.front() == g) groups_.pop_front();
+        g.reset();
+        continue;
+      }
+      try { (*g->fn)(i); }
+      catch (...) { std::lock_guard<std::mutex> lk(g->mu); g->err = std::current_exception(); }
+      if (g->done.fetch_add(1, std::memory_order_acq_rel) + 1 == g->n) {
+        std::lock_guard<std::mutex> lk(g->mu);
+        g->cv.notify_all();
+      }
+    }
+  }
+  std::vector<std::thread> threads_;
+  std::deque<std::shared_ptr<Group>> groups_;
+  std::mutex mu_;
+  std::condition_variable cv_;
+  bool stop_ = false;
+};
+
 struct Executor {
   Holder* holder;
   int workers = 1;  // executor.go:83-107 worker pool; server/config.go:172 NumCPU
+  mutable std::unique_ptr<WorkerPool> pool_;
+  mutable std::mutex pool_mu_;
+  WorkerPool& pool() const {  // started on first use, restarted when `workers` changes
+    std::lock_guard<std::mutex> g(pool_mu_);
+    if (!pool_ || pool_->size() != std::max(1, workers)) pool_.reset(new WorkerPool(workers));
+    return *pool_;
+  }
 
   // executor.go:654-680 executeBitmapCallShard on a flattened program.
   Row eval_shard(const pb200_node* prog, uint32_t n, uint64_t shard) const {
@@ -724,28 +802,45 @@ struct Executor {
     return std::move(st[0]);
   }
 
-  // executor.go:2576-2611 mapperLocal: one job per shard on the worker pool.
+  // executor.go:2576-2611 mapperLocal: one job per shard pushed to the (persistent) worker pool, one response each.
   template <class T>
   std::vector<T> map_shards(const std::vector<uint64_t>& shards, const std::function<T(uint64_t)>& fn) const {
     std::vector<T> out(shards.size());
-    int nw = std::max(1, std::min<int>(workers, (int)shards.size()));
-    if (nw == 1) { for (size_t i = 0; i < shards.size(); i++) out[i] = fn(shards[i]); return out; }
-    std::atomic<size_t> next{0};
-    std::vector<std::thread> th;
-    std::exception_ptr err;
-    std::mutex mu;
-    for (int w = 0; w < nw; w++)
-      th.emplace_back([&] {
-        for (;;) {
-          size_t i = next.fetch_add(1);
-          if (i >= shards.size()) break;
-          try { out[i] = fn(shards[i]); }
-          catch (...) { std::lock_guard<std::mutex> g(mu); err = std::current_exception(); }
-        }
-      });
-    for (auto& t : th) t.join();
-    if (err) std::rethrow_exception(err);
+    if (workers <= 1 || shards.size() <= 1) { for (size_t i = 0; i < shards.size(); i++) out[i] = fn(shards[i]); return out; }
+    pool().run(shards.size(), [&](size_t i) { out[i] = fn(shards[i]); });
     return out;
+  }
+
+  // Many Count calls in flight at once — what concurrent HTTP requests give the reference: every request runs its
+  // own mapperLocal, and all of them push their per-shard jobs onto the ONE shared pool (executor.go:99-105), so
+  // the workers see queries x shards jobs. Each job is executeCount's map function for one shard (:1804-1810), the
+  // per-query reduce is `uint64 +` (:1813). out[q] = Count of program q over `shards`.
+  std::vector<uint64_t> count_batch(const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries,
+                                    const std::vector<uint64_t>& shards, bool fused = false) const {
+    const size_t ns = shards.size();
+    std::vector<uint64_t> per(size_t(n_queries) * ns, 0), out(n_queries, 0);
+    auto job = [&](size_t j) {
+      const uint32_t q = uint32_t(j / ns);
+      per[j] = count_one_shard(progs + prog_off[q], prog_off[q + 1] - prog_off[q], shards[j % ns], fused);
+    };
+    if (workers <= 1) for (size_t j = 0; j < per.size(); j++) job(j);
+    else pool().run(per.size(), job);
+    for (uint32_t q = 0; q < n_queries; q++)
+      for (size_t s = 0; s < ns; s++) out[q] += per[size_t(q) * ns + s];
+    return out;
+  }
+
+  // The map function of executeCount for one shard. fused=false: executeBitmapCallShard materialises the row, then
+  // Row.Count (what the reference does). fused=true: a top-level two-leaf Intersect goes through intersectionCount
+  // without materialising (BASELINE.md mode B "best-effort CPU").
+  uint64_t count_one_shard(const pb200_node* prog, uint32_t n, uint64_t shard, bool fused) const {
+    if (fused && n == 3 && prog[0].op == PB200_OP_ROW && prog[1].op == PB200_OP_ROW && prog[2].op == PB200_OP_INTERSECT && prog[2].nargs == 2) {
+      Fragment* fa = holder->fragment(prog[0].family, shard);
+      Fragment* fb = holder->fragment(prog[1].family, shard);
+      if (!fa || !fb) return 0;
+      return fa->row(prog[0].row).intersection_count(fb->row(prog[1].row));
+    }
+    return eval_shard(prog, n, shard).count();
   }
 
   // executor.go:1793-1825. fused=false materialises then counts (what the
@@ -758,17 +853,7 @@ struct Executor {
     return tot;
   }
   std::vector<uint64_t> count_shards(const pb200_node* prog, uint32_t n, const std::vector<uint64_t>& shards, bool fused = false) const {
-    bool two_leaf = fused && n == 3 && prog[0].op == PB200_OP_ROW && prog[1].op == PB200_OP_ROW &&
-                    prog[2].op == PB200_OP_INTERSECT && prog[2].nargs == 2;
-    return map_shards<uint64_t>(shards, [&](uint64_t shard) -> uint64_t {
-      if (two_leaf) {
-        Fragment* fa = holder->fragment(prog[0].family, shard);
-        Fragment* fb = holder->fragment(prog[1].family, shard);
-        if (!fa || !fb) return 0;
-        return fa->row(prog[0].row).intersection_count(fb->row(prog[1].row));
-      }
-      return eval_shard(prog, n, shard).count();
-    });
+    return map_shards<uint64_t>(shards, [&](uint64_t shard) -> uint64_t { return count_one_shard(prog, n, shard, fused); });
   }
 
   // executor.go:933-1000 executeTopNShard

@@ -428,3 +428,44 @@ def test_min_max_views_and_time_of_view():
             with pytest.raises(ValueError, match=f"invalid time format on view: {view}"):
                 time_of_view(view, adj)
     assert time_of_view("", False) is None  # the zero time (:280-282)
+
+
+def test_oracle_worker_pool_batch_matches_single_calls():
+    """The oracle's persistent worker pool (executor.go:83-107): a batch of Count calls pushed as queries x shards jobs
+    gives the per-call results, in both modes, for any pool size, and the pool is reused across calls."""
+    import ctypes as C
+
+    import oracle
+    from pilosa_b200 import abi, synth
+    from pilosa_b200.abi import Intersect, Row, Union
+    from pilosa_b200.executor import Executor
+
+    orc = oracle.Oracle(workers=4)
+    ex = Executor(orc)
+    ex.create_field("f")
+    ex.create_field("m")
+    shards = [0, 1, 2, 3, 4]
+    for s in shards:
+        ex.load_fragment("f", s, synth.bernoulli(s, 0, 6, 0.10))
+        ex.load_fragment("m", s, synth.mixed(s, 0, 4))
+    calls = [Intersect(Row("f", a), Row("f", b)) for a in range(6) for b in range(a + 1, 6)] + [Union(Row("m", 0), Row("m", 1), Row("m", 3)), Row("m", 2)]
+    progs = [ex.program(c) for c in calls]
+    flat = (abi.Node * sum(len(p) for p in progs))()
+    off = (C.c_uint32 * (len(progs) + 1))()
+    k = 0
+    for i, p in enumerate(progs):
+        off[i] = k
+        for nd in p:
+            flat[k] = nd
+            k += 1
+    off[len(progs)] = k
+    sh = abi.u64_array(shards)
+    orc.set_workers(1)
+    want = [orc.count(p, shards) for p in progs]
+    for workers in (1, 3, 8):
+        orc.set_workers(workers)
+        for fused in (False, True):
+            for _ in range(3):
+                got = orc.count_batch_raw(flat, off, len(progs), sh, len(shards), fused)
+                assert list(got[: len(progs)]) == want
+        assert [orc.count(p, shards, True) for p in progs[:4]] == want[:4]
