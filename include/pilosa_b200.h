@@ -17,7 +17,8 @@
  *    fragment.go:394-431).
  *  - a context is bound to ONE CUDA device. Calls on the same context are serialised
  *    by an internal mutex (the reference serialises per fragment, fragment.go:601);
- *    use one context per GPU and batch entry points for throughput.
+ *    use one context per GPU and batch entry points for throughput. pb200_multi (below)
+ *    puts the GPUs of a box behind one handle: partition, fan-out and reduce inside the call.
  *  - there is NO CPU fallback: if no CUDA device is usable pb200_init fails with
  *    PB200_ERR_CUDA and nothing else can be called.
  */
@@ -122,6 +123,7 @@ int pb200_shutdown(pb200_ctx* ctx);
 const char* pb200_strerror(int status);
 const char* pb200_last_error(pb200_ctx* ctx);
 int pb200_abi_version(void);
+int pb200_device_count(void);   /* usable CUDA devices (0 when there is none: nothing else can then be called) */
 
 /* Run the engine's kernels on a caller-owned CUDA stream (a cudaStream_t passed as void*,
  * e.g. torch.cuda.current_stream().cuda_stream). NULL restores the context's own stream. */
@@ -433,6 +435,95 @@ int pb200_bsi_minmax_shards(pb200_ctx* ctx, pb200_family bsi_family, uint32_t bi
                             const pb200_node* filter_prog, uint32_t n_filter_nodes, int is_max,
                             const uint64_t* shards, uint32_t n_shards,
                             int64_t* out_vals, uint64_t* out_counts);
+
+/* ---- several GPUs of one box behind one handle --------------------------------------------
+ * The reference does its fan-out and reduce inside ONE call: executor.mapReduce / mapper / mapperLocal
+ * (executor.go:2458-2611) push per-shard jobs to the worker pool (:83-107) and fold the partial results
+ * with the call's reduce function (uint64 + :1813; ValCount.add / smaller / larger :3002-3029; Pairs.Add
+ * cache.go:356-374; Row.Merge executor.go:595-602). pb200_multi is that call over the GPUs of a box:
+ * one context per device inside ONE process, shard s resident on devices[s % ndev] (every family of a
+ * shard on the same device), and every entry point below takes the caller's WHOLE shard list, runs on the
+ * owning devices concurrently and returns the reduced answer — a Go host binds these and needs neither
+ * NCCL nor a partition of its own. Semantics are those of the single-device entry point of the same name.
+ *   - all-to-all peer access (NVLink) is enabled at init. Every device's fragment table lists all shards,
+ *     remote entries pointing into the owner's HBM, so a Count whose operands are small (estimated below
+ *     PB200_OPT_SMALL_CALL_BYTES, default 24 MiB) is run by ONE device over its peers' memory — one
+ *     launch, no fan-out latency; anything larger runs on the owners.
+ *   - bitmap-returning calls (pb200_multi_eval_shards / _eval_proto_columns) are evaluated by the owners;
+ *     the first device gathers their dense result rows over NVLink, types / serialises them once for the
+ *     whole shard list and ONE device -> host copy carries the bytes (identical to one device's output).
+ *     They need peer access (PB200_ERR_UNSUPPORTED otherwise; pb200_multi_peer_access tells).
+ *   - TopN runs pass 1 on every owner, merges (Pairs.Add), runs pass 2 for the merged candidate ids from
+ *     the counts pass 1 left behind, then sorts and trims: executeTopN (executor.go:863-903) as a whole.
+ *   - writes (load / apply / import / drop / rank_set) go through the handle too: they wait for queries on
+ *     EVERY device before a fragment's previous copy is released and keep the peers' tables current. Do
+ *     not call the single-device write entry points on the contexts pb200_multi_ctx returns.
+ *   - multi calls on one handle are serialised; the handle may be used from any thread. */
+typedef struct pb200_multi pb200_multi;
+int pb200_init_multi(const int* devices, int ndev, size_t hbm_budget_bytes_per_device, pb200_multi** out);
+int pb200_multi_shutdown(pb200_multi* m);
+const char* pb200_multi_last_error(pb200_multi* m);
+int pb200_multi_ndev(pb200_multi* m);
+int pb200_multi_peer_access(pb200_multi* m);                      /* 1 when all-to-all peer access is on */
+int pb200_multi_ctx(pb200_multi* m, int i, pb200_ctx** out);      /* the i-th device's context (statistics, pb200_last_timing) */
+int pb200_multi_last_timing(pb200_multi* m, pb200_timing* out);   /* kernel_ms = max over devices, bytes / launches summed */
+/* pb200_set_option on every device; PB200_OPT_SMALL_CALL_BYTES is the routing threshold above. */
+#define PB200_OPT_SMALL_CALL_BYTES 100u
+int pb200_multi_set_option(pb200_multi* m, uint32_t option, uint64_t value);
+int pb200_multi_host_register(pb200_multi* m, void* ptr, size_t len);   /* result arena of the first device's copies */
+int pb200_multi_host_unregister(pb200_multi* m, void* ptr);
+int pb200_multi_family_create(pb200_multi* m, pb200_family* out);  /* the same handle on every device */
+int pb200_multi_frag_load(pb200_multi* m, pb200_family family, uint64_t shard, const void* roaring_bytes, size_t len);
+int pb200_multi_frag_apply(pb200_multi* m, pb200_family family, uint64_t shard, const uint64_t* set_pos, size_t n_set,
+                           const uint64_t* clear_pos, size_t n_clear);
+int pb200_multi_frag_import_roaring(pb200_multi* m, pb200_family family, uint64_t shard, const void* data, size_t len,
+                                    int clear, int64_t* changed);
+int pb200_multi_frag_drop(pb200_multi* m, pb200_family family, uint64_t shard);
+int pb200_multi_rank_set(pb200_multi* m, pb200_family family, uint64_t shard, const uint64_t* row_ids,
+                         const uint64_t* counts, size_t n);
+int pb200_multi_rank_get(pb200_multi* m, pb200_family family, uint64_t shard, uint64_t* row_ids, uint64_t* counts,
+                         size_t cap, size_t* n);
+int pb200_multi_frag_stat(pb200_multi* m, pb200_family family, uint64_t shard, uint64_t* n_rows, uint64_t* n_containers,
+                          uint64_t* payload_bytes);
+int pb200_multi_count(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards,
+                      uint32_t n_shards, uint64_t* out_count);
+int pb200_multi_count_batch(pb200_multi* m, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries,
+                            const uint64_t* shards, uint32_t n_shards, uint64_t* out_counts);
+int pb200_multi_count_shards(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards,
+                             uint32_t n_shards, uint64_t* out_per_shard);
+int pb200_multi_eval(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, void* out, size_t cap,
+                     size_t* out_len);
+int pb200_multi_eval_columns(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, uint64_t shard,
+                             uint64_t* out_cols, size_t cap, size_t* out_n);
+int pb200_multi_eval_shards(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards,
+                            uint32_t n_shards, void* out, size_t cap, uint64_t* out_off, size_t* out_len);
+int pb200_multi_eval_proto_columns(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards,
+                                   uint32_t n_shards, void* out, size_t cap, size_t* out_len);
+int pb200_multi_rows(pb200_multi* m, pb200_family family, uint64_t start, uint32_t flags, uint64_t column,
+                     uint64_t limit, const uint64_t* shards, uint32_t n_shards, uint64_t* out_rows, size_t cap,
+                     size_t* n_out);
+int pb200_multi_groupby(pb200_multi* m, const pb200_groupby_child* children, uint32_t n_children,
+                        const pb200_node* filter_prog, uint32_t n_filter_nodes, uint64_t limit,
+                        const uint64_t* shards, uint32_t n_shards, pb200_group* out, size_t cap, size_t* n_out);
+int pb200_multi_topn(pb200_multi* m, pb200_family family, const pb200_node* src_prog, uint32_t n_src_nodes,
+                     uint32_t n, const uint64_t* ids, size_t n_ids, uint64_t min_threshold,
+                     uint64_t tanimoto_threshold, uint32_t flags, const uint64_t* shards, uint32_t n_shards,
+                     pb200_pair* out, size_t cap, size_t* n_out);
+int pb200_multi_topn_shard(pb200_multi* m, pb200_family family, const pb200_node* src_prog, uint32_t n_src_nodes,
+                           uint32_t n, const uint64_t* ids, size_t n_ids, uint64_t min_threshold,
+                           uint64_t tanimoto_threshold, uint64_t shard, pb200_pair* out, size_t cap, size_t* n_out);
+int pb200_multi_bsi_sum(pb200_multi* m, pb200_family bsi_family, uint32_t bit_depth, const pb200_node* filter_prog,
+                        uint32_t n_filter_nodes, uint32_t flags, const uint64_t* shards, uint32_t n_shards,
+                        int64_t* out_sum, uint64_t* out_count);
+int pb200_multi_bsi_min(pb200_multi* m, pb200_family bsi_family, uint32_t bit_depth, const pb200_node* filter_prog,
+                        uint32_t n_filter_nodes, const uint64_t* shards, uint32_t n_shards, int64_t* out_val,
+                        uint64_t* out_count);
+int pb200_multi_bsi_max(pb200_multi* m, pb200_family bsi_family, uint32_t bit_depth, const pb200_node* filter_prog,
+                        uint32_t n_filter_nodes, const uint64_t* shards, uint32_t n_shards, int64_t* out_val,
+                        uint64_t* out_count);
+int pb200_multi_bsi_minmax_shards(pb200_multi* m, pb200_family bsi_family, uint32_t bit_depth,
+                                  const pb200_node* filter_prog, uint32_t n_filter_nodes, int is_max,
+                                  const uint64_t* shards, uint32_t n_shards, int64_t* out_vals, uint64_t* out_counts);
 
 /* Timing / byte accounting of the last query call on this context. */
 int pb200_last_timing(pb200_ctx* ctx, pb200_timing* out);

@@ -10,6 +10,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <atomic>
+#include <condition_variable>
+#include <memory>
 #include <thread>
 
 #include "kernels.cuh"
@@ -85,6 +87,12 @@ struct DeviceGuard {  // make ctx->device current for the duration of a call
 // lifecycle
 // ---------------------------------------------------------------------------------------
 extern "C" int pb200_abi_version(void) { return PB200_ABI_VERSION; }
+
+extern "C" int pb200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
 
 extern "C" const char* pb200_strerror(int status) {
   switch (status) {
@@ -318,6 +326,7 @@ static int upload_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const st
   // then let go of the old one — a failure before that leaves the old fragment fully in place.
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   CUDA_TRY(ctx, cudaMemcpy(fam.d_frags + shard, &nf.dev, sizeof(FragDev), cudaMemcpyHostToDevice));
+  if (ctx->publish) TRY(ctx->publish(uint32_t(&fam - ctx->families.data()), shard, nf.dev, nf.all_bitmap, true));
   guard.p = nullptr;
   auto it = fam.frags.find(shard);
   if (it != fam.frags.end()) {
@@ -538,6 +547,7 @@ extern "C" int pb200_frag_drop(pb200_ctx* ctx, pb200_family family, uint64_t sha
   FragDev empty{};
   fam.h_frags[shard] = empty;
   CUDA_TRY(ctx, cudaMemcpy(fam.d_frags + shard, &empty, sizeof(FragDev), cudaMemcpyHostToDevice));
+  if (ctx->publish) TRY(ctx->publish(family, shard, empty, true, false));
   if (!it->second.all_bitmap) fam.n_not_all_bitmap--;
   ctx->used -= it->second.blob_bytes;
   free_fragment(it->second);
@@ -1306,3 +1316,5 @@ extern "C" int pb200_count_pairs_noalloc(pb200_ctx* ctx, pb200_family family, co
   CUDA_TRY(ctx, cudaGetLastError());
   return PB200_OK;
 }
+
+#include "engine_multi.inl"

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <functional>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -54,7 +55,8 @@ struct Family {
   std::vector<FragDev> h_frags;  // indexed by shard
   FragDev* d_frags = nullptr;
   uint32_t cap = 0;
-  uint64_t n_not_all_bitmap = 0;  // fragments holding array/run containers
+  uint64_t n_not_all_bitmap = 0;  // fragments holding array/run containers (local ones and, in a pb200_multi, the peers')
+  std::vector<uint8_t> remote_flags;  // pb200_multi: per shard, bit 0 = the entry points into a peer's HBM, bit 1 = not all bitmap
 };
 
 // A compiled batch of programs, ready for upload.
@@ -103,6 +105,9 @@ struct pb200_ctx {
   pb200::FamilyDev* d_families = nullptr;
   uint32_t d_families_cap = 0;
   bool families_dirty = true;
+  // pb200_multi: called with every new / dropped fragment-table entry of this device, before the previous copy of the
+  // fragment is freed, so that the peers' tables follow and no peer still reads the old copy
+  std::function<int(uint32_t family, uint64_t shard, const pb200::FragDev& dev, bool all_bitmap, bool present)> publish;
   uint64_t generation = 0;  // bumped by every load / write / drop / table growth: prepared batches re-validate against it
   pb200::DevBuf d_slow_descs, d_ovf;
   pb200::DevBuf d_rows, d_rows_off, d_rows_meta, d_rows_item_off;  // K11: serialised result rows (kernels_rows.cuh)

@@ -176,9 +176,8 @@ namespace {
 // K11: evaluate one program over the shards and serialise every shard's row on the device
 // (kernels_rows.cuh). Leaves ctx->d_rows (packed streams) and ctx->d_rows_off
 // ([n_shards + 1] u64 stream offsets) filled, in stream order.
-int eval_rows_device(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards) {
-  BatchDev bd{};
-  TRY(eval_dense(ctx, prog, n_nodes, shards, n_shards, bd));
+// Serialises the dense rows currently in ctx->d_dense / d_dense_n (n_shards rows, shard numbers at `shards_dev`).
+int emit_rows_from_dense(pb200_ctx* ctx, const uint64_t* shards_dev, uint32_t n_shards) {
   const uint32_t items = n_shards * kRowContainers;
   TRY(ensure_dev(ctx, ctx->d_rows_meta, size_t(items) * 4));
   TRY(ensure_dev(ctx, ctx->d_rows_item_off, size_t(items) * 8));
@@ -190,7 +189,7 @@ int eval_rows_device(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, c
   uint32_t* meta = static_cast<uint32_t*>(ctx->d_rows_meta.p);
   unsigned long long* item_off = static_cast<unsigned long long*>(ctx->d_rows_item_off.p);
   rows_classify_kernel<<<std::min<uint32_t>((items + 7) / 8, uint32_t(ctx->sm_count) * 8), 256, 0, ctx->stream>>>(dense, dense_n, items, meta);
-  rows_layout_kernel<<<1, 1024, 0, ctx->stream>>>(meta, dense_n, bd.shards, ctx->dense_has_ovf ? ctx->dense_ovf_dev : nullptr, n_shards,
+  rows_layout_kernel<<<1, 1024, 0, ctx->stream>>>(meta, dense_n, shards_dev, ctx->dense_has_ovf ? ctx->dense_ovf_dev : nullptr, n_shards,
                                                   static_cast<uint8_t*>(ctx->d_rows.p), static_cast<unsigned long long*>(ctx->d_rows_off.p), item_off);
   rows_emit_kernel<<<std::min<uint32_t>(items, uint32_t(ctx->sm_count) * 8), kRowsEmitThreads, 0, ctx->stream>>>(dense, meta, item_off, items,
                                                                                                             static_cast<uint8_t*>(ctx->d_rows.p));
@@ -199,18 +198,14 @@ int eval_rows_device(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, c
   return PB200_OK;
 }
 
-int eval_shards_impl(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards,
-                     void* out, size_t cap, uint64_t* out_off, size_t* out_len) {
-  if (!out_len) return PB200_ERR_INVALID;
-  TRY(validate_shards(ctx, shards, n_shards));
-  *out_len = 0;
-  if (n_shards == 0) { if (out_off) out_off[0] = 0; return PB200_OK; }
-  if (n_shards > (1u << 24)) return fail(ctx, PB200_ERR_RANGE, "too many shards in one call");
-  TRY(ensure_dev(ctx, ctx->d_misc, 64));
-  timing_begin(ctx);
-  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-  TRY(eval_rows_device(ctx, prog, n_nodes, shards, n_shards));
-  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+int eval_rows_device(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards) {
+  BatchDev bd{};
+  TRY(eval_dense(ctx, prog, n_nodes, shards, n_shards, bd));
+  return emit_rows_from_dense(ctx, bd.shards, n_shards);
+}
+
+// Second half of pb200_eval_shards: offsets, then the packed streams, device -> host.
+int fetch_rows(pb200_ctx* ctx, uint32_t n_shards, void* out, size_t cap, uint64_t* out_off, size_t* out_len) {
   std::vector<uint64_t> local_off;
   uint64_t* off = out_off;
   if (!off) { local_off.resize(size_t(n_shards) + 1); off = local_off.data(); }
@@ -227,6 +222,21 @@ int eval_shards_impl(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, c
   return finish_call(ctx);
 }
 
+int eval_shards_impl(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards,
+                     void* out, size_t cap, uint64_t* out_off, size_t* out_len) {
+  if (!out_len) return PB200_ERR_INVALID;
+  TRY(validate_shards(ctx, shards, n_shards));
+  *out_len = 0;
+  if (n_shards == 0) { if (out_off) out_off[0] = 0; return PB200_OK; }
+  if (n_shards > (1u << 24)) return fail(ctx, PB200_ERR_RANGE, "too many shards in one call");
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  timing_begin(ctx);
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  TRY(eval_rows_device(ctx, prog, n_nodes, shards, n_shards));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  return fetch_rows(ctx, n_shards, out, cap, out_off, out_len);
+}
+
 }  // namespace
 
 extern "C" int pb200_eval(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, void* out, size_t cap, size_t* out_len) {
@@ -240,19 +250,11 @@ extern "C" int pb200_eval_shards(pb200_ctx* ctx, const pb200_node* prog, uint32_
   return eval_shards_impl(ctx, prog, n_nodes, shards, n_shards, out, cap, out_off, out_len);
 }
 
-extern "C" int pb200_eval_proto_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards,
-                                        void* out, size_t cap, size_t* out_len) {
-  ENTER(ctx);
-  if (!out_len) return PB200_ERR_INVALID;
-  TRY(validate_shards(ctx, shards, n_shards));
-  *out_len = 0;
-  if (n_shards == 0) return PB200_OK;
-  if (n_shards > (1u << 24)) return fail(ctx, PB200_ERR_RANGE, "too many shards in one call");
-  TRY(ensure_dev(ctx, ctx->d_misc, 64));
-  timing_begin(ctx);
-  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-  BatchDev bd{};
-  TRY(eval_dense(ctx, prog, n_nodes, shards, n_shards, bd));
+namespace {
+
+// K12 over the dense rows currently in ctx->d_dense / d_dense_n: size, lay out and (when `out` is given) emit the
+// Columns field; the caller has recorded ev0.
+int emit_proto_from_dense(pb200_ctx* ctx, const uint64_t* shards_dev, uint32_t n_shards, void* out, size_t cap, size_t* out_len) {
   const uint32_t n_slots = n_shards * kProtoSlots;
   TRY(ensure_dev(ctx, ctx->d_rows_meta, size_t(n_slots) * 4));
   TRY(ensure_dev(ctx, ctx->d_rows_item_off, size_t(n_slots) * 8));
@@ -262,7 +264,7 @@ extern "C" int pb200_eval_proto_columns(pb200_ctx* ctx, const pb200_node* prog, 
   uint32_t* sizes = static_cast<uint32_t*>(ctx->d_rows_meta.p);
   unsigned long long* slot_off = static_cast<unsigned long long*>(ctx->d_rows_item_off.p);
   unsigned long long* totals = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 16);
-  proto_size_kernel<<<std::min<uint32_t>((n_slots + 7) / 8, uint32_t(ctx->sm_count) * 8), kProtoThreads, 0, ctx->stream>>>(dense, dense_n, bd.shards, ovf,
+  proto_size_kernel<<<std::min<uint32_t>((n_slots + 7) / 8, uint32_t(ctx->sm_count) * 8), kProtoThreads, 0, ctx->stream>>>(dense, dense_n, shards_dev, ovf,
                                                                                                                    n_shards, sizes);
   proto_layout_kernel<<<1, 1024, 0, ctx->stream>>>(sizes, n_slots, slot_off, totals);
   ctx->timing.launches += 2;
@@ -278,13 +280,31 @@ extern "C" int pb200_eval_proto_columns(pb200_ctx* ctx, const pb200_node* prog, 
   if (cap < total) { finish_call(ctx); return fail(ctx, PB200_ERR_RANGE, "output buffer too small"); }
   TRY(ensure_dev(ctx, ctx->d_rows, total));
   proto_emit_kernel<<<std::min<uint32_t>(n_slots, uint32_t(ctx->sm_count) * 8), kProtoThreads, 0, ctx->stream>>>(
-      dense, sizes, slot_off, totals, bd.shards, ovf, n_shards, static_cast<uint8_t*>(ctx->d_rows.p));
+      dense, sizes, slot_off, totals, shards_dev, ovf, n_shards, static_cast<uint8_t*>(ctx->d_rows.p));
   ctx->timing.launches += 1;
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(out, ctx->d_rows.p, total, cudaMemcpyDeviceToHost, ctx->stream));
   ctx->timing.d2h_bytes += total;
   return finish_call(ctx);
+}
+
+}  // namespace
+
+extern "C" int pb200_eval_proto_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards,
+                                        void* out, size_t cap, size_t* out_len) {
+  ENTER(ctx);
+  if (!out_len) return PB200_ERR_INVALID;
+  TRY(validate_shards(ctx, shards, n_shards));
+  *out_len = 0;
+  if (n_shards == 0) return PB200_OK;
+  if (n_shards > (1u << 24)) return fail(ctx, PB200_ERR_RANGE, "too many shards in one call");
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  timing_begin(ctx);
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  BatchDev bd{};
+  TRY(eval_dense(ctx, prog, n_nodes, shards, n_shards, bd));
+  return emit_proto_from_dense(ctx, bd.shards, n_shards, out, cap, out_len);
 }
 
 extern "C" int pb200_eval_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, uint64_t* out_cols, size_t cap, size_t* out_n) {

@@ -56,6 +56,7 @@ def load_library() -> C.CDLL:
         "pb200_strerror": (C.c_char_p, [i32]),
         "pb200_last_error": (C.c_char_p, [vp]),
         "pb200_abi_version": (i32, []),
+        "pb200_device_count": (i32, []),
         "pb200_set_stream": (i32, [vp, vp]),
         "pb200_family_create": (i32, [vp, u32p]),
         "pb200_frag_load": (i32, [vp, u32, u64, C.c_char_p, sz]),
@@ -95,11 +96,51 @@ def load_library() -> C.CDLL:
         "pb200_bsi_minmax_shards": (i32, [vp, u32, u32, np_, u32, i32, u64p, u32, i64p, u64p]),
         "pb200_last_timing": (i32, [vp, C.POINTER(Timing)]),
     }
+    # pb200_multi_*: the same argument lists behind the multi-GPU handle
+    for name in MULTI_FORWARDED:
+        sig["pb200_multi_" + name] = sig["pb200_" + name]
+    sig["pb200_init_multi"] = (i32, [C.POINTER(i32), i32, sz, C.POINTER(vp)])
+    sig["pb200_multi_shutdown"] = (i32, [vp])
+    sig["pb200_multi_last_error"] = (C.c_char_p, [vp])
+    sig["pb200_multi_ndev"] = (i32, [vp])
+    sig["pb200_multi_peer_access"] = (i32, [vp])
+    sig["pb200_multi_ctx"] = (i32, [vp, i32, C.POINTER(vp)])
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
         fn.restype, fn.argtypes = res, args
     _lib = L
     return L
+
+
+# single-device entry points that exist, with the same arguments, as pb200_multi_<name>
+MULTI_FORWARDED = [
+    "family_create", "frag_load", "frag_apply", "frag_import_roaring", "frag_drop", "rank_set", "rank_get", "frag_stat",
+    "count", "count_batch", "count_shards", "eval", "eval_columns", "eval_shards", "eval_proto_columns", "rows", "groupby",
+    "topn", "topn_shard", "bsi_sum", "bsi_min", "bsi_max", "bsi_minmax_shards", "last_timing", "set_option",
+    "host_register", "host_unregister",
+]
+
+
+class _MultiLib:
+    """Presents pb200_multi_<name> under the name pb200_<name>, so that Engine's methods drive the multi-GPU handle."""
+
+    def __init__(self, lib):
+        self._lib = lib
+
+    def __getattr__(self, name):
+        if name in ("pb200_strerror", "pb200_abi_version", "pb200_host_check_roaring"):
+            return getattr(self._lib, name)
+        if name == "pb200_last_error":
+            return self._lib.pb200_multi_last_error
+        if name == "pb200_shutdown":
+            return self._lib.pb200_multi_shutdown
+        if name.startswith("pb200_") and name[6:] in MULTI_FORWARDED:
+            return getattr(self._lib, "pb200_multi_" + name[6:])
+        raise AttributeError(f"{name} has no multi-GPU form")
+
+
+def device_count() -> int:
+    return int(load_library().pb200_device_count())
 
 
 def host_check_roaring(data: bytes) -> Tuple[int, int]:
@@ -433,4 +474,35 @@ class Engine:
     def last_timing(self) -> Timing:
         t = Timing()
         self._check(self.lib.pb200_last_timing(self._h, C.byref(t)))
+        return t
+
+
+class MultiEngine(Engine):
+    """pb200_multi: the GPUs of one box behind one handle (one process). Same methods as Engine; every query takes the
+    whole shard list — partition (shard % ndev), fan-out and reduce happen inside the library call."""
+
+    OPT_SMALL_CALL_BYTES = 100
+
+    def __init__(self, devices: Sequence[int], hbm_budget_bytes_per_device: int = 0):
+        raw = load_library()
+        self.lib = _MultiLib(raw)
+        self._raw = raw
+        h = C.c_void_p()
+        arr = (C.c_int * len(devices))(*devices)
+        rc = raw.pb200_init_multi(arr, len(devices), hbm_budget_bytes_per_device, C.byref(h))
+        if rc != 0:
+            raise EngineError(rc, f"pb200_init_multi(devices={list(devices)}) failed: {raw.pb200_strerror(rc).decode()} "
+                                  "(CUDA devices are required; there is no CPU fallback)")
+        self._h = h
+        self._rows_buf = None
+        self.devices = list(devices)
+
+    @property
+    def peer_access(self) -> bool:
+        return bool(self._raw.pb200_multi_peer_access(self._h))
+
+    def device_timing(self, i: int) -> Timing:
+        c, t = C.c_void_p(), Timing()
+        self._check(self._raw.pb200_multi_ctx(self._h, i, C.byref(c)))
+        self._raw.pb200_last_timing(c, C.byref(t))
         return t

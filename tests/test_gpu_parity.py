@@ -12,12 +12,19 @@ from pilosa_b200.executor import Executor
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def pair():
-    """Engine + oracle executors over the same small synthetic index (C1/C2/C3/C4/C5 shapes)."""
-    from pilosa_b200.engine import Engine
+@pytest.fixture(scope="module", params=["single", "multi", "multi-fanout"])
+def pair(request):
+    """Engine + oracle executors over the same small synthetic index (C1/C2/C3/C4/C5 shapes). The whole module runs
+    three times: on one context, and through the pb200_multi handle over every visible GPU — once with its router
+    (these small calls then run on ONE device over the peers' HBM) and once forced onto the shards' owners."""
+    from pilosa_b200.engine import Engine, MultiEngine, device_count
 
-    eng = Engine(0)
+    if request.param == "single":
+        eng = Engine(0)
+    else:
+        eng = MultiEngine(list(range(device_count())))
+        if request.param == "multi-fanout":
+            eng.set_option(MultiEngine.OPT_SMALL_CALL_BYTES, 0)
     orc = oracle.Oracle(workers=8)
     g, c = Executor(eng), Executor(orc)
     shards = [0, 1, 2, 5]  # shard 3/4 absent on purpose (missing fragments)
