@@ -1,33 +1,33 @@
 #!/usr/bin/env python
-"""bench_configs_dist.py — BASELINE.json configs C2..C5 with the shards partitioned over N GPUs of one box.
+"""bench_configs_dist.py — BASELINE.json configs C2..C5 over N GPUs of one box, through the C ABI only.
 
-    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench_configs_dist.py
+    python bench_configs_dist.py --gpus N          (ONE process; N = 1, 2, 4, 8)
 
-Shard s lives on rank s % N; every query goes through pilosa_b200.executor.Executor, i.e. one
-C-ABI call per rank plus the NCCL merge of the partials (sum all-reduce for Count / Sum, gathers for Min / Max /
-TopN). Per query rank 0 prints one JSON line: wall ms of the whole distributed call (median of the per-call
-maximum over ranks), the local kernel ms of rank 0, and the RESULT, so that runs at different N (N = 1 included:
-plain `python bench_configs_dist.py`) can be compared for equality — the full-size parity check across GPU counts.
+Every query is ONE call on the pb200_multi handle (include/pilosa_b200.h): the library partitions the caller's shard
+list (shard s on device s % N), runs the owners concurrently — or, for a small call, one device over its peers' HBM —
+and returns the reduced answer, which is what executor.mapReduce does in the reference (executor.go:2458-2611). No
+torch.distributed, no NCCL and no Python merge is involved. Per query one JSON line: wall ms of the call (median),
+the slowest device's kernel ms, and the RESULT, so that runs at different N can be compared for equality — the
+full-size parity check across GPU counts.
 """
 from __future__ import annotations
 
 import argparse
+import ctypes as C
 import json
 import os
 import statistics
 import sys
 import time
+import zlib
 from concurrent.futures import ThreadPoolExecutor
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-import torch  # noqa: E402
-import torch.distributed as dist  # noqa: E402
-
 from pilosa_b200 import abi, synth  # noqa: E402
 from pilosa_b200.abi import Difference, Intersect, Row, Union, Xor  # noqa: E402
-from pilosa_b200.engine import Engine  # noqa: E402
+from pilosa_b200.engine import MultiEngine, device_count  # noqa: E402
 from pilosa_b200.executor import Executor  # noqa: E402
 
 SEED = 20190416
@@ -35,48 +35,51 @@ SEED = 20190416
 
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=0, help="devices 0..N-1 (default: all visible)")
     ap.add_argument("--configs", default="c2,c3,c4,c5")
-    ap.add_argument("--reps", type=int, default=7)
+    ap.add_argument("--reps", type=int, default=9)
     ap.add_argument("--c2-shards", type=int, default=1024)
     ap.add_argument("--c3-shards", type=int, default=1024)
     ap.add_argument("--c3-rows", type=int, default=10000)
     ap.add_argument("--c4-shards", type=int, default=2048)
     ap.add_argument("--c5-shards", type=int, default=8192)
     args = ap.parse_args()
-    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    eng = Engine(local)
-    g = Executor(eng, rank=rank, world=world)
-    cores = max(1, (os.cpu_count() or 8) // world)
+    n = args.gpus or device_count()
+    eng = MultiEngine(list(range(n)))
+    g = Executor(eng)
+    cores = max(1, min(16, os.cpu_count() or 8))
     cfgs = args.configs.split(",")
 
     def load(field, gen, shards):
-        mine = [s for s in shards if s % world == rank]
         with ThreadPoolExecutor(max_workers=cores) as tp:
-            for s, fb in zip(mine, tp.map(gen, mine)):
+            for s, fb in zip(shards, tp.map(gen, shards)):
                 g.load_fragment(field, s, fb)
 
-    def run(config, name, fn, shards, reps=None):
+    def run(config, name, fn, shards, reps=None, show=lambda r: r):
         reps = reps or args.reps
         fn(); fn()
         walls, kern = [], []
         for _ in range(reps):
-            if world > 1:
-                dist.barrier()
             t0 = time.perf_counter()
             res = fn()
-            w = (time.perf_counter() - t0) * 1e3
-            if world > 1:
-                t = torch.tensor([w], dtype=torch.float64, device="cuda")
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                w = float(t.item())
-            walls.append(w)
+            walls.append((time.perf_counter() - t0) * 1e3)
             kern.append(eng.last_timing().kernel_ms)
-        if rank == 0:
-            print(json.dumps({"config": config, "query": name, "n_gpus": world, "shards": len(shards), "call_ms_max_over_ranks": round(statistics.median(walls), 4),
-                              "kernel_ms_rank0": round(statistics.median(kern), 4), "result": res}), flush=True)
+        print(json.dumps({"config": config, "query": name, "n_gpus": n, "shards": len(shards), "call_ms": round(statistics.median(walls), 4),
+                          "call_ms_min": round(min(walls), 4), "kernel_ms_slowest_device": round(statistics.median(kern), 4), "result": show(res)}), flush=True)
+
+    def counter(call, shards):
+        """One raw pb200_multi_count call with everything marshalled beforehand."""
+        prog = g.program(call)
+        sh = abi.u64_array(shards)
+        out = C.c_uint64()
+        lib, h, np_, ns = eng.lib.pb200_count, eng._h, len(prog), len(shards)
+
+        def fn():
+            rc = lib(h, prog, np_, sh, ns, C.byref(out))
+            if rc:
+                eng._check(rc)
+            return out.value
+        return fn
 
     if "c2" in cfgs:
         shards = tuple(range(args.c2_shards))
@@ -85,7 +88,7 @@ def main():
         leaves = [Row("m", r) for r in range(4)]
         for qname, call in (("Count(Union(r0..r3))", Union(*leaves)), ("Count(Difference(r0,r1,r2,r3))", Difference(*leaves)),
                             ("Count(Xor(r0..r3))", Xor(*leaves))):
-            run("C2", qname, lambda: g.count(call, shards), shards)
+            run("C2", qname, counter(call, shards), shards)
     if "c3" in cfgs:
         shards = tuple(range(args.c3_shards))
         g.create_field("z")
@@ -105,19 +108,21 @@ def main():
         run("C4", "Min(field=v)", lambda: g.min("v", shards), shards)
         run("C4", "Max(field=v)", lambda: g.max("v", shards), shards)
         for x in (0, 12345):
-            run("C4", f"Count(Row(v > {x}))", lambda x=x: g.count(g.row_range("v", abi.BSI_GT, x), shards), shards)
+            run("C4", f"Count(Row(v > {x}))", counter(g.row_range("v", abi.BSI_GT, x), shards), shards)
     if "c5" in cfgs:
         shards = tuple(range(args.c5_shards))
         g.create_field("sp")
         load("sp", lambda s: synth.bernoulli(s, 1, 2, 1e-4, SEED), shards)
         call = Intersect(Row("sp", 1), Row("sp", 2))
-        for n in (64, 512, args.c5_shards):
-            sh = shards[:n]
-            run("C5", f"Count(Intersect(Row(sp=1),Row(sp=2))) p=1e-4, {n} shards", lambda: g.count(call, sh), sh)
-            run("C5", f"batch of 256 x same query, {n} shards (whole batch)", lambda: g.count_batch([call] * 256, sh)[:2], sh)
+        sizes = sorted({k for k in (64, 512, args.c5_shards) if k <= args.c5_shards})
+        for k in sizes:
+            sh = shards[:k]
+            run("C5", f"Count(Intersect(Row(sp=1),Row(sp=2))) p=1e-4, {k} shards", counter(call, sh), sh)
+            run("C5", f"batch of 256 x same query, {k} shards (whole batch)", lambda: g.count_batch([call] * 256, sh)[:2], sh)
+        # a materialised sparse row over all shards: owners evaluate, the first device gathers and emits the protobuf Columns field
+        run("C5", f"Row(sp=1) as protobuf Columns, {len(shards)} shards", lambda: g.row_proto_columns(Row("sp", 1), shards), shards, 3,
+            show=lambda b: {"bytes": len(b), "crc32": zlib.crc32(b)})
     eng.close()
-    if world > 1:
-        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

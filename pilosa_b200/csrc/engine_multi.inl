@@ -81,7 +81,8 @@ struct pb200_multi {
   std::string err;
   bool peer = false;                                // all-to-all peer access is on
   uint32_t rr = 0;                                  // next device for a single-device call
-  uint64_t small_call_bytes = 24ull << 20;          // estimated operand bytes below which one device runs the whole call
+  uint64_t small_call_bytes = 24ull << 20;          // estimated operand bytes below which one device runs the whole call ...
+  uint32_t small_call_shards = 1024;                // ... provided it names no more shards than this
   std::vector<FamStat> fam;
   pb200_timing timing{};
   DevBuf g_dense, g_dense_n, g_ovf, g_shards, g_pos;  // on ctx[0]'s device: gathered result rows of a bitmap-returning call
@@ -201,7 +202,10 @@ uint64_t estimate_bytes(const pb200_multi* m, const pb200_node* progs, uint32_t 
 int route_count(pb200_multi* m, const pb200_node* progs, uint32_t n_nodes, uint32_t n_shards) {
   if (m->ctx.size() == 1) return 0;
   if (!m->peer) return -1;
-  if (estimate_bytes(m, progs, n_nodes, n_shards) >= m->small_call_bytes) return -1;
+  // Remote reads pay NVLink latency per dependent load (shard -> fragment -> row table -> payload), so what one device
+  // can cover over its peers is bounded by the NUMBER of shards as well as by the bytes: measured on 2 GPUs, a sparse
+  // two-row Count over 512 shards costs the same either way, over 8192 shards the owners are twice as fast.
+  if (n_shards > m->small_call_shards || estimate_bytes(m, progs, n_nodes, n_shards) >= m->small_call_bytes) return -1;
   return int(m->rr++ % m->ctx.size());
 }
 
