@@ -133,6 +133,17 @@ extern "C" int pb200_init(int device, size_t hbm_budget_bytes, pb200_ctx** out) 
   return PB200_OK;
 }
 
+static void arena_detach(pb200_ctx* ctx, Fragment& f) {  // the fragment stops referencing the write arena
+  if (!f.in_arena) return;
+  f.in_arena = false;
+  WriteArena& a = ctx->arena;
+  if (a.live_frags && --a.live_frags == 0) {  // nothing points into it any more: reclaim (retired chunks freed, current one reused)
+    for (auto& r : a.retired) { cudaFree(r.first); ctx->used -= std::min(ctx->used, r.second); }
+    a.retired.clear();
+    a.top = 0;
+  }
+}
+
 static void free_fragment(Fragment& f) {
   if (f.blob) cudaFree(f.blob);
   if (f.d_rank) cudaFree(f.d_rank);
@@ -153,9 +164,12 @@ extern "C" int pb200_shutdown(pb200_ctx* ctx) {
       if (fam.d_frags) cudaFree(fam.d_frags);
     }
     if (ctx->d_families) cudaFree(ctx->d_families);
-    for (DevBuf* b : {&ctx->d_rows, &ctx->d_rows_off, &ctx->d_rows_meta, &ctx->d_rows_item_off, &ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi})
+    for (DevBuf* b : {&ctx->d_rows, &ctx->d_rows_off, &ctx->d_rows_meta, &ctx->d_rows_item_off, &ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi, &ctx->d_ing, &ctx->d_ing_res})
       if (b->p) cudaFree(b->p);
-    for (PinBuf* b : {&ctx->h_stage, &ctx->h_out, &ctx->h_algo, &ctx->h_topn})
+    for (auto& r : ctx->arena.retired) cudaFree(r.first);
+    if (ctx->arena.base) cudaFree(ctx->arena.base);
+    if (ctx->arena.d_top) cudaFree(ctx->arena.d_top);
+    for (PinBuf* b : {&ctx->h_stage, &ctx->h_out, &ctx->h_algo, &ctx->h_topn, &ctx->h_ing, &ctx->h_ing_res})
       if (b->p) cudaFreeHost(b->p);
     for (auto& sl : ctx->slots) {
       if (sl.d_batch.p) cudaFree(sl.d_batch.p);
@@ -331,11 +345,14 @@ static int upload_fragment(pb200_ctx* ctx, Family& fam, uint64_t shard, const st
   auto it = fam.frags.find(shard);
   if (it != fam.frags.end()) {
     if (!it->second.all_bitmap) fam.n_not_all_bitmap--;
+    fam.payload_total -= it->second.payload_bytes; fam.containers_total -= it->second.n_containers;
     ctx->used -= it->second.blob_bytes;
+    arena_detach(ctx, it->second);
     free_fragment(it->second);
     fam.frags.erase(it);
   }
   ctx->used += nf.blob_bytes;
+  fam.payload_total += nf.payload_bytes; fam.containers_total += nf.n_containers;
   if (!nf.all_bitmap) fam.n_not_all_bitmap++;
   fam.h_frags[shard] = nf.dev;
   fam.frags.emplace(shard, std::move(nf));
@@ -421,11 +438,10 @@ static void rank_bulk_add(Fragment& f, uint64_t id, uint64_t n) {  // rankCache.
   f.rank_state.entries[id] = n;
 }
 
-extern "C" int pb200_frag_apply(pb200_ctx* ctx, pb200_family family, uint64_t shard, const uint64_t* set_pos, size_t n_set,
-                                const uint64_t* clear_pos, size_t n_clear) {
-  ENTER(ctx);
-  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
-  if ((n_set && !set_pos) || (n_clear && !clear_pos)) return PB200_ERR_INVALID;
+// Host-merge form of a position write: only used to CREATE a fragment (the shard had none); writes to a resident
+// fragment run on the device (engine_ingest.inl).
+static int frag_apply_host(pb200_ctx* ctx, pb200_family family, uint64_t shard, const uint64_t* set_pos, size_t n_set,
+                           const uint64_t* clear_pos, size_t n_clear) {
   Family& fam = ctx->families[family];
   std::vector<uint8_t> blob;
   std::vector<HostContainer> cs;
@@ -483,16 +499,8 @@ extern "C" int pb200_host_unregister(pb200_ctx* ctx, void* ptr) {
   return PB200_OK;
 }
 
-extern "C" int pb200_frag_import_roaring(pb200_ctx* ctx, pb200_family family, uint64_t shard, const void* data, size_t len, int clear,
-                                         int64_t* changed) {
-  ENTER(ctx);
-  if (family >= ctx->families.size()) return fail(ctx, PB200_ERR_NOTFOUND, "unknown family");
-  if (!data) return fail(ctx, PB200_ERR_INVALID, "no roaring bitmap provided");  // roaring.go:1464
-  std::vector<HostContainer> other;
-  std::string err;
-  if (!parse_any(static_cast<const uint8_t*>(data), len, other, err)) return fail(ctx, PB200_ERR_FORMAT, err);
-  for (auto& c : other)
-    if ((c.key >> 4) >= (1ull << 44)) return fail(ctx, PB200_ERR_FORMAT, "container key out of range");
+// Host-merge form of an import (creates the fragment); see frag_apply_host.
+static int frag_import_host(pb200_ctx* ctx, pb200_family family, uint64_t shard, const std::vector<HostContainer>& other, int clear, int64_t* changed) {
   Family& fam = ctx->families[family];
   std::vector<uint8_t> blob;
   std::vector<HostContainer> cs;
@@ -549,7 +557,9 @@ extern "C" int pb200_frag_drop(pb200_ctx* ctx, pb200_family family, uint64_t sha
   CUDA_TRY(ctx, cudaMemcpy(fam.d_frags + shard, &empty, sizeof(FragDev), cudaMemcpyHostToDevice));
   if (ctx->publish) TRY(ctx->publish(family, shard, empty, true, false));
   if (!it->second.all_bitmap) fam.n_not_all_bitmap--;
+  fam.payload_total -= it->second.payload_bytes; fam.containers_total -= it->second.n_containers;
   ctx->used -= it->second.blob_bytes;
+  arena_detach(ctx, it->second);
   free_fragment(it->second);
   fam.frags.erase(it);
   ctx->generation++;
@@ -608,8 +618,12 @@ struct Compiler {
   int add_leaf(uint32_t kind, uint32_t family, uint64_t row) {
     Leaf lf; lf.kind = kind; lf.family = family; lf.row = row;
     out.leaves.push_back(lf);
-    if (kind == L_TEMP) out.may_need_staging = true;
-    else if (kind == L_ROW && family < ctx->families.size() && ctx->families[family].n_not_all_bitmap) out.may_need_staging = true;
+    if (kind == L_TEMP) { out.may_need_staging = true; out.leaf_payload += kBitmapBytes; out.leaf_containers += 1; }
+    else if (kind == L_ROW && family < ctx->families.size()) {
+      const Family& fam = ctx->families[family];
+      if (fam.n_not_all_bitmap) out.may_need_staging = true;
+      out.leaf_payload += fam.payload_total; out.leaf_containers += fam.containers_total;
+    }
     return int(out.leaves.size() - 1 - leaf_base);
   }
   int leaf_node(int leaf) { TNode t; t.leaf = leaf; tree.push_back(t); return int(tree.size() - 1); }
@@ -644,6 +658,8 @@ struct Compiler {
     }
     if (maxsp > kMaxStack) { err = "expression too deeply nested (stack depth > 4)"; return false; }
     if (ins.size() > size_t(kMaxInstr)) { err = "expression too long (> 64 instructions)"; return false; }
+    for (size_t k = 0; k < ins.size(); k++)
+      if ((k > 0 && ins[k].op == I_LOAD) || ins[k].op >= I_AND_STACK || ins[k].op == I_RANDNOT_LEAF) out.any_bushy = true;
     pg.instr_off = uint32_t(out.instrs.size());
     pg.n_instr = uint32_t(ins.size());
     pg.leaf_off = leaf_base;
@@ -850,17 +866,20 @@ uint32_t resident_ctas(pb200_ctx* ctx, int slot, K kernel, int block, size_t dyn
   }
   return uint32_t(ctx->sm_count) * uint32_t(ctx->occ[slot]);
 }
-enum { OCC_FAST = 0, OCC_STAGED, OCC_SUM, OCC_MM, OCC_TOPN };
+enum { OCC_FAST = 0, OCC_STAGED, OCC_SUM, OCC_MM, OCC_TOPN, OCC_FOLD };
 
 // Launches the fast + staged kernels for `n_queries` programs starting at `progs`.
 int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards, bool staging,
                 unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, uint8_t* dense_out, uint32_t* dense_n,
-                uint32_t max_leaves = kMaxLeaves) {
+                uint32_t max_leaves = kMaxLeaves, bool bushy = true, bool fold_all = false) {
   const uint64_t n_items = uint64_t(n_queries) * n_shards * kRowContainers;
   if (n_items == 0) return PB200_OK;
   if (n_items >= (1ull << 32)) return fail(ctx, PB200_ERR_RANGE, "batch too large: queries x shards x 16 must be < 2^32");
+  // Containers of a kilobyte and more on average (mixed array / bitmap / run data): nearly every item would be deferred,
+  // so the fold evaluator walks all items itself and the first pass with its deferred list is skipped.
+  fold_all = fold_all && staging;
   // scratch: slow list + counter + algo-bytes counter
-  size_t slow_bytes = staging ? size_t(n_items) * 4 : 4;
+  size_t slow_bytes = staging && !fold_all ? size_t(n_items) * 4 : 4;
   TRY(ensure_dev(ctx, ctx->d_slow, slow_bytes));
   TRY(ensure_dev(ctx, ctx->d_misc, 64));
   EvalParams p{};
@@ -876,20 +895,28 @@ int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t 
   p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + ctx->algo_off);
   // descriptors of deferred items travel from the fast to the staged kernel when they fit a modest scratch budget
   const uint64_t desc_bytes = n_items * uint64_t(max_leaves) * sizeof(ContainerDesc);
-  if (staging && desc_bytes <= (256ull << 20)) {
+  p.fold_all = fold_all ? 1u : 0u;
+  if (staging && !fold_all && desc_bytes <= (256ull << 20)) {
     TRY(ensure_dev(ctx, ctx->d_slow_descs, size_t(desc_bytes)));
     p.slow_descs = static_cast<ContainerDesc*>(ctx->d_slow_descs.p);
     p.slow_desc_stride = max_leaves;
   }
-  CUDA_TRY(ctx, cudaMemsetAsync(p.slow_count, 0, 4, ctx->stream));
-  const uint64_t want = (n_items + kFastWarps - 1) / kFastWarps;
-  const uint32_t grid = uint32_t(std::min<uint64_t>(want, resident_ctas(ctx, OCC_FAST, eval_fast_kernel, kFastWarps * 32, 0)));
-  eval_fast_kernel<<<grid, kFastWarps * 32, 0, ctx->stream>>>(p);
-  ctx->timing.launches++;
-  if (staging) {
-    const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, resident_ctas(ctx, OCC_STAGED, eval_staged_kernel, kStagedThreads, 0)));
-    eval_staged_kernel<<<sgrid, kStagedThreads, 0, ctx->stream>>>(p);
+  if (!fold_all) {
+    CUDA_TRY(ctx, cudaMemsetAsync(p.slow_count, 0, 4, ctx->stream));
+    const uint64_t want = (n_items + kFastWarps - 1) / kFastWarps;
+    const uint32_t grid = uint32_t(std::min<uint64_t>(want, resident_ctas(ctx, OCC_FAST, eval_fast_kernel, kFastWarps * 32, 0)));
+    eval_fast_kernel<<<grid, kFastWarps * 32, 0, ctx->stream>>>(p);
     ctx->timing.launches++;
+  }
+  if (staging) {  // deferred items: flat left folds go to the fold kernel, anything else to the general staged evaluator
+    const uint32_t fgrid = uint32_t(std::min<uint64_t>(n_items, resident_ctas(ctx, OCC_FOLD, eval_fold_kernel, kFoldCtaThreads, kFoldSmem)));
+    eval_fold_kernel<<<fgrid, kFoldCtaThreads, kFoldSmem, ctx->stream>>>(p);
+    ctx->timing.launches++;
+    if (bushy) {
+      const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, resident_ctas(ctx, OCC_STAGED, eval_staged_kernel, kStagedThreads, 0)));
+      eval_staged_kernel<<<sgrid, kStagedThreads, 0, ctx->stream>>>(p);
+      ctx->timing.launches++;
+    }
   }
   CUDA_TRY(ctx, cudaGetLastError());
   return PB200_OK;
@@ -922,6 +949,9 @@ int finish_call(pb200_ctx* ctx) {
   ctx->timing.algo_bytes = *static_cast<unsigned long long*>(ctx->h_algo.p);
   return PB200_OK;
 }
+
+// mean payload of the containers the batch's Row leaves come from; at a kilobyte and more the fold evaluator runs alone
+bool fold_all_of(const Compiled& cp) { return cp.may_need_staging && cp.leaf_containers && cp.leaf_payload / cp.leaf_containers >= 1024; }
 
 uint32_t max_leaves_of(const Compiled& cp) {
   uint32_t m = 1;
@@ -1013,7 +1043,7 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
     if (rc == PB200_OK) rc = run_pretasks(ctx, cp, bd, n_shards);
     if (rc == PB200_OK)
       rc = launch_eval(ctx, bd, bd.progs, n_queries, n_shards, cp.may_need_staging, d_out, per_shard ? n_shards : 1, per_shard ? 1 : 0,
-                       nullptr, nullptr, max_leaves_of(cp));
+                       nullptr, nullptr, max_leaves_of(cp), cp.any_bushy, fold_all_of(cp));
     if (rc == PB200_OK && has_shift(cp))  // bits shifted past a shard's last column count too (roaring.go:970-974)
       rc = launch_overflow(ctx, bd, bd.progs, n_queries, n_shards, d_out, per_shard ? n_shards : 1, per_shard ? 1 : 0, nullptr);
     if (rc != PB200_OK) { ctx->n_pending--; ctx->algo_off = 8; return rc; }
@@ -1070,10 +1100,85 @@ int count_impl(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off
 #include "engine_queries.inl"
 #include "engine_groupby.inl"
 
+// ---- pb200_count from many host threads: a combining queue -------------------------------------------------------
+// The reference runs workerPoolSize goroutines and many HTTP requests side by side (executor.go:83-107), each of which
+// would issue its own Count here. One launch per call serialises them at the per-call cost (~45 us); instead a caller
+// files its request and, if nobody is combining, becomes the combiner: it takes every request that has arrived with
+// the same shard list, runs them as ONE batch (the batched kernels are what reaches the HBM roofline) and hands the
+// results out; requests that arrive meanwhile are taken by the next round. A lone caller pays one extra mutex.
+namespace {
+
+constexpr size_t kCombineMax = 1024;
+
+void run_count_group(pb200_ctx* ctx, std::vector<CountReq*>& grp) {
+  std::lock_guard<std::mutex> lock(ctx->mu);
+  DeviceGuard guard(ctx->device);
+  ctx->err.clear();
+  if (grp.size() == 1) {
+    CountReq* r = grp[0];
+    const uint32_t off[2] = {0, r->n_nodes};
+    r->rc = count_impl(ctx, r->prog, off, 1, r->shards, r->n_shards, false, r->out);
+    if (r->rc != PB200_OK) r->err = ctx->err;
+    return;
+  }
+  std::vector<pb200_node> flat;
+  std::vector<uint32_t> off(grp.size() + 1, 0);
+  for (size_t i = 0; i < grp.size(); i++) {
+    flat.insert(flat.end(), grp[i]->prog, grp[i]->prog + grp[i]->n_nodes);
+    off[i + 1] = uint32_t(flat.size());
+  }
+  std::vector<uint64_t> out(grp.size(), 0);
+  const int rc = count_impl(ctx, flat.data(), off.data(), uint32_t(grp.size()), grp[0]->shards, grp[0]->n_shards, false, out.data());
+  if (rc == PB200_OK) {
+    for (size_t i = 0; i < grp.size(); i++) { *grp[i]->out = out[i]; grp[i]->rc = PB200_OK; }
+    ctx->cq_batches++; ctx->cq_queries += grp.size();
+    return;
+  }
+  // some program of the group is at fault: each call gets its own verdict
+  for (CountReq* r : grp) {
+    const uint32_t o1[2] = {0, r->n_nodes};
+    ctx->err.clear();
+    r->rc = count_impl(ctx, r->prog, o1, 1, r->shards, r->n_shards, false, r->out);
+    if (r->rc != PB200_OK) r->err = ctx->err;
+  }
+}
+
+int combine_counts(pb200_ctx* ctx, CountReq& me) {
+  std::unique_lock<std::mutex> lk(ctx->cq_mu);
+  ctx->cq.push_back(&me);
+  while (!me.done) {
+    if (ctx->cq_busy) { ctx->cq_cv.wait(lk); continue; }
+    ctx->cq_busy = true;  // this thread combines until its own request has been served; a waiting thread takes over then
+    while (!me.done && !ctx->cq.empty()) {
+      std::vector<CountReq*> grp, rest;
+      CountReq* head = ctx->cq.front();
+      for (CountReq* r : ctx->cq) {
+        const bool same = grp.size() < kCombineMax && r->n_shards == head->n_shards && r->n_nodes && r->prog && r->out &&
+                          (r->n_shards == 0 || (r->shards && head->shards && std::memcmp(r->shards, head->shards, size_t(r->n_shards) * 8) == 0));
+        (r == head || same ? grp : rest).push_back(r);
+      }
+      ctx->cq.swap(rest);
+      lk.unlock();
+      run_count_group(ctx, grp);
+      lk.lock();
+      for (CountReq* r : grp) r->done = true;
+      ctx->cq_cv.notify_all();
+    }
+    ctx->cq_busy = false;
+    ctx->cq_cv.notify_all();
+  }
+  if (me.rc != PB200_OK) { std::lock_guard<std::mutex> lock(ctx->mu); ctx->err = me.err; }
+  return me.rc;
+}
+
+}  // namespace
+
 extern "C" int pb200_count(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards, uint64_t* out_count) {
-  ENTER(ctx);
-  const uint32_t off[2] = {0, n_nodes};
-  return count_impl(ctx, prog, off, 1, shards, n_shards, false, out_count);
+  if (!ctx) return PB200_ERR_INVALID;
+  if (!out_count) return PB200_ERR_INVALID;
+  CountReq me;
+  me.prog = prog; me.n_nodes = n_nodes; me.shards = shards; me.n_shards = n_shards; me.out = out_count;
+  return combine_counts(ctx, me);
 }
 
 extern "C" int pb200_count_batch(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off, uint32_t n_queries,
@@ -1175,7 +1280,7 @@ extern "C" int pb200_batch_launch(pb200_ctx* ctx, pb200_batch* b) {
   ctx->timing.launches = 0;
   CUDA_TRY(ctx, cudaMemsetAsync(b->d_counts.p, 0, size_t(b->n_queries) * 8, ctx->stream));
   return launch_eval(ctx, b->bd, b->bd.progs, b->n_queries, b->n_shards, b->cp.may_need_staging,
-                     static_cast<unsigned long long*>(b->d_counts.p), 1, 0, nullptr, nullptr, max_leaves_of(b->cp));
+                     static_cast<unsigned long long*>(b->d_counts.p), 1, 0, nullptr, nullptr, max_leaves_of(b->cp), b->cp.any_bushy, fold_all_of(b->cp));
 }
 
 extern "C" int pb200_batch_device_counts(pb200_ctx* ctx, pb200_batch* b, void** device_counts) {
@@ -1311,10 +1416,11 @@ extern "C" int pb200_count_pairs_noalloc(pb200_ctx* ctx, pb200_family family, co
   p.algo_bytes = reinterpret_cast<unsigned long long*>(scratch + kNaCounters + 8);
   const uint32_t grid = uint32_t(std::min<uint64_t>((n_items + kFastWarps - 1) / kFastWarps, uint64_t(ctx->sm_count) * 8));
   eval_fast_kernel<<<grid, kFastWarps * 32, 0, ctx->stream>>>(p);
-  const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, uint64_t(ctx->sm_count) * 6));
-  eval_staged_kernel<<<sgrid, kStagedThreads, 0, ctx->stream>>>(p);
+  const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, uint64_t(ctx->sm_count) * 5));
+  eval_fold_kernel<<<sgrid, kFoldCtaThreads, kFoldSmem, ctx->stream>>>(p);  // a two-leaf Intersect is a flat fold
   CUDA_TRY(ctx, cudaGetLastError());
   return PB200_OK;
 }
 
+#include "engine_ingest.inl"
 #include "engine_multi.inl"

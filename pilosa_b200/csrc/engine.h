@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <condition_variable>
 #include <functional>
 #include <mutex>
 #include <string>
@@ -23,7 +24,18 @@ struct PinBuf {  // growable pinned host staging
   size_t cap = 0;
 };
 
+// Where rewritten containers and rebuilt row tables go (engine_ingest.inl): large chunks, bump-allocated, 128 B aligned.
+struct WriteArena {
+  uint8_t* base = nullptr;             // the chunk being filled
+  size_t cap = 0, top = 0;             // top: host copy of the bump pointer (authoritative between launches)
+  unsigned long long* d_top = nullptr; // device copy the ingest kernel bumps
+  std::vector<std::pair<void*, size_t>> retired;  // full chunks (pointer, bytes) that descriptors still point into
+  uint32_t live_frags = 0;             // fragments referencing the arena; at 0 everything is reclaimed
+};
+
 struct Fragment {
+  bool in_arena = false;  // some descriptor or the row table points into the write arena
+  bool maybe_empty_rows = false;  // a write may have emptied a listed row (row_counts == 0): Rows / GroupBy skip those
   void* blob = nullptr;  // one cudaMalloc: [row_ids | descs | payloads]
   size_t blob_bytes = 0;
   FragDev dev{};
@@ -56,6 +68,7 @@ struct Family {
   FragDev* d_frags = nullptr;
   uint32_t cap = 0;
   uint64_t n_not_all_bitmap = 0;  // fragments holding array/run containers (local ones and, in a pb200_multi, the peers')
+  uint64_t payload_total = 0, containers_total = 0;  // over the local fragments: mean container size steers the evaluator choice
   std::vector<uint8_t> remote_flags;  // pb200_multi: per shard, bit 0 = the entry points into a peer's HBM, bit 1 = not all bitmap
 };
 
@@ -77,6 +90,8 @@ struct Compiled {
   std::vector<PreTask> pre;
   uint32_t n_temp_slots = 0;
   bool may_need_staging = false;  // some leaf family holds array/run containers (or temps)
+  uint64_t leaf_payload = 0, leaf_containers = 0;  // summed over the Row leaves' families (see Family)
+  bool any_bushy = false;         // some program is not a flat left fold (stack ops, Not): eval_staged_kernel is needed beside eval_fold_kernel
 };
 
 // One Count batch in flight (pb200_count_batch_begin .. _end). Two slots let a host compile and
@@ -93,8 +108,26 @@ struct CountSlot {
 
 }  // namespace pb200
 
+namespace pb200 {
+// One single-query Count call waiting to be combined with the calls of other host threads (engine.cu: combine_counts).
+struct CountReq {
+  const pb200_node* prog; uint32_t n_nodes;
+  const uint64_t* shards; uint32_t n_shards;
+  uint64_t* out;
+  int rc = 0;
+  bool done = false;
+  std::string err;
+};
+}  // namespace pb200
+
 struct pb200_ctx {
   int device = 0;
+  // combining queue of pb200_count: threads that arrive while a launch is in flight are folded into the next batch
+  std::mutex cq_mu;
+  std::condition_variable cq_cv;
+  std::vector<pb200::CountReq*> cq;
+  bool cq_busy = false;
+  uint64_t cq_batches = 0, cq_queries = 0;  // statistics: launches made for how many single-query calls
   int sm_count = 148;
   size_t budget = 0, used = 0;
   cudaStream_t own_stream = nullptr, stream = nullptr;
@@ -114,7 +147,9 @@ struct pb200_ctx {
   bool dense_has_ovf = false;                      // the rows in d_dense carry Shift overflow words
   unsigned long long* dense_ovf_dev = nullptr;
   pb200::DevBuf d_batch, d_out, d_slow, d_temp, d_dense, d_dense_n, d_misc, d_topn, d_bsi;
-  pb200::PinBuf h_stage, h_out, h_algo, h_topn;
+  pb200::PinBuf h_stage, h_out, h_algo, h_topn, h_ing, h_ing_res;
+  pb200::DevBuf d_ing, d_ing_res;
+  pb200::WriteArena arena;
   uint32_t densify_min_bytes = 0;  // PB200_OPT_DENSIFY_MIN_BYTES (0 = containers stay as loaded)
   uint32_t rank_cache_size = 50000;  // PB200_OPT_RANK_CACHE_SIZE (field.go:47 DefaultCacheSize)
   bool topn_attr_set = false, sum_attr_set = false, mm_attr_set = false;

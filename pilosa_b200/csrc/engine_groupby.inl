@@ -11,10 +11,18 @@
 namespace {
 
 // a row is present in a shard when the fragment's row table lists it (non-empty containers only)
-std::vector<uint64_t> present_rows(const Fragment& f, const uint64_t* only, uint64_t n_only) {
-  if (!only) return f.row_ids;
+std::vector<uint64_t> live_row_ids(const Fragment& f) {  // rows a write has emptied stay listed on the host with count 0
+  if (!f.maybe_empty_rows) return f.row_ids;
   std::vector<uint64_t> out;
-  std::set_intersection(f.row_ids.begin(), f.row_ids.end(), only, only + n_only, std::back_inserter(out));
+  for (size_t i = 0; i < f.row_ids.size(); i++) if (f.row_counts[i]) out.push_back(f.row_ids[i]);
+  return out;
+}
+
+std::vector<uint64_t> present_rows(const Fragment& f, const uint64_t* only, uint64_t n_only) {
+  if (!only) return live_row_ids(f);
+  const std::vector<uint64_t> live = live_row_ids(f);
+  std::vector<uint64_t> out;
+  std::set_intersection(live.begin(), live.end(), only, only + n_only, std::back_inserter(out));
   return out;
 }
 
@@ -241,7 +249,8 @@ extern "C" int pb200_rows(pb200_ctx* ctx, pb200_family family, uint64_t start, u
     const Fragment& f = it->second;
     std::vector<uint64_t> mine;
     if (!has_column) {
-      mine.assign(std::lower_bound(f.row_ids.begin(), f.row_ids.end(), start), f.row_ids.end());
+      const std::vector<uint64_t> live = live_row_ids(f);
+      mine.assign(std::lower_bound(live.begin(), live.end(), start), live.end());
     } else if (f.dev.nrows) {
       TRY(sync_families(ctx));
       TRY(ensure_dev(ctx, ctx->d_slow, f.dev.nrows));

@@ -13,6 +13,7 @@
 #include <stdint.h>
 
 #include "layout.h"
+#include "tma.cuh"
 
 namespace pb200 {
 
@@ -35,6 +36,7 @@ struct EvalParams {
   ContainerDesc* slow_descs;       // scratch (optional): resolved descriptors of deferred items, [slot][slow_desc_stride]
   uint32_t slow_desc_stride;
   unsigned long long* algo_bytes;  // accumulated algorithmic bytes (payload + 16 B / container)
+  uint32_t fold_all;               // eval_fold_kernel walks EVERY item itself (no eval_fast_kernel pass, no deferred list)
 };
 
 // ---------------------------------------------------------------------------------------
@@ -75,6 +77,18 @@ __device__ __forceinline__ ContainerDesc resolve_leaf(const EvalParams& p, const
 
 __device__ __forceinline__ bool is_const_or_bitmap(const ContainerDesc& d) {
   return d.n == 0 || d.n == kFullN || desc_type(d) == kBitmap;
+}
+
+// Which items the fold kernel takes (the staged kernel takes the rest): LOAD first, then only *_LEAF ops, and
+// RANDNOT (Not) only against a bitmap / constant existence container.
+__device__ __forceinline__ bool fold_can_take(const Prog& pg, const Instr* ins, const ContainerDesc* descs) {
+  if (pg.n_instr == 0 || ins[0].op != I_LOAD) return false;
+  for (uint32_t i = 1; i < pg.n_instr; i++) {
+    const uint8_t op = ins[i].op;
+    if (op == I_LOAD || op >= I_AND_STACK) return false;
+    if (op == I_RANDNOT_LEAF && !is_const_or_bitmap(descs[ins[i].leaf])) return false;
+  }
+  return true;
 }
 
 __device__ __forceinline__ uint32_t desc_algo_bytes(const ContainerDesc& d) {
@@ -494,11 +508,11 @@ __global__ void __launch_bounds__(kStagedThreads) eval_staged_kernel(EvalParams 
   __shared__ __align__(16) uint4 s_const[2];
   __shared__ __align__(16) uint64_t s_win[kSlotWords];
   const int tid = threadIdx.x;
-  const uint32_t n_slow = *p.slow_count;
+  const uint32_t n_slow = p.fold_all ? p.n_queries * p.n_shards * kRowContainers : *p.slow_count;
   if (tid == 0) { s_const[0] = make_uint4(0, 0, 0, 0); s_const[1] = make_uint4(~0u, ~0u, ~0u, ~0u); }
 
   for (uint32_t it = blockIdx.x; it < n_slow; it += gridDim.x) {
-    const uint64_t item = p.slow_list[it];
+    const uint64_t item = p.fold_all ? uint64_t(it) : uint64_t(p.slow_list[it]);
     const uint32_t c = uint32_t(item & 15);
     const uint64_t qs = item >> 4;
     const uint32_t s = uint32_t(qs % p.n_shards);
@@ -510,15 +524,17 @@ __global__ void __launch_bounds__(kStagedThreads) eval_staged_kernel(EvalParams 
     if (tid < 32) {  // warp 0: descriptors + staging-slot assignment (n_leaves <= 32)
       ContainerDesc d; d.addr = 0; d.n = 0; d.meta = 0;
       if (tid < pg.n_leaves) {
-        d = p.slow_descs ? p.slow_descs[uint64_t(it) * p.slow_desc_stride + tid] : resolve_leaf(p, p.leaves[pg.leaf_off + tid], s, c);
+        d = (p.slow_descs && !p.fold_all) ? p.slow_descs[uint64_t(it) * p.slow_desc_stride + tid] : resolve_leaf(p, p.leaves[pg.leaf_off + tid], s, c);
         s_desc[tid] = d;
       }
       const bool need = tid < pg.n_leaves && !is_const_or_bitmap(d);
       const uint32_t mask = __ballot_sync(0xffffffffu, need);
       if (tid < pg.n_leaves) s_slot[tid] = need ? int(__popc(mask & ((1u << tid) - 1u))) : -1;
-      if (tid == 0) s_nslots = __popc(mask);
+      __syncwarp();
+      if (tid == 0) s_nslots = fold_can_take(pg, ins, s_desc) ? -1 : __popc(mask);  // -1: eval_fold_kernel's item
     }
     __syncthreads();
+    if (s_nslots < 0) continue;
     // pull the bitmap operands towards L2 while the array / run operands are being staged
     for (uint32_t l = 0; l < pg.n_leaves; l++) {
       const ContainerDesc d = s_desc[l];
@@ -598,6 +614,344 @@ __global__ void __launch_bounds__(kStagedThreads) eval_staged_kernel(EvalParams 
       if (p.out_counts && tot) atomicAdd(p.out_counts + uint64_t(q) * p.out_qstride + uint64_t(s) * p.out_sstride, (unsigned long long)tot);
       if (p.dense_n) p.dense_n[item] = tot;
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// K2-K6, fold form: one CTA per deferred item whose program is a flat left fold
+//   acc = leaf0 ; acc = acc <op> leaf1 ; acc = acc <op> leaf2 ; ...
+// (what every n-ary PQL call over rows compiles to, executor.go:1668-1733,1003-1025). The accumulator is ONE 8 KiB
+// shared-memory window; each operand is applied to it IN ITS OWN ENCODING, so an operand costs its payload, not
+// 65536 bits: the type pairs of roaring.go:3078-4957 become
+//                bitmap (1024 words)     array (n x u16)                       run list
+//   load / OR    w (|)= g                set the value's bit                   set [start,last]   (union*  :3470-3839)
+//   XOR          w ^= g                  flip the bit                          flip [start,last]  (xor*    :4266-4957)
+//   ANDNOT       w &= ~g                 clear the bit                         clear [start,last] (difference* :3920-4205)
+//   AND          w &= g                  probe the bits, rebuild the window    clear the gaps     (intersect*  :3254-3418)
+// Payloads are contiguous 16 B aligned streams, so the bulk copy engine moves each one global -> shared with one
+// cp.async.bulk issued by one thread (local HBM only, no multicast), up to kFoldStages operands ahead of the one being
+// applied; completion is an mbarrier transaction count. Elements are sorted, so a thread that takes 16 consecutive
+// values (8 consecutive runs) owns every window word strictly between its first and its last one: only those two
+// words are edited with shared-memory atomics (ATOMS costs 2 cycles per lane on this part; one per value was the
+// whole run time), the rest with plain read-modify-writes. The count is the popcount of the window; no result
+// container is typed or written unless the caller wants the dense row.
+// ---------------------------------------------------------------------------------------
+constexpr int kFoldThreads = 256;                      // consumer threads (8 warps) ...
+constexpr int kFoldCtaThreads = kFoldThreads + 32;     // ... plus one producer warp
+constexpr int kFoldStages = 4;
+constexpr int kFoldMeta = 2;                            // items whose descriptors are resolved ahead
+constexpr int kFoldSmem = (1 + kFoldStages) * kBitmapBytes;  // dynamic shared memory: the window + the staging ring
+// barrier among the consumer warps only (the producer warp never joins it)
+__device__ __forceinline__ void fold_bar() { asm volatile("bar.sync 1, %0;" :: "n"(kFoldThreads) : "memory"); }
+enum RangeMode : int { R_SET = 0, R_CLEAR = 1, R_FLIP = 2 };
+
+// One (word, mask) edit; `shared_word` says whether another thread may edit the same word during this operand.
+__device__ __forceinline__ void fold_word(uint32_t* w, uint32_t mask, int mode, bool shared_word) {
+  if (shared_word) {
+    if (mode == R_SET) atomicOr(w, mask);
+    else if (mode == R_CLEAR) atomicAnd(w, ~mask);
+    else atomicXor(w, mask);
+  } else {
+    const uint32_t old = *w;
+    *w = mode == R_SET ? (old | mask) : mode == R_CLEAR ? (old & ~mask) : (old ^ mask);
+  }
+}
+
+// Sets / clears / flips the bits of 16 consecutive array values held by one thread. The values ascend, so the words
+// between the thread's first and last one are its own: the first and the last flush are atomic, the others plain.
+template <int MODE>
+__device__ __noinline__ void fold_array16(uint32_t* win32, const uint4* st4, uint32_t len, int tid) {
+  const uint32_t first = uint32_t(tid) * 16;
+  if (first >= len) return;
+  const uint32_t n = min(16u, len - first);
+  const uint4 q0 = st4[2 * tid], q1 = st4[2 * tid + 1];
+  const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+  uint32_t cur_w = (w[0] & 0xffff) >> 5, cur_bits = 0;
+  bool at_first = true;
+#pragma unroll
+  for (int k = 0; k < 16; k++) {
+    if (uint32_t(k) < n) {
+      const uint32_t val = (k & 1) ? (w[k >> 1] >> 16) : (w[k >> 1] & 0xffff);
+      if ((val >> 5) != cur_w) {
+        fold_word(&win32[cur_w], cur_bits, MODE, at_first);
+        at_first = false;
+        cur_w = val >> 5; cur_bits = 0;
+      }
+      cur_bits |= 1u << (val & 31);
+    }
+  }
+  fold_word(&win32[cur_w], cur_bits, MODE, true);
+}
+
+// A run list as a bitmap, without touching a word per run: every run toggles two bits of a zeroed scratch window —
+// its start and the position behind its last value — and the run bitmap is the running parity (prefix XOR) of those
+// toggles over the 65536 positions. The toggles go in like array values (sorted, 16 per thread, atomics only on a
+// thread's first and last word); the scan costs the same whatever the runs look like: a thread owns 8 consecutive
+// words, XOR-scans inside each word with five shifts, carries the parity from word to word, and gets the parity of
+// everything in front of it from a warp ballot and one shared-memory hop across the eight warps. The result is
+// applied to the accumulator word by word (op: I_OR / I_XOR / I_ANDNOT / I_AND _LEAF).
+// `scratch` is the operand's own staging slot: the runs are taken into registers first, then the slot is reused.
+template <int OP>
+__device__ __noinline__ void fold_runs_scan(uint32_t* win32, uint32_t* scratch, uint32_t len, uint32_t* s_par, int tid) {
+  const int lane = tid & 31, warp = tid >> 5;
+  const uint32_t first = uint32_t(tid) * 8;
+  const uint32_t n = first < len ? min(8u, len - first) : 0u;
+  uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
+  if (n) { q0 = reinterpret_cast<const uint4*>(scratch)[2 * tid]; q1 = reinterpret_cast<const uint4*>(scratch)[2 * tid + 1]; }
+  fold_bar();  // every run is in a register
+  reinterpret_cast<uint4*>(scratch)[tid] = make_uint4(0, 0, 0, 0);
+  reinterpret_cast<uint4*>(scratch)[tid + kFoldThreads] = make_uint4(0, 0, 0, 0);
+  fold_bar();
+  if (n) {  // toggles at start and last + 1 of each run: ascending positions, so the ownership rule of fold_array16 holds
+    const uint32_t r[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+    uint32_t cur_w = (r[0] & 0xffff) >> 5, cur_bits = 0;
+    bool at_first = true;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      if (uint32_t(k) < n) {
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+          const uint32_t pos = e == 0 ? (r[k] & 0xffff) : (r[k] >> 16) + 1u;
+          if (pos < 65536u) {
+            if ((pos >> 5) != cur_w) {
+              if (cur_bits) fold_word(&scratch[cur_w], cur_bits, R_FLIP, at_first);
+              at_first = false;
+              cur_w = pos >> 5; cur_bits = 0;
+            }
+            cur_bits ^= 1u << (pos & 31);
+          }
+        }
+      }
+    }
+    if (cur_bits) fold_word(&scratch[cur_w], cur_bits, R_FLIP, true);
+  }
+  fold_bar();
+  // scan: words 8 tid .. 8 tid + 7
+  const uint4 d0 = reinterpret_cast<const uint4*>(scratch)[2 * tid], d1 = reinterpret_cast<const uint4*>(scratch)[2 * tid + 1];
+  uint32_t x[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+  uint32_t par = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) par ^= x[k];
+  par = __popc(par) & 1u;
+  const uint32_t votes = __ballot_sync(0xffffffffu, par != 0);
+  if (lane == 0) s_par[warp] = __popc(votes) & 1u;
+  fold_bar();
+  uint32_t before = __popc(votes & ((1u << lane) - 1u)) & 1u;
+  for (int w = 0; w < warp; w++) before ^= s_par[w];
+  uint32_t carry = 0u - before;  // all ones when an odd number of toggles lies in front of this thread's words
+  uint4 a0 = reinterpret_cast<const uint4*>(win32)[2 * tid], a1 = reinterpret_cast<const uint4*>(win32)[2 * tid + 1];
+  uint32_t acc[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    uint32_t y = x[k];
+    y ^= y << 1; y ^= y << 2; y ^= y << 4; y ^= y << 8; y ^= y << 16;
+    y ^= carry;
+    carry = 0u - (y >> 31);
+    acc[k] = OP == I_OR_LEAF ? (acc[k] | y) : OP == I_XOR_LEAF ? (acc[k] ^ y) : OP == I_ANDNOT_LEAF ? (acc[k] & ~y) : (acc[k] & y);
+  }
+  reinterpret_cast<uint4*>(win32)[2 * tid] = make_uint4(acc[0], acc[1], acc[2], acc[3]);
+  reinterpret_cast<uint4*>(win32)[2 * tid + 1] = make_uint4(acc[4], acc[5], acc[6], acc[7]);
+}
+
+// Payload bytes the copy engine moves for an operand (a multiple of 16; 0 = constant operand, nothing to move).
+__device__ __forceinline__ uint32_t fold_bytes(const ContainerDesc& d) {
+  if (d.n == 0) return 0;
+  const uint32_t type = desc_type(d), len = desc_len(d);
+  if (type == kBitmap) return kBitmapBytes;
+  if (d.n == kFullN) return 0;
+  return type == kArray ? ((len * 2 + 15) & ~15u) : ((len * 4 + 15) & ~15u);
+}
+
+struct FoldMeta {  // one deferred item, resolved by the producer warp
+  uint64_t item;
+  uint32_t q, s, n_instr, take;
+  Instr ins[kMaxInstr];
+  ContainerDesc desc[kMaxLeaves];
+};
+
+// Warp-specialised: warp 8 is the PRODUCER — it walks the CTA's items one ahead of the consumers, resolves their
+// descriptors into a two-deep ring (meta_full / meta_empty mbarriers) and keeps the copy engine busy: every operand
+// payload is one cp.async.bulk into the next free slot of a kFoldStages-deep staging ring (full / empty mbarriers),
+// issued as soon as the slot is released, whatever item it belongs to. Warps 0-7 are the CONSUMERS: they never wait
+// for global memory except on a cold pipeline, only for `full`, and synchronise among themselves with a named barrier.
+__global__ void __launch_bounds__(kFoldCtaThreads, 5) eval_fold_kernel(EvalParams p) {
+  extern __shared__ __align__(128) uint8_t s_dyn[];  // [window 8 KiB][kFoldStages x 8 KiB staging]
+  __shared__ FoldMeta s_meta[kFoldMeta];
+  __shared__ uint32_t s_red[kFoldThreads / 32];
+  __shared__ __align__(8) uint64_t s_full[kFoldStages], s_empty[kFoldStages], s_mfull[kFoldMeta], s_mempty[kFoldMeta];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const uint32_t n_slow = p.fold_all ? p.n_queries * p.n_shards * kRowContainers : *p.slow_count;
+  if (tid == 0) {
+    for (int i = 0; i < kFoldStages; i++) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 1); }
+    for (int i = 0; i < kFoldMeta; i++) { mbar_init(&s_mfull[i], 1); mbar_init(&s_mempty[i], 1); }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (tid >= kFoldThreads) {
+    // ---------------- producer warp ----------------
+    uint32_t g = 0;  // payload loads issued so far (lane 0)
+    uint32_t j = 0;  // items handled so far
+    unsigned long long bytes_acc = 0;
+    for (uint32_t it = blockIdx.x; it < n_slow; it += gridDim.x, j++) {
+      const uint32_t ms = j % kFoldMeta;
+      if (j >= uint32_t(kFoldMeta)) mbar_wait(&s_mempty[ms], ((j / kFoldMeta) - 1u) & 1u);
+      FoldMeta& m = s_meta[ms];
+      const uint64_t item = p.fold_all ? uint64_t(it) : uint64_t(p.slow_list[it]);
+      const uint32_t c = uint32_t(item & 15);
+      const uint64_t qs = item >> 4;
+      const uint32_t sidx = uint32_t(qs % p.n_shards), q = uint32_t(qs / p.n_shards);
+      const Prog pg = p.progs[q];
+      const Instr* ins = p.instrs + pg.instr_off;
+      uint32_t bytes = 0;
+      if (uint32_t(lane) < pg.n_leaves) {
+        const ContainerDesc d = (p.slow_descs && !p.fold_all) ? p.slow_descs[uint64_t(it) * p.slow_desc_stride + lane]
+                                                              : resolve_leaf(p, p.leaves[pg.leaf_off + lane], sidx, c);
+        m.desc[lane] = d;
+        bytes = desc_algo_bytes(d);
+      }
+      if (p.fold_all) {  // no eval_fast_kernel pass did the byte accounting
+        bytes = warp_sum(bytes);
+        if (lane == 0) bytes_acc += bytes;
+      }
+      for (uint32_t k = lane; k < pg.n_instr; k += 32) m.ins[k] = ins[k];
+      __syncwarp();
+      if (lane == 0) {
+        bool take = fold_can_take(pg, m.ins, m.desc);
+        m.item = item; m.q = q; m.s = sidx; m.n_instr = pg.n_instr; m.take = take ? 1u : 0u;
+        // Count(Row): the cardinality is in the descriptor (roaring.go:405 Count = sum of n); temps carry none
+        if (take && pg.n_instr == 1 && !p.dense_out && p.leaves[pg.leaf_off + m.ins[0].leaf].kind != L_TEMP) { m.take = 2u; take = false; }
+        mbar_arrive(&s_mfull[ms]);  // (release) the item's descriptors are published
+        if (take)
+          for (uint32_t k = 0; k < pg.n_instr; k++) {
+            const ContainerDesc d = m.desc[m.ins[k].leaf];
+            const uint32_t bytes = fold_bytes(d);
+            if (!bytes) continue;
+            const uint32_t slot = g % kFoldStages;
+            if (g >= uint32_t(kFoldStages)) mbar_wait(&s_empty[slot], ((g / kFoldStages) - 1u) & 1u);
+            mbar_arrive_expect_tx(&s_full[slot], bytes);
+            tma_load_1d(s_dyn + size_t(slot + 1) * kBitmapBytes, reinterpret_cast<const void*>(d.addr), bytes, &s_full[slot]);
+            g++;
+          }
+      }
+      __syncwarp();
+    }
+    if (lane == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+    return;
+  }
+
+  // ---------------- consumer warps ----------------
+  uint32_t* s_win = reinterpret_cast<uint32_t*>(s_dyn);
+  uint4* win4 = reinterpret_cast<uint4*>(s_dyn);
+  const uint4 zero4 = make_uint4(0, 0, 0, 0), ones4 = make_uint4(~0u, ~0u, ~0u, ~0u);
+  uint32_t g = 0, j = 0;
+  for (uint32_t it = blockIdx.x; it < n_slow; it += gridDim.x, j++) {
+    const uint32_t ms = j % kFoldMeta;
+    mbar_wait(&s_mfull[ms], (j / kFoldMeta) & 1u);
+    const FoldMeta& m = s_meta[ms];
+    const uint32_t n_instr = m.n_instr;
+    if (m.take != 1u) {  // 0: not a flat fold, eval_staged_kernel handles it; 2: Count(Row) straight from the descriptor
+      if (tid == 0 && m.take == 2u) {
+        const uint32_t nrow = m.desc[m.ins[0].leaf].n;
+        if (p.out_counts && nrow) atomicAdd(p.out_counts + uint64_t(m.q) * p.out_qstride + uint64_t(m.s) * p.out_sstride, (unsigned long long)nrow);
+      }
+      fold_bar();
+      if (tid == 0) mbar_arrive(&s_mempty[ms]);
+      continue;
+    }
+#pragma unroll 1
+    for (uint32_t i = 0; i < n_instr; i++) {
+      const Instr in = m.ins[i];
+      const ContainerDesc d = m.desc[in.leaf];
+      const uint32_t type = desc_type(d), len = desc_len(d);
+      const bool nil = d.n == 0, full = d.n == kFullN && type != kBitmap;
+      const bool staged = !nil && !full;
+      const uint32_t slot = g % kFoldStages;
+      const uint4* st4 = reinterpret_cast<const uint4*>(s_dyn + size_t(slot + 1) * kBitmapBytes);
+      if (staged) mbar_wait(&s_full[slot], (g / kFoldStages) & 1u);  // this operand's payload has landed
+      int op = in.op;
+      bool skip = false;
+      if (op == I_LOAD) {  // load = clear, then OR (a bitmap is copied straight in)
+        if (staged && type == kBitmap) {
+          win4[tid] = st4[tid];
+          win4[tid + kFoldThreads] = st4[tid + kFoldThreads];
+          skip = true;
+        } else {
+          win4[tid] = full ? ones4 : zero4;
+          win4[tid + kFoldThreads] = full ? ones4 : zero4;
+          fold_bar();
+          skip = !staged;
+          op = I_OR_LEAF;
+        }
+      }
+      if (!skip) {
+        if (nil) {
+          if (op == I_AND_LEAF || op == I_RANDNOT_LEAF) { win4[tid] = zero4; win4[tid + kFoldThreads] = zero4; }
+        } else if (full) {
+          if (op == I_OR_LEAF) { win4[tid] = ones4; win4[tid + kFoldThreads] = ones4; }
+          else if (op == I_ANDNOT_LEAF) { win4[tid] = zero4; win4[tid + kFoldThreads] = zero4; }
+          else if (op == I_XOR_LEAF || op == I_RANDNOT_LEAF) {
+            const uint4 a = win4[tid], b = win4[tid + kFoldThreads];
+            win4[tid] = make_uint4(~a.x, ~a.y, ~a.z, ~a.w);
+            win4[tid + kFoldThreads] = make_uint4(~b.x, ~b.y, ~b.z, ~b.w);
+          }
+        } else if (type == kBitmap) {
+          win4[tid] = apply_op(uint8_t(op), win4[tid], st4[tid]);
+          win4[tid + kFoldThreads] = apply_op(uint8_t(op), win4[tid + kFoldThreads], st4[tid + kFoldThreads]);
+        } else if (type == kArray) {
+          if (op == I_OR_LEAF) fold_array16<R_SET>(s_win, st4, len, tid);
+          else if (op == I_XOR_LEAF) fold_array16<R_FLIP>(s_win, st4, len, tid);
+          else if (op == I_ANDNOT_LEAF) fold_array16<R_CLEAR>(s_win, st4, len, tid);
+          else {  // AND: keep exactly the array's values whose bit is set (intersectArrayBitmap roaring.go:3404)
+            const uint16_t* vals = reinterpret_cast<const uint16_t*>(st4) + tid * 16;
+            const uint32_t first = uint32_t(tid) * 16;
+            uint32_t keep = 0;
+            for (uint32_t k = 0; k < 16 && first + k < len; k++) {
+              const uint32_t val = vals[k];
+              if ((s_win[val >> 5] >> (val & 31)) & 1u) keep |= 1u << k;
+            }
+            fold_bar();  // every probe is done before the window is rebuilt
+            win4[tid] = zero4; win4[tid + kFoldThreads] = zero4;
+            fold_bar();
+            for (uint32_t k = 0; k < 16; k++)
+              if ((keep >> k) & 1u) { const uint32_t val = vals[k]; atomicOr(&s_win[val >> 5], 1u << (val & 31)); }
+          }
+        } else {  // run list
+          uint32_t* scratch = const_cast<uint32_t*>(reinterpret_cast<const uint32_t*>(st4));
+          if (op == I_OR_LEAF) fold_runs_scan<I_OR_LEAF>(s_win, scratch, len, s_red, tid);
+          else if (op == I_XOR_LEAF) fold_runs_scan<I_XOR_LEAF>(s_win, scratch, len, s_red, tid);
+          else if (op == I_ANDNOT_LEAF) fold_runs_scan<I_ANDNOT_LEAF>(s_win, scratch, len, s_red, tid);
+          else fold_runs_scan<I_AND_LEAF>(s_win, scratch, len, s_red, tid);
+        }
+      }
+      fold_bar();  // the operand is applied by every consumer
+      if (staged) {
+        if (tid == 0) {  // its staging slot goes back to the producer (the run scan wrote to it: order those writes before the copy engine's)
+          fence_proxy_async();
+          mbar_arrive(&s_empty[slot]);
+        }
+        g++;
+      }
+    }
+
+    const uint4 a = win4[tid], b = win4[tid + kFoldThreads];
+    uint32_t cnt = popc128(a) + popc128(b);
+    if (p.dense_out) {
+      uint4* dout = reinterpret_cast<uint4*>(p.dense_out + m.item * kBitmapBytes);
+      dout[tid] = a; dout[tid + kFoldThreads] = b;
+    }
+    cnt = warp_sum(cnt);
+    if (lane == 0) s_red[tid >> 5] = cnt;
+    fold_bar();
+    if (tid == 0) {
+      uint32_t tot = 0;
+#pragma unroll
+      for (int w = 0; w < kFoldThreads / 32; w++) tot += s_red[w];
+      if (p.out_counts && tot) atomicAdd(p.out_counts + uint64_t(m.q) * p.out_qstride + uint64_t(m.s) * p.out_sstride, (unsigned long long)tot);
+      if (p.dense_n) p.dense_n[m.item] = tot;
+      mbar_arrive(&s_mempty[ms]);  // the item's descriptors are no longer needed
+    }
+    fold_bar();  // s_red and the window are free for the next item
   }
 }
 

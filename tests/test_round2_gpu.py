@@ -163,3 +163,230 @@ def test_timing_after_failed_count(eng_orc):
         eng.count(bad, [0])
     eng.bsi_sum(fam, 10, None, [0])
     assert eng.last_timing().algo_bytes == want
+
+
+def _cont(kind, vals):
+    """(type, n, payload) of a container holding `vals` (sorted) in the given encoding."""
+    vals = sorted(vals)
+    if kind == "a":
+        return 1, len(vals), struct.pack("<%dH" % len(vals), *vals)
+    if kind == "b":
+        words = [0] * 1024
+        for v in vals:
+            words[v >> 6] |= 1 << (v & 63)
+        return 2, len(vals), struct.pack("<1024Q", *words)
+    runs, st, prev = [], None, None
+    for v in vals:
+        if st is None:
+            st = prev = v
+        elif v == prev + 1:
+            prev = v
+        else:
+            runs.append((st, prev))
+            st = prev = v
+    runs.append((st, prev))
+    return 3, len(vals), struct.pack("<H", len(runs)) + b"".join(struct.pack("<HH", a, b) for a, b in runs)
+
+
+def test_fold_kernel_edge_patterns(eng_orc):
+    """The encoding-native fold evaluator (eval_fold_kernel) on hand-made containers: run lists with the maximum of 2048
+    runs, runs touching 0 and 65535, values packed into one word or spread one per word, arrays of 1 / 4095 / 4096
+    values — every ordered pair under all four operations, and left folds of three and four operands, against the oracle."""
+    import itertools
+
+    eng, orc = eng_orc
+    g, c = Executor(eng), Executor(orc)
+    for ex in (g, c):
+        ex.create_field("e")
+    rnd = __import__("random").Random(5)
+    pats = [
+        ("a", [7]),                                               # one value
+        ("a", list(range(64, 96))),                               # one word full of values, array-encoded
+        ("a", list(range(0, 65536, 16))[:4095]),                  # 4095 values, one or two per word
+        ("a", sorted(rnd.sample(range(65536), 4096))),            # ArrayMaxSize values, unoptimized
+        ("a", [0, 31, 32, 63, 65504, 65535]),                     # word and container boundaries
+        ("r", [v for k in range(2048) for v in (32 * k, 32 * k + 1)]),              # 2048 runs: the run maximum
+        ("r", [v for k in range(2048) for v in range(32 * k + 30, 32 * k + 32)]),   # 2048 runs ending on word boundaries, last at 65535
+        ("r", list(range(0, 40000))),                             # one long run from 0
+        ("r", list(range(100, 65536))),                           # one long run to 65535
+        ("r", list(range(5, 9)) + list(range(40, 2000)) + list(range(2001, 2003)) + list(range(60000, 65000))),
+        ("r", [v for k in range(300) for v in range(200 * k, 200 * k + 150)]),       # 300 medium runs
+        ("b", sorted(rnd.sample(range(65536), 30000))),
+        ("b", sorted(rnd.sample(range(65536), 5000))),
+    ]
+    cs = []
+    for row, (kind, vals) in enumerate(pats):
+        t, n, pl = _cont(kind, vals)
+        cs.append((row * 16 + 5, t, n, pl))
+        if row % 3 == 0:   # a second column so that items differ inside one query
+            t2, n2, pl2 = _cont("b", sorted(rnd.sample(range(65536), 20000)))
+            cs.append((row * 16 + 9, t2, n2, pl2))
+    cs.sort()
+    data = pilosa_file(cs)
+    for ex in (g, c):
+        ex.load_fragment("e", 0, data)
+    sets = [set(v) for _, v in pats]
+    R = lambda i: Row("e", i)  # noqa: E731
+    calls, want = [], []
+    ops = [(Intersect, lambda a, b: a & b), (abi.Union, lambda a, b: a | b), (abi.Xor, lambda a, b: a ^ b), (abi.Difference, lambda a, b: a - b)]
+    for i, j in itertools.permutations(range(len(pats)), 2):
+        for op, _ in ops:
+            calls.append(op(R(i), R(j)))
+    for trip in ((0, 5, 11), (5, 2, 8), (8, 6, 3), (11, 5, 6), (3, 9, 10), (6, 7, 12), (9, 3, 5), (2, 10, 7), (12, 6, 9), (7, 8, 5)):
+        for op, _ in ops:
+            calls.append(op(*[R(i) for i in trip]))
+            calls.append(op(R(trip[0]), R(trip[1]), R(trip[2]), R(trip[1]), R(4)))
+    got = []
+    for k in range(0, len(calls), 256):
+        got += g.count_batch(calls[k:k + 256], [0])
+    exp = [c.count(x, [0]) for x in calls]
+    bad = [(repr(calls[k]), got[k], exp[k]) for k in range(len(calls)) if got[k] != exp[k]]
+    assert not bad, bad[:5]
+    # column 5 alone, from the sets (pins the oracle on these patterns as well)
+    for (i, j), (op, f) in itertools.product(((2, 5), (5, 6), (3, 9), (7, 8)), ops):
+        cols = [v for v in g.row_columns(op(R(i), R(j)), [0]) if (v >> 16) == 5]
+        assert [v & 0xffff for v in cols] == sorted(f(sets[i], sets[j])), (i, j, op)
+
+
+def test_writes_on_the_resident_copy_interleaved_with_queries(eng_orc):
+    """pb200_frag_apply / pb200_frag_import_roaring rewrite only the touched containers of the resident fragment (a kernel
+    per write, nothing of the fragment crosses PCIe): single bits, batches, new rows inside and far outside a dense row
+    table (the table is rebuilt on the device, dense -> sparse), rows emptied again, imports that add and subtract, all
+    interleaved with queries and compared with the oracle after every step."""
+    import random
+    import time
+
+    eng, orc = eng_orc
+    g, c = Executor(eng), Executor(orc)
+    for ex in (g, c):
+        ex.create_field("f")
+        ex.create_field("m")
+    shards = [0, 1]
+    for s in shards:
+        fb, mb = synth.bernoulli(s, 0, 64, 0.10), synth.mixed(s, 0, 8)
+        for ex in (g, c):
+            ex.load_fragment("f", s, fb)
+            ex.load_fragment("m", s, mb)
+    ff, fm = g.family("f"), g.family("m")
+    cf, cm = c.family("f"), c.family("m")
+    rnd = random.Random(17)
+
+    def check(rows_f=(0, 1, 2, 63, 64, 70, 5000), rows_m=(0, 1, 2, 3, 9)):
+        calls = [Row("f", r) for r in rows_f] + [Row("m", r) for r in rows_m]
+        calls += [Intersect(Row("f", 1), Row("f", 70)), abi.Union(Row("m", 0), Row("m", 9), Row("f", 5000)), abi.Xor(Row("m", 1), Row("m", 2), Row("f", 2)),
+                  abi.Difference(Row("f", 0), Row("m", 3), Row("f", 64))]
+        assert g.count_batch(calls, shards) == [c.count(x, shards) for x in calls]
+        for fld in ("f", "m"):
+            assert g.rows(fld, shards) == c.rows(fld, shards), fld
+        for call in (Row("f", 70), Row("m", 9), abi.Union(Row("m", 0), Row("m", 1))):
+            assert g.row_segments(call, shards) == c.row_segments(call, shards), repr(call)
+        assert g.topn("m", shards, n=5) == c.topn("m", shards, n=5)
+        assert g.topn("f", shards, n=4, src=Row("m", 1)) == c.topn("f", shards, n=4, src=Row("m", 1))
+
+    def both_apply(fg, fc, shard, sets, clears):
+        eng.frag_apply(fg, shard, sets, clears)
+        orc.frag_import_positions(fc, shard, sets, clears)
+
+    check()
+    # one bit, timed and metered: a write must move bytes, not the fragment (64 rows x 128 KiB here)
+    pos = 1 * SW + 12345
+    both_apply(ff, cf, 0, [pos], [])
+    t0 = time.perf_counter()
+    both_apply(ff, cf, 0, [2 * SW + 777], [])
+    dt = time.perf_counter() - t0
+    tm = eng.last_timing()
+    assert tm.h2d_bytes + tm.d2h_bytes < 65536, (tm.h2d_bytes, tm.d2h_bytes)
+    assert dt < 0.05
+    check()
+    # new rows: inside the dense table's slack, then far outside (the table turns sparse), then in between
+    both_apply(ff, cf, 0, [64 * SW + 5, 64 * SW + 6, 70 * SW + 99999], [])
+    check()
+    both_apply(ff, cf, 1, [5000 * SW + 1, 5000 * SW + 70000, 70 * SW + 3], [1 * SW + 3])
+    check()
+    both_apply(ff, cf, 1, [300 * SW + k * 17 for k in range(5000)], [])     # an array container grows into a bitmap / runs
+    both_apply(ff, cf, 1, [], [300 * SW + k * 17 for k in range(0, 5000, 2)])
+    check(rows_f=(0, 1, 70, 300, 5000))
+    # a row emptied again, and clears on rows / containers that do not exist
+    both_apply(ff, cf, 0, [], [64 * SW + 5, 64 * SW + 6, 9999 * SW + 1, 3 * SW + 5])
+    check()
+    assert 64 not in g.rows("f", [0])
+    # mixed containers: random batches of sets and clears over existing containers of every type
+    for step in range(4):
+        sets = [rnd.randrange(10) * SW + rnd.randrange(SW) for _ in range(400)]
+        clears = [rnd.randrange(10) * SW + rnd.randrange(SW) for _ in range(400)]
+        both_apply(fm, cm, step % 2, sets, clears)
+        check()
+    # imports: union and subtraction of serialized bitmaps, Pilosa format, into existing and new rows
+    imp = synth.mixed(0, 7, 4).bytes()     # rows 7..10 of the generator
+    for clear in (False, True, False):
+        assert eng.frag_import_roaring(fm, 0, imp, clear) == orc.frag_import_roaring(cm, 0, imp, clear)
+        check()
+    assert eng.rank_get(fm, 0) == orc.rankings(cm, 0)
+    # a reload replaces the written copy wholesale
+    fb = synth.bernoulli(0, 0, 64, 0.10)
+    for ex in (g, c):
+        ex.load_fragment("f", 0, fb)
+    check()
+
+
+def test_sixteen_host_threads_on_one_context():
+    """examples/concurrent_c: 16 OS threads x 1000 single pb200_count calls on ONE context; every answer is checked
+    against the single-threaded one inside the program (which exits non-zero on any difference), and the combining
+    queue must lift the aggregate rate well above the one-call-at-a-time rate."""
+    import json
+    import os
+    import subprocess
+
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples", "concurrent_c")
+    out = subprocess.run([exe, "16", "1000"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    rec = json.loads(out.stdout.strip().splitlines()[-1])
+    assert rec["speedup"] >= 3.0, rec
+
+
+def test_concurrent_counts_match_oracle(eng_orc):
+    """The same from Python threads with DIFFERENT programs and shard lists in flight together (ctypes drops the GIL
+    inside the call): requests with equal shard lists are combined into one batch, the others run in their own rounds,
+    a malformed program fails alone — every result equals the oracle's."""
+    import threading
+
+    eng, orc = eng_orc
+    g, c = Executor(eng), Executor(orc)
+    for ex in (g, c):
+        ex.create_field("f")
+        ex.create_field("m")
+    shards = [0, 1, 2]
+    for s in shards:
+        fb, mb = synth.bernoulli(s, 0, 8, 0.10), synth.mixed(s, 0, 6)
+        for ex in (g, c):
+            ex.load_fragment("f", s, fb)
+            ex.load_fragment("m", s, mb)
+    calls = [Intersect(Row("f", a), Row("f", b)) for a in range(8) for b in range(a)] + [abi.Union(Row("m", a), Row("m", (a + 1) % 6), Row("f", a)) for a in range(6)]
+    lists = [shards, [0], [2, 1], shards]
+    want = {(i, j): c.count(call, lists[j]) for i, call in enumerate(calls) for j in range(len(lists))}
+    progs = [g.program(x) for x in calls]
+    errors, bad_seen = [], []
+
+    def worker(tid):
+        for k in range(150):
+            i, j = (tid * 31 + k * 7) % len(calls), (tid + k) % len(lists)
+            try:
+                got = eng.count(progs[i], lists[j])
+                if got != want[(i, j)]:
+                    errors.append((tid, i, j, got, want[(i, j)]))
+            except Exception as e:  # noqa: BLE001
+                errors.append((tid, i, j, repr(e)))
+            if k % 50 == 7:
+                try:
+                    eng.count((abi.Node * 1)(abi.Node(op=abi.OP_INTERSECT, nargs=0)), lists[j])
+                    errors.append((tid, "malformed program accepted"))
+                except Exception:  # noqa: BLE001
+                    bad_seen.append(tid)
+
+    th = [threading.Thread(target=worker, args=(t,)) for t in range(12)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errors, errors[:5]
+    assert len(bad_seen) == 12 * 3

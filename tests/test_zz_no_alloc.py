@@ -4,8 +4,9 @@ deployment whose whole HBM budget went to fragments, a query thread that must ne
 the driver's allocator). Its scratch is a fixed array inside the library, shared by every
 call on the device, so the test calls it twice in a row with different inputs — the second
 call must not see anything the first one left behind — and checks both answers against the
-ordinary allocating entry point (pb200_count_batch); integer results, so the tolerance is
-exact equality, as everywhere else in this suite.
+ordinary allocating entry point (pb200_count_batch) and, so that the two engine paths cannot
+agree on a common mistake, against the CPU oracle holding the same fragments; integer
+results, so the tolerance is exact equality, as everywhere else in this suite.
 
 Named test_zz_* so pytest collects it last: if it fails under -x every other test has
 already run. It builds its own engine and index, so it also passes alone in a fresh process.
@@ -34,21 +35,30 @@ def test_count_pairs_noalloc_matches_allocating_entry_point_twice_in_a_row():
     stream = torch.cuda.Stream()
     eng.set_stream(stream.cuda_stream)
     fam = eng.family_create()
+    import oracle  # the checker; also used to splice two generated fragments into one file image
+
+    orc = oracle.Oracle(workers=2)
+    ofam = orc.family_create()
     shards = [0, 1, 2, 4]
     for s in shards:
         # rows 0-7: mixed array / bitmap / run containers (exercises the deferred-item list that
         # lives in the fixed scratch array); rows 8-11 dense bitmaps. One fragment per shard.
-        import oracle  # only to splice two generated fragments into one file image
-
         a = oracle.Bitmap.deserialize(synth.mixed(s, 0, 8).bytes())
         b = oracle.Bitmap.deserialize(synth.bernoulli(s, 8, 4, 0.10).bytes())
-        eng.frag_load(fam, s, a.union(b).serialize())
+        image = a.union(b).serialize()
+        eng.frag_load(fam, s, image)
+        orc.frag_load(ofam, s, image)
     rnd = random.Random(11)
     rows = list(range(12)) + [40]  # 40: a row that does not exist
     batches = [[(rnd.choice(rows), rnd.choice(rows)) for _ in range(n)] for n in (37, 64)]
     # the ordinary entry point first: it also refreshes the device-side fragment tables,
     # which the allocation-free path refuses to do itself
     expected = [_expected(eng, fam, pairs, shards + [3]) for pairs in batches]
+    from pilosa_b200 import abi
+
+    for pairs, exp in zip(batches, expected):  # the allocating entry point itself agrees with the oracle
+        want = [orc.count(abi.flatten(abi.Intersect(abi.Row("f", a), abi.Row("f", b)), lambda f, v: ofam), shards + [3]) for a, b in pairs]
+        assert exp == want
 
     with torch.cuda.stream(stream):
         d_shards = torch.tensor(shards + [3], dtype=torch.int64, device="cuda")  # shard 3 has no fragment
