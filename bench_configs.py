@@ -189,10 +189,15 @@ def main():
         load_parallel(lambda s: synth.bernoulli(s, 1, 2, 0.10, SEED), shards, sinks_for("a", set(cpu_sh)), cores)
         print(f"# c3 loaded in {time.perf_counter() - t0:.1f}s", file=sys.stderr)
         src = Intersect(Row("a", 1), Row("a", 2))
-        for qname, kw in ((f"TopN(z, Intersect(Row(a=1),Row(a=2)), n=50) [{args.c3_rows} rows]", dict(n=50, src=src)),
-                          ("TopN(z, n=50) [no source: rank cache only]", dict(n=50))):
+        # SURVEY 8d asks for both byte figures: A_pruned = what fragment.top's walk visits (the engine's default: it prunes
+        # by the reference's own rule on the device), A_full = every ranked row (pruning switched off)
+        for qname, kw, prune in ((f"TopN(z, Intersect(Row(a=1),Row(a=2)), n=50) [{args.c3_rows} rows] A_pruned", dict(n=50, src=src), 1),
+                                 (f"TopN(z, Intersect(Row(a=1),Row(a=2)), n=50) [{args.c3_rows} rows] A_full (pruning off)", dict(n=50, src=src), 0),
+                                 ("TopN(z, n=50) [no source: rank cache only]", dict(n=50), 1)):
+            eng.set_option(3, prune)  # PB200_OPT_TOPN_PRUNE
             _, k, wms, ab, ln = timed(eng, lambda: g.topn("z", shards, **kw), max(3, args.reps // 2))
             got = g.topn("z", cpu_sh, **kw)
+            eng.set_option(3, 1)
             exp, cms = cpu_timed(lambda: c.topn("z", cpu_sh, **kw))
             emit(rows, "C3", qname, len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
 

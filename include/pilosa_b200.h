@@ -326,6 +326,11 @@ int pb200_eval_proto_columns(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_
 /* PB200_OPT_RANK_CACHE_SIZE (default 50000 = DefaultCacheSize, field.go:47): entries the rank
  * cache of a fragment keeps (rankCache.maxEntries); applies to rankings derived after the call. */
 #define PB200_OPT_RANK_CACHE_SIZE 2u
+/* PB200_OPT_TOPN_PRUNE (default 1): TopN with a source row counts, per shard, only the ranked rows fragment.top's walk
+ * visits (fragment.go:1673-1688: it stops at the first row whose cached count is below the smallest count among the
+ * first n pushed) — the head of the ranking first, the stop position derived on the device, then the rest up to it.
+ * 0 counts every ranked row (same results; for measuring both byte figures of SURVEY.md 8d, A_full and A_pruned). */
+#define PB200_OPT_TOPN_PRUNE 3u
 int pb200_set_option(pb200_ctx* ctx, uint32_t option, uint64_t value);
 
 /* Page-lock a caller-owned host buffer (cudaHostRegister) so that result copies into it — the

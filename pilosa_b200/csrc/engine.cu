@@ -83,6 +83,60 @@ struct DeviceGuard {  // make ctx->device current for the duration of a call
   DeviceGuard guard__((ctx)->device);                \
   (ctx)->err.clear()
 
+namespace {
+
+// A persistent host thread: issues work for one device of a pb200_multi, or runs a slice of a host-side shard loop. Hand-off is a spin on an atomic for a short while after each job
+// (a burst of queries finds the worker awake: ~1 us) and a condition variable after that.
+class DevWorker {
+ public:
+  DevWorker() : th_([this] { loop(); }) {}
+  ~DevWorker() {
+    { std::lock_guard<std::mutex> g(mu_); stop_ = true; }
+    cv_.notify_all();
+    th_.join();
+  }
+  void post(std::function<int()> fn) {
+    fn_ = std::move(fn);
+    state_.store(1, std::memory_order_release);
+    { std::lock_guard<std::mutex> g(mu_); }
+    cv_.notify_one();
+  }
+  int wait() {
+    for (uint32_t spins = 0; state_.load(std::memory_order_acquire) != 2; spins++)
+      if (spins > 2000) std::this_thread::yield();
+    state_.store(0, std::memory_order_relaxed);
+    return rc_;
+  }
+
+ private:
+  void loop() {
+    for (;;) {
+      bool have = false;
+      const auto t0 = std::chrono::steady_clock::now();
+      for (uint32_t spins = 0;; spins++) {
+        if (state_.load(std::memory_order_acquire) == 1) { have = true; break; }
+        if ((spins & 255) == 255 && std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(200)) break;
+      }
+      if (!have) {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [&] { return stop_ || state_.load(std::memory_order_acquire) == 1; });
+        if (stop_) return;
+      }
+      rc_ = fn_();
+      state_.store(2, std::memory_order_release);
+    }
+  }
+  std::function<int()> fn_;
+  int rc_ = 0;
+  std::atomic<int> state_{0};  // 0 idle, 1 job posted, 2 job done
+  std::mutex mu_;
+  std::condition_variable cv_;
+  bool stop_ = false;
+  std::thread th_;
+};
+
+}  // namespace
+
 // ---------------------------------------------------------------------------------------
 // lifecycle
 // ---------------------------------------------------------------------------------------
@@ -149,6 +203,7 @@ static void free_fragment(Fragment& f) {
   if (f.d_rank) cudaFree(f.d_rank);
   f.blob = nullptr;
   f.d_rank = nullptr;
+  f.d_rank_counts = nullptr;
   f.d_rank_valid = false;
   f.rank_pos_valid = false;
 }
@@ -164,7 +219,7 @@ extern "C" int pb200_shutdown(pb200_ctx* ctx) {
       if (fam.d_frags) cudaFree(fam.d_frags);
     }
     if (ctx->d_families) cudaFree(ctx->d_families);
-    for (DevBuf* b : {&ctx->d_rows, &ctx->d_rows_off, &ctx->d_rows_meta, &ctx->d_rows_item_off, &ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi, &ctx->d_ing, &ctx->d_ing_res})
+    for (DevBuf* b : {&ctx->d_rows, &ctx->d_rows_off, &ctx->d_rows_meta, &ctx->d_rows_item_off, &ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi, &ctx->d_ing, &ctx->d_ing_res, &ctx->d_topn_compact})
       if (b->p) cudaFree(b->p);
     for (auto& r : ctx->arena.retired) cudaFree(r.first);
     if (ctx->arena.base) cudaFree(ctx->arena.base);
@@ -476,6 +531,9 @@ extern "C" int pb200_set_option(pb200_ctx* ctx, uint32_t option, uint64_t value)
       if (value > kBitmapBytes) return fail(ctx, PB200_ERR_INVALID, "densify threshold above 8192 bytes");
       ctx->densify_min_bytes = uint32_t(value);
       return PB200_OK;
+    case PB200_OPT_TOPN_PRUNE:
+      ctx->topn_prune = value != 0;
+      return PB200_OK;
     case PB200_OPT_RANK_CACHE_SIZE:
       if (value == 0 || value > 0xffffffffull) return fail(ctx, PB200_ERR_INVALID, "rank cache size out of range");
       ctx->rank_cache_size = uint32_t(value);
@@ -659,7 +717,7 @@ struct Compiler {
     if (maxsp > kMaxStack) { err = "expression too deeply nested (stack depth > 4)"; return false; }
     if (ins.size() > size_t(kMaxInstr)) { err = "expression too long (> 64 instructions)"; return false; }
     for (size_t k = 0; k < ins.size(); k++)
-      if ((k > 0 && ins[k].op == I_LOAD) || ins[k].op >= I_AND_STACK || ins[k].op == I_RANDNOT_LEAF) out.any_bushy = true;
+      if ((k > 0 && ins[k].op == I_LOAD) || (k > 0 && ins[k].op != I_AND_LEAF && ins[k].op != I_OR_LEAF)) out.any_bushy = true;  // what fold_can_take refuses
     pg.instr_off = uint32_t(out.instrs.size());
     pg.n_instr = uint32_t(ins.size());
     pg.leaf_off = leaf_base;
@@ -1146,27 +1204,52 @@ void run_count_group(pb200_ctx* ctx, std::vector<CountReq*>& grp) {
 int combine_counts(pb200_ctx* ctx, CountReq& me) {
   std::unique_lock<std::mutex> lk(ctx->cq_mu);
   ctx->cq.push_back(&me);
-  while (!me.done) {
-    if (ctx->cq_busy) { ctx->cq_cv.wait(lk); continue; }
-    ctx->cq_busy = true;  // this thread combines until its own request has been served; a waiting thread takes over then
-    while (!me.done && !ctx->cq.empty()) {
-      std::vector<CountReq*> grp, rest;
-      CountReq* head = ctx->cq.front();
-      for (CountReq* r : ctx->cq) {
-        const bool same = grp.size() < kCombineMax && r->n_shards == head->n_shards && r->n_nodes && r->prog && r->out &&
-                          (r->n_shards == 0 || (r->shards && head->shards && std::memcmp(r->shards, head->shards, size_t(r->n_shards) * 8) == 0));
-        (r == head || same ? grp : rest).push_back(r);
+  while (!me.done.load(std::memory_order_acquire)) {
+    if (!ctx->cq_busy.load(std::memory_order_relaxed)) {
+      ctx->cq_busy.store(true, std::memory_order_relaxed);  // this thread combines until its own request has been served; a waiting thread takes over then
+      while (!me.done.load(std::memory_order_relaxed) && !ctx->cq.empty()) {
+        // The callers of the last round are on their way back with their next request: when that round was a batch, give
+        // them a few microseconds to arrive so that this launch is as wide (a lone caller never waits: last round = 1).
+        if (ctx->cq_last > 1 && ctx->cq.size() < ctx->cq_last) {
+          lk.unlock();
+          const auto t0 = std::chrono::steady_clock::now();
+          for (int i = 0; i < 4000; i++) {
+            if ((i & 15) == 15 && std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(12)) break;
+            __builtin_ia32_pause();
+          }
+          lk.lock();
+        }
+        std::vector<CountReq*> grp, rest;
+        CountReq* head = ctx->cq.front();
+        for (CountReq* r : ctx->cq) {
+          const bool same = grp.size() < kCombineMax && r->n_shards == head->n_shards && r->n_nodes && r->prog && r->out &&
+                            (r->n_shards == 0 || (r->shards && head->shards && std::memcmp(r->shards, head->shards, size_t(r->n_shards) * 8) == 0));
+          (r == head || same ? grp : rest).push_back(r);
+        }
+        ctx->cq.swap(rest);
+        ctx->cq_last = grp.size();
+        lk.unlock();
+        run_count_group(ctx, grp);
+        lk.lock();
+        for (CountReq* r : grp) r->done.store(true, std::memory_order_release);  // last access to r: its owner may return now
       }
-      ctx->cq.swap(rest);
-      lk.unlock();
-      run_count_group(ctx, grp);
-      lk.lock();
-      for (CountReq* r : grp) r->done = true;
+      ctx->cq_busy.store(false, std::memory_order_release);
       ctx->cq_cv.notify_all();
+      continue;
     }
-    ctx->cq_busy = false;
-    ctx->cq_cv.notify_all();
+    // Somebody else is combining. A launch takes tens of microseconds: spin that long before sleeping — a futex wake-up
+    // costs as much as the launch and would leave the GPU idle between rounds.
+    lk.unlock();
+    bool progress = false;
+    for (int i = 0; i < 3000 && !progress; i++) {
+      progress = me.done.load(std::memory_order_acquire) || !ctx->cq_busy.load(std::memory_order_acquire);
+      if (!progress) __builtin_ia32_pause();
+    }
+    lk.lock();
+    if (!progress && !me.done.load(std::memory_order_acquire) && ctx->cq_busy.load(std::memory_order_relaxed))
+      ctx->cq_cv.wait_for(lk, std::chrono::microseconds(200));
   }
+  lk.unlock();
   if (me.rc != PB200_OK) { std::lock_guard<std::mutex> lock(ctx->mu); ctx->err = me.err; }
   return me.rc;
 }

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <condition_variable>
 #include <functional>
 #include <mutex>
@@ -48,7 +49,8 @@ struct Fragment {
   // (pb200_rank_set) or derived from exact row counts (count desc, id asc, 50000 entries).
   std::vector<uint64_t> rank_ids, rank_counts;
   bool rank_from_host = false;
-  uint32_t* d_rank = nullptr;  // device copy of the rank order as row-table indices (TopN)
+  uint32_t* d_rank = nullptr;  // device copy of the rank order as row-table indices (TopN) ...
+  uint64_t* d_rank_counts = nullptr;  // ... and of the cached counts in rank order (same allocation)
   bool d_rank_valid = false;
   std::vector<uint32_t> rank_pos_of_row;  // rank position of row_ids[j] (0xffffffff: not ranked); host index for TopN pass 2
   bool rank_pos_valid = false;
@@ -115,7 +117,7 @@ struct CountReq {
   const uint64_t* shards; uint32_t n_shards;
   uint64_t* out;
   int rc = 0;
-  bool done = false;
+  std::atomic<bool> done{false};
   std::string err;
 };
 }  // namespace pb200
@@ -126,7 +128,8 @@ struct pb200_ctx {
   std::mutex cq_mu;
   std::condition_variable cq_cv;
   std::vector<pb200::CountReq*> cq;
-  bool cq_busy = false;
+  std::atomic<bool> cq_busy{false};
+  size_t cq_last = 0;  // requests in the last round
   uint64_t cq_batches = 0, cq_queries = 0;  // statistics: launches made for how many single-query calls
   int sm_count = 148;
   size_t budget = 0, used = 0;
@@ -148,7 +151,8 @@ struct pb200_ctx {
   unsigned long long* dense_ovf_dev = nullptr;
   pb200::DevBuf d_batch, d_out, d_slow, d_temp, d_dense, d_dense_n, d_misc, d_topn, d_bsi;
   pb200::PinBuf h_stage, h_out, h_algo, h_topn, h_ing, h_ing_res;
-  pb200::DevBuf d_ing, d_ing_res;
+  pb200::DevBuf d_ing, d_ing_res, d_topn_compact;
+  bool topn_prune = true;  // PB200_OPT_TOPN_PRUNE
   pb200::WriteArena arena;
   uint32_t densify_min_bytes = 0;  // PB200_OPT_DENSIFY_MIN_BYTES (0 = containers stay as loaded)
   uint32_t rank_cache_size = 50000;  // PB200_OPT_RANK_CACHE_SIZE (field.go:47 DefaultCacheSize)

@@ -17,56 +17,6 @@
 
 namespace {
 
-// A host thread that issues work for one device. Hand-off is a spin on an atomic for a short while after each job
-// (a burst of queries finds the worker awake: ~1 us) and a condition variable after that.
-class DevWorker {
- public:
-  DevWorker() : th_([this] { loop(); }) {}
-  ~DevWorker() {
-    { std::lock_guard<std::mutex> g(mu_); stop_ = true; }
-    cv_.notify_all();
-    th_.join();
-  }
-  void post(std::function<int()> fn) {
-    fn_ = std::move(fn);
-    state_.store(1, std::memory_order_release);
-    { std::lock_guard<std::mutex> g(mu_); }
-    cv_.notify_one();
-  }
-  int wait() {
-    for (uint32_t spins = 0; state_.load(std::memory_order_acquire) != 2; spins++)
-      if (spins > 2000) std::this_thread::yield();
-    state_.store(0, std::memory_order_relaxed);
-    return rc_;
-  }
-
- private:
-  void loop() {
-    for (;;) {
-      bool have = false;
-      const auto t0 = std::chrono::steady_clock::now();
-      for (uint32_t spins = 0;; spins++) {
-        if (state_.load(std::memory_order_acquire) == 1) { have = true; break; }
-        if ((spins & 255) == 255 && std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(200)) break;
-      }
-      if (!have) {
-        std::unique_lock<std::mutex> lk(mu_);
-        cv_.wait(lk, [&] { return stop_ || state_.load(std::memory_order_acquire) == 1; });
-        if (stop_) return;
-      }
-      rc_ = fn_();
-      state_.store(2, std::memory_order_release);
-    }
-  }
-  std::function<int()> fn_;
-  int rc_ = 0;
-  std::atomic<int> state_{0};  // 0 idle, 1 job posted, 2 job done
-  std::mutex mu_;
-  std::condition_variable cv_;
-  bool stop_ = false;
-  std::thread th_;
-};
-
 struct FamStat {  // what the router knows about a family: bytes and rows resident over all devices
   std::unordered_map<uint64_t, std::pair<uint64_t, uint64_t>> per_shard;  // shard -> (rows, payload bytes)
   uint64_t rows = 0, bytes = 0;

@@ -364,22 +364,32 @@ void sort_pairs(std::vector<HPair>& p) {  // count desc; ties by ascending id (d
 
 // Host-side shard loop on a few threads (the reference runs its per-shard jobs on a worker
 // pool of NumCPU goroutines, executor.go:83-107; the selection walks are independent per shard).
+// persistent helper threads of the host-side shard loops (started once per process; a TopN call makes three of these
+// loops and thread start-up was a visible part of it); a second caller that finds them busy runs its loop inline
+std::mutex& host_pool_mutex() { static std::mutex mu; return mu; }
+std::vector<std::unique_ptr<DevWorker>>& host_pool() { static std::vector<std::unique_ptr<DevWorker>> pool; return pool; }
+
 template <class F>
 void parallel_shards(uint32_t n, F&& fn) {
+  std::mutex& pool_mu = host_pool_mutex();
+  std::vector<std::unique_ptr<DevWorker>>& pool = host_pool();
   unsigned hw = std::thread::hardware_concurrency();
-  unsigned nt = std::min<unsigned>(hw ? hw : 4, 8);
-  if (n < 256 || nt < 2) { for (uint32_t s = 0; s < n; s++) fn(s); return; }
-  std::vector<std::thread> th;
+  const unsigned nt = std::min<unsigned>(hw ? hw : 4, 12);
+  std::unique_lock<std::mutex> lk(pool_mu, std::try_to_lock);
+  if (n < 256 || nt < 2 || !lk.owns_lock()) { for (uint32_t s = 0; s < n; s++) fn(s); return; }
+  if (pool.empty()) for (unsigned t = 0; t + 1 < nt; t++) pool.emplace_back(new DevWorker());
   std::atomic<uint32_t> next{0};
-  for (unsigned t = 0; t < nt; t++)
-    th.emplace_back([&] {
-      for (;;) {
-        uint32_t b = next.fetch_add(32);
-        if (b >= n) break;
-        for (uint32_t s = b; s < std::min(n, b + 32); s++) fn(s);
-      }
-    });
-  for (auto& t : th) t.join();
+  auto body = [&]() -> int {
+    for (;;) {
+      const uint32_t b = next.fetch_add(16);
+      if (b >= n) break;
+      for (uint32_t s = b; s < std::min(n, b + 16); s++) fn(s);
+    }
+    return 0;
+  };
+  for (auto& w : pool) w->post(body);
+  body();
+  for (auto& w : pool) w->wait();
 }
 
 // fragment.top (fragment.go:1568-1700) over candidates (ids[k], cached counts[k]) whose
@@ -432,10 +442,12 @@ uint64_t exact_row_count(const Fragment& f, uint64_t id) {
 // changes (load / pb200_rank_set), reused by every TopN call.
 int ensure_rank_table(pb200_ctx* ctx, Fragment& f) {
   if (f.d_rank_valid) return PB200_OK;
-  if (f.d_rank) { CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream)); CUDA_TRY(ctx, cudaFree(f.d_rank)); f.d_rank = nullptr; }
+  if (f.d_rank) { CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream)); CUDA_TRY(ctx, cudaFree(f.d_rank)); f.d_rank = nullptr; f.d_rank_counts = nullptr; }
   const size_t n = f.rank_ids.size();
   if (n) {
-    std::vector<uint32_t> idx(n);
+    const size_t o_cnt = align_up(n * 4, 16);
+    std::vector<uint8_t> h(o_cnt + n * 8);
+    uint32_t* idx = reinterpret_cast<uint32_t*>(h.data());
     for (size_t k = 0; k < n; k++) {
       const uint64_t id = f.rank_ids[k];
       if (f.dev.dense) idx[k] = id < f.dev.nrows ? uint32_t(id) : 0xffffffffu;
@@ -444,8 +456,12 @@ int ensure_rank_table(pb200_ctx* ctx, Fragment& f) {
         idx[k] = (it != f.row_ids.end() && *it == id) ? uint32_t(it - f.row_ids.begin()) : 0xffffffffu;
       }
     }
-    CUDA_TRY(ctx, cudaMalloc(&f.d_rank, n * 4));
-    CUDA_TRY(ctx, cudaMemcpy(f.d_rank, idx.data(), n * 4, cudaMemcpyHostToDevice));
+    std::memcpy(h.data() + o_cnt, f.rank_counts.data(), n * 8);
+    void* d = nullptr;
+    CUDA_TRY(ctx, cudaMalloc(&d, h.size()));
+    CUDA_TRY(ctx, cudaMemcpy(d, h.data(), h.size(), cudaMemcpyHostToDevice));
+    f.d_rank = static_cast<uint32_t*>(d);
+    f.d_rank_counts = reinterpret_cast<uint64_t*>(static_cast<uint8_t*>(d) + o_cnt);
   }
   f.d_rank_valid = true;
   return PB200_OK;
@@ -458,7 +474,8 @@ int ensure_rank_table(pb200_ctx* ctx, Fragment& f) {
 // ids, executor.go:889-902) is a lookup instead of a second trip over the head rows.
 struct TopnCarry {
   bool valid = false;
-  std::vector<uint64_t> off;         // shard s owns isect[off[s] .. off[s+1]) in rank order
+  std::vector<uint64_t> off;         // shard s owns isect[off[s] .. ) in rank order ...
+  std::vector<uint32_t> limit;       // ... for its first limit[s] rank positions (pruned pass 1 counts no further)
   const uint32_t* isect = nullptr;   // pinned host buffer of pass 1 (ctx->h_out)
   std::vector<uint64_t> src_counts;  // |source row| per shard (Tanimoto)
 };
@@ -501,7 +518,7 @@ bool topn_pass2_from_carry(pb200_ctx* ctx, pb200_family family, const uint64_t* 
       if (it == f.row_ids.end() || *it != ids[k]) continue;  // the shard does not have this row
       const size_t j = size_t(it - f.row_ids.begin());
       const uint32_t pos = f.rank_pos_of_row[j];
-      if (pos == 0xffffffffu) { miss.store(true, std::memory_order_relaxed); return; }
+      if (pos == 0xffffffffu || pos >= carry.limit[s]) { miss.store(true, std::memory_order_relaxed); return; }
       uint64_t c = f.rank_from_host ? f.rank_counts[pos] : f.row_counts[j];
       if (c == 0) c = f.row_counts[j];
       if (c > 0) cd.push_back({ids[k], c, carry.isect[carry.off[s] + pos]});
@@ -567,6 +584,7 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
 
   lap("candidates");
   std::vector<uint64_t> off(n_shards + 1, 0);
+  std::vector<uint32_t> visible;  // with a source: how many rank positions of each shard have a count on the host
   std::vector<uint64_t> src_counts(n_shards, 0);
   const uint32_t* isect = nullptr;
   TRY(ensure_dev(ctx, ctx->d_misc, 64));
@@ -587,32 +605,41 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
     if (trace) { cudaStreamSynchronize(ctx->stream); lap("  rank tables + src"); }
     const uint64_t total = off[n_shards];
     const size_t n_counts = n_ids ? size_t(n_shards) * n_ids : size_t(total);
-    // d_topn: [cand_off u64 x ns][rank_n u32 x ns][ptrs x ns][ids u64 x n_ids] ; counts in d_bsi
+    // Pruned pass (the reference's own rule, fragment.go:1673-1688): count the head of every shard's ranking, let the
+    // device replay the start of the walk to find where it stops, count only up to there, fetch only those counts.
+    const bool prune = ctx->topn_prune && !n_ids && n > 0 && tanimoto == 0;
+    // d_topn: [cand_off u64 x ns][out_off u64 x ns][rank_n u32 x ns][limit u32 x ns][idx ptrs x ns][count ptrs x ns][ids u64 x n_ids] ; counts in d_bsi
     size_t o_off = 0;
-    size_t o_n = o_off + size_t(n_shards) * 8;
-    size_t o_ptr = align_up(o_n + size_t(n_shards) * 4, 16);
-    size_t o_ids = o_ptr + size_t(n_shards) * 8;
+    size_t o_out = o_off + size_t(n_shards) * 8;
+    size_t o_n = o_out + size_t(n_shards) * 8;
+    size_t o_lim = o_n + size_t(n_shards) * 4;
+    size_t o_ptr = align_up(o_lim + size_t(n_shards) * 4, 16);
+    size_t o_cptr = o_ptr + size_t(n_shards) * 8;
+    size_t o_ids = o_cptr + size_t(n_shards) * 8;
     size_t total_bytes = o_ids + n_ids * 8;
     TRY(ensure_dev(ctx, ctx->d_topn, total_bytes));
     TRY(ensure_pin(ctx, ctx->h_topn, total_bytes));  // not h_stage: the program upload issued above may still be reading it
     TRY(ensure_dev(ctx, ctx->d_bsi, std::max<size_t>(n_counts, 1) * 4));
-    TRY(ensure_pin(ctx, ctx->h_out, std::max<size_t>(n_counts, 1) * 4 + size_t(n_shards) * kRowContainers * 4));
     uint8_t* h = static_cast<uint8_t*>(ctx->h_topn.p);
     uint8_t* d = static_cast<uint8_t*>(ctx->d_topn.p);
     std::memcpy(h + o_off, off.data(), size_t(n_shards) * 8);
     auto* hn = reinterpret_cast<uint32_t*>(h + o_n);
     auto* hp = reinterpret_cast<const uint32_t**>(h + o_ptr);
+    auto* hcp = reinterpret_cast<const uint64_t**>(h + o_cptr);
     uint32_t max_cand = uint32_t(n_ids);
     for (uint32_t s = 0; s < n_shards; s++) {
       const bool use = frs[s] && !n_ids;
       hn[s] = use ? uint32_t(frs[s]->rank_ids.size()) : 0;
       hp[s] = use ? frs[s]->d_rank : nullptr;
+      hcp[s] = use ? frs[s]->d_rank_counts : nullptr;
       max_cand = std::max(max_cand, hn[s]);
     }
     if (n_ids) std::memcpy(h + o_ids, ids, n_ids * 8);
-    CUDA_TRY(ctx, cudaMemcpyAsync(d, h, total_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d, h, o_out, cudaMemcpyHostToDevice, ctx->stream));  // cand_off
+    CUDA_TRY(ctx, cudaMemcpyAsync(d + o_n, h + o_n, total_bytes - o_n, cudaMemcpyHostToDevice, ctx->stream));
     ctx->timing.h2d_bytes += total_bytes;
     uint32_t* d_counts = static_cast<uint32_t*>(ctx->d_bsi.p);
+    uint32_t* d_limit = reinterpret_cast<uint32_t*>(d + o_lim);
     TopnParams tp{};
     tp.families = ctx->d_families; tp.family = family; tp.shards = bd.shards; tp.n_shards = n_shards;
     tp.src_dense = static_cast<const uint8_t*>(ctx->d_dense.p);
@@ -623,33 +650,73 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
     tp.ids = n_ids ? reinterpret_cast<const uint64_t*>(d + o_ids) : nullptr;
     tp.n_ids = uint32_t(n_ids);
     tp.chunk = 2048;
-    tp.chunks_per_shard = std::max<uint32_t>(1, (max_cand + tp.chunk - 1) / tp.chunk);
     tp.counts = d_counts;
     tp.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 8);
-    if (n_counts) {
+    auto launch_counts = [&](uint32_t span) -> int {  // one pass of the count kernel over `span` candidates per shard at most
       if (!ctx->topn_attr_set) {
         CUDA_TRY(ctx, cudaFuncSetAttribute(topn_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopnSmem));
         ctx->topn_attr_set = true;
       }
+      tp.chunks_per_shard = std::max<uint32_t>(1, (span + tp.chunk - 1) / tp.chunk);
       const uint64_t items = uint64_t(n_shards) * tp.chunks_per_shard;
       const uint32_t grid = uint32_t(std::min<uint64_t>(items, resident_ctas(ctx, OCC_TOPN, topn_count_kernel, kTopnThreads, kTopnSmem)));
       topn_count_kernel<<<grid, kTopnThreads, kTopnSmem, ctx->stream>>>(tp);
       ctx->timing.launches++;
       CUDA_TRY(ctx, cudaGetLastError());
+      return PB200_OK;
+    };
+    std::vector<uint32_t> limit(n_shards, 0);   // rank positions of shard s whose counts reach the host: [0, limit[s])
+    std::vector<uint64_t> host_off = off;       // where they start in the host buffer
+    size_t n_fetch = n_counts;
+    const uint32_t* d_fetch = d_counts;
+    if (n_counts && prune) {
+      const uint32_t head = std::min<uint32_t>(max_cand, std::max<uint32_t>(4 * n, 64));
+      tp.range_lo = 0; tp.range_cap = head; tp.range_hi = nullptr;
+      TRY(launch_counts(head));
+      topn_limit_kernel<<<(n_shards * 32 + 255) / 256, 256, 0, ctx->stream>>>(reinterpret_cast<const uint64_t* const*>(d + o_cptr), tp.rank_n, tp.cand_off, d_counts,
+                                                                           n_shards, head, n, min_threshold, d_limit);
+      ctx->timing.launches++;
+      CUDA_TRY(ctx, cudaGetLastError());
+      if (max_cand > head) {
+        tp.range_lo = head; tp.range_cap = 0; tp.range_hi = d_limit;
+        TRY(launch_counts(max_cand - head));
+      }
+      CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+      CUDA_TRY(ctx, cudaMemcpyAsync(limit.data(), d_limit, size_t(n_shards) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+      uint64_t acc = 0;
+      for (uint32_t s = 0; s < n_shards; s++) { host_off[s] = acc; acc += limit[s]; }
+      host_off[n_shards] = acc;
+      n_fetch = size_t(acc);
+      std::memcpy(h + o_out, host_off.data(), size_t(n_shards) * 8);
+      CUDA_TRY(ctx, cudaMemcpyAsync(d + o_out, h + o_out, size_t(n_shards) * 8, cudaMemcpyHostToDevice, ctx->stream));
+      TRY(ensure_dev(ctx, ctx->d_topn_compact, std::max<size_t>(n_fetch, 1) * 4));
+      topn_compact_kernel<<<std::min<uint32_t>(n_shards, uint32_t(ctx->sm_count) * 8), 128, 0, ctx->stream>>>(
+          d_counts, tp.cand_off, d_limit, reinterpret_cast<const uint64_t*>(d + o_out), n_shards, static_cast<uint32_t*>(ctx->d_topn_compact.p));
+      ctx->timing.launches++;
+      CUDA_TRY(ctx, cudaGetLastError());
+      d_fetch = static_cast<const uint32_t*>(ctx->d_topn_compact.p);
+      ctx->timing.d2h_bytes += size_t(n_shards) * 4;
+    } else {
+      if (n_counts) { tp.range_lo = 0; tp.range_cap = 0; tp.range_hi = nullptr; TRY(launch_counts(max_cand)); }
+      CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+      for (uint32_t s = 0; s < n_shards; s++) limit[s] = uint32_t(off[s + 1] - off[s]);
     }
-    CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-    if (trace) { cudaStreamSynchronize(ctx->stream); lap("  count kernel"); }
+    if (trace) { cudaStreamSynchronize(ctx->stream); lap("  count kernels"); }
+    TRY(ensure_pin(ctx, ctx->h_out, std::max<size_t>(n_fetch, 1) * 4 + size_t(n_shards) * kRowContainers * 4));
     uint32_t* h_counts = static_cast<uint32_t*>(ctx->h_out.p);
-    uint32_t* h_dn = h_counts + std::max<size_t>(n_counts, 1);
-    if (n_counts) CUDA_TRY(ctx, cudaMemcpyAsync(h_counts, d_counts, n_counts * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t* h_dn = h_counts + std::max<size_t>(n_fetch, 1);
+    if (n_fetch) CUDA_TRY(ctx, cudaMemcpyAsync(h_counts, d_fetch, n_fetch * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CUDA_TRY(ctx, cudaMemcpyAsync(h_dn, ctx->d_dense_n.p, size_t(n_shards) * kRowContainers * 4, cudaMemcpyDeviceToHost, ctx->stream));
     TRY(finish_call(ctx));
-    ctx->timing.d2h_bytes += n_counts * 4 + size_t(n_shards) * kRowContainers * 4;
+    ctx->timing.d2h_bytes += n_fetch * 4 + size_t(n_shards) * kRowContainers * 4;
     for (uint32_t s = 0; s < n_shards; s++)
       for (int c = 0; c < kRowContainers; c++) src_counts[s] += h_dn[size_t(s) * kRowContainers + c];
     isect = h_counts;
+    off = host_off;
+    visible = limit;
     lap("device + copies");
-    if (carry && !n_ids) { carry->valid = true; carry->off = off; carry->isect = h_counts; carry->src_counts = src_counts; }
+    if (carry && !n_ids) { carry->valid = true; carry->off = off; carry->limit = limit; carry->isect = h_counts; carry->src_counts = src_counts; }
   }
 
   // per-shard selection walk (host: sequential, data-dependent, a few thousand steps per shard)
@@ -666,7 +733,8 @@ int topn_pass(pb200_ctx* ctx, pb200_family family, const pb200_node* src_prog, u
       }
       per_shard[s] = top_walk(id_ids[s].data(), id_counts[s].data(), id_ids[s].size(), is, has_src, 0, min_threshold, tanimoto, src_counts[s]);
     } else {
-      per_shard[s] = top_walk(f.rank_ids.data(), f.rank_counts.data(), f.rank_ids.size(), has_src ? isect + off[s] : nullptr, has_src,
+      // a pruned pass holds counts for the prefix the walk visits; the walk ends there by the same rule the device applied
+      per_shard[s] = top_walk(f.rank_ids.data(), f.rank_counts.data(), has_src ? size_t(visible[s]) : f.rank_ids.size(), has_src ? isect + off[s] : nullptr, has_src,
                               int(n), min_threshold, tanimoto, src_counts[s]);
     }
   });

@@ -32,8 +32,11 @@ struct TopnParams {
   uint32_t n_ids;
   uint32_t chunk;                      // candidates per CTA
   uint32_t chunks_per_shard;
-  uint32_t* counts;                    // [sum rank_n] or [n_shards * n_ids]; every entry is written
+  uint32_t* counts;                    // [sum rank_n] or [n_shards * n_ids]; every entry of the range is written
   unsigned long long* algo_bytes;
+  // by-rank passes count the rank positions [range_lo, min(rank_n, range_cap, range_hi[s])) of every shard
+  uint32_t range_lo, range_cap;        // range_cap == 0: no cap
+  const uint32_t* range_hi;            // per shard (optional)
 };
 
 constexpr int kTopnThreads = 1024;
@@ -103,8 +106,12 @@ __global__ void __launch_bounds__(kTopnThreads, 1) topn_count_kernel(TopnParams 
   for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
     const uint32_t s = item / p.chunks_per_shard, ch = item % p.chunks_per_shard;
     const bool by_rank = p.ids == nullptr;
-    const uint32_t n_cand = by_rank ? p.rank_n[s] : p.n_ids;
-    const uint32_t k0 = ch * p.chunk;
+    uint32_t n_cand = by_rank ? p.rank_n[s] : p.n_ids;
+    if (by_rank) {
+      if (p.range_cap) n_cand = min(n_cand, p.range_cap);
+      if (p.range_hi) n_cand = min(n_cand, p.range_hi[s]);
+    }
+    const uint32_t k0 = (by_rank ? p.range_lo : 0u) + ch * p.chunk;
     if (k0 >= n_cand) continue;
     const uint32_t k1 = min(n_cand, k0 + p.chunk);
     uint32_t* out = p.counts + (by_rank ? p.cand_off[s] : uint64_t(s) * p.n_ids);
@@ -248,6 +255,77 @@ __global__ void __launch_bounds__(kTopnThreads, 1) topn_count_kernel(TopnParams 
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) bytes_acc += __shfl_xor_sync(0xffffffffu, bytes_acc, o);
   if (lane == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+}
+
+// ---------------------------------------------------------------------------------------
+// Pruning like fragment.top (fragment.go:1599-1689). The walk pushes the first n ranked rows whose intersection count
+// is non-zero and at least MinThreshold; from then on its threshold is the smallest count pushed (later pushes are
+// never smaller, so it stays), and it stops at the first row whose CACHED count is below it. Everything behind that
+// row is never visited by the reference — and need not be counted here. One warp per shard replays the first part
+// of the walk over the counts of the first `head` ranked rows and returns the rank position where the walk stops
+// (`limit`): rows [head, limit) are counted by a second pass of topn_count_kernel, rows >= limit not at all.
+//   rank_counts[s]: cached counts in rank order; counts: intersection counts (valid for positions < head)
+// ---------------------------------------------------------------------------------------
+__global__ void topn_limit_kernel(const uint64_t* const* __restrict__ rank_counts, const uint32_t* __restrict__ rank_n,
+                                  const uint64_t* __restrict__ cand_off, const uint32_t* __restrict__ counts, uint32_t n_shards, uint32_t head,
+                                  uint32_t n, uint64_t min_threshold, uint32_t* __restrict__ limit) {
+  const uint32_t s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (s >= n_shards) return;
+  const uint32_t total = rank_n[s];
+  const uint64_t* rc = rank_counts[s];
+  const uint32_t* ic = counts + cand_off[s];
+  const uint32_t h = min(head, total);
+  // first part of the walk: which ranked rows get pushed (lanes test 32 rows at a time, in rank order)
+  uint32_t pushed = 0, stop_at = 0xffffffffu;
+  uint64_t thr = ~0ull;
+  for (uint32_t base = 0; base < h && stop_at == 0xffffffffu; base += 32) {
+    const uint32_t k = base + lane;
+    bool push = false;
+    uint64_t c = 0;
+    if (k < h) {
+      const uint64_t cached = rc[k];
+      c = ic[k];
+      push = cached != 0 && cached >= min_threshold && c != 0 && c >= min_threshold;
+    }
+    const uint32_t m = __ballot_sync(0xffffffffu, push);
+    const uint32_t need = n - pushed;
+    uint32_t take = m;
+    if (uint32_t(__popc(m)) >= need) {  // the n-th push happens in this group: keep only the first `need` of them
+      uint32_t mm = m, kept = 0;
+      for (uint32_t i = 0; i < need; i++) { const uint32_t b = mm & (0u - mm); kept |= b; mm ^= b; }
+      take = kept;
+      stop_at = base + 31u - uint32_t(__clz(kept));  // position of the n-th push
+    }
+    uint64_t mine = (take >> lane) & 1u ? c : ~0ull;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) { const uint64_t y = __shfl_xor_sync(0xffffffffu, mine, o); mine = y < mine ? y : mine; }
+    thr = mine < thr ? mine : thr;
+    pushed += uint32_t(__popc(take));
+  }
+  uint32_t lim = total;
+  if (stop_at != 0xffffffffu) {
+    // n rows are in the heap: the walk continues while cached >= thr (and thr >= MinThreshold, which holds by construction)
+    lim = total;
+    for (uint32_t base = stop_at + 1; base < total; base += 32) {
+      const uint32_t k = base + lane;
+      // rows whose cached count is zero or under MinThreshold are skipped by the walk, they do not end it
+      const bool below = k < total && rc[k] != 0 && rc[k] >= min_threshold && rc[k] < thr;
+      const uint32_t m = __ballot_sync(0xffffffffu, below);
+      if (m) { lim = base + uint32_t(__ffs(m)) - 1u; break; }
+    }
+  }
+  if (lane == 0) limit[s] = lim;
+}
+
+// counts of the visited prefixes, packed: out[out_off[s] + k] = counts[cand_off[s] + k] for k < limit[s]
+__global__ void topn_compact_kernel(const uint32_t* __restrict__ counts, const uint64_t* __restrict__ cand_off, const uint32_t* __restrict__ limit,
+                                    const uint64_t* __restrict__ out_off, uint32_t n_shards, uint32_t* __restrict__ out) {
+  for (uint32_t s = blockIdx.x; s < n_shards; s += gridDim.x) {
+    const uint32_t* src = counts + cand_off[s];
+    uint32_t* dst = out + out_off[s];
+    const uint32_t n = limit[s];
+    for (uint32_t k = threadIdx.x; k < n; k += blockDim.x) dst[k] = src[k];
+  }
 }
 
 }  // namespace pb200

@@ -28,11 +28,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "{\n\t"
       ".reg .pred p;\n\t"
       "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"  // suspends up to the hint instead of spinning
       "@p bra DONE_%=;\n\t"
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t"
-      "}" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+      "}" :: "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u) : "memory");
 }
 // global -> shared bulk copy; `bytes` multiple of 16, both addresses 16 B aligned
 __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {

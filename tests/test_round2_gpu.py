@@ -390,3 +390,55 @@ def test_concurrent_counts_match_oracle(eng_orc):
         t.join()
     assert not errors, errors[:5]
     assert len(bad_seen) == 12 * 3
+
+
+def test_topn_pruned_like_fragment_top(eng_orc):
+    """TopN with a source counts only the ranked rows fragment.top's walk visits (fragment.go:1673-1688): same pairs as
+    the oracle and as the engine with pruning switched off, for several n / thresholds, with fewer bytes read."""
+    eng, orc = eng_orc
+    g, c = Executor(eng), Executor(orc)
+    for ex in (g, c):
+        ex.create_field("z")
+        ex.create_field("a")
+    shards = [0, 1, 2, 3]
+    for s in shards:
+        zb, ab = synth.zipf(s, n_rows=1500, k=6), synth.bernoulli(s, 1, 2, 0.10)
+        for ex in (g, c):
+            ex.load_fragment("z", s, zb)
+            ex.load_fragment("a", s, ab)
+    src = Intersect(Row("a", 1), Row("a", 2))
+    cases = [dict(n=5, src=src), dict(n=50, src=src), dict(n=1, src=Row("a", 1)), dict(n=20, src=src, threshold=40), dict(n=400, src=src),
+             dict(n=2000, src=Row("a", 2)), dict(n=10, src=Row("z", 3)), dict(n=7, src=abi.Union(Row("z", 0), Row("a", 1)))]
+    OPT_TOPN_PRUNE = 3
+    for kw in cases:
+        want = c.topn("z", shards, **kw)
+        eng.set_option(OPT_TOPN_PRUNE, 1)
+        got = g.topn("z", shards, **kw)
+        pruned_bytes = eng.last_timing().algo_bytes
+        eng.set_option(OPT_TOPN_PRUNE, 0)
+        full = g.topn("z", shards, **kw)
+        full_bytes = eng.last_timing().algo_bytes
+        eng.set_option(OPT_TOPN_PRUNE, 1)
+        assert got == want, kw
+        assert full == want, kw
+        if kw["n"] <= 5:  # (a pruned pass stages the source twice: on this small index it only pays when the walk stops early)
+            assert pruned_bytes < full_bytes, (kw, pruned_bytes, full_bytes)
+    # per shard, exactly fragment.top's list and order
+    for s in shards:
+        assert g.be.topn_shard(g.family("z"), g.program(src), 9, s) == c.be.topn_shard(c.family("z"), c.program(src), 9, s)
+    # a host-supplied ranking that is NOT in descending order of the cached counts: the walk's rule, not sortedness, decides
+    ids, counts = orc.rankings(c.family("z"), 0)
+    ids2, counts2 = ids[:40][::-1] + ids[40:], counts[:40][::-1] + counts[40:]
+    eng.rank_set(g.family("z"), 0, ids2, counts2)
+    orc_pairs = None
+    try:
+        orc.rank_set(c.family("z"), 0, ids2, counts2)
+        orc_pairs = c.be.topn_shard(c.family("z"), c.program(src), 6, 0)
+    except AttributeError:
+        pass
+    got = g.be.topn_shard(g.family("z"), g.program(src), 6, 0)
+    eng.set_option(OPT_TOPN_PRUNE, 0)
+    assert got == g.be.topn_shard(g.family("z"), g.program(src), 6, 0)
+    eng.set_option(OPT_TOPN_PRUNE, 1)
+    if orc_pairs is not None:
+        assert got == orc_pairs
