@@ -311,6 +311,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-scan", action="store_true", help="reference arm: also time the pool at 1/2/4/P workers")
     ap.add_argument("--sustained-seconds", type=float, default=2.0)
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (fixed 128-shard index)")
     args = ap.parse_args()
     if args.warmup < 3:
         raise SystemExit("bench.py: --warmup must be >= 3 (timing rule); got %d" % args.warmup)
@@ -472,6 +473,52 @@ def main():
         tm = eng.last_timing()
         assert list(out_e2e) == last_resident, "resident and e2e legs disagree"
 
+        # ---- leg 3: strong scaling on a FIXED index — 128 shards x 512 rows (8 GiB), whatever N is; rank r holds the
+        # shards s < 128 with s % N == r, so the per-GPU work shrinks as N grows. One step = the same 1024-pair batch over
+        # the whole 128-shard index (+ the all-reduce of the counts for N > 1). ----
+        strong = None
+        if not args.no_strong:
+            S_SHARDS, S_ROWS = 128, 512
+            fam2 = eng.family_create()
+            mine = [s for s in range(S_SHARDS) if s % world == rank]
+            with ThreadPoolExecutor(max_workers=workers) as tp:
+                futs = [tp.submit(synth.bernoulli, s, 0, S_ROWS, P_DENSITY, SEED) for s in mine]
+                for s, f in zip(mine, futs):
+                    eng.frag_load(fam2, s, f.result())
+            mine_arr = (C.c_uint64 * len(mine))(*mine)
+            sbatches = [pack_pairs(pp, fam2) for pp in make_batches(n_batches, B, S_ROWS)]
+            sprep = [eng.batch_prepare(fl, off, B, mine_arr, len(mine)) for fl, off in sbatches]
+            stens = [torch.as_tensor(DevArray(eng.batch_device_counts(b), B), device="cuda") for b in sprep] if world > 1 else None
+
+            def step_strong(i):
+                eng.batch_launch(sprep[i])
+                if world > 1:
+                    ev_k[i].record(stream)
+                    side.wait_event(ev_k[i])
+                    with torch.cuda.stream(side):
+                        dist.all_reduce(stens[i], op=dist.ReduceOp.SUM)
+
+            for i in range(args.warmup):
+                step_strong(i)
+            join_side()
+            barrier()
+            q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            q0.record(stream)
+            for i in range(args.warmup, n_batches):
+                step_strong(i)
+            join_side()
+            q1.record(stream)
+            barrier()
+            s_ms = max_over_ranks(q0.elapsed_time(q1)) / args.steps
+            chk = (C.c_uint64 * B)()
+            eng.batch_fetch(sprep[-1], chk)
+            strong = {"index": f"{S_SHARDS} shards x {S_ROWS} rows x 2^20 columns, 10% density ({S_SHARDS * S_ROWS * 16 * 8192 / 2**30:.0f} GiB), fixed for every N",
+                      "shards_per_gpu": len(mine), "ms_per_step": s_ms, "value": B / (s_ms * 1e-3), "unit": "queries/s over the whole fixed index",
+                      "checksum_last_batch": int(sum(chk) % (1 << 61)),
+                      "note": "strong scaling: divide this value at N by the value at N = 1 (the checksum must be equal at every N)"}
+            for b in sprep:
+                eng.batch_free(b)
+
     ms_per_step = ms_total / args.steps
     units_per_step = B * world
     value = units_per_step / (ms_per_step * 1e-3)
@@ -500,6 +547,7 @@ def main():
                      "note": "achieved = algorithmic bytes per launch / mean launch duration from CUDA events over the timed region "
                              "(includes the per-step 8 KiB count memset" + (" and the NCCL all-reduce of the counts" if world > 1 else "") + ")"},
         "sustained": sustained,
+        "strong_scaling": strong,
         "columns_per_s": value * SHARDS_PER_GPU * (1 << 20) * 2,
         "global_queries_per_s": value / world,
         "index_build_s": t_build,
