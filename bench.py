@@ -340,6 +340,10 @@ def main():
     eng.set_stream(stream.cuda_stream)
     fam = eng.family_create()
     shards = [rank + world * i for i in range(SHARDS_PER_GPU)]
+    if world > 1:  # the ranks' mailboxes are exchanged once; from then on the sum over the ranks is the tail of each batch's kernel
+        handles = [None] * world
+        dist.all_gather_object(handles, eng.peer_export())
+        eng.peer_connect(rank, world, b"".join(handles))
 
     # ---- build + load the index (not timed) ----
     t_build = time.perf_counter()
@@ -374,24 +378,19 @@ def main():
     with torch.cuda.stream(stream):
         # ---- leg 1: device-resident (prepared batches) ----
         prepared = [eng.batch_prepare(fl, off, B, shards_arr, len(shards)) for fl, off in batches]
-        tens = [torch.as_tensor(DevArray(eng.batch_device_counts(b), B), device="cuda") for b in prepared] if world > 1 else None
 
-        # N > 1: the all-reduce(sum) of a batch's counts does not gate the next batch's kernel, so it is queued on a side
-        # stream behind an event recorded after the kernel; the launching stream goes straight on to the next batch.
-        side = torch.cuda.Stream() if world > 1 else None
-        ev_k = [torch.cuda.Event() for _ in prepared] if world > 1 else None
-
+        # N > 1: the sum of a batch's counts over the ranks is done by the batch's own kernel — its last CTA adds this GPU's
+        # counts into every rank's mailbox over NVLink peer memory (pb200_batch_launch_allreduce); no collective is launched
+        # between two batches. A batch's total is picked up two launches later in stream order (join_side flushes the rest).
         def step_resident(i):
-            eng.batch_launch(prepared[i])
             if world > 1:
-                ev_k[i].record(stream)
-                side.wait_event(ev_k[i])
-                with torch.cuda.stream(side):
-                    dist.all_reduce(tens[i], op=dist.ReduceOp.SUM)
+                eng.batch_launch_allreduce(prepared[i])
+            else:
+                eng.batch_launch(prepared[i])
 
         def join_side():
             if world > 1:
-                stream.wait_stream(side)
+                eng.peer_flush()
 
         for i in range(args.warmup):
             step_resident(i)
@@ -451,17 +450,15 @@ def main():
                     if n + 1 < len(idx):
                         begin(idx[n + 1])
                     eng.count_batch_end(out_e2e)                           # D2H on the copy stream + wait
-            else:
-                def begin_reduce(i):
-                    begin(i)
-                    t = torch.as_tensor(DevArray(eng.count_batch_device(), B), device="cuda")
-                    dist.all_reduce(t, op=dist.ReduceOp.SUM)   # in place in HBM, queued behind the kernel
-                begin_reduce(idx[0])
+            else:  # PB200_OPT_PEER_ALLREDUCE: _begin's kernel pushes to the peers, _end waits for their counts on the copy stream
+                begin(idx[0])
                 for n in range(len(idx)):
                     if n + 1 < len(idx):
-                        begin_reduce(idx[n + 1])                 # the next batch is queued before this one is fetched
+                        begin(idx[n + 1])
                     eng.count_batch_end(out_e2e)
 
+        if world > 1:
+            eng.set_option(eng.OPT_PEER_ALLREDUCE, 1)
         run_e2e(list(range(args.warmup)))
         barrier()
         t0 = time.perf_counter()
@@ -488,15 +485,12 @@ def main():
             mine_arr = (C.c_uint64 * len(mine))(*mine)
             sbatches = [pack_pairs(pp, fam2) for pp in make_batches(n_batches, B, S_ROWS)]
             sprep = [eng.batch_prepare(fl, off, B, mine_arr, len(mine)) for fl, off in sbatches]
-            stens = [torch.as_tensor(DevArray(eng.batch_device_counts(b), B), device="cuda") for b in sprep] if world > 1 else None
 
             def step_strong(i):
-                eng.batch_launch(sprep[i])
                 if world > 1:
-                    ev_k[i].record(stream)
-                    side.wait_event(ev_k[i])
-                    with torch.cuda.stream(side):
-                        dist.all_reduce(stens[i], op=dist.ReduceOp.SUM)
+                    eng.batch_launch_allreduce(sprep[i])
+                else:
+                    eng.batch_launch(sprep[i])
 
             for i in range(args.warmup):
                 step_strong(i)
@@ -545,7 +539,7 @@ def main():
                      "kernel": "eval_fast_kernel (K1: 128-bit AND + popcount over bitmap container pairs)",
                      "algo_bytes_per_launch": algo_bytes, "peak_source": peak_src,
                      "note": "achieved = algorithmic bytes per launch / mean launch duration from CUDA events over the timed region "
-                             "(includes the per-step 8 KiB count memset" + (" and the NCCL all-reduce of the counts" if world > 1 else "") + ")"},
+                             "(includes the per-step 8 KiB count memset" + (" and the peer reduction of the counts in the kernel's tail" if world > 1 else "") + ")"},
         "sustained": sustained,
         "strong_scaling": strong,
         "columns_per_s": value * SHARDS_PER_GPU * (1 << 20) * 2,

@@ -530,6 +530,28 @@ int pb200_multi_bsi_minmax_shards(pb200_multi* m, pb200_family bsi_family, uint3
                                   const pb200_node* filter_prog, uint32_t n_filter_nodes, int is_max,
                                   const uint64_t* shards, uint32_t n_shards, int64_t* out_vals, uint64_t* out_counts);
 
+/* ---- one process per GPU: the cross-GPU sum of a Count batch without a collective library --------------
+ * When every GPU of the box is driven by its own process (one rank per device, e.g. under torchrun), the reduce
+ * function of executeCount (uint64 +, executor.go:1813) over the ranks is done by the batch's own kernel: the last CTA
+ * to retire adds this GPU's partial counts into a mailbox of every rank with system-scope reductions over NVLink peer
+ * memory (the peers' mailboxes are mapped through CUDA IPC; plain stores, no multicast), so no collective is launched
+ * between two batches and no rank waits for another inside the launch sequence. A batch's total is picked up two
+ * batches later (in stream order) or when the host fetches it.
+ *   1. every rank: pb200_peer_export -> a PB200_PEER_HANDLE_BYTES handle; exchange the handles (any transport);
+ *   2. every rank: pb200_peer_connect(rank, world, handles[world]); world <= 8, batches <= PB200_PEER_MAX_COUNTS queries;
+ *   3. pb200_batch_launch_allreduce instead of pb200_batch_launch: after pb200_batch_fetch (or pb200_peer_flush + a
+ *      stream synchronisation) the batch's device counts hold the sum over all ranks. Every rank must launch the same
+ *      sequence of all-reduced batches. With PB200_OPT_PEER_ALLREDUCE = 1 pb200_count_batch_begin / _end do the same.
+ * A rank that waits ~2 s for a peer's counts gives up: the fetch returns PB200_ERR_CUDA instead of hanging.
+ * No reference counterpart (the reference reduces on the host, executor.go:2458-2574). */
+#define PB200_PEER_HANDLE_BYTES 64
+#define PB200_PEER_MAX_COUNTS 4096u
+#define PB200_OPT_PEER_ALLREDUCE 4u
+int pb200_peer_export(pb200_ctx* ctx, void* handle_out);
+int pb200_peer_connect(pb200_ctx* ctx, int rank, int world, const void* handles);
+int pb200_peer_flush(pb200_ctx* ctx);   /* queue the pick-up of every batch still in flight on the context's stream */
+int pb200_batch_launch_allreduce(pb200_ctx* ctx, pb200_batch* batch);
+
 /* Timing / byte accounting of the last query call on this context. */
 int pb200_last_timing(pb200_ctx* ctx, pb200_timing* out);
 

@@ -39,6 +39,8 @@ using namespace pb200;
     if (rc__ != PB200_OK) return rc__; \
   } while (0)
 
+namespace { void peer_teardown(pb200_ctx* ctx); }  // engine_peer.inl
+
 static int fail(pb200_ctx* ctx, int code, const std::string& msg) {
   ctx->err = msg;
   return code;
@@ -235,6 +237,7 @@ extern "C" int pb200_shutdown(pb200_ctx* ctx) {
       if (sl.k1) cudaEventDestroy(sl.k1);
       if (sl.done) cudaEventDestroy(sl.done);
     }
+    peer_teardown(ctx);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -530,6 +533,10 @@ extern "C" int pb200_set_option(pb200_ctx* ctx, uint32_t option, uint64_t value)
     case PB200_OPT_DENSIFY_MIN_BYTES:
       if (value > kBitmapBytes) return fail(ctx, PB200_ERR_INVALID, "densify threshold above 8192 bytes");
       ctx->densify_min_bytes = uint32_t(value);
+      return PB200_OK;
+    case PB200_OPT_PEER_ALLREDUCE:
+      if (value && !ctx->peer.on) return fail(ctx, PB200_ERR_INVALID, "no peers connected (pb200_peer_connect)");
+      ctx->peer_allreduce = value != 0;
       return PB200_OK;
     case PB200_OPT_TOPN_PRUNE:
       ctx->topn_prune = value != 0;
@@ -929,7 +936,7 @@ enum { OCC_FAST = 0, OCC_STAGED, OCC_SUM, OCC_MM, OCC_TOPN, OCC_FOLD };
 // Launches the fast + staged kernels for `n_queries` programs starting at `progs`.
 int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards, bool staging,
                 unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, uint8_t* dense_out, uint32_t* dense_n,
-                uint32_t max_leaves = kMaxLeaves, bool bushy = true, bool fold_all = false) {
+                uint32_t max_leaves = kMaxLeaves, bool bushy = true, bool fold_all = false, const PushDesc* push = nullptr) {
   const uint64_t n_items = uint64_t(n_queries) * n_shards * kRowContainers;
   if (n_items == 0) return PB200_OK;
   if (n_items >= (1ull << 32)) return fail(ctx, PB200_ERR_RANGE, "batch too large: queries x shards x 16 must be < 2^32");
@@ -959,10 +966,14 @@ int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t 
     p.slow_descs = static_cast<ContainerDesc*>(ctx->d_slow_descs.p);
     p.slow_desc_stride = max_leaves;
   }
+  const bool push_fused = push && !staging;  // eval_fast_kernel is the batch's only kernel: the peer reduction rides in its tail
+  if (push_fused) p.push = *push;
   if (!fold_all) {
     CUDA_TRY(ctx, cudaMemsetAsync(p.slow_count, 0, 4, ctx->stream));
     const uint64_t want = (n_items + kFastWarps - 1) / kFastWarps;
-    const uint32_t grid = uint32_t(std::min<uint64_t>(want, resident_ctas(ctx, OCC_FAST, eval_fast_kernel, kFastWarps * 32, 0)));
+    uint32_t resident = resident_ctas(ctx, OCC_FAST, eval_fast_kernel, kFastWarps * 32, 0);
+    if (push && resident > 1) resident -= 1;  // one CTA slot stays free: the one-CTA collect kernel of an older batch can run beside this grid
+    const uint32_t grid = uint32_t(std::min<uint64_t>(want, resident));
     eval_fast_kernel<<<grid, kFastWarps * 32, 0, ctx->stream>>>(p);
     ctx->timing.launches++;
   }
@@ -975,6 +986,10 @@ int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t 
       eval_staged_kernel<<<sgrid, kStagedThreads, 0, ctx->stream>>>(p);
       ctx->timing.launches++;
     }
+  }
+  if (push && !push_fused) {
+    peer_push_kernel<<<1, 256, 0, ctx->stream>>>(*push);
+    ctx->timing.launches++;
   }
   CUDA_TRY(ctx, cudaGetLastError());
   return PB200_OK;
@@ -995,6 +1010,13 @@ int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_
 bool has_shift(const Compiled& cp);
 int launch_overflow(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards,
                     unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, unsigned long long* ovf_out);
+
+// engine_peer.inl
+int peer_begin_epoch(pb200_ctx* ctx, unsigned long long* target, uint32_t n, PushDesc& out, int* slot_out);
+int peer_collect(pb200_ctx* ctx, int slot);
+int peer_end_epoch(pb200_ctx* ctx, int slot);
+int peer_check_error(pb200_ctx* ctx);
+int pb200_peer_flush_locked(pb200_ctx* ctx);
 
 // Ends a query call: fetches the algorithmic-byte counter with the other results, waits for
 // the stream once, and reads the kernel time between the ev0/ev1 events.
@@ -1043,6 +1065,7 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
   const int si = (ctx->head + ctx->n_pending) & 1;
   CountSlot& sl = ctx->slots[si];
   sl.external = false;
+  sl.peer_slot = -1;
   if (!sl.k0) {
     CUDA_TRY(ctx, cudaEventCreate(&sl.k0)); CUDA_TRY(ctx, cudaEventCreate(&sl.k1));
     CUDA_TRY(ctx, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
@@ -1067,7 +1090,17 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
   ctx->n_pending++;
   unsigned long long* d_out = static_cast<unsigned long long*>(sl.d_out.p);
   CUDA_TRY(ctx, cudaEventRecord(sl.k0, ctx->stream));
-  if (n_queries != 0 && n_shards == 0) CUDA_TRY(ctx, cudaMemsetAsync(d_out, 0, n_out * 8, ctx->stream));
+  if (n_queries != 0 && n_shards == 0) {
+    CUDA_TRY(ctx, cudaMemsetAsync(d_out, 0, n_out * 8, ctx->stream));
+    if (ctx->peer_allreduce && !per_shard) {  // a rank without local shards still takes part in the sum (its zeros, its arrival)
+      PushDesc pd{};
+      const int rc0 = peer_begin_epoch(ctx, d_out, n_queries, pd, &sl.peer_slot);
+      if (rc0 != PB200_OK) { ctx->n_pending--; ctx->algo_off = 8; return rc0; }
+      peer_push_kernel<<<1, 256, 0, ctx->stream>>>(pd);
+      CUDA_TRY(ctx, cudaGetLastError());
+      TRY(peer_end_epoch(ctx, sl.peer_slot));
+    }
+  }
   if (n_queries != 0 && n_shards != 0) {
     Compiled cp;
     rc = compile_batch(ctx, progs, prog_off, n_queries, cp);
@@ -1099,11 +1132,19 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
     if (rc == PB200_OK && need_temp) rc = ensure_dev(ctx, ctx->d_temp, size_t(cp.n_temp_slots) * n_shards * kRowContainers * kBitmapBytes);
     if (rc == PB200_OK && cudaMemsetAsync(d_out, 0, n_out * 8, ctx->stream) != cudaSuccess) rc = fail(ctx, PB200_ERR_CUDA, "cudaMemsetAsync(counts) failed");
     if (rc == PB200_OK) rc = run_pretasks(ctx, cp, bd, n_shards);
+    PushDesc pd{};
+    const bool reduce = ctx->peer_allreduce && !per_shard;
+    if (rc == PB200_OK && reduce) rc = peer_begin_epoch(ctx, d_out, n_queries, pd, &sl.peer_slot);
     if (rc == PB200_OK)
       rc = launch_eval(ctx, bd, bd.progs, n_queries, n_shards, cp.may_need_staging, d_out, per_shard ? n_shards : 1, per_shard ? 1 : 0,
-                       nullptr, nullptr, max_leaves_of(cp), cp.any_bushy, fold_all_of(cp));
+                       nullptr, nullptr, max_leaves_of(cp), cp.any_bushy, fold_all_of(cp), reduce && !has_shift(cp) ? &pd : nullptr);
+    if (rc == PB200_OK && reduce && has_shift(cp)) {  // the overflow pass below adds to the counts: push after it
+      rc = launch_overflow(ctx, bd, bd.progs, n_queries, n_shards, d_out, 1, 0, nullptr);
+      if (rc == PB200_OK) { peer_push_kernel<<<1, 256, 0, ctx->stream>>>(pd); ctx->timing.launches++; }
+    } else
     if (rc == PB200_OK && has_shift(cp))  // bits shifted past a shard's last column count too (roaring.go:970-974)
       rc = launch_overflow(ctx, bd, bd.progs, n_queries, n_shards, d_out, per_shard ? n_shards : 1, per_shard ? 1 : 0, nullptr);
+    if (rc == PB200_OK && reduce) rc = peer_end_epoch(ctx, sl.peer_slot);
     if (rc != PB200_OK) { ctx->n_pending--; ctx->algo_off = 8; return rc; }
   }
   ctx->algo_off = 8;
@@ -1130,11 +1171,16 @@ int count_end(pb200_ctx* ctx, uint64_t* out) {
   // stream after _begin (an NCCL all-reduce of the device-resident counts) is waited for too.
   if (ctx->n_pending == 1) CUDA_TRY(ctx, cudaEventRecord(sl.done, ctx->stream));
   CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copy_stream, sl.done, 0));
+  if (sl.peer_slot >= 0) {  // the sum over the ranks: wait for the peers' counts beside whatever the compute stream is running
+    TRY(peer_collect(ctx, sl.peer_slot));
+    sl.peer_slot = -1;
+  }
   uint8_t* h = static_cast<uint8_t*>(sl.h_out.p);
   if (n_out) CUDA_TRY(ctx, cudaMemcpyAsync(h, sl.d_out.p, n_out * 8, cudaMemcpyDeviceToHost, ctx->copy_stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(h + std::max<size_t>(n_out, 1) * 8, static_cast<uint8_t*>(ctx->d_misc.p) + 16 + 8 * size_t(ctx->head), 8,
                                 cudaMemcpyDeviceToHost, ctx->copy_stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->copy_stream));
+  if (ctx->peer_allreduce) TRY(peer_check_error(ctx));
   float ms = 0;
   if (cudaEventElapsedTime(&ms, sl.k0, sl.k1) == cudaSuccess) ctx->timing.kernel_ms = ms;
   std::memcpy(&ctx->timing.algo_bytes, h + std::max<size_t>(n_out, 1) * 8, 8);
@@ -1375,11 +1421,13 @@ extern "C" int pb200_batch_device_counts(pb200_ctx* ctx, pb200_batch* b, void** 
 extern "C" int pb200_batch_fetch(pb200_ctx* ctx, pb200_batch* b, uint64_t* out_counts) {
   ENTER(ctx);
   if (!b || !out_counts) return PB200_ERR_INVALID;
+  for (int k = 0; k < 4 && ctx->peer.on; k++)  // an all-reduced launch of this batch still in flight: pick its total up first
+    if (ctx->peer.pend[k].open && ctx->peer.pend[k].target == b->d_counts.p) TRY(pb200_peer_flush_locked(ctx));
   TRY(ensure_pin(ctx, ctx->h_out, size_t(b->n_queries) * 8));
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_out.p, b->d_counts.p, size_t(b->n_queries) * 8, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   std::memcpy(out_counts, ctx->h_out.p, size_t(b->n_queries) * 8);
-  return PB200_OK;
+  return peer_check_error(ctx);
 }
 
 extern "C" int pb200_batch_free(pb200_ctx* ctx, pb200_batch* b) {
@@ -1506,4 +1554,5 @@ extern "C" int pb200_count_pairs_noalloc(pb200_ctx* ctx, pb200_family family, co
 }
 
 #include "engine_ingest.inl"
+#include "engine_peer.inl"
 #include "engine_multi.inl"

@@ -104,6 +104,7 @@ struct CountSlot {
   cudaEvent_t k0 = nullptr, k1 = nullptr, done = nullptr;
   size_t n_out = 0;
   bool launched = false;
+  int peer_slot = -1;     // mailbox slot of the batch's peer reduction (PB200_OPT_PEER_ALLREDUCE), -1: none
   bool external = false;  // the caller took the device counts (pb200_count_batch_device) and may have queued work on them
   uint64_t seq = 0;  // begin order
 };
@@ -120,9 +121,22 @@ struct CountReq {
   std::atomic<bool> done{false};
   std::string err;
 };
+// Peer reduction between processes (engine_peer.inl): this context's mailbox and the peers' as mapped here.
+struct PeerState {
+  bool on = false;
+  int rank = 0, world = 1;
+  uint8_t* box = nullptr;
+  uint8_t* peer_box[8] = {};
+  uint64_t epoch = 0;
+  struct Pending { unsigned long long* target = nullptr; uint32_t n = 0; bool open = false; } pend[4];
+  cudaEvent_t launched[4] = {}, collected[4] = {};  // per slot: the batch's kernels are queued / its total has been picked up
+  bool collected_valid[4] = {};
+};
 }  // namespace pb200
 
 struct pb200_ctx {
+  pb200::PeerState peer;
+  bool peer_allreduce = false;  // PB200_OPT_PEER_ALLREDUCE: the split Count batches (_begin / _end) return counts summed over the peers
   int device = 0;
   // combining queue of pb200_count: threads that arrive while a launch is in flight are folded into the next batch
   std::mutex cq_mu;

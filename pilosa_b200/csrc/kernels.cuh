@@ -17,6 +17,63 @@
 
 namespace pb200 {
 
+// Cross-GPU sum of a batch's counts without a collective library: when the last CTA of the batch's last kernel retires,
+// it adds this GPU's partial counts into a mailbox slot of every participating GPU (plain system-scope reductions over
+// NVLink peer memory — the peers' buffers are mapped into this process, nothing is multicast) and then bumps each
+// mailbox's arrival counter; a GPU's own total is complete when its counter reaches the number of participants.
+constexpr int kPeerMax = 8;
+struct PushDesc {
+  uint32_t n_dst;                        // 0: no push
+  uint32_t n;                            // counts to push
+  unsigned int* ticket;                  // local, zeroed before the launch: CTAs retired so far
+  const unsigned long long* local;       // this GPU's partial counts
+  unsigned long long* dst[kPeerMax];     // slot of this epoch in every participant's mailbox (own one included)
+  unsigned long long* flag[kPeerMax];    // its arrival counter
+};
+
+__device__ __forceinline__ void peer_push(const PushDesc& pd, int tid, int nthreads) {
+  for (uint32_t q = tid; q < pd.n; q += nthreads) {
+    const unsigned long long v = __ldcg(pd.local + q);  // the counts were accumulated with L2 atomics
+    if (v)
+      for (uint32_t d = 0; d < pd.n_dst; d++) atomicAdd_system(pd.dst[d] + q, v);
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid == 0) {
+    for (uint32_t d = 0; d < pd.n_dst; d++) atomicAdd_system(pd.flag[d], 1ull);
+    *pd.ticket = 0u;  // this CTA was the ticket's last user: the slot's next batch finds it at zero
+  }
+}
+
+// stand-alone form, for batches whose last kernel is not eval_fast_kernel
+__global__ void peer_push_kernel(PushDesc pd) { peer_push(pd, threadIdx.x, blockDim.x); }
+
+// Waits until `world` participants have pushed into a mailbox slot, moves the totals to `out` and re-arms the slot.
+// err[0] is set when the peers do not arrive within ~2 s (a peer process died): the host reports it instead of hanging.
+__global__ void peer_collect_kernel(unsigned long long* slot, unsigned long long* flag, uint32_t world, uint32_t n, unsigned long long* out,
+                                    unsigned int* err) {
+  __shared__ int s_ok;
+  if (threadIdx.x == 0) {
+    const long long t0 = clock64();
+    int ok = 1;
+    while (*reinterpret_cast<volatile unsigned long long*>(flag) < world) {
+      if (clock64() - t0 > 4000000000ll) { ok = 0; break; }
+      __nanosleep(200);
+    }
+    __threadfence_system();
+    s_ok = ok;
+  }
+  __syncthreads();
+  if (!s_ok) { if (threadIdx.x == 0) atomicExch(err, 1u); return; }
+  for (uint32_t q = threadIdx.x; q < n; q += blockDim.x) {
+    out[q] = __ldcg(slot + q);
+    slot[q] = 0ull;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long*>(flag) = 0ull;
+}
+
 struct EvalParams {
   const FamilyDev* families;
   uint32_t n_families;
@@ -37,6 +94,7 @@ struct EvalParams {
   uint32_t slow_desc_stride;
   unsigned long long* algo_bytes;  // accumulated algorithmic bytes (payload + 16 B / container)
   uint32_t fold_all;               // eval_fold_kernel walks EVERY item itself (no eval_fast_kernel pass, no deferred list)
+  PushDesc push;                   // eval_fast_kernel only: peer reduction fused into the kernel's tail (n_dst == 0: none)
 };
 
 // ---------------------------------------------------------------------------------------
@@ -393,6 +451,17 @@ __global__ void __launch_bounds__(kFastWarps * 32) eval_fast_kernel(EvalParams p
     __syncwarp();
   }
   if (lane == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+  if (p.push.n_dst) {  // the CTA that retires last sends this GPU's counts to the peers: compute and reduction in one kernel
+    __shared__ int s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(p.push.ticket, 1u) == gridDim.x - 1 ? 1 : 0;
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      peer_push(p.push, threadIdx.x, blockDim.x);
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------

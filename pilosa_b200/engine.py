@@ -95,6 +95,10 @@ def load_library() -> C.CDLL:
         "pb200_bsi_max": (i32, [vp, u32, u32, np_, u32, u64p, u32, i64p, u64p]),
         "pb200_bsi_minmax_shards": (i32, [vp, u32, u32, np_, u32, i32, u64p, u32, i64p, u64p]),
         "pb200_last_timing": (i32, [vp, C.POINTER(Timing)]),
+        "pb200_peer_export": (i32, [vp, C.c_char_p]),
+        "pb200_peer_connect": (i32, [vp, i32, i32, C.c_char_p]),
+        "pb200_peer_flush": (i32, [vp]),
+        "pb200_batch_launch_allreduce": (i32, [vp, vp]),
     }
     # pb200_multi_*: the same argument lists behind the multi-GPU handle
     for name in MULTI_FORWARDED:
@@ -309,6 +313,25 @@ class Engine:
 
     def batch_launch(self, b) -> None:
         self._check(self.lib.pb200_batch_launch(self._h, b))
+
+    # ---- one process per GPU: counts summed over the ranks by the batch's own kernel (NVLink peer memory, no NCCL) ----
+    OPT_PEER_ALLREDUCE = 4
+    PEER_HANDLE_BYTES = 64
+
+    def peer_export(self) -> bytes:
+        buf = C.create_string_buffer(self.PEER_HANDLE_BYTES)
+        self._check(self.lib.pb200_peer_export(self._h, buf))
+        return buf.raw
+
+    def peer_connect(self, rank: int, world: int, handles: bytes) -> None:
+        assert len(handles) == world * self.PEER_HANDLE_BYTES
+        self._check(self.lib.pb200_peer_connect(self._h, rank, world, handles))
+
+    def peer_flush(self) -> None:
+        self._check(self.lib.pb200_peer_flush(self._h))
+
+    def batch_launch_allreduce(self, b) -> None:
+        self._check(self.lib.pb200_batch_launch_allreduce(self._h, b))
 
     def batch_device_counts(self, b) -> int:
         p = C.c_void_p()

@@ -81,6 +81,45 @@ def main():
     checks.append(("wide union", g.count(wide, shards), c.count(wide, shards)))
     checks.append(("wide in a batch", g.count_batch([wide, src, Difference(Row("m", 0), *[Row("z", r) for r in range(40)])], shards),
                    c.count_batch([wide, src, Difference(Row("m", 0), *[Row("z", r) for r in range(40)])], shards)))
+    # counts summed over the ranks by the batch's own kernel (peer mailboxes over NVLink, no NCCL): prepared batches
+    # launched back to back, several epochs deep, and the split _begin / _end form
+    import ctypes as C
+
+    handles = [None] * world
+    dist.all_gather_object(handles, eng.peer_export())
+    eng.peer_connect(rank, world, b"".join(handles))
+    local = [s for s in shards if s % world == rank]
+    qsets = [[src, Row("m", 1), Union(Row("m", 0), Row("f", 3))], [Row("f", 0), Xor(Row("m", 2), Row("m", 3))], [Intersect(Row("m", 0), Row("f", 1), Row("f", 2))] * 5]
+    sh = abi.u64_array(local)
+    prepared = []
+    for qs in qsets:
+        flat, off = eng.pack_programs([g.program(q) for q in qs])
+        prepared.append((eng.batch_prepare(flat, off, len(qs), sh, len(local)), qs, flat, off))
+    for rep in range(3):                      # 9 launches in a row: the mailbox slots are reused twice
+        for b, _, _, _ in prepared:
+            eng.batch_launch_allreduce(b)
+    for b, qs, _, _ in prepared:
+        out = (C.c_uint64 * len(qs))()
+        eng.batch_fetch(b, out)
+        checks.append((f"peer reduce / prepared x{len(qs)}", list(out), [c.count(q, shards) for q in qs]))
+    eng.set_option(eng.OPT_PEER_ALLREDUCE, 1)
+    outs = []
+    for k in range(5):                        # two batches in flight, like bench.py's e2e leg
+        _, qs, flat, off = prepared[k % 3]
+        eng.count_batch_begin(flat, off, len(qs), sh, len(local))
+        if k:
+            pq = prepared[(k - 1) % 3][1]
+            out = (C.c_uint64 * len(pq))()
+            eng.count_batch_end(out)
+            outs.append((list(out), [c.count(q, shards) for q in pq]))
+    pq = prepared[4 % 3][1]
+    out = (C.c_uint64 * len(pq))()
+    eng.count_batch_end(out)
+    outs.append((list(out), [c.count(q, shards) for q in pq]))
+    eng.set_option(eng.OPT_PEER_ALLREDUCE, 0)
+    checks.append(("peer reduce / begin-end", [a for a, _ in outs], [b for _, b in outs]))
+    for b, _, _, _ in prepared:
+        eng.batch_free(b)
     bad = [(n, a, b) for n, a, b in checks if a != b]
     ok = torch.tensor([0 if bad else 1], device="cuda")
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
