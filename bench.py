@@ -362,9 +362,18 @@ def main():
     B = args.batch
 
     def barrier():
+        """All ranks idle, then released together: the processes of one box share a clock, so after the collective
+        barrier rank 0 names a start time 2 ms ahead and every rank spins up to it — the ranks leave an NCCL barrier
+        hundreds of microseconds apart, which a 20-step timed region would otherwise carry as its tail."""
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
+            t = torch.tensor([time.time() + 0.002], dtype=torch.float64, device="cuda")
+            dist.broadcast(t, src=0)
+            deadline = float(t.item())
+            torch.cuda.synchronize()
+            while time.time() < deadline:
+                pass
         torch.cuda.synchronize()
 
     def max_over_ranks(x: float) -> float:
@@ -533,7 +542,7 @@ def main():
         "data": "synthetic", "config": workload_config(args, world),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(tm.h2d_bytes), "d2h_bytes_per_step": int(tm.d2h_bytes) + 8,
                 "ms_per_step": 1e3 * e2e_s / args.steps},
-        "gpu_launches": args.steps * 2 * int(max(1, tm.launches)),
+        "gpu_launches": args.steps * 2 * (1 + (1 if world > 1 else 0)),  # timed steps of both legs: one eval_fast_kernel each (+ one pick-up kernel for N > 1)
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "kernel": "eval_fast_kernel (K1: 128-bit AND + popcount over bitmap container pairs)",
