@@ -531,9 +531,9 @@ def main():
     achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9
     traffic, traffic_src = None, None
     try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
-        prof = json.load(open(os.path.join(ROOT, "profiles", "r01_eval_fast_summary.json")))
-        if B == 1024 and len(shards) == SHARDS_PER_GPU:
-            traffic, traffic_src = prof["traffic_bytes_per_launch"], "profiles/r01_eval_fast_summary.json (" + prof["command"] + ")"
+        prof = json.load(open(os.path.join(ROOT, "profiles", "r02_eval_fast_summary.json")))
+        if B == 1024 and len(shards) == SHARDS_PER_GPU and args.rows == 4096:  # the capture was taken on exactly this configuration
+            traffic, traffic_src = prof["traffic_bytes_per_launch"], "ncu capture of this configuration, not of this run: profiles/r02_eval_fast_summary.json (" + prof["command"] + ")"
     except Exception:
         pass
     line = {

@@ -723,8 +723,10 @@ struct Compiler {
     }
     if (maxsp > kMaxStack) { err = "expression too deeply nested (stack depth > 4)"; return false; }
     if (ins.size() > size_t(kMaxInstr)) { err = "expression too long (> 64 instructions)"; return false; }
-    for (size_t k = 0; k < ins.size(); k++)
-      if ((k > 0 && ins[k].op == I_LOAD) || (k > 0 && ins[k].op != I_AND_LEAF && ins[k].op != I_OR_LEAF)) out.any_bushy = true;  // what fold_can_take refuses
+    bool flat = !ins.empty() && ins[0].op == I_LOAD;
+    for (size_t k = 1; k < ins.size(); k++)
+      if (ins[k].op != I_AND_LEAF && ins[k].op != I_OR_LEAF) flat = false;  // what fold_can_take refuses
+    (flat ? out.any_flat : out.any_bushy) = true;
     pg.instr_off = uint32_t(out.instrs.size());
     pg.n_instr = uint32_t(ins.size());
     pg.leaf_off = leaf_base;
@@ -936,7 +938,7 @@ enum { OCC_FAST = 0, OCC_STAGED, OCC_SUM, OCC_MM, OCC_TOPN, OCC_FOLD };
 // Launches the fast + staged kernels for `n_queries` programs starting at `progs`.
 int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards, bool staging,
                 unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, uint8_t* dense_out, uint32_t* dense_n,
-                uint32_t max_leaves = kMaxLeaves, bool bushy = true, bool fold_all = false, const PushDesc* push = nullptr) {
+                uint32_t max_leaves = kMaxLeaves, bool bushy = true, bool fold_all = false, const PushDesc* push = nullptr, bool flat = true) {
   const uint64_t n_items = uint64_t(n_queries) * n_shards * kRowContainers;
   if (n_items == 0) return PB200_OK;
   if (n_items >= (1ull << 32)) return fail(ctx, PB200_ERR_RANGE, "batch too large: queries x shards x 16 must be < 2^32");
@@ -978,9 +980,11 @@ int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t 
     ctx->timing.launches++;
   }
   if (staging) {  // deferred items: flat left folds go to the fold kernel, anything else to the general staged evaluator
-    const uint32_t fgrid = uint32_t(std::min<uint64_t>(n_items, resident_ctas(ctx, OCC_FOLD, eval_fold_kernel, kFoldCtaThreads, kFoldSmem)));
-    eval_fold_kernel<<<fgrid, kFoldCtaThreads, kFoldSmem, ctx->stream>>>(p);
-    ctx->timing.launches++;
+    if (flat) {
+      const uint32_t fgrid = uint32_t(std::min<uint64_t>(n_items, resident_ctas(ctx, OCC_FOLD, eval_fold_kernel, kFoldCtaThreads, kFoldSmem)));
+      eval_fold_kernel<<<fgrid, kFoldCtaThreads, kFoldSmem, ctx->stream>>>(p);
+      ctx->timing.launches++;
+    }
     if (bushy) {
       const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, resident_ctas(ctx, OCC_STAGED, eval_staged_kernel, kStagedThreads, 0)));
       eval_staged_kernel<<<sgrid, kStagedThreads, 0, ctx->stream>>>(p);
@@ -1031,7 +1035,9 @@ int finish_call(pb200_ctx* ctx) {
 }
 
 // mean payload of the containers the batch's Row leaves come from; at a kilobyte and more the fold evaluator runs alone
-bool fold_all_of(const Compiled& cp) { return cp.may_need_staging && cp.leaf_containers && cp.leaf_payload / cp.leaf_containers >= 1024; }
+bool fold_all_of(const Compiled& cp) {  // (a batch with programs the fold kernel refuses keeps the first pass: all-bitmap items are cheapest there)
+  return cp.may_need_staging && !cp.any_bushy && cp.leaf_containers && cp.leaf_payload / cp.leaf_containers >= 1024;
+}
 
 uint32_t max_leaves_of(const Compiled& cp) {
   uint32_t m = 1;
@@ -1137,7 +1143,7 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
     if (rc == PB200_OK && reduce) rc = peer_begin_epoch(ctx, d_out, n_queries, pd, &sl.peer_slot);
     if (rc == PB200_OK)
       rc = launch_eval(ctx, bd, bd.progs, n_queries, n_shards, cp.may_need_staging, d_out, per_shard ? n_shards : 1, per_shard ? 1 : 0,
-                       nullptr, nullptr, max_leaves_of(cp), cp.any_bushy, fold_all_of(cp), reduce && !has_shift(cp) ? &pd : nullptr);
+                       nullptr, nullptr, max_leaves_of(cp), cp.any_bushy, fold_all_of(cp), reduce && !has_shift(cp) ? &pd : nullptr, cp.any_flat);
     if (rc == PB200_OK && reduce && has_shift(cp)) {  // the overflow pass below adds to the counts: push after it
       rc = launch_overflow(ctx, bd, bd.progs, n_queries, n_shards, d_out, 1, 0, nullptr);
       if (rc == PB200_OK) { peer_push_kernel<<<1, 256, 0, ctx->stream>>>(pd); ctx->timing.launches++; }
@@ -1409,7 +1415,7 @@ extern "C" int pb200_batch_launch(pb200_ctx* ctx, pb200_batch* b) {
   ctx->timing.launches = 0;
   CUDA_TRY(ctx, cudaMemsetAsync(b->d_counts.p, 0, size_t(b->n_queries) * 8, ctx->stream));
   return launch_eval(ctx, b->bd, b->bd.progs, b->n_queries, b->n_shards, b->cp.may_need_staging,
-                     static_cast<unsigned long long*>(b->d_counts.p), 1, 0, nullptr, nullptr, max_leaves_of(b->cp), b->cp.any_bushy, fold_all_of(b->cp));
+                     static_cast<unsigned long long*>(b->d_counts.p), 1, 0, nullptr, nullptr, max_leaves_of(b->cp), b->cp.any_bushy, fold_all_of(b->cp), nullptr, b->cp.any_flat);
 }
 
 extern "C" int pb200_batch_device_counts(pb200_ctx* ctx, pb200_batch* b, void** device_counts) {

@@ -93,6 +93,7 @@ struct Compiled {
   uint32_t n_temp_slots = 0;
   bool may_need_staging = false;  // some leaf family holds array/run containers (or temps)
   uint64_t leaf_payload = 0, leaf_containers = 0;  // summed over the Row leaves' families (see Family)
+  bool any_flat = false;          // some program is a fold eval_fold_kernel takes (LOAD, then AND / OR steps against leaves)
   bool any_bushy = false;         // some program is not a flat left fold (stack ops, Not): eval_staged_kernel is needed beside eval_fold_kernel
 };
 

@@ -365,7 +365,7 @@ void sort_pairs(std::vector<HPair>& p) {  // count desc; ties by ascending id (d
 // Host-side shard loop on a few threads (the reference runs its per-shard jobs on a worker
 // pool of NumCPU goroutines, executor.go:83-107; the selection walks are independent per shard).
 // persistent helper threads of the host-side shard loops (started once per process; a TopN call makes three of these
-// loops and thread start-up was a visible part of it); a second caller that finds them busy runs its loop inline
+// loops and thread start-up was a visible part of it)
 std::mutex& host_pool_mutex() { static std::mutex mu; return mu; }
 std::vector<std::unique_ptr<DevWorker>>& host_pool() { static std::vector<std::unique_ptr<DevWorker>> pool; return pool; }
 
@@ -375,8 +375,9 @@ void parallel_shards(uint32_t n, F&& fn) {
   std::vector<std::unique_ptr<DevWorker>>& pool = host_pool();
   unsigned hw = std::thread::hardware_concurrency();
   const unsigned nt = std::min<unsigned>(hw ? hw : 4, 12);
-  std::unique_lock<std::mutex> lk(pool_mu, std::try_to_lock);
-  if (n < 256 || nt < 2 || !lk.owns_lock()) { for (uint32_t s = 0; s < n; s++) fn(s); return; }
+  if (n < 256 || nt < 2) { for (uint32_t s = 0; s < n; s++) fn(s); return; }
+  std::unique_lock<std::mutex> lk(pool_mu);  // concurrent big loops (the devices of a pb200_multi) take turns on the helpers
+
   if (pool.empty()) for (unsigned t = 0; t + 1 < nt; t++) pool.emplace_back(new DevWorker());
   std::atomic<uint32_t> next{0};
   auto body = [&]() -> int {
