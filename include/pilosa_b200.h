@@ -452,7 +452,7 @@ int pb200_bsi_minmax_shards(pb200_ctx* ctx, pb200_family bsi_family, uint32_t bi
  * NCCL nor a partition of its own. Semantics are those of the single-device entry point of the same name.
  *   - all-to-all peer access (NVLink) is enabled at init. Every device's fragment table lists all shards,
  *     remote entries pointing into the owner's HBM, so a Count whose operands are small (estimated below
- *     PB200_OPT_SMALL_CALL_BYTES, default 24 MiB, and naming at most 1024 shards) is run by ONE device over its peers' memory — one
+ *     PB200_OPT_SMALL_CALL_BYTES, default 24 MiB, and at most 1024 (query, shard) pairs) is run by ONE device over its peers' memory — one
  *     launch, no fan-out latency; anything larger runs on the owners.
  *   - bitmap-returning calls (pb200_multi_eval_shards / _eval_proto_columns) are evaluated by the owners;
  *     the first device gathers their dense result rows over NVLink, types / serialises them once for the

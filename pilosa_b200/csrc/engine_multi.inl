@@ -32,7 +32,7 @@ struct pb200_multi {
   bool peer = false;                                // all-to-all peer access is on
   uint32_t rr = 0;                                  // next device for a single-device call
   uint64_t small_call_bytes = 24ull << 20;          // estimated operand bytes below which one device runs the whole call ...
-  uint32_t small_call_shards = 1024;                // ... provided it names no more shards than this
+  uint32_t small_call_shards = 1024;                // ... provided queries x shards is no more than this
   std::vector<FamStat> fam;
   pb200_timing timing{};
   DevBuf g_dense, g_dense_n, g_ovf, g_shards, g_pos;  // on ctx[0]'s device: gathered result rows of a bitmap-returning call
@@ -149,13 +149,14 @@ uint64_t estimate_bytes(const pb200_multi* m, const pb200_node* progs, uint32_t 
 }
 
 // Where a Count call runs: -1 = on the owners of its shards, else the one device that runs all of it over peer memory.
-int route_count(pb200_multi* m, const pb200_node* progs, uint32_t n_nodes, uint32_t n_shards) {
+int route_count(pb200_multi* m, const pb200_node* progs, uint32_t n_nodes, uint32_t n_queries, uint32_t n_shards) {
   if (m->ctx.size() == 1) return 0;
   if (!m->peer) return -1;
   // Remote reads pay NVLink latency per dependent load (shard -> fragment -> row table -> payload), so what one device
-  // can cover over its peers is bounded by the NUMBER of shards as well as by the bytes: measured on 2 GPUs, a sparse
-  // two-row Count over 512 shards costs the same either way, over 8192 shards the owners are twice as fast.
-  if (n_shards > m->small_call_shards || estimate_bytes(m, progs, n_nodes, n_shards) >= m->small_call_bytes) return -1;
+  // can cover over its peers is bounded by the NUMBER of (query, shard) pairs as well as by the bytes: measured, a
+  // sparse two-row Count over 512 shards costs the same either way, over 8192 shards the owners are twice as fast, and
+  // a batch of 256 such queries over 64 shards is 2x slower on one device than on the owners.
+  if (uint64_t(n_queries) * n_shards > m->small_call_shards || estimate_bytes(m, progs, n_nodes, n_shards) >= m->small_call_bytes) return -1;
   return int(m->rr++ % m->ctx.size());
 }
 
@@ -180,7 +181,7 @@ int count_batch_multi(pb200_multi* m, const pb200_node* progs, const uint32_t* p
                       uint32_t n_shards, uint64_t* out) {
   if (n_queries && (!progs || !prog_off || !out)) return PB200_ERR_INVALID;
   if (n_shards && !shards) return mfail(m, PB200_ERR_INVALID, "null shard list");
-  const int one = route_count(m, progs, n_queries ? prog_off[n_queries] : 0, n_shards);
+  const int one = route_count(m, progs, n_queries ? prog_off[n_queries] : 0, n_queries, n_shards);
   if (one >= 0) {
     const int rc = pb200_count_batch(m->ctx[one], progs, prog_off, n_queries, shards, n_shards, out);
     if (rc != PB200_OK) m->err = m->ctx[one]->err;
