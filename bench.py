@@ -83,7 +83,7 @@ class ClockSampler:
                 pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
             except Exception:
                 pw = None
-            self._samples.append((sm, mx, [k for k, b in bits.items() if r & b], pw))
+            self._samples.append((sm, mx, [k for k, b in bits.items() if r & b], pw, time.time()))
             time.sleep(0.002)
 
     def start(self):
@@ -107,10 +107,18 @@ class ClockSampler:
         for ln in self.proc.stdout:
             self.lines.append(ln.strip())
 
+    def mark(self):
+        """Start of the timed region: earlier samples (the poller is started BEFORE the barrier so that rank 0 does not
+        enter the region late) are dropped when the result is formed."""
+        self.t_mark = time.time()
+
     def stop(self):
         if self.nvml is not None:
             self._stop = True
             self.nvml.join(timeout=2)
+            t_mark = getattr(self, "t_mark", 0.0)
+            kept = [s for s in self._samples if s[4] >= t_mark]
+            self._samples = kept or self._samples[-1:]
             sm = [s[0] for s in self._samples]
             reasons = sorted({r for s in self._samples for r in s[2]})
             pw = [s[3] for s in self._samples if s[3] is not None]
@@ -312,6 +320,7 @@ def main():
     ap.add_argument("--cpu-scan", action="store_true", help="reference arm: also time the pool at 1/2/4/P workers")
     ap.add_argument("--sustained-seconds", type=float, default=2.0)
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (fixed 128-shard index)")
+    ap.add_argument("--trace-steps", action="store_true", help="stderr: device time of every timed step of the resident leg (diagnostic)")
     args = ap.parse_args()
     if args.warmup < 3:
         raise SystemExit("bench.py: --warmup must be >= 3 (timing rule); got %d" % args.warmup)
@@ -404,17 +413,25 @@ def main():
         for i in range(args.warmup):
             step_resident(i)
         join_side()
-        barrier()
         if rank == 0:  # one poller per box: concurrent NVML queries from every rank serialise in the driver
             sampler.start()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        sampler.mark()
         ev0.record(stream)
+        marks = []
         for i in range(args.warmup, n_batches):
             step_resident(i)
+            if args.trace_steps:
+                marks.append(torch.cuda.Event(enable_timing=True))
+                marks[-1].record(stream)
         join_side()                      # the last all-reduce is inside the timed region
         ev1.record(stream)
         barrier()
         ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+        if args.trace_steps:
+            ts = [ev0.elapsed_time(m) for m in marks] + [ev0.elapsed_time(ev1)]
+            print(f"rank {rank} step ends (ms): " + " ".join(f"{t:.3f}" for t in ts), file=sys.stderr, flush=True)
         out = (C.c_uint64 * B)()
         eng.batch_fetch(prepared[-1], out)
         last_resident = list(out)
@@ -425,10 +442,11 @@ def main():
         if args.sustained_seconds > 0:
             n_sus = max(args.steps, int(args.sustained_seconds / max(1e-6, ms_total / args.steps * 1e-3)) + 1)
             sus_sampler = ClockSampler(local_rank)
-            barrier()
             if rank == 0:
                 sus_sampler.start()
             s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            sus_sampler.mark()
             s0.record(stream)
             for k in range(n_sus):
                 step_resident(k % len(prepared))
