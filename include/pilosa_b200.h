@@ -552,6 +552,14 @@ int pb200_peer_connect(pb200_ctx* ctx, int rank, int world, const void* handles)
 int pb200_peer_flush(pb200_ctx* ctx);   /* queue the pick-up of every batch still in flight on the context's stream */
 int pb200_batch_launch_allreduce(pb200_ctx* ctx, pb200_batch* batch);
 
+/* Size the context's scratch (device and page-locked) once for the largest Count batch the host will issue:
+ * max_queries programs of up to max_nodes_per_query nodes over max_shards shards. Without it the scratch grows on
+ * demand — a cudaMalloc plus a cudaFree of the smaller buffer, which stalls the whole device — on the first calls of
+ * each new size; after it no pb200_count / _count_batch / _count_batch_begin call within those bounds allocates.
+ * Programs with BSI range / Shift leaves materialise temporaries sized by the call and are outside the reservation.
+ * Also brings the device-side fragment tables up to date. No reference counterpart (Go allocates per call). */
+int pb200_reserve(pb200_ctx* ctx, uint32_t max_queries, uint32_t max_shards, uint32_t max_nodes_per_query);
+
 /* Timing / byte accounting of the last query call on this context. */
 int pb200_last_timing(pb200_ctx* ctx, pb200_timing* out);
 

@@ -179,6 +179,8 @@ extern "C" int pb200_init(int device, size_t hbm_budget_bytes, pb200_ctx** out) 
   cudaDeviceProp prop{};
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return PB200_ERR_CUDA; }
   ctx->sm_count = prop.multiProcessorCount;
+  // the fold evaluator's window + scratch + staging ring may exceed the 48 KiB a kernel gets without asking
+  if (cudaFuncSetAttribute(eval_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFoldSmem) != cudaSuccess) { delete ctx; return PB200_ERR_CUDA; }
   if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
     delete ctx;
@@ -1553,7 +1555,7 @@ extern "C" int pb200_count_pairs_noalloc(pb200_ctx* ctx, pb200_family family, co
   p.algo_bytes = reinterpret_cast<unsigned long long*>(scratch + kNaCounters + 8);
   const uint32_t grid = uint32_t(std::min<uint64_t>((n_items + kFastWarps - 1) / kFastWarps, uint64_t(ctx->sm_count) * 8));
   eval_fast_kernel<<<grid, kFastWarps * 32, 0, ctx->stream>>>(p);
-  const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, uint64_t(ctx->sm_count) * 5));
+  const uint32_t sgrid = uint32_t(std::min<uint64_t>(n_items, uint64_t(ctx->sm_count) * PB200_FOLD_CTAS));
   eval_fold_kernel<<<sgrid, kFoldCtaThreads, kFoldSmem, ctx->stream>>>(p);  // a two-leaf Intersect is a flat fold
   CUDA_TRY(ctx, cudaGetLastError());
   return PB200_OK;

@@ -166,3 +166,44 @@ extern "C" int pb200_batch_launch_allreduce(pb200_ctx* ctx, pb200_batch* b) {
                   nullptr, nullptr, max_leaves_of(b->cp), b->cp.any_bushy, fold_all_of(b->cp), &pd, b->cp.any_flat));
   return peer_end_epoch(ctx, slot);
 }
+
+// ---------------------------------------------------------------------------------------
+// Scratch reservation: the query path grows its device / pinned scratch on demand (cudaMalloc, and a cudaFree of the
+// smaller buffer, which synchronises the whole device). A serving host sizes it once, up front, for the largest batch
+// it will issue; afterwards no Count / batch call of that size or smaller allocates.
+// ---------------------------------------------------------------------------------------
+extern "C" int pb200_reserve(pb200_ctx* ctx, uint32_t max_queries, uint32_t max_shards, uint32_t max_nodes_per_query) {
+  ENTER(ctx);
+  if (!max_queries || !max_shards) return PB200_ERR_INVALID;
+  const uint64_t n_items = uint64_t(max_queries) * max_shards * kRowContainers;
+  if (n_items >= (1ull << 32)) return fail(ctx, PB200_ERR_RANGE, "queries x shards x 16 must be < 2^32");
+  const uint32_t nodes = std::max<uint32_t>(3, max_nodes_per_query);
+  const uint32_t leaves = std::min<uint32_t>(nodes, uint32_t(kMaxLeaves));
+  // upload image of a batch: programs, leaves, instructions, shard list (upload_batch)
+  const size_t batch_bytes = 2 * size_t(max_queries) * (sizeof(Prog) + size_t(nodes) * (sizeof(Leaf) + sizeof(Instr))) + size_t(max_shards) * 8 + 256;
+  TRY(ensure_dev(ctx, ctx->d_misc, 64));
+  TRY(ensure_dev(ctx, ctx->d_slow, size_t(n_items) * 4));
+  const uint64_t desc_bytes = n_items * uint64_t(leaves) * sizeof(ContainerDesc);
+  if (desc_bytes <= (256ull << 20)) TRY(ensure_dev(ctx, ctx->d_slow_descs, size_t(desc_bytes)));
+  TRY(ensure_dev(ctx, ctx->d_batch, batch_bytes));
+  TRY(ensure_pin(ctx, ctx->h_stage, batch_bytes));
+  TRY(ensure_dev(ctx, ctx->d_out, size_t(max_queries) * 8));
+  TRY(ensure_pin(ctx, ctx->h_out, size_t(max_queries) * 8 + 8));
+  TRY(ensure_pin(ctx, ctx->h_algo, 64));
+  if (!ctx->copy_stream) CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  for (CountSlot& sl : ctx->slots) {  // the two slots of pb200_count / pb200_count_batch(_begin)
+    if (!sl.k0) {
+      CUDA_TRY(ctx, cudaEventCreate(&sl.k0)); CUDA_TRY(ctx, cudaEventCreate(&sl.k1));
+      CUDA_TRY(ctx, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    }
+    std::swap(ctx->d_out, sl.d_out); std::swap(ctx->d_batch, sl.d_batch); std::swap(ctx->h_stage, sl.h_stage); std::swap(ctx->h_out, sl.h_out);
+    int rc = ensure_dev(ctx, ctx->d_out, size_t(max_queries) * 8);
+    if (rc == PB200_OK) rc = ensure_dev(ctx, ctx->d_batch, batch_bytes);
+    if (rc == PB200_OK) rc = ensure_pin(ctx, ctx->h_stage, batch_bytes);
+    if (rc == PB200_OK) rc = ensure_pin(ctx, ctx->h_out, size_t(max_queries) * 8 + 8);
+    std::swap(ctx->d_out, sl.d_out); std::swap(ctx->d_batch, sl.d_batch); std::swap(ctx->h_stage, sl.h_stage); std::swap(ctx->h_out, sl.h_out);
+    TRY(rc);
+  }
+  TRY(sync_families(ctx));
+  return PB200_OK;
+}

@@ -695,138 +695,168 @@ __global__ void __launch_bounds__(kStagedThreads) eval_staged_kernel(EvalParams 
 // shared-memory window; each operand is applied to it IN ITS OWN ENCODING, so an operand costs its payload, not
 // 65536 bits: the type pairs of roaring.go:3078-4957 become
 //                bitmap (1024 words)     array (n x u16)                       run list
-//   load / OR    w (|)= g                set the value's bit                   set [start,last]   (union*  :3470-3839)
-//   XOR          w ^= g                  flip the bit                          flip [start,last]  (xor*    :4266-4957)
-//   ANDNOT       w &= ~g                 clear the bit                         clear [start,last] (difference* :3920-4205)
-//   AND          w &= g                  probe the bits, rebuild the window    clear the gaps     (intersect*  :3254-3418)
+//   load / OR    w (|)= g                set the value's bit                   OR  the run bitmap (union*     :3470-3839)
+//   AND          w &= g                  AND the array's bitmap                AND the run bitmap (intersect* :3254-3418)
 // Payloads are contiguous 16 B aligned streams, so the bulk copy engine moves each one global -> shared with one
 // cp.async.bulk issued by one thread (local HBM only, no multicast), up to kFoldStages operands ahead of the one being
-// applied; completion is an mbarrier transaction count. Elements are sorted, so a thread that takes 16 consecutive
-// values (8 consecutive runs) owns every window word strictly between its first and its last one: only those two
-// words are edited with shared-memory atomics (ATOMS costs 2 cycles per lane on this part; one per value was the
-// whole run time), the rest with plain read-modify-writes. The count is the popcount of the window; no result
-// container is typed or written unless the caller wants the dense row.
+// applied; completion is an mbarrier transaction count.
+//   Sorted elements -> bits without atomics: a thread takes a slice of 8 consecutive values (4 consecutive runs). A
+// bitmap word belongs to the slice that holds the word's FIRST element: a thread drops its leading elements that fall
+// into the word of the element in front of its slice, and reads on past the end of its slice while elements stay in
+// its last word. Every word is then written by exactly one thread, once, with a plain store.
+//   Run list -> bitmap without touching a word per run: starts go into one zeroed scratch bitmap S, the positions
+// behind the runs' last values into another, E, and the run bitmap is the 65536-bit integer E - S: (1 << (last + 1))
+// - (1 << start) is exactly the ones of one run, and disjoint runs do not interfere. A thread owns 8 consecutive
+// words, subtracts them with one borrow chain (9 instructions), and gets its borrow-in — "a run is open at my first
+// position" — as the parity of the bits in front of it: a warp ballot plus one shared-memory hop across the warps.
+// S and E are kept zero between uses (the subtraction clears what it reads).
+// The count is the popcount of the window; no result container is typed or written unless the caller wants the row.
 // ---------------------------------------------------------------------------------------
 constexpr int kFoldThreads = 256;                      // consumer threads (8 warps) ...
 constexpr int kFoldCtaThreads = kFoldThreads + 32;     // ... plus one producer warp
-constexpr int kFoldStages = 4;
+#ifndef PB200_FOLD_STAGES
+#define PB200_FOLD_STAGES 2
+#endif
+#ifndef PB200_FOLD_CTAS
+#define PB200_FOLD_CTAS 5
+#endif
+constexpr int kFoldStages = PB200_FOLD_STAGES;          // 2: applying an operand takes longer than fetching the next one
 constexpr int kFoldMeta = 2;                            // items whose descriptors are resolved ahead
-constexpr int kFoldSmem = (1 + kFoldStages) * kBitmapBytes;  // dynamic shared memory: the window + the staging ring
+constexpr int kFoldFixed = 3;                           // window, S, E
+constexpr int kFoldSmem = (kFoldFixed + kFoldStages) * kBitmapBytes;  // dynamic shared memory
+constexpr uint32_t kWords32 = kBitmapBytes / 4;
 // barrier among the consumer warps only (the producer warp never joins it)
 __device__ __forceinline__ void fold_bar() { asm volatile("bar.sync 1, %0;" :: "n"(kFoldThreads) : "memory"); }
-enum RangeMode : int { R_SET = 0, R_CLEAR = 1, R_FLIP = 2 };
 
-// One (word, mask) edit; `shared_word` says whether another thread may edit the same word during this operand.
-__device__ __forceinline__ void fold_word(uint32_t* w, uint32_t mask, int mode, bool shared_word) {
-  if (shared_word) {
-    if (mode == R_SET) atomicOr(w, mask);
-    else if (mode == R_CLEAR) atomicAnd(w, ~mask);
-    else atomicXor(w, mask);
-  } else {
-    const uint32_t old = *w;
-    *w = mode == R_SET ? (old | mask) : mode == R_CLEAR ? (old & ~mask) : (old ^ mask);
-  }
+// shared-window accesses by 32-bit shared address: the helpers below are handed addresses, not generic pointers, so no
+// store pays for a generic -> shared conversion
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a) { uint32_t v; asm volatile("{ .reg .u16 h; ld.shared.u16 h, [%1]; cvt.u32.u16 %0, h; }" : "=r"(v) : "r"(a) : "memory"); return v; }
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
+
+// element i of a staged payload (at shared address `base`) as a bit position
+struct PosArray { uint32_t base; __device__ __forceinline__ uint32_t operator()(uint32_t i) const { return lds_u16(base + 2u * i); } };
+struct PosRunStart { uint32_t base; __device__ __forceinline__ uint32_t operator()(uint32_t i) const { return lds_u16(base + 4u * i); } };
+struct PosRunEnd { uint32_t base; __device__ __forceinline__ uint32_t operator()(uint32_t i) const { return lds_u16(base + 4u * i + 2u) + 1u; } };  // 65536 behind a run that ends the container
+
+template <bool RMW>
+__device__ __forceinline__ void fold_put(uint32_t bm, uint32_t w, uint32_t bits) {
+  const uint32_t a = bm + 4u * w;
+  sts_u32(a, RMW ? (lds_u32(a) | bits) : bits);
 }
 
-// Sets / clears / flips the bits of 16 consecutive array values held by one thread. The values ascend, so the words
-// between the thread's first and last one are its own: the first and the last flush are atomic, the others plain.
-template <int MODE>
-__device__ __noinline__ void fold_array16(uint32_t* win32, const uint4* st4, uint32_t len, int tid) {
-  // 8 values per thread up to 2048 values (every warp has work), 16 beyond
-  const uint32_t per = len <= 8u * kFoldThreads ? 8u : 16u;
-  const uint32_t first = uint32_t(tid) * per;
-  if (first >= len) return;
-  const uint32_t n = min(per, len - first);
-  const uint4 q0 = st4[first >> 3];
-  uint4 q1 = make_uint4(0, 0, 0, 0);
-  if (n > 8) q1 = st4[(first >> 3) + 1];
-  const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-  uint32_t cur_w = (w[0] & 0xffff) >> 5, cur_bits = 0;
-  bool at_first = true;
+// One slice: elements [first, first + cnt) are in v[0 .. cnt), cnt <= N; `pos` reads any element of the sequence.
+// RMW: the bitmap (shared address bm) holds other bits already (the window); otherwise it is zero (S / E).
+// GUARD: the last element may be position 65536, which has no word.
+template <int N, bool FULL, bool RMW, bool GUARD, class POS>
+__device__ __forceinline__ void fold_set_slice(uint32_t bm, const uint32_t (&v)[N], uint32_t cnt, uint32_t first, uint32_t len, const POS& pos) {
+  // the word in front of the slice belongs to an earlier slice: bits gathered for it are dropped. Words ascend, so
+  // "cur_w is mine" is "cur_w != foreign" at every flush — no flag is carried through the loop.
+  const uint32_t foreign = first ? (pos(first - 1) >> 5) : 0xffffffffu;
+  uint32_t cur_w = foreign, cur_b = 0;
 #pragma unroll
-  for (int k = 0; k < 16; k++) {
-    if (uint32_t(k) < n) {
-      const uint32_t val = (k & 1) ? (w[k >> 1] >> 16) : (w[k >> 1] & 0xffff);
-      if ((val >> 5) != cur_w) {
-        fold_word(&win32[cur_w], cur_bits, MODE, at_first);
-        at_first = false;
-        cur_w = val >> 5; cur_bits = 0;
-      }
-      cur_bits |= 1u << (val & 31);
+  for (int k = 0; k < N; k++) {
+    if (FULL || uint32_t(k) < cnt) {
+      const uint32_t w = v[k] >> 5;
+      const uint32_t bit = __funnelshift_l(0u, 1u, v[k]);  // 1 << (v & 31)
+      const bool chg = w != cur_w;
+      if (chg && cur_w != foreign) fold_put<RMW>(bm, cur_w, cur_b);
+      cur_b = chg ? bit : (cur_b | bit);
+      cur_w = w;
     }
   }
-  fold_word(&win32[cur_w], cur_bits, MODE, true);
+  if (cur_w == foreign) return;  // the whole slice lies in a word of an earlier slice
+  for (uint32_t i = first + cnt; i < len; i++) {  // the rest of the last word: at most 31 elements
+    const uint32_t x = pos(i);
+    if ((x >> 5) != cur_w) break;
+    cur_b |= __funnelshift_l(0u, 1u, x);
+  }
+  if (!GUARD || cur_w < kWords32) fold_put<RMW>(bm, cur_w, cur_b);
 }
 
-// A run list as a bitmap, without touching a word per run: every run toggles two bits of a zeroed scratch window —
-// its start and the position behind its last value — and the run bitmap is the running parity (prefix XOR) of those
-// toggles over the 65536 positions. The toggles go in like array values (sorted, 16 per thread, atomics only on a
-// thread's first and last word); the scan costs the same whatever the runs look like: a thread owns 8 consecutive
-// words, XOR-scans inside each word with five shifts, carries the parity from word to word, and gets the parity of
-// everything in front of it from a warp ballot and one shared-memory hop across the eight warps. The result is
-// applied to the accumulator word by word (op: I_OR / I_XOR / I_ANDNOT / I_AND _LEAF).
-// `scratch` is the operand's own staging slot: the runs are taken into registers first, then the slot is reused.
+// The bits of a sorted array container into `bm`: the window (RMW, union) or the zeroed scratch S (intersection).
+template <bool RMW>
+__device__ __noinline__ void fold_array_set(uint32_t bm, uint32_t st, uint32_t len, int tid) {
+  const PosArray pos{st};
+  for (uint32_t first = uint32_t(tid) * 8u; first < len; first += kFoldThreads * 8u) {
+    uint4 q;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w) : "r"(st + 2u * first) : "memory");
+    const uint32_t v[8] = {q.x & 0xffffu, q.x >> 16, q.y & 0xffffu, q.y >> 16, q.z & 0xffffu, q.z >> 16, q.w & 0xffffu, q.w >> 16};
+    const uint32_t cnt = len - first;
+    if (cnt >= 8u) fold_set_slice<8, true, RMW, false>(bm, v, 8u, first, len, pos);
+    else fold_set_slice<8, false, RMW, false>(bm, v, cnt, first, len, pos);
+  }
+}
+
+// r = e - s - borrow over 8 words, least significant first
+__device__ __forceinline__ void fold_sub8(uint32_t (&r)[8], const uint32_t (&e)[8], const uint32_t (&s)[8], uint32_t borrow) {
+  asm("{\n\t"
+      ".reg .u32 t;\n\t"
+      "sub.cc.u32 t, 0, %24;\n\t"
+      "subc.cc.u32 %0, %8, %16;\n\t"
+      "subc.cc.u32 %1, %9, %17;\n\t"
+      "subc.cc.u32 %2, %10, %18;\n\t"
+      "subc.cc.u32 %3, %11, %19;\n\t"
+      "subc.cc.u32 %4, %12, %20;\n\t"
+      "subc.cc.u32 %5, %13, %21;\n\t"
+      "subc.cc.u32 %6, %14, %22;\n\t"
+      "subc.u32 %7, %15, %23;\n\t"
+      "}"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+      : "r"(e[0]), "r"(e[1]), "r"(e[2]), "r"(e[3]), "r"(e[4]), "r"(e[5]), "r"(e[6]), "r"(e[7]),
+        "r"(s[0]), "r"(s[1]), "r"(s[2]), "r"(s[3]), "r"(s[4]), "r"(s[5]), "r"(s[6]), "r"(s[7]), "r"(borrow));
+}
+
+// A run list applied to the window (OP: I_OR_LEAF / I_AND_LEAF). S, E: the zeroed scratch bitmaps; left zeroed.
 template <int OP>
-__device__ __noinline__ void fold_runs_scan(uint32_t* win32, uint32_t* scratch, uint32_t len, uint32_t* s_par, int tid) {
+__device__ __noinline__ void fold_runs(uint32_t* win32, uint32_t* S, uint32_t* E, uint32_t st, uint32_t len, uint32_t* s_par, int tid) {
   const int lane = tid & 31, warp = tid >> 5;
-  const uint32_t per = len <= 4u * kFoldThreads ? 4u : 8u;  // runs per thread: every warp has work up to 1024 runs
-  const uint32_t first = uint32_t(tid) * per;
-  const uint32_t n = first < len ? min(per, len - first) : 0u;
-  uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
-  if (n) { q0 = reinterpret_cast<const uint4*>(scratch)[first >> 2]; if (n > 4) q1 = reinterpret_cast<const uint4*>(scratch)[(first >> 2) + 1]; }
-  fold_bar();  // every run is in a register
-  reinterpret_cast<uint4*>(scratch)[tid] = make_uint4(0, 0, 0, 0);
-  reinterpret_cast<uint4*>(scratch)[tid + kFoldThreads] = make_uint4(0, 0, 0, 0);
-  fold_bar();
-  if (n) {  // toggles at start and last + 1 of each run: ascending positions, so the ownership rule of fold_array16 holds
-    const uint32_t r[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-    uint32_t cur_w = (r[0] & 0xffff) >> 5, cur_bits = 0;
-    bool at_first = true;
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      if (uint32_t(k) < n) {
-#pragma unroll
-        for (int e = 0; e < 2; e++) {
-          const uint32_t pos = e == 0 ? (r[k] & 0xffff) : (r[k] >> 16) + 1u;
-          if (pos < 65536u) {
-            if ((pos >> 5) != cur_w) {
-              if (cur_bits) fold_word(&scratch[cur_w], cur_bits, R_FLIP, at_first);
-              at_first = false;
-              cur_w = pos >> 5; cur_bits = 0;
-            }
-            cur_bits ^= 1u << (pos & 31);
-          }
-        }
-      }
+  const PosRunStart ps{st};
+  const PosRunEnd pe{st};
+  const uint32_t S_a = smem_u32(S), E_a = smem_u32(E);
+  for (uint32_t first = uint32_t(tid) * 4u; first < len; first += kFoldThreads * 4u) {
+    uint4 q;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w) : "r"(st + 4u * first) : "memory");
+    const uint32_t vs[4] = {q.x & 0xffffu, q.y & 0xffffu, q.z & 0xffffu, q.w & 0xffffu};
+    const uint32_t ve[4] = {(q.x >> 16) + 1u, (q.y >> 16) + 1u, (q.z >> 16) + 1u, (q.w >> 16) + 1u};
+    const uint32_t cnt = len - first;
+    if (cnt >= 4u) {
+      fold_set_slice<4, true, false, false>(S_a, vs, 4u, first, len, ps);
+      fold_set_slice<4, true, false, true>(E_a, ve, 4u, first, len, pe);
+    } else {
+      fold_set_slice<4, false, false, false>(S_a, vs, cnt, first, len, ps);
+      fold_set_slice<4, false, false, true>(E_a, ve, cnt, first, len, pe);
     }
-    if (cur_bits) fold_word(&scratch[cur_w], cur_bits, R_FLIP, true);
   }
   fold_bar();
-  // scan: words 8 tid .. 8 tid + 7
-  const uint4 d0 = reinterpret_cast<const uint4*>(scratch)[2 * tid], d1 = reinterpret_cast<const uint4*>(scratch)[2 * tid + 1];
-  uint32_t x[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+  // words 8 tid .. 8 tid + 7 of E - S
+  uint4* S4 = reinterpret_cast<uint4*>(S);
+  uint4* E4 = reinterpret_cast<uint4*>(E);
+  const uint4 s0 = S4[2 * tid], s1 = S4[2 * tid + 1], e0 = E4[2 * tid], e1 = E4[2 * tid + 1];
+  const uint4 zero4 = make_uint4(0, 0, 0, 0);
+  S4[2 * tid] = zero4; S4[2 * tid + 1] = zero4; E4[2 * tid] = zero4; E4[2 * tid + 1] = zero4;
+  const uint32_t s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+  const uint32_t e[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
   uint32_t par = 0;
 #pragma unroll
-  for (int k = 0; k < 8; k++) par ^= x[k];
-  par = __popc(par) & 1u;
-  const uint32_t votes = __ballot_sync(0xffffffffu, par != 0);
+  for (int k = 0; k < 8; k++) par ^= s[k] ^ e[k];
+  const uint32_t votes = __ballot_sync(0xffffffffu, (__popc(par) & 1u) != 0);
   if (lane == 0) s_par[warp] = __popc(votes) & 1u;
   fold_bar();
-  uint32_t before = __popc(votes & ((1u << lane) - 1u)) & 1u;
-  for (int w = 0; w < warp; w++) before ^= s_par[w];
-  uint32_t carry = 0u - before;  // all ones when an odd number of toggles lies in front of this thread's words
-  uint4 a0 = reinterpret_cast<const uint4*>(win32)[2 * tid], a1 = reinterpret_cast<const uint4*>(win32)[2 * tid + 1];
-  uint32_t acc[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-#pragma unroll
-  for (int k = 0; k < 8; k++) {
-    uint32_t y = x[k];
-    y ^= y << 1; y ^= y << 2; y ^= y << 4; y ^= y << 8; y ^= y << 16;
-    y ^= carry;
-    carry = 0u - (y >> 31);
-    acc[k] = OP == I_OR_LEAF ? (acc[k] | y) : OP == I_XOR_LEAF ? (acc[k] ^ y) : OP == I_ANDNOT_LEAF ? (acc[k] & ~y) : (acc[k] & y);
+  const uint32_t wvotes = __ballot_sync(0xffffffffu, lane < kFoldThreads / 32 && s_par[lane & (kFoldThreads / 32 - 1)] != 0);
+  // starts minus ends in front of this thread's words: 0 or 1 — a run is open there
+  const uint32_t borrow = (__popc(votes & ((1u << lane) - 1u)) + __popc(wvotes & ((1u << warp) - 1u))) & 1u;
+  uint32_t r[8];
+  fold_sub8(r, e, s, borrow);
+  uint4* W4 = reinterpret_cast<uint4*>(win32);
+  const uint4 a0 = W4[2 * tid], a1 = W4[2 * tid + 1];
+  if (OP == I_OR_LEAF) {
+    W4[2 * tid] = make_uint4(a0.x | r[0], a0.y | r[1], a0.z | r[2], a0.w | r[3]);
+    W4[2 * tid + 1] = make_uint4(a1.x | r[4], a1.y | r[5], a1.z | r[6], a1.w | r[7]);
+  } else {
+    W4[2 * tid] = make_uint4(a0.x & r[0], a0.y & r[1], a0.z & r[2], a0.w & r[3]);
+    W4[2 * tid + 1] = make_uint4(a1.x & r[4], a1.y & r[5], a1.z & r[6], a1.w & r[7]);
   }
-  reinterpret_cast<uint4*>(win32)[2 * tid] = make_uint4(acc[0], acc[1], acc[2], acc[3]);
-  reinterpret_cast<uint4*>(win32)[2 * tid + 1] = make_uint4(acc[4], acc[5], acc[6], acc[7]);
 }
 
 // Payload bytes the copy engine moves for an operand (a multiple of 16; 0 = constant operand, nothing to move).
@@ -850,8 +880,8 @@ struct FoldMeta {  // one deferred item, resolved by the producer warp
 // payload is one cp.async.bulk into the next free slot of a kFoldStages-deep staging ring (full / empty mbarriers),
 // issued as soon as the slot is released, whatever item it belongs to. Warps 0-7 are the CONSUMERS: they never wait
 // for global memory except on a cold pipeline, only for `full`, and synchronise among themselves with a named barrier.
-__global__ void __launch_bounds__(kFoldCtaThreads, 5) eval_fold_kernel(EvalParams p) {
-  extern __shared__ __align__(128) uint8_t s_dyn[];  // [window 8 KiB][kFoldStages x 8 KiB staging]
+__global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_kernel(EvalParams p) {
+  extern __shared__ __align__(128) uint8_t s_dyn[];  // [window][S][E][kFoldStages x staging], 8 KiB each
   __shared__ FoldMeta s_meta[kFoldMeta];
   __shared__ uint32_t s_red[kFoldThreads / 32];
   __shared__ __align__(8) uint64_t s_full[kFoldStages], s_empty[kFoldStages], s_mfull[kFoldMeta], s_mempty[kFoldMeta];
@@ -885,6 +915,10 @@ __global__ void __launch_bounds__(kFoldCtaThreads, 5) eval_fold_kernel(EvalParam
                                                               : resolve_leaf(p, p.leaves[pg.leaf_off + lane], sidx, c);
         m.desc[lane] = d;
         bytes = desc_algo_bytes(d);
+        // the staging ring is two operands deep; the payloads of the whole item are pulled towards L2 now, an item ahead
+        // of the consumers, so that the ring's loads find them there
+        const uint32_t fb = fold_bytes(d);
+        if (fb && pg.n_instr > 1) l2_prefetch_bulk(reinterpret_cast<const void*>(d.addr), fb);
       }
       if (p.fold_all) {  // no eval_fast_kernel pass did the byte accounting
         bytes = warp_sum(bytes);
@@ -906,7 +940,7 @@ __global__ void __launch_bounds__(kFoldCtaThreads, 5) eval_fold_kernel(EvalParam
             const uint32_t slot = g % kFoldStages;
             if (g >= uint32_t(kFoldStages)) mbar_wait(&s_empty[slot], ((g / kFoldStages) - 1u) & 1u);
             mbar_arrive_expect_tx(&s_full[slot], bytes);
-            tma_load_1d(s_dyn + size_t(slot + 1) * kBitmapBytes, reinterpret_cast<const void*>(d.addr), bytes, &s_full[slot]);
+            tma_load_1d(s_dyn + size_t(slot + kFoldFixed) * kBitmapBytes, reinterpret_cast<const void*>(d.addr), bytes, &s_full[slot]);
             g++;
           }
       }
@@ -918,19 +952,35 @@ __global__ void __launch_bounds__(kFoldCtaThreads, 5) eval_fold_kernel(EvalParam
 
   // ---------------- consumer warps ----------------
   uint32_t* s_win = reinterpret_cast<uint32_t*>(s_dyn);
+  uint32_t* s_S = reinterpret_cast<uint32_t*>(s_dyn + kBitmapBytes);
+  uint32_t* s_E = reinterpret_cast<uint32_t*>(s_dyn + 2 * kBitmapBytes);
   uint4* win4 = reinterpret_cast<uint4*>(s_dyn);
+  uint4* S4 = reinterpret_cast<uint4*>(s_S);
+  const uint32_t dyn_a = smem_u32(s_dyn), win_a = dyn_a, S_a = dyn_a + kBitmapBytes;
   const uint4 zero4 = make_uint4(0, 0, 0, 0), ones4 = make_uint4(~0u, ~0u, ~0u, ~0u);
+  for (int i = tid; i < 2 * kBitmapBytes / 16; i += kFoldThreads) S4[i] = zero4;  // S and E start out zero (and stay so between uses)
+  fold_bar();
   uint32_t g = 0, j = 0;
+  // Counts: every warp keeps a running sum of its part of the windows for as long as the items add into the same
+  // output counter (for Count that is the whole launch: all shards of a query share one), and adds it once — one
+  // atomic per warp and counter instead of one per item on what is often a single address.
+  uint64_t acc_off = ~0ull;
+  unsigned long long acc = 0;
+  auto add_count = [&](uint64_t off, uint32_t v) {
+    if (off != acc_off) {
+      if (lane == 0 && acc) atomicAdd(p.out_counts + acc_off, acc);
+      acc_off = off; acc = 0;
+    }
+    acc += v;
+  };
   for (uint32_t it = blockIdx.x; it < n_slow; it += gridDim.x, j++) {
     const uint32_t ms = j % kFoldMeta;
     mbar_wait(&s_mfull[ms], (j / kFoldMeta) & 1u);
     const FoldMeta& m = s_meta[ms];
     const uint32_t n_instr = m.n_instr;
     if (m.take != 1u) {  // 0: not a flat fold, eval_staged_kernel handles it; 2: Count(Row) straight from the descriptor
-      if (tid == 0 && m.take == 2u) {
-        const uint32_t nrow = m.desc[m.ins[0].leaf].n;
-        if (p.out_counts && nrow) atomicAdd(p.out_counts + uint64_t(m.q) * p.out_qstride + uint64_t(m.s) * p.out_sstride, (unsigned long long)nrow);
-      }
+      if (tid < 32 && m.take == 2u && p.out_counts)
+        add_count(uint64_t(m.q) * p.out_qstride + uint64_t(m.s) * p.out_sstride, m.desc[m.ins[0].leaf].n);
       fold_bar();
       if (tid == 0) mbar_arrive(&s_mempty[ms]);
       continue;
@@ -943,7 +993,8 @@ __global__ void __launch_bounds__(kFoldCtaThreads, 5) eval_fold_kernel(EvalParam
       const bool nil = d.n == 0, full = d.n == kFullN && type != kBitmap;
       const bool staged = !nil && !full;
       const uint32_t slot = g % kFoldStages;
-      const uint4* st4 = reinterpret_cast<const uint4*>(s_dyn + size_t(slot + 1) * kBitmapBytes);
+      const uint4* st4 = reinterpret_cast<const uint4*>(s_dyn + size_t(slot + kFoldFixed) * kBitmapBytes);
+      const uint32_t st_a = dyn_a + (slot + kFoldFixed) * kBitmapBytes;
       if (staged) mbar_wait(&s_full[slot], (g / kFoldStages) & 1u);  // this operand's payload has landed
       int op = in.op;
       bool skip = false;
@@ -971,30 +1022,23 @@ __global__ void __launch_bounds__(kFoldCtaThreads, 5) eval_fold_kernel(EvalParam
           win4[tid] = op == I_OR_LEAF ? or128(win4[tid], g0) : and128(win4[tid], g0);
           win4[tid + kFoldThreads] = op == I_OR_LEAF ? or128(win4[tid + kFoldThreads], g1) : and128(win4[tid + kFoldThreads], g1);
         } else if (type == kArray) {
-          if (op == I_OR_LEAF) fold_array16<R_SET>(s_win, st4, len, tid);
-          else {  // AND: keep exactly the array's values whose bit is set (intersectArrayBitmap roaring.go:3404)
-            const uint16_t* vals = reinterpret_cast<const uint16_t*>(st4) + tid * 16;
-            const uint32_t first = uint32_t(tid) * 16;
-            uint32_t keep = 0;
-            for (uint32_t k = 0; k < 16 && first + k < len; k++) {
-              const uint32_t val = vals[k];
-              if ((s_win[val >> 5] >> (val & 31)) & 1u) keep |= 1u << k;
-            }
-            fold_bar();  // every probe is done before the window is rebuilt
-            win4[tid] = zero4; win4[tid + kFoldThreads] = zero4;
+          if (op == I_OR_LEAF) fold_array_set<true>(win_a, st_a, len, tid);
+          else {  // AND: the array as a bitmap in S, then word by word (intersectArrayBitmap roaring.go:3404)
+            fold_array_set<false>(S_a, st_a, len, tid);
             fold_bar();
-            for (uint32_t k = 0; k < 16; k++)
-              if ((keep >> k) & 1u) { const uint32_t val = vals[k]; atomicOr(&s_win[val >> 5], 1u << (val & 31)); }
+            const uint4 g0 = S4[tid], g1 = S4[tid + kFoldThreads];
+            S4[tid] = zero4; S4[tid + kFoldThreads] = zero4;
+            win4[tid] = and128(win4[tid], g0);
+            win4[tid + kFoldThreads] = and128(win4[tid + kFoldThreads], g1);
           }
         } else {  // run list
-          uint32_t* scratch = const_cast<uint32_t*>(reinterpret_cast<const uint32_t*>(st4));
-          if (op == I_OR_LEAF) fold_runs_scan<I_OR_LEAF>(s_win, scratch, len, s_red, tid);
-          else fold_runs_scan<I_AND_LEAF>(s_win, scratch, len, s_red, tid);
+          if (op == I_OR_LEAF) fold_runs<I_OR_LEAF>(s_win, s_S, s_E, st_a, len, s_red, tid);
+          else fold_runs<I_AND_LEAF>(s_win, s_S, s_E, st_a, len, s_red, tid);
         }
       }
       fold_bar();  // the operand is applied by every consumer
       if (staged) {
-        if (tid == 0) {  // its staging slot goes back to the producer (the run scan wrote to it: order those writes before the copy engine's)
+        if (tid == 0) {  // its staging slot goes back to the producer (the consumers' reads are ordered before the copy engine's next write)
           fence_proxy_async();
           mbar_arrive(&s_empty[slot]);
         }
@@ -1009,6 +1053,12 @@ __global__ void __launch_bounds__(kFoldCtaThreads, 5) eval_fold_kernel(EvalParam
       dout[tid] = a; dout[tid + kFoldThreads] = b;
     }
     cnt = warp_sum(cnt);
+    if (!p.dense_n) {  // count only: every warp adds its part, one barrier less per item
+      if (p.out_counts) add_count(uint64_t(m.q) * p.out_qstride + uint64_t(m.s) * p.out_sstride, cnt);
+      fold_bar();  // the window and the item's descriptors are no longer needed
+      if (tid == 0) mbar_arrive(&s_mempty[ms]);
+      continue;
+    }
     if (lane == 0) s_red[tid >> 5] = cnt;
     fold_bar();
     if (tid == 0) {
@@ -1021,6 +1071,7 @@ __global__ void __launch_bounds__(kFoldCtaThreads, 5) eval_fold_kernel(EvalParam
     }
     fold_bar();  // s_red and the window are free for the next item
   }
+  if (lane == 0 && acc) atomicAdd(p.out_counts + acc_off, acc);
 }
 
 // ---------------------------------------------------------------------------------------

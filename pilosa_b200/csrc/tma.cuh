@@ -40,4 +40,9 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src
                :: "r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// asks the copy engine to pull `bytes` (multiple of 16) at a 16 B aligned global address into L2; nothing is signalled
+__device__ __forceinline__ void l2_prefetch_bulk(const void* gmem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(gmem_src), "r"(bytes) : "memory");
+}
+
 }  // namespace pb200

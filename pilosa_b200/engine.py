@@ -95,6 +95,7 @@ def load_library() -> C.CDLL:
         "pb200_bsi_max": (i32, [vp, u32, u32, np_, u32, u64p, u32, i64p, u64p]),
         "pb200_bsi_minmax_shards": (i32, [vp, u32, u32, np_, u32, i32, u64p, u32, i64p, u64p]),
         "pb200_last_timing": (i32, [vp, C.POINTER(Timing)]),
+        "pb200_reserve": (i32, [vp, u32, u32, u32]),
         "pb200_peer_export": (i32, [vp, C.c_char_p]),
         "pb200_peer_connect": (i32, [vp, i32, i32, C.c_char_p]),
         "pb200_peer_flush": (i32, [vp]),
@@ -317,6 +318,10 @@ class Engine:
     # ---- one process per GPU: counts summed over the ranks by the batch's own kernel (NVLink peer memory, no NCCL) ----
     OPT_PEER_ALLREDUCE = 4
     PEER_HANDLE_BYTES = 64
+
+    def reserve(self, max_queries: int, max_shards: int, max_nodes_per_query: int = 3) -> None:
+        """Pre-size the scratch of the Count paths so that serving never allocates (pb200_reserve)."""
+        self._check(self.lib.pb200_reserve(self._h, max_queries, max_shards, max_nodes_per_query))
 
     def peer_export(self) -> bytes:
         buf = C.create_string_buffer(self.PEER_HANDLE_BYTES)

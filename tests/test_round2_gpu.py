@@ -213,10 +213,23 @@ def test_fold_kernel_edge_patterns(eng_orc):
         ("r", [v for k in range(300) for v in range(200 * k, 200 * k + 150)]),       # 300 medium runs
         ("b", sorted(rnd.sample(range(65536), 30000))),
         ("b", sorted(rnd.sample(range(65536), 5000))),
+        # slices of 8 values / 4 runs that share words with their neighbours in every possible way
+        ("a", list(range(0, 4096))),                               # 32 values per word: four slices per word
+        ("a", list(range(1000, 1000 + 37)) + list(range(3000, 3000 + 91)) + [65535]),
+        ("a", [v for k in range(400) for v in range(160 * k + 27, 160 * k + 37)]),   # clusters of 10 straddling word borders
+        ("r", list(range(0, 4096, 2))),                            # 2048 runs of one value: 16 starts and 16 ends per word
+        ("r", [v for k in range(1500) for v in range(40 * k + 29, 40 * k + 35)]),    # 1500 runs, every one across a word border
+        ("r", [v for k in range(1023) for v in range(64 * k + 3, 64 * k + 64)] + list(range(65480, 65536))),  # 1024 runs, each ends on a word border
+        ("R", [(10 * k, 10 * k + 9) for k in range(1000)] + [(20000, 20000), (20001, 65535)]),  # adjacent runs, not merged (a reader accepts them)
     ]
     cs = []
     for row, (kind, vals) in enumerate(pats):
-        t, n, pl = _cont(kind, vals)
+        if kind == "R":   # a raw run list, written as given
+            n = sum(b - a + 1 for a, b in vals)
+            t, pl = 3, struct.pack("<H", len(vals)) + b"".join(struct.pack("<HH", a, b) for a, b in vals)
+            pats[row] = ("r", [v for a, b in vals for v in range(a, b + 1)])
+        else:
+            t, n, pl = _cont(kind, vals)
         cs.append((row * 16 + 5, t, n, pl))
         if row % 3 == 0:   # a second column so that items differ inside one query
             t2, n2, pl2 = _cont("b", sorted(rnd.sample(range(65536), 20000)))
@@ -232,7 +245,8 @@ def test_fold_kernel_edge_patterns(eng_orc):
     for i, j in itertools.permutations(range(len(pats)), 2):
         for op, _ in ops:
             calls.append(op(R(i), R(j)))
-    for trip in ((0, 5, 11), (5, 2, 8), (8, 6, 3), (11, 5, 6), (3, 9, 10), (6, 7, 12), (9, 3, 5), (2, 10, 7), (12, 6, 9), (7, 8, 5)):
+    for trip in ((0, 5, 11), (5, 2, 8), (8, 6, 3), (11, 5, 6), (3, 9, 10), (6, 7, 12), (9, 3, 5), (2, 10, 7), (12, 6, 9), (7, 8, 5),
+                 (13, 16, 19), (16, 14, 17), (19, 15, 18), (17, 18, 13), (15, 19, 16), (14, 13, 12)):
         for op, _ in ops:
             calls.append(op(*[R(i) for i in trip]))
             calls.append(op(R(trip[0]), R(trip[1]), R(trip[2]), R(trip[1]), R(4)))
@@ -243,7 +257,7 @@ def test_fold_kernel_edge_patterns(eng_orc):
     bad = [(repr(calls[k]), got[k], exp[k]) for k in range(len(calls)) if got[k] != exp[k]]
     assert not bad, bad[:5]
     # column 5 alone, from the sets (pins the oracle on these patterns as well)
-    for (i, j), (op, f) in itertools.product(((2, 5), (5, 6), (3, 9), (7, 8)), ops):
+    for (i, j), (op, f) in itertools.product(((2, 5), (5, 6), (3, 9), (7, 8), (13, 16), (15, 17), (19, 14), (18, 16)), ops):
         cols = [v for v in g.row_columns(op(R(i), R(j)), [0]) if (v >> 16) == 5]
         assert [v & 0xffff for v in cols] == sorted(f(sets[i], sets[j])), (i, j, op)
 
@@ -442,3 +456,33 @@ def test_topn_pruned_like_fragment_top(eng_orc):
     eng.set_option(OPT_TOPN_PRUNE, 1)
     if orc_pairs is not None:
         assert got == orc_pairs
+
+
+def test_reserve_then_counts_do_not_allocate(eng_orc):
+    """pb200_reserve sizes the scratch once; the Count calls within its bounds then leave the device's free memory
+    untouched (no cudaMalloc / cudaFree on the query path) and still agree with the oracle."""
+    import torch
+
+    from pilosa_b200.abi import Difference, Union, Xor
+
+    eng, orc = eng_orc
+    g, c = Executor(eng), Executor(orc)
+    shards = list(range(24))
+    for ex in (g, c):
+        ex.create_field("m")
+        for s in shards:
+            ex.load_fragment("m", s, synth.mixed(s, 0, 4, 7))
+    rows = [Row("m", r) for r in range(4)]
+    calls = [Union(*rows), Difference(*rows), Xor(*rows), Intersect(*rows), Intersect(Union(rows[0], rows[1]), Xor(rows[2], rows[3]))]
+    eng.reserve(64, len(shards), 7)
+    g.count(rows[0], shards)                       # first call: lazily created streams / events, if any are left
+    torch.cuda.synchronize(0)
+    free0 = torch.cuda.mem_get_info(0)[0]
+    for call in calls:
+        assert g.count(call, shards) == c.count(call, shards), repr(call)
+    batch = [calls[i % len(calls)] for i in range(64)]
+    assert g.count_batch(batch, shards) == c.count_batch(batch, shards)
+    torch.cuda.synchronize(0)
+    assert torch.cuda.mem_get_info(0)[0] == free0
+    with pytest.raises(Exception):
+        eng.reserve(0, 4, 3)
