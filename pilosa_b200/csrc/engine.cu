@@ -727,7 +727,7 @@ struct Compiler {
     if (ins.size() > size_t(kMaxInstr)) { err = "expression too long (> 64 instructions)"; return false; }
     bool flat = !ins.empty() && ins[0].op == I_LOAD;
     for (size_t k = 1; k < ins.size(); k++)
-      if (ins[k].op != I_AND_LEAF && ins[k].op != I_OR_LEAF) flat = false;  // what fold_can_take refuses
+      if (!fold_op_ok(ins[k].op)) flat = false;  // what fold_can_take refuses
     (flat ? out.any_flat : out.any_bushy) = true;
     pg.instr_off = uint32_t(out.instrs.size());
     pg.n_instr = uint32_t(ins.size());

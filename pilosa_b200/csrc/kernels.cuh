@@ -137,16 +137,21 @@ __device__ __forceinline__ bool is_const_or_bitmap(const ContainerDesc& d) {
   return d.n == 0 || d.n == kFullN || desc_type(d) == kBitmap;
 }
 
-// Which items the fold kernel takes (the staged kernel takes the rest): LOAD first, then only AND / OR against leaves.
-// Folds with XOR / AND-NOT steps (Xor, Difference, Not) stay with the general staged evaluator: measured on the mixed
-// container config it is 13-19 % faster on those (the fold kernel's per-operation code paths are long; with three of
-// them live it stalls on instruction fetch), while the fold kernel wins on Intersect (-38 %) and ties on Union.
+// Which items the fold kernel takes (the staged kernel takes the rest): LOAD first, then AND / OR / XOR / AND-NOT
+// steps against leaves — Intersect, Union, Xor, Difference of rows. (Round-2 history: with atomics on the slice edges
+// and a prefix-XOR run scan the XOR / AND-NOT folds were 13-19 % faster on the staged evaluator and stayed there; with
+// the atomics-free slices and the E - S run fill they are 16 % faster here, PB200_FOLD_XOR=0 builds the old routing.)
+// the steps a flat fold may consist of after its LOAD (the host's classification, engine.cu finish(), uses the same test)
+#ifndef PB200_FOLD_XOR
+#define PB200_FOLD_XOR 1
+#endif
+__host__ __device__ inline bool fold_op_ok(uint8_t op) {
+  return op == I_AND_LEAF || op == I_OR_LEAF || (PB200_FOLD_XOR && (op == I_XOR_LEAF || op == I_ANDNOT_LEAF));
+}
 __device__ __forceinline__ bool fold_can_take(const Prog& pg, const Instr* ins, const ContainerDesc* descs) {
   if (pg.n_instr == 0 || ins[0].op != I_LOAD) return false;
-  for (uint32_t i = 1; i < pg.n_instr; i++) {
-    const uint8_t op = ins[i].op;
-    if (op != I_AND_LEAF && op != I_OR_LEAF) return false;
-  }
+  for (uint32_t i = 1; i < pg.n_instr; i++)
+    if (!fold_op_ok(ins[i].op)) return false;
   (void)descs;
   return true;
 }
@@ -174,6 +179,7 @@ __device__ __forceinline__ uint32_t popc128(const uint4& v) {
 }
 __device__ __forceinline__ uint4 and128(const uint4& a, const uint4& b) { return make_uint4(a.x & b.x, a.y & b.y, a.z & b.z, a.w & b.w); }
 __device__ __forceinline__ uint4 or128(const uint4& a, const uint4& b) { return make_uint4(a.x | b.x, a.y | b.y, a.z | b.z, a.w | b.w); }
+__device__ __forceinline__ uint4 not128(const uint4& a) { return make_uint4(~a.x, ~a.y, ~a.z, ~a.w); }
 __device__ __forceinline__ uint4 xor128(const uint4& a, const uint4& b) { return make_uint4(a.x ^ b.x, a.y ^ b.y, a.z ^ b.z, a.w ^ b.w); }
 __device__ __forceinline__ uint4 andnot128(const uint4& a, const uint4& b) { return make_uint4(a.x & ~b.x, a.y & ~b.y, a.z & ~b.z, a.w & ~b.w); }
 
@@ -695,8 +701,11 @@ __global__ void __launch_bounds__(kStagedThreads) eval_staged_kernel(EvalParams 
 // shared-memory window; each operand is applied to it IN ITS OWN ENCODING, so an operand costs its payload, not
 // 65536 bits: the type pairs of roaring.go:3078-4957 become
 //                bitmap (1024 words)     array (n x u16)                       run list
-//   load / OR    w (|)= g                set the value's bit                   OR  the run bitmap (union*     :3470-3839)
-//   AND          w &= g                  AND the array's bitmap                AND the run bitmap (intersect* :3254-3418)
+//   load         window = g              the array's bits, into a zero window  window = run bitmap
+//   OR           w |= g                  set the values' bits                  w |= run bitmap    (union*        :3470-3839)
+//   XOR          w ^= g                  flip them                             w ^= run bitmap    (xor*          :4266-4957)
+//   AND-NOT      w &= ~g                 clear them                            w &= ~run bitmap   (difference*   :3920-4205)
+//   AND          w &= g                  AND with the array's bitmap (in S)    w &= run bitmap    (intersect*    :3254-3418)
 // Payloads are contiguous 16 B aligned streams, so the bulk copy engine moves each one global -> shared with one
 // cp.async.bulk issued by one thread (local HBM only, no multicast), up to kFoldStages operands ahead of the one being
 // applied; completion is an mbarrier transaction count.
@@ -739,16 +748,21 @@ struct PosArray { uint32_t base; __device__ __forceinline__ uint32_t operator()(
 struct PosRunStart { uint32_t base; __device__ __forceinline__ uint32_t operator()(uint32_t i) const { return lds_u16(base + 4u * i); } };
 struct PosRunEnd { uint32_t base; __device__ __forceinline__ uint32_t operator()(uint32_t i) const { return lds_u16(base + 4u * i + 2u) + 1u; } };  // 65536 behind a run that ends the container
 
-template <bool RMW>
+enum FoldEdit : int { E_STORE = 0, E_SET = 1, E_FLIP = 2, E_CLEAR = 3 };  // E_STORE: the target is zero, nothing to read
+template <int MODE>
 __device__ __forceinline__ void fold_put(uint32_t bm, uint32_t w, uint32_t bits) {
   const uint32_t a = bm + 4u * w;
-  sts_u32(a, RMW ? (lds_u32(a) | bits) : bits);
+  if (MODE == E_STORE) sts_u32(a, bits);
+  else {
+    const uint32_t old = lds_u32(a);
+    sts_u32(a, MODE == E_SET ? (old | bits) : MODE == E_FLIP ? (old ^ bits) : (old & ~bits));
+  }
 }
 
 // One slice: elements [first, first + cnt) are in v[0 .. cnt), cnt <= N; `pos` reads any element of the sequence.
-// RMW: the bitmap (shared address bm) holds other bits already (the window); otherwise it is zero (S / E).
+// MODE: how a word of the bitmap at shared address bm is edited (E_STORE for the zeroed S / E, else the window).
 // GUARD: the last element may be position 65536, which has no word.
-template <int N, bool FULL, bool RMW, bool GUARD, class POS>
+template <int N, bool FULL, int MODE, bool GUARD, class POS>
 __device__ __forceinline__ void fold_set_slice(uint32_t bm, const uint32_t (&v)[N], uint32_t cnt, uint32_t first, uint32_t len, const POS& pos) {
   // the word in front of the slice belongs to an earlier slice: bits gathered for it are dropped. Words ascend, so
   // "cur_w is mine" is "cur_w != foreign" at every flush — no flag is carried through the loop.
@@ -760,7 +774,7 @@ __device__ __forceinline__ void fold_set_slice(uint32_t bm, const uint32_t (&v)[
       const uint32_t w = v[k] >> 5;
       const uint32_t bit = __funnelshift_l(0u, 1u, v[k]);  // 1 << (v & 31)
       const bool chg = w != cur_w;
-      if (chg && cur_w != foreign) fold_put<RMW>(bm, cur_w, cur_b);
+      if (chg && cur_w != foreign) fold_put<MODE>(bm, cur_w, cur_b);
       cur_b = chg ? bit : (cur_b | bit);
       cur_w = w;
     }
@@ -771,11 +785,11 @@ __device__ __forceinline__ void fold_set_slice(uint32_t bm, const uint32_t (&v)[
     if ((x >> 5) != cur_w) break;
     cur_b |= __funnelshift_l(0u, 1u, x);
   }
-  if (!GUARD || cur_w < kWords32) fold_put<RMW>(bm, cur_w, cur_b);
+  if (!GUARD || cur_w < kWords32) fold_put<MODE>(bm, cur_w, cur_b);
 }
 
-// The bits of a sorted array container into `bm`: the window (RMW, union) or the zeroed scratch S (intersection).
-template <bool RMW>
+// The bits of a sorted array container set / flipped / cleared in the window, or stored into the zeroed scratch S.
+template <int MODE>
 __device__ __noinline__ void fold_array_set(uint32_t bm, uint32_t st, uint32_t len, int tid) {
   const PosArray pos{st};
   for (uint32_t first = uint32_t(tid) * 8u; first < len; first += kFoldThreads * 8u) {
@@ -783,8 +797,8 @@ __device__ __noinline__ void fold_array_set(uint32_t bm, uint32_t st, uint32_t l
     asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w) : "r"(st + 2u * first) : "memory");
     const uint32_t v[8] = {q.x & 0xffffu, q.x >> 16, q.y & 0xffffu, q.y >> 16, q.z & 0xffffu, q.z >> 16, q.w & 0xffffu, q.w >> 16};
     const uint32_t cnt = len - first;
-    if (cnt >= 8u) fold_set_slice<8, true, RMW, false>(bm, v, 8u, first, len, pos);
-    else fold_set_slice<8, false, RMW, false>(bm, v, cnt, first, len, pos);
+    if (cnt >= 8u) fold_set_slice<8, true, MODE, false>(bm, v, 8u, first, len, pos);
+    else fold_set_slice<8, false, MODE, false>(bm, v, cnt, first, len, pos);
   }
 }
 
@@ -807,9 +821,8 @@ __device__ __forceinline__ void fold_sub8(uint32_t (&r)[8], const uint32_t (&e)[
         "r"(s[0]), "r"(s[1]), "r"(s[2]), "r"(s[3]), "r"(s[4]), "r"(s[5]), "r"(s[6]), "r"(s[7]), "r"(borrow));
 }
 
-// A run list applied to the window (OP: I_OR_LEAF / I_AND_LEAF). S, E: the zeroed scratch bitmaps; left zeroed.
-template <int OP>
-__device__ __noinline__ void fold_runs(uint32_t* win32, uint32_t* S, uint32_t* E, uint32_t st, uint32_t len, uint32_t* s_par, int tid) {
+// A run list applied to the window (OP: I_LOAD / I_OR_LEAF / I_AND_LEAF). S, E: the zeroed scratch bitmaps; left zeroed.
+__device__ __noinline__ void fold_runs(const int OP, uint32_t* win32, uint32_t* S, uint32_t* E, uint32_t st, uint32_t len, uint32_t* s_par, int tid) {
   const int lane = tid & 31, warp = tid >> 5;
   const PosRunStart ps{st};
   const PosRunEnd pe{st};
@@ -821,11 +834,11 @@ __device__ __noinline__ void fold_runs(uint32_t* win32, uint32_t* S, uint32_t* E
     const uint32_t ve[4] = {(q.x >> 16) + 1u, (q.y >> 16) + 1u, (q.z >> 16) + 1u, (q.w >> 16) + 1u};
     const uint32_t cnt = len - first;
     if (cnt >= 4u) {
-      fold_set_slice<4, true, false, false>(S_a, vs, 4u, first, len, ps);
-      fold_set_slice<4, true, false, true>(E_a, ve, 4u, first, len, pe);
+      fold_set_slice<4, true, E_STORE, false>(S_a, vs, 4u, first, len, ps);
+      fold_set_slice<4, true, E_STORE, true>(E_a, ve, 4u, first, len, pe);
     } else {
-      fold_set_slice<4, false, false, false>(S_a, vs, cnt, first, len, ps);
-      fold_set_slice<4, false, false, true>(E_a, ve, cnt, first, len, pe);
+      fold_set_slice<4, false, E_STORE, false>(S_a, vs, cnt, first, len, ps);
+      fold_set_slice<4, false, E_STORE, true>(E_a, ve, cnt, first, len, pe);
     }
   }
   fold_bar();
@@ -849,14 +862,29 @@ __device__ __noinline__ void fold_runs(uint32_t* win32, uint32_t* S, uint32_t* E
   uint32_t r[8];
   fold_sub8(r, e, s, borrow);
   uint4* W4 = reinterpret_cast<uint4*>(win32);
-  const uint4 a0 = W4[2 * tid], a1 = W4[2 * tid + 1];
-  if (OP == I_OR_LEAF) {
-    W4[2 * tid] = make_uint4(a0.x | r[0], a0.y | r[1], a0.z | r[2], a0.w | r[3]);
-    W4[2 * tid + 1] = make_uint4(a1.x | r[4], a1.y | r[5], a1.z | r[6], a1.w | r[7]);
-  } else {
-    W4[2 * tid] = make_uint4(a0.x & r[0], a0.y & r[1], a0.z & r[2], a0.w & r[3]);
-    W4[2 * tid + 1] = make_uint4(a1.x & r[4], a1.y & r[5], a1.z & r[6], a1.w & r[7]);
+  if (OP == I_LOAD) {  // the run bitmap is the window: nothing to read, nothing to clear beforehand
+    W4[2 * tid] = make_uint4(r[0], r[1], r[2], r[3]);
+    W4[2 * tid + 1] = make_uint4(r[4], r[5], r[6], r[7]);
+    return;
   }
+  const uint4 a0 = W4[2 * tid], a1 = W4[2 * tid + 1];
+  const uint32_t a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+  uint32_t o[8];
+  if (OP == I_OR_LEAF) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) o[k] = a[k] | r[k];
+  } else if (OP == I_AND_LEAF) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) o[k] = a[k] & r[k];
+  } else if (OP == I_XOR_LEAF) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) o[k] = a[k] ^ r[k];
+  } else {
+#pragma unroll
+    for (int k = 0; k < 8; k++) o[k] = a[k] & ~r[k];
+  }
+  W4[2 * tid] = make_uint4(o[0], o[1], o[2], o[3]);
+  W4[2 * tid + 1] = make_uint4(o[4], o[5], o[6], o[7]);
 }
 
 // Payload bytes the copy engine moves for an operand (a multiple of 16; 0 = constant operand, nothing to move).
@@ -951,14 +979,13 @@ __global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_ke
   }
 
   // ---------------- consumer warps ----------------
-  uint32_t* s_win = reinterpret_cast<uint32_t*>(s_dyn);
-  uint32_t* s_S = reinterpret_cast<uint32_t*>(s_dyn + kBitmapBytes);
+  // regions 0 and 1 are the window and S; they trade places when an array is LOADed (it is set into the zeroed S with
+  // plain stores, the old window is cleared to become the next S — no clear-then-barrier-then-edit of the window)
+  uint32_t wsel = 0;
   uint32_t* s_E = reinterpret_cast<uint32_t*>(s_dyn + 2 * kBitmapBytes);
-  uint4* win4 = reinterpret_cast<uint4*>(s_dyn);
-  uint4* S4 = reinterpret_cast<uint4*>(s_S);
-  const uint32_t dyn_a = smem_u32(s_dyn), win_a = dyn_a, S_a = dyn_a + kBitmapBytes;
+  const uint32_t dyn_a = smem_u32(s_dyn);
   const uint4 zero4 = make_uint4(0, 0, 0, 0), ones4 = make_uint4(~0u, ~0u, ~0u, ~0u);
-  for (int i = tid; i < 2 * kBitmapBytes / 16; i += kFoldThreads) S4[i] = zero4;  // S and E start out zero (and stay so between uses)
+  for (int i = tid; i < 3 * kBitmapBytes / 16; i += kFoldThreads) reinterpret_cast<uint4*>(s_dyn)[i] = zero4;  // S and E start out zero (and stay so between uses)
   fold_bar();
   uint32_t g = 0, j = 0;
   // Counts: every warp keeps a running sum of its part of the windows for as long as the items add into the same
@@ -996,45 +1023,54 @@ __global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_ke
       const uint4* st4 = reinterpret_cast<const uint4*>(s_dyn + size_t(slot + kFoldFixed) * kBitmapBytes);
       const uint32_t st_a = dyn_a + (slot + kFoldFixed) * kBitmapBytes;
       if (staged) mbar_wait(&s_full[slot], (g / kFoldStages) & 1u);  // this operand's payload has landed
-      int op = in.op;
-      bool skip = false;
-      if (op == I_LOAD) {  // load = clear, then OR (a bitmap is copied straight in)
-        if (staged && type == kBitmap) {
-          win4[tid] = st4[tid];
-          win4[tid + kFoldThreads] = st4[tid + kFoldThreads];
-          skip = true;
-        } else {
+      uint32_t* s_win = reinterpret_cast<uint32_t*>(s_dyn + wsel * kBitmapBytes);
+      uint32_t* s_S = reinterpret_cast<uint32_t*>(s_dyn + (wsel ^ 1u) * kBitmapBytes);
+      uint4* win4 = reinterpret_cast<uint4*>(s_win);
+      uint4* S4 = reinterpret_cast<uint4*>(s_S);
+      const uint32_t win_a = dyn_a + wsel * kBitmapBytes, S_a = dyn_a + (wsel ^ 1u) * kBitmapBytes;
+      const int op = in.op;
+      // (fold_can_take admits LOAD first, then OR and AND steps only; the other operations' code is not instantiated here)
+      if (op == I_LOAD) {
+        if (!staged) {
           win4[tid] = full ? ones4 : zero4;
           win4[tid + kFoldThreads] = full ? ones4 : zero4;
-          fold_bar();
-          skip = !staged;
-          op = I_OR_LEAF;
-        }
-      }
-      if (!skip) {
-        // (fold_can_take admits OR and AND steps only; the other operations' code is not instantiated here)
-        if (nil) {
-          if (op == I_AND_LEAF) { win4[tid] = zero4; win4[tid + kFoldThreads] = zero4; }
-        } else if (full) {
-          if (op == I_OR_LEAF) { win4[tid] = ones4; win4[tid + kFoldThreads] = ones4; }
         } else if (type == kBitmap) {
-          const uint4 g0 = st4[tid], g1 = st4[tid + kFoldThreads];
-          win4[tid] = op == I_OR_LEAF ? or128(win4[tid], g0) : and128(win4[tid], g0);
-          win4[tid + kFoldThreads] = op == I_OR_LEAF ? or128(win4[tid + kFoldThreads], g1) : and128(win4[tid + kFoldThreads], g1);
+          win4[tid] = st4[tid];
+          win4[tid + kFoldThreads] = st4[tid + kFoldThreads];
         } else if (type == kArray) {
-          if (op == I_OR_LEAF) fold_array_set<true>(win_a, st_a, len, tid);
-          else {  // AND: the array as a bitmap in S, then word by word (intersectArrayBitmap roaring.go:3404)
-            fold_array_set<false>(S_a, st_a, len, tid);
-            fold_bar();
-            const uint4 g0 = S4[tid], g1 = S4[tid + kFoldThreads];
-            S4[tid] = zero4; S4[tid + kFoldThreads] = zero4;
-            win4[tid] = and128(win4[tid], g0);
-            win4[tid + kFoldThreads] = and128(win4[tid + kFoldThreads], g1);
-          }
-        } else {  // run list
-          if (op == I_OR_LEAF) fold_runs<I_OR_LEAF>(s_win, s_S, s_E, st_a, len, s_red, tid);
-          else fold_runs<I_AND_LEAF>(s_win, s_S, s_E, st_a, len, s_red, tid);
+          fold_array_set<E_STORE>(S_a, st_a, len, tid);
+          win4[tid] = zero4; win4[tid + kFoldThreads] = zero4;
+          wsel ^= 1u;
+        } else {
+          fold_runs(I_LOAD, s_win, s_S, s_E, st_a, len, s_red, tid);
         }
+      } else if (nil) {
+        if (op == I_AND_LEAF) { win4[tid] = zero4; win4[tid + kFoldThreads] = zero4; }
+      } else if (full) {
+        if (op == I_OR_LEAF) { win4[tid] = ones4; win4[tid + kFoldThreads] = ones4; }
+        else if (op == I_ANDNOT_LEAF) { win4[tid] = zero4; win4[tid + kFoldThreads] = zero4; }
+        else if (op == I_XOR_LEAF) { win4[tid] = not128(win4[tid]); win4[tid + kFoldThreads] = not128(win4[tid + kFoldThreads]); }
+      } else if (type == kBitmap) {
+        const uint4 g0 = st4[tid], g1 = st4[tid + kFoldThreads];
+        const uint4 w0 = win4[tid], w1 = win4[tid + kFoldThreads];
+        win4[tid] = op == I_OR_LEAF ? or128(w0, g0) : op == I_AND_LEAF ? and128(w0, g0) : op == I_XOR_LEAF ? xor128(w0, g0) : andnot128(w0, g0);
+        win4[tid + kFoldThreads] = op == I_OR_LEAF ? or128(w1, g1) : op == I_AND_LEAF ? and128(w1, g1) : op == I_XOR_LEAF ? xor128(w1, g1) : andnot128(w1, g1);
+      } else if (type == kArray) {
+        if (op == I_OR_LEAF) fold_array_set<E_SET>(win_a, st_a, len, tid);
+#if PB200_FOLD_XOR
+        else if (op == I_XOR_LEAF) fold_array_set<E_FLIP>(win_a, st_a, len, tid);
+        else if (op == I_ANDNOT_LEAF) fold_array_set<E_CLEAR>(win_a, st_a, len, tid);
+#endif
+        else {  // AND: the array as a bitmap in S, then word by word (intersectArrayBitmap roaring.go:3404)
+          fold_array_set<E_STORE>(S_a, st_a, len, tid);
+          fold_bar();
+          const uint4 g0 = S4[tid], g1 = S4[tid + kFoldThreads];
+          S4[tid] = zero4; S4[tid + kFoldThreads] = zero4;
+          win4[tid] = and128(win4[tid], g0);
+          win4[tid + kFoldThreads] = and128(win4[tid + kFoldThreads], g1);
+        }
+      } else {  // run list
+        fold_runs(op, s_win, s_S, s_E, st_a, len, s_red, tid);
       }
       fold_bar();  // the operand is applied by every consumer
       if (staged) {
@@ -1046,6 +1082,7 @@ __global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_ke
       }
     }
 
+    const uint4* win4 = reinterpret_cast<const uint4*>(s_dyn + wsel * kBitmapBytes);
     const uint4 a = win4[tid], b = win4[tid + kFoldThreads];
     uint32_t cnt = popc128(a) + popc128(b);
     if (p.dense_out) {
