@@ -223,7 +223,7 @@ extern "C" int pb200_shutdown(pb200_ctx* ctx) {
       if (fam.d_frags) cudaFree(fam.d_frags);
     }
     if (ctx->d_families) cudaFree(ctx->d_families);
-    for (DevBuf* b : {&ctx->d_rows, &ctx->d_rows_off, &ctx->d_rows_meta, &ctx->d_rows_item_off, &ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi, &ctx->d_ing, &ctx->d_ing_res, &ctx->d_topn_compact})
+    for (DevBuf* b : {&ctx->d_rows, &ctx->d_rows_off, &ctx->d_rows_meta, &ctx->d_rows_item_off, &ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_rest, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi, &ctx->d_ing, &ctx->d_ing_res, &ctx->d_topn_compact})
       if (b->p) cudaFree(b->p);
     for (auto& r : ctx->arena.retired) cudaFree(r.first);
     if (ctx->arena.base) cudaFree(ctx->arena.base);
@@ -935,12 +935,13 @@ uint32_t resident_ctas(pb200_ctx* ctx, int slot, K kernel, int block, size_t dyn
   }
   return uint32_t(ctx->sm_count) * uint32_t(ctx->occ[slot]);
 }
-enum { OCC_FAST = 0, OCC_STAGED, OCC_SUM, OCC_MM, OCC_TOPN, OCC_FOLD };
+enum { OCC_FAST = 0, OCC_STAGED, OCC_SUM, OCC_MM, OCC_TOPN, OCC_FOLD, OCC_TINY };
 
 // Launches the fast + staged kernels for `n_queries` programs starting at `progs`.
 int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards, bool staging,
                 unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, uint8_t* dense_out, uint32_t* dense_n,
-                uint32_t max_leaves = kMaxLeaves, bool bushy = true, bool fold_all = false, const PushDesc* push = nullptr, bool flat = true) {
+                uint32_t max_leaves = kMaxLeaves, bool bushy = true, bool fold_all = false, const PushDesc* push = nullptr, bool flat = true,
+                bool tiny = false) {
   const uint64_t n_items = uint64_t(n_queries) * n_shards * kRowContainers;
   if (n_items == 0) return PB200_OK;
   if (n_items >= (1ull << 32)) return fail(ctx, PB200_ERR_RANGE, "batch too large: queries x shards x 16 must be < 2^32");
@@ -972,8 +973,20 @@ int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t 
   }
   const bool push_fused = push && !staging;  // eval_fast_kernel is the batch's only kernel: the peer reduction rides in its tail
   if (push_fused) p.push = *push;
+  // Very sparse rows (containers of a few values): a first pass with one lane per item counts the pairs of tiny arrays
+  // in registers and leaves eval_fast_kernel a list of the rest.
+  // (only when the items outnumber the warps the device holds at once: below that a warp per item is one wave anyway)
+  tiny = tiny && staging && !fold_all && !dense_out && out_counts && n_items > uint64_t(ctx->sm_count) * 64;
+  if (tiny) TRY(ensure_dev(ctx, ctx->d_rest, size_t(n_items) * 4));
   if (!fold_all) {
-    CUDA_TRY(ctx, cudaMemsetAsync(p.slow_count, 0, 4, ctx->stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(p.slow_count, 0, 8, ctx->stream));  // slow_count and, behind it, the tiny pass's item count
+    if (tiny) {
+      p.item_list = static_cast<uint32_t*>(ctx->d_rest.p);
+      p.item_count = p.slow_count + 1;
+      const uint32_t tgrid = uint32_t(std::min<uint64_t>((n_items + 255) / 256, resident_ctas(ctx, OCC_TINY, eval_tiny_kernel, 256, 0)));
+      eval_tiny_kernel<<<tgrid, 256, 0, ctx->stream>>>(p);
+      ctx->timing.launches++;
+    }
     const uint64_t want = (n_items + kFastWarps - 1) / kFastWarps;
     uint32_t resident = resident_ctas(ctx, OCC_FAST, eval_fast_kernel, kFastWarps * 32, 0);
     if (push && resident > 1) resident -= 1;  // one CTA slot stays free: the one-CTA collect kernel of an older batch can run beside this grid
@@ -1039,6 +1052,11 @@ int finish_call(pb200_ctx* ctx) {
 // mean payload of the containers the batch's Row leaves come from; at a kilobyte and more the fold evaluator runs alone
 bool fold_all_of(const Compiled& cp) {  // (a batch with programs the fold kernel refuses keeps the first pass: all-bitmap items are cheapest there)
   return cp.may_need_staging && !cp.any_bushy && cp.leaf_containers && cp.leaf_payload / cp.leaf_containers >= 1024;
+}
+
+// containers of at most a few dozen bytes on average: the lane-per-item first pass pays (eval_tiny_kernel)
+bool tiny_of(const Compiled& cp) {
+  return cp.may_need_staging && cp.leaf_containers && cp.leaf_payload / cp.leaf_containers <= 64;
 }
 
 uint32_t max_leaves_of(const Compiled& cp) {
@@ -1145,7 +1163,7 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
     if (rc == PB200_OK && reduce) rc = peer_begin_epoch(ctx, d_out, n_queries, pd, &sl.peer_slot);
     if (rc == PB200_OK)
       rc = launch_eval(ctx, bd, bd.progs, n_queries, n_shards, cp.may_need_staging, d_out, per_shard ? n_shards : 1, per_shard ? 1 : 0,
-                       nullptr, nullptr, max_leaves_of(cp), cp.any_bushy, fold_all_of(cp), reduce && !has_shift(cp) ? &pd : nullptr, cp.any_flat);
+                       nullptr, nullptr, max_leaves_of(cp), cp.any_bushy, fold_all_of(cp), reduce && !has_shift(cp) ? &pd : nullptr, cp.any_flat, tiny_of(cp));
     if (rc == PB200_OK && reduce && has_shift(cp)) {  // the overflow pass below adds to the counts: push after it
       rc = launch_overflow(ctx, bd, bd.progs, n_queries, n_shards, d_out, 1, 0, nullptr);
       if (rc == PB200_OK) { peer_push_kernel<<<1, 256, 0, ctx->stream>>>(pd); ctx->timing.launches++; }
@@ -1417,7 +1435,7 @@ extern "C" int pb200_batch_launch(pb200_ctx* ctx, pb200_batch* b) {
   ctx->timing.launches = 0;
   CUDA_TRY(ctx, cudaMemsetAsync(b->d_counts.p, 0, size_t(b->n_queries) * 8, ctx->stream));
   return launch_eval(ctx, b->bd, b->bd.progs, b->n_queries, b->n_shards, b->cp.may_need_staging,
-                     static_cast<unsigned long long*>(b->d_counts.p), 1, 0, nullptr, nullptr, max_leaves_of(b->cp), b->cp.any_bushy, fold_all_of(b->cp), nullptr, b->cp.any_flat);
+                     static_cast<unsigned long long*>(b->d_counts.p), 1, 0, nullptr, nullptr, max_leaves_of(b->cp), b->cp.any_bushy, fold_all_of(b->cp), nullptr, b->cp.any_flat, tiny_of(b->cp));
 }
 
 extern "C" int pb200_batch_device_counts(pb200_ctx* ctx, pb200_batch* b, void** device_counts) {

@@ -160,7 +160,7 @@ struct pb200_ctx {
   // fragment is freed, so that the peers' tables follow and no peer still reads the old copy
   std::function<int(uint32_t family, uint64_t shard, const pb200::FragDev& dev, bool all_bitmap, bool present)> publish;
   uint64_t generation = 0;  // bumped by every load / write / drop / table growth: prepared batches re-validate against it
-  pb200::DevBuf d_slow_descs, d_ovf;
+  pb200::DevBuf d_slow_descs, d_ovf, d_rest;  // d_rest: items eval_tiny_kernel leaves to eval_fast_kernel
   pb200::DevBuf d_rows, d_rows_off, d_rows_meta, d_rows_item_off;  // K11: serialised result rows (kernels_rows.cuh)
   bool dense_has_ovf = false;                      // the rows in d_dense carry Shift overflow words
   unsigned long long* dense_ovf_dev = nullptr;

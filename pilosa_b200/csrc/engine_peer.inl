@@ -163,7 +163,7 @@ extern "C" int pb200_batch_launch_allreduce(pb200_ctx* ctx, pb200_batch* b) {
   TRY(peer_begin_epoch(ctx, static_cast<unsigned long long*>(b->d_counts.p), b->n_queries, pd, &slot));
   CUDA_TRY(ctx, cudaMemsetAsync(b->d_counts.p, 0, size_t(b->n_queries) * 8, ctx->stream));
   TRY(launch_eval(ctx, b->bd, b->bd.progs, b->n_queries, b->n_shards, b->cp.may_need_staging, static_cast<unsigned long long*>(b->d_counts.p), 1, 0,
-                  nullptr, nullptr, max_leaves_of(b->cp), b->cp.any_bushy, fold_all_of(b->cp), &pd, b->cp.any_flat));
+                  nullptr, nullptr, max_leaves_of(b->cp), b->cp.any_bushy, fold_all_of(b->cp), &pd, b->cp.any_flat, tiny_of(b->cp)));
   return peer_end_epoch(ctx, slot);
 }
 

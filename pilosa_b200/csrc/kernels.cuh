@@ -94,6 +94,8 @@ struct EvalParams {
   uint32_t slow_desc_stride;
   unsigned long long* algo_bytes;  // accumulated algorithmic bytes (payload + 16 B / container)
   uint32_t fold_all;               // eval_fold_kernel walks EVERY item itself (no eval_fast_kernel pass, no deferred list)
+  uint32_t* item_list;             // eval_tiny_kernel ran first: the items it left for eval_fast_kernel ...
+  uint32_t* item_count;            // ... and how many (null: eval_fast_kernel walks every item)
   PushDesc push;                   // eval_fast_kernel only: peer reduction fused into the kernel's tail (n_dst == 0: none)
 };
 
@@ -198,6 +200,29 @@ __device__ __forceinline__ uint4 apply_op(uint8_t op, const uint4& acc, const ui
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
   return __reduce_add_sync(0xffffffffu, v);  // one REDUX.SUM instead of a five-step shuffle tree
 }
+__device__ __forceinline__ unsigned long long warp_sum64(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// Sum of v over the lanes of `grp`, the caller's own group from __match_any_sync (all 32 lanes call). The whole warp
+// and the two half warps — what a run of consecutive items gives — take shuffle trees; anything else a plain walk.
+__device__ __forceinline__ unsigned long long warp_group_sum(uint32_t grp, unsigned long long v) {
+  const bool whole = __all_sync(0xffffffffu, grp == 0xffffffffu);
+  if (whole) return warp_sum64(v);
+  const bool halves = __all_sync(0xffffffffu, grp == 0x0000ffffu || grp == 0xffff0000u);
+  if (halves) {
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+  }
+  unsigned long long tot = 0;
+  for (int src = 0; src < 32; src++) {
+    const unsigned long long x = __shfl_sync(0xffffffffu, v, src);
+    if ((grp >> src) & 1u) tot += x;
+  }
+  return tot;
+}
 
 // ---------------------------------------------------------------------------------------
 // K2-K5 (count form), warp-level: |a AND b| when the smaller operand is a short array or a
@@ -299,7 +324,9 @@ __global__ void __launch_bounds__(kFastWarps * 32) eval_fast_kernel(EvalParams p
   const uint64_t warp_stride = uint64_t(gridDim.x) * kFastWarps;
   unsigned long long bytes_acc = 0;
 
-  for (uint64_t item = uint64_t(blockIdx.x) * kFastWarps + warp; item < n_items; item += warp_stride) {
+  const uint64_t n_walk = p.item_list ? uint64_t(*p.item_count) : n_items;
+  for (uint64_t k_item = uint64_t(blockIdx.x) * kFastWarps + warp; k_item < n_walk; k_item += warp_stride) {
+    const uint64_t item = p.item_list ? uint64_t(p.item_list[k_item]) : k_item;
     const uint32_t c = uint32_t(item & 15);
     const uint64_t qs = item >> 4;
     const uint32_t s = uint32_t(qs % p.n_shards);
@@ -468,6 +495,116 @@ __global__ void __launch_bounds__(kFastWarps * 32) eval_fast_kernel(EvalParams p
       peer_push(p.push, threadIdx.x, blockDim.x);
     }
   }
+}
+
+// ---------------------------------------------------------------------------------------
+// K2 (count form) for very sparse rows: one LANE per item. A field with many rows and few bits per row (BASELINE
+// config C5: p = 1e-4, 6.5 values per container) has items of two 13-byte arrays; a warp per item spends its time on
+// the three dependent loads of leaf resolution with 31 lanes idle. Here every lane resolves its own item — lanes
+// 0-15 / 16-31 are the 16 container columns of two consecutive shards, so the descriptor reads coalesce — and, when
+// both operands are arrays of at most 16 values (or empty / full), counts the pair in registers: the values of both
+// sides come in with at most two 16-byte loads each and meet in a 16 x 16 compare (intersectionCountArrayArray,
+// roaring.go:3115, without the merge loop's dependent loads); Union / Xor / Difference counts follow from the
+// cardinalities. Everything else — longer arrays, runs, bitmaps, programs of more than two steps — is appended to a
+// list that eval_fast_kernel then walks instead of the full item space. Counts are kept per lane for as long as the
+// lane's items add into the same output counter and are added once per group of lanes that share it.
+// Launched only when the leaf families' containers average <= 64 B (host: tiny_of).
+// ---------------------------------------------------------------------------------------
+constexpr uint32_t kTinyMax = 16;
+
+__device__ __forceinline__ void tiny_values(const ContainerDesc& d, uint32_t sentinel, uint32_t (&v)[kTinyMax]) {
+  const uint32_t len = d.n == 0 ? 0u : desc_len(d);
+  uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
+  if (len) q0 = ldg128(reinterpret_cast<const void*>(d.addr));
+  if (len > 8) q1 = ldg128(reinterpret_cast<const void*>(d.addr + 16));
+  const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+  for (int k = 0; k < int(kTinyMax); k++) {
+    const uint32_t x = (k & 1) ? (w[k >> 1] >> 16) : (w[k >> 1] & 0xffffu);
+    v[k] = uint32_t(k) < len ? x : sentinel + uint32_t(k);  // sentinels are above 16 bits and differ per side: never equal
+  }
+}
+
+__global__ void __launch_bounds__(256) eval_tiny_kernel(EvalParams p) {
+  const int lane = threadIdx.x & 31;
+  const uint64_t n_items = uint64_t(p.n_queries) * p.n_shards * kRowContainers;
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  unsigned long long bytes_acc = 0, acc = 0;
+  uint64_t acc_off = ~0ull;
+  for (uint64_t base = uint64_t(blockIdx.x) * blockDim.x + (threadIdx.x & ~31u); base < n_items; base += stride) {  // warp-uniform trips
+    const uint64_t item = base + lane;
+    const bool valid = item < n_items;
+    bool defer = false;
+    uint32_t r = 0;
+    uint64_t off = acc_off;
+    if (valid) {
+      const uint32_t c = uint32_t(item & 15);
+      const uint64_t qs = item >> 4;
+      const uint32_t s = uint32_t(qs % p.n_shards), q = uint32_t(qs / p.n_shards);
+      const Prog pg = p.progs[q];
+      const Instr* ins = p.instrs + pg.instr_off;
+      off = uint64_t(q) * p.out_qstride + uint64_t(s) * p.out_sstride;
+      if (pg.n_instr == 1 && p.leaves[pg.leaf_off + ins[0].leaf].kind != L_TEMP) {  // Count(Row): roaring.go:405
+        const ContainerDesc d = resolve_leaf(p, p.leaves[pg.leaf_off + ins[0].leaf], s, c);
+        r = d.n;
+        bytes_acc += desc_algo_bytes(d);
+      } else if (pg.n_instr == 2 && ins[0].op == I_LOAD && ins[1].op >= I_AND_LEAF && ins[1].op <= I_ANDNOT_LEAF &&
+                 p.leaves[pg.leaf_off + ins[0].leaf].kind != L_TEMP && p.leaves[pg.leaf_off + ins[1].leaf].kind != L_TEMP) {
+        const ContainerDesc a = resolve_leaf(p, p.leaves[pg.leaf_off + ins[0].leaf], s, c);
+        const ContainerDesc b = resolve_leaf(p, p.leaves[pg.leaf_off + ins[1].leaf], s, c);
+        const bool trivial = a.n == 0 || b.n == 0 || a.n == kFullN || b.n == kFullN;  // the cardinalities decide
+        const bool both_tiny = desc_type(a) == kArray && desc_len(a) <= kTinyMax && desc_type(b) == kArray && desc_len(b) <= kTinyMax;
+        if (!trivial && !both_tiny) defer = true;
+        else {
+          uint32_t ic;
+          if (a.n == 0 || b.n == 0) ic = 0;
+          else if (a.n == kFullN) ic = b.n;  // roaring.go:3079-3084
+          else if (b.n == kFullN) ic = a.n;
+          else {
+            uint32_t va[kTinyMax], vb[kTinyMax];
+            tiny_values(a, 0x10000u, va);
+            tiny_values(b, 0x20000u, vb);
+            ic = 0;
+#pragma unroll
+            for (int i = 0; i < int(kTinyMax); i++)
+#pragma unroll
+              for (int j = 0; j < int(kTinyMax); j++) ic += va[i] == vb[j] ? 1u : 0u;
+          }
+          switch (ins[1].op) {
+            case I_AND_LEAF: r = ic; break;
+            case I_OR_LEAF: r = a.n + b.n - ic; break;
+            case I_XOR_LEAF: r = a.n + b.n - 2 * ic; break;
+            default: r = a.n - ic; break;  // I_ANDNOT_LEAF
+          }
+          bytes_acc += desc_algo_bytes(a) + desc_algo_bytes(b);
+        }
+      } else defer = true;
+    }
+    // deferred items: one list slot each, claimed with one atomic per warp
+    const uint32_t dmask = __ballot_sync(0xffffffffu, defer);
+    if (dmask) {
+      uint32_t slot0 = 0;
+      if (lane == 0) slot0 = atomicAdd(p.item_count, uint32_t(__popc(dmask)));
+      slot0 = __shfl_sync(0xffffffffu, slot0, 0);
+      if (defer) p.item_list[slot0 + __popc(dmask & ((1u << lane) - 1u))] = uint32_t(item);
+    }
+    // counts: flush when some lane moves on to another output counter
+    const bool moved = valid && !defer && r && off != acc_off;
+    if (__any_sync(0xffffffffu, moved && acc != 0)) {
+      const uint32_t grp = __match_any_sync(0xffffffffu, acc_off);
+      const unsigned long long tot = warp_group_sum(grp, acc);
+      if (lane == __ffs(grp) - 1 && tot && p.out_counts) atomicAdd(p.out_counts + acc_off, tot);
+      acc = 0;
+    }
+    if (valid && !defer && r) { acc_off = off; acc += r; }
+  }
+  {
+    const uint32_t grp = __match_any_sync(0xffffffffu, acc_off);
+    const unsigned long long tot = warp_group_sum(grp, acc);
+    if (lane == __ffs(grp) - 1 && tot && p.out_counts) atomicAdd(p.out_counts + acc_off, tot);
+  }
+  bytes_acc = warp_sum64(bytes_acc);
+  if (lane == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -486,3 +486,34 @@ def test_reserve_then_counts_do_not_allocate(eng_orc):
     assert torch.cuda.mem_get_info(0)[0] == free0
     with pytest.raises(Exception):
         eng.reserve(0, 4, 3)
+
+
+def test_lane_per_item_pass_on_very_sparse_rows(eng_orc):
+    """eval_tiny_kernel: rows of a few values per container (p = 1e-4 .. 3e-4) — pairs of tiny arrays are counted one lane
+    per item, longer arrays / runs / three-operand programs are handed on to the other evaluators; totals, per-shard
+    counts and batches against the oracle, with shards missing from one field."""
+    from pilosa_b200.abi import Difference, Union, Xor
+
+    eng, orc = eng_orc
+    g, c = Executor(eng), Executor(orc)
+    shards = list(range(40))
+    for ex in (g, c):
+        ex.create_field("sp")
+        ex.create_field("md")
+        for s in shards:
+            ex.load_fragment("sp", s, synth.bernoulli(s, 1, 4, 1e-4, 11))
+            if s % 7 != 3:
+                ex.load_fragment("md", s, synth.bernoulli(s, 1, 3, 3e-4, 12))     # ~20 values: many containers beyond 16
+    A, B, C_, D = Row("sp", 1), Row("sp", 2), Row("sp", 3), Row("sp", 4)
+    M, N = Row("md", 1), Row("md", 2)
+    calls = [A, M, Row("sp", 99)]
+    for op in (Intersect, Union, Xor, Difference):
+        calls += [op(A, B), op(B, A), op(A, A), op(A, M), op(M, N), op(N, A), op(A, Row("sp", 99)), op(Row("md", 77), B), op(A, B, C_), op(M, A, D, N)]
+    for call in calls:
+        assert g.count(call, shards) == c.count(call, shards), repr(call)
+        assert g.be.count_shards(g.program(call), shards) == c.be.count_shards(c.program(call), shards), repr(call)
+    assert g.count_batch(calls * 3, shards) == c.count_batch(calls * 3, shards)
+    assert g.count_batch(calls, shards[5:6]) == c.count_batch(calls, shards[5:6])
+    # self-consistency on every shard: |A| + |B| = |A or B| + |A and B|
+    n = {k: g.count(x, shards) for k, x in dict(a=A, b=B, u=Union(A, B), i=Intersect(A, B), x=Xor(A, B), d=Difference(A, B)).items()}
+    assert n["a"] + n["b"] == n["u"] + n["i"] and n["x"] == n["u"] - n["i"] and n["d"] == n["a"] - n["i"]
