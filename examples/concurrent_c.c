@@ -80,10 +80,14 @@ int main(int argc, char** argv) {
       if (pb200_count(ctx, p, 3, shards, SHARDS, &expect[a][b]) != PB200_OK) { fprintf(stderr, "count: %s\n", pb200_last_error(ctx)); return 1; }
     }
   run(1, 200); /* warm-up */
-  const double r1 = run(1, calls), rn = run(threads, calls);
+  const double r1 = run(1, calls);
+  uint64_t l0 = 0, q0 = 0, l1 = 0, q1 = 0;
+  pb200_combine_stats(ctx, &l0, &q0);
+  const double rn = run(threads, calls);
+  pb200_combine_stats(ctx, &l1, &q1);
   printf("{\"threads\": %d, \"calls_per_thread\": %d, \"queries_per_s_1_thread\": %.0f, \"queries_per_s_n_threads\": %.0f, \"speedup\": %.2f, "
-         "\"call_us_1_thread\": %.2f, \"call_us_n_threads_per_query\": %.2f}\n",
-         threads, calls, r1, rn, rn / r1, 1e6 / r1, 1e6 / rn);
+         "\"call_us_1_thread\": %.2f, \"call_us_n_threads_per_query\": %.2f, \"combined_launches\": %llu, \"queries_per_combined_launch\": %.2f}\n",
+         threads, calls, r1, rn, rn / r1, 1e6 / r1, 1e6 / rn, (unsigned long long)(l1 - l0), l1 > l0 ? (double)(q1 - q0) / (double)(l1 - l0) : 0.0);
   pb200_shutdown(ctx);
   return 0;
 }

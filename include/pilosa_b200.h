@@ -563,6 +563,10 @@ int pb200_reserve(pb200_ctx* ctx, uint32_t max_queries, uint32_t max_shards, uin
 /* Timing / byte accounting of the last query call on this context. */
 int pb200_last_timing(pb200_ctx* ctx, pb200_timing* out);
 
+/* Statistics of the combining queue behind pb200_count: how many batched launches served how many single-query calls
+ * since pb200_init (calls that ran alone are not counted). queries / launches = the mean width of a combined launch. */
+int pb200_combine_stats(pb200_ctx* ctx, uint64_t* launches, uint64_t* queries);
+
 #ifdef __cplusplus
 }
 #endif

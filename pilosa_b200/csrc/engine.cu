@@ -223,7 +223,7 @@ extern "C" int pb200_shutdown(pb200_ctx* ctx) {
       if (fam.d_frags) cudaFree(fam.d_frags);
     }
     if (ctx->d_families) cudaFree(ctx->d_families);
-    for (DevBuf* b : {&ctx->d_rows, &ctx->d_rows_off, &ctx->d_rows_meta, &ctx->d_rows_item_off, &ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_rest, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi, &ctx->d_ing, &ctx->d_ing_res, &ctx->d_topn_compact})
+    for (DevBuf* b : {&ctx->d_rows, &ctx->d_rows_off, &ctx->d_rows_meta, &ctx->d_rows_item_off, &ctx->d_ovf, &ctx->d_slow_descs, &ctx->d_rest, &ctx->d_sparse, &ctx->d_batch, &ctx->d_out, &ctx->d_slow, &ctx->d_temp, &ctx->d_dense, &ctx->d_dense_n, &ctx->d_misc, &ctx->d_topn, &ctx->d_bsi, &ctx->d_ing, &ctx->d_ing_res, &ctx->d_topn_compact})
       if (b->p) cudaFree(b->p);
     for (auto& r : ctx->arena.retired) cudaFree(r.first);
     if (ctx->arena.base) cudaFree(ctx->arena.base);
@@ -924,6 +924,13 @@ int upload_batch(pb200_ctx* ctx, const Compiled& cp, const uint64_t* shards, uin
   return PB200_OK;
 }
 
+// Where the kernels of the call being enqueued add their algorithmic bytes: a Count call keeps the counter (and the
+// deferred-item counters) behind its counts, so that one memset clears and one copy fetches everything; other calls
+// use the context's word.
+unsigned long long* algo_ptr(pb200_ctx* ctx) {
+  return ctx->algo_dev ? ctx->algo_dev : reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 8);
+}
+
 // Persistent grids are sized to exactly the number of CTAs that can be resident (SMs x CTAs
 // per SM from the occupancy calculator): a grid larger than that runs a second, thinner wave.
 template <class K>
@@ -941,7 +948,7 @@ enum { OCC_FAST = 0, OCC_STAGED, OCC_SUM, OCC_MM, OCC_TOPN, OCC_FOLD, OCC_TINY }
 int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards, bool staging,
                 unsigned long long* out_counts, uint32_t qstride, uint32_t sstride, uint8_t* dense_out, uint32_t* dense_n,
                 uint32_t max_leaves = kMaxLeaves, bool bushy = true, bool fold_all = false, const PushDesc* push = nullptr, bool flat = true,
-                bool tiny = false) {
+                bool tiny = false, uint16_t* sparse_out = nullptr) {
   const uint64_t n_items = uint64_t(n_queries) * n_shards * kRowContainers;
   if (n_items == 0) return PB200_OK;
   if (n_items >= (1ull << 32)) return fail(ctx, PB200_ERR_RANGE, "batch too large: queries x shards x 16 must be < 2^32");
@@ -959,10 +966,10 @@ int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t 
   p.n_shards = n_shards; p.n_queries = n_queries;
   p.temp_base = static_cast<const uint8_t*>(ctx->d_temp.p);
   p.out_counts = out_counts; p.out_qstride = qstride; p.out_sstride = sstride;
-  p.dense_out = dense_out; p.dense_n = dense_n;
+  p.dense_out = dense_out; p.dense_n = dense_n; p.sparse_out = sparse_out;
   p.slow_list = static_cast<uint32_t*>(ctx->d_slow.p);
-  p.slow_count = static_cast<uint32_t*>(ctx->d_misc.p);
-  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + ctx->algo_off);
+  p.slow_count = ctx->slow_dev ? ctx->slow_dev : static_cast<uint32_t*>(ctx->d_misc.p);
+  p.algo_bytes = algo_ptr(ctx);
   // descriptors of deferred items travel from the fast to the staged kernel when they fit a modest scratch budget
   const uint64_t desc_bytes = n_items * uint64_t(max_leaves) * sizeof(ContainerDesc);
   p.fold_all = fold_all ? 1u : 0u;
@@ -976,10 +983,12 @@ int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t 
   // Very sparse rows (containers of a few values): a first pass with one lane per item counts the pairs of tiny arrays
   // in registers and leaves eval_fast_kernel a list of the rest.
   // (only when the items outnumber the warps the device holds at once: below that a warp per item is one wave anyway)
-  tiny = tiny && staging && !fold_all && !dense_out && out_counts && n_items > uint64_t(ctx->sm_count) * 64;
+  tiny = tiny && staging && !fold_all && (dense_out ? (sparse_out && dense_n && n_queries == 1) : out_counts != nullptr) && n_items > uint64_t(ctx->sm_count) * 64;
   if (tiny) TRY(ensure_dev(ctx, ctx->d_rest, size_t(n_items) * 4));
   if (!fold_all) {
-    CUDA_TRY(ctx, cudaMemsetAsync(p.slow_count, 0, 8, ctx->stream));  // slow_count and, behind it, the tiny pass's item count
+    // slow_count and, behind it, the tiny pass's item count (a Count call's first launch finds them cleared with its counts)
+    if (ctx->slow_zeroed) ctx->slow_zeroed = false;
+    else CUDA_TRY(ctx, cudaMemsetAsync(p.slow_count, 0, 8, ctx->stream));
     if (tiny) {
       p.item_list = static_cast<uint32_t*>(ctx->d_rest.p);
       p.item_count = p.slow_count + 1;
@@ -1102,7 +1111,7 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
   sl.launched = false;
   sl.seq = ++ctx->begin_seq;
   std::swap(ctx->d_out, sl.d_out);  // ensure_* work on the context's named buffers
-  int rc = ensure_dev(ctx, ctx->d_out, std::max<size_t>(n_out, 1) * 8);
+  int rc = ensure_dev(ctx, ctx->d_out, (std::max<size_t>(n_out, 1) + 2) * 8);  // [counts][algorithmic bytes][deferred-item counters]
   std::swap(ctx->d_out, sl.d_out);
   TRY(rc);
   std::swap(ctx->h_out, sl.h_out);
@@ -1111,17 +1120,22 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
   TRY(rc);
   TRY(ensure_dev(ctx, ctx->d_misc, 64));
   ctx->timing = pb200_timing{};
-  ctx->algo_off = 16 + 8 * size_t(si);
-  CUDA_TRY(ctx, cudaMemsetAsync(static_cast<uint8_t*>(ctx->d_misc.p) + ctx->algo_off, 0, 8, ctx->stream));
   ctx->n_pending++;
   unsigned long long* d_out = static_cast<unsigned long long*>(sl.d_out.p);
   CUDA_TRY(ctx, cudaEventRecord(sl.k0, ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(d_out, 0, (std::max<size_t>(n_out, 1) + 2) * 8, ctx->stream));
+  struct Counters {  // the slot's own counters are the context's for the duration of this call
+    pb200_ctx* c;
+    Counters(pb200_ctx* cc, unsigned long long* base, size_t n) : c(cc) {
+      c->algo_dev = base + n; c->slow_dev = reinterpret_cast<uint32_t*>(base + n + 1); c->slow_zeroed = true;
+    }
+    ~Counters() { c->algo_dev = nullptr; c->slow_dev = nullptr; c->slow_zeroed = false; }
+  } counters(ctx, d_out, std::max<size_t>(n_out, 1));
   if (n_queries != 0 && n_shards == 0) {
-    CUDA_TRY(ctx, cudaMemsetAsync(d_out, 0, n_out * 8, ctx->stream));
     if (ctx->peer_allreduce && !per_shard) {  // a rank without local shards still takes part in the sum (its zeros, its arrival)
       PushDesc pd{};
       const int rc0 = peer_begin_epoch(ctx, d_out, n_queries, pd, &sl.peer_slot);
-      if (rc0 != PB200_OK) { ctx->n_pending--; ctx->algo_off = 8; return rc0; }
+      if (rc0 != PB200_OK) { ctx->n_pending--; return rc0; }
       peer_push_kernel<<<1, 256, 0, ctx->stream>>>(pd);
       CUDA_TRY(ctx, cudaGetLastError());
       TRY(peer_end_epoch(ctx, sl.peer_slot));
@@ -1130,7 +1144,7 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
   if (n_queries != 0 && n_shards != 0) {
     Compiled cp;
     rc = compile_batch(ctx, progs, prog_off, n_queries, cp);
-    if (rc != PB200_OK) { ctx->n_pending--; ctx->algo_off = 8; return rc; }
+    if (rc != PB200_OK) { ctx->n_pending--; return rc; }
     // Count(Row(v <op> x)) with nothing around it: let the comparator kernel count, skip the dense row
     for (uint32_t q = 0; q < n_queries; q++) {
       const Prog& pg = cp.progs[q];
@@ -1156,7 +1170,6 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
     bool need_temp = false;
     for (auto& pt : cp.pre) need_temp |= !(pt.kind == 0 && pt.count_only);
     if (rc == PB200_OK && need_temp) rc = ensure_dev(ctx, ctx->d_temp, size_t(cp.n_temp_slots) * n_shards * kRowContainers * kBitmapBytes);
-    if (rc == PB200_OK && cudaMemsetAsync(d_out, 0, n_out * 8, ctx->stream) != cudaSuccess) rc = fail(ctx, PB200_ERR_CUDA, "cudaMemsetAsync(counts) failed");
     if (rc == PB200_OK) rc = run_pretasks(ctx, cp, bd, n_shards);
     PushDesc pd{};
     const bool reduce = ctx->peer_allreduce && !per_shard;
@@ -1171,9 +1184,8 @@ int count_begin(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_of
     if (rc == PB200_OK && has_shift(cp))  // bits shifted past a shard's last column count too (roaring.go:970-974)
       rc = launch_overflow(ctx, bd, bd.progs, n_queries, n_shards, d_out, per_shard ? n_shards : 1, per_shard ? 1 : 0, nullptr);
     if (rc == PB200_OK && reduce) rc = peer_end_epoch(ctx, sl.peer_slot);
-    if (rc != PB200_OK) { ctx->n_pending--; ctx->algo_off = 8; return rc; }
+    if (rc != PB200_OK) { ctx->n_pending--; return rc; }
   }
-  ctx->algo_off = 8;
   CUDA_TRY(ctx, cudaEventRecord(sl.k1, ctx->stream));
   CUDA_TRY(ctx, cudaEventRecord(sl.done, ctx->stream));
   sl.launched = true;
@@ -1193,19 +1205,25 @@ int count_end(pb200_ctx* ctx, uint64_t* out) {
   CountSlot& sl = ctx->slots[ctx->head];
   const size_t n_out = sl.n_out;
   if (n_out && !out) return PB200_ERR_INVALID;
-  // Nothing younger queued: re-record `done` now so that work the host enqueued on the compute
-  // stream after _begin (an NCCL all-reduce of the device-resident counts) is waited for too.
-  if (ctx->n_pending == 1) CUDA_TRY(ctx, cudaEventRecord(sl.done, ctx->stream));
-  CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copy_stream, sl.done, 0));
-  if (sl.peer_slot >= 0) {  // the sum over the ranks: wait for the peers' counts beside whatever the compute stream is running
-    TRY(peer_collect(ctx, sl.peer_slot));
-    sl.peer_slot = -1;
-  }
   uint8_t* h = static_cast<uint8_t*>(sl.h_out.p);
-  if (n_out) CUDA_TRY(ctx, cudaMemcpyAsync(h, sl.d_out.p, n_out * 8, cudaMemcpyDeviceToHost, ctx->copy_stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(h + std::max<size_t>(n_out, 1) * 8, static_cast<uint8_t*>(ctx->d_misc.p) + 16 + 8 * size_t(ctx->head), 8,
-                                cudaMemcpyDeviceToHost, ctx->copy_stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->copy_stream));
+  const size_t fetch = (std::max<size_t>(n_out, 1) + 1) * 8;  // the counts and, behind them, the algorithmic bytes: one copy
+  if (ctx->n_pending == 1 && sl.peer_slot < 0) {
+    // Nothing younger is queued and nothing arrives from peers: the compute stream itself carries the copy (whatever the
+    // host queued on it after _begin, an in-place NCCL all-reduce, runs before it) — no event, no second stream.
+    CUDA_TRY(ctx, cudaMemcpyAsync(h, sl.d_out.p, fetch, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  } else {
+    // Re-record `done` when nothing younger is queued, so that work the host enqueued on the compute stream after
+    // _begin is waited for too; the copy runs on the copy stream, beside a younger batch's kernels.
+    if (ctx->n_pending == 1) CUDA_TRY(ctx, cudaEventRecord(sl.done, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copy_stream, sl.done, 0));
+    if (sl.peer_slot >= 0) {  // the sum over the ranks: wait for the peers' counts beside whatever the compute stream is running
+      TRY(peer_collect(ctx, sl.peer_slot));
+      sl.peer_slot = -1;
+    }
+    CUDA_TRY(ctx, cudaMemcpyAsync(h, sl.d_out.p, fetch, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->copy_stream));
+  }
   if (ctx->peer_allreduce) TRY(peer_check_error(ctx));
   float ms = 0;
   if (cudaEventElapsedTime(&ms, sl.k0, sl.k1) == cudaSuccess) ctx->timing.kernel_ms = ms;
@@ -1327,6 +1345,13 @@ int combine_counts(pb200_ctx* ctx, CountReq& me) {
 }
 
 }  // namespace
+
+extern "C" int pb200_combine_stats(pb200_ctx* ctx, uint64_t* launches, uint64_t* queries) {
+  ENTER(ctx);
+  if (launches) *launches = ctx->cq_batches;
+  if (queries) *queries = ctx->cq_queries;
+  return PB200_OK;
+}
 
 extern "C" int pb200_count(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards, uint64_t* out_count) {
   if (!ctx) return PB200_ERR_INVALID;

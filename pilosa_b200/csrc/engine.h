@@ -160,6 +160,8 @@ struct pb200_ctx {
   // fragment is freed, so that the peers' tables follow and no peer still reads the old copy
   std::function<int(uint32_t family, uint64_t shard, const pb200::FragDev& dev, bool all_bitmap, bool present)> publish;
   uint64_t generation = 0;  // bumped by every load / write / drop / table growth: prepared batches re-validate against it
+  pb200::DevBuf d_sparse;        // value lists of short result containers (K12 path, EvalParams::sparse_out)
+  bool dense_lists = false;      // d_dense_n carries kSparseFlag entries backed by d_sparse
   pb200::DevBuf d_slow_descs, d_ovf, d_rest;  // d_rest: items eval_tiny_kernel leaves to eval_fast_kernel
   pb200::DevBuf d_rows, d_rows_off, d_rows_meta, d_rows_item_off;  // K11: serialised result rows (kernels_rows.cuh)
   bool dense_has_ovf = false;                      // the rows in d_dense carry Shift overflow words
@@ -180,6 +182,8 @@ struct pb200_ctx {
   int n_pending = 0, head = 0;   // ring of pending slots
   uint64_t begin_seq = 0;
   cudaStream_t copy_stream = nullptr;
-  size_t algo_off = 8;           // byte offset in d_misc of the algorithmic-bytes counter the next kernels add to
+  unsigned long long* algo_dev = nullptr;  // set while a Count call is enqueued: its own algorithmic-bytes counter (behind its counts) ...
+  uint32_t* slow_dev = nullptr;            // ... and deferred-item counters; null: the words in d_misc
+  bool slow_zeroed = false;                // the call's memset has cleared slow_dev already (consumed by its first launch_eval)
   pb200_timing timing{};
 };

@@ -299,6 +299,7 @@ int gather_dense(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const
   if (cudaGetLastError() != cudaSuccess) return fail0(fail(c0, PB200_ERR_CUDA, "gather launch failed"));
   *shards_dev = static_cast<const uint64_t*>(m->g_shards.p);
   c0->dense_has_ovf = any_ovf;
+  c0->dense_lists = false;  // gathered rows are words throughout
   c0->dense_ovf_dev = static_cast<unsigned long long*>(m->g_ovf.p);
   timing_merge(m, active);
   return PB200_OK;

@@ -187,7 +187,7 @@ extern "C" int pb200_reserve(pb200_ctx* ctx, uint32_t max_queries, uint32_t max_
   if (desc_bytes <= (256ull << 20)) TRY(ensure_dev(ctx, ctx->d_slow_descs, size_t(desc_bytes)));
   TRY(ensure_dev(ctx, ctx->d_batch, batch_bytes));
   TRY(ensure_pin(ctx, ctx->h_stage, batch_bytes));
-  TRY(ensure_dev(ctx, ctx->d_out, size_t(max_queries) * 8));
+  TRY(ensure_dev(ctx, ctx->d_out, (size_t(max_queries) + 2) * 8));
   TRY(ensure_pin(ctx, ctx->h_out, size_t(max_queries) * 8 + 8));
   TRY(ensure_pin(ctx, ctx->h_algo, 64));
   if (!ctx->copy_stream) CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
@@ -197,7 +197,7 @@ extern "C" int pb200_reserve(pb200_ctx* ctx, uint32_t max_queries, uint32_t max_
       CUDA_TRY(ctx, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
     }
     std::swap(ctx->d_out, sl.d_out); std::swap(ctx->d_batch, sl.d_batch); std::swap(ctx->h_stage, sl.h_stage); std::swap(ctx->h_out, sl.h_out);
-    int rc = ensure_dev(ctx, ctx->d_out, size_t(max_queries) * 8);
+    int rc = ensure_dev(ctx, ctx->d_out, (size_t(max_queries) + 2) * 8);
     if (rc == PB200_OK) rc = ensure_dev(ctx, ctx->d_batch, batch_bytes);
     if (rc == PB200_OK) rc = ensure_pin(ctx, ctx->h_stage, batch_bytes);
     if (rc == PB200_OK) rc = ensure_pin(ctx, ctx->h_out, size_t(max_queries) * 8 + 8);

@@ -31,7 +31,7 @@ int launch_bsi_range(pb200_ctx* ctx, const BatchDev& bd, const pb200_node& nd, u
   p.shards = bd.shards; p.n_shards = n_shards;
   p.bsi_op = nd.bsi_op; p.a = nd.a; p.b = nd.b;
   p.dense_out = dense_out;
-  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + ctx->algo_off);
+  p.algo_bytes = algo_ptr(ctx);
   const uint32_t items = n_shards * kRowContainers;
   {
     const RangePlan plan = range_plan(p.bsi_op, p.a, p.b);
@@ -89,7 +89,7 @@ int launch_union_rows(pb200_ctx* ctx, const BatchDev& bd, const Prog* prog, uint
   p.n_shards = n_shards; p.n_queries = 1;
   p.temp_base = static_cast<const uint8_t*>(ctx->d_temp.p);
   p.dense_out = dense_out;
-  p.algo_bytes = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + ctx->algo_off);
+  p.algo_bytes = algo_ptr(ctx);
   const uint32_t grid = uint32_t(std::min<uint64_t>(n_items, uint64_t(ctx->sm_count) * 8));
   union_rows_kernel<<<grid, kUnionThreads, 0, ctx->stream>>>(p);
   ctx->timing.launches++;
@@ -131,7 +131,7 @@ int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_
 // Compile one program and evaluate it into dense rows [n_shards][16][1024 words] at
 // ctx->d_dense with per-container cardinalities at ctx->d_dense_n. Leaves timing open:
 // the caller records ev1.
-int eval_dense(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards, BatchDev& bd) {
+int eval_dense(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards, BatchDev& bd, bool allow_lists = false) {
   Compiled cp;
   Compiler cc(ctx, cp);
   if (!cc.compile(prog, n_nodes)) return fail(ctx, PB200_ERR_INVALID, cc.err);
@@ -147,7 +147,11 @@ int eval_dense(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, const u
     ctx->dense_ovf_dev = ovf_slot(ctx, cp.n_temp_slots, n_shards);
     TRY(launch_overflow(ctx, bd, bd.progs, 1, n_shards, nullptr, 0, 0, ctx->dense_ovf_dev));
   }
-  return launch_eval(ctx, bd, bd.progs, 1, n_shards, true, nullptr, 0, 0, static_cast<uint8_t*>(ctx->d_dense.p), static_cast<uint32_t*>(ctx->d_dense_n.p));
+  // K12 reads short result containers as value lists (64 B instead of 8 KiB each way); every other consumer of the dense rows gets words
+  ctx->dense_lists = allow_lists && !ctx->dense_has_ovf;
+  if (ctx->dense_lists) TRY(ensure_dev(ctx, ctx->d_sparse, items * kSparseListMax * 2));
+  return launch_eval(ctx, bd, bd.progs, 1, n_shards, true, nullptr, 0, 0, static_cast<uint8_t*>(ctx->d_dense.p), static_cast<uint32_t*>(ctx->d_dense_n.p),
+                     max_leaves_of(cp), cp.any_bushy, false, nullptr, cp.any_flat, tiny_of(cp), ctx->dense_lists ? static_cast<uint16_t*>(ctx->d_sparse.p) : nullptr);
 }
 
 int eval_one_shard(pb200_ctx* ctx, const pb200_node* prog, uint32_t n_nodes, uint64_t shard, std::vector<uint64_t>& words, std::vector<uint32_t>& ns,
@@ -264,7 +268,8 @@ int emit_proto_from_dense(pb200_ctx* ctx, const uint64_t* shards_dev, uint32_t n
   uint32_t* sizes = static_cast<uint32_t*>(ctx->d_rows_meta.p);
   unsigned long long* slot_off = static_cast<unsigned long long*>(ctx->d_rows_item_off.p);
   unsigned long long* totals = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ctx->d_misc.p) + 16);
-  proto_size_kernel<<<std::min<uint32_t>((n_slots + 7) / 8, uint32_t(ctx->sm_count) * 8), kProtoThreads, 0, ctx->stream>>>(dense, dense_n, shards_dev, ovf,
+  const uint16_t* sparse = ctx->dense_lists ? static_cast<const uint16_t*>(ctx->d_sparse.p) : nullptr;  // (no list flags are set without it)
+  proto_size_kernel<<<std::min<uint32_t>((n_slots + 7) / 8, uint32_t(ctx->sm_count) * 8), kProtoThreads, 0, ctx->stream>>>(dense, dense_n, sparse, shards_dev, ovf,
                                                                                                                    n_shards, sizes);
   proto_layout_kernel<<<1, 1024, 0, ctx->stream>>>(sizes, n_slots, slot_off, totals);
   ctx->timing.launches += 2;
@@ -280,7 +285,7 @@ int emit_proto_from_dense(pb200_ctx* ctx, const uint64_t* shards_dev, uint32_t n
   if (cap < total) { finish_call(ctx); return fail(ctx, PB200_ERR_RANGE, "output buffer too small"); }
   TRY(ensure_dev(ctx, ctx->d_rows, total));
   proto_emit_kernel<<<std::min<uint32_t>(n_slots, uint32_t(ctx->sm_count) * 8), kProtoThreads, 0, ctx->stream>>>(
-      dense, sizes, slot_off, totals, shards_dev, ovf, n_shards, static_cast<uint8_t*>(ctx->d_rows.p));
+      dense, dense_n, sparse, sizes, slot_off, totals, shards_dev, ovf, n_shards, static_cast<uint8_t*>(ctx->d_rows.p));
   ctx->timing.launches += 1;
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
@@ -303,7 +308,7 @@ extern "C" int pb200_eval_proto_columns(pb200_ctx* ctx, const pb200_node* prog, 
   timing_begin(ctx);
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
   BatchDev bd{};
-  TRY(eval_dense(ctx, prog, n_nodes, shards, n_shards, bd));
+  TRY(eval_dense(ctx, prog, n_nodes, shards, n_shards, bd, true));
   return emit_proto_from_dense(ctx, bd.shards, n_shards, out, cap, out_len);
 }
 

@@ -96,6 +96,8 @@ struct EvalParams {
   uint32_t fold_all;               // eval_fold_kernel walks EVERY item itself (no eval_fast_kernel pass, no deferred list)
   uint32_t* item_list;             // eval_tiny_kernel ran first: the items it left for eval_fast_kernel ...
   uint32_t* item_count;            // ... and how many (null: eval_fast_kernel walks every item)
+  uint16_t* sparse_out;            // optional, with dense_out: a result container of <= kSparseListMax values is written as a sorted
+                                   // list at sparse_out[item * kSparseListMax] instead of 8 KiB of words; dense_n[item] carries kSparseFlag
   PushDesc push;                   // eval_fast_kernel only: peer reduction fused into the kernel's tail (n_dst == 0: none)
 };
 
@@ -233,6 +235,8 @@ __device__ __forceinline__ unsigned long long warp_group_sum(uint32_t grp, unsig
 // the pair should be staged instead. The result is uniform across the warp.
 // ---------------------------------------------------------------------------------------
 constexpr uint32_t kNotSparse = 0xffffffffu;
+constexpr uint32_t kSparseListMax = 32;        // values of a result container kept as a list (EvalParams::sparse_out)
+constexpr uint32_t kSparseFlag = 0x80000000u;  // in dense_n: the container is in the list, its dense words were not written
 constexpr uint32_t kSparseArrayMax = 1024;  // elements of the probing side
 constexpr uint32_t kSparseRunMax = 256;     // runs of the probing side
 
@@ -529,6 +533,7 @@ __global__ void __launch_bounds__(256) eval_tiny_kernel(EvalParams p) {
   const int lane = threadIdx.x & 31;
   const uint64_t n_items = uint64_t(p.n_queries) * p.n_shards * kRowContainers;
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  const bool lists = p.sparse_out != nullptr;  // the rows are wanted (one query): short results go out as value lists, see EvalParams
   unsigned long long bytes_acc = 0, acc = 0;
   uint64_t acc_off = ~0ull;
   for (uint64_t base = uint64_t(blockIdx.x) * blockDim.x + (threadIdx.x & ~31u); base < n_items; base += stride) {  // warp-uniform trips
@@ -547,14 +552,49 @@ __global__ void __launch_bounds__(256) eval_tiny_kernel(EvalParams p) {
       if (pg.n_instr == 1 && p.leaves[pg.leaf_off + ins[0].leaf].kind != L_TEMP) {  // Count(Row): roaring.go:405
         const ContainerDesc d = resolve_leaf(p, p.leaves[pg.leaf_off + ins[0].leaf], s, c);
         r = d.n;
-        bytes_acc += desc_algo_bytes(d);
+        if (lists) {  // the row itself is wanted: a short array IS its value list
+          if (d.n == 0) p.dense_n[item] = 0;
+          else if (desc_type(d) == kArray && desc_len(d) <= kSparseListMax) {
+            const uint4* src = reinterpret_cast<const uint4*>(d.addr);
+            uint4* dst = reinterpret_cast<uint4*>(p.sparse_out + item * kSparseListMax);
+            const uint32_t len = desc_len(d);
+#pragma unroll
+            for (int k = 0; k < int(kSparseListMax / 8); k++)
+              if (uint32_t(k) * 8 < len) dst[k] = ldg128(src + k);
+            p.dense_n[item] = len | kSparseFlag;
+          } else defer = true;
+        }
+        if (!defer) bytes_acc += desc_algo_bytes(d);
       } else if (pg.n_instr == 2 && ins[0].op == I_LOAD && ins[1].op >= I_AND_LEAF && ins[1].op <= I_ANDNOT_LEAF &&
                  p.leaves[pg.leaf_off + ins[0].leaf].kind != L_TEMP && p.leaves[pg.leaf_off + ins[1].leaf].kind != L_TEMP) {
         const ContainerDesc a = resolve_leaf(p, p.leaves[pg.leaf_off + ins[0].leaf], s, c);
         const ContainerDesc b = resolve_leaf(p, p.leaves[pg.leaf_off + ins[1].leaf], s, c);
         const bool trivial = a.n == 0 || b.n == 0 || a.n == kFullN || b.n == kFullN;  // the cardinalities decide
         const bool both_tiny = desc_type(a) == kArray && desc_len(a) <= kTinyMax && desc_type(b) == kArray && desc_len(b) <= kTinyMax;
-        if (!trivial && !both_tiny) defer = true;
+        if (lists) {
+          // the result row is wanted: an intersection or a difference of two tiny arrays is a subset of the first one, kept
+          // in its order; unions, symmetric differences and anything with a full or a long operand go the general way
+          const uint8_t op = ins[1].op;
+          if (a.n == 0 || (op == I_AND_LEAF && b.n == 0)) p.dense_n[item] = 0;
+          else if (both_tiny && (op == I_AND_LEAF || op == I_ANDNOT_LEAF)) {
+            uint32_t va[kTinyMax], vb[kTinyMax];
+            tiny_values(a, 0x10000u, va);
+            tiny_values(b, 0x20000u, vb);
+            uint16_t* lst = p.sparse_out + item * kSparseListMax;
+            const uint32_t la = desc_len(a);
+            uint32_t k = 0;
+#pragma unroll
+            for (int i = 0; i < int(kTinyMax); i++) {
+              bool hit = false;
+#pragma unroll
+              for (int j = 0; j < int(kTinyMax); j++) hit |= va[i] == vb[j];
+              if (uint32_t(i) < la && hit == (op == I_AND_LEAF)) lst[k++] = uint16_t(va[i]);
+            }
+            r = k;
+            p.dense_n[item] = k ? (k | kSparseFlag) : 0u;
+            bytes_acc += desc_algo_bytes(a) + desc_algo_bytes(b);
+          } else defer = true;
+        } else if (!trivial && !both_tiny) defer = true;
         else {
           uint32_t ic;
           if (a.n == 0 || b.n == 0) ic = 0;
@@ -1048,7 +1088,7 @@ struct FoldMeta {  // one deferred item, resolved by the producer warp
 __global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_kernel(EvalParams p) {
   extern __shared__ __align__(128) uint8_t s_dyn[];  // [window][S][E][kFoldStages x staging], 8 KiB each
   __shared__ FoldMeta s_meta[kFoldMeta];
-  __shared__ uint32_t s_red[kFoldThreads / 32];
+  __shared__ uint32_t s_red[kFoldThreads / 32], s_red2[kFoldThreads / 32];
   __shared__ __align__(8) uint64_t s_full[kFoldStages], s_empty[kFoldStages], s_mfull[kFoldMeta], s_mempty[kFoldMeta];
   const int tid = threadIdx.x, lane = tid & 31;
   const uint32_t n_slow = p.fold_all ? p.n_queries * p.n_shards * kRowContainers : *p.slow_count;
@@ -1221,26 +1261,53 @@ __global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_ke
 
     const uint4* win4 = reinterpret_cast<const uint4*>(s_dyn + wsel * kBitmapBytes);
     const uint4 a = win4[tid], b = win4[tid + kFoldThreads];
-    uint32_t cnt = popc128(a) + popc128(b);
-    if (p.dense_out) {
-      uint4* dout = reinterpret_cast<uint4*>(p.dense_out + m.item * kBitmapBytes);
-      dout[tid] = a; dout[tid + kFoldThreads] = b;
-    }
-    cnt = warp_sum(cnt);
-    if (!p.dense_n) {  // count only: every warp adds its part, one barrier less per item
+    const uint32_t ca = popc128(a), cb = popc128(b);
+    if (!p.dense_n) {  // no per-container cardinalities wanted (a count, or a temp row): every warp adds its part, one barrier less per item
+      if (p.dense_out) {
+        uint4* dout = reinterpret_cast<uint4*>(p.dense_out + m.item * kBitmapBytes);
+        dout[tid] = a; dout[tid + kFoldThreads] = b;
+      }
+      const uint32_t cnt = warp_sum(ca + cb);
       if (p.out_counts) add_count(uint64_t(m.q) * p.out_qstride + uint64_t(m.s) * p.out_sstride, cnt);
       fold_bar();  // the window and the item's descriptors are no longer needed
       if (tid == 0) mbar_arrive(&s_mempty[ms]);
       continue;
     }
-    if (lane == 0) s_red[tid >> 5] = cnt;
-    fold_bar();
-    if (tid == 0) {
-      uint32_t tot = 0;
+    // the row is wanted: thread t holds words 4t .. 4t+3 (a) and 1024 + 4t .. (b) of the container; inclusive scans of
+    // both halves give the total and, for a short result, every thread's place in the value list
+    uint32_t xa = ca, xb = cb;
 #pragma unroll
-      for (int w = 0; w < kFoldThreads / 32; w++) tot += s_red[w];
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t ya = __shfl_up_sync(0xffffffffu, xa, o), yb = __shfl_up_sync(0xffffffffu, xb, o);
+      if (lane >= o) { xa += ya; xb += yb; }
+    }
+    if (lane == 31) { s_red[tid >> 5] = xa; s_red2[tid >> 5] = xb; }
+    fold_bar();
+    uint32_t tot_a = 0, tot_b = 0, pre_a = 0, pre_b = 0;
+#pragma unroll
+    for (int w = 0; w < kFoldThreads / 32; w++) {
+      const uint32_t ra = s_red[w], rb = s_red2[w];
+      if (w < (tid >> 5)) { pre_a += ra; pre_b += rb; }
+      tot_a += ra; tot_b += rb;
+    }
+    const uint32_t tot = tot_a + tot_b;
+    const bool as_list = p.sparse_out && tot <= kSparseListMax;
+    if (as_list) {
+      uint16_t* lst = p.sparse_out + m.item * kSparseListMax;
+      uint32_t ia = pre_a + xa - ca, ib = tot_a + pre_b + xb - cb;
+      const uint32_t wa[4] = {a.x, a.y, a.z, a.w}, wb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        for (uint32_t v = wa[k]; v; v &= v - 1) lst[ia++] = uint16_t((4 * tid + k) * 32 + __ffs(v) - 1);
+        for (uint32_t v = wb[k]; v; v &= v - 1) lst[ib++] = uint16_t((4 * (tid + kFoldThreads) + k) * 32 + __ffs(v) - 1);
+      }
+    } else if (p.dense_out) {
+      uint4* dout = reinterpret_cast<uint4*>(p.dense_out + m.item * kBitmapBytes);
+      dout[tid] = a; dout[tid + kFoldThreads] = b;
+    }
+    if (tid == 0) {
       if (p.out_counts && tot) atomicAdd(p.out_counts + uint64_t(m.q) * p.out_qstride + uint64_t(m.s) * p.out_sstride, (unsigned long long)tot);
-      if (p.dense_n) p.dense_n[m.item] = tot;
+      p.dense_n[m.item] = as_list ? (tot | kSparseFlag) : tot;
       mbar_arrive(&s_mempty[ms]);  // the item's descriptors are no longer needed
     }
     fold_bar();  // s_red and the window are free for the next item

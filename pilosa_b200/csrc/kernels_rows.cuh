@@ -240,8 +240,8 @@ __device__ __forceinline__ uint8_t* put_varint(uint8_t* p, uint64_t x) {
 
 // A warp per slot: bytes its columns take as varints.
 __global__ void __launch_bounds__(kProtoThreads) proto_size_kernel(const uint64_t* __restrict__ dense, const uint32_t* __restrict__ dense_n,
-                                                                   const uint64_t* __restrict__ shards, const unsigned long long* __restrict__ ovf,
-                                                                   uint32_t n_shards, uint32_t* __restrict__ sizes) {
+                                                                   const uint16_t* __restrict__ sparse, const uint64_t* __restrict__ shards,
+                                                                   const unsigned long long* __restrict__ ovf, uint32_t n_shards, uint32_t* __restrict__ sizes) {
   const uint32_t lane = threadIdx.x & 31, n_slots = n_shards * kProtoSlots;
   const uint32_t warps = gridDim.x * (kProtoThreads / 32);
   for (uint32_t slot = blockIdx.x * (kProtoThreads / 32) + (threadIdx.x >> 5); slot < n_slots; slot += warps) {
@@ -252,9 +252,12 @@ __global__ void __launch_bounds__(kProtoThreads) proto_size_kernel(const uint64_
         for (unsigned long long v = ovf[s]; v; v &= v - 1) bytes += varint_len(((shards[s] + 1) << 20) + uint32_t(__ffsll((long long)v) - 1));
     } else {
       const uint32_t item = s * kRowContainers + c;
-      if (dense_n[item]) {
+      const uint32_t dn = dense_n[item];
+      const uint64_t base = (shards[s] << 20) + (uint64_t(c) << 16);
+      if (dn & kSparseFlag) {  // a short result kept as a value list: one value per lane
+        if (lane < (dn & ~kSparseFlag)) bytes = varint_len(base + sparse[size_t(item) * kSparseListMax + lane]);
+      } else if (dn) {
         const uint64_t* w = dense + size_t(item) * kBitmapWords;
-        const uint64_t base = (shards[s] << 20) + (uint64_t(c) << 16);
         for (uint32_t i = lane; i < kBitmapWords; i += 32) bytes += uint32_t(__popcll(w[i])) * varint_len(base + i * 64);
       }
     }
@@ -265,43 +268,41 @@ __global__ void __launch_bounds__(kProtoThreads) proto_size_kernel(const uint64_
 
 // One CTA: exclusive scan of the slot sizes (payload-relative offsets); totals[0] = message length
 // (0 for an empty row: the field is omitted), totals[1] = length of tag + length prefix.
+// Every thread sums a contiguous chunk of slots, the 1024 chunk sums are scanned once, and a second walk over the
+// chunk writes the offsets: two barriers whatever the number of slots (139 264 for 8192 shards).
 __global__ void __launch_bounds__(1024) proto_layout_kernel(const uint32_t* __restrict__ sizes, uint32_t n_slots,
                                                             unsigned long long* __restrict__ slot_off, unsigned long long* __restrict__ totals) {
   __shared__ unsigned long long warp_tot[32];
-  __shared__ unsigned long long running;
   const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  if (threadIdx.x == 0) running = 0;
+  const uint32_t per = (n_slots + 1023) / 1024;
+  const uint32_t b = min(n_slots, threadIdx.x * per), e = min(n_slots, b + per);
+  unsigned long long mine = 0;
+  for (uint32_t i = b; i < e; i++) mine += sizes[i];
+  unsigned long long x = mine;
+  #pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+  if (lane == 31) warp_tot[wid] = x;
   __syncthreads();
-  for (uint32_t base = 0; base < n_slots; base += 1024) {
-    const uint32_t i = base + threadIdx.x;
-    const unsigned long long size = i < n_slots ? sizes[i] : 0ull;
-    unsigned long long x = size;
+  if (wid == 0) {
+    unsigned long long t = warp_tot[lane], z = t;
     #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-    if (lane == 31) warp_tot[wid] = x;
-    __syncthreads();
-    if (wid == 0) {
-      unsigned long long t = warp_tot[lane], z = t;
-      #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, z, o); if (lane >= o) z += y; }
-      warp_tot[lane] = z - t;
+    for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, z, o); if (lane >= o) z += y; }
+    warp_tot[lane] = z - t;
+    if (lane == 31) {
+      const unsigned long long payload = z;
+      const unsigned long long hdr = payload ? 1ull + varint_len(payload) : 0ull;
+      totals[0] = hdr + payload;
+      totals[1] = hdr;
     }
-    __syncthreads();
-    if (i < n_slots) slot_off[i] = running + warp_tot[wid] + x - size;
-    __syncthreads();
-    if (threadIdx.x == 1023) running += warp_tot[31] + x;
-    __syncthreads();
   }
-  if (threadIdx.x == 0) {
-    const unsigned long long payload = running;
-    const unsigned long long hdr = payload ? 1ull + varint_len(payload) : 0ull;
-    totals[0] = hdr + payload;
-    totals[1] = hdr;
-  }
+  __syncthreads();
+  unsigned long long run = warp_tot[wid] + x - mine;
+  for (uint32_t i = b; i < e; i++) { slot_off[i] = run; run += sizes[i]; }
 }
 
 // A CTA per slot: thread t owns words 4t .. 4t+3 of the container, a block scan places its bytes.
-__global__ void __launch_bounds__(kProtoThreads) proto_emit_kernel(const uint64_t* __restrict__ dense, const uint32_t* __restrict__ sizes,
+__global__ void __launch_bounds__(kProtoThreads) proto_emit_kernel(const uint64_t* __restrict__ dense, const uint32_t* __restrict__ dense_n,
+                                                                   const uint16_t* __restrict__ sparse, const uint32_t* __restrict__ sizes,
                                                                    const unsigned long long* __restrict__ slot_off,
                                                                    const unsigned long long* __restrict__ totals, const uint64_t* __restrict__ shards,
                                                                    const unsigned long long* __restrict__ ovf, uint32_t n_shards,
@@ -310,15 +311,30 @@ __global__ void __launch_bounds__(kProtoThreads) proto_emit_kernel(const uint64_
   const uint32_t t = threadIdx.x, lane = t & 31, wid = t >> 5, n_slots = n_shards * kProtoSlots;
   const unsigned long long hdr = totals[1];
   if (blockIdx.x == 0 && t == 0 && hdr) { out[0] = 0x0a; put_varint(out + 1, totals[0] - hdr); }
-  for (uint32_t slot = blockIdx.x; slot < n_slots; slot += gridDim.x) {
-    if (sizes[slot] == 0) continue;  // uniform over the CTA
+  // value lists and Shift overflow words: a warp per slot (a sparse row over thousands of shards is nothing but these)
+  for (uint32_t slot = blockIdx.x * (kProtoThreads / 32) + wid; slot < n_slots; slot += gridDim.x * (kProtoThreads / 32)) {
+    if (sizes[slot] == 0) continue;
     const uint32_t s = slot / kProtoSlots, c = slot % kProtoSlots;
     uint8_t* dst = out + hdr + slot_off[slot];
     if (c == kRowContainers) {
-      if (t == 0)
+      if (lane == 0)
         for (unsigned long long v = ovf[s]; v; v &= v - 1) dst = put_varint(dst, ((shards[s] + 1) << 20) + uint32_t(__ffsll((long long)v) - 1));
       continue;
     }
+    const uint32_t dn = dense_n[s * kRowContainers + c];
+    if (!(dn & kSparseFlag)) continue;
+    const uint64_t col = (shards[s] << 20) + (uint64_t(c) << 16) + (lane < (dn & ~kSparseFlag) ? sparse[(size_t(s) * kRowContainers + c) * kSparseListMax + lane] : 0u);
+    const uint32_t len = lane < (dn & ~kSparseFlag) ? varint_len(col) : 0u;
+    uint32_t x = len;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (len) put_varint(dst + x - len, col);
+  }
+  // containers kept as words: a CTA per slot
+  for (uint32_t slot = blockIdx.x; slot < n_slots; slot += gridDim.x) {
+    const uint32_t s = slot / kProtoSlots, c = slot % kProtoSlots;
+    if (c == kRowContainers || sizes[slot] == 0 || (dense_n[s * kRowContainers + c] & kSparseFlag)) continue;  // uniform over the CTA
+    uint8_t* dst = out + hdr + slot_off[slot];
     const uint64_t* w = dense + (size_t(s) * kRowContainers + c) * kBitmapWords + 4 * t;
     const uint64_t base = (shards[s] << 20) + (uint64_t(c) << 16) + uint64_t(4 * t) * 64;
     uint64_t word[4];

@@ -96,6 +96,7 @@ def load_library() -> C.CDLL:
         "pb200_bsi_minmax_shards": (i32, [vp, u32, u32, np_, u32, i32, u64p, u32, i64p, u64p]),
         "pb200_last_timing": (i32, [vp, C.POINTER(Timing)]),
         "pb200_reserve": (i32, [vp, u32, u32, u32]),
+        "pb200_combine_stats": (i32, [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
         "pb200_peer_export": (i32, [vp, C.c_char_p]),
         "pb200_peer_connect": (i32, [vp, i32, i32, C.c_char_p]),
         "pb200_peer_flush": (i32, [vp]),
@@ -322,6 +323,12 @@ class Engine:
     def reserve(self, max_queries: int, max_shards: int, max_nodes_per_query: int = 3) -> None:
         """Pre-size the scratch of the Count paths so that serving never allocates (pb200_reserve)."""
         self._check(self.lib.pb200_reserve(self._h, max_queries, max_shards, max_nodes_per_query))
+
+    def combine_stats(self):
+        """(combined launches, single-query calls they served) of pb200_count's combining queue."""
+        a, b = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.pb200_combine_stats(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def peer_export(self) -> bytes:
         buf = C.create_string_buffer(self.PEER_HANDLE_BYTES)

@@ -496,7 +496,7 @@ def test_lane_per_item_pass_on_very_sparse_rows(eng_orc):
 
     eng, orc = eng_orc
     g, c = Executor(eng), Executor(orc)
-    shards = list(range(40))
+    shards = list(range(700))   # x 16 containers: more items than the device holds warps, or the pass is not used for a single call
     for ex in (g, c):
         ex.create_field("sp")
         ex.create_field("md")
@@ -512,8 +512,41 @@ def test_lane_per_item_pass_on_very_sparse_rows(eng_orc):
     for call in calls:
         assert g.count(call, shards) == c.count(call, shards), repr(call)
         assert g.be.count_shards(g.program(call), shards) == c.be.count_shards(c.program(call), shards), repr(call)
-    assert g.count_batch(calls * 3, shards) == c.count_batch(calls * 3, shards)
+    assert g.count_batch(calls * 3, shards[:60]) == c.count_batch(calls * 3, shards[:60])
     assert g.count_batch(calls, shards[5:6]) == c.count_batch(calls, shards[5:6])
     # self-consistency on every shard: |A| + |B| = |A or B| + |A and B|
     n = {k: g.count(x, shards) for k, x in dict(a=A, b=B, u=Union(A, B), i=Intersect(A, B), x=Xor(A, B), d=Difference(A, B)).items()}
     assert n["a"] + n["b"] == n["u"] + n["i"] and n["x"] == n["u"] - n["i"] and n["d"] == n["a"] - n["i"]
+
+
+def test_proto_columns_of_short_containers_as_value_lists(eng_orc):
+    """K12 over results whose containers hold 0, 1, 31, 32 (kept as 64-byte value lists) and 33, 40, 5000 values (kept
+    as words), side by side in one shard and across shards, for plain rows and for folds: the Columns field against the
+    oracle's, byte for byte."""
+    from pilosa_b200.abi import Difference, Union, Xor
+
+    eng, orc = eng_orc
+    g, c = Executor(eng), Executor(orc)
+    rnd = __import__("random").Random(9)
+    sizes = [0, 1, 31, 32, 33, 40, 5000, 2, 32, 33, 7, 0, 31, 64, 3, 65536]
+    for ex in (g, c):
+        ex.create_field("l")
+    for shard in (0, 3, 4, 9):
+        cs = []
+        for row in range(3):
+            for col, n in enumerate(sizes):
+                n = (n + row * 5) % 65537 if n not in (0, 65536) else n
+                if n == 0:
+                    continue
+                vals = list(range(65536)) if n == 65536 else sorted(rnd.sample(range(65536), n))
+                t, nn, pl = _cont("a" if n <= 4096 else "b", vals)
+                cs.append((row * 16 + col, t, nn, pl))
+        data = pilosa_file(sorted(cs))
+        for ex in (g, c):
+            ex.load_fragment("l", shard, data)
+    shards = [0, 3, 4, 5, 9]
+    R = lambda i: Row("l", i)  # noqa: E731
+    for call in (R(0), R(1), R(2), R(7), Intersect(R(0), R(1)), Union(R(0), R(1), R(2)), Xor(R(0), R(2)), Difference(R(1), R(0))):
+        assert g.row_proto_columns(call, shards) == c.be.eval_proto_columns(c.program(call), shards), repr(call)
+        assert g.row_proto_columns(call, shards[1:2]) == c.be.eval_proto_columns(c.program(call), shards[1:2]), repr(call)
+        assert g.row_columns(call, shards) == c.row_columns(call, shards), repr(call)
