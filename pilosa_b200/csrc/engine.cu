@@ -667,7 +667,7 @@ namespace {
 struct TNode {
   uint32_t op = 0;  // pb200_op of an n-ary node, or 0 for a leaf, or PB200_OP_NOT
   int leaf = -1;    // leaf index (leaf nodes; NOT: the existence leaf)
-  std::vector<int> kids;
+  uint32_t kid0 = 0, n_kids = 0;  // children: Compiler::kid_pool[kid0 .. kid0 + n_kids) — no allocation per node
 };
 
 constexpr uint32_t kOpInternalTemp = 0x100;  // leaf = dense temp row slot `row`; engine-internal (GroupBy), refused from the C ABI
@@ -678,9 +678,14 @@ struct Compiler {
   bool internal_ok = false;
   uint32_t leaf_base = 0;
   std::vector<TNode> tree;
+  std::vector<int> kid_pool;      // children of the n-ary nodes of the call being compiled
+  std::vector<int> st;            // operand stack of compile_once ...
+  std::vector<Instr> ins_buf;     // ... and the instruction list of finish: reused from call to call of a batch
   std::string err;
 
   Compiler(pb200_ctx* c, Compiled& o) : ctx(c), out(o) {}
+  int kid(const TNode& t, size_t k) const { return kid_pool[t.kid0 + k]; }
+  void set_kids(TNode& t, const int* b, const int* e2) { t.kid0 = uint32_t(kid_pool.size()); t.n_kids = uint32_t(e2 - b); kid_pool.insert(kid_pool.end(), b, e2); }
 
   int add_leaf(uint32_t kind, uint32_t family, uint64_t row) {
     Leaf lf; lf.kind = kind; lf.family = family; lf.row = row;
@@ -698,7 +703,7 @@ struct Compiler {
   void emit(int n, std::vector<Instr>& ins) {
     const TNode& t = tree[n];
     if (t.op == 0) { ins.push_back({I_LOAD, uint8_t(t.leaf)}); return; }
-    if (t.op == PB200_OP_NOT) { emit(t.kids[0], ins); ins.push_back({I_RANDNOT_LEAF, uint8_t(t.leaf)}); return; }
+    if (t.op == PB200_OP_NOT) { emit(kid(t, 0), ins); ins.push_back({I_RANDNOT_LEAF, uint8_t(t.leaf)}); return; }
     uint8_t lop, sop;
     switch (t.op) {
       case PB200_OP_INTERSECT: lop = I_AND_LEAF; sop = I_AND_STACK; break;
@@ -706,17 +711,18 @@ struct Compiler {
       case PB200_OP_XOR: lop = I_XOR_LEAF; sop = I_XOR_STACK; break;
       default: lop = I_ANDNOT_LEAF; sop = I_ANDNOT_STACK; break;
     }
-    emit(t.kids[0], ins);
-    for (size_t k = 1; k < t.kids.size(); k++) {
-      const TNode& ch = tree[t.kids[k]];
+    emit(kid(t, 0), ins);
+    for (size_t k = 1; k < t.n_kids; k++) {
+      const TNode& ch = tree[kid(t, k)];
       if (ch.op == 0) ins.push_back({lop, uint8_t(ch.leaf)});
-      else { emit(t.kids[k], ins); ins.push_back({sop, 0}); }
+      else { emit(kid(t, k), ins); ins.push_back({sop, 0}); }
     }
   }
 
   // Emits the program of subtree `root` as a new Prog; returns false on limits.
   bool finish(int root, Prog& pg) {
-    std::vector<Instr> ins;
+    std::vector<Instr>& ins = ins_buf;
+    ins.clear();
     emit(root, ins);
     int sp = 0, maxsp = 0; bool live = false;
     for (auto& i : ins) {
@@ -801,9 +807,10 @@ struct Compiler {
     }
     if (lead == 0 && temps.size() == 1) { st.push_back(temps[0]); return true; }
     TNode t; t.op = nd.op;
-    t.kids.assign(st.end() - lead, st.end());
+    std::vector<int> ks(st.end() - lead, st.end());
     st.resize(st.size() - lead);
-    t.kids.insert(t.kids.end(), temps.begin(), temps.end());
+    ks.insert(ks.end(), temps.begin(), temps.end());
+    set_kids(t, ks.data(), ks.data() + ks.size());
     tree.push_back(t);
     st.push_back(int(tree.size() - 1));
     return true;
@@ -814,7 +821,8 @@ struct Compiler {
     leaf_base = uint32_t(out.leaves.size());
     pre_base = out.pre.size();
     tree.clear();
-    std::vector<int> st;
+    kid_pool.clear();
+    st.clear();
     uint32_t n_shifts = 0;
     for (uint32_t k = 0; k < n; k++) {
       const pb200_node& nd = nodes[k];
@@ -848,7 +856,7 @@ struct Compiler {
           if (nd.nargs == 1) break;  // identity
           if (split_min && nd.nargs >= split_min && wide_split(nd, st)) break;
           TNode t; t.op = nd.op;
-          t.kids.assign(st.end() - nd.nargs, st.end());
+          set_kids(t, st.data() + (st.size() - nd.nargs), st.data() + st.size());
           st.resize(st.size() - nd.nargs);
           tree.push_back(t);
           st.push_back(int(tree.size() - 1));
@@ -857,7 +865,8 @@ struct Compiler {
         case PB200_OP_NOT: {
           if (st.empty()) { err = "Not() requires an input row"; return false; }  // executor.go:1741
           if (nd.family >= ctx->families.size()) { err = "index does not support existence tracking"; return false; }
-          TNode t; t.op = PB200_OP_NOT; t.kids = {st.back()}; t.leaf = add_leaf(L_ROW, nd.family, 0);
+          TNode t; t.op = PB200_OP_NOT; t.leaf = add_leaf(L_ROW, nd.family, 0);
+          set_kids(t, &st.back(), &st.back() + 1);
           st.pop_back();
           tree.push_back(t);
           st.push_back(int(tree.size() - 1));
@@ -1257,6 +1266,10 @@ int count_impl(pb200_ctx* ctx, const pb200_node* progs, const uint32_t* prog_off
 namespace {
 
 constexpr size_t kCombineMax = 1024;
+#ifndef PB200_GATHER_US
+#define PB200_GATHER_US 12
+#endif
+constexpr int kGatherMaxUs = PB200_GATHER_US;  // longest wait for the callers of the last round
 
 void run_count_group(pb200_ctx* ctx, std::vector<CountReq*>& grp) {
   std::lock_guard<std::mutex> lock(ctx->mu);
@@ -1292,23 +1305,33 @@ void run_count_group(pb200_ctx* ctx, std::vector<CountReq*>& grp) {
 }
 
 int combine_counts(pb200_ctx* ctx, CountReq& me) {
-  std::unique_lock<std::mutex> lk(ctx->cq_mu);
-  ctx->cq.push_back(&me);
+  // file the request: one compare-and-swap, no lock (callers re-entering together would queue up on a mutex)
+  ctx->cq_n.fetch_add(1, std::memory_order_relaxed);  // (before the push: the count never runs behind the list)
+  me.next = ctx->cq_head.load(std::memory_order_relaxed);
+  while (!ctx->cq_head.compare_exchange_weak(me.next, &me, std::memory_order_release, std::memory_order_relaxed)) {}
   while (!me.done.load(std::memory_order_acquire)) {
-    if (!ctx->cq_busy.load(std::memory_order_relaxed)) {
-      ctx->cq_busy.store(true, std::memory_order_relaxed);  // this thread combines until its own request has been served; a waiting thread takes over then
-      while (!me.done.load(std::memory_order_relaxed) && !ctx->cq.empty()) {
+    if (!ctx->cq_busy.load(std::memory_order_relaxed) && !ctx->cq_busy.exchange(true, std::memory_order_acquire)) {
+      // this thread combines until its own request has been served; a waiting thread takes over then
+      while (!me.done.load(std::memory_order_relaxed)) {
         // The callers of the last round are on their way back with their next request: when that round was a batch, give
-        // them a few microseconds to arrive so that this launch is as wide (a lone caller never waits: last round = 1).
-        if (ctx->cq_last > 1 && ctx->cq.size() < ctx->cq_last) {
-          lk.unlock();
+        // them up to 12 us to arrive so that this launch is as wide — until as many requests wait as callers were seen
+        // in and during the last round (the ones it served plus the ones that arrived meanwhile: counting only the
+        // former lets the callers settle into two cohorts that alternate, each launch half as wide). A lone caller
+        // never waits: last round = 1.
+        if (ctx->cq_last > 1 && ctx->cq_n.load(std::memory_order_relaxed) < ctx->cq_target) {
           const auto t0 = std::chrono::steady_clock::now();
           for (int i = 0; i < 4000; i++) {
-            if ((i & 15) == 15 && std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(12)) break;
+            if ((i & 7) == 7 && (ctx->cq_n.load(std::memory_order_relaxed) >= ctx->cq_target ||
+                                 std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(kGatherMaxUs))) break;
             __builtin_ia32_pause();
           }
-          lk.lock();
         }
+        // take the arrivals (newest first) and put them behind what earlier rounds left over, oldest first
+        CountReq* lst = ctx->cq_head.exchange(nullptr, std::memory_order_acquire);
+        const size_t old = ctx->cq.size();
+        for (CountReq* r = lst; r; r = r->next) ctx->cq.push_back(r);
+        std::reverse(ctx->cq.begin() + old, ctx->cq.end());
+        if (ctx->cq.empty()) break;  // (cannot happen while this thread's own request is unserved)
         std::vector<CountReq*> grp, rest;
         CountReq* head = ctx->cq.front();
         for (CountReq* r : ctx->cq) {
@@ -1318,28 +1341,34 @@ int combine_counts(pb200_ctx* ctx, CountReq& me) {
         }
         ctx->cq.swap(rest);
         ctx->cq_last = grp.size();
-        lk.unlock();
+        ctx->cq_n.fetch_sub(grp.size(), std::memory_order_relaxed);  // cq_n: requests filed and not yet launched
         run_count_group(ctx, grp);
-        lk.lock();
+        ctx->cq_target = grp.size() + ctx->cq_n.load(std::memory_order_relaxed);
         for (CountReq* r : grp) r->done.store(true, std::memory_order_release);  // last access to r: its owner may return now
+        if (ctx->cq_sleepers.load(std::memory_order_acquire)) { std::lock_guard<std::mutex> lk(ctx->cq_mu); ctx->cq_cv.notify_all(); }
       }
       ctx->cq_busy.store(false, std::memory_order_release);
-      ctx->cq_cv.notify_all();
+      // a caller that sleeps may have been served, or may have to take over
+      if (ctx->cq_sleepers.load(std::memory_order_acquire)) { std::lock_guard<std::mutex> lk(ctx->cq_mu); ctx->cq_cv.notify_all(); }
       continue;
     }
     // Somebody else is combining. A launch takes tens of microseconds: spin that long before sleeping — a futex wake-up
     // costs as much as the launch and would leave the GPU idle between rounds.
-    lk.unlock();
     bool progress = false;
-    for (int i = 0; i < 3000 && !progress; i++) {
+    const auto s0 = std::chrono::steady_clock::now();
+    for (int i = 0; !progress; i++) {
       progress = me.done.load(std::memory_order_acquire) || !ctx->cq_busy.load(std::memory_order_acquire);
-      if (!progress) __builtin_ia32_pause();
+      if (progress || ((i & 63) == 63 && std::chrono::steady_clock::now() - s0 > std::chrono::microseconds(150))) break;
+      __builtin_ia32_pause();
     }
-    lk.lock();
-    if (!progress && !me.done.load(std::memory_order_acquire) && ctx->cq_busy.load(std::memory_order_relaxed))
-      ctx->cq_cv.wait_for(lk, std::chrono::microseconds(200));
+    if (!progress) {
+      std::unique_lock<std::mutex> lk(ctx->cq_mu);
+      ctx->cq_sleepers.fetch_add(1, std::memory_order_acq_rel);
+      if (!me.done.load(std::memory_order_acquire) && ctx->cq_busy.load(std::memory_order_acquire))
+        ctx->cq_cv.wait_for(lk, std::chrono::microseconds(200));
+      ctx->cq_sleepers.fetch_sub(1, std::memory_order_acq_rel);
+    }
   }
-  lk.unlock();
   if (me.rc != PB200_OK) { std::lock_guard<std::mutex> lock(ctx->mu); ctx->err = me.err; }
   return me.rc;
 }

@@ -119,6 +119,7 @@ struct CountReq {
   const uint64_t* shards; uint32_t n_shards;
   uint64_t* out;
   int rc = 0;
+  CountReq* next = nullptr;  // arrival list (newest first), linked with one compare-and-swap per caller
   std::atomic<bool> done{false};
   std::string err;
 };
@@ -142,9 +143,13 @@ struct pb200_ctx {
   // combining queue of pb200_count: threads that arrive while a launch is in flight are folded into the next batch
   std::mutex cq_mu;
   std::condition_variable cq_cv;
-  std::vector<pb200::CountReq*> cq;
+  std::atomic<pb200::CountReq*> cq_head{nullptr};  // arrivals: pushed lock-free by the callers, taken whole by the combiner
+  std::vector<pb200::CountReq*> cq;                // taken, not yet served; owned by whoever holds cq_busy (cq_mu: only for callers that sleep)
   std::atomic<bool> cq_busy{false};
   size_t cq_last = 0;  // requests in the last round
+  size_t cq_target = 0;               // ... plus the ones that arrived during it: the callers the next round waits for
+  std::atomic<size_t> cq_n{0};        // requests filed and not yet launched
+  std::atomic<int> cq_sleepers{0};    // callers that gave up spinning and wait on cq_cv
   uint64_t cq_batches = 0, cq_queries = 0;  // statistics: launches made for how many single-query calls
   int sm_count = 148;
   size_t budget = 0, used = 0;
