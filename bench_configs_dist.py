@@ -122,8 +122,9 @@ def main():
             sh_arr = abi.u64_array(sh)
             run("C5", f"batch of 256 x same query, {k} shards (whole batch)", lambda: list(eng.count_batch_raw(flat, off, 256, sh_arr, len(sh))[:2]), sh)
         # a materialised sparse row over all shards: owners evaluate, the first device gathers and emits the protobuf Columns field
-        run("C5", f"Row(sp=1) as protobuf Columns, {len(shards)} shards", lambda: g.row_proto_columns(Row("sp", 1), shards), shards, 3,
-            show=lambda b: {"bytes": len(b), "crc32": zlib.crc32(b)})
+        prog_row, sh_all = g.program(Row("sp", 1)), abi.u64_array(shards)   # marshalled once; the message lands in a reused page-locked buffer
+        run("C5", f"Row(sp=1) as protobuf Columns, {len(shards)} shards", lambda: eng.eval_proto_columns_raw(prog_row, sh_all), shards, 5,
+            show=lambda r: {"bytes": r[1], "crc32": zlib.crc32(C.string_at(r[0], r[1]))})
     eng.close()
 
 

@@ -35,7 +35,7 @@ struct pb200_multi {
   uint32_t small_call_shards = 1024;                // ... provided queries x shards is no more than this
   std::vector<FamStat> fam;
   pb200_timing timing{};
-  DevBuf g_dense, g_dense_n, g_ovf, g_shards, g_pos;  // on ctx[0]'s device: gathered result rows of a bitmap-returning call
+  DevBuf g_dense, g_dense_n, g_sparse, g_ovf, g_shards, g_pos;  // on ctx[0]'s device: gathered result rows of a bitmap-returning call
   std::vector<cudaEvent_t> ev;                      // per device: "dense rows ready"
 };
 
@@ -210,18 +210,30 @@ int count_batch_multi(pb200_multi* m, const pb200_node* progs, const uint32_t* p
   return PB200_OK;
 }
 
-// strided copy of dense result rows from an owner's buffers (peer memory) into the gathered buffers of device 0
-__global__ void gather_rows_kernel(const uint4* __restrict__ src, const uint32_t* __restrict__ src_n, const unsigned long long* __restrict__ src_ovf,
-                                   const uint32_t* __restrict__ pos, uint32_t n_local, uint4* __restrict__ dst, uint32_t* __restrict__ dst_n,
+// Copy of the result rows of an owner (peer memory, plain loads) into the gathered buffers of device 0, a warp per
+// container: 8 KiB of words, or — when the owner kept a short container as a value list (src_sparse given) — its 64
+// bytes; with lists on, empty containers move nothing.
+__global__ void gather_rows_kernel(const uint4* __restrict__ src, const uint32_t* __restrict__ src_n, const uint4* __restrict__ src_sparse,
+                                   const unsigned long long* __restrict__ src_ovf, const uint32_t* __restrict__ pos, uint32_t n_local,
+                                   uint4* __restrict__ dst, uint32_t* __restrict__ dst_n, uint4* __restrict__ dst_sparse,
                                    unsigned long long* __restrict__ dst_ovf) {
-  constexpr uint32_t kRowVec = kRowContainers * kBitmapBytes / 16;  // uint4 per dense row
-  const uint64_t total = uint64_t(n_local) * kRowVec;
-  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += uint64_t(gridDim.x) * blockDim.x) {
-    const uint32_t r = uint32_t(i / kRowVec), k = uint32_t(i % kRowVec);
-    dst[uint64_t(pos[r]) * kRowVec + k] = src[i];
+  constexpr uint32_t kVec = kBitmapBytes / 16;              // uint4 per container
+  constexpr uint32_t kListVec = kSparseListMax * 2 / 16;    // uint4 per value list
+  const uint32_t lane = threadIdx.x & 31, warps = gridDim.x * (blockDim.x >> 5);
+  const uint32_t n_items = n_local * kRowContainers;
+  for (uint32_t item = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); item < n_items; item += warps) {
+    const uint32_t dn = src_n[item];
+    const uint32_t to = pos[item / kRowContainers] * kRowContainers + item % kRowContainers;
+    if (src_sparse && (dn & kSparseFlag)) {
+      if (lane < kListVec) dst_sparse[size_t(to) * kListVec + lane] = src_sparse[size_t(item) * kListVec + lane];
+    } else if (dn || !src_sparse) {
+      const uint4* f = src + size_t(item) * kVec;
+      uint4* t = dst + size_t(to) * kVec;
+#pragma unroll 4
+      for (uint32_t k = lane; k < kVec; k += 32) t[k] = f[k];
+    }
+    if (lane == 0) dst_n[to] = dn;
   }
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_local * kRowContainers; i += gridDim.x * blockDim.x)
-    dst_n[pos[i / kRowContainers] * kRowContainers + i % kRowContainers] = src_n[i];
   if (dst_ovf)
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_local; i += gridDim.x * blockDim.x) dst_ovf[pos[i]] = src_ovf ? src_ovf[i] : 0ull;
 }
@@ -229,7 +241,8 @@ __global__ void gather_rows_kernel(const uint4* __restrict__ src, const uint32_t
 // Owners evaluate the call into dense rows; device 0 pulls them together in the caller's shard order and is left
 // with ctx[0]->d_dense / d_dense_n / overflow words describing ALL n_shards rows, shard numbers at *shards_dev.
 // On return ctx[0]'s mutex is NOT held; the caller re-enters ctx[0] for the emission.
-int gather_dense(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards, const uint64_t** shards_dev) {
+int gather_dense(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const uint64_t* shards, uint32_t n_shards, const uint64_t** shards_dev,
+                 bool allow_lists = false) {
   if (!m->peer && m->ctx.size() > 1) return mfail(m, PB200_ERR_UNSUPPORTED, "bitmap-returning multi-GPU calls need peer access between the devices");
   const ShardSplit sp = split_shards(m, shards, n_shards);
   const std::vector<uint8_t> active = active_of(sp);
@@ -245,7 +258,7 @@ int gather_dense(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const
     timing_begin(c);
     CUDA_TRY(c, cudaEventRecord(c->ev0, c->stream));
     BatchDev bd{};
-    TRY(eval_dense(c, prog, n_nodes, sp.shards[d].data(), uint32_t(sp.shards[d].size()), bd));
+    TRY(eval_dense(c, prog, n_nodes, sp.shards[d].data(), uint32_t(sp.shards[d].size()), bd, allow_lists));
     CUDA_TRY(c, cudaEventRecord(c->ev1, c->stream));
     has_ovf[d] = c->dense_has_ovf ? 1 : 0;
     CUDA_TRY(c, cudaEventRecord(m->ev[d], c->stream));
@@ -272,6 +285,8 @@ int gather_dense(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const
   }
   int rc = ensure0(m->g_dense, items * kBitmapBytes);
   if (rc == PB200_OK) rc = ensure0(m->g_dense_n, items * 4);
+  const bool lists = allow_lists && !any_ovf;  // (a program property: every owner decided the same)
+  if (rc == PB200_OK && lists) rc = ensure0(m->g_sparse, items * kSparseListMax * 2);
   if (rc == PB200_OK) rc = ensure0(m->g_ovf, size_t(n_shards) * 8);
   if (rc == PB200_OK) rc = ensure0(m->g_shards, size_t(n_shards) * 8);
   if (rc == PB200_OK) rc = ensure0(m->g_pos, size_t(n_shards) * 4);
@@ -289,17 +304,19 @@ int gather_dense(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const
     pb200_ctx* c = m->ctx[d];
     const uint32_t nl = uint32_t(sp.shards[d].size());
     if (cudaStreamWaitEvent(c0->stream, m->ev[d], 0) != cudaSuccess) return fail0(fail(c0, PB200_ERR_CUDA, "cudaStreamWaitEvent failed"));
-    const uint64_t vecs = uint64_t(nl) * kRowContainers * kBitmapBytes / 16;
-    const uint32_t grid = uint32_t(std::min<uint64_t>((vecs + 255) / 256, uint64_t(c0->sm_count) * 8));
+    const uint64_t warps = uint64_t(nl) * kRowContainers;
+    const uint32_t grid = uint32_t(std::min<uint64_t>((warps + 7) / 8, uint64_t(c0->sm_count) * 8));
     gather_rows_kernel<<<grid, 256, 0, c0->stream>>>(static_cast<const uint4*>(c->d_dense.p), static_cast<const uint32_t*>(c->d_dense_n.p),
+                                                     lists ? static_cast<const uint4*>(c->d_sparse.p) : nullptr,
                                                      has_ovf[d] ? c->dense_ovf_dev : nullptr, static_cast<const uint32_t*>(m->g_pos.p) + pos_off[d], nl,
                                                      static_cast<uint4*>(m->g_dense.p), static_cast<uint32_t*>(m->g_dense_n.p),
+                                                     lists ? static_cast<uint4*>(m->g_sparse.p) : nullptr,
                                                      any_ovf ? static_cast<unsigned long long*>(m->g_ovf.p) : nullptr);
   }
   if (cudaGetLastError() != cudaSuccess) return fail0(fail(c0, PB200_ERR_CUDA, "gather launch failed"));
   *shards_dev = static_cast<const uint64_t*>(m->g_shards.p);
   c0->dense_has_ovf = any_ovf;
-  c0->dense_lists = false;  // gathered rows are words throughout
+  c0->dense_lists = lists;
   c0->dense_ovf_dev = static_cast<unsigned long long*>(m->g_ovf.p);
   timing_merge(m, active);
   return PB200_OK;
@@ -308,8 +325,9 @@ int gather_dense(pb200_multi* m, const pb200_node* prog, uint32_t n_nodes, const
 // The gathered rows take the place of ctx[0]'s own dense buffers for the duration of the emission.
 struct GatherSwap {
   pb200_multi* m;
-  explicit GatherSwap(pb200_multi* mm) : m(mm) { std::swap(m->ctx[0]->d_dense, m->g_dense); std::swap(m->ctx[0]->d_dense_n, m->g_dense_n); }
-  ~GatherSwap() { std::swap(m->ctx[0]->d_dense, m->g_dense); std::swap(m->ctx[0]->d_dense_n, m->g_dense_n); }
+  explicit GatherSwap(pb200_multi* mm) : m(mm) { swap(); }
+  ~GatherSwap() { swap(); }
+  void swap() { std::swap(m->ctx[0]->d_dense, m->g_dense); std::swap(m->ctx[0]->d_dense_n, m->g_dense_n); std::swap(m->ctx[0]->d_sparse, m->g_sparse); }
 };
 
 }  // namespace
@@ -380,7 +398,7 @@ extern "C" int pb200_multi_shutdown(pb200_multi* m) {
     for (pb200_ctx* c : m->ctx) { DeviceGuard g(c->device); cudaStreamSynchronize(c->stream); }
     {
       DeviceGuard g(m->ctx[0]->device);
-      for (DevBuf* b : {&m->g_dense, &m->g_dense_n, &m->g_ovf, &m->g_shards, &m->g_pos})
+      for (DevBuf* b : {&m->g_dense, &m->g_dense_n, &m->g_sparse, &m->g_ovf, &m->g_shards, &m->g_pos})
         if (b->p) cudaFree(b->p);
     }
     for (size_t i = 0; i < m->ev.size(); i++)
@@ -798,7 +816,7 @@ extern "C" int pb200_multi_eval_proto_columns(pb200_multi* m, const pb200_node* 
   if (n_shards == 0 || m->ctx.size() == 1) MFORWARD(m, m->ctx[0], pb200_eval_proto_columns(m->ctx[0], prog, n_nodes, shards, n_shards, out, cap, out_len));
   if (n_shards > (1u << 24)) return mfail(m, PB200_ERR_RANGE, "too many shards in one call");
   const uint64_t* shards_dev = nullptr;
-  TRY(gather_dense(m, prog, n_nodes, shards, n_shards, &shards_dev));
+  TRY(gather_dense(m, prog, n_nodes, shards, n_shards, &shards_dev, true));  // short containers travel as value lists
   pb200_ctx* c0 = m->ctx[0];
   std::lock_guard<std::mutex> lock(c0->mu);
   DeviceGuard g(c0->device);
