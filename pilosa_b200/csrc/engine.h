@@ -165,6 +165,7 @@ struct pb200_ctx {
   // fragment is freed, so that the peers' tables follow and no peer still reads the old copy
   std::function<int(uint32_t family, uint64_t shard, const pb200::FragDev& dev, bool all_bitmap, bool present)> publish;
   uint64_t generation = 0;  // bumped by every load / write / drop / table growth: prepared batches re-validate against it
+  pb200::DevBuf d_gb;            // GroupBy: group totals summed over the shards on the device
   pb200::DevBuf d_sparse;        // value lists of short result containers (K12 path, EvalParams::sparse_out)
   bool dense_lists = false;      // d_dense_n carries kSparseFlag entries backed by d_sparse
   pb200::DevBuf d_slow_descs, d_ovf, d_rest;  // d_rest: items eval_tiny_kernel leaves to eval_fast_kernel

@@ -87,7 +87,7 @@ struct GbWalk {
       if (!level_empty(i)) break;
     }
   }
-  bool next_group(pb200_group* out) {  // :3193-3230
+  bool next_group(pb200_group* out, uint64_t* dense_index = nullptr) {  // :3193-3230
     uint64_t count;
     for (;;) {
       if (done) return false;
@@ -98,6 +98,7 @@ struct GbWalk {
     *out = pb200_group{};
     for (uint32_t i = 0; i < t.k; i++) out->rows[i] = t.G[i][ids[i]];
     out->count = count;
+    if (dense_index) *dense_index = (t.k == 1 ? 0 : prefix_index()) * t.n_last() + ids[t.k - 1];  // groups in key order = index order
     next_at(t.k - 1);
     return true;
   }
@@ -149,10 +150,24 @@ std::vector<pb200_group> merge_group_counts(std::vector<pb200_group> a, const st
   return ret;
 }
 
+// sums[q * n_ids + j] = sum over the S shards of counts[(q * S + s) * n_ids + j]: the reduce of a GroupBy without a
+// limit or a `previous` bound, where every shard's walk emits exactly its non-zero counts (one thread per group)
+__global__ void gb_sum_kernel(const uint32_t* __restrict__ counts, uint32_t Q, uint32_t S, uint32_t n_ids, unsigned long long* __restrict__ sums) {
+  const uint64_t n = uint64_t(Q) * n_ids;
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += uint64_t(gridDim.x) * blockDim.x) {
+    const uint64_t q = i / n_ids, j = i % n_ids;
+    const uint32_t* c = counts + q * S * n_ids + j;
+    unsigned long long t = 0;
+    for (uint32_t s = 0; s < S; s++) t += c[uint64_t(s) * n_ids];
+    sums[i] = t;
+  }
+}
+
 // Runs the TopN count kernel for `n_virtual` (prefix, shard) source rows resident in d_dense against the
-// explicit id list `ids`; counts land in h_counts[v * n_ids + j].
+// explicit id list `ids`; counts land in h_counts[v * n_ids + j] — or, with d_sums, stay on the device and are summed
+// over the S shards of each of the n_virtual / S prefix tuples into d_sums[q * n_ids + j].
 int gb_count_against(pb200_ctx* ctx, pb200_family family, const uint64_t* virtual_shards, uint32_t n_virtual,
-                     const std::vector<uint64_t>& ids, uint32_t* h_counts) {
+                     const std::vector<uint64_t>& ids, uint32_t* h_counts, unsigned long long* d_sums = nullptr, uint32_t S = 0) {
   const size_t n_ids = ids.size();
   const size_t o_sh = 0, o_ids = size_t(n_virtual) * 8, total_bytes = o_ids + n_ids * 8;
   TRY(ensure_dev(ctx, ctx->d_topn, total_bytes));
@@ -185,6 +200,14 @@ int gb_count_against(pb200_ctx* ctx, pb200_family family, const uint64_t* virtua
   topn_count_kernel<<<grid, kTopnThreads, kTopnSmem, ctx->stream>>>(tp);
   ctx->timing.launches++;
   CUDA_TRY(ctx, cudaGetLastError());
+  if (d_sums) {
+    const uint32_t Q = n_virtual / S;
+    const uint64_t n = uint64_t(Q) * n_ids;
+    gb_sum_kernel<<<uint32_t(std::min<uint64_t>((n + 255) / 256, uint64_t(ctx->sm_count) * 8)), 256, 0, ctx->stream>>>(tp.counts, Q, S, uint32_t(n_ids), d_sums);
+    ctx->timing.launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return PB200_OK;
+  }
   TRY(ensure_pin(ctx, ctx->h_out, n_counts * 4));
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_out.p, tp.counts, n_counts * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
@@ -338,7 +361,21 @@ extern "C" int pb200_groupby(pb200_ctx* ctx, const pb200_groupby_child* children
     }
     const uint64_t n_last = t.G[k - 1].size();
     if (n_prefix * S * n_last > (1ull << 27)) return fail(ctx, PB200_ERR_RANGE, "GroupBy cross product too large (rows x shards > 2^27 counts)");
-    t.final_counts.assign(size_t(n_prefix * S * n_last), 0);
+    // Without a limit that can cut a shard's list and without a `previous` bound, the walk of a shard emits exactly its
+    // non-zero counts, and the reduce over the shards is a plain sum per group: that sum is taken on the device and only
+    // the group totals come back (no per-shard counts over PCIe, no host walk). (k == 1 without a filter has its counts
+    // on the host already.)
+    uint64_t n_groups_all = n_prefix * n_last;
+    bool any_prev = false;
+    for (uint32_t i = 0; i < k; i++) any_prev |= children[i].has_previous != 0;
+    const bool device_reduce = !any_prev && limit >= n_groups_all && (k >= 2 || has_filter) && n_groups_all <= (1ull << 24);
+    unsigned long long* d_sums = nullptr;
+    if (device_reduce) {
+      TRY(ensure_dev(ctx, ctx->d_gb, size_t(n_groups_all) * 8));
+      d_sums = static_cast<unsigned long long*>(ctx->d_gb.p);
+    } else {
+      t.final_counts.assign(size_t(n_prefix * S * n_last), 0);
+    }
     TRY(sync_families(ctx));
     const size_t row_bytes = size_t(kRowContainers) * kBitmapBytes;
 
@@ -352,7 +389,7 @@ extern "C" int pb200_groupby(pb200_ctx* ctx, const pb200_groupby_child* children
     }
     if (k == 1) {
       if (has_filter) {  // counts of filter & row: the filter rows are the sources
-        TRY(gb_count_against(ctx, children[0].family, live_shards.data(), S, t.G[0], t.final_counts.data()));
+        TRY(gb_count_against(ctx, children[0].family, live_shards.data(), S, t.G[0], device_reduce ? nullptr : t.final_counts.data(), d_sums, S));
       } else {           // Row.Count() of every present row: the loader already holds the exact cardinalities
         for (uint32_t v = 0; v < S; v++) {
           const Fragment& f = ctx->families[children[0].family].frags.find(live_shards[v])->second;
@@ -363,7 +400,7 @@ extern "C" int pb200_groupby(pb200_ctx* ctx, const pb200_groupby_child* children
         }
       }
     } else {
-      t.prefix_counts.assign(size_t(n_prefix * S), 0);
+      if (!device_reduce) t.prefix_counts.assign(size_t(n_prefix * S), 0);
       // prefix tuples in chunks of at most 8192 dense rows (1 GiB)
       const uint64_t q_per_chunk = std::max<uint64_t>(1, 8192 / S);
       std::vector<pb200_node> nodes;
@@ -395,20 +432,44 @@ extern "C" int pb200_groupby(pb200_ctx* ctx, const pb200_groupby_child* children
         TRY(ensure_dev(ctx, ctx->d_dense_n, n_dense * kRowContainers * 4));
         TRY(launch_eval(ctx, bd, bd.progs, Q, S, true, nullptr, 0, 0, static_cast<uint8_t*>(ctx->d_dense.p),
                         static_cast<uint32_t*>(ctx->d_dense_n.p), max_leaves_of(cp)));
-        TRY(gb_dense_row_counts(ctx, uint32_t(n_dense), t.prefix_counts.data() + size_t(q0) * S));
+        if (!device_reduce) TRY(gb_dense_row_counts(ctx, uint32_t(n_dense), t.prefix_counts.data() + size_t(q0) * S));
         vshards.resize(n_dense);
         for (uint32_t qi = 0; qi < Q; qi++)
           for (uint32_t v = 0; v < S; v++) vshards[size_t(qi) * S + v] = live_shards[v];
         TRY(gb_count_against(ctx, children[k - 1].family, vshards.data(), uint32_t(n_dense), t.G[k - 1],
-                             t.final_counts.data() + size_t(q0) * S * n_last));
+                             device_reduce ? nullptr : t.final_counts.data() + size_t(q0) * S * n_last, d_sums ? d_sums + size_t(q0) * n_last : nullptr, S));
       }
     }
     ctx->dense_shards_dev = nullptr;  // d_dense no longer holds a TopN source
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    std::vector<unsigned long long> h_sums;
+    if (device_reduce) {
+      h_sums.resize(size_t(n_groups_all));
+      CUDA_TRY(ctx, cudaMemcpyAsync(h_sums.data(), d_sums, h_sums.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+      ctx->timing.d2h_bytes += h_sums.size() * 8;
+    }
     TRY(finish_call(ctx));
+    if (device_reduce) {
+      for (uint64_t gi = 0; gi < n_groups_all; gi++) {  // key order = index order
+        if (!h_sums[size_t(gi)]) continue;
+        pb200_group g{};
+        uint64_t rem = gi;
+        for (int i = int(k) - 1; i >= 0; i--) { g.rows[i] = t.G[i][size_t(rem % t.G[i].size())]; rem /= t.G[i].size(); }
+        g.count = h_sums[size_t(gi)];
+        acc.push_back(g);
+      }
+    } else {
 
-    // per-shard walks, then the reduce in shard-list order
-    std::vector<std::vector<pb200_group>> per(S);
+    // per-shard walks, then the reduce. mergeGroupCounts (:1166-1200) is a sorted union with summed counts, cut to `limit`:
+    // what survives the reference's left fold over the shards are the `limit` smallest keys with the sums of everything
+    // the shards' walks emitted for them (a surviving key is never cut on the way). The keys are positions in the
+    // cross product of the sorted candidate lists, so the sums go into one dense array in index order; the pairwise
+    // merges remain for cross products too large for that.
+    uint64_t n_groups = 1;
+    for (uint32_t i = 0; i < k; i++) n_groups *= t.G[i].size();
+    const bool dense_reduce = n_groups <= (1ull << 22);
+    std::vector<std::vector<pb200_group>> per(dense_reduce ? 0 : S);
+    std::vector<std::vector<std::pair<uint64_t, uint64_t>>> per_idx(dense_reduce ? S : 0);  // (group index, count)
     parallel_shards(S, [&](uint32_t v) {
       GbWalk w(t, v);
       for (uint32_t i = 0; i < k; i++) {
@@ -418,9 +479,27 @@ extern "C" int pb200_groupby(pb200_ctx* ctx, const pb200_groupby_child* children
       }
       w.init(children);
       pb200_group g;
-      while (per[v].size() < limit && w.next_group(&g)) per[v].push_back(g);  // executeGroupByShard :1262-1274
+      uint64_t gi = 0;
+      if (dense_reduce) { while (per_idx[v].size() < limit && w.next_group(&g, &gi)) per_idx[v].push_back({gi, g.count}); }
+      else { while (per[v].size() < limit && w.next_group(&g)) per[v].push_back(g); }  // executeGroupByShard :1262-1274
     });
-    for (uint32_t v = 0; v < S; v++) acc = merge_group_counts(std::move(acc), per[v], limit, k);
+    if (dense_reduce) {
+      std::vector<uint64_t> sum(size_t(n_groups), 0);
+      std::vector<uint8_t> seen(size_t(n_groups), 0);
+      for (uint32_t v = 0; v < S; v++)
+        for (auto& e : per_idx[v]) { sum[size_t(e.first)] += e.second; seen[size_t(e.first)] = 1; }
+      for (uint64_t gi = 0; gi < n_groups && acc.size() < limit; gi++) {
+        if (!seen[size_t(gi)]) continue;
+        pb200_group g{};
+        uint64_t rem = gi;
+        for (int i = int(k) - 1; i >= 0; i--) { g.rows[i] = t.G[i][size_t(rem % t.G[i].size())]; rem /= t.G[i].size(); }
+        g.count = sum[size_t(gi)];
+        acc.push_back(g);
+      }
+    } else {
+      for (uint32_t v = 0; v < S; v++) acc = merge_group_counts(std::move(acc), per[v], limit, k);
+    }
+    }
   } else {
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     TRY(finish_call(ctx));
