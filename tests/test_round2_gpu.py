@@ -550,3 +550,77 @@ def test_proto_columns_of_short_containers_as_value_lists(eng_orc):
         assert g.row_proto_columns(call, shards) == c.be.eval_proto_columns(c.program(call), shards), repr(call)
         assert g.row_proto_columns(call, shards[1:2]) == c.be.eval_proto_columns(c.program(call), shards[1:2]), repr(call)
         assert g.row_columns(call, shards) == c.row_columns(call, shards), repr(call)
+
+
+def test_fold_kernel_random_clustered_containers(eng_orc):
+    """Randomised stress of the fold evaluator's slice ownership and run fill: containers whose values cluster inside
+    single words and straddle slice borders (8 values / 4 runs per thread), in all three encodings, folded with all
+    four operations over 2..5 operands; every count against Python sets (and the oracle on a sample)."""
+    import random
+
+    from pilosa_b200.abi import Difference, Union, Xor
+
+    eng, orc = eng_orc
+    g, c = Executor(eng), Executor(orc)
+    rnd = random.Random(20261107)
+
+    def clustered(n_clusters, max_len, step_choices):
+        vals, pos = set(), 0
+        for _ in range(n_clusters):
+            pos += rnd.choice(step_choices)
+            ln = rnd.randint(1, max_len)
+            for k in range(ln):
+                if pos + k < 65536 and rnd.random() < 0.8:
+                    vals.add(pos + k)
+            pos += ln
+            if pos >= 65536:
+                break
+        return sorted(vals)
+
+    n_rows, cols = 48, (0, 7, 15)
+    sets, cs = {}, []
+    for row in range(n_rows):
+        for col in cols:
+            kind = rnd.choice("aarrb")
+            if kind == "a":
+                vals = clustered(rnd.randint(1, 500), rnd.choice((3, 9, 40)), (1, 2, 5, 31, 33, 64, 300))[:4096]
+            elif kind == "r":
+                vals = clustered(rnd.randint(1, 1500), rnd.choice((2, 6, 70, 400)), (2, 3, 7, 32, 65, 500))
+            else:
+                vals = sorted(rnd.sample(range(65536), rnd.randint(4097, 40000)))
+            if not vals:
+                vals = [rnd.randrange(65536)]
+            if kind == "r":   # keep the run encoding legal: at most 2048 runs
+                runs = 1 + sum(1 for i in range(1, len(vals)) if vals[i] != vals[i - 1] + 1)
+                if runs > 2048:
+                    kind = "a" if len(vals) <= 4096 else "b"
+            if kind == "a" and len(vals) > 4096:
+                kind = "b"
+            t, n, pl = _cont(kind, vals)
+            cs.append((row * 16 + col, t, n, pl))
+            sets[(row, col)] = set(vals)
+    data = pilosa_file(sorted(cs))
+    for ex in (g, c):
+        ex.create_field("k")
+        ex.load_fragment("k", 0, data)
+    ops = [(Intersect, lambda a, b: a & b), (Union, lambda a, b: a | b), (Xor, lambda a, b: a ^ b), (Difference, lambda a, b: a - b)]
+    calls, want = [], []
+    for _ in range(600):
+        op, f = rnd.choice(ops)
+        rows = [rnd.randrange(n_rows) for _ in range(rnd.randint(2, 5))]
+        calls.append(op(*[Row("k", r) for r in rows]))
+        tot = 0
+        for col in cols:
+            acc = set(sets[(rows[0], col)])
+            for r in rows[1:]:
+                acc = f(acc, sets[(r, col)])
+            tot += len(acc)
+        want.append(tot)
+    got = []
+    for k in range(0, len(calls), 200):
+        got += g.count_batch(calls[k:k + 200], [0])
+    bad = [(repr(calls[i]), got[i], want[i]) for i in range(len(calls)) if got[i] != want[i]]
+    assert not bad, bad[:3]
+    for i in range(0, len(calls), 37):
+        assert c.count(calls[i], [0]) == want[i]
+        assert g.row_columns(calls[i], [0]) == c.row_columns(calls[i], [0])
