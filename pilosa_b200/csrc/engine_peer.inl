@@ -183,6 +183,7 @@ extern "C" int pb200_reserve(pb200_ctx* ctx, uint32_t max_queries, uint32_t max_
   const size_t batch_bytes = 2 * size_t(max_queries) * (sizeof(Prog) + size_t(nodes) * (sizeof(Leaf) + sizeof(Instr))) + size_t(max_shards) * 8 + 256;
   TRY(ensure_dev(ctx, ctx->d_misc, 64));
   TRY(ensure_dev(ctx, ctx->d_slow, size_t(n_items) * 4));
+  TRY(ensure_dev(ctx, ctx->d_rest, size_t(n_items) * 4));  // the lane-per-item pass's hand-over list (very sparse rows)
   const uint64_t desc_bytes = n_items * uint64_t(leaves) * sizeof(ContainerDesc);
   if (desc_bytes <= (256ull << 20)) TRY(ensure_dev(ctx, ctx->d_slow_descs, size_t(desc_bytes)));
   TRY(ensure_dev(ctx, ctx->d_batch, batch_bytes));
