@@ -65,7 +65,7 @@ def main():
             walls.append((time.perf_counter() - t0) * 1e3)
             kern.append(eng.last_timing().kernel_ms)
         print(json.dumps({"config": config, "query": name, "n_gpus": n, "shards": len(shards), "call_ms": round(statistics.median(walls), 4),
-                          "call_ms_min": round(min(walls), 4), "kernel_ms_slowest_device": round(statistics.median(kern), 4), "result": show(res)}), flush=True)
+                          "call_ms_min": round(min(walls), 4), "call_ms_max": round(max(walls), 4), "kernel_ms_slowest_device": round(statistics.median(kern), 4), "result": show(res)}), flush=True)
 
     def counter(call, shards):
         """One raw pb200_multi_count call with everything marshalled beforehand."""
