@@ -15,6 +15,14 @@
 #include <thread>
 
 #include "kernels.cuh"
+// A measured alternative to eval_fold_kernel for count-only launches (consumer warps that share no barrier): fewer stalls,
+// twice the instructions, 0.34 vs 0.26 ms on the mixed-container config. Built only with -DPB200_FOLDW=1.
+#ifndef PB200_FOLDW
+#define PB200_FOLDW 0
+#endif
+#if PB200_FOLDW
+#include "kernels_foldw.cuh"
+#endif
 #include "kernels_bsi.cuh"
 #include "kernels_topn.cuh"
 #include "kernels_rows.cuh"
@@ -181,6 +189,9 @@ extern "C" int pb200_init(int device, size_t hbm_budget_bytes, pb200_ctx** out) 
   ctx->sm_count = prop.multiProcessorCount;
   // the fold evaluator's window + scratch + staging ring may exceed the 48 KiB a kernel gets without asking
   if (cudaFuncSetAttribute(eval_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFoldSmem) != cudaSuccess) { delete ctx; return PB200_ERR_CUDA; }
+#if PB200_FOLDW
+  if (cudaFuncSetAttribute(eval_foldw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFoldSmem) != cudaSuccess) { delete ctx; return PB200_ERR_CUDA; }
+#endif
   if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
     delete ctx;
@@ -951,7 +962,7 @@ uint32_t resident_ctas(pb200_ctx* ctx, int slot, K kernel, int block, size_t dyn
   }
   return uint32_t(ctx->sm_count) * uint32_t(ctx->occ[slot]);
 }
-enum { OCC_FAST = 0, OCC_STAGED, OCC_SUM, OCC_MM, OCC_TOPN, OCC_FOLD, OCC_TINY };
+enum { OCC_FAST = 0, OCC_STAGED, OCC_SUM, OCC_MM, OCC_TOPN, OCC_FOLD, OCC_TINY, OCC_FOLDW };
 
 // Launches the fast + staged kernels for `n_queries` programs starting at `progs`.
 int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t n_queries, uint32_t n_shards, bool staging,
@@ -1014,8 +1025,16 @@ int launch_eval(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint32_t 
   }
   if (staging) {  // deferred items: flat left folds go to the fold kernel, anything else to the general staged evaluator
     if (flat) {
-      const uint32_t fgrid = uint32_t(std::min<uint64_t>(n_items, resident_ctas(ctx, OCC_FOLD, eval_fold_kernel, kFoldCtaThreads, kFoldSmem)));
-      eval_fold_kernel<<<fgrid, kFoldCtaThreads, kFoldSmem, ctx->stream>>>(p);
+#if PB200_FOLDW
+      if (!dense_out && !dense_n) {  // counts only: the consumers need no barrier among themselves (kernels_foldw.cuh)
+        const uint32_t fgrid = uint32_t(std::min<uint64_t>(n_items, resident_ctas(ctx, OCC_FOLDW, eval_foldw_kernel, kFoldCtaThreads, kFoldSmem)));
+        eval_foldw_kernel<<<fgrid, kFoldCtaThreads, kFoldSmem, ctx->stream>>>(p);
+      } else
+#endif
+      {
+        const uint32_t fgrid = uint32_t(std::min<uint64_t>(n_items, resident_ctas(ctx, OCC_FOLD, eval_fold_kernel, kFoldCtaThreads, kFoldSmem)));
+        eval_fold_kernel<<<fgrid, kFoldCtaThreads, kFoldSmem, ctx->stream>>>(p);
+      }
       ctx->timing.launches++;
     }
     if (bushy) {

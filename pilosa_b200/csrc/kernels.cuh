@@ -1080,27 +1080,10 @@ struct FoldMeta {  // one deferred item, resolved by the producer warp
   ContainerDesc desc[kMaxLeaves];
 };
 
-// Warp-specialised: warp 8 is the PRODUCER — it walks the CTA's items one ahead of the consumers, resolves their
-// descriptors into a two-deep ring (meta_full / meta_empty mbarriers) and keeps the copy engine busy: every operand
-// payload is one cp.async.bulk into the next free slot of a kFoldStages-deep staging ring (full / empty mbarriers),
-// issued as soon as the slot is released, whatever item it belongs to. Warps 0-7 are the CONSUMERS: they never wait
-// for global memory except on a cold pipeline, only for `full`, and synchronise among themselves with a named barrier.
-__global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_kernel(EvalParams p) {
-  extern __shared__ __align__(128) uint8_t s_dyn[];  // [window][S][E][kFoldStages x staging], 8 KiB each
-  __shared__ FoldMeta s_meta[kFoldMeta];
-  __shared__ uint32_t s_red[kFoldThreads / 32], s_red2[kFoldThreads / 32];
-  __shared__ __align__(8) uint64_t s_full[kFoldStages], s_empty[kFoldStages], s_mfull[kFoldMeta], s_mempty[kFoldMeta];
-  const int tid = threadIdx.x, lane = tid & 31;
-  const uint32_t n_slow = p.fold_all ? p.n_queries * p.n_shards * kRowContainers : *p.slow_count;
-  if (tid == 0) {
-    for (int i = 0; i < kFoldStages; i++) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 1); }
-    for (int i = 0; i < kFoldMeta; i++) { mbar_init(&s_mfull[i], 1); mbar_init(&s_mempty[i], 1); }
-    mbar_fence_init();
-  }
-  __syncthreads();
-
-  if (tid >= kFoldThreads) {
-    // ---------------- producer warp ----------------
+// The producer warp of the fold evaluators (see eval_fold_kernel): walks the CTA's items one ahead of the consumers,
+// resolves their descriptors into the meta ring and keeps the copy engine busy.
+__device__ __forceinline__ void fold_producer(const EvalParams& p, uint32_t n_slow, int lane, uint8_t* s_dyn, FoldMeta* s_meta,
+                                              uint64_t* s_full, uint64_t* s_empty, uint64_t* s_mfull, uint64_t* s_mempty) {
     uint32_t g = 0;  // payload loads issued so far (lane 0)
     uint32_t j = 0;  // items handled so far
     unsigned long long bytes_acc = 0;
@@ -1152,6 +1135,29 @@ __global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_ke
       __syncwarp();
     }
     if (lane == 0 && bytes_acc && p.algo_bytes) atomicAdd(p.algo_bytes, bytes_acc);
+}
+
+// Warp-specialised: warp 8 is the PRODUCER — it walks the CTA's items one ahead of the consumers, resolves their
+// descriptors into a two-deep ring (meta_full / meta_empty mbarriers) and keeps the copy engine busy: every operand
+// payload is one cp.async.bulk into the next free slot of a kFoldStages-deep staging ring (full / empty mbarriers),
+// issued as soon as the slot is released, whatever item it belongs to. Warps 0-7 are the CONSUMERS: they never wait
+// for global memory except on a cold pipeline, only for `full`, and synchronise among themselves with a named barrier.
+__global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_kernel(EvalParams p) {
+  extern __shared__ __align__(128) uint8_t s_dyn[];  // [window][S][E][kFoldStages x staging], 8 KiB each
+  __shared__ FoldMeta s_meta[kFoldMeta];
+  __shared__ uint32_t s_red[kFoldThreads / 32], s_red2[kFoldThreads / 32];
+  __shared__ __align__(8) uint64_t s_full[kFoldStages], s_empty[kFoldStages], s_mfull[kFoldMeta], s_mempty[kFoldMeta];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const uint32_t n_slow = p.fold_all ? p.n_queries * p.n_shards * kRowContainers : *p.slow_count;
+  if (tid == 0) {
+    for (int i = 0; i < kFoldStages; i++) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 1); }
+    for (int i = 0; i < kFoldMeta; i++) { mbar_init(&s_mfull[i], 1); mbar_init(&s_mempty[i], 1); }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (tid >= kFoldThreads) {
+    fold_producer(p, n_slow, lane, s_dyn, s_meta, s_full, s_empty, s_mfull, s_mempty);  // ---------------- producer warp ----------------
     return;
   }
 
