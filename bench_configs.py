@@ -208,6 +208,13 @@ def main():
             got = g.count(call, cpu_sh)
             exp, cms = cpu_timed(lambda: c.count(call, cpu_sh))
             emit(rows, "C3", f"Count(Union(Row(z={lo}) .. Row(z={hi - 1}))) [{hi - lo} operands]", len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
+        # ... Xor / Intersect of more than 32 rows: chunks of 32 folded into dense temp rows by the fold evaluator, then combined
+        for opname, op, lo, hi in (("Xor", Xor, 0, 100), ("Intersect", Intersect, 0, 100), ("Xor", Xor, 1000, 1400)):
+            call = op(*[Row("z", r) for r in range(lo, hi)])
+            _, k, wms, ab, ln = timed(eng, lambda: g.count(call, shards), max(3, args.reps // 2))
+            got = g.count(call, cpu_sh)
+            exp, cms = cpu_timed(lambda: c.count(call, cpu_sh))
+            emit(rows, "C3", f"Count({opname}(Row(z={lo}) .. Row(z={hi - 1}))) [{hi - lo} operands]", len(shards), k, wms, ab, ln, cms, len(cpu_sh), got == exp)
         wide = Union(*[Row("z", r) for r in range(0, 64)])
         prop(rows, "C3", "Count(Union of 64 rows) = sum over inclusion-exclusion halves: |A u B| = |A| + |B| - |A n B|",
              g.count(wide, shards) == g.count(Union(*[Row("z", r) for r in range(32)]), shards) + g.count(Union(*[Row("z", r) for r in range(32, 64)]), shards)

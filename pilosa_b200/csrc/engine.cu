@@ -798,15 +798,17 @@ struct Compiler {
     st.resize(st.size() - m);
     const uint8_t lop = nd.op == PB200_OP_INTERSECT ? I_AND_LEAF : nd.op == PB200_OP_XOR ? I_XOR_LEAF : I_OR_LEAF;
     std::vector<int> temps;
-    if (lop == I_OR_LEAF) {  // a Union of rows is one accumulating pass whatever its width (union_rows_kernel)
+    const bool one_pass = lop == I_OR_LEAF || lop == I_XOR_LEAF;  // OR and XOR commute and need no operand kept apart
+    if (one_pass) {  // a Union (Xor) of rows is one accumulating pass whatever its width (union_rows_kernel)
       Compiled::PreTask ev; ev.kind = 2; ev.slot = out.n_temp_slots++;
       ev.prog.instr_off = uint32_t(out.instrs.size()); ev.prog.n_instr = 0;
       ev.prog.leaf_off = wide_base; ev.prog.n_leaves = m;
       ev.union_rows = true;
+      ev.xor_rows = lop == I_XOR_LEAF;
       out.pre.push_back(ev);
       temps.push_back(leaf_node(add_leaf(L_TEMP, ev.slot, 0)));
     }
-    for (uint32_t b = 0; lop != I_OR_LEAF && b < m; b += uint32_t(kMaxLeaves)) {
+    for (uint32_t b = 0; !one_pass && b < m; b += uint32_t(kMaxLeaves)) {
       const uint32_t cnt = std::min<uint32_t>(uint32_t(kMaxLeaves), m - b);
       Compiled::PreTask ev; ev.kind = 2; ev.slot = out.n_temp_slots++;
       ev.prog.instr_off = uint32_t(out.instrs.size()); ev.prog.n_instr = cnt;

@@ -85,6 +85,7 @@ struct Compiled {
     uint32_t slot = 0, src_slot = 0;
     Prog prog{};          // kind 2: sub-program (offsets into instrs / leaves)
     bool union_rows = false;              // kind 2 that is a plain Union of Row leaves: one accumulating pass (K13)
+    bool xor_rows = false;                // ... or a plain Xor of Row leaves: the same pass, flipping instead of setting
     bool count_only = false;              // kind 0 feeding a bare Count(): count in the comparator kernel
     unsigned long long* count_out = nullptr;
     uint32_t count_sstride = 0;

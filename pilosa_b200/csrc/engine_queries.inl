@@ -78,7 +78,7 @@ int launch_overflow(pb200_ctx* ctx, const BatchDev& bd, const Prog* progs, uint3
 }
 
 // K13: one chunk of a wide Union (plain Row leaves only) into a dense temp row.
-int launch_union_rows(pb200_ctx* ctx, const BatchDev& bd, const Prog* prog, uint32_t n_shards, uint8_t* dense_out) {
+int launch_union_rows(pb200_ctx* ctx, const BatchDev& bd, const Prog* prog, uint32_t n_shards, uint8_t* dense_out, bool xor_rows = false) {
   const uint64_t n_items = uint64_t(n_shards) * kRowContainers;
   if (n_items == 0) return PB200_OK;
   TRY(ensure_dev(ctx, ctx->d_misc, 64));
@@ -91,7 +91,8 @@ int launch_union_rows(pb200_ctx* ctx, const BatchDev& bd, const Prog* prog, uint
   p.dense_out = dense_out;
   p.algo_bytes = algo_ptr(ctx);
   const uint32_t grid = uint32_t(std::min<uint64_t>(n_items, uint64_t(ctx->sm_count) * 8));
-  union_rows_kernel<<<grid, kUnionThreads, 0, ctx->stream>>>(p);
+  if (xor_rows) union_rows_kernel<true><<<grid, kUnionThreads, 0, ctx->stream>>>(p);
+  else union_rows_kernel<false><<<grid, kUnionThreads, 0, ctx->stream>>>(p);
   ctx->timing.launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   return PB200_OK;
@@ -111,7 +112,7 @@ int run_pretasks(pb200_ctx* ctx, const Compiled& cp, const BatchDev& bd, uint32_
       else
         TRY(launch_bsi_range(ctx, bd, pt.node, n_shards, temp_slot(ctx, pt.slot, n_shards)));
     } else if (pt.kind == 2) {
-      if (pt.union_rows) TRY(launch_union_rows(ctx, bd, bd.progs + cp.progs.size() + i, n_shards, temp_slot(ctx, pt.slot, n_shards)));
+      if (pt.union_rows) TRY(launch_union_rows(ctx, bd, bd.progs + cp.progs.size() + i, n_shards, temp_slot(ctx, pt.slot, n_shards), pt.xor_rows));
       else TRY(launch_eval(ctx, bd, bd.progs + cp.progs.size() + i, 1, n_shards, true, nullptr, 0, 0, temp_slot(ctx, pt.slot, n_shards), nullptr));
       if (has_shift(cp) && !pt.union_rows)  // plain rows carry no overflow: the slot's word stays zero
         TRY(launch_overflow(ctx, bd, bd.progs + cp.progs.size() + i, 1, n_shards, nullptr, 0, 0, ovf_slot(ctx, pt.slot, n_shards)));

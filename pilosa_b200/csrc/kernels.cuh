@@ -653,6 +653,9 @@ __global__ void __launch_bounds__(256) eval_tiny_kernel(EvalParams p) {
 // every 3x3 type pair and every op of roaring.go:3078-4957 is the same word-parallel
 // boolean function. The whole CTA cooperates; the window must be pre-zeroed.
 // ---------------------------------------------------------------------------------------
+// XOR: the container's bits are flipped in the window instead of set (the window need not be zero; operands staged by
+// different warps at the same time commute).
+template <bool XOR = false>
 __device__ __forceinline__ void stage_container(const ContainerDesc& d, uint32_t* win32, uint32_t w0, uint32_t nwords,
                                                 int tid, int nthreads) {
   const uint32_t lo = w0 * 64, hi = (w0 + nwords) * 64;  // value range [lo, hi)
@@ -689,13 +692,13 @@ __device__ __forceinline__ void stage_container(const ContainerDesc& d, uint32_t
         if (k < int(m)) {
           const uint32_t v = vals[k] - lo, w = v >> 5;
           if (w != cur_w) {
-            if (cur_w != 0xffffffffu) atomicOr(&win32[cur_w], cur_bits);
+            if (cur_w != 0xffffffffu) { if (XOR) atomicXor(&win32[cur_w], cur_bits); else atomicOr(&win32[cur_w], cur_bits); }
             cur_w = w; cur_bits = 0;
           }
           cur_bits |= 1u << (v & 31);
         }
       }
-      if (cur_w != 0xffffffffu) atomicOr(&win32[cur_w], cur_bits);
+      if (cur_w != 0xffffffffu) { if (XOR) atomicXor(&win32[cur_w], cur_bits); else atomicOr(&win32[cur_w], cur_bits); }
     }
   } else if (type == kRun) {
     const ushort2* r = reinterpret_cast<const ushort2*>(d.addr);
@@ -727,17 +730,18 @@ __device__ __forceinline__ void stage_container(const ContainerDesc& d, uint32_t
         s -= lo; l -= lo;
         ws = s >> 5; we = l >> 5;
         const uint32_t ms = ~0u << (s & 31), me = ~0u >> (31 - (l & 31));
-        if (ws == we) atomicOr(&win32[ws], ms & me);
+        if (XOR) { if (ws == we) atomicXor(&win32[ws], ms & me); else { atomicXor(&win32[ws], ms); atomicXor(&win32[we], me); } }
+        else if (ws == we) atomicOr(&win32[ws], ms & me);
         else { atomicOr(&win32[ws], ms); atomicOr(&win32[we], me); }
       }
       const bool long_run = we > ws + 1 + 16;  // short interiors: by the owning thread; long ones: by the warp
-      if (!long_run) for (uint32_t k = ws + 1; k < we; k++) win32[k] = ~0u;
+      if (!long_run) for (uint32_t k = ws + 1; k < we; k++) win32[k] = XOR ? ~win32[k] : ~0u;
       uint32_t todo = __ballot_sync(0xffffffffu, long_run);
       while (todo) {
         const int src = __ffs(todo) - 1;
         todo &= todo - 1;
         const uint32_t k0 = __shfl_sync(0xffffffffu, ws, src) + 1, k1 = __shfl_sync(0xffffffffu, we, src);
-        for (uint32_t k = k0 + lane; k < k1; k += 32) win32[k] = ~0u;
+        for (uint32_t k = k0 + lane; k < k1; k += 32) win32[k] = XOR ? ~win32[k] : ~0u;
       }
     }
   }
@@ -1332,6 +1336,7 @@ __global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_ke
 // ---------------------------------------------------------------------------------------
 constexpr int kUnionThreads = 256;
 
+template <bool XOR>
 __global__ void __launch_bounds__(kUnionThreads) union_rows_kernel(EvalParams p) {
   __shared__ __align__(16) uint32_t s_win[kBitmapWords * 2];
   __shared__ ContainerDesc s_desc[kUnionThreads];  // a batch of operands: one descriptor lookup per thread
@@ -1356,7 +1361,7 @@ __global__ void __launch_bounds__(kUnionThreads) union_rows_kernel(EvalParams p)
       // instead of one; their expansion uses shared-memory atomicOr only, so operands may overlap freely
       for (uint32_t l = warp; l < nl; l += kUnionThreads / 32) {
         const ContainerDesc d = s_desc[l];
-        if (d.n && desc_type(d) == kArray) stage_container(d, s_win, 0, kBitmapWords, lane, 32);
+        if (d.n && desc_type(d) == kArray) stage_container<XOR>(d, s_win, 0, kBitmapWords, lane, 32);
       }
       __syncthreads();
       for (uint32_t l = 0; l < nl; l++) {  // bitmaps and runs: the whole CTA on one operand
@@ -1364,9 +1369,9 @@ __global__ void __launch_bounds__(kUnionThreads) union_rows_kernel(EvalParams p)
         if (d.n == 0 || desc_type(d) == kArray) continue;  // uniform over the CTA
         if (desc_type(d) == kBitmap) {  // every thread owns the same words for every bitmap operand
           const uint4* src = reinterpret_cast<const uint4*>(d.addr);
-          for (int j = tid; j < kBitmapWords / 2; j += kUnionThreads) win4[j] = or128(win4[j], ldg128_stream(src + j));
+          for (int j = tid; j < kBitmapWords / 2; j += kUnionThreads) win4[j] = XOR ? xor128(win4[j], ldg128_stream(src + j)) : or128(win4[j], ldg128_stream(src + j));
         } else {
-          stage_container(d, s_win, 0, kBitmapWords, tid, kUnionThreads);
+          stage_container<XOR>(d, s_win, 0, kBitmapWords, tid, kUnionThreads);
         }
         __syncthreads();  // plain stores of this operand before the atomics / read-modify-writes of the next one
       }
