@@ -1123,6 +1123,13 @@ __device__ __forceinline__ void fold_producer(const EvalParams& p, uint32_t n_sl
         m.item = item; m.q = q; m.s = sidx; m.n_instr = pg.n_instr; m.take = take ? 1u : 0u;
         // Count(Row): the cardinality is in the descriptor (roaring.go:405 Count = sum of n); temps carry none
         if (take && pg.n_instr == 1 && !p.dense_out && p.leaves[pg.leaf_off + m.ins[0].leaf].kind != L_TEMP) { m.take = 2u; take = false; }
+        // A pure intersection with an empty operand is empty (roaring.go:3079-3087 per pair; Row.Intersect over no
+        // container): when only counts are wanted nothing of the item has to be loaded. take = 3: the consumers skip it.
+        if (take && pg.n_instr > 1 && !p.dense_out && !p.dense_n) {
+          bool pure_and = true, any_nil = m.desc[m.ins[0].leaf].n == 0;
+          for (uint32_t k = 1; k < pg.n_instr; k++) { pure_and &= m.ins[k].op == I_AND_LEAF; any_nil |= m.desc[m.ins[k].leaf].n == 0; }
+          if (pure_and && any_nil) { m.take = 3u; take = false; }
+        }
         mbar_arrive(&s_mfull[ms]);  // (release) the item's descriptors are published
         if (take)
           for (uint32_t k = 0; k < pg.n_instr; k++) {
@@ -1192,7 +1199,7 @@ __global__ void __launch_bounds__(kFoldCtaThreads, PB200_FOLD_CTAS) eval_fold_ke
     mbar_wait(&s_mfull[ms], (j / kFoldMeta) & 1u);
     const FoldMeta& m = s_meta[ms];
     const uint32_t n_instr = m.n_instr;
-    if (m.take != 1u) {  // 0: not a flat fold, eval_staged_kernel handles it; 2: Count(Row) straight from the descriptor
+    if (m.take != 1u) {  // 0: not a flat fold, eval_staged_kernel handles it; 2: Count(Row) straight from the descriptor; 3: empty intersection
       if (tid < 32 && m.take == 2u && p.out_counts)
         add_count(uint64_t(m.q) * p.out_qstride + uint64_t(m.s) * p.out_sstride, m.desc[m.ins[0].leaf].n);
       fold_bar();
