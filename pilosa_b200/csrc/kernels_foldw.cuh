@@ -1,4 +1,7 @@
-// K2-K6, fold form without a barrier among the consumers (count-only launches).
+// K2-K6, fold form without a barrier among the consumers (count-only launches). NOT BUILT BY DEFAULT: parity-green, but
+// measured slower than eval_fold_kernel on the mixed-container config (0.34 vs 0.26 ms: no barrier stall, 72 % issue
+// utilisation, but twice the instructions — every warp pays the border search and the partly filled chunks of every
+// operand). Kept as the measured alternative; engine.cu includes it only with -DPB200_FOLDW=1.
 //
 // eval_fold_kernel's eight consumer warps apply every operand together and meet at a named barrier after it (three
 // times for a run list): ncu attributes 29 % of its stall samples to that barrier and the issue slots are busy 53 % of
