@@ -51,14 +51,18 @@ struct ShardSplit {
   std::vector<std::vector<uint32_t>> pos;     // position of each in the caller's list
 };
 
-ShardSplit split_shards(const pb200_multi* m, const uint64_t* shards, uint32_t n) {
+ShardSplit split_shards(const pb200_multi* m, const uint64_t* shards, uint32_t n, bool want_pos = true) {
   const size_t nd = m->ctx.size();
   ShardSplit sp;
   sp.shards.resize(nd); sp.pos.resize(nd);
+  for (size_t d = 0; d < nd; d++) {  // (a call over thousands of shards should not pay for vector growth: this is on every query's path)
+    sp.shards[d].reserve(n / nd + 8);
+    if (want_pos) sp.pos[d].reserve(n / nd + 8);
+  }
   for (uint32_t i = 0; i < n; i++) {
     const size_t d = size_t(shards[i] % nd);
     sp.shards[d].push_back(shards[i]);
-    sp.pos[d].push_back(i);
+    if (want_pos) sp.pos[d].push_back(i);
   }
   return sp;
 }
@@ -188,7 +192,7 @@ int count_batch_multi(pb200_multi* m, const pb200_node* progs, const uint32_t* p
     m->timing = m->ctx[one]->timing;
     return rc;
   }
-  const ShardSplit sp = split_shards(m, shards, n_shards);
+  const ShardSplit sp = split_shards(m, shards, n_shards, false);
   const std::vector<uint8_t> active = active_of(sp);
   std::vector<std::vector<uint64_t>> part(m->ctx.size());
   TRY(fan_out(m, active, [&](size_t d) {
